@@ -1,0 +1,190 @@
+/* TEST INFRASTRUCTURE — CPU oracle (see cv_primitives.h). Restates OpenCV 4.13.0 arithmetic;
+ * pinned bit-for-bit against the cv2 4.13.0 wheel by tests/test_oracle_cv.py.
+ * Build with -ffp-contract=off: every float op below must round separately (no FMA). */
+#include "cv_primitives.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+extern "C" {
+
+int ocv_round_f(float v) { return (int)lrintf(v); }
+int ocv_round_d(double v) { return (int)lrint(v); }
+
+/* OpenCV modules/core/src/mathfuncs_core.simd.hpp atan_f32(): p1..p7 scaled to degrees. */
+float ocv_fast_atan2(float y, float x) {
+    static const float p1 = 0.9997878412794807f * (float)(180 / 3.14159265358979323846);
+    static const float p3 = -0.3258083974640975f * (float)(180 / 3.14159265358979323846);
+    static const float p5 = 0.1555786518463281f * (float)(180 / 3.14159265358979323846);
+    static const float p7 = -0.04432655554792128f * (float)(180 / 3.14159265358979323846);
+    float ax = std::fabs(x), ay = std::fabs(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = ay / (ax + (float)DBL_EPSILON);
+        c2 = c * c;
+        a = (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * c;
+    } else {
+        c = ax / (ay + (float)DBL_EPSILON);
+        c2 = c * c;
+        a = 90.f - (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * c;
+    }
+    if (x < 0) a = 180.f - a;
+    if (y < 0) a = 360.f - a;
+    return a;
+}
+
+/* OpenCV modules/imgproc/src/resize.cpp, INTER_LINEAR 8U path: per-axis tables of
+ * (source index, two short coefficients scaled by 2048), horizontal pass to int32,
+ * vertical pass (((b0*(S0>>4))>>16) + ((b1*(S1>>4))>>16) + 2) >> 2. */
+static void linear_table(int ssize, int dsize, std::vector<int>& ofs, std::vector<short>& coef) {
+    const double inv_scale = (double)dsize / ssize;
+    const double scale = 1. / inv_scale;
+    ofs.resize(dsize);
+    coef.resize(2 * (size_t)dsize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        if (s < 0) { f = 0; s = 0; }
+        if (s >= ssize - 1) { f = 0; s = ssize - 1; }
+        ofs[d] = s;
+        coef[2 * d] = (short)lrintf((1.f - f) * 2048.f);
+        coef[2 * d + 1] = (short)lrintf(f * 2048.f);
+    }
+}
+
+void ocv_resize_linear_u8(const uint8_t* src, int sw, int sh, size_t sstep,
+                          uint8_t* dst, int dw, int dh, size_t dstep) {
+    std::vector<int> xo, yo;
+    std::vector<short> xa, ya;
+    linear_table(sw, dw, xo, xa);
+    linear_table(sh, dh, yo, ya);
+    std::vector<int> r0(dw), r1(dw);
+    for (int y = 0; y < dh; y++) {
+        const int sy0 = yo[y], sy1 = sy0 + 1 < sh ? sy0 + 1 : sh - 1;
+        const uint8_t* s0 = src + (size_t)sy0 * sstep;
+        const uint8_t* s1 = src + (size_t)sy1 * sstep;
+        for (int x = 0; x < dw; x++) {
+            const int sx0 = xo[x], sx1 = sx0 + 1 < sw ? sx0 + 1 : sw - 1;
+            const int a0 = xa[2 * x], a1 = xa[2 * x + 1];
+            r0[x] = s0[sx0] * a0 + s0[sx1] * a1;
+            r1[x] = s1[sx0] * a0 + s1[sx1] * a1;
+        }
+        const int b0 = ya[2 * y], b1 = ya[2 * y + 1];
+        uint8_t* d = dst + (size_t)y * dstep;
+        for (int x = 0; x < dw; x++)
+            d[x] = (uint8_t)((((b0 * (r0[x] >> 4)) >> 16) + ((b1 * (r1[x] >> 4)) >> 16) + 2) >> 2);
+    }
+}
+
+static inline int reflect101(int p, int len) {
+    if (len == 1) return 0;
+    while (p < 0 || p >= len) {
+        if (p < 0) p = -p;
+        else p = 2 * (len - 1) - p;
+    }
+    return p;
+}
+
+void ocv_border_reflect101_u8(const uint8_t* src, int w, int h, size_t sstep,
+                              uint8_t* dst, size_t dstep, int top, int bottom, int left, int right) {
+    const int W = w + left + right, H = h + top + bottom;
+    /* interior rows first (src may alias dst's interior, as in ORBextractor.cpp:1295), then borders */
+    std::vector<uint8_t> row(w);
+    for (int y = 0; y < h; y++) {
+        std::memcpy(row.data(), src + (size_t)y * sstep, w);
+        uint8_t* d = dst + (size_t)(y + top) * dstep;
+        for (int x = 0; x < W; x++) d[x] = row[reflect101(x - left, w)];
+    }
+    for (int y = 0; y < H; y++) {
+        if (y >= top && y < top + h) continue;
+        const int sy = reflect101(y - top, h);
+        std::memcpy(dst + (size_t)y * dstep, dst + (size_t)(sy + top) * dstep, W);
+    }
+}
+
+/* OpenCV 4.x GaussianBlur CV_8U fixed-point path (smooth.simd.hpp): 8.8 ufixedpoint16 kernel
+ * {18,34,48,56,48,34,18}/256 for ksize 7, sigma 2 (recovered from cv2 and pinned by test),
+ * exact integer row+column accumulation, one final round-half-up: (sum + 2^15) >> 16. */
+void ocv_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep) {
+    static const int k[7] = {18, 34, 48, 56, 48, 34, 18};
+    std::vector<int> hbuf((size_t)w * h);
+    for (int y = 0; y < h; y++) {
+        const uint8_t* s = src + (size_t)y * sstep;
+        for (int x = 0; x < w; x++) {
+            int acc = 0;
+            for (int i = 0; i < 7; i++) acc += k[i] * s[reflect101(x + i - 3, w)];
+            hbuf[(size_t)y * w + x] = acc;
+        }
+    }
+    for (int y = 0; y < h; y++) {
+        uint8_t* d = dst + (size_t)y * dstep;
+        for (int x = 0; x < w; x++) {
+            int acc = 0;
+            for (int i = 0; i < 7; i++) acc += k[i] * hbuf[(size_t)reflect101(y + i - 3, h) * w + x];
+            d[x] = (uint8_t)((acc + 32768) >> 16);
+        }
+    }
+}
+
+/* OpenCV modules/features2d/src/fast_score.cpp cornerScore<16>: radius-3 Bresenham ring,
+ * score = max over the 16 arcs of 9 contiguous ring pixels of min(|signed difference|) - 1,
+ * taken separately for "all darker" and "all brighter" arcs. Independent of the threshold
+ * for every pixel that passes the threshold test. */
+int ocv_fast_score_9_16(const uint8_t* p, size_t step) {
+    const ptrdiff_t s = (ptrdiff_t)step;
+    const ptrdiff_t ring[16] = {3 * s,      3 * s + 1,  2 * s + 2,  s + 3,  3,       -s + 3,  -2 * s + 2, -3 * s + 1,
+                                -3 * s,     -3 * s - 1, -2 * s - 2, -s - 3, -3,      s - 3,   2 * s - 2,  3 * s - 1};
+    int d[16];
+    const int v = p[0];
+    for (int k = 0; k < 16; k++) d[k] = v - p[ring[k]];
+    int best = -1000;
+    for (int k = 0; k < 16; k++) {
+        int mn = 1000, mx = -1000;
+        for (int i = 0; i < 9; i++) {
+            const int x = d[(k + i) & 15];
+            if (x < mn) mn = x;
+            if (x > mx) mx = x;
+        }
+        if (mn > best) best = mn;
+        if (-mx > best) best = -mx;
+    }
+    return best - 1;
+}
+
+/* OpenCV modules/features2d/src/fast.cpp FAST_t<16>: scores exist only for pixels at least 3 px
+ * from each edge of THIS image and only if they are corners at THIS threshold (else 0); with
+ * nonmax, a corner survives iff its score is strictly greater than all 8 neighbours' entries. */
+int ocv_fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, int nonmax,
+                 ocv_corner* out, int cap) {
+    if (w < 7 || h < 7) return 0;
+    if (threshold < 0) threshold = 0;
+    if (threshold > 255) threshold = 255;
+    std::vector<int> sc((size_t)w * h, 0);
+    std::vector<uint8_t> is((size_t)w * h, 0);
+    for (int y = 3; y < h - 3; y++)
+        for (int x = 3; x < w - 3; x++) {
+            const int s = ocv_fast_score_9_16(img + (size_t)y * step + x, step);
+            if (s >= threshold) { sc[(size_t)y * w + x] = s; is[(size_t)y * w + x] = 1; }
+        }
+    int n = 0;
+    for (int y = 3; y < h - 3; y++)
+        for (int x = 3; x < w - 3; x++) {
+            const size_t i = (size_t)y * w + x;
+            if (!is[i]) continue;
+            const int s = sc[i];
+            if (nonmax) {
+                if (!(s > sc[i - 1] && s > sc[i + 1] && s > sc[i - w - 1] && s > sc[i - w] && s > sc[i - w + 1] &&
+                      s > sc[i + w - 1] && s > sc[i + w] && s > sc[i + w + 1]))
+                    continue;
+            }
+            if (n < cap) { out[n].x = x; out[n].y = y; out[n].score = nonmax ? s : 0; }
+            n++;
+        }
+    return n;
+}
+
+}  // extern "C"
