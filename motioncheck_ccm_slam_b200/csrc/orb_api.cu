@@ -1,0 +1,400 @@
+// Host side of the extractor C ABI (include/ccm_orb.h): scale/quota tables exactly as the reference constructor
+// computes them, per-shape level geometry, the device arena, and the kernel sequence of one batch.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/ccm_orb.h"
+#include "ccm_common.cuh"
+
+// kernels: this file is compiled as part of the single translation unit ccm_orb_cuda.cu, after
+// orb_pyramid_fast.cu, orb_quadtree.cu and orb_describe.cu.
+
+static thread_local std::string g_create_error = "";
+
+struct ccm_orb {
+    ccm_orb_config cfg;
+    // reference constructor tables (ORBextractor.cpp:579-615)
+    std::vector<float> sf, isf, sig2, isig2;
+    std::vector<int> quota;
+    // current shape
+    int rows = 0, cols = 0;
+    LevelTable T;
+    int qt_cap = 0;           // quadtree node capacity (power of two)
+    size_t qt_smem = 0;
+    int max_kps = 0;          // == T.kps_per_frame
+    // device arena
+    std::vector<void*> allocs;
+    uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
+    uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
+    ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
+    // pinned staging
+    ccm_keypoint* h_kp = nullptr; uint8_t* h_desc = nullptr; int* h_n = nullptr;
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+    int last_frames = 0;
+    const uint8_t* last_l0 = nullptr; size_t last_l0_pitch = 0, last_l0_stride = 0;
+    std::string err;
+};
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+            return CCM_E_CUDA;                                                                           \
+        }                                                                                                \
+    } while (0)
+
+static inline int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+template <typename Tp> static int dev_alloc(ccm_orb* h, Tp** p, size_t count) {
+    void* q = nullptr;
+    CK(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(Tp)));
+    h->allocs.push_back(q);
+    *p = (Tp*)q;
+    return CCM_OK;
+}
+
+static void free_arena(ccm_orb* h) {
+    for (void* p : h->allocs) cudaFree(p);
+    h->allocs.clear();
+    if (h->h_kp) cudaFreeHost(h->h_kp);
+    if (h->h_desc) cudaFreeHost(h->h_desc);
+    if (h->h_n) cudaFreeHost(h->h_n);
+    h->h_kp = nullptr; h->h_desc = nullptr; h->h_n = nullptr;
+}
+
+// cv::resize INTER_LINEAR coefficient table (OpenCV resize.cpp), see oracle/cv_primitives.cpp linear_table
+static void linear_table(int ssize, int dsize, std::vector<int>& ofs, std::vector<short>& coef) {
+    const double scale = 1. / ((double)dsize / ssize);
+    ofs.resize(dsize); coef.resize(2 * (size_t)dsize);
+    for (int d = 0; d < dsize; d++) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        if (s < 0) { f = 0; s = 0; }
+        if (s >= ssize - 1) { f = 0; s = ssize - 1; }
+        ofs[d] = s;
+        coef[2 * d] = (short)lrintf((1.f - f) * 2048.f);
+        coef[2 * d + 1] = (short)lrintf(f * 2048.f);
+    }
+}
+
+// Level geometry for one image shape, following ComputePyramid (:1284-1286), ComputeKeyPointsOctTree (:941-955)
+// and DistributeOctTree (:711-713). Allocates the arena for cfg.max_batch frames of this shape.
+static int configure_shape(ccm_orb* h, int rows, int cols) {
+    if (rows == h->rows && cols == h->cols) return CCM_OK;
+    if (rows > h->cfg.max_height || cols > h->cfg.max_width) { h->err = "image larger than max_width x max_height of the handle"; return CCM_E_CAPACITY; }
+    CK(cudaStreamSynchronize(h->stream));
+    free_arena(h);
+    h->rows = h->cols = 0;
+    LevelTable& T = h->T;
+    std::memset(&T, 0, sizeof(T));
+    const int L = h->cfg.nlevels, B = h->cfg.max_batch;
+    T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
+    int cells = 0, corners = 0, kps = 0, max_node_cap = 0;
+    for (int l = 0; l < L; l++) {
+        LevelDesc& D = T.l[l];
+        D.w = (int)lrintf((float)cols * h->isf[l]);
+        D.h = (int)lrintf((float)rows * h->isf[l]);
+        const float width = (float)(D.w - 2 * CCM_MIN_BORDER), height = (float)(D.h - 2 * CCM_MIN_BORDER);
+        D.nCols = (int)(width / 30.f); D.nRows = (int)(height / 30.f);
+        if (D.nCols <= 0 || D.nRows <= 0) { h->err = "image too small for this many pyramid levels (a level has no 30-px cell)"; return CCM_E_BADARG; }
+        D.wCell = (int)std::ceil(width / D.nCols); D.hCell = (int)std::ceil(height / D.nRows);
+        if (D.wCell > 64 || D.hCell > 64) { h->err = "internal: cell larger than 64 px"; return CCM_E_BADARG; }
+        D.cell_base = cells; cells += D.nCols * D.nRows;
+        D.quota = h->quota[l];
+        D.nIni = (int)std::round((float)(D.w - 32) / (D.h - 32));
+        if (D.nIni < 1) { h->err = "unsupported aspect ratio (height > 2*width): the reference divides by zero here"; return CCM_E_BADARG; }
+        D.hX = (float)(D.w - 32) / D.nIni;
+        D.node_cap = std::max(D.quota + 3, 4 * D.nIni);
+        max_node_cap = std::max(max_node_cap, D.node_cap);
+        int cc = 0;
+        for (int i = 0; i < D.nRows; i++)
+            for (int j = 0; j < D.nCols; j++) {
+                const int x0 = CCM_EDGE + j * D.wCell, y0 = CCM_EDGE + i * D.hCell;
+                const int cw = std::min(x0 + D.wCell, D.w - CCM_EDGE) - x0, ch = std::min(y0 + D.hCell, D.h - CCM_EDGE) - y0;
+                if (cw > 0 && ch > 0) cc += ((cw + 1) / 2) * ((ch + 1) / 2);
+            }
+        D.corner_cap = std::max(cc, 1); D.corner_off = corners; corners += align_up(D.corner_cap, 4);
+        if (D.corner_cap > 0x7FFFF) { h->err = "image too large (corner capacity per level exceeds 2^19)"; return CCM_E_BADARG; }
+        D.kp_off = kps; kps += D.node_cap;
+        D.scale = h->sf[l];
+        D.kp_size = (float)(int)(31 * h->sf[l]);
+        D.img_pitch = D.blur_pitch = align_up(D.w, 32);
+        D.img_stride = D.blur_stride = (size_t)D.img_pitch * D.h;
+    }
+    if (max_node_cap > 2048) { h->err = "nfeatures too large: more than 2045 features on one level"; return CCM_E_BADARG; }
+    T.total_cells = cells; T.corners_per_frame = corners; T.kps_per_frame = kps;
+    h->max_kps = kps;
+    int cap = 32; while (cap < max_node_cap) cap <<= 1;
+    h->qt_cap = cap;
+    h->qt_smem = (size_t)cap * 60 + (512 + 1) * sizeof(int);
+    CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
+
+    for (int l = 0; l < L; l++) {
+        LevelDesc& D = T.l[l];
+        int rc;
+        if ((rc = dev_alloc(h, &D.img, D.img_stride * B + 64))) return rc;     // +64: 4-pixel stores may touch the pitch padding
+        if ((rc = dev_alloc(h, &D.blur, D.blur_stride * B + 64))) return rc;
+        if (l > 0) {
+            std::vector<int> xo, yo; std::vector<short> xa, ya;
+            linear_table(T.l[l - 1].w, D.w, xo, xa);
+            linear_table(T.l[l - 1].h, D.h, yo, ya);
+            int* dxo; int* dyo; short* dxa; short* dya;
+            if ((rc = dev_alloc(h, &dxo, xo.size()))) return rc;
+            if ((rc = dev_alloc(h, &dyo, yo.size()))) return rc;
+            if ((rc = dev_alloc(h, &dxa, xa.size()))) return rc;
+            if ((rc = dev_alloc(h, &dya, ya.size()))) return rc;
+            CK(cudaMemcpy(dxo, xo.data(), xo.size() * sizeof(int), cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(dyo, yo.data(), yo.size() * sizeof(int), cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(dxa, xa.data(), xa.size() * sizeof(short), cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(dya, ya.data(), ya.size() * sizeof(short), cudaMemcpyHostToDevice));
+            D.xofs = dxo; D.yofs = dyo; D.xcoef = dxa; D.ycoef = dya;
+        }
+    }
+    int rc;
+    if ((rc = dev_alloc(h, &h->d_corners, (size_t)corners * B))) return rc;
+    if ((rc = dev_alloc(h, &h->d_node_of, (size_t)corners * B))) return rc;
+    if ((rc = dev_alloc(h, &h->d_corner_count, (size_t)CCM_MAX_LEVELS * B))) return rc;
+    if ((rc = dev_alloc(h, &h->d_level_kp_count, (size_t)CCM_MAX_LEVELS * B))) return rc;
+    if ((rc = dev_alloc(h, &h->d_level_kps, (size_t)kps * B))) return rc;
+    if ((rc = dev_alloc(h, &h->d_kp, (size_t)kps * B))) return rc;
+    if ((rc = dev_alloc(h, &h->d_desc, (size_t)kps * B * 32))) return rc;
+    if ((rc = dev_alloc(h, &h->d_n, (size_t)B))) return rc;
+    CK(cudaMallocHost((void**)&h->h_kp, (size_t)kps * B * sizeof(ccm_keypoint)));
+    CK(cudaMallocHost((void**)&h->h_desc, (size_t)kps * B * 32));
+    CK(cudaMallocHost((void**)&h->h_n, (size_t)B * sizeof(int)));
+    h->rows = rows; h->cols = cols;
+    return CCM_OK;
+}
+
+// One batch through K1..K7 on the handle's stream. Level 0 is read in place from (l0, pitch, stride).
+static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, size_t l0_stride,
+                        ccm_keypoint* d_kp, uint8_t* d_desc, int* d_n, int capacity) {
+    LevelTable& T = h->T;
+    T.l[0].img = const_cast<uint8_t*>(l0);
+    T.l[0].img_pitch = (int)l0_pitch;
+    T.l[0].img_stride = l0_stride;
+    h->last_frames = n; h->last_l0 = l0; h->last_l0_pitch = l0_pitch; h->last_l0_stride = l0_stride;
+    cudaStream_t s = h->stream;
+    CK(cudaMemsetAsync(h->d_corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
+    for (int l = 1; l < T.nlevels; l++) {
+        dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
+        k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
+        h->launches++;
+    }
+    k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_corners, h->d_corner_count);
+    h->launches++;
+    for (int l = 0; l < T.nlevels; l++) {
+        dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 31) / 32, n);
+        k_blur_level<<<g, 256, 0, s>>>(T, l);
+        h->launches++;
+    }
+    k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, h->d_corners, h->d_corner_count, h->d_node_of,
+                                                          h->d_level_kps, h->d_level_kp_count);
+    h->launches++;
+    k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, h->d_level_kps, h->d_level_kp_count,
+                                                                        (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
+    h->launches++;
+    CK(cudaGetLastError());
+    return CCM_OK;
+}
+
+extern "C" {
+
+const char* ccm_last_error(const ccm_orb* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
+    if (!cfg || !out) { g_create_error = "null argument"; return CCM_E_BADARG; }
+    *out = nullptr;
+    if (cfg->nfeatures < 1 || cfg->nlevels < 1 || cfg->nlevels > CCM_MAX_LEVELS || !(cfg->scale_factor > 1.0f) ||
+        cfg->ini_th_fast < 1 || cfg->ini_th_fast > 255 || cfg->min_th_fast < 1 || cfg->min_th_fast > 255 ||
+        cfg->max_width < 1 || cfg->max_width > 4095 || cfg->max_height < 1 || cfg->max_height > 4095 || cfg->max_batch < 1 ||
+        cfg->max_batch > 65535) {
+        g_create_error = "bad ccm_orb_config (need nfeatures>=1, 1<=nlevels<=16, scale_factor>1, FAST thresholds in 1..255, size<=4095, 1<=max_batch<=65535)";
+        return CCM_E_BADARG;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || cfg->device < 0 || cfg->device >= ndev) {
+        g_create_error = std::string("no usable CUDA device ") + std::to_string(cfg->device) + ": " + cudaGetErrorString(e) + " (there is no CPU fallback)";
+        return CCM_E_CUDA;
+    }
+    ccm_orb* h = new ccm_orb();
+    h->cfg = *cfg;
+    // ORBextractor::ORBextractor, cslam/src/ORBextractor.cpp:579-615 — float/double mix kept as written
+    const int L = cfg->nlevels;
+    const double scaleFactor = cfg->scale_factor;
+    h->sf.assign(L, 1.0f); h->sig2.assign(L, 1.0f); h->isf.resize(L); h->isig2.resize(L); h->quota.assign(L, 0);
+    for (int i = 1; i < L; i++) { h->sf[i] = (float)(h->sf[i - 1] * scaleFactor); h->sig2[i] = h->sf[i] * h->sf[i]; }
+    for (int i = 0; i < L; i++) { h->isf[i] = 1.0f / h->sf[i]; h->isig2[i] = 1.0f / h->sig2[i]; }
+    float factor = (float)(1.0f / scaleFactor);
+    float nDesired = cfg->nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)L));
+    int sum = 0;
+    for (int l = 0; l < L - 1; l++) { h->quota[l] = (int)lrintf(nDesired); sum += h->quota[l]; nDesired *= factor; }
+    h->quota[L - 1] = std::max(cfg->nfeatures - sum, 0);
+
+    auto fail = [&](int rc) { g_create_error = h->err; free_arena(h); if (h->stream) cudaStreamDestroy(h->stream); delete h; return rc; };
+    if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+    if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+    int rc = configure_shape(h, cfg->max_height, cfg->max_width);
+    if (rc != CCM_OK) return fail(rc);
+    *out = h;
+    return CCM_OK;
+}
+
+void ccm_orb_destroy(ccm_orb* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_arena(h);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int ccm_orb_get_tables(const ccm_orb* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* fpl) {
+    if (!h) return CCM_E_BADARG;
+    for (int l = 0; l < h->cfg.nlevels; l++) {
+        if (scale) scale[l] = h->sf[l];
+        if (inv_scale) inv_scale[l] = h->isf[l];
+        if (sigma2) sigma2[l] = h->sig2[l];
+        if (inv_sigma2) inv_sigma2[l] = h->isig2[l];
+        if (fpl) fpl[l] = h->quota[l];
+    }
+    return CCM_OK;
+}
+
+int ccm_orb_max_keypoints(const ccm_orb* h) { return h ? h->max_kps : CCM_E_BADARG; }
+void* ccm_orb_stream(ccm_orb* h) { return h ? (void*)h->stream : nullptr; }
+long long ccm_orb_launch_count(const ccm_orb* h) { return h ? h->launches : 0; }
+
+int ccm_orb_sync(ccm_orb* h) {
+    if (!h) return CCM_E_BADARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    return CCM_OK;
+}
+
+int ccm_orb_extract_batch_device(ccm_orb* h, const uint8_t* d_imgs, int n, int rows, int cols, size_t pitch, size_t frame_stride,
+                                 ccm_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_n) {
+    if (!h) return CCM_E_BADARG;
+    if (!d_imgs || !d_kp || !d_desc || !d_n || n < 1 || rows < 1 || cols < 1 || capacity < 1 || pitch < (size_t)cols) { h->err = "bad argument"; return CCM_E_BADARG; }
+    if (n > h->cfg.max_batch) { h->err = "batch larger than max_batch"; return CCM_E_CAPACITY; }
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = configure_shape(h, rows, cols);
+    if (rc != CCM_OK) return rc;
+    return run_pipeline(h, n, d_imgs, pitch, frame_stride, d_kp, d_desc, d_n, capacity);
+}
+
+int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int rows, int cols, size_t step,
+                          ccm_keypoint* out_kp, uint8_t* out_desc, int capacity, int* out_n) {
+    if (!h) return CCM_E_BADARG;
+    if (!imgs || !out_n || n < 1 || capacity < 0 || (capacity > 0 && (!out_kp || !out_desc))) { h->err = "bad argument"; return CCM_E_BADARG; }
+    if (rows == 0 || cols == 0) { for (int f = 0; f < n; f++) out_n[f] = 0; return CCM_OK; }
+    if (rows < 0 || cols < 0 || step < (size_t)cols) { h->err = "bad image geometry"; return CCM_E_BADARG; }
+    if (n > h->cfg.max_batch) { h->err = "batch larger than max_batch"; return CCM_E_CAPACITY; }
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = configure_shape(h, rows, cols);
+    if (rc != CCM_OK) return rc;
+    // level 0 lives in the handle's own (pitched) level-0 buffer
+    LevelDesc& L0 = h->T.l[0];
+    uint8_t* l0 = (uint8_t*)h->allocs[0];
+    const size_t pitch = (size_t)align_up(cols, 32), stride = pitch * rows;
+    for (int f = 0; f < n; f++) {
+        if (!imgs[f]) { h->err = "null image in batch"; return CCM_E_BADARG; }
+        CK(cudaMemcpy2DAsync(l0 + f * stride, pitch, imgs[f], step, cols, rows, cudaMemcpyHostToDevice, h->stream));
+    }
+    (void)L0;
+    const int cap = h->max_kps;
+    rc = run_pipeline(h, n, l0, pitch, stride, h->d_kp, h->d_desc, h->d_n, cap);
+    if (rc != CCM_OK) return rc;
+    CK(cudaMemcpyAsync(h->h_n, h->d_n, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(h->h_kp, h->d_kp, sizeof(ccm_keypoint) * (size_t)cap * n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * cap * n, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int f = 0; f < n; f++) {
+        const int cnt = h->h_n[f];
+        out_n[f] = cnt;
+        const int m = std::min(std::min(cnt, capacity), cap);
+        if (m > 0) {
+            std::memcpy(out_kp + (size_t)f * capacity, h->h_kp + (size_t)f * cap, sizeof(ccm_keypoint) * m);
+            std::memcpy(out_desc + (size_t)f * capacity * 32, h->h_desc + (size_t)f * cap * 32, (size_t)32 * m);
+        }
+    }
+    return CCM_OK;
+}
+
+int ccm_orb_extract(ccm_orb* h, const uint8_t* img, int rows, int cols, size_t step, ccm_keypoint* out_kp, uint8_t* out_desc,
+                    int capacity, int* out_n) {
+    if (!h) return CCM_E_BADARG;
+    if (!out_n) { h->err = "bad argument"; return CCM_E_BADARG; }
+    if (!img || rows == 0 || cols == 0) { *out_n = 0; return CCM_OK; }   // ORBextractor.cpp:1219-1220
+    const uint8_t* one[1] = {img};
+    return ccm_orb_extract_batch(h, one, 1, rows, cols, step, out_kp, out_desc, capacity, out_n);
+}
+
+}  // extern "C"
+
+// ---- readback of intermediate stages of the last call ----
+static int read_level(ccm_orb* h, int frame, int level, bool blurred, int border, uint8_t* out, size_t out_step, int* ow, int* oh) {
+    if (!h) return CCM_E_BADARG;
+    if (!out || frame < 0 || frame >= h->last_frames || level < 0 || level >= h->cfg.nlevels) { h->err = "bad argument"; return CCM_E_BADARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    const LevelDesc& D = h->T.l[level];
+    const int W = D.w + 2 * border, H = D.h + 2 * border;
+    if (out_step < (size_t)W) { h->err = "out_step too small"; return CCM_E_CAPACITY; }
+    std::vector<uint8_t> tmp((size_t)D.w * D.h);
+    const uint8_t* src = blurred ? D.blur + (size_t)frame * D.blur_stride : D.img + (size_t)frame * D.img_stride;
+    const size_t pitch = blurred ? D.blur_pitch : D.img_pitch;
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaMemcpy2D(tmp.data(), D.w, src, pitch, D.w, D.h, cudaMemcpyDeviceToHost));
+    auto refl = [](int p, int len) { if (len == 1) return 0; while (p < 0 || p >= len) p = p < 0 ? -p : 2 * (len - 1) - p; return p; };
+    for (int y = 0; y < H; y++) {
+        const uint8_t* s = &tmp[(size_t)refl(y - border, D.h) * D.w];
+        uint8_t* d = out + (size_t)y * out_step;
+        if (border == 0) std::memcpy(d, s, D.w);
+        else for (int x = 0; x < W; x++) d[x] = s[refl(x - border, D.w)];
+    }
+    if (ow) *ow = W;
+    if (oh) *oh = H;
+    return CCM_OK;
+}
+
+extern "C" {
+
+int ccm_orb_get_pyramid_level(ccm_orb* h, int frame, int level, int with_border, uint8_t* out, size_t out_step, int* ow, int* oh) {
+    return read_level(h, frame, level, false, with_border ? CCM_EDGE : 0, out, out_step, ow, oh);
+}
+int ccm_orb_debug_blurred_level(ccm_orb* h, int frame, int level, uint8_t* out, size_t out_step, int* ow, int* oh) {
+    return read_level(h, frame, level, true, 0, out, out_step, ow, oh);
+}
+
+int ccm_orb_debug_level_corners(ccm_orb* h, int frame, int level, int* xys, int capacity, int* out_n) {
+    if (!h) return CCM_E_BADARG;
+    if (!out_n || frame < 0 || frame >= h->last_frames || level < 0 || level >= h->cfg.nlevels || (capacity > 0 && !xys)) { h->err = "bad argument"; return CCM_E_BADARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    const LevelDesc& D = h->T.l[level];
+    int n = 0;
+    CK(cudaMemcpy(&n, h->d_corner_count + frame * CCM_MAX_LEVELS + level, sizeof(int), cudaMemcpyDeviceToHost));
+    n = std::min(n, D.corner_cap);
+    std::vector<uint32_t> pk(n);
+    if (n) CK(cudaMemcpy(pk.data(), h->d_corners + (size_t)frame * h->T.corners_per_frame + D.corner_off, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost));
+    // reference order: cells row-major, raster inside a cell (ORBextractor.cpp:957-997)
+    auto ord = [&](uint32_t c) {
+        const int x = (int)(c & 4095u), y = (int)((c >> 12) & 4095u);
+        const int cj = (x - CCM_EDGE) / D.wCell, ci = (y - CCM_EDGE) / D.hCell;
+        return (long long)(((ci * D.nCols + cj) * D.hCell + (y - CCM_EDGE - ci * D.hCell))) * D.wCell + (x - CCM_EDGE - cj * D.wCell);
+    };
+    std::sort(pk.begin(), pk.end(), [&](uint32_t a, uint32_t b) { return ord(a) < ord(b); });
+    for (int i = 0; i < n && i < capacity; i++) { xys[3 * i] = (int)(pk[i] & 4095u); xys[3 * i + 1] = (int)((pk[i] >> 12) & 4095u); xys[3 * i + 2] = (int)(pk[i] >> 24); }
+    *out_n = n;
+    return CCM_OK;
+}
+
+}  // extern "C"

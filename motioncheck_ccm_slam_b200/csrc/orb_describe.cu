@@ -1,0 +1,174 @@
+// K6 (7x7 Gaussian blur), K5 (intensity-centroid orientation) + K7 (steered rBRIEF-256), sm_100a.
+#include "ccm_common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// K6: cv::GaussianBlur(level.clone(), 7x7, sigma 2, BORDER_REFLECT_101), cslam/src/ORBextractor.cpp:1258-1259.
+// OpenCV 4.x CV_8U fixed-point path: 8.8 kernel {18,34,48,56,48,34,18}/256, exact integer row and column
+// accumulation, single rounding (sum + 2^15) >> 16. Tile = 128 x 32 outputs; source tile with 3-px reflected
+// halo staged in shared memory, row pass into u16 shared memory, column pass packs 4 pixels per 32-bit store.
+// ---------------------------------------------------------------------------------------------
+#define BLUR_TW 128
+#define BLUR_TH 32
+
+__global__ void __launch_bounds__(256) k_blur_level(const __grid_constant__ LevelTable T, int lvl) {
+    __shared__ uint8_t src[BLUR_TH + 6][BLUR_TW + 8];
+    __shared__ uint16_t hb[BLUR_TH + 6][BLUR_TW];
+    const LevelDesc& L = T.l[lvl];
+    const int f = blockIdx.z;
+    const int x0 = blockIdx.x * BLUR_TW, y0 = blockIdx.y * BLUR_TH;
+    const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
+    uint8_t* __restrict__ out = L.blur + (size_t)f * L.blur_stride;
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
+        const int ty = i / (BLUR_TW + 6), tx = i - ty * (BLUR_TW + 6);
+        // clamp tile coordinates that fall beyond the image + halo (only feed outputs that are never stored)
+        const int gy = ccm_reflect101(min(y0 - 3 + ty, L.h + 2), L.h);
+        const int gx = ccm_reflect101(min(x0 - 3 + tx, L.w + 2), L.w);
+        src[ty][tx] = img[(size_t)gy * L.img_pitch + gx];
+    }
+    __syncthreads();
+    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
+        const int ty = i / BLUR_TW, tx = i - ty * BLUR_TW;
+        const uint8_t* s = &src[ty][tx];
+        const int acc = 18 * (s[0] + s[6]) + 34 * (s[1] + s[5]) + 48 * (s[2] + s[4]) + 56 * s[3];
+        hb[ty][tx] = (uint16_t)acc;          // <= 255*256 = 65280
+    }
+    __syncthreads();
+    for (int i = tid; i < BLUR_TH * (BLUR_TW / 4); i += 256) {
+        const int ty = i / (BLUR_TW / 4), tx = (i - ty * (BLUR_TW / 4)) * 4;
+        const int gy = y0 + ty, gx = x0 + tx;
+        if (gy >= L.h || gx >= L.w) continue;
+        uint32_t packed = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int acc = 18 * (hb[ty][tx + k] + hb[ty + 6][tx + k]) + 34 * (hb[ty + 1][tx + k] + hb[ty + 5][tx + k]) +
+                            48 * (hb[ty + 2][tx + k] + hb[ty + 4][tx + k]) + 56 * hb[ty + 3][tx + k];
+            packed |= (uint32_t)((acc + 32768) >> 16) << (8 * k);
+        }
+        *reinterpret_cast<uint32_t*>(out + (size_t)gy * L.blur_pitch + gx) = packed;   // pitch multiple of 32: in-bounds
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K5 + K7, one warp per selected keypoint.
+//   IC_Angle (cslam/src/ORBextractor.cpp:68-95): integer moments over the 749-px disc of the UNBLURRED level,
+//   then cv::fastAtan2 restated with separately rounded float ops (bit-exact).
+//   computeOrbDescriptor (:100-316): 256 steered comparisons on the BLURRED level; lane l produces byte l.
+//   cos/sin are evaluated in double and rounded to float (glibc cosf/sinf are not reproducible bit-for-bit on a
+//   GPU; this differs from them by 1 ulp for ~1.3 % of angles, which flips a tap only at an exact .5 boundary —
+//   the north-star tolerance >= 99.9 % identical descriptor bits covers it; measured in tests).
+//   Output: ccm_keypoint with pt scaled by mvScaleFactor[level] for level != 0 (:1268-1274), descriptor as two
+//   16-byte stores per keypoint.
+// ---------------------------------------------------------------------------------------------
+struct BriefPattern { signed char v[256][4]; };
+__constant__ BriefPattern c_pattern_init = {{
+#include "brief_pattern.inc"
+}};
+__constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};   // :623-638 for HALF_PATCH_SIZE 15
+
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+    // OpenCV atan2_p1..p7: float(coef) * float(180/pi), evaluated in float
+    const float p1 = 0x1.ca44dep+5f, p3 = -0x1.2aaddcp+4f, p5 = 0x1.1d3f7ep+3f, p7 = -0x1.4515b2p+1f;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, 0x1p-52f));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, 0x1p-52f));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+__global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ LevelTable T,
+                                                         const uint32_t* __restrict__ level_kps,     // [frames][kps_per_frame]
+                                                         const int* __restrict__ level_kp_count,     // [frames][CCM_MAX_LEVELS]
+                                                         ccm_keypoint_dev* __restrict__ out_kp,      // [frames][capacity]
+                                                         uint8_t* __restrict__ out_desc,             // [frames][capacity][32]
+                                                         int* __restrict__ out_count,                // [frames]
+                                                         int capacity) {
+    __shared__ int pat[8][32][2];     // pat[k][lane] = packed taps of test 8*lane+k (conflict-free per k)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 256; i += 256) {
+        const signed char* p = c_pattern_init.v[i];
+        pat[i & 7][i >> 3][0] = ((int)p[0] & 0xFFFF) | ((int)p[1] << 16);
+        pat[i & 7][i >> 3][1] = ((int)p[2] & 0xFFFF) | ((int)p[3] << 16);
+    }
+    __syncthreads();
+
+    const int f = blockIdx.y;
+    const int slot = blockIdx.x * 8 + warp;
+    if (slot >= T.kps_per_frame) return;
+    int lvl = 0;
+    while (lvl + 1 < T.nlevels && slot >= T.l[lvl + 1].kp_off) lvl++;
+    const LevelDesc& L = T.l[lvl];
+    const int pos = slot - L.kp_off;
+    const int* cnt = level_kp_count + f * CCM_MAX_LEVELS;
+    int before = 0, total = 0;
+    for (int l = 0; l < T.nlevels; l++) { const int c = cnt[l]; if (l < lvl) before += c; total += c; }
+    if (slot == 0 && lane == 0) out_count[f] = total;
+    if (pos >= cnt[lvl]) return;
+    const int oi = before + pos;
+    if (oi >= capacity) return;
+
+    const uint32_t pk = level_kps[(size_t)f * T.kps_per_frame + slot];
+    const int kx = (int)(pk & 4095u), ky = (int)((pk >> 12) & 4095u), score = (int)(pk >> 24);
+
+    // --- orientation ---
+    const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride + (size_t)ky * L.img_pitch + kx;
+    int m10 = 0, m01 = 0;
+    const int u = lane - CCM_HALF_PATCH;
+#pragma unroll 1
+    for (int v = -CCM_HALF_PATCH; v <= CCM_HALF_PATCH; v++) {
+        if (lane < 31 && abs(u) <= c_umax[abs(v)]) {
+            const int val = img[v * L.img_pitch + u];
+            m10 += u * val;
+            m01 += v * val;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { m10 += __shfl_xor_sync(0xffffffffu, m10, o); m01 += __shfl_xor_sync(0xffffffffu, m01, o); }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+    // --- descriptor ---
+    const float rad = __fmul_rn(angle, 0x1.1df46ap-6f);      // factorPI = (float)(CV_PI/180.f)
+    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+    const uint8_t* __restrict__ bl = L.blur + (size_t)f * L.blur_stride + (size_t)ky * L.blur_pitch + kx;
+    uint32_t byte = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const int p0 = pat[k][lane][0], p1 = pat[k][lane][1];
+        const float x1 = (float)(short)(p0 & 0xFFFF), y1 = (float)(p0 >> 16);
+        const float x2 = (float)(short)(p1 & 0xFFFF), y2 = (float)(p1 >> 16);
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
+        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
+        const int r2 = __float2int_rn(__fadd_rn(__fmul_rn(x2, b), __fmul_rn(y2, a)));
+        const int c2 = __float2int_rn(__fsub_rn(__fmul_rn(x2, a), __fmul_rn(y2, b)));
+        const int t0 = bl[r1 * L.blur_pitch + c1], t1 = bl[r2 * L.blur_pitch + c2];
+        byte |= (uint32_t)(t0 < t1) << k;
+    }
+    uint32_t w = byte << (8 * (lane & 3));
+    w |= __shfl_xor_sync(0xffffffffu, w, 1);
+    w |= __shfl_xor_sync(0xffffffffu, w, 2);                  // every lane of a quad now holds descriptor word lane/4
+    const int half = lane & 1;
+    uint4 q;
+    q.x = __shfl_sync(0xffffffffu, w, 16 * half + 0);
+    q.y = __shfl_sync(0xffffffffu, w, 16 * half + 4);
+    q.z = __shfl_sync(0xffffffffu, w, 16 * half + 8);
+    q.w = __shfl_sync(0xffffffffu, w, 16 * half + 12);
+    uint8_t* d = out_desc + ((size_t)f * capacity + oi) * 32;
+    if (lane < 2) *reinterpret_cast<uint4*>(d + 16 * lane) = q;
+    if (lane == 0) {
+        ccm_keypoint_dev kp;
+        kp.x = (float)kx; kp.y = (float)ky;
+        if (lvl != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
+        kp.size = L.kp_size; kp.angle = angle; kp.response = (float)score; kp.octave = lvl;
+        out_kp[(size_t)f * capacity + oi] = kp;
+    }
+}

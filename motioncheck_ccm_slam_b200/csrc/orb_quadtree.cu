@@ -1,0 +1,262 @@
+// K4: quadtree keypoint distribution, one CTA per (frame, level). Replaces ORBextractor::DistributeOctTree
+// (cslam/src/ORBextractor.cpp:707-931) and ExtractorNode::DivideNode (:650-705).
+//
+// The reference walks a std::list with push_front/erase; here the list is an array indexed by list position
+// (front = 0) that is rebuilt level-synchronously each round:
+//   new list = reverse(children of the nodes split this round, in split order, n1..n4)  ++  untouched nodes in old order
+// which is exactly what repeated push_front + erase produces. Every corner carries the list position of its node.
+// Round kinds:
+//   "sweep"  (:767-830)  every node holding >1 corner is split, in list order;
+//   "greedy" (:841-905)  entered when size + 3*nToExpand > N: nodes holding >1 corner are split largest first
+//                        until the list reaches N.  Ties between equal sizes: the reference compares heap
+//                        addresses (:852); the rule fixed here is "later-created first" == smaller list position
+//                        first, i.e. the reference under a monotone allocator (quadtree tie rule).
+// Final pick (:910-928): per node the corner with the largest response, first in vToDistributeKeys order on
+// ties; that order (cells row-major, raster inside a cell) is recomputed from the coordinates, so the corner
+// list itself may be in any order.
+#include "ccm_common.cuh"
+
+namespace {
+
+struct QNode { short ulx, uly, brx, bry; int cnt; };
+
+// exclusive prefix sum of v[0..n) in place (block-wide); returns the total. scratch: blockDim.x ints.
+__device__ int block_exclusive_scan(int* v, int n, int* scratch) {
+    const int T = blockDim.x, tid = threadIdx.x;
+    const int per = (n + T - 1) / T;
+    const int b = min(tid * per, n), e = min(b + per, n);
+    int s = 0;
+    for (int i = b; i < e; i++) s += v[i];
+    scratch[tid] = s;
+    __syncthreads();
+    if (tid < 32) {      // T <= 1024: one warp scans the per-thread totals
+        int carry = 0;
+        for (int base = 0; base < T; base += 32) {
+            int x = scratch[base + tid];
+            int inc = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, inc, o); if (tid >= o) inc += y; }
+            scratch[base + tid] = carry + inc - x;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (tid == 0) scratch[T] = carry;
+    }
+    __syncthreads();
+    int run = scratch[tid];
+    for (int i = b; i < e; i++) { int x = v[i]; v[i] = run; run += x; }
+    const int total = scratch[T];
+    __syncthreads();
+    return total;
+}
+
+__device__ __forceinline__ void child_bounds(const QNode& p, int q, QNode& c) {
+    const int mx = p.ulx + ((p.brx - p.ulx + 1) >> 1);   // ceil(float(UR.x-UL.x)/2), :652
+    const int my = p.uly + ((p.bry - p.uly + 1) >> 1);
+    c.ulx = (q & 1) ? mx : p.ulx;  c.brx = (q & 1) ? p.brx : mx;
+    c.uly = (q & 2) ? my : p.uly;  c.bry = (q & 2) ? p.bry : my;
+}
+__device__ __forceinline__ int quadrant(const QNode& p, int x, int y) {
+    const int mx = p.ulx + ((p.brx - p.ulx + 1) >> 1);
+    const int my = p.uly + ((p.bry - p.uly + 1) >> 1);
+    return (x < mx ? 0 : 1) | (y < my ? 0 : 2);           // n1=0 n2=1 n3=2 n4=3, :680-695
+}
+
+}  // namespace
+
+// dynamic smem layout (cap = node capacity rounded up to a power of two, >= 32):
+//   QNode A[cap], B[cap]; int cc[4*cap]; int key[cap]; int aux[cap]; int newpos[cap]; short childpos[4*cap];
+//   int scratch[blockDim+1]
+__global__ void __launch_bounds__(512) k_quadtree(const __grid_constant__ LevelTable T, int cap,
+                                                  const uint32_t* __restrict__ corners, const int* __restrict__ corner_count,
+                                                  uint16_t* __restrict__ node_of,          // [frames][corners_per_frame]
+                                                  uint32_t* __restrict__ level_kps,        // [frames][kps_per_frame] packed x|y<<12|score<<24
+                                                  int* __restrict__ level_kp_count) {      // [frames][CCM_MAX_LEVELS]
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lvl = blockIdx.x, f = blockIdx.y;
+    const LevelDesc& L = T.l[lvl];
+    const int tid = threadIdx.x, NT = blockDim.x;
+
+    QNode* A = reinterpret_cast<QNode*>(smem_raw);
+    QNode* B = A + cap;
+    int* cc = reinterpret_cast<int*>(B + cap);
+    int* key = cc + 4 * cap;
+    int* aux = key + cap;
+    int* newpos = aux + cap;
+    short* childpos = reinterpret_cast<short*>(newpos + cap);
+    int* scratch = reinterpret_cast<int*>(childpos + 4 * cap);
+    __shared__ int s_n, s_expand, s_P, s_C;
+
+    const int nC = min(corner_count[f * CCM_MAX_LEVELS + lvl], L.corner_cap);
+    const uint32_t* ck = corners + (size_t)f * T.corners_per_frame + L.corner_off;
+    uint16_t* nof = node_of + (size_t)f * T.corners_per_frame + L.corner_off;
+    const int N = L.quota;
+    const int H = L.h - 2 * CCM_MIN_BORDER;   // maxY-minY
+
+    // ---- initial nodes (:711-741) ----
+    for (int i = tid; i < cap; i += NT) { A[i].cnt = 0; }
+    __syncthreads();
+    if (tid < L.nIni) {
+        A[tid].ulx = (short)(int)(L.hX * (float)tid);
+        A[tid].brx = (short)(int)(L.hX * (float)(tid + 1));
+        A[tid].uly = 0; A[tid].bry = (short)H;
+    }
+    __syncthreads();
+    for (int k = tid; k < nC; k += NT) {
+        const uint32_t c = ck[k];
+        const int x = (int)(c & 4095u) - CCM_MIN_BORDER;
+        const int nd = (int)(__fdiv_rn((float)x, L.hX));
+        nof[k] = (uint16_t)nd;
+        atomicAdd(&A[nd].cnt, 1);
+    }
+    __syncthreads();
+    // drop empty initial nodes (:743-757), keeping order
+    if (tid == 0) {
+        int n = 0;
+        for (int i = 0; i < L.nIni; i++) { newpos[i] = n; if (A[i].cnt > 0) { B[n] = A[i]; n++; } }
+        s_n = n;
+    }
+    __syncthreads();
+    int n = s_n;
+    for (int k = tid; k < nC; k += NT) nof[k] = (uint16_t)newpos[nof[k]];
+    for (int i = tid; i < n; i += NT) A[i] = B[i];
+    __syncthreads();
+
+    bool greedy = false;
+#pragma unroll 1
+    while (true) {
+        // child occupancy of every node holding more than one corner
+        for (int i = tid; i < 4 * n; i += NT) cc[i] = 0;
+        __syncthreads();
+        for (int k = tid; k < nC; k += NT) {
+            const int nd = nof[k];
+            if (A[nd].cnt > 1) {
+                const uint32_t c = ck[k];
+                const int q = quadrant(A[nd], (int)(c & 4095u) - CCM_MIN_BORDER, (int)((c >> 12) & 4095u) - CCM_MIN_BORDER);
+                atomicAdd(&cc[4 * nd + q], 1);
+            }
+        }
+        __syncthreads();
+
+        // ---- choose the nodes split this round and their split order: key[r] = list position of the r-th split ----
+        int P;   // number of nodes split
+        if (!greedy) {
+            for (int i = tid; i < n; i += NT) aux[i] = A[i].cnt > 1 ? 1 : 0;
+            __syncthreads();
+            P = block_exclusive_scan(aux, n, scratch);
+            for (int i = tid; i < n; i += NT) if (A[i].cnt > 1) key[aux[i]] = i;
+            __syncthreads();
+        } else {
+            // sort descending by (count, earlier list position first): bitonic over `cap` keys
+            for (int i = tid; i < cap; i += NT) key[i] = (i < n && A[i].cnt > 1) ? ((min(A[i].cnt, 0x7FFFF) << 12) | (4095 - i)) : 0;
+            __syncthreads();
+            for (int k2 = 2; k2 <= cap; k2 <<= 1)
+                for (int j = k2 >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < cap; i += NT) {
+                        const int ixj = i ^ j;
+                        if (ixj > i) {
+                            const int a = key[i], b = key[ixj];
+                            const bool desc = (i & k2) == 0;
+                            if (desc ? (a < b) : (a > b)) { key[i] = b; key[ixj] = a; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            // aux[r] = growth of the list when the r-th candidate is split (children - 1); prefix -> cut (:895-896)
+            for (int r = tid; r < cap; r += NT) {
+                int g = 0;
+                if (key[r] != 0) {
+                    const int i = 4095 - (key[r] & 4095);
+                    g = (cc[4 * i] > 0) + (cc[4 * i + 1] > 0) + (cc[4 * i + 2] > 0) + (cc[4 * i + 3] > 0) - 1;
+                }
+                aux[r] = g;
+            }
+            __syncthreads();
+            block_exclusive_scan(aux, cap, scratch);      // aux[r] = growth before splitting candidate r
+            if (tid == 0) s_P = 0;
+            __syncthreads();
+            for (int r = tid; r < cap; r += NT)
+                if (key[r] != 0 && n + aux[r] < N) atomicAdd(&s_P, 1);   // candidates form a prefix: growth is monotone
+            __syncthreads();
+            P = s_P;
+            for (int r = tid; r < P; r += NT) key[r] = 4095 - (key[r] & 4095);
+            __syncthreads();
+        }
+
+        // ---- creation index of every child, in split order (n1..n4 within a node) ----
+        for (int r = tid; r < P; r += NT) {
+            const int i = key[r];
+            aux[r] = (cc[4 * i] > 0) + (cc[4 * i + 1] > 0) + (cc[4 * i + 2] > 0) + (cc[4 * i + 3] > 0);
+        }
+        __syncthreads();
+        const int C = block_exclusive_scan(aux, P, scratch);
+        if (tid == 0) s_expand = 0;
+        for (int i = tid; i < n; i += NT) newpos[i] = 0;      // 1 marks "split this round"
+        __syncthreads();
+        for (int r = tid; r < P; r += NT) {
+            const int i = key[r];
+            newpos[i] = 1;
+            int created = aux[r], expand = 0;
+            for (int q = 0; q < 4; q++) {
+                const int cnt = cc[4 * i + q];
+                if (cnt > 0) {
+                    const int pos = C - 1 - created;            // push_front: later-created sits closer to the front
+                    QNode c; child_bounds(A[i], q, c); c.cnt = cnt;
+                    B[pos] = c;
+                    childpos[4 * i + q] = (short)pos;
+                    created++;
+                    expand += cnt > 1;
+                }
+            }
+            if (expand) atomicAdd(&s_expand, expand);
+        }
+        __syncthreads();
+        // survivors keep their relative order behind the new children
+        for (int i = tid; i < n; i += NT) aux[i] = newpos[i];
+        __syncthreads();
+        block_exclusive_scan(aux, n, scratch);                  // aux[i] = number of split nodes before position i
+        for (int i = tid; i < n; i += NT) {
+            if (!newpos[i]) { const int pos = C + i - aux[i]; B[pos] = A[i]; newpos[i] = pos; }
+            else newpos[i] = -1;
+        }
+        __syncthreads();
+        for (int k = tid; k < nC; k += NT) {
+            const int nd = nof[k];
+            int np = newpos[nd];
+            if (np < 0) {
+                const uint32_t c = ck[k];
+                const int q = quadrant(A[nd], (int)(c & 4095u) - CCM_MIN_BORDER, (int)((c >> 12) & 4095u) - CCM_MIN_BORDER);
+                np = childpos[4 * nd + q];
+            }
+            nof[k] = (uint16_t)np;
+        }
+        const int n_new = C + n - P;
+        const int nToExpand = s_expand;
+        __syncthreads();
+        for (int i = tid; i < n_new; i += NT) A[i] = B[i];
+        __syncthreads();
+        const int prev = n;
+        n = n_new;
+        if (n >= N || n == prev) break;                          // :833-836 / :901-902
+        if (!greedy && n + nToExpand * 3 > N) greedy = true;     // :838
+    }
+
+    // ---- best corner per node (:910-928): max response, earliest in (cell row, cell col, y, x) order ----
+    unsigned long long* best = reinterpret_cast<unsigned long long*>(cc);   // cap*8 B <= 4*cap*4 B
+    for (int i = tid; i < n; i += NT) best[i] = 0ull;
+    __syncthreads();
+    for (int k = tid; k < nC; k += NT) {
+        const uint32_t c = ck[k];
+        const int x = (int)(c & 4095u), y = (int)((c >> 12) & 4095u);
+        const int cj = (x - CCM_EDGE) / L.wCell, ci = (y - CCM_EDGE) / L.hCell;
+        const uint32_t ord = (uint32_t)(((ci * L.nCols + cj) * L.hCell + (y - CCM_EDGE - ci * L.hCell)) * L.wCell + (x - CCM_EDGE - cj * L.wCell));
+        const unsigned long long v = ((unsigned long long)(c >> 24) << 56) | ((unsigned long long)(0xFFFFFFFFu - ord) << 24) | (unsigned long long)(c & 0xFFFFFFu);
+        atomicMax(&best[nof[k]], v);
+    }
+    __syncthreads();
+    uint32_t* out = level_kps + (size_t)f * T.kps_per_frame + L.kp_off;
+    for (int i = tid; i < n; i += NT) {
+        const unsigned long long v = best[i];
+        out[i] = (uint32_t)(v & 0xFFFFFFu) | ((uint32_t)(v >> 56) << 24);
+    }
+    if (tid == 0) level_kp_count[f * CCM_MAX_LEVELS + lvl] = n;
+}
