@@ -91,11 +91,12 @@ class ORBextractor:
         for im in imgs:
             if im.dtype != np.uint8 or im.ndim != 2:
                 raise TypeError("images must be 2-D uint8 (CV_8UC1), as ORBextractor.cpp:1223 asserts")
+        rows, cols = imgs[0].shape
+        if rows == 0 or cols == 0:      # ORBextractor.cpp:1219-1220: empty image, outputs untouched
+            return [np.zeros(0, KP_DTYPE) for _ in imgs], [np.zeros((0, 32), np.uint8) for _ in imgs]
+        for im in imgs:
             if im.shape != imgs[0].shape or im.strides != imgs[0].strides or im.strides[1] != 1:
                 raise ValueError("batch images must share shape and row stride, with unit pixel stride")
-        rows, cols = imgs[0].shape
-        if rows == 0 or cols == 0:
-            return [np.zeros(0, KP_DTYPE) for _ in imgs], [np.zeros((0, 32), np.uint8) for _ in imgs]
         cap = self.max_keypoints_for(rows, cols)
         kp = np.zeros((n, cap), dtype=KP_DTYPE)
         desc = np.zeros((n, cap, 32), dtype=np.uint8)

@@ -1,0 +1,182 @@
+"""Parity of the CUDA extractor (through the C ABI) with the CPU oracle / reference fixtures. Bars:
+keypoint set, order, coordinates, FAST scores, quadtree selection, octave, size and ANGLE bit-exact;
+descriptor bits >= 99.9 % identical (north_star tolerance for float cos/sin; measured 100 % so far)."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+
+from _oracle import OracleExtractor
+from motioncheck_ccm_slam_b200.synth import make_frame, make_stream
+
+pytestmark = pytest.mark.gpu
+DESC_BITS_TOL = 0.999
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_extract.npz"))
+
+
+def make(cuda_lib, *args, **kw):
+    from motioncheck_ccm_slam_b200 import ORBextractor
+    return ORBextractor(*args, **kw)
+
+
+def assert_same(kp, desc, ko, do, tag=""):
+    assert len(kp) == len(ko), (tag, len(kp), len(ko))
+    for f in ("octave", "x", "y", "response", "size", "angle"):
+        assert np.array_equal(kp[f], ko[f]), (tag, f)
+    if len(kp):
+        same = 1.0 - np.unpackbits(desc ^ do, axis=1).mean()
+        assert same >= DESC_BITS_TOL, (tag, same)
+
+
+def test_c1_stream_batch_bit_exact(cuda_lib):
+    frames = make_stream(1000, 8)
+    ex = make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=8)
+    orc = OracleExtractor(1000, 1.2, 8, 20, 7)
+    kps, descs = ex.extract_batch(list(frames))
+    for f in range(8):
+        ko, do = orc(frames[f])
+        assert_same(kps[f], descs[f], ko, do, "frame %d" % f)
+        if f in (0, 7):     # stage taps
+            for l in range(8):
+                assert np.array_equal(ex.pyramid_level(l, f), orc.level_image(l)), ("pyr", f, l)
+                assert np.array_equal(ex.pyramid_level(l, f, blurred=True), orc.level_image(l, True)), ("blur", f, l)
+                assert np.array_equal(ex.level_corners(l, f), orc.level_corners(l)), ("corners", f, l)
+    assert ex.launch_count() > 0
+
+
+@pytest.mark.parametrize("name", ["c1", "small", "kitti_half"])
+def test_reference_fixtures(cuda_lib, name):
+    """Against the reference's own ORBextractor.cpp output (committed fixture, tests/golden/make_golden.py)."""
+    w, h, nf, nl, seed = [int(v) for v in G[name + "_cfg"]]
+    ex = make(cuda_lib, nf, 1.2, nl, 20, 7, max_width=w, max_height=h)
+    kp, desc = ex(make_frame(seed, w, h))
+    assert_same(kp, desc, G[name + "_kp"], G[name + "_desc"], name)
+
+
+@pytest.mark.parametrize("w,h,nf,nl,seed", [(1241, 376, 2000, 8, 3000), (752, 480, 2000, 8, 11), (641, 479, 700, 6, 5),
+                                             (320, 240, 300, 4, 7), (400, 300, 20, 5, 2), (752, 480, 5000, 8, 13),
+                                             (512, 512, 1500, 7, 17), (380, 560, 600, 5, 19)])
+def test_shapes_and_quotas(cuda_lib, w, h, nf, nl, seed):
+    ex = make(cuda_lib, nf, 1.2, nl, 20, 7, max_width=w, max_height=h, max_batch=2)
+    orc = OracleExtractor(nf, 1.2, nl, 20, 7)
+    frames = make_stream(seed, 2, w, h)
+    kps, descs = ex.extract_batch(list(frames))
+    for f in range(2):
+        ko, do = orc(frames[f])
+        assert_same(kps[f], descs[f], ko, do, (w, h, nf, f))
+
+
+def test_other_scale_and_thresholds(cuda_lib):
+    img = make_frame(23, 640, 480)
+    for args in [(800, 1.5, 4, 20, 7), (800, 1.1, 10, 30, 10), (800, 1.2, 8, 12, 12), (300, 2.0, 3, 40, 5)]:
+        kp, desc = make(cuda_lib, *args, max_width=640, max_height=480)(img)
+        ko, do = OracleExtractor(*args)(img)
+        assert_same(kp, desc, ko, do, args)
+
+
+def test_sparse_and_flat_images(cuda_lib):
+    ex = make(cuda_lib, 500, 1.2, 6, 20, 7, max_width=400, max_height=300)
+    orc = OracleExtractor(500, 1.2, 6, 20, 7)
+    flat = np.full((300, 400), 128, np.uint8)
+    kp, desc = ex(flat)
+    assert len(kp) == 0 and desc.shape == (0, 32)
+    # weak texture: most cells only fire at minThFAST (fallback path, ORBextractor.cpp:981-985)
+    rng = np.random.default_rng(3)
+    weak = (128 + rng.integers(-9, 10, (300, 400))).astype(np.uint8)
+    weak[100:140, 50:90] = 200
+    kp, desc = ex(weak)
+    ko, do = orc(weak)
+    assert len(ko) > 0
+    assert_same(kp, desc, ko, do, "weak")
+    # saturated checkerboard: plateaus of equal scores annihilate under strict NMS
+    cb = (np.indices((300, 400)).sum(0) // 16 % 2 * 255).astype(np.uint8)
+    kp, desc = ex(cb)
+    ko, do = orc(cb)
+    assert_same(kp, desc, ko, do, "checker")
+
+
+def test_strided_input_and_empty(cuda_lib):
+    ex = make(cuda_lib, 300, 1.2, 4, 20, 7, max_width=320, max_height=240)
+    big = np.zeros((260, 400), np.uint8)
+    img = make_frame(7, 320, 240)
+    big[10:250, 40:360] = img
+    view = big[10:250, 40:360]                      # step 400 != cols 320 (a cv::Mat ROI)
+    kp, desc = ex(view)
+    kc, dc = ex(img)
+    assert np.array_equal(kp, kc) and np.array_equal(desc, dc)
+    kp, desc = ex(np.zeros((0, 0), np.uint8))       # ORBextractor.cpp:1219: empty image returns silently
+    assert len(kp) == 0
+
+
+def test_batch64_equals_single_and_is_deterministic(cuda_lib):
+    frames = make_stream(2000, 64)
+    ex = make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=64)
+    k1, d1 = ex.extract_batch(list(frames))
+    k2, d2 = ex.extract_batch(list(frames))
+    one = make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=1)
+    orc = OracleExtractor(1000, 1.2, 8, 20, 7)
+    for f in range(64):
+        assert np.array_equal(k1[f], k2[f]) and np.array_equal(d1[f], d2[f])
+        assert abs(len(k1[f]) - 1000) <= 3 * 8 + 8, len(k1[f])       # every level met its quota
+        if f % 8 == 0:
+            ks, ds = one(frames[f])
+            assert np.array_equal(k1[f], ks) and np.array_equal(d1[f], ds)
+        if f in (31, 63):
+            ko, do = orc(frames[f])
+            assert_same(k1[f], d1[f], ko, do, f)
+
+
+def test_capacity_and_errors(cuda_lib):
+    from motioncheck_ccm_slam_b200._lib import CCM_E_CAPACITY, CcmError
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    ex = make(cuda_lib, 300, 1.2, 4, 20, 7, max_width=320, max_height=240)
+    img = make_frame(7, 320, 240)
+    kfull, dfull = ex(img)
+    kp = np.zeros(50, KP_DTYPE)
+    desc = np.zeros((50, 32), np.uint8)
+    n = ctypes.c_int()
+    rc = cuda_lib.ccm_orb_extract(ex._h, img.ctypes.data, 240, 320, 320, kp.ctypes.data, desc.ctypes.data, 50, ctypes.byref(n))
+    assert rc == 0 and n.value == len(kfull)
+    assert np.array_equal(kp, kfull[:50]) and np.array_equal(desc, dfull[:50])
+    with pytest.raises(CcmError) as e:
+        ex(make_frame(1, 400, 300))
+    assert e.value.code == CCM_E_CAPACITY
+    with pytest.raises(CcmError):
+        make(cuda_lib, 300, 1.2, 8, 20, 7, max_width=100, max_height=100)   # level 7 has no 30-px cell
+
+
+def test_pyramid_member_with_border(cuda_lib):
+    """mvImagePyramid (ORBextractor.h:138) incl. the 19-px BORDER_REFLECT_101 apron of ComputePyramid."""
+    img = make_frame(9, 320, 240)
+    ex = make(cuda_lib, 300, 1.2, 4, 20, 7, max_width=320, max_height=240)
+    ex(img)
+    orc = OracleExtractor(300, 1.2, 4, 20, 7)
+    orc(img)
+    for l in range(4):
+        lv = orc.level_image(l)
+        want = np.pad(lv, 19, mode="reflect")
+        assert np.array_equal(ex.pyramid_level(l, 0, with_border=True), want)
+        assert np.array_equal(ex.mvImagePyramid[l], lv)
+
+
+def test_device_resident_path_matches_host_path(cuda_lib):
+    torch = pytest.importorskip("torch")
+    frames = make_stream(3000, 4)
+    ex = make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=4)
+    kh, dh = ex.extract_batch(list(frames))
+    cap = ex.max_keypoints()
+    d_img = torch.from_numpy(frames).cuda()                          # [4, 480, 752] u8, pitch 752
+    d_kp = torch.zeros((4, cap, 6), dtype=torch.float32, device="cuda")
+    d_desc = torch.zeros((4, cap, 32), dtype=torch.uint8, device="cuda")
+    d_n = torch.zeros(4, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    ex.extract_batch_device(d_img.data_ptr(), 4, 480, 752, 752, 752 * 480, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+    ex.sync()
+    n = d_n.cpu().numpy()
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    for f in range(4):
+        assert n[f] == len(kh[f])
+        kp = d_kp[f, :n[f]].cpu().numpy().view(np.uint8).reshape(-1).view(KP_DTYPE)
+        assert np.array_equal(kp, kh[f])
+        assert np.array_equal(d_desc[f, :n[f]].cpu().numpy(), dh[f])
