@@ -1,0 +1,334 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200 ORB front-end (BASELINE.json metric / config).
+
+One "step" = one pass of the hot path over one batch of synthetic frames of one agent stream:
+ORBextractor::operator() on BATCH frames (752x480, 1000 features, 8 levels, 1.2 — EuRoC settings, configs[1]),
+followed (when the matcher library is present) by the tracking-side Hamming searches on the extracted frames.
+  value        frames/s with the input frames already resident in HBM (device-resident C-ABI entry point)
+  e2e          frames/s through the host-buffer C-ABI call a user of the reference interface makes
+               (pinned host images in, keypoints + descriptors out, copies inside the timed region)
+  roofline     dominant kernel: algorithmic bytes per launch / its CUDA-event time, against MEASURED_PEAKS.json
+  cpu_baseline the reference's own ORBextractor.cpp (oracle/_ref, compiled unmodified) on the host cores
+Launch: python bench.py [--gpus N --steps K --warmup W]; for N>1 via torch.distributed.run (one rank per GPU,
+one agent stream per rank, no data-path collective: "scaling": "weak").  --impl reference times the CPU reference.
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (width, height, nfeatures, nlevels)
+    "c1_euroc_752x480_1000kp": (752, 480, 1000, 8),
+    "c3_kitti_1241x376_2000kp": (1241, 376, 2000, 8),
+}
+SCALE, INI_TH, MIN_TH = 1.2, 20, 7
+METRIC = "ORB frames/s @752x480,1k kp"
+STAGES = ["pyramid_resize", "fast_cells", "gaussian_blur", "quadtree", "orient_describe"]
+
+
+def level_sizes(w, h, nlevels, scale=SCALE):
+    """Level geometry exactly as ORBextractor.cpp:579-592,1284-1286 computes it (float/double mix kept)."""
+    sf = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        sf.append(np.float32(np.float64(sf[-1]) * np.float64(np.float32(scale))))
+    out = []
+    for s in sf:
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
+
+
+def algorithmic_bytes(w, h, nfeatures, nlevels):
+    """Bytes per frame each stage must move at minimum, and the pipeline total."""
+    px = [a * b for a, b in level_sizes(w, h, nlevels)]
+    tot = sum(px)
+    per = {
+        "pyramid_resize": sum(px[:-1]) + sum(px[1:]),        # read level l-1, write level l
+        "fast_cells": tot,                                   # read every level once
+        "gaussian_blur": 2 * tot,                            # read level, write blurred level
+        "quadtree": 0,                                       # corner lists: latency-bound, no roofline claimed
+        "orient_describe": nfeatures * (749 + 512 + 56),     # patch + taps + outputs per keypoint
+    }
+    pipeline = w * h + 4 * tot + nfeatures * 56              # SURVEY §8d un-fused figure (4.89 MB at C1)
+    return per, pipeline
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CPU leg: the reference's own ORBextractor.cpp (oracle/_ref/libref_orb.so, compiled unmodified over the
+# OpenCV-4.13-exact shim), one extractor per host thread, one agent stream per thread. This is the ONLY place
+# bench.py touches oracle/: as the reported baseline, never as the measured product.
+# ----------------------------------------------------------------------------------------------------------
+def cpu_reference_fps(frames, nfeatures, nlevels, threads, frames_per_thread):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle
+    if _oracle.ref_available(mono=False):
+        kind, mk = "reference", lambda: _oracle.RefExtractor(nfeatures, SCALE, nlevels, INI_TH, MIN_TH, mono=False)
+    else:
+        kind, mk = "port", lambda: _oracle.OracleExtractor(nfeatures, SCALE, nlevels, INI_TH, MIN_TH)
+    exs = [mk() for _ in range(threads)]
+    exs[0](frames[0])                                   # warm-up (page-in, allocator)
+    done = [0] * threads
+
+    def work(t):
+        for i in range(frames_per_thread):
+            exs[t](frames[(t * frames_per_thread + i) % len(frames)])   # ctypes releases the GIL during the call
+            done[t] += 1
+
+    ths = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    t0 = time.perf_counter()
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    dt = time.perf_counter() - t0
+    return sum(done) / dt, dt, kind
+
+
+def run_reference(args, wl, rank):
+    """--impl reference: the reference's CPU implementation of the path on all host threads; rank 0 only."""
+    if rank != 0:
+        return
+    from motioncheck_ccm_slam_b200.synth import make_stream
+    w, h, nf, nl = WORKLOADS[wl]
+    cores = os.cpu_count() or 1
+    frames = make_stream(1000, 16, w, h)
+    per_step = 8                                         # frames per thread per step: a bounded sample of the 64-frame batch
+    for _ in range(max(args.warmup, 0)):
+        cpu_reference_fps(frames, nf, nl, cores, 1)
+    tot_frames, tot_t, kind = 0, 0.0, "reference"
+    for _ in range(args.steps):
+        fps, dt, kind = cpu_reference_fps(frames, nf, nl, cores, per_step)
+        tot_frames += per_step * cores
+        tot_t += dt
+    v = tot_frames / tot_t
+    sample = "%d steps x %d threads x %d frames of the %s stream (seed 1000)" % (args.steps, cores, per_step, wl)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / max(args.steps, 1), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": wl, "frames_per_step": per_step * cores, "host": "cpu"},
+        "cpu_baseline": {"value": v, "unit": "frames/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ----------------------------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------------------------
+def run_ours(args, wl, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from motioncheck_ccm_slam_b200 import ORBextractor
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    from motioncheck_ccm_slam_b200.synth import make_stream
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w, h, nf, nl = WORKLOADS[wl]
+    B, R = args.batch, args.rotate
+    per_stage_bytes, pipeline_bytes = algorithmic_bytes(w, h, nf, nl)
+
+    # one agent stream per rank: R rotating batches of B frames, so that inputs exceed the 126 MB L2
+    frames = np.stack([make_stream(1000 * (rank + 1) + 17 * r, B, w, h) for r in range(R)])        # [R,B,h,w] u8
+    ex = ORBextractor(nf, SCALE, nl, INI_TH, MIN_TH, max_width=w, max_height=h, max_batch=B, device=local_rank)
+    cap = ex.max_keypoints()
+    ext = torch.cuda.ExternalStream(ex.stream(), device=dev)
+
+    pitch = (w + 31) // 32 * 32                                                                      # device rows start on 32-B sectors
+    d_frames = torch.zeros((R, B, h, pitch), dtype=torch.uint8, device=dev)
+    d_frames[..., :w] = torch.from_numpy(frames).to(dev)
+    d_kp = torch.zeros((B, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros((B,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+
+    def step_device(i):
+        src = d_frames[i % R]
+        ex.extract_batch_device(src.data_ptr(), B, h, w, pitch, pitch * h, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput (value) ----
+    for i in range(args.warmup):
+        step_device(i)
+    ex.sync()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ex.set_stage_timing(True)
+    l0 = ex.launch_count()
+    barrier()
+    with torch.cuda.stream(ext):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            step_device(args.warmup + i)
+        e1.record()
+    ex.sync()
+    barrier()
+    dev_ms = e0.elapsed_time(e1)
+    launches = ex.launch_count() - l0
+    stage_ms, stage_calls = ex.get_stage_ms(reset=True)
+    ex.set_stage_timing(False)
+    n_kp = int(d_n.sum().item())
+
+    # ---- end to end through the host-buffer C-ABI call (pinned host images in, host keypoints/descriptors out) ----
+    pin = torch.from_numpy(frames).pin_memory()
+    pin_np = pin.numpy()
+    out_kp = torch.zeros((B, cap, 6), dtype=torch.float32).pin_memory()
+    out_desc = torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory()
+    out_n = (ctypes.c_int * B)()
+
+    def step_host(i):
+        r = i % R
+        ptrs = (ctypes.c_void_p * B)(*[pin_np[r, f].ctypes.data for f in range(B)])
+        ex.extract_batch_raw(ptrs, B, h, w, w, out_kp.data_ptr(), out_desc.data_ptr(), cap, out_n)
+
+    for i in range(args.warmup):
+        step_host(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_host(args.warmup + i)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    n_kp_host = int(sum(out_n[:]))
+
+    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)          # max over ranks
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    frames_total = B * args.steps * world
+    value = frames_total / (dev_ms * 1e-3)
+    e2e = frames_total / (e2e_ms * 1e-3)
+    peak, peak_kind = peaks()
+    per_launch_ms = [m / max(stage_calls, 1) for m in stage_ms]
+    dom = int(np.argmax(per_launch_ms))
+    dom_bytes = per_stage_bytes[STAGES[dom]] * B
+    achieved = dom_bytes / (per_launch_ms[dom] * 1e-3) / 1e9 if per_launch_ms[dom] > 0 else 0.0
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu --set full capture
+    if os.path.exists(tp):
+        with open(tp) as f:
+            traffic = json.load(f).get(STAGES[dom])
+    line = {
+        "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": wl, "frames_per_step_per_gpu": B, "nfeatures": nf, "nlevels": nl, "scale": SCALE,
+                   "agents": world, "parallelism": "agent-stream per GPU, no data-path collective",
+                   "l2": "inputs larger than L2: %d rotating %d-frame batches (%.0f MB) + %.0f MB of pyramid scratch rewritten per step"
+                         % (R, B, frames.nbytes / 1e6, 2 * sum(a * b for a, b in level_sizes(w, h, nl)) * B / 1e6),
+                   "keypoints_per_frame": n_kp / B},
+        "roofline": {"bound": "hbm", "kernel": STAGES[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
+                     "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": per_launch_ms[dom]},
+        "roofline_pipeline": {"bound": "hbm", "achieved": value / world * pipeline_bytes / 1e9, "peak": peak, "unit": "GB/s",
+                              "frac": value / world * pipeline_bytes / 1e9 / peak, "algorithmic_bytes_per_frame": pipeline_bytes},
+        "stage_ms_per_step": dict(zip(STAGES, per_launch_ms)),
+        "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": B * w * h,
+                "d2h_bytes_per_step": B * cap * 56 + 4 * B, "keypoints_per_frame": n_kp_host / B},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+    }
+    if not args.no_cpu and world == 1:
+        cores = os.cpu_count() or 1
+        fpt = 24
+        fps, dt, kind = cpu_reference_fps(frames[0], nf, nl, cores, fpt)
+        line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
+                                "sample": "%d threads x %d frames of the same stream, %.1f s" % (cores, fpt, dt)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c1_euroc_752x480_1000kp", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=64, help="frames in flight per step (configs[1]: 64)")
+    ap.add_argument("--rotate", type=int, default=8, help="distinct input batches cycled through (inputs > L2)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, args.workload, rank)
+    else:
+        run_ours(args, args.workload, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

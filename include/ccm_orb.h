@@ -82,6 +82,13 @@ void* ccm_orb_stream(ccm_orb* h);
 /* kernels launched by this handle since creation (bench.py's gpu_launches) */
 long long ccm_orb_launch_count(const ccm_orb* h);
 
+/* Per-stage device time of the extractor pipeline, measured with CUDA events on the handle's stream (bench.py's
+ * live roofline figure). Stages: 0 pyramid resize (K1), 1 FAST cells (K2+K3), 2 Gaussian blur (K6),
+ * 3 quadtree (K4), 4 orientation + rBRIEF (K5+K7). sum_ms[CCM_N_STAGES] accumulates over *calls batches. */
+#define CCM_N_STAGES 5
+int ccm_orb_set_stage_timing(ccm_orb* h, int enable);
+int ccm_orb_get_stage_ms(ccm_orb* h, double* sum_ms, long long* calls, int reset);
+
 /* mvImagePyramid[level] of frame `frame` of the last call (ORBextractor.h:138). with_border != 0 adds the 19-px
  * BORDER_REFLECT_101 apron (ORBextractor.cpp:1295,1300). out has out_step bytes per row. */
 int ccm_orb_get_pyramid_level(ccm_orb* h, int frame, int level, int with_border, uint8_t* out, size_t out_step,

@@ -36,6 +36,8 @@ SIGNATURES = {
     "ccm_orb_sync": (_i, [_vp]),
     "ccm_orb_stream": (_vp, [_vp]),
     "ccm_orb_launch_count": (_c.c_longlong, [_vp]),
+    "ccm_orb_set_stage_timing": (_i, [_vp, _i]),
+    "ccm_orb_get_stage_ms": (_i, [_vp, _c.POINTER(_c.c_double), _c.POINTER(_c.c_longlong), _i]),
     "ccm_orb_get_pyramid_level": (_i, [_vp, _i, _i, _i, _vp, _sz, _ip, _ip]),
     "ccm_orb_debug_blurred_level": (_i, [_vp, _i, _i, _vp, _sz, _ip, _ip]),
     "ccm_orb_debug_level_corners": (_i, [_vp, _i, _i, _vp, _i, _ip]),

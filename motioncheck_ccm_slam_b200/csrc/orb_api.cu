@@ -35,6 +35,12 @@ struct ccm_orb {
     ccm_keypoint* h_kp = nullptr; uint8_t* h_desc = nullptr; int* h_n = nullptr;
     cudaStream_t stream = nullptr;
     long long launches = 0;
+    // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
+    bool stage_timing = false;
+    cudaEvent_t ev[CCM_N_STAGES + 1] = {};
+    double stage_ms[CCM_N_STAGES] = {};
+    long long stage_calls = 0;
+    bool stage_pending = false;
     int last_frames = 0;
     const uint8_t* last_l0 = nullptr; size_t last_l0_pitch = 0, last_l0_stride = 0;
     std::string err;
@@ -173,6 +179,20 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     return CCM_OK;
 }
 
+// Fold the event intervals of the previous timed batch into the per-stage sums (waits for that batch).
+static int collect_stage_times(ccm_orb* h) {
+    if (!h->stage_pending) return CCM_OK;
+    CK(cudaEventSynchronize(h->ev[CCM_N_STAGES]));
+    for (int i = 0; i < CCM_N_STAGES; i++) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, h->ev[i], h->ev[i + 1]));
+        h->stage_ms[i] += ms;
+    }
+    h->stage_calls++;
+    h->stage_pending = false;
+    return CCM_OK;
+}
+
 // One batch through K1..K7 on the handle's stream. Level 0 is read in place from (l0, pitch, stride).
 static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, size_t l0_stride,
                         ccm_keypoint* d_kp, uint8_t* d_desc, int* d_n, int capacity) {
@@ -182,25 +202,33 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
     T.l[0].img_stride = l0_stride;
     h->last_frames = n; h->last_l0 = l0; h->last_l0_pitch = l0_pitch; h->last_l0_stride = l0_stride;
     cudaStream_t s = h->stream;
+    if (h->stage_timing) { int rc = collect_stage_times(h); if (rc != CCM_OK) return rc; }
+    const bool st = h->stage_timing;
     CK(cudaMemsetAsync(h->d_corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
+    if (st) CK(cudaEventRecord(h->ev[0], s));
     for (int l = 1; l < T.nlevels; l++) {
         dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
         k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
         h->launches++;
     }
+    if (st) CK(cudaEventRecord(h->ev[1], s));
     k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_corners, h->d_corner_count);
     h->launches++;
+    if (st) CK(cudaEventRecord(h->ev[2], s));
     for (int l = 0; l < T.nlevels; l++) {
         dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 31) / 32, n);
         k_blur_level<<<g, 256, 0, s>>>(T, l);
         h->launches++;
     }
+    if (st) CK(cudaEventRecord(h->ev[3], s));
     k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, h->d_corners, h->d_corner_count, h->d_node_of,
                                                           h->d_level_kps, h->d_level_kp_count);
     h->launches++;
+    if (st) CK(cudaEventRecord(h->ev[4], s));
     k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, h->d_level_kps, h->d_level_kp_count,
                                                                         (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
     h->launches++;
+    if (st) { CK(cudaEventRecord(h->ev[5], s)); h->stage_pending = true; }
     CK(cudaGetLastError());
     return CCM_OK;
 }
@@ -253,6 +281,7 @@ void ccm_orb_destroy(ccm_orb* h) {
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_arena(h);
+    for (int i = 0; i <= CCM_N_STAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -272,6 +301,27 @@ int ccm_orb_get_tables(const ccm_orb* h, float* scale, float* inv_scale, float* 
 int ccm_orb_max_keypoints(const ccm_orb* h) { return h ? h->max_kps : CCM_E_BADARG; }
 void* ccm_orb_stream(ccm_orb* h) { return h ? (void*)h->stream : nullptr; }
 long long ccm_orb_launch_count(const ccm_orb* h) { return h ? h->launches : 0; }
+
+int ccm_orb_set_stage_timing(ccm_orb* h, int enable) {
+    if (!h) return CCM_E_BADARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (enable && !h->ev[0])
+        for (int i = 0; i <= CCM_N_STAGES; i++) CK(cudaEventCreate(&h->ev[i]));
+    if (!enable) { int rc = collect_stage_times(h); if (rc != CCM_OK) return rc; }
+    h->stage_timing = enable != 0;
+    return CCM_OK;
+}
+
+int ccm_orb_get_stage_ms(ccm_orb* h, double* sum_ms, long long* calls, int reset) {
+    if (!h) return CCM_E_BADARG;
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = collect_stage_times(h);
+    if (rc != CCM_OK) return rc;
+    for (int i = 0; i < CCM_N_STAGES; i++) { if (sum_ms) sum_ms[i] = h->stage_ms[i]; if (reset) h->stage_ms[i] = 0; }
+    if (calls) *calls = h->stage_calls;
+    if (reset) h->stage_calls = 0;
+    return CCM_OK;
+}
 
 int ccm_orb_sync(ccm_orb* h) {
     if (!h) return CCM_E_BADARG;

@@ -115,6 +115,21 @@ class ORBextractor:
         self._check(self._lib.ccm_orb_extract_batch_device(self._h, d_imgs_ptr, n, rows, cols, pitch, frame_stride,
                                                            d_kp_ptr, d_desc_ptr, capacity, d_n_ptr))
 
+    def extract_batch_raw(self, img_ptrs, n, rows, cols, step, out_kp_ptr, out_desc_ptr, capacity, out_n):
+        """ccm_orb_extract_batch with caller-owned host buffers (e.g. pinned): no numpy allocation per call."""
+        self._check(self._lib.ccm_orb_extract_batch(self._h, img_ptrs, n, rows, cols, step, out_kp_ptr, out_desc_ptr,
+                                                    capacity, out_n))
+
+    def set_stage_timing(self, on):
+        self._check(self._lib.ccm_orb_set_stage_timing(self._h, 1 if on else 0))
+
+    def get_stage_ms(self, reset=False):
+        """(per-stage summed CUDA-event ms [resize, fast, blur, quadtree, describe], number of timed batches)."""
+        ms = (ctypes.c_double * 5)()
+        calls = ctypes.c_longlong()
+        self._check(self._lib.ccm_orb_get_stage_ms(self._h, ms, ctypes.byref(calls), 1 if reset else 0))
+        return list(ms), int(calls.value)
+
     def sync(self):
         self._check(self._lib.ccm_orb_sync(self._h))
 

@@ -111,20 +111,22 @@ void ocv_border_reflect101_u8(const uint8_t* src, int w, int h, size_t sstep,
  * exact integer row+column accumulation, one final round-half-up: (sum + 2^15) >> 16. */
 void ocv_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep) {
     static const int k[7] = {18, 34, 48, 56, 48, 34, 18};
-    std::vector<int> hbuf((size_t)w * h);
+    std::vector<uint16_t> hbuf((size_t)w * h);          /* row sums <= 255*256 fit u16 */
+    std::vector<uint8_t> pad((size_t)w + 6);
     for (int y = 0; y < h; y++) {
         const uint8_t* s = src + (size_t)y * sstep;
-        for (int x = 0; x < w; x++) {
-            int acc = 0;
-            for (int i = 0; i < 7; i++) acc += k[i] * s[reflect101(x + i - 3, w)];
-            hbuf[(size_t)y * w + x] = acc;
-        }
+        for (int x = -3; x < w + 3; x++) pad[x + 3] = s[reflect101(x, w)];
+        uint16_t* hb = &hbuf[(size_t)y * w];
+        const uint8_t* p = pad.data();
+        for (int x = 0; x < w; x++)
+            hb[x] = (uint16_t)(k[0] * (p[x] + p[x + 6]) + k[1] * (p[x + 1] + p[x + 5]) + k[2] * (p[x + 2] + p[x + 4]) + k[3] * p[x + 3]);
     }
     for (int y = 0; y < h; y++) {
+        const uint16_t* r[7];
+        for (int i = 0; i < 7; i++) r[i] = &hbuf[(size_t)reflect101(y + i - 3, h) * w];
         uint8_t* d = dst + (size_t)y * dstep;
         for (int x = 0; x < w; x++) {
-            int acc = 0;
-            for (int i = 0; i < 7; i++) acc += k[i] * hbuf[(size_t)reflect101(y + i - 3, h) * w + x];
+            const int acc = k[0] * (r[0][x] + r[6][x]) + k[1] * (r[1][x] + r[5][x]) + k[2] * (r[2][x] + r[4][x]) + k[3] * r[3][x];
             d[x] = (uint8_t)((acc + 32768) >> 16);
         }
     }
@@ -165,9 +167,29 @@ int ocv_fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, i
     if (threshold > 255) threshold = 255;
     std::vector<int> sc((size_t)w * h, 0);
     std::vector<uint8_t> is((size_t)w * h, 0);
+    const ptrdiff_t s_ = (ptrdiff_t)step;
+    const ptrdiff_t ring[16] = {3 * s_,  3 * s_ + 1,  2 * s_ + 2,  s_ + 3,  3,  -s_ + 3,  -2 * s_ + 2, -3 * s_ + 1,
+                                -3 * s_, -3 * s_ - 1, -2 * s_ - 2, -s_ - 3, -3, s_ - 3,   2 * s_ - 2,  3 * s_ - 1};
     for (int y = 3; y < h - 3; y++)
         for (int x = 3; x < w - 3; x++) {
-            const int s = ocv_fast_score_9_16(img + (size_t)y * step + x, step);
+            /* early rejection, as OpenCV's scalar path does (same result: a pixel is a corner at t iff score >= t):
+             * any arc of 9 ring pixels holds at least 2 of the 4 compass pixels {0,4,8,12} */
+            const uint8_t* p = img + (size_t)y * step + x;
+            const int v = p[0], hi = v + threshold, lo = v - threshold;
+            const int c0 = p[ring[0]], c4 = p[ring[4]], c8 = p[ring[8]], c12 = p[ring[12]];
+            const int nb = (c0 > hi) + (c4 > hi) + (c8 > hi) + (c12 > hi);
+            const int nd = (c0 < lo) + (c4 < lo) + (c8 < lo) + (c12 < lo);
+            if (nb < 2 && nd < 2) continue;
+            unsigned mb = 0, md = 0;
+            for (int k = 0; k < 16; k++) { const int q = p[ring[k]]; mb |= (unsigned)(q > hi) << k; md |= (unsigned)(q < lo) << k; }
+            bool corner = false;
+            for (unsigned m : {mb, md}) {
+                unsigned z = m | (m << 16);
+                z &= z >> 1; z &= z >> 2; z &= z >> 4; z &= z >> 1;
+                if (z) corner = true;
+            }
+            if (!corner) continue;
+            const int s = ocv_fast_score_9_16(p, step);
             if (s >= threshold) { sc[(size_t)y * w + x] = s; is[(size_t)y * w + x] = 1; }
         }
     int n = 0;
