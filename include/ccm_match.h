@@ -1,0 +1,147 @@
+/* libccm_orb_cuda.so — C ABI of the B200 (sm_100a) Hamming-distance searches of CCM-SLAM's ORBmatcher.
+ *
+ * The reference has no FFI layer: the boundary is the C++ class cslam::ORBmatcher
+ * (cslam/include/cslam/ORBmatcher.h:77-132, cslam/src/ORBmatcher.cpp). The drop-in class keeps that declaration;
+ * each Search* body gathers what the reference gathers on the host (projection geometry u, v, radius, predicted
+ * level, the query map points' descriptors, "has a good map point" flags) and calls one entry point below, which
+ * returns exactly the state the reference loop leaves behind (who matched whom, in the reference's greedy order,
+ * after the rotation-histogram pruning). Plain pointers and sizes; no exceptions; no CPU fallback.
+ *
+ * Memory spaces: every pointer argument of a function whose name does not end in `_device` is HOST memory; the
+ * call is synchronous. `_device` variants take device pointers, enqueue on the matcher's stream and return
+ * without waiting (pair with ccm_matcher_sync), so the extractor's output feeds the matcher without a host copy.
+ */
+#ifndef CCM_MATCH_H_
+#define CCM_MATCH_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "ccm_orb.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CCM_TH_HIGH 100      /* ORBmatcher::TH_HIGH, ORBmatcher.cpp:63 */
+#define CCM_TH_LOW 50        /* ORBmatcher::TH_LOW,  :64 */
+#define CCM_HISTO_LENGTH 30  /* ORBmatcher::HISTO_LENGTH, :65 */
+
+typedef struct ccm_matcher ccm_matcher;         /* one device, one CUDA stream, a grow-only scratch arena */
+typedef struct ccm_frame_pack ccm_frame_pack;   /* device copy of what the matcher reads of a Frame / KeyFrame */
+
+int ccm_matcher_create(int device, ccm_matcher** out);
+void ccm_matcher_destroy(ccm_matcher* m);
+const char* ccm_matcher_last_error(const ccm_matcher* m);   /* m == NULL: error of the failed create */
+int ccm_matcher_sync(ccm_matcher* m);
+void* ccm_matcher_stream(ccm_matcher* m);                   /* cudaStream_t */
+long long ccm_matcher_launch_count(const ccm_matcher* m);
+
+/* static ORBmatcher::DescriptorDistance (ORBmatcher.cpp:1653-1669) for n descriptor pairs: out[i] = |a[i] xor b[i]| */
+int ccm_descriptor_distance(ccm_matcher* m, const uint8_t* a, const uint8_t* b, int n, int* out);
+
+/* ---- frame pack: descriptors + undistorted keypoints + the feature grid ------------------------------------
+ * Frame: mDescriptors, mvKeysUn, mGrid[75][48] (Frame.h:128-149; AssignFeaturesToGrid/PosInGrid, Frame.cpp:103-118,
+ * 255-265); KeyFrame: same fields (KeyFrame.cpp:1162-1201). The grid is built on the device. */
+typedef struct ccm_grid_params {
+    float min_x, min_y;        /* mnMinX, mnMinY */
+    float inv_w, inv_h;        /* mfGridElementWidthInv, mfGridElementHeightInv (Frame.cpp:87-88) */
+    int cols, rows;            /* FRAME_GRID_COLS 75, FRAME_GRID_ROWS 48 (Frame.h:51-52); cols*rows <= 8192 */
+} ccm_grid_params;
+
+int ccm_frame_pack_create(ccm_matcher* m, int capacity /* <= 65535 features */, ccm_frame_pack** out);
+void ccm_frame_pack_destroy(ccm_frame_pack* p);
+/* host arrays of n features: desc [n][32], x/y = mvKeysUn[i].pt, octave, angle (degrees) */
+int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, const uint8_t* desc, const float* x,
+                          const float* y, const int* octave, const float* angle);
+/* straight from ccm_orb_extract_batch_device output (device pointers; *d_n features); the keypoints are used as
+ * mvKeysUn, i.e. a camera without distortion (Frame.cpp:279-283), or pass d_xy_un [capacity][2] to override them */
+int ccm_frame_pack_from_extractor_device(ccm_frame_pack* p, const ccm_grid_params* g, const ccm_keypoint* d_kp,
+                                         const uint8_t* d_desc, const int* d_n, const float* d_xy_un);
+/* test tap: the grid as CSR over cells in (ix*rows + iy) order: cell_start[cols*rows+1], items[n]; *n_items out */
+int ccm_frame_pack_get_grid(ccm_frame_pack* p, int* cell_start, int* items, int* n_items);
+int ccm_frame_pack_count(ccm_frame_pack* p, int* n);
+
+/* ---- windowed searches (GetFeaturesInArea candidates) -------------------------------------------------------
+ * One query per map point / feature the reference loop reaches; the loop's host-side early `continue`s are the
+ * valid flag. Query order is the reference's loop order: results are those of the sequential greedy loop. */
+typedef struct ccm_window_query {
+    float u, v;            /* projected position */
+    float r;               /* search radius as passed to GetFeaturesInArea */
+    float angle;           /* query keypoint angle (rotation histogram), degrees */
+    int16_t min_level;     /* level window: candidates with octave < min_level are skipped; */
+    int16_t max_level;     /* with max_level >= 0, octave > max_level too (Frame.cpp:236-244; KeyFrame callers :397-400) */
+    uint32_t flags;        /* CCM_Q_* */
+} ccm_window_query;
+#define CCM_Q_VALID 1u     /* the reference reaches the candidate loop for this query */
+#define CCM_Q_OBS 2u       /* PROJ_MAPPOINTS/LASTFRAME: pMP->Observations()>0 (a later query is blocked by this claim) */
+#define CCM_Q_CLAIMS 2u    /* PROJ_KF_SIM3: pMP->GetIndexInKeyFrame(pKF)==-1, the accept writes vpMatched (:436-440) */
+
+typedef struct ccm_match_result {
+    int best_idx;          /* -1: no candidate */
+    int best_dist, best_dist2;
+    int accepted;
+} ccm_match_result;
+
+#define CCM_WIN_PROJ_MAPPOINTS 0   /* SearchByProjection(Frame&, vector<mpptr>&, th)           ORBmatcher.cpp:71-148   */
+#define CCM_WIN_PROJ_LASTFRAME 1   /* SearchByProjection(Frame&, const Frame&, th)             :1350-1476              */
+#define CCM_WIN_PROJ_KF_SIM3 2     /* SearchByProjection(kfptr, Scw, vpPoints, vpMatched, th)  :308-446                */
+#define CCM_WIN_BEST 3             /* SearchBySim3 passes :1216-1252,:1296-1327; Fuse distance phase :929-962,:1082-1103 */
+#define CCM_WIN_INIT 4             /* SearchForInitialization                                  :448-563                */
+
+typedef struct ccm_window_params {
+    int mode;                  /* CCM_WIN_* */
+    float nnratio;             /* mfNNratio */
+    int th_dist;               /* TH_HIGH or TH_LOW as the reference function uses */
+    int check_orientation;     /* mbCheckOrientation (LASTFRAME, INIT) */
+    const float* inv_sigma2;   /* CCM_WIN_BEST only: mvInvLevelSigma2 for Fuse's chi2 gate (:950), NULL = no gate; HOST ptr, <= 16 */
+    int n_levels;
+} ccm_window_params;
+
+/* holder [n_targets] in/out: -1 no map point, -2 map point with Observations()>0 (blocks), -3 map point with
+ * Observations()==0; on return a claimed target holds the claiming query index. INIT mode: holder is output only
+ * (vnMatches21). res [nq] per-query outcome (may be NULL). *nmatches = the reference function's return value
+ * (for CCM_WIN_BEST: number of accepted queries). */
+int ccm_search_window(ccm_matcher* m, ccm_frame_pack* targets, const ccm_window_params* prm, int nq,
+                      const ccm_window_query* q, const uint8_t* q_desc, int* holder, ccm_match_result* res, int* nmatches);
+
+/* batched, device-resident: job j searches packs[j] with queries d_q + j*q_stride (d_nq[j] of them, <= q_stride);
+ * d_holder [n_jobs][holder_stride]; d_res [n_jobs][q_stride]; d_nmatches [n_jobs]. One CTA per job, one launch. */
+int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs, int n_jobs, const ccm_window_params* prm,
+                                   const int* d_nq, int q_stride, const ccm_window_query* d_q, const uint8_t* d_q_desc,
+                                   int* d_holder, int holder_stride, ccm_match_result* d_res, int* d_nmatches);
+
+/* ---- BoW-guided searches -----------------------------------------------------------------------------------
+ * A DBoW2::FeatureVector is given as node_id per feature (-1 = not in the vector): nodes iterate ascending,
+ * features inside a node ascending (FeatureVector.cpp:31-45). valid = "has a good map point". */
+#define CCM_BOW_KF_FRAME 0   /* SearchByBoW(kfptr, Frame&, out)   ORBmatcher.cpp:178-306: accept best <= TH_LOW; valid_b ignored */
+#define CCM_BOW_KF_KF 1      /* SearchByBoW(kfptr, kfptr, out)    :565-698: accept best < TH_LOW */
+/* match_a [n_a]: matched b index or -1 (vpMatches12); match_b [n_b]: matched a index or -1 (vpMapPointMatches) */
+int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientation,
+                   int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* valid_a, const float* angle_a,
+                   int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* valid_b, const float* angle_b,
+                   int* match_a, int* match_b, ccm_match_result* res_a, int* nmatches);
+
+/* ---- server keyframe-database search (BASELINE.json configs[4]) --------------------------------------------
+ * Best and second-best Hamming distance of every query descriptor over a (shard of a) target descriptor database,
+ * first-wins on ties: the inner loop of SearchByBoW(KF,KF) (:607-637) with one all-inclusive node. */
+typedef struct ccm_best2 {
+    uint32_t idx;          /* global target index of the best match (index_base + local), 0xFFFFFFFF if the shard is empty */
+    uint16_t d1, d2;       /* best and second-best distance, 256 = none */
+} ccm_best2;
+
+/* device-resident, asynchronous: d_out [nq] = best-2 of d_q [nq][32] over d_targets [nt][32] */
+int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
+                                    uint32_t index_base, ccm_best2* d_out);
+/* cross-shard merge after the allgather of per-shard records: d_parts [n_parts][nq] -> d_out [nq], and the
+ * reference accept rule (best < TH_LOW and (float)best < nnratio*(float)best2, :641-643) -> d_accept [nq] (may be NULL) */
+int ccm_match_allpairs_merge_device(ccm_matcher* m, const ccm_best2* d_parts, int n_parts, int nq, float nnratio,
+                                    ccm_best2* d_out, uint8_t* d_accept);
+/* host convenience: upload, search one shard, download */
+int ccm_match_allpairs_best2(ccm_matcher* m, const uint8_t* q, int nq, const uint8_t* targets, long long nt,
+                             uint32_t index_base, ccm_best2* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCM_MATCH_H_ */
