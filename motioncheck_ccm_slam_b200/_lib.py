@@ -1,4 +1,4 @@
-"""ctypes binding of libccm_orb_cuda.so (include/ccm_orb.h). Fails loudly when the library is missing:
+"""ctypes binding of libccm_orb_cuda.so (include/ccm_orb.h, include/ccm_match.h). Fails loudly when the library is missing:
 there is no CPU fallback anywhere in this package."""
 import ctypes
 import os
@@ -42,6 +42,49 @@ SIGNATURES = {
     "ccm_orb_debug_blurred_level": (_i, [_vp, _i, _i, _vp, _sz, _ip, _ip]),
     "ccm_orb_debug_level_corners": (_i, [_vp, _i, _i, _vp, _i, _ip]),
 }
+
+
+
+class GridParams(ctypes.Structure):
+    _fields_ = [("min_x", ctypes.c_float), ("min_y", ctypes.c_float), ("inv_w", ctypes.c_float), ("inv_h", ctypes.c_float),
+                ("cols", ctypes.c_int), ("rows", ctypes.c_int)]
+
+
+class WindowQuery(ctypes.Structure):
+    _fields_ = [("u", ctypes.c_float), ("v", ctypes.c_float), ("r", ctypes.c_float), ("angle", ctypes.c_float),
+                ("min_level", ctypes.c_int16), ("max_level", ctypes.c_int16), ("flags", ctypes.c_uint32)]
+
+
+class WindowParams(ctypes.Structure):
+    _fields_ = [("mode", ctypes.c_int), ("nnratio", ctypes.c_float), ("th_dist", ctypes.c_int),
+                ("check_orientation", ctypes.c_int), ("inv_sigma2", ctypes.POINTER(ctypes.c_float)), ("n_levels", ctypes.c_int)]
+
+
+_ll, _u32, _f = _c.c_longlong, _c.c_uint32, _c.c_float
+_gp, _wp = _c.POINTER(GridParams), _c.POINTER(WindowParams)
+
+# every symbol include/ccm_match.h declares
+SIGNATURES.update({
+    "ccm_matcher_create": (_i, [_i, _c.POINTER(_vp)]),
+    "ccm_matcher_destroy": (None, [_vp]),
+    "ccm_matcher_last_error": (_c.c_char_p, [_vp]),
+    "ccm_matcher_sync": (_i, [_vp]),
+    "ccm_matcher_stream": (_vp, [_vp]),
+    "ccm_matcher_launch_count": (_ll, [_vp]),
+    "ccm_descriptor_distance": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "ccm_frame_pack_create": (_i, [_vp, _i, _c.POINTER(_vp)]),
+    "ccm_frame_pack_destroy": (None, [_vp]),
+    "ccm_frame_pack_upload": (_i, [_vp, _gp, _i, _vp, _vp, _vp, _vp, _vp]),
+    "ccm_frame_pack_from_extractor_device": (_i, [_vp, _gp, _vp, _vp, _vp, _vp]),
+    "ccm_frame_pack_get_grid": (_i, [_vp, _vp, _vp, _ip]),
+    "ccm_frame_pack_count": (_i, [_vp, _ip]),
+    "ccm_search_window": (_i, [_vp, _vp, _wp, _i, _vp, _vp, _vp, _vp, _ip]),
+    "ccm_search_window_batch_device": (_i, [_vp, _c.POINTER(_vp), _i, _wp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ccm_search_bow": (_i, [_vp, _i, _f, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ip]),
+    "ccm_match_allpairs_best2_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
+    "ccm_match_allpairs_merge_device": (_i, [_vp, _vp, _i, _i, _f, _vp, _vp]),
+    "ccm_match_allpairs_best2": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
+})
 
 _lib = None
 

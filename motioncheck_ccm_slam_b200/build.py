@@ -13,6 +13,7 @@ def sources():
     d = os.path.join(HERE, "csrc")
     out = [os.path.join(d, f) for f in sorted(os.listdir(d))]
     out.append(os.path.join(HERE, "..", "include", "ccm_orb.h"))
+    out.append(os.path.join(HERE, "..", "include", "ccm_match.h"))
     return out
 
 

@@ -4,3 +4,7 @@
 #include "orb_quadtree.cu"
 #include "orb_describe.cu"
 #include "orb_api.cu"
+#include "match_allpairs.cu"
+#include "match_window.cu"
+#include "match_bow.cu"
+#include "match_api.cu"

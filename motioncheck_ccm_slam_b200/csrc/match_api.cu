@@ -1,0 +1,476 @@
+// Host side of the matcher C ABI (include/ccm_match.h): frame packs, scratch arena, launches.
+// Compiled as part of the single translation unit ccm_orb_cuda.cu after match_allpairs.cu, match_window.cu, match_bow.cu.
+#include <algorithm>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/ccm_match.h"
+#include "match_common.cuh"
+
+static_assert(sizeof(WindowQueryDev) == sizeof(ccm_window_query), "window query layout");
+static_assert(sizeof(MatchResultDev) == sizeof(ccm_match_result), "match result layout");
+static_assert(sizeof(Best2Dev) == sizeof(ccm_best2) && sizeof(ccm_best2) == 8, "best2 layout");
+
+static thread_local std::string g_match_create_error = "";
+
+enum { MB_JOBS, MB_Q, MB_QDESC, MB_HOLDER, MB_RES, MB_NM, MB_SCRATCH, MB_PARTS, MB_A, MB_B, MB_C, MB_D, MB_E, MB_F, MB_G, MB_H, MB_COUNT };
+
+struct ccm_matcher {
+    int device = 0;
+    int sms = 0;
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+    struct Buf { void* p = nullptr; size_t cap = 0; } buf[MB_COUNT];
+    std::string err;
+};
+
+struct ccm_frame_pack {
+    ccm_matcher* m = nullptr;
+    int cap = 0;
+    int n_host = -1;      // -1: count lives on the device only
+    uint8_t* desc = nullptr; float* x = nullptr; float* y = nullptr; float* angle = nullptr; int* octave = nullptr;
+    int* cell_start = nullptr; int* items = nullptr; int* n = nullptr;
+    const uint8_t* desc_view = nullptr;   // descriptors borrowed from the extractor (zero-copy), else == desc
+    ccm_grid_params g = {};
+};
+
+#define MCK(call)                                                                                        \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            m->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+            return CCM_E_CUDA;                                                                           \
+        }                                                                                                \
+    } while (0)
+
+template <typename Tp> static int mbuf(ccm_matcher* m, int slot, size_t count, Tp** out) {
+    const size_t bytes = std::max<size_t>(count * sizeof(Tp), 256);
+    ccm_matcher::Buf& b = m->buf[slot];
+    if (b.cap < bytes) {
+        MCK(cudaStreamSynchronize(m->stream));
+        if (b.p) cudaFree(b.p);
+        b.p = nullptr; b.cap = 0;
+        const size_t want = bytes + bytes / 2;
+        MCK(cudaMalloc(&b.p, want));
+        b.cap = want;
+    }
+    *out = (Tp*)b.p;
+    return CCM_OK;
+}
+
+extern "C" {
+
+int ccm_matcher_create(int device, ccm_matcher** out) {
+    if (!out) return CCM_E_BADARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) {
+        g_match_create_error = e != cudaSuccess ? std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e)
+                                                : "no such CUDA device (there is no CPU fallback)";
+        return CCM_E_CUDA;
+    }
+    ccm_matcher* m = new ccm_matcher();
+    m->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_match_create_error = std::string("cuda init: ") + cudaGetErrorString(e);
+        delete m;
+        return CCM_E_CUDA;
+    }
+    cudaDeviceGetAttribute(&m->sms, cudaDevAttrMultiProcessorCount, device);
+    *out = m;
+    return CCM_OK;
+}
+
+void ccm_matcher_destroy(ccm_matcher* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
+    for (auto& b : m->buf) if (b.p) cudaFree(b.p);
+    delete m;
+}
+
+const char* ccm_matcher_last_error(const ccm_matcher* m) { return m ? m->err.c_str() : g_match_create_error.c_str(); }
+int ccm_matcher_sync(ccm_matcher* m) { if (!m) return CCM_E_BADARG; cudaSetDevice(m->device); MCK(cudaStreamSynchronize(m->stream)); return CCM_OK; }
+void* ccm_matcher_stream(ccm_matcher* m) { return m ? (void*)m->stream : nullptr; }
+long long ccm_matcher_launch_count(const ccm_matcher* m) { return m ? m->launches : 0; }
+
+int ccm_descriptor_distance(ccm_matcher* m, const uint8_t* a, const uint8_t* b, int n, int* out) {
+    if (!m || !a || !b || !out || n < 0) return CCM_E_BADARG;
+    if (n == 0) return CCM_OK;
+    cudaSetDevice(m->device);
+    uint8_t *da, *db; int* dout;
+    int rc;
+    if ((rc = mbuf(m, MB_A, (size_t)n * 32, &da))) return rc;
+    if ((rc = mbuf(m, MB_B, (size_t)n * 32, &db))) return rc;
+    if ((rc = mbuf(m, MB_C, (size_t)n, &dout))) return rc;
+    MCK(cudaMemcpyAsync(da, a, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(db, b, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+    k_descriptor_distance<<<(n + 255) / 256, 256, 0, m->stream>>>((const uint4*)da, (const uint4*)db, n, dout);
+    m->launches++;
+    MCK(cudaGetLastError());
+    MCK(cudaMemcpyAsync(out, dout, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
+/* ---- frame packs ------------------------------------------------------------------------------------------ */
+int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
+    if (!m || !out || capacity <= 0 || capacity > 65535) return CCM_E_BADARG;
+    *out = nullptr;
+    cudaSetDevice(m->device);
+    ccm_frame_pack* p = new ccm_frame_pack();
+    p->m = m; p->cap = capacity;
+    const size_t c = (size_t)capacity;
+    // one allocation, 256-B aligned sections
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_desc = 0, o_x = o_desc + up(c * 32), o_y = o_x + up(c * 4), o_ang = o_y + up(c * 4), o_oct = o_ang + up(c * 4),
+                 o_cs = o_oct + up(c * 4), o_it = o_cs + up((CCM_MAX_GRID_CELLS + 1) * 4), o_n = o_it + up(c * 4), total = o_n + 256;
+    uint8_t* base = nullptr;
+    cudaError_t e = cudaMalloc(&base, total);
+    if (e != cudaSuccess) { m->err = std::string("cudaMalloc(frame pack): ") + cudaGetErrorString(e); delete p; return CCM_E_CUDA; }
+    p->desc = base + o_desc; p->x = (float*)(base + o_x); p->y = (float*)(base + o_y); p->angle = (float*)(base + o_ang);
+    p->octave = (int*)(base + o_oct); p->cell_start = (int*)(base + o_cs); p->items = (int*)(base + o_it); p->n = (int*)(base + o_n);
+    p->desc_view = p->desc;
+    cudaMemsetAsync(base, 0, total, m->stream);
+    *out = p;
+    return CCM_OK;
+}
+
+void ccm_frame_pack_destroy(ccm_frame_pack* p) {
+    if (!p) return;
+    cudaSetDevice(p->m->device);
+    cudaStreamSynchronize(p->m->stream);
+    cudaFree(p->desc);
+    delete p;
+}
+
+static PackDev pack_dev(const ccm_frame_pack* p) {
+    PackDev d;
+    d.desc = p->desc_view; d.x = p->x; d.y = p->y; d.angle = p->angle; d.octave = p->octave;
+    d.cell_start = p->cell_start; d.items = p->items; d.n = p->n; d.cap = p->cap;
+    d.min_x = p->g.min_x; d.min_y = p->g.min_y; d.inv_w = p->g.inv_w; d.inv_h = p->g.inv_h; d.cols = p->g.cols; d.rows = p->g.rows;
+    return d;
+}
+
+static int check_grid(ccm_matcher* m, const ccm_grid_params* g) {
+    if (!g || g->cols <= 0 || g->rows <= 0 || (long long)g->cols * g->rows > CCM_MAX_GRID_CELLS) {
+        m->err = "grid must have 1..8192 cells";
+        return CCM_E_BADARG;
+    }
+    return CCM_OK;
+}
+
+int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, const uint8_t* desc, const float* x,
+                          const float* y, const int* octave, const float* angle) {
+    if (!p) return CCM_E_BADARG;
+    ccm_matcher* m = p->m;
+    if (n < 0 || (n > 0 && (!desc || !x || !y || !octave || !angle))) return CCM_E_BADARG;
+    if (n > p->cap) { m->err = "frame pack capacity too small"; return CCM_E_CAPACITY; }
+    int rc = check_grid(m, g);
+    if (rc) return rc;
+    cudaSetDevice(m->device);
+    p->g = *g; p->n_host = n; p->desc_view = p->desc;
+    if (n > 0) {
+        MCK(cudaMemcpyAsync(p->desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(p->x, x, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(p->y, y, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(p->octave, octave, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(p->angle, angle, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    }
+    MCK(cudaMemcpyAsync(p->n, &p->n_host, sizeof(int), cudaMemcpyHostToDevice, m->stream));
+    k_build_grid<<<1, 1024, 0, m->stream>>>(pack_dev(p), p->cell_start, p->items);
+    m->launches++;
+    MCK(cudaGetLastError());
+    MCK(cudaStreamSynchronize(m->stream));    // host arrays (and &p->n_host) may be reused by the caller
+    return CCM_OK;
+}
+
+int ccm_frame_pack_from_extractor_device(ccm_frame_pack* p, const ccm_grid_params* g, const ccm_keypoint* d_kp,
+                                         const uint8_t* d_desc, const int* d_n, const float* d_xy_un) {
+    if (!p || !d_kp || !d_desc || !d_n) return CCM_E_BADARG;
+    ccm_matcher* m = p->m;
+    int rc = check_grid(m, g);
+    if (rc) return rc;
+    cudaSetDevice(m->device);
+    p->g = *g; p->n_host = -1;
+    p->desc_view = d_desc;     // zero-copy: the matcher reads the extractor's descriptor rows in place
+    k_pack_from_keypoints<<<(p->cap + 255) / 256, 256, 0, m->stream>>>((const ccm_keypoint_dev*)d_kp, d_xy_un, d_n, p->cap,
+                                                                         p->x, p->y, p->angle, p->octave, p->n);
+    k_build_grid<<<1, 1024, 0, m->stream>>>(pack_dev(p), p->cell_start, p->items);
+    m->launches += 2;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_frame_pack_count(ccm_frame_pack* p, int* n) {
+    if (!p || !n) return CCM_E_BADARG;
+    ccm_matcher* m = p->m;
+    cudaSetDevice(m->device);
+    if (p->n_host < 0) {
+        MCK(cudaMemcpyAsync(n, p->n, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+        MCK(cudaStreamSynchronize(m->stream));
+        *n = std::min(*n, p->cap);
+    } else *n = p->n_host;
+    return CCM_OK;
+}
+
+int ccm_frame_pack_get_grid(ccm_frame_pack* p, int* cell_start, int* items, int* n_items) {
+    if (!p || !cell_start || !items || !n_items) return CCM_E_BADARG;
+    ccm_matcher* m = p->m;
+    cudaSetDevice(m->device);
+    const int ncell = p->g.cols * p->g.rows;
+    MCK(cudaMemcpyAsync(cell_start, p->cell_start, (size_t)(ncell + 1) * 4, cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    *n_items = cell_start[ncell];
+    if (*n_items > 0) {
+        MCK(cudaMemcpyAsync(items, p->items, (size_t)*n_items * 4, cudaMemcpyDeviceToHost, m->stream));
+        MCK(cudaStreamSynchronize(m->stream));
+    }
+    return CCM_OK;
+}
+
+/* ---- windowed searches ------------------------------------------------------------------------------------ */
+static int fill_params(ccm_matcher* m, const ccm_window_params* prm, WindowParamsDev* d) {
+    if (!prm || prm->mode < CCM_WIN_PROJ_MAPPOINTS || prm->mode > CCM_WIN_INIT) { m->err = "bad window mode"; return CCM_E_BADARG; }
+    std::memset(d, 0, sizeof(*d));
+    d->mode = prm->mode; d->nnratio = prm->nnratio; d->th_dist = prm->th_dist; d->check_orientation = prm->check_orientation;
+    d->use_gate = 0;
+    if (prm->mode == CCM_WIN_BEST && prm->inv_sigma2) {
+        if (prm->n_levels <= 0 || prm->n_levels > CCM_MATCH_MAX_LEVELS) { m->err = "n_levels must be 1..16 with inv_sigma2"; return CCM_E_BADARG; }
+        d->use_gate = 1;
+        for (int i = 0; i < prm->n_levels; i++) d->inv_sigma2[i] = prm->inv_sigma2[i];
+    }
+    return CCM_OK;
+}
+
+// scratch of one job, carved from MB_SCRATCH: head[cap] claim0[qs] claim1[qs] qbest[3*qs]
+static size_t job_scratch_ints(int cap, int qs) { return (size_t)cap + 5 * (size_t)qs + 16; }
+
+static void carve_job(WindowJob& J, int* s, int cap, int qs) {
+    J.head = s; s += cap;
+    J.claim[0] = s; s += qs;
+    J.claim[1] = s; s += qs;
+    J.qbest = s;
+}
+
+int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs, int n_jobs, const ccm_window_params* prm,
+                                   const int* d_nq, int q_stride, const ccm_window_query* d_q, const uint8_t* d_q_desc,
+                                   int* d_holder, int holder_stride, ccm_match_result* d_res, int* d_nmatches) {
+    if (!m || !packs || n_jobs < 0 || q_stride <= 0 || !d_q || !d_q_desc || !d_nmatches) return CCM_E_BADARG;
+    if (n_jobs == 0) return CCM_OK;
+    WindowParamsDev P;
+    int rc = fill_params(m, prm, &P);
+    if (rc) return rc;
+    if (P.mode != CCM_WIN_BEST && !d_holder) { m->err = "holder required"; return CCM_E_BADARG; }
+    cudaSetDevice(m->device);
+    int max_cap = 0;
+    for (int j = 0; j < n_jobs; j++) {
+        if (!packs[j] || packs[j]->m != m) { m->err = "pack belongs to another matcher"; return CCM_E_BADARG; }
+        max_cap = std::max(max_cap, packs[j]->cap);
+        if (P.mode != CCM_WIN_BEST && holder_stride < packs[j]->cap) { m->err = "holder_stride smaller than pack capacity"; return CCM_E_CAPACITY; }
+    }
+    const size_t per = job_scratch_ints(max_cap, q_stride);
+    int* scratch; WindowJob* djobs;
+    if ((rc = mbuf(m, MB_SCRATCH, per * n_jobs, &scratch))) return rc;
+    if ((rc = mbuf(m, MB_JOBS, (size_t)n_jobs, &djobs))) return rc;
+    std::vector<WindowJob> jobs(n_jobs);
+    for (int j = 0; j < n_jobs; j++) {
+        WindowJob& J = jobs[j];
+        J.pack = pack_dev(packs[j]);
+        J.q = (const WindowQueryDev*)d_q + (size_t)j * q_stride;
+        J.q_desc = d_q_desc + (size_t)j * q_stride * 32;
+        J.nq_ptr = d_nq ? d_nq + j : nullptr;
+        J.nq = q_stride;
+        J.holder = d_holder ? d_holder + (size_t)j * holder_stride : nullptr;
+        J.res = d_res ? (MatchResultDev*)d_res + (size_t)j * q_stride : nullptr;
+        J.nmatches = d_nmatches + j;
+        carve_job(J, scratch + per * j, max_cap, q_stride);
+    }
+    // pageable -> device copy is staged by the runtime before it returns, so `jobs` may die at scope exit
+    MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(WindowJob) * n_jobs, cudaMemcpyHostToDevice, m->stream));
+    k_window_search<<<n_jobs, WIN_THREADS, 0, m->stream>>>(djobs, P);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_search_window(ccm_matcher* m, ccm_frame_pack* targets, const ccm_window_params* prm, int nq,
+                      const ccm_window_query* q, const uint8_t* q_desc, int* holder, ccm_match_result* res, int* nmatches) {
+    if (!m || !targets || nq < 0 || (nq > 0 && (!q || !q_desc))) return CCM_E_BADARG;
+    if (!prm) return CCM_E_BADARG;
+    if (prm->mode != CCM_WIN_BEST && !holder) { m->err = "holder required"; return CCM_E_BADARG; }
+    if (nq == 0) { if (nmatches) *nmatches = 0; return CCM_OK; }
+    cudaSetDevice(m->device);
+    int rc;
+    WindowQueryDev* dq; uint8_t* dqd; int* dh; MatchResultDev* dres; int* dnm;
+    const int cap = targets->cap;
+    if ((rc = mbuf(m, MB_Q, (size_t)nq, &dq))) return rc;
+    if ((rc = mbuf(m, MB_QDESC, (size_t)nq * 32, &dqd))) return rc;
+    if ((rc = mbuf(m, MB_HOLDER, (size_t)cap, &dh))) return rc;
+    if ((rc = mbuf(m, MB_RES, (size_t)nq, &dres))) return rc;
+    if ((rc = mbuf(m, MB_NM, (size_t)1, &dnm))) return rc;
+    int n_t = 0;
+    if ((rc = ccm_frame_pack_count(targets, &n_t))) return rc;
+    MCK(cudaMemcpyAsync(dq, q, sizeof(WindowQueryDev) * nq, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(dqd, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
+    const bool holder_in = holder && prm->mode != CCM_WIN_BEST && prm->mode != CCM_WIN_INIT;
+    if (holder_in && n_t > 0) MCK(cudaMemcpyAsync(dh, holder, sizeof(int) * n_t, cudaMemcpyHostToDevice, m->stream));
+    ccm_frame_pack* packs[1] = {targets};
+    rc = ccm_search_window_batch_device(m, packs, 1, prm, nullptr, nq, (const ccm_window_query*)dq, dqd, dh, cap,
+                                        res ? (ccm_match_result*)dres : nullptr, dnm);
+    if (rc) return rc;
+    int nm = 0;
+    MCK(cudaMemcpyAsync(&nm, dnm, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    if (res) MCK(cudaMemcpyAsync(res, dres, sizeof(MatchResultDev) * nq, cudaMemcpyDeviceToHost, m->stream));
+    if (holder && prm->mode != CCM_WIN_BEST && n_t > 0) MCK(cudaMemcpyAsync(holder, dh, sizeof(int) * n_t, cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    if (nmatches) *nmatches = nm;
+    return CCM_OK;
+}
+
+/* ---- BoW-guided searches ---------------------------------------------------------------------------------- */
+// FeatureVector iteration order: (node id, feature index) ascending, features with node < 0 absent
+static void feature_vector_order(int n, const int* node, std::vector<int>& order) {
+    order.clear();
+    for (int i = 0; i < n; i++) if (node[i] >= 0) order.push_back(i);
+    std::stable_sort(order.begin(), order.end(), [node](int a, int b) { return node[a] < node[b]; });
+}
+
+int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientation,
+                   int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* valid_a, const float* angle_a,
+                   int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* valid_b, const float* angle_b,
+                   int* match_a, int* match_b, ccm_match_result* res_a, int* nmatches) {
+    if (!m || (mode != CCM_BOW_KF_FRAME && mode != CCM_BOW_KF_KF) || n_a < 0 || n_b < 0 || n_a > 65535 || n_b > 65535) return CCM_E_BADARG;
+    if ((n_a > 0 && (!desc_a || !node_a || !valid_a || !angle_a)) || (n_b > 0 && (!desc_b || !node_b || !angle_b))) return CCM_E_BADARG;
+    if (mode == CCM_BOW_KF_KF && n_b > 0 && !valid_b) return CCM_E_BADARG;
+    if (nmatches) *nmatches = 0;
+    if (n_a == 0 || n_b == 0) {
+        if (match_a) for (int i = 0; i < n_a; i++) match_a[i] = -1;
+        if (match_b) for (int i = 0; i < n_b; i++) match_b[i] = -1;
+        if (res_a) for (int i = 0; i < n_a; i++) res_a[i] = ccm_match_result{-1, 256, 256, 0};
+        return CCM_OK;
+    }
+    cudaSetDevice(m->device);
+    // merge-join of the two vectors on node id (ORBmatcher.cpp:203-278): shared nodes, ascending
+    std::vector<int> oa, ob;
+    feature_vector_order(n_a, node_a, oa);
+    feature_vector_order(n_b, node_b, ob);
+    std::vector<BowNode> nodes;
+    size_t ia = 0, ib = 0;
+    while (ia < oa.size() && ib < ob.size()) {
+        const int na = node_a[oa[ia]], nb = node_b[ob[ib]];
+        size_t ea = ia, eb = ib;
+        if (na <= nb) while (ea < oa.size() && node_a[oa[ea]] == na) ea++;
+        if (nb <= na) while (eb < ob.size() && node_b[ob[eb]] == nb) eb++;
+        if (na == nb) { nodes.push_back(BowNode{(int)ia, (int)ea, (int)ib, (int)eb}); ia = ea; ib = eb; }
+        else if (na < nb) ia = ea;
+        else ib = eb;
+    }
+    int rc;
+    uint8_t *dda, *ddb, *dva, *dvb; float *daa, *dab; int *doa, *dob, *dma, *dmb, *dnm; BowNode* dn; MatchResultDev* dres;
+    uint8_t* blob_a; uint8_t* blob_b;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t A = (size_t)n_a, B = (size_t)n_b;
+    // side A blob: desc | valid | angle | order | match | res ; side B blob: desc | valid | angle | order | match
+    const size_t a_desc = 0, a_val = a_desc + up(A * 32), a_ang = a_val + up(A), a_ord = a_ang + up(A * 4), a_mat = a_ord + up(A * 4),
+                 a_res = a_mat + up(A * 4), a_tot = a_res + up(A * 16);
+    const size_t b_desc = 0, b_val = b_desc + up(B * 32), b_ang = b_val + up(B), b_ord = b_ang + up(B * 4), b_mat = b_ord + up(B * 4),
+                 b_tot = b_mat + up(B * 4);
+    if ((rc = mbuf(m, MB_A, a_tot, &blob_a))) return rc;
+    if ((rc = mbuf(m, MB_B, b_tot, &blob_b))) return rc;
+    if ((rc = mbuf(m, MB_C, nodes.size() + 1, &dn))) return rc;
+    if ((rc = mbuf(m, MB_NM, (size_t)1, &dnm))) return rc;
+    dda = blob_a + a_desc; dva = blob_a + a_val; daa = (float*)(blob_a + a_ang); doa = (int*)(blob_a + a_ord); dma = (int*)(blob_a + a_mat);
+    dres = (MatchResultDev*)(blob_a + a_res);
+    ddb = blob_b + b_desc; dvb = blob_b + b_val; dab = (float*)(blob_b + b_ang); dob = (int*)(blob_b + b_ord); dmb = (int*)(blob_b + b_mat);
+    MCK(cudaMemcpyAsync(dda, desc_a, A * 32, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(dva, valid_a, A, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(daa, angle_a, A * 4, cudaMemcpyHostToDevice, m->stream));
+    if (!oa.empty()) MCK(cudaMemcpyAsync(doa, oa.data(), oa.size() * 4, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(ddb, desc_b, B * 32, cudaMemcpyHostToDevice, m->stream));
+    if (valid_b) MCK(cudaMemcpyAsync(dvb, valid_b, B, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(dab, angle_b, B * 4, cudaMemcpyHostToDevice, m->stream));
+    if (!ob.empty()) MCK(cudaMemcpyAsync(dob, ob.data(), ob.size() * 4, cudaMemcpyHostToDevice, m->stream));
+    if (!nodes.empty()) MCK(cudaMemcpyAsync(dn, nodes.data(), nodes.size() * sizeof(BowNode), cudaMemcpyHostToDevice, m->stream));
+    BowJob J;
+    J.desc_a = dda; J.desc_b = ddb; J.valid_a = dva; J.valid_b = valid_b ? dvb : nullptr; J.angle_a = daa; J.angle_b = dab;
+    J.order_a = doa; J.order_b = dob; J.nodes = dn; J.n_nodes = (int)nodes.size(); J.n_a = n_a; J.n_b = n_b;
+    J.match_a = dma; J.match_b = dmb; J.res_a = res_a ? dres : nullptr; J.nmatches = dnm;
+    J.mode = mode; J.nnratio = nnratio; J.th_low = CCM_TH_LOW; J.check_orientation = check_orientation;
+    k_bow_init<<<(std::max(n_a, n_b) + 255) / 256, 256, 0, m->stream>>>(J);
+    if (J.n_nodes > 0) k_bow_search<<<(J.n_nodes + 7) / 8, 256, 0, m->stream>>>(J);
+    k_bow_finish<<<1, 1024, 0, m->stream>>>(J);
+    m->launches += J.n_nodes > 0 ? 3 : 2;
+    MCK(cudaGetLastError());
+    int nm = 0;
+    MCK(cudaMemcpyAsync(&nm, dnm, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
+    if (match_a) MCK(cudaMemcpyAsync(match_a, dma, A * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (match_b) MCK(cudaMemcpyAsync(match_b, dmb, B * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (res_a) MCK(cudaMemcpyAsync(res_a, dres, A * sizeof(MatchResultDev), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    if (nmatches) *nmatches = nm;
+    return CCM_OK;
+}
+
+/* ---- server keyframe-database search ---------------------------------------------------------------------- */
+int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
+                                    uint32_t index_base, ccm_best2* d_out) {
+    if (!m || nq < 0 || nt < 0 || !d_out || (nq > 0 && !d_q) || (nt > 0 && !d_targets)) return CCM_E_BADARG;
+    if (nq == 0) return CCM_OK;
+    if (((uintptr_t)d_q | (uintptr_t)d_targets) & 15) { m->err = "descriptor arrays must be 16-byte aligned"; return CCM_E_BADARG; }
+    cudaSetDevice(m->device);
+    // queries per thread: as many as keep (almost) every thread of a query tile busy
+    const int Q = nq >= 896 ? 4 : (nq >= 384 ? 2 : 1);
+    const int q_tiles = (nq + AP_THREADS * Q - 1) / (AP_THREADS * Q);
+    // chunks of the target range: enough CTAs for ~3 per SM, chunk a multiple of the tile, <= 2^23
+    long long want = std::max<long long>(1, ((long long)m->sms * 3 + q_tiles - 1) / q_tiles);
+    long long chunk = std::max<long long>(AP_TILE, (nt + want - 1) / want);
+    chunk = (chunk + AP_TILE - 1) / AP_TILE * AP_TILE;
+    chunk = std::min<long long>(chunk, AP_MAX_CHUNK);
+    const long long n_chunks = std::max<long long>(1, (nt + chunk - 1) / chunk);
+    if (n_chunks > 65535) { m->err = "target shard too large for one launch (> 2^39 descriptors)"; return CCM_E_BADARG; }
+    Best2Dev* parts;
+    int rc;
+    if ((rc = mbuf(m, MB_PARTS, (size_t)n_chunks * nq, &parts))) return rc;
+    const dim3 grid((unsigned)q_tiles, (unsigned)n_chunks);
+    if (Q == 4) k_allpairs_best2<4><<<grid, AP_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_targets, nt, (int)chunk, index_base, parts);
+    else if (Q == 2) k_allpairs_best2<2><<<grid, AP_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_targets, nt, (int)chunk, index_base, parts);
+    else k_allpairs_best2<1><<<grid, AP_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_targets, nt, (int)chunk, index_base, parts);
+    k_allpairs_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>(parts, (int)n_chunks, nq, 0.f, CCM_TH_LOW, (Best2Dev*)d_out, nullptr);
+    m->launches += 2;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_match_allpairs_merge_device(ccm_matcher* m, const ccm_best2* d_parts, int n_parts, int nq, float nnratio,
+                                    ccm_best2* d_out, uint8_t* d_accept) {
+    if (!m || !d_parts || n_parts <= 0 || nq < 0 || !d_out) return CCM_E_BADARG;
+    if (nq == 0) return CCM_OK;
+    cudaSetDevice(m->device);
+    k_allpairs_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>((const Best2Dev*)d_parts, n_parts, nq, nnratio, CCM_TH_LOW, (Best2Dev*)d_out, d_accept);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_match_allpairs_best2(ccm_matcher* m, const uint8_t* q, int nq, const uint8_t* targets, long long nt,
+                             uint32_t index_base, ccm_best2* out) {
+    if (!m || nq < 0 || nt < 0 || !out || (nq > 0 && !q) || (nt > 0 && !targets)) return CCM_E_BADARG;
+    if (nq == 0) return CCM_OK;
+    cudaSetDevice(m->device);
+    uint8_t *dq, *dt; Best2Dev* dout;
+    int rc;
+    if ((rc = mbuf(m, MB_A, (size_t)nq * 32, &dq))) return rc;
+    if ((rc = mbuf(m, MB_B, (size_t)std::max<long long>(nt, 1) * 32, &dt))) return rc;
+    if ((rc = mbuf(m, MB_C, (size_t)nq, &dout))) return rc;
+    MCK(cudaMemcpyAsync(dq, q, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
+    if (nt > 0) MCK(cudaMemcpyAsync(dt, targets, (size_t)nt * 32, cudaMemcpyHostToDevice, m->stream));
+    if ((rc = ccm_match_allpairs_best2_device(m, dq, nq, dt, nt, index_base, (ccm_best2*)dout))) return rc;
+    MCK(cudaMemcpyAsync(out, dout, sizeof(Best2Dev) * nq, cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,340 @@
+// K8a — windowed Hamming searches of ORBmatcher: every SearchByProjection overload, the SearchBySim3 passes, the
+// distance phase of Fuse, and SearchForInitialization (cslam/src/ORBmatcher.cpp:71-148, 308-446, 448-563, 929-962,
+// 1082-1103, 1216-1252, 1296-1327, 1350-1476), over the feature grid of Frame / KeyFrame
+// (cslam/src/Frame.cpp:103-118, 200-265; cslam/src/KeyFrame.cpp:1162-1201).
+//
+// One CTA per job (one query list against one frame pack), one warp per query, lanes striding the candidates.
+// The grid is CSR in (ix*rows + iy) cell order, so the cells of one grid column that a window touches are one
+// contiguous item range: a query walks (window columns) ranges in exactly the order GetFeaturesInArea emits them.
+// Candidates are ranked by the packed key (distance << 32 | position-in-that-order << 16 | feature index); the two
+// smallest keys of a warp-shuffle reduction are the reference's best / second-best under its strict-`<` first-wins rule.
+//
+// The reference loops are greedy and sequential: an accepted match writes F.mvpMapPoints[idx] / vpMatched[idx] and a
+// LATER query skips that feature. Query i's outcome depends only on queries j < i, so the sequential result is the
+// unique fixpoint of "evaluate every query against the claims of lower-numbered queries"; the kernel iterates that
+// map in parallel until the claim vector stops changing (after k rounds the first k queries are final, in practice
+// 2-3 rounds because conflicts are rare). SearchForInitialization's steal-back rule (:487-513) compares distances of
+// earlier claims and is run in query order by one warp instead (it is called a handful of times per session).
+#include "match_common.cuh"
+
+#define WIN_THREADS 1024
+#define WIN_MODE_MAPPOINTS 0
+#define WIN_MODE_LASTFRAME 1
+#define WIN_MODE_KF_SIM3 2
+#define WIN_MODE_BEST 3
+#define WIN_MODE_INIT 4
+#define WQ_VALID 1u
+#define WQ_BLOCKS 2u
+#define KEY_NONE 0xffffffffffffffffull
+
+// ---- frame pack construction ----------------------------------------------------------------------------------
+// ccm_keypoint (AoS, extractor output) -> pack SoA; xy_un overrides the positions (mvKeysUn of a distorted camera)
+__global__ void k_pack_from_keypoints(const ccm_keypoint_dev* __restrict__ kp, const float* __restrict__ xy_un,
+                                      const int* __restrict__ n_ptr, int cap, float* x, float* y, float* angle,
+                                      int* octave, int* n_out) {
+    const int n = min(*n_ptr, cap);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *n_out = n;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const ccm_keypoint_dev k = kp[i];
+        x[i] = xy_un ? xy_un[2 * i] : k.x;
+        y[i] = xy_un ? xy_un[2 * i + 1] : k.y;
+        angle[i] = k.angle;
+        octave[i] = k.octave;
+    }
+}
+
+// Frame::AssignFeaturesToGrid + PosInGrid (Frame.cpp:103-118, 255-265; note round(), not floor()): one CTA per pack.
+// Counting pass, block scan, scatter, then an insertion sort inside each cell restores ascending feature index
+// (what push_back in index order produces).
+__global__ void __launch_bounds__(1024) k_build_grid(PackDev P, int* cell_start, int* items) {
+    __shared__ int cnt[CCM_MAX_GRID_CELLS];
+    __shared__ int wsum[32];
+    const int ncell = P.cols * P.rows;
+    const int n = min(*P.n, P.cap);
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(P.x[i], P.min_x), P.inv_w));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(P.y[i], P.min_y), P.inv_h));
+        if (px < 0 || px >= P.cols || py < 0 || py >= P.rows) continue;
+        atomicAdd(&cnt[px * P.rows + py], 1);
+    }
+    __syncthreads();
+    // exclusive scan of cnt[0..ncell): each thread owns a contiguous run of cells
+    const int per = (ncell + blockDim.x - 1) / blockDim.x;
+    const int c0 = min(threadIdx.x * per, ncell), c1 = min(c0 + per, ncell);
+    int s = 0;
+    for (int c = c0; c < c1; c++) s += cnt[c];
+    int incl = s;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+    if (lane == 31) wsum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int v = wsum[lane], w = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += u; }
+        wsum[lane] = w - v;
+    }
+    __syncthreads();
+    int run = wsum[wid] + incl - s;
+    for (int c = c0; c < c1; c++) { const int k = cnt[c]; cell_start[c] = run; cnt[c] = run; run += k; }
+    if (threadIdx.x == blockDim.x - 1) cell_start[ncell] = run;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(P.x[i], P.min_x), P.inv_w));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(P.y[i], P.min_y), P.inv_h));
+        if (px < 0 || px >= P.cols || py < 0 || py >= P.rows) continue;
+        items[atomicAdd(&cnt[px * P.rows + py], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+        const int a = cell_start[c], b = cnt[c];   // cnt[c] is now the end of cell c
+        for (int i = a + 1; i < b; i++) {
+            const int v = items[i];
+            int j = i - 1;
+            while (j >= a && items[j] > v) { items[j + 1] = items[j]; j--; }
+            items[j + 1] = v;
+        }
+    }
+}
+
+// ---- one query against the grid ---------------------------------------------------------------------------------
+struct WinEval { unsigned long long b1, b2; };
+
+// blocked(k): the feature already holds a map point that makes the reference `continue` (:113-115, :393, :1417-1419)
+template <int MODE>
+__device__ __forceinline__ WinEval eval_query(const PackDev& P, const WindowParamsDev& prm, const WindowQueryDev& q,
+                                              const uint4 qd0, const uint4 qd1, int qi, const int* __restrict__ holder,
+                                              const int* __restrict__ minclaim, const int* __restrict__ mdist, int lane) {
+    WinEval e; e.b1 = KEY_NONE; e.b2 = KEY_NONE;
+    // GetFeaturesInArea cell window (Frame.cpp:205-221)
+    const float fx = __fsub_rn(q.u, P.min_x), fy = __fsub_rn(q.v, P.min_y);
+    const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(fx, q.r), P.inv_w)));
+    if (minCX >= P.cols) return e;
+    const int maxCX = min(P.cols - 1, (int)ceilf(__fmul_rn(__fadd_rn(fx, q.r), P.inv_w)));
+    if (maxCX < 0) return e;
+    const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(fy, q.r), P.inv_h)));
+    if (minCY >= P.rows) return e;
+    const int maxCY = min(P.rows - 1, (int)ceilf(__fmul_rn(__fadd_rn(fy, q.r), P.inv_h)));
+    if (maxCY < 0) return e;
+    const uint4* __restrict__ desc = reinterpret_cast<const uint4*>(P.desc);
+    int pos_base = 0;
+    for (int ix = minCX; ix <= maxCX; ix++) {
+        const int s = P.cell_start[ix * P.rows + minCY], t = P.cell_start[ix * P.rows + maxCY + 1];
+        for (int p = s + lane; p < t; p += 32) {
+            const int k = P.items[p];
+            const int oct = P.octave[k];
+            if (oct < q.min_level) continue;
+            if (q.max_level >= 0 && oct > q.max_level) continue;
+            const float dx = __fsub_rn(P.x[k], q.u), dy = __fsub_rn(P.y[k], q.v);
+            if (!(fabsf(dx) < q.r && fabsf(dy) < q.r)) continue;
+            if (MODE == WIN_MODE_BEST && prm.use_gate) {       // Fuse chi2 gate, ORBmatcher.cpp:944-951
+                const float ex = __fsub_rn(q.u, P.x[k]), ey = __fsub_rn(q.v, P.y[k]);
+                const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                if ((double)__fmul_rn(e2, prm.inv_sigma2[oct]) > 5.99) continue;
+            }
+            if (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) {
+                if (holder[k] == -2 || minclaim[k] < qi) continue;
+            } else if (MODE == WIN_MODE_KF_SIM3) {
+                if (holder[k] != -1 || minclaim[k] < qi) continue;
+            }
+            const int dist = hamming256(qd0, qd1, desc[2 * (size_t)k], desc[2 * (size_t)k + 1]);
+            if (MODE == WIN_MODE_INIT) { if (mdist[k] <= dist) continue; }   // vMatchedDistance, :487-488
+            const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned long long)(pos_base + p - s) << 16) | (unsigned)k;
+            push_top2(e.b1, e.b2, key);
+        }
+        pos_base += t - s;
+    }
+    warp_top2(e.b1, e.b2);
+    return e;
+}
+
+template <int MODE>
+__device__ __forceinline__ bool accept_rule(const PackDev& P, const WindowParamsDev& prm, const WinEval& e, int& bestIdx,
+                                            int& bestDist, int& bestDist2) {
+    bestIdx = -1; bestDist = 256; bestDist2 = 256;
+    if (e.b1 == KEY_NONE) return false;
+    bestIdx = (int)(e.b1 & 0xffff); bestDist = (int)(e.b1 >> 32);
+    const bool has2 = e.b2 != KEY_NONE;
+    if (has2) bestDist2 = (int)(e.b2 >> 32);
+    if (MODE == WIN_MODE_MAPPOINTS) {
+        if (bestDist > prm.th_dist) return false;
+        const int bestLevel = P.octave[bestIdx];
+        const int bestLevel2 = has2 ? P.octave[(int)(e.b2 & 0xffff)] : -1;
+        // `bestDist > mfNNratio*bestDist2` with int operands promoted to float (:139)
+        if (bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(prm.nnratio, (float)bestDist2)) return false;
+        return true;
+    }
+    if (MODE == WIN_MODE_INIT) {
+        if (bestDist > prm.th_dist) return false;
+        // `bestDist < (float)bestDist2*mfNNratio` (:498); with no second candidate bestDist2 is INT_MAX there
+        if (!has2) return true;
+        return (float)bestDist < __fmul_rn((float)bestDist2, prm.nnratio);
+    }
+    return bestDist <= prm.th_dist;
+}
+
+template <int MODE>
+__device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
+    __shared__ int s_changed, s_nm, s_hist[32], s_keep[3];
+    const PackDev& P = J.pack;
+    const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
+    const int n = min(*P.n, P.cap);
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
+    int* minclaim = J.head;
+    const bool stateful = (MODE != WIN_MODE_BEST);
+
+    if (threadIdx.x == 0) { s_nm = 0; }
+    if (threadIdx.x < 32) s_hist[threadIdx.x] = 0;
+    for (int i = threadIdx.x; i < nq; i += blockDim.x) { J.claim[0][i] = -1; J.claim[1][i] = -1; }
+    __syncthreads();
+
+    int cur = 0;
+    for (int it = 0; it <= nq; it++) {
+        cur = it & 1;
+        const int prev = cur ^ 1;
+        if (stateful) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) minclaim[i] = 0x7fffffff;
+            __syncthreads();
+            if (it > 0)
+                for (int i = threadIdx.x; i < nq; i += blockDim.x) {
+                    const int t = J.claim[prev][i];
+                    if (t >= 0 && (J.q[i].flags & WQ_BLOCKS)) atomicMin(&minclaim[t], i);
+                }
+            __syncthreads();
+        }
+        int changed = 0;
+        for (int i = wid; i < nq; i += nw) {
+            const WindowQueryDev q = J.q[i];
+            int bestIdx = -1, bestDist = 256, bestDist2 = 256;
+            bool acc = false;
+            if (q.flags & WQ_VALID) {
+                const WinEval e = eval_query<MODE>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i, J.holder,
+                                                   minclaim, nullptr, lane);
+                acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
+            }
+            if (lane == 0) {
+                const int c = acc ? bestIdx : -1;
+                if (c != J.claim[prev][i]) changed = 1;
+                J.claim[cur][i] = c;
+                J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist;
+                J.qbest[3 * i + 2] = (MODE == WIN_MODE_MAPPOINTS) ? bestDist2 : 256;
+            }
+        }
+        if (!stateful) break;
+        if (!__syncthreads_or(changed)) break;
+    }
+    __syncthreads();
+
+    // ---- outcome: res[], holder[], nmatches, rotation histogram (LASTFRAME, :1436-1465) ----
+    const bool ori = (MODE == WIN_MODE_LASTFRAME) && prm.check_orientation;
+    int my_nm = 0;
+    for (int i = threadIdx.x; i < nq; i += blockDim.x) {
+        const int t = J.claim[cur][i];
+        if (J.res) {
+            MatchResultDev r; r.best_idx = J.qbest[3 * i]; r.best_dist = J.qbest[3 * i + 1]; r.best_dist2 = J.qbest[3 * i + 2];
+            r.accepted = t >= 0;
+            J.res[i] = r;
+        }
+        if (t < 0) continue;
+        const bool writes = (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) ||
+                            (MODE == WIN_MODE_KF_SIM3 && (J.q[i].flags & WQ_BLOCKS));
+        if (writes) atomicMax(&J.holder[t], i);       // later queries overwrite earlier non-blocking claims
+        if (MODE != WIN_MODE_KF_SIM3 || writes) my_nm++;
+        if (ori) atomicAdd(&s_hist[rot_bin(J.q[i].angle, P.angle[t])], 1);
+    }
+    if (my_nm) atomicAdd(&s_nm, my_nm);
+    __syncthreads();
+    if (ori) {
+        if (threadIdx.x == 0) three_maxima(s_hist, 30, s_keep[0], s_keep[1], s_keep[2]);
+        __syncthreads();
+        int drop = 0;
+        for (int i = threadIdx.x; i < nq; i += blockDim.x) {
+            const int t = J.claim[cur][i];
+            if (t < 0) continue;
+            const int b = rot_bin(J.q[i].angle, P.angle[t]);
+            if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) { J.holder[t] = -1; drop++; }
+        }
+        if (drop) atomicSub(&s_nm, drop);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *J.nmatches = s_nm;
+}
+
+// SearchForInitialization (ORBmatcher.cpp:448-563): queries in order on warp 0; holder = vnMatches21 (output),
+// head = vMatchedDistance, claim[0] = vnMatches12, claim[1] = rotation bin of the accept event.
+__device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) {
+    __shared__ int s_hist[32], s_keep[3], s_nm;
+    const PackDev& P = J.pack;
+    const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
+    const int n = min(*P.n, P.cap);
+    const int lane = threadIdx.x & 31;
+    const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
+    int* mdist = J.head;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) { mdist[i] = 0x7fffffff; J.holder[i] = -1; }
+    for (int i = threadIdx.x; i < nq; i += blockDim.x) { J.claim[0][i] = -1; J.claim[1][i] = -1; }
+    if (threadIdx.x < 32) s_hist[threadIdx.x] = 0;
+    if (threadIdx.x == 0) s_nm = 0;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        int nm = 0;
+        for (int i = 0; i < nq; i++) {
+            const WindowQueryDev q = J.q[i];
+            int bestIdx = -1, bestDist = 256, bestDist2 = 256;
+            bool acc = false;
+            if (q.flags & WQ_VALID) {
+                const WinEval e = eval_query<WIN_MODE_INIT>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i,
+                                                            J.holder, nullptr, mdist, lane);
+                acc = accept_rule<WIN_MODE_INIT>(P, prm, e, bestIdx, bestDist, bestDist2);
+            }
+            if (lane == 0) {
+                J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist; J.qbest[3 * i + 2] = bestDist2;
+                if (acc) {
+                    const int old = J.holder[bestIdx];
+                    if (old >= 0) { J.claim[0][old] = -1; nm--; }          // steal-back, :506-510
+                    J.claim[0][i] = bestIdx; J.holder[bestIdx] = i; mdist[bestIdx] = bestDist; nm++;
+                    if (prm.check_orientation) {
+                        const int b = rot_bin(q.angle, P.angle[bestIdx]);
+                        J.claim[1][i] = b; s_hist[b]++;
+                    }
+                }
+            }
+            __syncwarp();
+        }
+        if (lane == 0) s_nm = nm;
+    }
+    __syncthreads();
+    if (prm.check_orientation) {
+        if (threadIdx.x == 0) three_maxima(s_hist, 30, s_keep[0], s_keep[1], s_keep[2]);
+        __syncthreads();
+        int drop = 0;
+        for (int i = threadIdx.x; i < nq; i += blockDim.x) {
+            const int b = J.claim[1][i], t = J.claim[0][i];
+            if (b < 0 || t < 0) continue;                                   // `if(vnMatches12[idx1]>=0)`, :548
+            if (b != s_keep[0] && b != s_keep[1] && b != s_keep[2]) { J.claim[0][i] = -1; J.holder[t] = -1; drop++; }
+        }
+        if (drop) atomicSub(&s_nm, drop);
+        __syncthreads();
+    }
+    for (int i = threadIdx.x; i < nq; i += blockDim.x)
+        if (J.res) {
+            MatchResultDev r; r.best_idx = J.qbest[3 * i]; r.best_dist = J.qbest[3 * i + 1]; r.best_dist2 = J.qbest[3 * i + 2];
+            r.accepted = J.claim[0][i] >= 0;
+            J.res[i] = r;
+        }
+    if (threadIdx.x == 0) *J.nmatches = s_nm;
+}
+
+__global__ void __launch_bounds__(WIN_THREADS) k_window_search(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
+    const WindowJob J = jobs[blockIdx.x];
+    switch (prm.mode) {
+        case WIN_MODE_MAPPOINTS: window_job<WIN_MODE_MAPPOINTS>(J, prm); break;
+        case WIN_MODE_LASTFRAME: window_job<WIN_MODE_LASTFRAME>(J, prm); break;
+        case WIN_MODE_KF_SIM3: window_job<WIN_MODE_KF_SIM3>(J, prm); break;
+        case WIN_MODE_BEST: window_job<WIN_MODE_BEST>(J, prm); break;
+        default: window_job_init(J, prm); break;
+    }
+}

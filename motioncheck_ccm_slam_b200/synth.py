@@ -59,3 +59,58 @@ def make_stream(seed, n_frames, w=752, h=480):
 
 def make_frame(seed, w=752, h=480):
     return make_stream(seed, 1, w, h)[0]
+
+
+# ---- synthetic matching workloads -------------------------------------------------------
+def random_descriptors(rng, n):
+    """i.i.d. uniform 256-bit descriptors, uint8 [n, 32]."""
+    return rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
+
+
+def perturb_descriptors(rng, desc, flip_prob):
+    """Flip each bit with probability flip_prob (the same feature seen again)."""
+    bits = np.unpackbits(desc, axis=1)
+    flips = (rng.random(bits.shape) < flip_prob).astype(np.uint8)
+    return np.packbits(bits ^ flips, axis=1)
+
+
+def make_feature_frame(seed, n=1000, w=752, h=480, nlevels=8):
+    """A frame as the matcher sees it: dict(desc, x, y, octave, angle). Positions inside the image, clustered so that
+    grid cells hold several features and windows hold tens of candidates; octaves geometric like the extractor's quotas."""
+    rng = np.random.default_rng(seed)
+    centers = rng.uniform([20, 20], [w - 20, h - 20], size=(max(n // 12, 1), 2))
+    pts = centers[rng.integers(0, len(centers), n)] + rng.normal(0, 9.0, size=(n, 2))
+    x = np.clip(pts[:, 0], 0.5, w - 1.5).astype(np.float32)
+    y = np.clip(pts[:, 1], 0.5, h - 1.5).astype(np.float32)
+    p = 0.8333 ** np.arange(nlevels)
+    octave = rng.choice(nlevels, size=n, p=p / p.sum()).astype(np.int32)
+    angle = rng.uniform(0, 360, n).astype(np.float32)
+    return dict(desc=random_descriptors(rng, n), x=x, y=y, octave=octave, angle=angle)
+
+
+def make_next_frame(seed, fr, w=752, h=480, motion=(2.0, 1.0), flip_prob=0.06, keep=0.85, n_new=None, d_angle=3.0):
+    """The scene of `fr` one time step later: most features survive (permuted, moved by `motion` + jitter, a few descriptor
+    bits flipped, angle turned by ~d_angle), the rest are new. Returns (frame dict, src) with src[i] = index in `fr` or -1."""
+    rng = np.random.default_rng(seed)
+    n = len(fr["x"])
+    keep_idx = np.nonzero(rng.random(n) < keep)[0]
+    n_new = n - len(keep_idx) if n_new is None else n_new
+    new = make_feature_frame(seed + 77, max(n_new, 1), w, h, int(fr["octave"].max()) + 1)
+    desc = np.concatenate([perturb_descriptors(rng, fr["desc"][keep_idx], flip_prob), new["desc"][:n_new]])
+    x = np.concatenate([fr["x"][keep_idx] + motion[0] + rng.normal(0, 0.7, len(keep_idx)), new["x"][:n_new]]).astype(np.float32)
+    y = np.concatenate([fr["y"][keep_idx] + motion[1] + rng.normal(0, 0.7, len(keep_idx)), new["y"][:n_new]]).astype(np.float32)
+    octave = np.concatenate([np.clip(fr["octave"][keep_idx] + rng.choice([-1, 0, 0, 0, 1], len(keep_idx)), 0, fr["octave"].max()),
+                             new["octave"][:n_new]]).astype(np.int32)
+    angle = np.concatenate([np.mod(fr["angle"][keep_idx] + rng.normal(d_angle, 2.0, len(keep_idx)), 360.0),
+                            new["angle"][:n_new]]).astype(np.float32)
+    src = np.concatenate([keep_idx, np.full(n_new, -1)]).astype(np.int64)
+    perm = rng.permutation(len(src))
+    x = np.clip(x, 0.5, w - 1.5); y = np.clip(y, 0.5, h - 1.5)
+    return dict(desc=desc[perm], x=x[perm], y=y[perm], octave=octave[perm], angle=angle[perm]), src[perm]
+
+
+def bow_node_ids(desc, n_nodes=1000):
+    """Stand-in for DBoW2's FeatureVector node ids (the ORB vocabulary blob is absent from the reference checkout,
+    SURVEY.md §8c): node = first 13 descriptor bits mod n_nodes, the same rule on both sides."""
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    return (((d[:, 0].astype(np.int32) << 5) | (d[:, 1].astype(np.int32) >> 3)) % n_nodes).astype(np.int32)

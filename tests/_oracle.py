@@ -138,3 +138,156 @@ class RefExtractor:
         rc = self.L.ref_orb_pyramid_level(self.h, level, buf.ctypes.data, buf.size, ctypes.byref(w), ctypes.byref(h))
         assert rc == 0
         return buf[:w.value * h.value].reshape(h.value, w.value).copy()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# matcher oracle (oracle/match_oracle.cpp): restated ORBmatcher loops over plain arrays
+# ---------------------------------------------------------------------------------------------------------------
+RESULT_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("best_dist2", "<i4"), ("accepted", "<i4")])
+_u8p = _vp
+_mo = None
+
+
+def match_lib():
+    global _mo
+    if _mo is None:
+        L = oracle_lib()
+        L.mo_descriptor_distance.argtypes = [_vp, _vp]
+        L.mo_frame_create.restype = _vp
+        L.mo_frame_create.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _i, _i]
+        L.mo_frame_destroy.argtypes = [_vp]
+        L.mo_frame_grid.argtypes = [_vp, _vp, _vp]
+        L.mo_features_in_area.argtypes = [_vp, _c.c_float, _c.c_float, _c.c_float, _i, _i, _i, _vp, _i]
+        L.mo_search_projection_mappoints.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _vp, _vp, _vp]
+        L.mo_search_projection_lastframe.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _vp, _i, _vp, _vp]
+        L.mo_search_projection_kf_sim3.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp]
+        L.mo_search_best_in_window.restype = None
+        L.mo_search_best_in_window.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp]
+        L.mo_search_bow_kf_frame.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _c.c_float, _i, _vp, _vp]
+        L.mo_search_bow_kf_kf.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _c.c_float, _i, _vp, _vp]
+        L.mo_search_for_initialization.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _i, _c.c_float, _i, _vp]
+        L.mo_match_allpairs_best2.restype = None
+        L.mo_match_allpairs_best2.argtypes = [_i, _vp, _c.c_longlong, _vp, _c.c_float, _vp]
+        _mo = L
+    return _mo
+
+
+def _a(x, dt):
+    return np.ascontiguousarray(x, dt)
+
+
+class OracleFrame:
+    """Matching data of a Frame / KeyFrame: descriptors, undistorted keypoints and the 75x48 feature grid."""
+
+    def __init__(self, desc, x, y, octave, angle, grid):
+        self.L = match_lib()
+        self.desc = _a(desc, np.uint8).reshape(-1, 32)
+        self.x, self.y, self.octave, self.angle = _a(x, np.float32), _a(y, np.float32), _a(octave, np.int32), _a(angle, np.float32)
+        self.n = len(self.desc)
+        self.grid = grid
+        self.h = self.L.mo_frame_create(self.n, self.desc.ctypes.data, self.x.ctypes.data, self.y.ctypes.data,
+                                        self.octave.ctypes.data, self.angle.ctypes.data, grid.min_x, grid.min_y,
+                                        grid.inv_w, grid.inv_h, grid.cols, grid.rows)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.mo_frame_destroy(self.h)
+            self.h = None
+
+    def csr(self):
+        cs = np.zeros(self.grid.cols * self.grid.rows + 1, np.int32)
+        items = np.zeros(max(self.n, 1), np.int32)
+        k = self.L.mo_frame_grid(self.h, cs.ctypes.data, items.ctypes.data)
+        return cs, items[:k].copy()
+
+    def features_in_area(self, x, y, r, min_level, max_level, kf_variant=False):
+        out = np.zeros(max(self.n, 1), np.int32)
+        k = self.L.mo_features_in_area(self.h, x, y, r, min_level, max_level, 1 if kf_variant else 0, out.ctypes.data, len(out))
+        return out[:k].copy()
+
+
+class OracleMatcher:
+    """CPU oracle with the reference's ORBmatcher(nnratio, checkOri) arguments."""
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        self.L = match_lib()
+        self.nnratio = float(np.float32(nnratio))
+        self.ori = 1 if checkOri else 0
+
+    def descriptor_distance(self, a, b):
+        a = _a(a, np.uint8).reshape(-1, 32); b = _a(b, np.uint8).reshape(-1, 32)
+        return np.array([self.L.mo_descriptor_distance(a[i].ctypes.data, b[i].ctypes.data) for i in range(len(a))], np.int32)
+
+    def projection_mappoints(self, F, q_valid, q_u, q_v, q_level, q_viewcos, q_desc, q_obs, th, sf, holder):
+        n = len(q_u)
+        res = np.zeros(n, RESULT_DTYPE)
+        v, u_, v_, l, c, d, o, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
+                                    _a(q_viewcos, np.float32), _a(q_desc, np.uint8), _a(q_obs, np.uint8), _a(sf, np.float32))
+        nm = self.L.mo_search_projection_mappoints(F.h, n, v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
+                                                   c.ctypes.data, d.ctypes.data, o.ctypes.data, th, self.nnratio,
+                                                   s.ctypes.data, holder.ctypes.data, res.ctypes.data)
+        return nm, res
+
+    def projection_lastframe(self, F, q_valid, q_u, q_v, q_octave, q_angle, q_desc, q_obs, th, sf, holder):
+        n = len(q_u)
+        res = np.zeros(n, RESULT_DTYPE)
+        v, u_, v_, l, a, d, o, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_octave, np.int32),
+                                    _a(q_angle, np.float32), _a(q_desc, np.uint8), _a(q_obs, np.uint8), _a(sf, np.float32))
+        nm = self.L.mo_search_projection_lastframe(F.h, n, v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
+                                                   a.ctypes.data, d.ctypes.data, o.ctypes.data, th, s.ctypes.data, self.ori,
+                                                   holder.ctypes.data, res.ctypes.data)
+        return nm, res
+
+    def projection_kf_sim3(self, F, q_valid, q_u, q_v, q_level, q_desc, q_claims, th, sf, holder):
+        n = len(q_u)
+        res = np.zeros(n, RESULT_DTYPE)
+        v, u_, v_, l, d, c, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
+                                 _a(q_desc, np.uint8), _a(q_claims, np.uint8), _a(sf, np.float32))
+        nm = self.L.mo_search_projection_kf_sim3(F.h, n, v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
+                                                 d.ctypes.data, c.ctypes.data, int(th), s.ctypes.data, holder.ctypes.data,
+                                                 res.ctypes.data)
+        return nm, res
+
+    def best_in_window(self, F, q_valid, q_u, q_v, q_radius, q_level, q_desc, th_dist, inv_sigma2=None):
+        n = len(q_u)
+        res = np.zeros(n, RESULT_DTYPE)
+        v, u_, v_, r, l, d = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_radius, np.float32),
+                              _a(q_level, np.int32), _a(q_desc, np.uint8))
+        s = _a(inv_sigma2, np.float32) if inv_sigma2 is not None else None
+        self.L.mo_search_best_in_window(F.h, n, v.ctypes.data, u_.ctypes.data, v_.ctypes.data, r.ctypes.data, l.ctypes.data,
+                                        d.ctypes.data, th_dist, s.ctypes.data if s is not None else None, res.ctypes.data)
+        return int(res["accepted"].sum()), res
+
+    def bow_kf_frame(self, desc_kf, node_kf, valid_kf, angle_kf, desc_f, node_f, angle_f):
+        dk, nk, vk, ak = _a(desc_kf, np.uint8), _a(node_kf, np.int32), _a(valid_kf, np.uint8), _a(angle_kf, np.float32)
+        df, nf, af = _a(desc_f, np.uint8), _a(node_f, np.int32), _a(angle_f, np.float32)
+        mf = np.full(max(len(nf), 1), -1, np.int32)
+        res = np.zeros(max(len(nk), 1), RESULT_DTYPE)
+        nm = self.L.mo_search_bow_kf_frame(len(nk), dk.ctypes.data, nk.ctypes.data, vk.ctypes.data, ak.ctypes.data, len(nf),
+                                           df.ctypes.data, nf.ctypes.data, af.ctypes.data, self.nnratio, self.ori,
+                                           mf.ctypes.data, res.ctypes.data)
+        return nm, mf[:len(nf)], res[:len(nk)]
+
+    def bow_kf_kf(self, d1, n1, v1, a1, d2, n2, v2, a2):
+        d1, n1, v1, a1 = _a(d1, np.uint8), _a(n1, np.int32), _a(v1, np.uint8), _a(a1, np.float32)
+        d2, n2, v2, a2 = _a(d2, np.uint8), _a(n2, np.int32), _a(v2, np.uint8), _a(a2, np.float32)
+        m12 = np.full(max(len(n1), 1), -1, np.int32)
+        res = np.zeros(max(len(n1), 1), RESULT_DTYPE)
+        nm = self.L.mo_search_bow_kf_kf(len(n1), d1.ctypes.data, n1.ctypes.data, v1.ctypes.data, a1.ctypes.data, len(n2),
+                                        d2.ctypes.data, n2.ctypes.data, v2.ctypes.data, a2.ctypes.data, self.nnratio, self.ori,
+                                        m12.ctypes.data, res.ctypes.data)
+        return nm, m12[:len(n1)], res[:len(n1)]
+
+    def search_for_initialization(self, desc1, octave1, angle1, prev_xy, F2, windowSize):
+        d1, o1, a1 = _a(desc1, np.uint8), _a(octave1, np.int32), _a(angle1, np.float32)
+        assert prev_xy.dtype == np.float32 and prev_xy.flags.c_contiguous
+        m12 = np.full(max(len(o1), 1), -1, np.int32)
+        nm = self.L.mo_search_for_initialization(len(o1), d1.ctypes.data, o1.ctypes.data, a1.ctypes.data, prev_xy.ctypes.data,
+                                                 F2.h, int(windowSize), self.nnratio, self.ori, m12.ctypes.data)
+        return nm, m12[:len(o1)]
+
+    def allpairs_best2(self, q, t):
+        q = _a(q, np.uint8).reshape(-1, 32); t = _a(t, np.uint8).reshape(-1, 32)
+        res = np.zeros(max(len(q), 1), RESULT_DTYPE)
+        self.L.mo_match_allpairs_best2(len(q), q.ctypes.data, len(t), t.ctypes.data, self.nnratio, res.ctypes.data)
+        return res[:len(q)]

@@ -64,3 +64,25 @@ def test_product_does_not_import_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 txt = open(os.path.join(dirpath, fn), errors="ignore").read()
                 assert "liborb_oracle" not in txt and "_oracle" not in txt and "oracle/" not in txt.replace("oracle/cv_primitives.cpp linear_table", ""), fn
+
+
+def test_matcher_no_cpu_fallback_and_badargs(cuda_lib):
+    from motioncheck_ccm_slam_b200._lib import CCM_E_BADARG, CCM_E_CUDA
+    h = ctypes.c_void_p()
+    assert cuda_lib.ccm_matcher_create(0, None) == CCM_E_BADARG
+    assert cuda_lib.ccm_matcher_create(-1, ctypes.byref(h)) in (CCM_E_CUDA,)
+    assert not h.value
+    try:
+        import torch
+        has_gpu = torch.cuda.is_available()
+    except ImportError:
+        has_gpu = False
+    if not has_gpu:
+        assert cuda_lib.ccm_matcher_create(0, ctypes.byref(h)) == CCM_E_CUDA and not h.value
+        assert len(cuda_lib.ccm_matcher_last_error(None)) > 0
+    # null handles never dereference
+    assert cuda_lib.ccm_matcher_sync(None) == CCM_E_BADARG
+    assert cuda_lib.ccm_frame_pack_create(None, 10, ctypes.byref(h)) == CCM_E_BADARG
+    assert cuda_lib.ccm_search_window(None, None, None, 0, None, None, None, None, None) == CCM_E_BADARG
+    assert cuda_lib.ccm_match_allpairs_best2(None, None, 0, None, 0, 0, None) == CCM_E_BADARG
+    assert cuda_lib.ccm_matcher_launch_count(None) == 0

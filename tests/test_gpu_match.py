@@ -1,0 +1,265 @@
+"""GPU parity: the CUDA Hamming searches (through the C ABI, include/ccm_match.h) against the CPU oracle
+(oracle/match_oracle.cpp, the restated loops of cslam/src/ORBmatcher.cpp) on the same seeded inputs. Everything here
+is integer / index work: the bar is bit-exact (distances, indices, accepted sets, holder state, return values)."""
+import numpy as np
+import pytest
+
+from _oracle import OracleFrame, OracleMatcher
+
+pytestmark = pytest.mark.gpu
+
+W, H = 752, 480
+SF = (np.float32(1.2) ** np.arange(8)).astype(np.float32)   # stand-in for mvScaleFactor; both sides get the same table
+
+
+@pytest.fixture(scope="module")
+def gm(cuda_lib):
+    from motioncheck_ccm_slam_b200.matcher import Matcher
+    m = Matcher(0)
+    yield m
+    m.close()
+
+
+def _frames(seed, n=1000, **kw):
+    from motioncheck_ccm_slam_b200.synth import make_feature_frame, make_next_frame
+    a = make_feature_frame(seed, n, W, H)
+    b, src = make_next_frame(seed + 1, a, W, H, **kw)
+    return a, b, src
+
+
+def _pack(gm, fr, grid=None, cap=None):
+    from motioncheck_ccm_slam_b200.matcher import FramePack, frame_grid
+    grid = grid or frame_grid(W, H)
+    p = FramePack(gm, cap or max(len(fr["x"]), 1))
+    p.upload(grid, fr["desc"], fr["x"], fr["y"], fr["octave"], fr["angle"])
+    return p, OracleFrame(fr["desc"], fr["x"], fr["y"], fr["octave"], fr["angle"], grid)
+
+
+def _same_res(r_gpu, r_cpu, fields=("best_idx", "best_dist", "best_dist2", "accepted")):
+    for f in fields:
+        bad = np.nonzero(r_gpu[f] != r_cpu[f])[0]
+        assert len(bad) == 0, (f, bad[:10], r_gpu[bad[:10]], r_cpu[bad[:10]])
+
+
+def test_descriptor_distance(gm):
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (4097, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (4097, 32), dtype=np.uint8)
+    b[:5] = a[:5]
+    b[5] = ~a[5]
+    d = gm.DescriptorDistance(a, b)
+    assert np.array_equal(d, np.unpackbits(a ^ b, axis=1).sum(1))
+    assert np.array_equal(d[:64], OracleMatcher().descriptor_distance(a[:64], b[:64]))
+    assert d[5] == 256 and d[0] == 0
+
+
+@pytest.mark.parametrize("seed,n", [(11, 1000), (12, 2000), (13, 1), (14, 0), (15, 5000)])
+def test_grid_matches_frame_assign(gm, seed, n):
+    from motioncheck_ccm_slam_b200.matcher import frame_grid
+    from motioncheck_ccm_slam_b200.synth import make_feature_frame
+    fr = make_feature_frame(seed, max(n, 1), W, H)
+    fr = {k: v[:n] for k, v in fr.items()}
+    if n > 10:   # features outside the image bounds (undistortion can push them out) and on cell boundaries
+        fr["x"][:4] = [-30.0, W + 20.0, 10.0, 375.99]
+        fr["y"][:4] = [10.0, 10.0, H + 9.0, -0.49]
+        fr["x"][4:8] = [5.0133333, 10.026666, 15.04, 20.053333]
+    grid = frame_grid(W, H, min_x=-3.5, min_y=-2.25) if seed % 2 else frame_grid(W, H)
+    p, of = _pack(gm, fr, grid, cap=max(n, 1) + 7)
+    cs, items = p.get_grid()
+    ocs, oitems = of.csr()
+    assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
+    assert p.count() == n
+
+
+def _projection_inputs(a, b, src, rng, level_from="b"):
+    """Queries = map points seen in frame a, projected into frame b at (their true position + noise)."""
+    n = len(a["x"])
+    inv = np.full(n, -1)
+    inv[src[src >= 0]] = np.nonzero(src >= 0)[0]
+    u = np.where(inv >= 0, b["x"][np.maximum(inv, 0)], a["x"] + 2).astype(np.float32) + rng.normal(0, 1.5, n).astype(np.float32)
+    v = np.where(inv >= 0, b["y"][np.maximum(inv, 0)], a["y"] + 1).astype(np.float32) + rng.normal(0, 1.5, n).astype(np.float32)
+    level = np.where(inv >= 0, b["octave"][np.maximum(inv, 0)], a["octave"]).astype(np.int32)
+    level = np.clip(level + rng.choice([0, 0, 0, 1], n), 0, 7).astype(np.int32)
+    valid = (rng.random(n) < 0.9).astype(np.uint8)
+    obs = (rng.random(n) < 0.8).astype(np.uint8)
+    return valid, u, v, level, obs
+
+
+@pytest.mark.parametrize("seed,th,nnratio", [(21, 1.0, 0.8), (22, 5.0, 0.8), (23, 3.0, 0.6), (24, 12.0, 0.9)])
+def test_search_by_projection_mappoints(gm, seed, th, nnratio):
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    rng = np.random.default_rng(seed)
+    a, b, src = _frames(seed)
+    valid, u, v, level, obs = _projection_inputs(a, b, src, rng)
+    viewcos = rng.choice([0.9, 0.9985, 0.998, 0.99801], len(u)).astype(np.float32)
+    holder0 = rng.choice([-1, -1, -1, -2, -3], len(b["x"])).astype(np.int32)
+    p, of = _pack(gm, b)
+    hg, hc = holder0.copy(), holder0.copy()
+    nm_g, res_g = ORBmatcher(gm, nnratio, True).SearchByProjection_MapPoints(p, valid, u, v, level, viewcos, a["desc"], obs, th, SF, hg)
+    nm_c, res_c = OracleMatcher(nnratio, True).projection_mappoints(of, valid, u, v, level, viewcos, a["desc"], obs, th, SF, hc)
+    _same_res(res_g, res_c)
+    assert nm_g == nm_c and np.array_equal(hg, hc)
+    assert nm_c > 200
+
+
+@pytest.mark.parametrize("seed,th,ori", [(31, 7.0, True), (32, 14.0, True), (33, 7.0, False), (34, 30.0, True)])
+def test_search_by_projection_lastframe(gm, seed, th, ori):
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    rng = np.random.default_rng(seed)
+    a, b, src = _frames(seed)
+    valid, u, v, _, obs = _projection_inputs(a, b, src, rng)
+    holder0 = rng.choice([-1, -1, -1, -1, -2, -3], len(b["x"])).astype(np.int32)
+    p, of = _pack(gm, b)
+    hg, hc = holder0.copy(), holder0.copy()
+    nm_g, res_g = ORBmatcher(gm, 0.9, ori).SearchByProjection_LastFrame(p, valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hg)
+    nm_c, res_c = OracleMatcher(0.9, ori).projection_lastframe(of, valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hc)
+    _same_res(res_g, res_c)
+    assert nm_g == nm_c and np.array_equal(hg, hc)
+    assert nm_c > 200
+
+
+@pytest.mark.parametrize("seed,th", [(41, 10), (42, 4)])
+def test_search_by_projection_kf_sim3(gm, seed, th):
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    rng = np.random.default_rng(seed)
+    a, b, src = _frames(seed, n=3000)
+    valid, u, v, level, claims = _projection_inputs(a, b, src, rng)
+    holder0 = rng.choice([-1, -1, -1, -2], len(b["x"])).astype(np.int32)
+    p, of = _pack(gm, b)
+    hg, hc = holder0.copy(), holder0.copy()
+    nm_g, res_g = ORBmatcher(gm, 0.75, True).SearchByProjection_KFSim3(p, valid, u, v, level, a["desc"], claims, th, SF, hg)
+    nm_c, res_c = OracleMatcher(0.75, True).projection_kf_sim3(of, valid, u, v, level, a["desc"], claims, th, SF, hc)
+    _same_res(res_g, res_c)
+    assert nm_g == nm_c and np.array_equal(hg, hc)
+    assert nm_c > 100
+
+
+@pytest.mark.parametrize("seed,gate,th_dist", [(51, False, 100), (52, True, 50), (53, False, 50)])
+def test_search_best_in_window(gm, seed, gate, th_dist):
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    rng = np.random.default_rng(seed)
+    a, b, src = _frames(seed)
+    valid, u, v, level, _ = _projection_inputs(a, b, src, rng)
+    radius = (np.float32(7.5) * SF[level]).astype(np.float32)
+    inv_sigma2 = (1.0 / (SF * SF)).astype(np.float32) if gate else None
+    p, of = _pack(gm, b)
+    nm_g, res_g = ORBmatcher(gm).SearchBestInWindow(p, valid, u, v, radius, level, a["desc"], th_dist, inv_sigma2)
+    nm_c, res_c = OracleMatcher().best_in_window(of, valid, u, v, radius, level, a["desc"], th_dist, inv_sigma2)
+    _same_res(res_g, res_c)
+    assert nm_g == nm_c and nm_c > 100
+
+
+def test_greedy_chain_conflicts(gm):
+    """Many identical queries fighting for few targets: the reference's sequential claim order must be reproduced."""
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    rng = np.random.default_rng(61)
+    nt, nq = 40, 300
+    base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    from motioncheck_ccm_slam_b200.synth import perturb_descriptors
+    b = dict(desc=perturb_descriptors(rng, np.repeat(base, nt, 0), 0.05), x=rng.uniform(100, 130, nt).astype(np.float32),
+             y=rng.uniform(100, 130, nt).astype(np.float32), octave=np.zeros(nt, np.int32), angle=rng.uniform(0, 360, nt).astype(np.float32))
+    qd = perturb_descriptors(rng, np.repeat(base, nq, 0), 0.02)
+    u = np.full(nq, 115, np.float32); v = np.full(nq, 115, np.float32)
+    valid = np.ones(nq, np.uint8); obs = (rng.random(nq) < 0.7).astype(np.uint8)
+    p, of = _pack(gm, b)
+    for mode in ("last", "mp", "sim3"):
+        hg, hc = np.full(nt, -1, np.int32), np.full(nt, -1, np.int32)
+        if mode == "last":
+            nm_g, res_g = ORBmatcher(gm, 0.9, False).SearchByProjection_LastFrame(p, valid, u, v, np.zeros(nq), np.zeros(nq), qd, obs, 30.0, SF, hg)
+            nm_c, res_c = OracleMatcher(0.9, False).projection_lastframe(of, valid, u, v, np.zeros(nq), np.zeros(nq), qd, obs, 30.0, SF, hc)
+        elif mode == "mp":
+            nm_g, res_g = ORBmatcher(gm, 0.95, False).SearchByProjection_MapPoints(p, valid, u, v, np.zeros(nq), np.ones(nq), qd, obs, 8.0, SF, hg)
+            nm_c, res_c = OracleMatcher(0.95, False).projection_mappoints(of, valid, u, v, np.zeros(nq), np.ones(nq), qd, obs, 8.0, SF, hc)
+        else:
+            nm_g, res_g = ORBmatcher(gm).SearchByProjection_KFSim3(p, valid, u, v, np.zeros(nq), qd, obs, 30, SF, hg)
+            nm_c, res_c = OracleMatcher().projection_kf_sim3(of, valid, u, v, np.zeros(nq), qd, obs, 30, SF, hc)
+        _same_res(res_g, res_c)
+        assert nm_g == nm_c and np.array_equal(hg, hc), mode
+        assert nm_c >= 20
+
+
+@pytest.mark.parametrize("seed,window,ori", [(71, 100, True), (72, 30, True), (73, 100, False)])
+def test_search_for_initialization(gm, seed, window, ori):
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    a, b, src = _frames(seed, n=2000, motion=(6.0, -3.0))
+    p, of = _pack(gm, b)
+    prev_g = np.stack([a["x"], a["y"]], 1).astype(np.float32).copy()
+    prev_c = prev_g.copy()
+    nm_g, m_g = ORBmatcher(gm, 0.9, ori).SearchForInitialization(a["desc"], a["octave"], a["angle"], prev_g, p,
+                                                                np.stack([b["x"], b["y"]], 1), window)
+    nm_c, m_c = OracleMatcher(0.9, ori).search_for_initialization(a["desc"], a["octave"], a["angle"], prev_c, of, window)
+    assert nm_g == nm_c and np.array_equal(m_g, m_c) and np.array_equal(prev_g, prev_c)
+    assert nm_c > 50
+
+
+@pytest.mark.parametrize("seed,nnratio,ori,n_nodes", [(81, 0.7, True, 1000), (82, 0.75, False, 100), (83, 0.9, True, 7)])
+def test_search_by_bow(gm, seed, nnratio, ori, n_nodes):
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    from motioncheck_ccm_slam_b200.synth import bow_node_ids
+    rng = np.random.default_rng(seed)
+    a, b, src = _frames(seed, flip_prob=0.03)
+    na, nb = bow_node_ids(a["desc"], n_nodes), bow_node_ids(b["desc"], n_nodes)
+    na[rng.random(len(na)) < 0.05] = -1
+    nb[rng.random(len(nb)) < 0.05] = -1
+    va = (rng.random(len(na)) < 0.8).astype(np.uint8)
+    vb = (rng.random(len(nb)) < 0.8).astype(np.uint8)
+    g, c = ORBmatcher(gm, nnratio, ori), OracleMatcher(nnratio, ori)
+    nm_g, mf_g, res_g = g.SearchByBoW_KF_Frame(a["desc"], na, va, a["angle"], b["desc"], nb, b["angle"])
+    nm_c, mf_c, res_c = c.bow_kf_frame(a["desc"], na, va, a["angle"], b["desc"], nb, b["angle"])
+    _same_res(res_g, res_c)
+    assert nm_g == nm_c and np.array_equal(mf_g, mf_c) and nm_c > 20
+    nm_g, m12_g, res_g = g.SearchByBoW_KF_KF(a["desc"], na, va, a["angle"], b["desc"], nb, vb, b["angle"])
+    nm_c, m12_c, res_c = c.bow_kf_kf(a["desc"], na, va, a["angle"], b["desc"], nb, vb, b["angle"])
+    _same_res(res_g, res_c)
+    assert nm_g == nm_c and np.array_equal(m12_g, m12_c) and nm_c > 10
+
+
+@pytest.mark.parametrize("nq,nt", [(1000, 20000), (1, 1), (255, 257), (257, 255), (1025, 4099), (500, 70001), (3, 0), (2048, 513)])
+def test_allpairs_best2(gm, nq, nt):
+    from motioncheck_ccm_slam_b200.synth import perturb_descriptors
+    rng = np.random.default_rng(nq * 7 + nt)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    if nt > 10:
+        k = min(nq, nt) // 2
+        q[:k] = perturb_descriptors(rng, t[rng.integers(0, nt, k)], 0.05)
+        t[nt // 2] = t[3]; t[nt - 1] = t[3]                 # exact duplicates: first index wins, second distance == best
+        q[0] = t[3]
+    out = gm.match_allpairs_best2(q, t, index_base=0)
+    ref = OracleMatcher(0.75).allpairs_best2(q, t)
+    if nt == 0:
+        assert np.all(out["idx"] == 0xFFFFFFFF) and np.all(out["d1"] == 256) and np.all(out["d2"] == 256)
+        return
+    assert np.array_equal(out["idx"].astype(np.int64), ref["best_idx"].astype(np.int64))
+    assert np.array_equal(out["d1"], ref["best_dist"]) and np.array_equal(out["d2"], ref["best_dist2"])
+    if nt > 10:
+        assert out["idx"][0] == 3 and out["d1"][0] == 0 and out["d2"][0] == 0
+
+
+def test_allpairs_sharded_merge_equals_single(gm):
+    """Shard the target database, search each shard with its index base, merge: identical to one search (the NCCL
+    path of BASELINE.json configs[4] does exactly this with the allgather in between)."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200.matcher import BEST2_DTYPE
+    rng = np.random.default_rng(5)
+    nq, nt, shards = 1000, 60000, 4
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    t[50000] = t[100]; q[7] = t[100]
+    whole = gm.match_allpairs_best2(q, t)
+    dq = torch.from_numpy(q).cuda(); dt = torch.from_numpy(t).cuda()
+    parts = torch.zeros((shards, nq, 8), dtype=torch.uint8, device="cuda")
+    out = torch.zeros((nq, 8), dtype=torch.uint8, device="cuda")
+    acc = torch.zeros(nq, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    bounds = [0, 9000, 9000 + 256, 41000, nt]
+    for s in range(shards):
+        lo, hi = bounds[s], bounds[s + 1]
+        gm.match_allpairs_best2_device(dt.data_ptr() * 0 + dq.data_ptr(), nq, dt.data_ptr() + lo * 32, hi - lo, lo, parts[s].data_ptr())
+    gm.match_allpairs_merge_device(parts.data_ptr(), shards, nq, 0.75, out.data_ptr(), acc.data_ptr())
+    gm.sync()
+    merged = out.cpu().numpy().view(BEST2_DTYPE).reshape(-1)
+    assert np.array_equal(merged, whole)
+    ref = OracleMatcher(0.75).allpairs_best2(q, t)
+    assert np.array_equal(acc.cpu().numpy().astype(np.int32), ref["accepted"])
+    assert merged["idx"][7] == 100 and merged["d2"][7] == 0
