@@ -167,6 +167,173 @@ def run_reference(args, wl, rank):
 
 
 # ----------------------------------------------------------------------------------------------------------
+# Hamming legs of the metric ("Hamming Gmatch/s"): the server keyframe-database search (configs[4]: 1000 query
+# descriptors against 8 x 500 KF x 1000 = 4.0 M target descriptors, sharded by rank + NCCL allgather of the per-shard
+# best-2 records + merge) and the tracking-side windowed searches on the extractor's own output (configs[1]/[3]).
+# ----------------------------------------------------------------------------------------------------------
+def int_pipe_peak_gpairs(sms, sm_mhz):
+    """POPC-pipe roofline for the textbook loop (8 XOR + 8 POPC per pair): POPC issues 16 lanes/clk/SM on B200
+    (tools/ubench_int.cu -> profiles/r1_ubench_int.json: 15.9 measured)."""
+    return sms * 16 * sm_mhz * 1e6 / 8 / 1e9
+
+
+def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d_desc, d_n, cap, w, h, pitch, barrier):
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    from motioncheck_ccm_slam_b200.matcher import (FramePack, Matcher, QUERY_DTYPE, Q_OBS, Q_VALID, WIN_PROJ_LASTFRAME,
+                                                   WIN_PROJ_MAPPOINTS, frame_grid, packs_from_extractor_batch_device,
+                                                   search_window_batch_device)
+    out = {}
+    m = Matcher(dev.index)
+    ms = torch.cuda.ExternalStream(m.stream(), device=dev)
+    B = d_kp.shape[0]
+
+    # ---- (1) all-pairs best-2 over the keyframe database, target shard per rank ----
+    nq, nt_total = 1000, args.db
+    lo, hi = nt_total * rank // world, nt_total * (rank + 1) // world
+    g = torch.Generator(device=dev); g.manual_seed(7)
+    d_q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)     # same queries on every rank
+    g.manual_seed(100 + rank)
+    d_t = torch.randint(0, 256, (hi - lo, 32), dtype=torch.uint8, device=dev, generator=g)
+    d_part = torch.zeros((nq, 8), dtype=torch.uint8, device=dev)
+    d_all = torch.zeros((world, nq, 8), dtype=torch.uint8, device=dev)
+    d_best = torch.zeros((nq, 8), dtype=torch.uint8, device=dev)
+    d_acc = torch.zeros((nq,), dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+
+    def ap_step():
+        m.match_allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), hi - lo, lo, d_part.data_ptr())
+        if world > 1:
+            with torch.cuda.stream(ms):
+                dist.all_gather_into_tensor(d_all, d_part)       # 8 KB per rank: the only data-path collective
+            m.match_allpairs_merge_device(d_all.data_ptr(), world, nq, 0.75, d_best.data_ptr(), d_acc.data_ptr())
+        else:
+            m.match_allpairs_merge_device(d_part.data_ptr(), 1, nq, 0.75, d_best.data_ptr(), d_acc.data_ptr())
+
+    ksteps = max(3, min(args.steps, 10))
+    for _ in range(3):
+        ap_step()
+    m.sync(); barrier()
+    l0 = m.launch_count()
+    with torch.cuda.stream(ms):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(ksteps):
+            ap_step()
+        e1.record()
+    m.sync(); barrier()
+    ap_ms = e0.elapsed_time(e1) / ksteps
+    ap_launches = m.launch_count() - l0
+    out["_ap_ms"] = ap_ms
+    out["allpairs"] = {"nq": nq, "nt_total": nt_total, "nt_per_gpu": hi - lo, "steps": ksteps,
+                       "collective": "nccl all_gather of %d B per rank + merge kernel" % (nq * 8) if world > 1 else "none (1 shard)",
+                       "l2": "target shard %.0f MB streamed once per step" % ((hi - lo) * 32 / 1e6)}
+
+    # ---- (2) tracking-side searches on the extractor's output: pack build + LastFrame(th 7) + MapPoints(th 1) ----
+    R = min(d_frames.shape[0], 2)
+    grid = frame_grid(w, h)
+    packs = [FramePack(m, cap) for _ in range(B)]
+    sf = ex.GetScaleFactors()
+    q_sets = []
+    for r in range(R):
+        ex.extract_batch_device(d_frames[r].data_ptr(), B, h, w, pitch, pitch * h, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+        ex.sync()
+        kp = d_kp.cpu().numpy().view(KP_DTYPE).reshape(B, cap)
+        n = d_n.cpu().numpy()
+        q1 = np.zeros((B, cap), QUERY_DTYPE); q2 = np.zeros((B, cap), QUERY_DTYPE)
+        for j in range(B):
+            k = kp[j, :n[j]]
+            # host geometry of the reference loops: last frame's points moved by the stream's motion (-2,-1) per frame
+            q1["u"][j, :n[j]] = k["x"] - 2; q1["v"][j, :n[j]] = k["y"] - 1; q1["angle"][j, :n[j]] = k["angle"]
+            q1["r"][j, :n[j]] = np.float32(7.0) * sf[k["octave"]]
+            q1["min_level"][j, :n[j]] = k["octave"] - 1; q1["max_level"][j, :n[j]] = k["octave"] + 1
+            q1["flags"][j, :n[j]] = Q_VALID | Q_OBS
+            q2["u"][j, :n[j]] = k["x"] - 4; q2["v"][j, :n[j]] = k["y"] - 2
+            q2["r"][j, :n[j]] = np.float32(2.5) * sf[k["octave"]]            # RadiusByViewingCos(1.0) * th(1) * scale
+            q2["min_level"][j, :n[j]] = k["octave"] - 1; q2["max_level"][j, :n[j]] = k["octave"]
+            q2["flags"][j, :n[j]] = Q_VALID | Q_OBS
+        q_sets.append((torch.from_numpy(q1.view(np.uint8).reshape(B, cap, 24)).to(dev),
+                       torch.from_numpy(q2.view(np.uint8).reshape(B, cap, 24)).to(dev)))
+    d_holder = torch.zeros((B, cap), dtype=torch.int32, device=dev)
+    d_nm = torch.zeros((2, B), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+
+    def track_step(i):
+        r = i % R
+        ex.extract_batch_device(d_frames[r].data_ptr(), B, h, w, pitch, pitch * h, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+        ms.wait_stream(ext)
+        with torch.cuda.stream(ms):
+            d_holder.fill_(-1)
+        packs_from_extractor_batch_device(packs, grid, d_kp.data_ptr(), d_desc.data_ptr(), d_n.data_ptr(), cap)
+        # frame t searched with frame t-1's features (jobs 1..B-1), then with frame t-2's as "map points" (jobs 2..B-1)
+        search_window_batch_device(m, packs[1:], WIN_PROJ_LASTFRAME, 0.9, 100, True, d_n.data_ptr(), cap, q_sets[r][0].data_ptr(),
+                                   d_desc.data_ptr(), d_holder[1:].data_ptr(), cap, None, d_nm[0, 1:].data_ptr())
+        search_window_batch_device(m, packs[2:], WIN_PROJ_MAPPOINTS, 0.8, 100, True, d_n.data_ptr(), cap, q_sets[r][1].data_ptr(),
+                                   d_desc.data_ptr(), d_holder[2:].data_ptr(), cap, None, d_nm[1, 2:].data_ptr())
+        ext.wait_stream(ms)       # the next batch overwrites d_kp / d_desc
+
+    for i in range(3):
+        track_step(i)
+    m.sync(); ex.sync(); barrier()
+    l0 = m.launch_count()
+    with torch.cuda.stream(ext):
+        e0 = torch.cuda.Event(enable_timing=True); e0.record()
+    for i in range(args.steps):
+        track_step(3 + i)
+    with torch.cuda.stream(ext):
+        e1 = torch.cuda.Event(enable_timing=True); e1.record()
+    m.sync(); ex.sync(); barrier()
+    tr_ms = e0.elapsed_time(e1) / args.steps
+    nm = d_nm.cpu().numpy()
+    out["_tr_ms"] = tr_ms
+    out["tracking"] = {"what": "extract + device frame packs (75x48 grid) + SearchByProjection(F,LastF,th=7) + SearchByProjection(F,mappoints,th=1), "
+                               "%d frames per step, queries = previous frames' keypoints moved by the stream motion" % B,
+                       "matches_per_frame_lastframe": float(nm[0, 1:].mean()), "matches_per_frame_mappoints": float(nm[1, 2:].mean()),
+                       "matcher_launches_per_step": (m.launch_count() - l0) / args.steps}
+    out["_launches"] = ap_launches + (m.launch_count() - l0)
+    for p in packs:
+        p.close()
+    m.close()
+    return out
+
+
+def cpu_matcher_baseline(frames, nf, nl, n_pairs=6):
+    """Oracle port of the two tracking-side searches, single thread, on consecutive frames of the same stream."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle
+    from motioncheck_ccm_slam_b200.matcher import frame_grid
+    h, w = frames.shape[1:]
+    ex = _oracle.OracleExtractor(nf, SCALE, nl, INI_TH, MIN_TH)
+    sf = ex.tables()[0][0]
+    grid = frame_grid(w, h)
+    ext = [ex(frames[i]) for i in range(n_pairs + 1)]
+    om = _oracle.OracleMatcher(0.9, True)
+    t0 = time.perf_counter()
+    nm = 0
+    for i in range(n_pairs):
+        (k0, d0), (k1, d1) = ext[i], ext[i + 1]
+        F = _oracle.OracleFrame(d1, k1["x"], k1["y"], k1["octave"], k1["angle"], grid)
+        hold = np.full(len(k1), -1, np.int32)
+        one = np.ones(len(k0), np.uint8)
+        nm += om.projection_lastframe(F, one, k0["x"] - 2, k0["y"] - 1, k0["octave"], k0["angle"], d0, one, 7.0, sf, hold)[0]
+        hold[:] = -1
+        nm += om.projection_mappoints(F, one, k0["x"] - 2, k0["y"] - 1, k0["octave"], one.astype(np.float32), d0, one, 1.0, sf, hold)[0]
+    dt = time.perf_counter() - t0
+    return n_pairs / dt, nm / n_pairs
+
+
+def cpu_allpairs_baseline(nq=64, nt=200000):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle
+    rng = np.random.default_rng(7)
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    om = _oracle.OracleMatcher(0.75)
+    t0 = time.perf_counter()
+    om.allpairs_best2(q, t)
+    return nq * nt / (time.perf_counter() - t0) / 1e9
+
+
+# ----------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------
 def run_ours(args, wl, rank, world, local_rank):
@@ -257,10 +424,14 @@ def run_ours(args, wl, rank, world, local_rank):
     clocks = sampler.stop() if rank == 0 else None
     n_kp_host = int(sum(out_n[:]))
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    ham = None
+    if not args.no_match:
+        ham = hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d_desc, d_n, cap, w, h, pitch, barrier)
+    t = torch.tensor([dev_ms, e2e_s * 1e3, ham["_ap_ms"] if ham else 0.0, ham["_tr_ms"] if ham else 0.0],
+                     dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)          # max over ranks
-    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    dev_ms, e2e_ms, ap_ms, tr_ms = float(t[0]), float(t[1]), float(t[2]), float(t[3])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -299,12 +470,30 @@ def run_ours(args, wl, rank, world, local_rank):
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
+    if ham:
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        sm_max = (clocks or {}).get("sm_max_mhz") or 1965.0
+        peak_pairs = int_pipe_peak_gpairs(sms, sm_max)
+        gp = ham["allpairs"]["nq"] * ham["allpairs"]["nt_total"] / (ap_ms * 1e-3) / 1e9
+        ham["allpairs"].update({"gpairs_per_s": gp, "ms_per_query_keyframe": ap_ms})
+        ham["allpairs"]["roofline"] = {
+            "bound": "int-pipe (POPC)", "achieved": gp / world, "peak": peak_pairs, "unit": "Gpair/s per GPU", "frac": gp / world / peak_pairs,
+            "peak_kind": "SMs x 16 POPC/clk (measured 15.9, profiles/r1_ubench_int.json) x %.0f MHz / 8 POPC per pair; the kernel's carry-save "
+                         "LOP3 tree needs 4 POPC per pair, so frac can exceed 1 (microbenchmarked ceiling of that loop: 680 Gpair/s)" % sm_max}
+        ham["tracking"].update({"frames_per_s": B * world / (tr_ms * 1e-3), "ms_per_step": tr_ms})
+        line["hamming"] = {k: v for k, v in ham.items() if not k.startswith("_")}
+        line["gpu_launches"] += int(ham["_launches"])
     if not args.no_cpu and world == 1:
         cores = os.cpu_count() or 1
         fpt = 24
         fps, dt, kind = cpu_reference_fps(frames[0], nf, nl, cores, fpt)
         line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                                 "sample": "%d threads x %d frames of the same stream, %.1f s" % (cores, fpt, dt)}
+        if ham:
+            pps, nmm = cpu_matcher_baseline(frames[0], nf, nl)
+            line["cpu_baseline"]["matcher"] = {
+                "tracking_searches_frame_pairs_per_s": pps, "matches_per_pair": nmm, "allpairs_gpairs_per_s": cpu_allpairs_baseline(),
+                "cores": 1, "kind": "port", "sample": "6 consecutive frame pairs (both SearchByProjection calls); 64 x 200000 descriptor pairs"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -320,6 +509,8 @@ def main():
     ap.add_argument("--batch", type=int, default=64, help="frames in flight per step (configs[1]: 64)")
     ap.add_argument("--rotate", type=int, default=8, help="distinct input batches cycled through (inputs > L2)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-match", action="store_true", help="skip the Hamming-search legs")
+    ap.add_argument("--db", type=int, default=4000000, help="keyframe-database descriptors (configs[4]: 8 x 500 x 1000)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -58,6 +58,11 @@ int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, co
  * mvKeysUn, i.e. a camera without distortion (Frame.cpp:279-283), or pass d_xy_un [capacity][2] to override them */
 int ccm_frame_pack_from_extractor_device(ccm_frame_pack* p, const ccm_grid_params* g, const ccm_keypoint* d_kp,
                                          const uint8_t* d_desc, const int* d_n, const float* d_xy_un);
+/* same for a whole extractor batch in two launches: packs[j] takes frame j of ccm_orb_extract_batch_device's output
+ * (d_kp [n][kp_stride], d_desc [n][kp_stride][32], d_n [n]; d_xy_un [n][kp_stride][2] or NULL) */
+int ccm_frame_pack_from_extractor_batch_device(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g,
+                                               const ccm_keypoint* d_kp, const uint8_t* d_desc, const int* d_n, int kp_stride,
+                                               const float* d_xy_un);
 /* test tap: the grid as CSR over cells in (ix*rows + iy) order: cell_start[cols*rows+1], items[n]; *n_items out */
 int ccm_frame_pack_get_grid(ccm_frame_pack* p, int* cell_start, int* items, int* n_items);
 int ccm_frame_pack_count(ccm_frame_pack* p, int* n);

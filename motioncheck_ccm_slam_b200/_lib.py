@@ -76,6 +76,7 @@ SIGNATURES.update({
     "ccm_frame_pack_destroy": (None, [_vp]),
     "ccm_frame_pack_upload": (_i, [_vp, _gp, _i, _vp, _vp, _vp, _vp, _vp]),
     "ccm_frame_pack_from_extractor_device": (_i, [_vp, _gp, _vp, _vp, _vp, _vp]),
+    "ccm_frame_pack_from_extractor_batch_device": (_i, [_c.POINTER(_vp), _i, _gp, _vp, _vp, _vp, _i, _vp]),
     "ccm_frame_pack_get_grid": (_i, [_vp, _vp, _vp, _ip]),
     "ccm_frame_pack_count": (_i, [_vp, _ip]),
     "ccm_search_window": (_i, [_vp, _vp, _wp, _i, _vp, _vp, _vp, _vp, _ip]),

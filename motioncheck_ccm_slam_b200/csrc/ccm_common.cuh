@@ -23,6 +23,8 @@ struct LevelDesc {
     // cell grid of ComputeKeyPointsOctTree (:941-955)
     int nCols, nRows, wCell, hCell;
     int cell_base;           // first cell id of this level in the flattened (all levels) cell list
+    int blur_tile_base;      // first blur tile (128 x 128 px) of this level in the flattened tile list
+    int blur_tiles_x;
     // quadtree (:707-726)
     int quota;               // mnFeaturesPerLevel[l]
     int nIni;
@@ -43,6 +45,7 @@ struct LevelTable {
     LevelDesc l[CCM_MAX_LEVELS];
     int nlevels;
     int total_cells;
+    int total_blur_tiles;
     int corners_per_frame;   // u32 units
     int kps_per_frame;       // slot-list length per frame (sum of node_cap)
     int ini_th, min_th;

@@ -162,6 +162,19 @@ static int check_grid(ccm_matcher* m, const ccm_grid_params* g) {
     return CCM_OK;
 }
 
+static int launch_build_grid(ccm_matcher* m, ccm_frame_pack* const* packs, int n_packs) {
+    std::vector<GridJob> jobs(n_packs);
+    for (int j = 0; j < n_packs; j++) jobs[j] = GridJob{pack_dev(packs[j]), packs[j]->cell_start, packs[j]->items};
+    GridJob* djobs;
+    int rc;
+    if ((rc = mbuf(m, MB_E, (size_t)n_packs, &djobs))) return rc;
+    MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(GridJob) * n_packs, cudaMemcpyHostToDevice, m->stream));
+    k_build_grid<<<n_packs, 1024, 0, m->stream>>>(djobs);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
 int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, const uint8_t* desc, const float* x,
                           const float* y, const int* octave, const float* angle) {
     if (!p) return CCM_E_BADARG;
@@ -180,28 +193,40 @@ int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, co
         MCK(cudaMemcpyAsync(p->angle, angle, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
     }
     MCK(cudaMemcpyAsync(p->n, &p->n_host, sizeof(int), cudaMemcpyHostToDevice, m->stream));
-    k_build_grid<<<1, 1024, 0, m->stream>>>(pack_dev(p), p->cell_start, p->items);
-    m->launches++;
-    MCK(cudaGetLastError());
+    { int rc2 = launch_build_grid(m, &p, 1); if (rc2) return rc2; }
     MCK(cudaStreamSynchronize(m->stream));    // host arrays (and &p->n_host) may be reused by the caller
     return CCM_OK;
 }
 
-int ccm_frame_pack_from_extractor_device(ccm_frame_pack* p, const ccm_grid_params* g, const ccm_keypoint* d_kp,
-                                         const uint8_t* d_desc, const int* d_n, const float* d_xy_un) {
-    if (!p || !d_kp || !d_desc || !d_n) return CCM_E_BADARG;
-    ccm_matcher* m = p->m;
+int ccm_frame_pack_from_extractor_batch_device(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g,
+                                               const ccm_keypoint* d_kp, const uint8_t* d_desc, const int* d_n, int kp_stride,
+                                               const float* d_xy_un) {
+    if (!packs || n_packs <= 0 || !packs[0] || !d_kp || !d_desc || !d_n || kp_stride <= 0) return CCM_E_BADARG;
+    ccm_matcher* m = packs[0]->m;
     int rc = check_grid(m, g);
     if (rc) return rc;
     cudaSetDevice(m->device);
-    p->g = *g; p->n_host = -1;
-    p->desc_view = d_desc;     // zero-copy: the matcher reads the extractor's descriptor rows in place
-    k_pack_from_keypoints<<<(p->cap + 255) / 256, 256, 0, m->stream>>>((const ccm_keypoint_dev*)d_kp, d_xy_un, d_n, p->cap,
-                                                                         p->x, p->y, p->angle, p->octave, p->n);
-    k_build_grid<<<1, 1024, 0, m->stream>>>(pack_dev(p), p->cell_start, p->items);
-    m->launches += 2;
+    std::vector<PackFill> fills(n_packs);
+    for (int j = 0; j < n_packs; j++) {
+        ccm_frame_pack* p = packs[j];
+        if (!p || p->m != m) { m->err = "pack belongs to another matcher"; return CCM_E_BADARG; }
+        p->g = *g; p->n_host = -1;
+        p->desc_view = d_desc + (size_t)j * kp_stride * 32;   // zero-copy: the matcher reads the extractor's descriptor rows in place
+        fills[j] = PackFill{p->x, p->y, p->angle, p->octave, p->n, p->cap};
+    }
+    PackFill* dfills;
+    if ((rc = mbuf(m, MB_D, (size_t)n_packs, &dfills))) return rc;
+    MCK(cudaMemcpyAsync(dfills, fills.data(), sizeof(PackFill) * n_packs, cudaMemcpyHostToDevice, m->stream));
+    k_pack_from_keypoints<<<n_packs, 256, 0, m->stream>>>(dfills, (const ccm_keypoint_dev*)d_kp, d_xy_un, d_n, kp_stride);
+    m->launches++;
     MCK(cudaGetLastError());
-    return CCM_OK;
+    return launch_build_grid(m, packs, n_packs);
+}
+
+int ccm_frame_pack_from_extractor_device(ccm_frame_pack* p, const ccm_grid_params* g, const ccm_keypoint* d_kp,
+                                         const uint8_t* d_desc, const int* d_n, const float* d_xy_un) {
+    if (!p) return CCM_E_BADARG;
+    return ccm_frame_pack_from_extractor_batch_device(&p, 1, g, d_kp, d_desc, d_n, p->cap, d_xy_un);
 }
 
 int ccm_frame_pack_count(ccm_frame_pack* p, int* n) {

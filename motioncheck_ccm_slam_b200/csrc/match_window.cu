@@ -28,25 +28,33 @@
 #define KEY_NONE 0xffffffffffffffffull
 
 // ---- frame pack construction ----------------------------------------------------------------------------------
-// ccm_keypoint (AoS, extractor output) -> pack SoA; xy_un overrides the positions (mvKeysUn of a distorted camera)
-__global__ void k_pack_from_keypoints(const ccm_keypoint_dev* __restrict__ kp, const float* __restrict__ xy_un,
-                                      const int* __restrict__ n_ptr, int cap, float* x, float* y, float* angle,
-                                      int* octave, int* n_out) {
-    const int n = min(*n_ptr, cap);
-    if (blockIdx.x == 0 && threadIdx.x == 0) *n_out = n;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+// ccm_keypoint (AoS, extractor output) -> pack SoA, one CTA per pack; xy_un overrides the positions (mvKeysUn of a
+// distorted camera). Pack j reads frame j of the extractor's batch output (kp_stride keypoints apart).
+struct PackFill { float* x; float* y; float* angle; int* octave; int* n; int cap; };
+__global__ void __launch_bounds__(256) k_pack_from_keypoints(const PackFill* __restrict__ fills, const ccm_keypoint_dev* __restrict__ kp,
+                                                             const float* __restrict__ xy_un, const int* __restrict__ n_ptr, int kp_stride) {
+    const PackFill F = fills[blockIdx.x];
+    kp += (size_t)blockIdx.x * kp_stride;
+    if (xy_un) xy_un += (size_t)blockIdx.x * kp_stride * 2;
+    const int n = min(n_ptr[blockIdx.x], min(F.cap, kp_stride));
+    if (threadIdx.x == 0) *F.n = n;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
         const ccm_keypoint_dev k = kp[i];
-        x[i] = xy_un ? xy_un[2 * i] : k.x;
-        y[i] = xy_un ? xy_un[2 * i + 1] : k.y;
-        angle[i] = k.angle;
-        octave[i] = k.octave;
+        F.x[i] = xy_un ? xy_un[2 * i] : k.x;
+        F.y[i] = xy_un ? xy_un[2 * i + 1] : k.y;
+        F.angle[i] = k.angle;
+        F.octave[i] = k.octave;
     }
 }
 
 // Frame::AssignFeaturesToGrid + PosInGrid (Frame.cpp:103-118, 255-265; note round(), not floor()): one CTA per pack.
 // Counting pass, block scan, scatter, then an insertion sort inside each cell restores ascending feature index
 // (what push_back in index order produces).
-__global__ void __launch_bounds__(1024) k_build_grid(PackDev P, int* cell_start, int* items) {
+struct GridJob { PackDev pack; int* cell_start; int* items; };
+__global__ void __launch_bounds__(1024) k_build_grid(const GridJob* __restrict__ jobs) {
+    const PackDev P = jobs[blockIdx.x].pack;
+    int* cell_start = jobs[blockIdx.x].cell_start;
+    int* items = jobs[blockIdx.x].items;
     __shared__ int cnt[CCM_MAX_GRID_CELLS];
     __shared__ int wsum[32];
     const int ncell = P.cols * P.rows;

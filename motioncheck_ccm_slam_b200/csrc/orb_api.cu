@@ -102,7 +102,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     std::memset(&T, 0, sizeof(T));
     const int L = h->cfg.nlevels, B = h->cfg.max_batch;
     T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
-    int cells = 0, corners = 0, kps = 0, max_node_cap = 0;
+    int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0;
     for (int l = 0; l < L; l++) {
         LevelDesc& D = T.l[l];
         D.w = (int)lrintf((float)cols * h->isf[l]);
@@ -113,6 +113,8 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         D.wCell = (int)std::ceil(width / D.nCols); D.hCell = (int)std::ceil(height / D.nRows);
         if (D.wCell > 64 || D.hCell > 64) { h->err = "internal: cell larger than 64 px"; return CCM_E_BADARG; }
         D.cell_base = cells; cells += D.nCols * D.nRows;
+        D.blur_tile_base = blur_tiles; D.blur_tiles_x = (D.w + BLUR_TW - 1) / BLUR_TW;
+        blur_tiles += D.blur_tiles_x * ((D.h + BLUR_TH - 1) / BLUR_TH);
         D.quota = h->quota[l];
         D.nIni = (int)std::round((float)(D.w - 32) / (D.h - 32));
         if (D.nIni < 1) { h->err = "unsupported aspect ratio (height > 2*width): the reference divides by zero here"; return CCM_E_BADARG; }
@@ -135,7 +137,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         D.img_stride = D.blur_stride = (size_t)D.img_pitch * D.h;
     }
     if (max_node_cap > 2048) { h->err = "nfeatures too large: more than 2045 features on one level"; return CCM_E_BADARG; }
-    T.total_cells = cells; T.corners_per_frame = corners; T.kps_per_frame = kps;
+    T.total_cells = cells; T.total_blur_tiles = blur_tiles; T.corners_per_frame = corners; T.kps_per_frame = kps;
     h->max_kps = kps;
     int cap = 32; while (cap < max_node_cap) cap <<= 1;
     h->qt_cap = cap;
@@ -215,11 +217,8 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
     k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_corners, h->d_corner_count);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[2], s));
-    for (int l = 0; l < T.nlevels; l++) {
-        dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 31) / 32, n);
-        k_blur_level<<<g, 256, 0, s>>>(T, l);
-        h->launches++;
-    }
+    k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+    h->launches++;
     if (st) CK(cudaEventRecord(h->ev[3], s));
     k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, h->d_corners, h->d_corner_count, h->d_node_of,
                                                           h->d_level_kps, h->d_level_kp_count);

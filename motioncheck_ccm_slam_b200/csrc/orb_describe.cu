@@ -4,49 +4,74 @@
 // ---------------------------------------------------------------------------------------------
 // K6: cv::GaussianBlur(level.clone(), 7x7, sigma 2, BORDER_REFLECT_101), cslam/src/ORBextractor.cpp:1258-1259.
 // OpenCV 4.x CV_8U fixed-point path: 8.8 kernel {18,34,48,56,48,34,18}/256, exact integer row and column
-// accumulation, single rounding (sum + 2^15) >> 16. Tile = 128 x 32 outputs; source tile with 3-px reflected
-// halo staged in shared memory, row pass into u16 shared memory, column pass packs 4 pixels per 32-bit store.
+// accumulation, single rounding (sum + 2^15) >> 16.
+// All levels of all frames in ONE launch. A warp owns a 128-px x 16-row strip: each lane loads one aligned 32-bit
+// word per source row (a warp reads 128 contiguous bytes), takes its left/right neighbour words by shuffle, forms the
+// four horizontal sums of its 4 pixels, and keeps the last seven row results in registers as a sliding window for the
+// vertical pass: no shared memory, every source byte is loaded once per strip (22 rows for 16 outputs), the output
+// is one coalesced 32-bit store per lane. Reflect-101 borders take a per-byte path only in the lanes that touch them.
 // ---------------------------------------------------------------------------------------------
 #define BLUR_TW 128
-#define BLUR_TH 32
+#define BLUR_RPW 16                      // output rows per warp
+#define BLUR_TH (8 * BLUR_RPW)           // rows per CTA (8 warps)
 
-__global__ void __launch_bounds__(256) k_blur_level(const __grid_constant__ LevelTable T, int lvl) {
-    __shared__ uint8_t src[BLUR_TH + 6][BLUR_TW + 8];
-    __shared__ uint16_t hb[BLUR_TH + 6][BLUR_TW];
+__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, int x, int x0, int w, int lane, uint32_t (&hs)[4]) {
+    const bool in = x < w;
+    uint32_t own = 0;
+    if (in) own = *reinterpret_cast<const uint32_t*>(row + x);
+    uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
+    uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
+    if (lane == 0 && x0 > 0) prev = *reinterpret_cast<const uint32_t*>(row + x - 4);
+    if (lane == 31 && x + 4 < w) next = *reinterpret_cast<const uint32_t*>(row + x + 4);
+    int b[10];
+    if (x - 3 >= 0 && x + 6 < w) {
+        b[0] = (prev >> 8) & 255; b[1] = (prev >> 16) & 255; b[2] = prev >> 24;
+        b[3] = own & 255; b[4] = (own >> 8) & 255; b[5] = (own >> 16) & 255; b[6] = own >> 24;
+        b[7] = next & 255; b[8] = (next >> 8) & 255; b[9] = (next >> 16) & 255;
+    } else if (in) {
+#pragma unroll
+        for (int k = 0; k < 10; k++) b[k] = row[ccm_reflect101(min(x - 3 + k, w + 2), w)];
+    } else {
+#pragma unroll
+        for (int k = 0; k < 10; k++) b[k] = 0;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++)
+        hs[k] = 18 * (b[k] + b[k + 6]) + 34 * (b[k + 1] + b[k + 5]) + 48 * (b[k + 2] + b[k + 4]) + 56 * b[k + 3];   // <= 65280
+}
+
+__global__ void __launch_bounds__(256) k_blur_levels(const __grid_constant__ LevelTable T) {
+    int lvl = 0;
+#pragma unroll 1
+    while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].blur_tile_base) lvl++;
     const LevelDesc& L = T.l[lvl];
-    const int f = blockIdx.z;
-    const int x0 = blockIdx.x * BLUR_TW, y0 = blockIdx.y * BLUR_TH;
+    const int tile = blockIdx.x - L.blur_tile_base;
+    const int tyi = tile / L.blur_tiles_x, txi = tile - tyi * L.blur_tiles_x;
+    const int f = blockIdx.y;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x0 = txi * BLUR_TW, x = x0 + 4 * lane;
+    const int wy0 = tyi * BLUR_TH + warp * BLUR_RPW;
+    const int w = L.w, h = L.h;
+    if (wy0 >= h) return;                                    // warp-uniform
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     uint8_t* __restrict__ out = L.blur + (size_t)f * L.blur_stride;
-    const int tid = threadIdx.x;
-
-    for (int i = tid; i < (BLUR_TH + 6) * (BLUR_TW + 6); i += 256) {
-        const int ty = i / (BLUR_TW + 6), tx = i - ty * (BLUR_TW + 6);
-        // clamp tile coordinates that fall beyond the image + halo (only feed outputs that are never stored)
-        const int gy = ccm_reflect101(min(y0 - 3 + ty, L.h + 2), L.h);
-        const int gx = ccm_reflect101(min(x0 - 3 + tx, L.w + 2), L.w);
-        src[ty][tx] = img[(size_t)gy * L.img_pitch + gx];
-    }
-    __syncthreads();
-    for (int i = tid; i < (BLUR_TH + 6) * BLUR_TW; i += 256) {
-        const int ty = i / BLUR_TW, tx = i - ty * BLUR_TW;
-        const uint8_t* s = &src[ty][tx];
-        const int acc = 18 * (s[0] + s[6]) + 34 * (s[1] + s[5]) + 48 * (s[2] + s[4]) + 56 * s[3];
-        hb[ty][tx] = (uint16_t)acc;          // <= 255*256 = 65280
-    }
-    __syncthreads();
-    for (int i = tid; i < BLUR_TH * (BLUR_TW / 4); i += 256) {
-        const int ty = i / (BLUR_TW / 4), tx = (i - ty * (BLUR_TW / 4)) * 4;
-        const int gy = y0 + ty, gx = x0 + tx;
-        if (gy >= L.h || gx >= L.w) continue;
-        uint32_t packed = 0;
+    uint32_t ring[7][4];
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const int acc = 18 * (hb[ty][tx + k] + hb[ty + 6][tx + k]) + 34 * (hb[ty + 1][tx + k] + hb[ty + 5][tx + k]) +
-                            48 * (hb[ty + 2][tx + k] + hb[ty + 4][tx + k]) + 56 * hb[ty + 3][tx + k];
-            packed |= (uint32_t)((acc + 32768) >> 16) << (8 * k);
+    for (int r = 0; r < BLUR_RPW + 6; r++) {
+        // source row wy0 + r - 3 (rows past the bottom only feed outputs that are never stored)
+        const int gy = ccm_reflect101(min(wy0 + r - 3, h + 2), h);
+        blur_hrow(img + (size_t)gy * L.img_pitch, x, x0, w, lane, ring[r % 7]);
+        if (r >= 6) {
+            const int oy = wy0 + r - 6;
+            uint32_t packed = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t acc = 18 * (ring[(r - 6) % 7][k] + ring[r % 7][k]) + 34 * (ring[(r - 5) % 7][k] + ring[(r - 1) % 7][k]) +
+                                     48 * (ring[(r - 4) % 7][k] + ring[(r - 2) % 7][k]) + 56 * ring[(r - 3) % 7][k];
+                packed |= ((acc + 32768u) >> 16) << (8 * k);
+            }
+            if (oy < h && x < w) *reinterpret_cast<uint32_t*>(out + (size_t)oy * L.blur_pitch + x) = packed;   // pitch multiple of 32: in-bounds
         }
-        *reinterpret_cast<uint32_t*>(out + (size_t)gy * L.blur_pitch + gx) = packed;   // pitch multiple of 32: in-bounds
     }
 }
 

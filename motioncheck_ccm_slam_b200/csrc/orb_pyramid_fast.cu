@@ -81,11 +81,32 @@ __device__ __forceinline__ int fast_score16(const int (&d)[16]) {
     return best - 1;
 }
 
+// Work is staged through shared-memory lists so that the expensive steps only run on pixels that need them, with all
+// lanes busy: (B) 4-point compass test on every pixel (a 9-arc always holds two adjacent compass points) -> candidate
+// list; (C) full 16-ring FAST-9 test on candidates -> corner list; (D) cornerScore on corners -> score map;
+// (E) 3x3 NMS on corners only -> warp-aggregated append to the (frame, level) corner list in HBM.
+#define FAST_TS 76                             // tile row stride: 64 + 6 halo + up to 3 bytes of word-alignment shift
+#define FAST_SS (FAST_MAX_CELL + 4)            // score row stride
+#define FAST_SCORE_BYTES (((FAST_MAX_CELL + 2) * FAST_SS + 15) / 16 * 16)
+
+__device__ __forceinline__ void list_append(bool pred, uint16_t val, uint16_t* list, int* count) {
+    const uint32_t ballot = __ballot_sync(0xffffffffu, pred);
+    if (!ballot) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(count, __popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (pred) list[base + __popc(ballot & ((1u << lane) - 1))] = val;
+}
+
 __global__ void __launch_bounds__(256) k_fast_cells(const __grid_constant__ LevelTable T,
                                                     uint32_t* __restrict__ corners,      // [frames][corners_per_frame]
                                                     int* __restrict__ corner_count) {    // [frames][CCM_MAX_LEVELS]
-    __shared__ uint8_t tile[FAST_TILE][FAST_TILE + 2];
-    __shared__ uint8_t score[FAST_MAX_CELL + 2][FAST_MAX_CELL + 4];   // 1-px zero ring around the cell
+    __shared__ __align__(16) uint8_t tile[FAST_TILE][FAST_TS];
+    __shared__ __align__(16) uint8_t score[FAST_SCORE_BYTES];   // [cell + 1-px zero ring][FAST_SS]
+    __shared__ uint16_t cand[FAST_MAX_CELL * FAST_MAX_CELL];
+    __shared__ uint16_t corn[FAST_MAX_CELL * FAST_MAX_CELL];
+    __shared__ int n_cand, n_corn;
 
     const int f = blockIdx.y;
     int lvl = 0;
@@ -102,48 +123,93 @@ __global__ void __launch_bounds__(256) k_fast_cells(const __grid_constant__ Leve
 
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int tid = threadIdx.x;
-    const int tw = cw + 6, th = ch + 6;
-    for (int i = tid; i < tw * th; i += 256) {
-        const int ty = i / tw, tx = i - ty * tw;
-        tile[ty][tx] = img[(size_t)(y0 - 3 + ty) * L.img_pitch + (x0 - 3 + tx)];
+    // (A) tile = cell + 3-px ring, loaded as aligned 32-bit words (rows are 32-B aligned, pitch a multiple of 32)
+    const int gx = x0 - 3, gxa = gx & ~3, shift = gx - gxa;
+    const int wpr = (shift + cw + 6 + 3) >> 2, th = ch + 6;           // words per tile row
+    const uint32_t wmagic = (0x100000u + wpr - 1) / wpr;              // i / wpr for i < 4096
+    for (int i = tid; i < wpr * th; i += 256) {
+        const int ty = (int)(((uint32_t)i * wmagic) >> 20), tx = i - ty * wpr;
+        const uint32_t v = *reinterpret_cast<const uint32_t*>(img + (size_t)(y0 - 3 + ty) * L.img_pitch + gxa + 4 * tx);
+        *reinterpret_cast<uint32_t*>(&tile[ty][4 * tx]) = v;
     }
-    for (int i = tid; i < (FAST_MAX_CELL + 2) * (FAST_MAX_CELL + 4); i += 256) (&score[0][0])[i] = 0;
+    for (int i = tid; i < FAST_SCORE_BYTES / 16; i += 256) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
+    if (tid == 0) { n_cand = 0; n_corn = 0; }
     __syncthreads();
 
+    const int npx = cw * ch;
+    const uint32_t cmagic = (0x100000u + cw - 1) / cw;                 // i / cw for i < 4096
+    const int S = FAST_TS;
     int threshold = T.ini_th;
 #pragma unroll 1
     for (int pass = 0; pass < 2; pass++) {
-        for (int i = tid; i < cw * ch; i += 256) {
-            const int py = i / cw, px = i - py * cw;
-            const uint8_t* c = &tile[py + 3][px + 3];
+        // (B) compass test
+        for (int base = 0; base < npx; base += 256) {
+            const int i = base + tid;
+            bool c4 = false;
+            if (i < npx) {
+                const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
+                const uint8_t* c = &tile[py + 3][px + 3 + shift];
+                const int v = c[0], hi = v + threshold, lo = v - threshold;
+                const int p0 = c[3 * S], p4 = c[3], p8 = c[-3 * S], p12 = c[-3];
+                const uint32_t b = (p0 > hi) | ((p4 > hi) << 1) | ((p8 > hi) << 2) | ((p12 > hi) << 3);
+                const uint32_t d = (p0 < lo) | ((p4 < lo) << 1) | ((p8 < lo) << 2) | ((p12 < lo) << 3);
+                c4 = ((b & ((b << 1) | (b >> 3))) | (d & ((d << 1) | (d >> 3)))) & 15u;
+            }
+            list_append(c4, (uint16_t)i, cand, &n_cand);
+        }
+        __syncthreads();
+        // (C) full FAST-9/16 segment test on the candidates
+        const int nc = n_cand;
+        for (int base = 0; base < nc; base += 256) {
+            const int j = base + tid;
+            bool is_corner = false;
+            int i = 0;
+            if (j < nc) {
+                i = cand[j];
+                const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
+                const uint8_t* c = &tile[py + 3][px + 3 + shift];
+                const int v = c[0], hi = v + threshold, lo = v - threshold;
+                int r[16];
+                r[0] = c[3 * S];       r[1] = c[3 * S + 1];   r[2] = c[2 * S + 2];   r[3] = c[S + 3];
+                r[4] = c[3];           r[5] = c[-S + 3];      r[6] = c[-2 * S + 2];  r[7] = c[-3 * S + 1];
+                r[8] = c[-3 * S];      r[9] = c[-3 * S - 1];  r[10] = c[-2 * S - 2]; r[11] = c[-S - 3];
+                r[12] = c[-3];         r[13] = c[S - 3];      r[14] = c[2 * S - 2];  r[15] = c[3 * S - 1];
+                uint32_t dark = 0, bright = 0;      // ring darker than v-t  /  brighter than v+t
+#pragma unroll
+                for (int k = 0; k < 16; k++) { dark |= (uint32_t)(r[k] < lo) << k; bright |= (uint32_t)(r[k] > hi) << k; }
+                is_corner = has_run9(dark) || has_run9(bright);
+            }
+            list_append(is_corner, (uint16_t)i, corn, &n_corn);
+        }
+        __syncthreads();
+        // (D) cornerScore of the corners -> score map
+        const int nk = n_corn;
+        for (int j = tid; j < nk; j += 256) {
+            const int i = corn[j];
+            const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
+            const uint8_t* c = &tile[py + 3][px + 3 + shift];
             const int v = c[0];
-            const int S = FAST_TILE + 2;
             int d[16];
             d[0] = v - c[3 * S];       d[1] = v - c[3 * S + 1];   d[2] = v - c[2 * S + 2];   d[3] = v - c[S + 3];
             d[4] = v - c[3];           d[5] = v - c[-S + 3];      d[6] = v - c[-2 * S + 2];  d[7] = v - c[-3 * S + 1];
             d[8] = v - c[-3 * S];      d[9] = v - c[-3 * S - 1];  d[10] = v - c[-2 * S - 2]; d[11] = v - c[-S - 3];
             d[12] = v - c[-3];         d[13] = v - c[S - 3];      d[14] = v - c[2 * S - 2];  d[15] = v - c[3 * S - 1];
-            uint32_t dark = 0, bright = 0;      // ring darker than v-t  /  brighter than v+t
-#pragma unroll
-            for (int k = 0; k < 16; k++) { dark |= (uint32_t)(d[k] > threshold) << k; bright |= (uint32_t)(d[k] < -threshold) << k; }
-            int s = 0;
-            if (has_run9(dark) || has_run9(bright)) s = fast_score16(d);
-            score[py + 1][px + 1] = (uint8_t)s;   // s >= threshold > 0 for corners (threshold >= 1 enforced at create)
+            score[(py + 1) * FAST_SS + px + 1] = (uint8_t)fast_score16(d);   // >= threshold > 0 (threshold >= 1 enforced at create)
         }
         __syncthreads();
+        // (E) non-maximum suppression over the corners, append survivors
         int found = 0;
-        for (int base = 0; base < cw * ch; base += 256) {     // uniform trip count: ballots below need whole warps
-            const int i = base + tid;
+        for (int base = 0; base < nk; base += 256) {     // uniform trip count: ballots below need whole warps
+            const int j = base + tid;
             bool keep = false;
             int px = 0, py = 0, s = 0;
-            if (i < cw * ch) {
-                py = i / cw; px = i - py * cw;
-                s = score[py + 1][px + 1];
-                if (s > 0) {
-                    keep = s > score[py][px] && s > score[py][px + 1] && s > score[py][px + 2] &&
-                           s > score[py + 1][px] && s > score[py + 1][px + 2] &&
-                           s > score[py + 2][px] && s > score[py + 2][px + 1] && s > score[py + 2][px + 2];
-                }
+            if (j < nk) {
+                const int i = corn[j];
+                py = (int)(((uint32_t)i * cmagic) >> 20); px = i - py * cw;
+                const uint8_t* sc = &score[(py + 1) * FAST_SS + px + 1];
+                s = sc[0];
+                keep = s > sc[-FAST_SS - 1] && s > sc[-FAST_SS] && s > sc[-FAST_SS + 1] && s > sc[-1] && s > sc[1] &&
+                       s > sc[FAST_SS - 1] && s > sc[FAST_SS] && s > sc[FAST_SS + 1];
             }
             const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
             if (ballot) {
@@ -162,5 +228,7 @@ __global__ void __launch_bounds__(256) k_fast_cells(const __grid_constant__ Leve
         }
         if (__syncthreads_or(found) || threshold == T.min_th) break;
         threshold = T.min_th;     // cell empty at iniThFAST -> rerun at minThFAST (:981-985)
+        if (tid == 0) { n_cand = 0; n_corn = 0; }
+        __syncthreads();
     }
 }

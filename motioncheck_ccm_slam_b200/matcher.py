@@ -265,3 +265,23 @@ class ORBmatcher:
     def SearchByBoW_KF_KF(self, desc1, node1, valid1, angle1, desc2, node2, valid2, angle2):
         nm, ma, _, res = self._search_bow(BOW_KF_KF, desc1, node1, valid1, angle1, desc2, node2, valid2, angle2)
         return nm, ma, res
+
+
+# ---- device-resident batch path (extractor output -> packs -> searches, no host round trip) ----------------------
+def packs_from_extractor_batch_device(packs, grid, d_kp, d_desc, d_n, kp_stride, d_xy_un=None):
+    """packs[j] takes frame j of ORBextractor.extract_batch_device's output (raw device pointers); asynchronous."""
+    m = packs[0].m
+    arr = (ctypes.c_void_p * len(packs))(*[p._h.value for p in packs])
+    for p in packs:
+        p.grid = grid
+    m._check(m._lib.ccm_frame_pack_from_extractor_batch_device(arr, len(packs), ctypes.byref(grid), d_kp, d_desc, d_n,
+                                                               int(kp_stride), d_xy_un))
+
+
+def search_window_batch_device(matcher, packs, mode, nnratio, th_dist, check_orientation, d_nq, q_stride, d_q, d_q_desc,
+                               d_holder, holder_stride, d_res, d_nmatches):
+    """ccm_search_window_batch_device: job j searches packs[j] with the q_stride-strided query block j; asynchronous."""
+    arr = (ctypes.c_void_p * len(packs))(*[p._h.value for p in packs])
+    prm = WindowParams(mode, float(nnratio), int(th_dist), 1 if check_orientation else 0, None, 0)
+    matcher._check(matcher._lib.ccm_search_window_batch_device(matcher._h, arr, len(packs), ctypes.byref(prm), d_nq, int(q_stride),
+                                                               d_q, d_q_desc, d_holder, int(holder_stride), d_res, d_nmatches))

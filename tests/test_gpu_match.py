@@ -263,3 +263,66 @@ def test_allpairs_sharded_merge_equals_single(gm):
     ref = OracleMatcher(0.75).allpairs_best2(q, t)
     assert np.array_equal(acc.cpu().numpy().astype(np.int32), ref["accepted"])
     assert merged["idx"][7] == 100 and merged["d2"][7] == 0
+
+
+def test_extractor_to_matcher_zero_copy_batch(gm):
+    """Extractor output stays in HBM: packs are built from it on the device, frame t is searched with frame t-1's
+    keypoints as queries (SearchByProjection(Frame, LastFrame)), all frames of the batch in one launch. Checked against
+    the oracle fed with the host copies of the same extractor output."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200 import ORBextractor
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    from motioncheck_ccm_slam_b200.matcher import (FramePack, QUERY_DTYPE, RESULT_DTYPE, WIN_PROJ_LASTFRAME, Q_VALID, Q_OBS,
+                                                   frame_grid, packs_from_extractor_batch_device, search_window_batch_device)
+    from motioncheck_ccm_slam_b200.synth import make_stream
+    B, w, h = 4, 640, 400
+    frames = make_stream(4242, B, w, h)
+    ex = ORBextractor(800, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B, device=0)
+    cap = ex.max_keypoints()
+    dev = torch.device("cuda", 0)
+    d_img = torch.from_numpy(frames).to(dev)
+    d_kp = torch.zeros((B, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros((B,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    ex.extract_batch_device(d_img.data_ptr(), B, h, w, w, w * h, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+    ex.sync()
+    kp = d_kp.cpu().numpy().view(KP_DTYPE).reshape(B, cap)
+    desc = d_desc.cpu().numpy()
+    n = d_n.cpu().numpy()
+    assert n.min() > 500
+    grid = frame_grid(w, h)
+    packs = [FramePack(gm, cap) for _ in range(B)]
+    packs_from_extractor_batch_device(packs, grid, d_kp.data_ptr(), d_desc.data_ptr(), d_n.data_ptr(), cap)
+    sf = ex.GetScaleFactors()
+    # queries for job j (pack j+1): frame j's keypoints moved by the stream's motion (-2, -1)
+    q = np.zeros((B - 1, cap), QUERY_DTYPE)
+    for j in range(B - 1):
+        k = kp[j, :n[j]]
+        q["u"][j, :n[j]] = k["x"] - 2; q["v"][j, :n[j]] = k["y"] - 1; q["angle"][j, :n[j]] = k["angle"]
+        q["r"][j, :n[j]] = np.float32(7.0) * sf[k["octave"]]
+        q["min_level"][j, :n[j]] = k["octave"] - 1; q["max_level"][j, :n[j]] = k["octave"] + 1
+        q["flags"][j, :n[j]] = Q_VALID | Q_OBS
+    d_q = torch.from_numpy(q.view(np.uint8).reshape(B - 1, cap, 24)).to(dev)
+    d_holder = torch.full((B - 1, cap), -1, dtype=torch.int32, device=dev)
+    d_res = torch.zeros((B - 1, cap, 4), dtype=torch.int32, device=dev)
+    d_nm = torch.zeros((B - 1,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    search_window_batch_device(gm, packs[1:], WIN_PROJ_LASTFRAME, 0.9, 100, True, d_n.data_ptr(), cap, d_q.data_ptr(),
+                               d_desc.data_ptr(), d_holder.data_ptr(), cap, d_res.data_ptr(), d_nm.data_ptr())
+    gm.sync()
+    holder, res, nm = d_holder.cpu().numpy(), d_res.cpu().numpy().view(RESULT_DTYPE).reshape(B - 1, cap), d_nm.cpu().numpy()
+    for j in range(B - 1):
+        t = kp[j + 1, :n[j + 1]]
+        of = OracleFrame(desc[j + 1, :n[j + 1]], t["x"], t["y"], t["octave"], t["angle"], grid)
+        cs, items = packs[j + 1].get_grid()
+        ocs, oitems = of.csr()
+        assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
+        k = kp[j, :n[j]]
+        hc = np.full(n[j + 1], -1, np.int32)
+        nm_c, res_c = OracleMatcher(0.9, True).projection_lastframe(of, np.ones(n[j]), k["x"] - 2, k["y"] - 1, k["octave"], k["angle"],
+                                                                    desc[j, :n[j]], np.ones(n[j]), 7.0, sf, hc)
+        _same_res(res[j, :n[j]], res_c)
+        assert nm[j] == nm_c and np.array_equal(holder[j, :n[j + 1]], hc)
+        assert nm_c > 300, nm_c        # consecutive frames of the stream really match
+    ex.close()
