@@ -28,6 +28,7 @@ struct ccm_orb {
     int max_kps = 0;          // == T.kps_per_frame
     // device arena
     std::vector<void*> allocs;
+    uint4* d_cell_info = nullptr;
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
     ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
@@ -103,6 +104,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     const int L = h->cfg.nlevels, B = h->cfg.max_batch;
     T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
     int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0;
+    std::vector<uint4> cell_info;
     for (int l = 0; l < L; l++) {
         LevelDesc& D = T.l[l];
         D.w = (int)lrintf((float)cols * h->isf[l]);
@@ -127,6 +129,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
                 const int x0 = CCM_EDGE + j * D.wCell, y0 = CCM_EDGE + i * D.hCell;
                 const int cw = std::min(x0 + D.wCell, D.w - CCM_EDGE) - x0, ch = std::min(y0 + D.hCell, D.h - CCM_EDGE) - y0;
                 if (cw > 0 && ch > 0) cc += ((cw + 1) / 2) * ((ch + 1) / 2);
+                cell_info.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l, 0u));
             }
         D.corner_cap = std::max(cc, 1); D.corner_off = corners; corners += align_up(D.corner_cap, 4);
         if (D.corner_cap > 0x7FFFF) { h->err = "image too large (corner capacity per level exceeds 2^19)"; return CCM_E_BADARG; }
@@ -166,6 +169,8 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         }
     }
     int rc;
+    if ((rc = dev_alloc(h, &h->d_cell_info, cell_info.size()))) return rc;
+    CK(cudaMemcpy(h->d_cell_info, cell_info.data(), cell_info.size() * sizeof(uint4), cudaMemcpyHostToDevice));
     if ((rc = dev_alloc(h, &h->d_corners, (size_t)corners * B))) return rc;
     if ((rc = dev_alloc(h, &h->d_node_of, (size_t)corners * B))) return rc;
     if ((rc = dev_alloc(h, &h->d_corner_count, (size_t)CCM_MAX_LEVELS * B))) return rc;
@@ -214,7 +219,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         h->launches++;
     }
     if (st) CK(cudaEventRecord(h->ev[1], s));
-    k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_corners, h->d_corner_count);
+    k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_cell_info, h->d_corners, h->d_corner_count);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[2], s));
     k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);

@@ -15,32 +15,34 @@
 #define BLUR_RPW 16                      // output rows per warp
 #define BLUR_TH (8 * BLUR_RPW)           // rows per CTA (8 warps)
 
-__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, int x, int x0, int w, int lane, uint32_t (&hs)[4]) {
-    const bool in = x < w;
-    uint32_t own = 0;
-    if (in) own = *reinterpret_cast<const uint32_t*>(row + x);
+// own word of this lane for one source row (0 beyond the row); issued one row ahead of its use
+__device__ __forceinline__ uint32_t blur_load(const uint8_t* __restrict__ row, int x, int w) {
+    return x < w ? *reinterpret_cast<const uint32_t*>(row + x) : 0u;
+}
+
+// four horizontal 7-tap sums of pixels x..x+3 from the words holding pixels x-4..x+7: eight unaligned 4-byte windows
+// (PRMT) and eight IDP4A with the packed 8.8 coefficients {18,34,48,56 | 48,34,18,0}
+__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint32_t own, int x, int x0, int w, int lane, uint32_t (&hs)[4]) {
     uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
     uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
     if (lane == 0 && x0 > 0) prev = *reinterpret_cast<const uint32_t*>(row + x - 4);
     if (lane == 31 && x + 4 < w) next = *reinterpret_cast<const uint32_t*>(row + x + 4);
-    int b[10];
-    if (x - 3 >= 0 && x + 6 < w) {
-        b[0] = (prev >> 8) & 255; b[1] = (prev >> 16) & 255; b[2] = prev >> 24;
-        b[3] = own & 255; b[4] = (own >> 8) & 255; b[5] = (own >> 16) & 255; b[6] = own >> 24;
-        b[7] = next & 255; b[8] = (next >> 8) & 255; b[9] = (next >> 16) & 255;
-    } else if (in) {
+    if ((x - 3 < 0 || x + 6 >= w) && x < w) {          // lanes touching the reflected border: gather bytes x-4..x+7
+        uint32_t wd[3] = {0u, 0u, 0u};
 #pragma unroll
-        for (int k = 0; k < 10; k++) b[k] = row[ccm_reflect101(min(x - 3 + k, w + 2), w)];
-    } else {
-#pragma unroll
-        for (int k = 0; k < 10; k++) b[k] = 0;
+        for (int k = 0; k < 12; k++) wd[k >> 2] |= (uint32_t)row[ccm_reflect101(min(x - 4 + k, w + 2), w)] << (8 * (k & 3));
+        prev = wd[0]; own = wd[1]; next = wd[2];
     }
-#pragma unroll
-    for (int k = 0; k < 4; k++)
-        hs[k] = 18 * (b[k] + b[k + 6]) + 34 * (b[k + 1] + b[k + 5]) + 48 * (b[k + 2] + b[k + 4]) + 56 * b[k + 3];   // <= 65280
+    const uint32_t C1 = 18u | (34u << 8) | (48u << 16) | (56u << 24), C2 = 48u | (34u << 8) | (18u << 16);
+    const uint32_t wm3 = __byte_perm(prev, own, 0x4321), wm2 = __byte_perm(prev, own, 0x5432), wm1 = __byte_perm(prev, own, 0x6543);
+    const uint32_t wp1 = __byte_perm(own, next, 0x4321), wp2 = __byte_perm(own, next, 0x5432), wp3 = __byte_perm(own, next, 0x6543);
+    hs[0] = __dp4a(wm3, C1, __dp4a(wp1, C2, 0u));     // <= 65280
+    hs[1] = __dp4a(wm2, C1, __dp4a(wp2, C2, 0u));
+    hs[2] = __dp4a(wm1, C1, __dp4a(wp3, C2, 0u));
+    hs[3] = __dp4a(own, C1, __dp4a(next, C2, 0u));
 }
 
-__global__ void __launch_bounds__(256) k_blur_levels(const __grid_constant__ LevelTable T) {
+__global__ void __launch_bounds__(256, 4) k_blur_levels(const __grid_constant__ LevelTable T) {
     int lvl = 0;
 #pragma unroll 1
     while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].blur_tile_base) lvl++;
@@ -56,11 +58,15 @@ __global__ void __launch_bounds__(256) k_blur_levels(const __grid_constant__ Lev
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     uint8_t* __restrict__ out = L.blur + (size_t)f * L.blur_stride;
     uint32_t ring[7][4];
+    // source row of window row r is wy0 + r - 3 (rows past the bottom only feed outputs that are never stored)
+    const uint8_t* row = img + (size_t)ccm_reflect101(min(wy0 - 3, h + 2), h) * L.img_pitch;
+    uint32_t own = blur_load(row, x, w);
 #pragma unroll
     for (int r = 0; r < BLUR_RPW + 6; r++) {
-        // source row wy0 + r - 3 (rows past the bottom only feed outputs that are never stored)
-        const int gy = ccm_reflect101(min(wy0 + r - 3, h + 2), h);
-        blur_hrow(img + (size_t)gy * L.img_pitch, x, x0, w, lane, ring[r % 7]);
+        const uint8_t* row_n = img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * L.img_pitch;
+        const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
+        blur_hrow(row, own, x, x0, w, lane, ring[r % 7]);
+        row = row_n; own = own_n;
         if (r >= 6) {
             const int oy = wy0 + r - 6;
             uint32_t packed = 0;

@@ -99,7 +99,8 @@ __device__ __forceinline__ void list_append(bool pred, uint16_t val, uint16_t* l
     if (pred) list[base + __popc(ballot & ((1u << lane) - 1))] = val;
 }
 
-__global__ void __launch_bounds__(256) k_fast_cells(const __grid_constant__ LevelTable T,
+__global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ LevelTable T,
+                                                    const uint4* __restrict__ cell_info,  // per cell: x0|y0<<16, cw|ch<<16, level, 0
                                                     uint32_t* __restrict__ corners,      // [frames][corners_per_frame]
                                                     int* __restrict__ corner_count) {    // [frames][CCM_MAX_LEVELS]
     __shared__ __align__(16) uint8_t tile[FAST_TILE][FAST_TS];
@@ -109,17 +110,11 @@ __global__ void __launch_bounds__(256) k_fast_cells(const __grid_constant__ Leve
     __shared__ int n_cand, n_corn;
 
     const int f = blockIdx.y;
-    int lvl = 0;
-#pragma unroll 1
-    while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].cell_base) lvl++;
-    const LevelDesc& L = T.l[lvl];
-    const int cell = blockIdx.x - L.cell_base;
-    const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
-    // detection block of this cell in level coordinates
-    const int x0 = CCM_EDGE + cj * L.wCell, y0 = CCM_EDGE + ci * L.hCell;
-    const int x1 = min(x0 + L.wCell, L.w - CCM_EDGE), y1 = min(y0 + L.hCell, L.h - CCM_EDGE);
-    const int cw = x1 - x0, ch = y1 - y0;
+    // detection block of this cell in level coordinates (host-built table: configure_shape, orb_api.cu)
+    const uint4 ci = __ldg(cell_info + blockIdx.x);
+    const int x0 = (int)(ci.x & 0xffff), y0 = (int)(ci.x >> 16), cw = (int)(ci.y & 0xffff), ch = (int)(ci.y >> 16), lvl = (int)ci.z;
     if (cw <= 0 || ch <= 0) return;          // clipped-away cell (the :962/:971 `continue`s)
+    const LevelDesc& L = T.l[lvl];
 
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int tid = threadIdx.x;
@@ -139,23 +134,49 @@ __global__ void __launch_bounds__(256) k_fast_cells(const __grid_constant__ Leve
     const int npx = cw * ch;
     const uint32_t cmagic = (0x100000u + cw - 1) / cw;                 // i / cw for i < 4096
     const int S = FAST_TS;
+    const int g0 = (3 + shift) >> 2, ngx = ((cw + 2 + shift) >> 2) - g0 + 1, ngrp = ngx * ch;   // aligned 4-px words covering the cell
+    const uint32_t gmagic = (0x100000u + ngx - 1) / ngx;              // i / ngx for i < 4096
     int threshold = T.ini_th;
 #pragma unroll 1
     for (int pass = 0; pass < 2; pass++) {
-        // (B) compass test
-        for (int base = 0; base < npx; base += 256) {
-            const int i = base + tid;
-            bool c4 = false;
-            if (i < npx) {
-                const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-                const uint8_t* c = &tile[py + 3][px + 3 + shift];
-                const int v = c[0], hi = v + threshold, lo = v - threshold;
-                const int p0 = c[3 * S], p4 = c[3], p8 = c[-3 * S], p12 = c[-3];
-                const uint32_t b = (p0 > hi) | ((p4 > hi) << 1) | ((p8 > hi) << 2) | ((p12 > hi) << 3);
-                const uint32_t d = (p0 < lo) | ((p4 < lo) << 1) | ((p8 < lo) << 2) | ((p12 < lo) << 3);
-                c4 = ((b & ((b << 1) | (b >> 3))) | (d & ((d << 1) | (d >> 3)))) & 15u;
+        // (B) opposite-pair test on 4 pixels per thread (a 9-arc of the ring contains one pixel of every diametral pair,
+        //     so |v-p0|<=t && |v-p8|<=t, or the same for p4/p12, rules a pixel out): aligned 32-bit tile words, byte SIMD
+        const uint32_t t4 = (uint32_t)threshold * 0x01010101u;
+        for (int base = 0; base < ngrp; base += 256) {
+            const int gi = base + tid;
+            uint32_t nib = 0;
+            int py = 0, pxb = 0;
+            if (gi < ngrp) {
+                py = (int)(((uint32_t)gi * gmagic) >> 20);
+                const int g = g0 + gi - py * ngx;
+                pxb = 4 * g - 3 - shift;                                      // pixel of byte 0 of this word
+                const uint32_t* rowc = reinterpret_cast<const uint32_t*>(&tile[py + 3][0]) + g;
+                const uint32_t cen = rowc[0], lft = rowc[-1], rgt = rowc[1];
+                const uint32_t up = rowc[-3 * (FAST_TS / 4)], dn = rowc[3 * (FAST_TS / 4)];
+                const uint32_t p4 = __funnelshift_r(cen, rgt, 24), p12 = __funnelshift_r(lft, cen, 8);
+                const uint32_t m = (__vcmpgtu4(__vabsdiffu4(cen, dn), t4) | __vcmpgtu4(__vabsdiffu4(cen, up), t4)) &
+                                   (__vcmpgtu4(__vabsdiffu4(cen, p4), t4) | __vcmpgtu4(__vabsdiffu4(cen, p12), t4));
+                nib = (((m & 0x01010101u) * 0x01020408u) >> 24) & 15u;
+                // keep the bytes that are pixels of this cell: 0 <= pxb + k < cw
+                const uint32_t lo_ok = pxb >= 0 ? 15u : (15u << (-pxb)) & 15u;
+                const uint32_t hi_ok = pxb + 3 < cw ? 15u : 15u >> (pxb + 4 - cw);
+                nib &= lo_ok & hi_ok;
             }
-            list_append(c4, (uint16_t)i, cand, &n_cand);
+            const uint32_t b0 = __ballot_sync(0xffffffffu, nib & 1u), b1 = __ballot_sync(0xffffffffu, nib & 2u);
+            const uint32_t b2 = __ballot_sync(0xffffffffu, nib & 4u), b3 = __ballot_sync(0xffffffffu, nib & 8u);
+            if (b0 | b1 | b2 | b3) {
+                const int lane = tid & 31;
+                const uint32_t lt = (1u << lane) - 1;
+                const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
+                int slot = 0;
+                if (lane == 0) slot = atomicAdd(&n_cand, c0 + c1 + c2 + c3);
+                slot = __shfl_sync(0xffffffffu, slot, 0);
+                const int pi = py * cw + pxb;
+                if (nib & 1u) cand[slot + __popc(b0 & lt)] = (uint16_t)pi;
+                if (nib & 2u) cand[slot + c0 + __popc(b1 & lt)] = (uint16_t)(pi + 1);
+                if (nib & 4u) cand[slot + c0 + c1 + __popc(b2 & lt)] = (uint16_t)(pi + 2);
+                if (nib & 8u) cand[slot + c0 + c1 + c2 + __popc(b3 & lt)] = (uint16_t)(pi + 3);
+            }
         }
         __syncthreads();
         // (C) full FAST-9/16 segment test on the candidates
