@@ -13,6 +13,7 @@
 // kernels: this file is compiled as part of the single translation unit ccm_orb_cuda.cu, after
 // orb_pyramid_fast.cu, orb_quadtree.cu and orb_describe.cu.
 
+#define CCM_MAX_CHUNKS 8
 static thread_local std::string g_create_error = "";
 
 struct ccm_orb {
@@ -35,6 +36,9 @@ struct ccm_orb {
     // pinned staging
     ccm_keypoint* h_kp = nullptr; uint8_t* h_desc = nullptr; int* h_n = nullptr;
     cudaStream_t stream = nullptr;
+    // host entry point: copy-in / compute / copy-out overlap over sub-batches ("chunks") of one call
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[CCM_MAX_CHUNKS] = {}, ev_done[CCM_MAX_CHUNKS] = {}, ev_out[CCM_MAX_CHUNKS] = {};
     long long launches = 0;
     // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
     bool stage_timing = false;
@@ -201,17 +205,29 @@ static int collect_stage_times(ccm_orb* h) {
 }
 
 // One batch through K1..K7 on the handle's stream. Level 0 is read in place from (l0, pitch, stride).
+// Frames [f0, f0+n) of the arena: every per-frame array is addressed through pointers advanced by f0 frames, so a call
+// can be cut into sub-batches that overlap with their own copies (ccm_orb_extract_batch).
 static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, size_t l0_stride,
-                        ccm_keypoint* d_kp, uint8_t* d_desc, int* d_n, int capacity) {
-    LevelTable& T = h->T;
-    T.l[0].img = const_cast<uint8_t*>(l0);
-    T.l[0].img_pitch = (int)l0_pitch;
-    T.l[0].img_stride = l0_stride;
-    h->last_frames = n; h->last_l0 = l0; h->last_l0_pitch = l0_pitch; h->last_l0_stride = l0_stride;
+                        ccm_keypoint* d_kp, uint8_t* d_desc, int* d_n, int capacity, int f0 = 0, bool allow_timing = true) {
+    h->T.l[0].img = const_cast<uint8_t*>(l0);
+    h->T.l[0].img_pitch = (int)l0_pitch;
+    h->T.l[0].img_stride = l0_stride;
+    if (f0 == 0) { h->last_l0 = l0; h->last_l0_pitch = l0_pitch; h->last_l0_stride = l0_stride; }
+    h->last_frames = f0 + n;
+    LevelTable T = h->T;
+    for (int l = 0; l < T.nlevels; l++) {
+        T.l[l].img += (size_t)f0 * T.l[l].img_stride;
+        T.l[l].blur += (size_t)f0 * T.l[l].blur_stride;
+    }
+    struct Off {
+        uint32_t* corners; int* corner_count; uint16_t* node_of; uint32_t* level_kps; int* level_kp_count;
+    } A = {h->d_corners + (size_t)f0 * T.corners_per_frame, h->d_corner_count + (size_t)f0 * CCM_MAX_LEVELS,
+           h->d_node_of + (size_t)f0 * T.corners_per_frame, h->d_level_kps + (size_t)f0 * T.kps_per_frame,
+           h->d_level_kp_count + (size_t)f0 * CCM_MAX_LEVELS};
     cudaStream_t s = h->stream;
-    if (h->stage_timing) { int rc = collect_stage_times(h); if (rc != CCM_OK) return rc; }
-    const bool st = h->stage_timing;
-    CK(cudaMemsetAsync(h->d_corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
+    const bool st = h->stage_timing && allow_timing;
+    if (st) { int rc = collect_stage_times(h); if (rc != CCM_OK) return rc; }
+    CK(cudaMemsetAsync(A.corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
     if (st) CK(cudaEventRecord(h->ev[0], s));
     for (int l = 1; l < T.nlevels; l++) {
         dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
@@ -219,17 +235,17 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         h->launches++;
     }
     if (st) CK(cudaEventRecord(h->ev[1], s));
-    k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_cell_info, h->d_corners, h->d_corner_count);
+    k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_cell_info, A.corners, A.corner_count);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[2], s));
     k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[3], s));
-    k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, h->d_corners, h->d_corner_count, h->d_node_of,
-                                                          h->d_level_kps, h->d_level_kp_count);
+    k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, A.corners, A.corner_count, A.node_of,
+                                                          A.level_kps, A.level_kp_count);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[4], s));
-    k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, h->d_level_kps, h->d_level_kp_count,
+    k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, A.level_kps, A.level_kp_count,
                                                                         (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
     h->launches++;
     if (st) { CK(cudaEventRecord(h->ev[5], s)); h->stage_pending = true; }
@@ -274,6 +290,12 @@ int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
     auto fail = [&](int rc) { g_create_error = h->err; free_arena(h); if (h->stream) cudaStreamDestroy(h->stream); delete h; return rc; };
     if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+    if ((e = cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+    for (int i = 0; i < CCM_MAX_CHUNKS; i++)
+        if ((e = cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)) != cudaSuccess ||
+            (e = cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming)) != cudaSuccess ||
+            (e = cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     int rc = configure_shape(h, cfg->max_height, cfg->max_width);
     if (rc != CCM_OK) return fail(rc);
     *out = h;
@@ -286,6 +308,13 @@ void ccm_orb_destroy(ccm_orb* h) {
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_arena(h);
     for (int i = 0; i <= CCM_N_STAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+    for (int i = 0; i < CCM_MAX_CHUNKS; i++) {
+        if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
+        if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
+        if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
+    }
+    if (h->s_in) cudaStreamDestroy(h->s_in);
+    if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -355,31 +384,53 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     CK(cudaSetDevice(h->cfg.device));
     int rc = configure_shape(h, rows, cols);
     if (rc != CCM_OK) return rc;
-    // level 0 lives in the handle's own (pitched) level-0 buffer
-    LevelDesc& L0 = h->T.l[0];
+    // Level 0 lives in the handle's own level-0 buffer. When the caller's rows are 4-byte multiples that fit the
+    // buffer's row budget the device pitch equals the host step and a frame is ONE contiguous copy; otherwise a
+    // pitched 2-D copy. The call is cut into up to CCM_MAX_CHUNKS sub-batches: copy-in (s_in), kernels (stream) and
+    // copy-out (s_out) of different sub-batches overlap, and the host-side scatter into the caller's arrays runs
+    // while later sub-batches are still on the device.
     uint8_t* l0 = (uint8_t*)h->allocs[0];
-    const size_t pitch = (size_t)align_up(cols, 32), stride = pitch * rows;
-    for (int f = 0; f < n; f++) {
-        if (!imgs[f]) { h->err = "null image in batch"; return CCM_E_BADARG; }
-        CK(cudaMemcpy2DAsync(l0 + f * stride, pitch, imgs[f], step, cols, rows, cudaMemcpyHostToDevice, h->stream));
-    }
-    (void)L0;
+    const size_t budget = (size_t)align_up(cols, 32);
+    const bool flat = (step % 4 == 0) && step <= budget;
+    const size_t pitch = flat ? step : budget, stride = budget * rows;
     const int cap = h->max_kps;
-    rc = run_pipeline(h, n, l0, pitch, stride, h->d_kp, h->d_desc, h->d_n, cap);
-    if (rc != CCM_OK) return rc;
-    CK(cudaMemcpyAsync(h->h_n, h->d_n, sizeof(int) * n, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(h->h_kp, h->d_kp, sizeof(ccm_keypoint) * (size_t)cap * n, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * cap * n, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
-    for (int f = 0; f < n; f++) {
-        const int cnt = h->h_n[f];
-        out_n[f] = cnt;
-        const int m = std::min(std::min(cnt, capacity), cap);
-        if (m > 0) {
-            std::memcpy(out_kp + (size_t)f * capacity, h->h_kp + (size_t)f * cap, sizeof(ccm_keypoint) * m);
-            std::memcpy(out_desc + (size_t)f * capacity * 32, h->h_desc + (size_t)f * cap * 32, (size_t)32 * m);
+    int n_chunks = n <= 8 ? 1 : std::min(CCM_MAX_CHUNKS, std::min(4, n / 4));
+    const int per = (n + n_chunks - 1) / n_chunks;
+    n_chunks = (n + per - 1) / per;
+    for (int f = 0; f < n; f++)
+        if (!imgs[f]) { h->err = "null image in batch"; return CCM_E_BADARG; }
+    for (int c = 0; c < n_chunks; c++) {
+        const int f0 = c * per, m = std::min(per, n - f0);
+        for (int f = f0; f < f0 + m; f++) {
+            if (flat) CK(cudaMemcpyAsync(l0 + f * stride, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
+            else CK(cudaMemcpy2DAsync(l0 + f * stride, pitch, imgs[f], step, cols, rows, cudaMemcpyHostToDevice, h->s_in));
+        }
+        CK(cudaEventRecord(h->ev_in[c], h->s_in));
+        CK(cudaStreamWaitEvent(h->stream, h->ev_in[c], 0));
+        rc = run_pipeline(h, m, l0, pitch, stride, h->d_kp + (size_t)f0 * cap, h->d_desc + (size_t)f0 * cap * 32, h->d_n + f0, cap, f0, n_chunks == 1);
+        if (rc != CCM_OK) return rc;
+        CK(cudaEventRecord(h->ev_done[c], h->stream));
+        CK(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
+        CK(cudaMemcpyAsync(h->h_n + f0, h->d_n + f0, sizeof(int) * m, cudaMemcpyDeviceToHost, h->s_out));
+        CK(cudaMemcpyAsync(h->h_kp + (size_t)f0 * cap, h->d_kp + (size_t)f0 * cap, sizeof(ccm_keypoint) * (size_t)cap * m, cudaMemcpyDeviceToHost, h->s_out));
+        CK(cudaMemcpyAsync(h->h_desc + (size_t)f0 * cap * 32, h->d_desc + (size_t)f0 * cap * 32, (size_t)32 * cap * m, cudaMemcpyDeviceToHost, h->s_out));
+        CK(cudaEventRecord(h->ev_out[c], h->s_out));
+    }
+    for (int c = 0; c < n_chunks; c++) {
+        const int f0 = c * per, m = std::min(per, n - f0);
+        CK(cudaEventSynchronize(h->ev_out[c]));
+        for (int f = f0; f < f0 + m; f++) {
+            const int cnt = h->h_n[f];
+            out_n[f] = cnt;
+            const int k = std::min(std::min(cnt, capacity), cap);
+            if (k > 0) {
+                std::memcpy(out_kp + (size_t)f * capacity, h->h_kp + (size_t)f * cap, sizeof(ccm_keypoint) * k);
+                std::memcpy(out_desc + (size_t)f * capacity * 32, h->h_desc + (size_t)f * cap * 32, (size_t)32 * k);
+            }
         }
     }
+    // the next call's copy-in must not overtake this call's kernels (they read the level-0 buffer)
+    CK(cudaStreamSynchronize(h->stream));
     return CCM_OK;
 }
 

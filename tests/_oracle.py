@@ -95,11 +95,16 @@ def ref_available(mono=True):
     return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_orb_mono.so" if mono else "libref_orb.so"))
 
 
+def dropin_available():
+    """oracle/_ref/libdropin_orb.so: the product's drop-in cslam::ORBextractor class behind the reference glue."""
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libdropin_orb.so"))
+
+
 class RefExtractor:
     """The reference's own ORBextractor.cpp (compiled unmodified, oracle/_ref). mono=True: monotone operator new."""
 
-    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, mono=True):
-        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", "libref_orb_mono.so" if mono else "libref_orb.so"))
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, mono=True, lib=None):
+        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", lib or ("libref_orb_mono.so" if mono else "libref_orb.so")))
         L.ref_orb_create.restype = _vp
         L.ref_orb_create.argtypes = [_i, _c.c_float, _i, _i, _i]
         L.ref_orb_destroy.argtypes = [_vp]

@@ -180,3 +180,34 @@ def test_device_resident_path_matches_host_path(cuda_lib):
         kp = d_kp[f, :n[f]].cpu().numpy().view(np.uint8).reshape(-1).view(KP_DTYPE)
         assert np.array_equal(kp, kh[f])
         assert np.array_equal(d_desc[f, :n[f]].cpu().numpy(), dh[f])
+
+
+def test_dropin_cpp_class_matches_reference_class(cuda_lib):
+    """The drop-in C++ class (motioncheck_ccm_slam_b200/host/ORBextractor.cpp, compiled against the reference's own
+    <cslam/ORBextractor.h>) and the reference's ORBextractor.cpp, both driven through the same glue
+    (cslam::ORBextractor::operator() on a cv::Mat): identical keypoints, descriptors within tolerance, identical
+    mvImagePyramid levels. Built only where /root/reference exists; the prebuilt .so travels to the GPU box."""
+    import _oracle
+    if not (_oracle.dropin_available() and _oracle.ref_available(mono=True)):
+        pytest.skip("oracle/_ref/libdropin_orb.so not built (needs the reference header at build time)")
+    os.environ["CCM_ORB_FILL_PYRAMID"] = "1"
+    from motioncheck_ccm_slam_b200.synth import make_frame
+    args = (1000, 1.2, 8, 20, 7)
+    drop = _oracle.RefExtractor(*args, lib="libdropin_orb.so")
+    ref = _oracle.RefExtractor(*args, mono=True)
+    for seed, (w, h) in [(101, (752, 480)), (102, (640, 400)), (103, (752, 480))]:
+        img = make_frame(seed, w, h)
+        kd, dd = drop(img)
+        kr, dr = ref(img)
+        assert len(kd) == len(kr) > 900
+        for name in ("x", "y", "size", "angle", "response", "octave"):
+            assert np.array_equal(kd[name], kr[name]), name
+        assert 1.0 - np.unpackbits(dd ^ dr, axis=1).mean() >= 0.999
+        for lvl in (0, 3, 7):
+            assert np.array_equal(drop.pyramid_level(lvl), ref.pyramid_level(lvl))
+    # strided ROI input (cv::Mat with step > cols), as Frame.cpp may hand over
+    big = make_frame(104, 800, 500)
+    roi = big[10:490, 20:772]
+    kd, dd = drop(np.ascontiguousarray(roi))
+    kr, dr = ref(np.ascontiguousarray(roi))
+    assert len(kd) == len(kr) and np.array_equal(kd["x"], kr["x"]) and np.array_equal(kd["angle"], kr["angle"])
