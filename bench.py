@@ -189,7 +189,8 @@ def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d
 
     # ---- (1) all-pairs best-2 over the keyframe database, target shard per rank ----
     nq, nt_total = 1000, args.db
-    lo, hi = nt_total * rank // world, nt_total * (rank + 1) // world
+    from motioncheck_ccm_slam_b200.sharding import shard_range
+    lo, hi = shard_range(nt_total, rank, world)                    # database sharded across ranks
     g = torch.Generator(device=dev); g.manual_seed(7)
     d_q = torch.randint(0, 256, (nq, 32), dtype=torch.uint8, device=dev, generator=g)     # same queries on every rank
     g.manual_seed(100 + rank)
