@@ -125,6 +125,12 @@ void* mo_frame_create(int n, const uint8_t* desc, const float* x, const float* y
 }
 void mo_frame_destroy(void* f) { delete (MoFrame*)f; }
 
+/* read-only view of a frame's arrays (used by oracle/ref_match_glue.cpp to build the mock Frame / KeyFrame) */
+void mo_frame_view(const void* fp, int* n, const uint8_t** desc, const float** x, const float** y, const int** octave, const float** angle) {
+    const MoFrame* f = (const MoFrame*)fp;
+    *n = f->n; *desc = f->desc.data(); *x = f->x.data(); *y = f->y.data(); *octave = f->octave.data(); *angle = f->angle.data();
+}
+
 /* the grid as CSR over cells in (ix * rows + iy) order: cell_start[cols*rows+1], items[<= n]; returns #items */
 int mo_frame_grid(const void* fp, int* cell_start, int* items) {
     const MoFrame* f = (const MoFrame*)fp;

@@ -1,0 +1,233 @@
+/* TEST INFRASTRUCTURE — C wrapper around the reference's OWN cslam::ORBmatcher, compiled UNMODIFIED from
+ * /root/reference/cslam/src/ORBmatcher.cpp against the mock Frame / KeyFrame / MapPoint headers in oracle/matchshim
+ * (oracle/Makefile target _ref/libref_match.so). Each rm_* function takes the same plain arrays as the corresponding
+ * mo_* function of oracle/match_oracle.cpp, builds the mock objects so that the reference's own host-side geometry
+ * reproduces exactly those inputs (identity poses, unit focal length, world point = (u, v, 1)), calls the reference
+ * method and translates the object state it leaves behind back into arrays. tests/test_match_oracle_vs_ref.py compares
+ * the two. Nothing here is shipped or called by the product path. */
+#include <cslam/ORBmatcher.h>
+
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+extern "C" void mo_frame_view(const void* fp, int* n, const uint8_t** desc, const float** x, const float** y, const int** octave, const float** angle);
+
+namespace cslam {
+float Frame::fx = 1.f, Frame::fy = 1.f, Frame::cx = 0.f, Frame::cy = 0.f;
+float Frame::mnMinX = -1e30f, Frame::mnMaxX = 1e30f, Frame::mnMinY = -1e30f, Frame::mnMaxY = 1e30f;
+}
+
+namespace {
+using namespace cslam;
+typedef boost::shared_ptr<MapPoint> mpptr;
+typedef boost::shared_ptr<KeyFrame> kfptr;
+
+cv::Mat desc_mat(const uint8_t* d, int n) {
+    cv::Mat m(n > 0 ? n : 1, 32, CV_8U);
+    if (n > 0) std::memcpy(m.data, d, (size_t)n * 32);
+    m.rows = n;
+    return m;
+}
+cv::Mat vec3(float a, float b, float c) { cv::Mat m(3, 1, CV_32F); m.at<float>(0) = a; m.at<float>(1) = b; m.at<float>(2) = c; return m; }
+
+void fill_common(const void* fp, int& N, std::vector<cv::KeyPoint>& keysUn, cv::Mat& desc) {
+    const uint8_t* d; const float *x, *y, *ang; const int* oct;
+    mo_frame_view(fp, &N, &d, &x, &y, &oct, &ang);
+    keysUn.resize(N);
+    for (int i = 0; i < N; i++) keysUn[i] = cv::KeyPoint(x[i], y[i], 31.f, ang[i], 0.f, oct[i]);
+    desc = desc_mat(d, N);
+}
+
+void make_frame(Frame& F, const void* fp, const float* sf, int nlevels) {
+    fill_common(fp, F.N, F.mvKeysUn, F.mDescriptors);
+    F.mvKeys = F.mvKeysUn;
+    F.grid = const_cast<void*>(fp);
+    F.mvpMapPoints.assign(F.N, mpptr());
+    F.mvbOutlier.assign(F.N, false);
+    F.mTcw = cv::Mat::eye(4, 4, CV_32F);
+    if (sf) F.mvScaleFactors.assign(sf, sf + nlevels);
+}
+
+kfptr make_kf(const void* fp, const float* sf, int nlevels) {
+    kfptr K(new KeyFrame());
+    fill_common(fp, K->N, K->mvKeysUn, K->mDescriptors);
+    K->grid = const_cast<void*>(fp);
+    K->mvpMapPoints.assign(K->N, mpptr());
+    K->minX = K->minY = -1e30f; K->maxX = K->maxY = 1e30f;
+    K->R = cv::Mat::eye(3, 3, CV_32F); K->t = vec3(0, 0, 0); K->C = vec3(0, 0, 0);
+    if (sf) K->mvScaleFactors.assign(sf, sf + nlevels);
+    return K;
+}
+
+mpptr make_mp(int id, const uint8_t* desc32, int nObs) {
+    mpptr p(new MapPoint());
+    p->id = id; p->nObs = nObs;
+    if (desc32) p->descriptor = desc_mat(desc32, 1);
+    return p;
+}
+
+/* holder codes of oracle/match_oracle.cpp -> occupants of F.mvpMapPoints / vpMatched, and back */
+void holder_to_points(const int* holder, int n, std::vector<mpptr>& v) {
+    v.assign(n, mpptr());
+    for (int i = 0; i < n; i++) {
+        if (holder[i] == -2) v[i] = make_mp(-2, nullptr, 1);
+        else if (holder[i] == -3) v[i] = make_mp(-3, nullptr, 0);
+    }
+}
+void points_to_holder(const std::vector<mpptr>& v, int* holder) {
+    for (size_t i = 0; i < v.size(); i++) holder[i] = v[i] ? v[i]->id : -1;
+}
+
+void set_world(mpptr p, float u, float v) {
+    p->worldPos = vec3(u, v, 1.f);
+    const float d = std::sqrt(u * u + v * v + 1.f);
+    p->normal = vec3(u / d, v / d, 1.f / d);          /* viewing-angle gates pass: PO.Pn ~ dist >= 0.5*dist */
+}
+
+DBoW2::FeatureVector feat_vec(int n, const int* node) {
+    DBoW2::FeatureVector fv;
+    for (int i = 0; i < n; i++) if (node[i] >= 0) fv.addFeature((DBoW2::NodeId)node[i], (unsigned)i);
+    return fv;
+}
+const int NLEV = 8;
+}  // namespace
+
+extern "C" {
+
+int rm_descriptor_distance(const uint8_t* a, const uint8_t* b) { return ORBmatcher::DescriptorDistance(desc_mat(a, 1), desc_mat(b, 1)); }
+
+/* ORBmatcher::SearchByProjection(Frame&, const vector<mpptr>&, th), ORBmatcher.cpp:71-148 */
+int rm_search_projection_mappoints(const void* fp, int nq, const uint8_t* q_valid, const float* q_u, const float* q_v,
+                                   const int* q_level, const float* q_viewcos, const uint8_t* q_desc, const uint8_t* q_obs,
+                                   float th, float nnratio, const float* scale_factors, int* holder) {
+    Frame F;
+    make_frame(F, fp, scale_factors, NLEV);
+    holder_to_points(holder, F.N, F.mvpMapPoints);
+    std::vector<mpptr> mps(nq);
+    for (int i = 0; i < nq; i++) {
+        mps[i] = make_mp(i, q_desc + (size_t)32 * i, q_obs[i] ? 1 : 0);
+        mps[i]->mbTrackInView = q_valid[i] != 0;
+        mps[i]->mTrackProjX = q_u[i]; mps[i]->mTrackProjY = q_v[i];
+        mps[i]->mnTrackScaleLevel = q_level[i]; mps[i]->mTrackViewCos = q_viewcos[i];
+    }
+    ORBmatcher m(nnratio, true);
+    const int nm = m.SearchByProjection(F, mps, th);
+    points_to_holder(F.mvpMapPoints, holder);
+    return nm;
+}
+
+/* ORBmatcher::SearchByProjection(Frame& Current, const Frame& Last, th), ORBmatcher.cpp:1350-1476 */
+int rm_search_projection_lastframe(const void* fp, int nq, const uint8_t* q_valid, const float* q_u, const float* q_v,
+                                   const int* q_octave, const float* q_angle, const uint8_t* q_desc, const uint8_t* q_obs,
+                                   float th, const float* scale_factors, int check_orientation, int* holder) {
+    boost::shared_ptr<Frame> Cur(new Frame());
+    make_frame(*Cur, fp, scale_factors, NLEV);
+    holder_to_points(holder, Cur->N, Cur->mvpMapPoints);
+    Frame Last;
+    Last.N = nq;
+    Last.mTcw = cv::Mat::eye(4, 4, CV_32F);
+    Last.mvKeys.resize(nq); Last.mvKeysUn.resize(nq);
+    Last.mvpMapPoints.assign(nq, mpptr());
+    Last.mvbOutlier.assign(nq, false);
+    for (int i = 0; i < nq; i++) {
+        Last.mvKeys[i] = cv::KeyPoint(q_u[i], q_v[i], 31.f, q_angle[i], 0.f, q_octave[i]);
+        Last.mvKeysUn[i] = Last.mvKeys[i];
+        if (!q_valid[i]) continue;
+        Last.mvpMapPoints[i] = make_mp(i, q_desc + (size_t)32 * i, q_obs[i] ? 1 : 0);
+        set_world(Last.mvpMapPoints[i], q_u[i], q_v[i]);
+    }
+    ORBmatcher m(0.9f, check_orientation != 0);
+    const int nm = m.SearchByProjection(*Cur, Last, th);
+    points_to_holder(Cur->mvpMapPoints, holder);
+    return nm;
+}
+
+/* ORBmatcher::SearchByProjection(kfptr, Scw, vpPoints, vpMatched, th), ORBmatcher.cpp:308-446 */
+int rm_search_projection_kf_sim3(const void* fp, int nq, const uint8_t* q_valid, const float* q_u, const float* q_v,
+                                 const int* q_level, const uint8_t* q_desc, const uint8_t* q_claims, int th,
+                                 const float* scale_factors, int* holder) {
+    kfptr K = make_kf(fp, scale_factors, NLEV);
+    std::vector<mpptr> matched;
+    holder_to_points(holder, K->N, matched);
+    std::vector<mpptr> pts(nq);
+    for (int i = 0; i < nq; i++) {
+        pts[i] = make_mp(i, q_desc + (size_t)32 * i, 1);
+        pts[i]->bad = !q_valid[i];
+        pts[i]->predictedLevel = q_level[i];
+        set_world(pts[i], q_u[i], q_v[i]);
+        if (!q_claims[i]) pts[i]->indexInKF[K.get()] = 0;      /* already observed by pKF: the re-map branch, :414-433 */
+    }
+    ORBmatcher m(0.75f, true);
+    const int nm = m.SearchByProjection(K, cv::Mat::eye(4, 4, CV_32F), pts, matched, th);
+    points_to_holder(matched, holder);
+    return nm;
+}
+
+/* ORBmatcher::SearchByBoW(kfptr, Frame&, vpMapPointMatches), ORBmatcher.cpp:178-306 */
+int rm_search_bow_kf_frame(int nKF, const uint8_t* desc_kf, const int* node_kf, const uint8_t* valid_kf, const float* angle_kf,
+                           int nF, const uint8_t* desc_f, const int* node_f, const float* angle_f,
+                           float nnratio, int check_orientation, int* match_of_f) {
+    kfptr K(new KeyFrame());
+    K->N = nKF; K->mDescriptors = desc_mat(desc_kf, nKF); K->mFeatVec = feat_vec(nKF, node_kf);
+    K->mvKeysUn.resize(nKF); K->mvpMapPoints.assign(nKF, mpptr());
+    for (int i = 0; i < nKF; i++) {
+        K->mvKeysUn[i] = cv::KeyPoint(0, 0, 31.f, angle_kf[i]);
+        if (valid_kf[i]) K->mvpMapPoints[i] = make_mp(i, nullptr, 1);
+    }
+    Frame F;
+    F.N = nF; F.mDescriptors = desc_mat(desc_f, nF); F.mFeatVec = feat_vec(nF, node_f);
+    F.mvKeys.resize(nF);
+    for (int i = 0; i < nF; i++) F.mvKeys[i] = cv::KeyPoint(0, 0, 31.f, angle_f[i]);
+    F.mvKeysUn = F.mvKeys;
+    std::vector<mpptr> out;
+    ORBmatcher m(nnratio, check_orientation != 0);
+    const int nm = m.SearchByBoW(K, F, out);
+    for (int i = 0; i < nF; i++) match_of_f[i] = (i < (int)out.size() && out[i]) ? out[i]->id : -1;
+    return nm;
+}
+
+/* ORBmatcher::SearchByBoW(kfptr, kfptr, vpMatches12), ORBmatcher.cpp:565-698 */
+int rm_search_bow_kf_kf(int n1, const uint8_t* desc1, const int* node1, const uint8_t* valid1, const float* angle1,
+                        int n2, const uint8_t* desc2, const int* node2, const uint8_t* valid2, const float* angle2,
+                        float nnratio, int check_orientation, int* match12) {
+    kfptr K[2] = {kfptr(new KeyFrame()), kfptr(new KeyFrame())};
+    const int n[2] = {n1, n2}; const uint8_t* d[2] = {desc1, desc2}; const int* nd[2] = {node1, node2};
+    const uint8_t* v[2] = {valid1, valid2}; const float* a[2] = {angle1, angle2};
+    for (int k = 0; k < 2; k++) {
+        K[k]->N = n[k]; K[k]->mDescriptors = desc_mat(d[k], n[k]); K[k]->mFeatVec = feat_vec(n[k], nd[k]);
+        K[k]->mvKeysUn.resize(n[k]); K[k]->mvpMapPoints.assign(n[k], mpptr());
+        for (int i = 0; i < n[k]; i++) {
+            K[k]->mvKeysUn[i] = cv::KeyPoint(0, 0, 31.f, a[k][i]);
+            if (v[k][i]) K[k]->mvpMapPoints[i] = make_mp(i, nullptr, 1);
+        }
+    }
+    std::vector<mpptr> out;
+    ORBmatcher m(nnratio, check_orientation != 0);
+    const int nm = m.SearchByBoW(K[0], K[1], out);
+    for (int i = 0; i < n1; i++) match12[i] = (i < (int)out.size() && out[i]) ? out[i]->id : -1;
+    return nm;
+}
+
+/* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), ORBmatcher.cpp:448-563 */
+int rm_search_for_initialization(int n1, const uint8_t* desc1, const int* octave1, const float* angle1, float* prev_xy,
+                                 const void* f2, int windowSize, float nnratio, int check_orientation, int* matches12) {
+    Frame F1, F2;
+    F1.N = n1; F1.mDescriptors = desc_mat(desc1, n1);
+    F1.mvKeysUn.resize(n1);
+    for (int i = 0; i < n1; i++) F1.mvKeysUn[i] = cv::KeyPoint(prev_xy[2 * i], prev_xy[2 * i + 1], 31.f, angle1[i], 0.f, octave1[i]);
+    F1.mvKeys = F1.mvKeysUn;
+    make_frame(F2, f2, nullptr, 0);
+    std::vector<cv::Point2f> prev(n1);
+    for (int i = 0; i < n1; i++) prev[i] = cv::Point2f(prev_xy[2 * i], prev_xy[2 * i + 1]);
+    std::vector<int> m12;
+    ORBmatcher m(nnratio, check_orientation != 0);
+    const int nm = m.SearchForInitialization(F1, F2, prev, m12, windowSize);
+    for (int i = 0; i < n1; i++) {
+        matches12[i] = i < (int)m12.size() ? m12[i] : -1;
+        prev_xy[2 * i] = prev[i].x; prev_xy[2 * i + 1] = prev[i].y;
+    }
+    return nm;
+}
+
+}  // extern "C"

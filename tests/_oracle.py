@@ -296,3 +296,90 @@ class OracleMatcher:
         res = np.zeros(max(len(q), 1), RESULT_DTYPE)
         self.L.mo_match_allpairs_best2(len(q), q.ctypes.data, len(t), t.ctypes.data, self.nnratio, res.ctypes.data)
         return res[:len(q)]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the reference's own ORBmatcher.cpp, compiled unmodified over mock Frame/KeyFrame/MapPoint (oracle/_ref/libref_match.so)
+# ---------------------------------------------------------------------------------------------------------------
+def ref_match_available():
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_match.so"))
+
+
+class RefMatcher:
+    """Same array interface as OracleMatcher, executed by the reference's ORBmatcher methods. `F` arguments are
+    OracleFrame objects whose handles must come from the SAME library (pass lib=self.L to OracleFrame)."""
+
+    def __init__(self, nnratio=0.6, checkOri=True):
+        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", "libref_match.so"))
+        L.mo_frame_create.restype = _vp
+        L.mo_frame_create.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _i, _i]
+        L.mo_frame_destroy.argtypes = [_vp]
+        L.rm_descriptor_distance.argtypes = [_vp, _vp]
+        L.rm_search_projection_mappoints.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _vp, _vp]
+        L.rm_search_projection_lastframe.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _vp, _i, _vp]
+        L.rm_search_projection_kf_sim3.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp]
+        L.rm_search_bow_kf_frame.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _c.c_float, _i, _vp]
+        L.rm_search_bow_kf_kf.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _c.c_float, _i, _vp]
+        L.rm_search_for_initialization.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _i, _c.c_float, _i, _vp]
+        self.L = L
+        self.nnratio = float(np.float32(nnratio))
+        self.ori = 1 if checkOri else 0
+
+    def frame(self, fr, grid):
+        """Frame handle living in libref_match.so's copy of the grid code."""
+        f = OracleFrame.__new__(OracleFrame)
+        f.L = self.L
+        f.desc = _a(fr["desc"], np.uint8).reshape(-1, 32)
+        f.x, f.y, f.octave, f.angle = _a(fr["x"], np.float32), _a(fr["y"], np.float32), _a(fr["octave"], np.int32), _a(fr["angle"], np.float32)
+        f.n, f.grid = len(f.desc), grid
+        f.h = self.L.mo_frame_create(f.n, f.desc.ctypes.data, f.x.ctypes.data, f.y.ctypes.data, f.octave.ctypes.data,
+                                     f.angle.ctypes.data, grid.min_x, grid.min_y, grid.inv_w, grid.inv_h, grid.cols, grid.rows)
+        return f
+
+    def descriptor_distance(self, a, b):
+        a = _a(a, np.uint8).reshape(-1, 32); b = _a(b, np.uint8).reshape(-1, 32)
+        return np.array([self.L.rm_descriptor_distance(a[i].ctypes.data, b[i].ctypes.data) for i in range(len(a))], np.int32)
+
+    def projection_mappoints(self, F, q_valid, q_u, q_v, q_level, q_viewcos, q_desc, q_obs, th, sf, holder):
+        v, u_, v_, l, c, d, o, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
+                                    _a(q_viewcos, np.float32), _a(q_desc, np.uint8), _a(q_obs, np.uint8), _a(sf, np.float32))
+        return self.L.rm_search_projection_mappoints(F.h, len(u_), v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
+                                                     c.ctypes.data, d.ctypes.data, o.ctypes.data, th, self.nnratio, s.ctypes.data,
+                                                     holder.ctypes.data)
+
+    def projection_lastframe(self, F, q_valid, q_u, q_v, q_octave, q_angle, q_desc, q_obs, th, sf, holder):
+        v, u_, v_, l, a, d, o, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_octave, np.int32),
+                                    _a(q_angle, np.float32), _a(q_desc, np.uint8), _a(q_obs, np.uint8), _a(sf, np.float32))
+        return self.L.rm_search_projection_lastframe(F.h, len(u_), v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
+                                                     a.ctypes.data, d.ctypes.data, o.ctypes.data, th, s.ctypes.data, self.ori,
+                                                     holder.ctypes.data)
+
+    def projection_kf_sim3(self, F, q_valid, q_u, q_v, q_level, q_desc, q_claims, th, sf, holder):
+        v, u_, v_, l, d, c, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
+                                 _a(q_desc, np.uint8), _a(q_claims, np.uint8), _a(sf, np.float32))
+        return self.L.rm_search_projection_kf_sim3(F.h, len(u_), v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
+                                                   d.ctypes.data, c.ctypes.data, int(th), s.ctypes.data, holder.ctypes.data)
+
+    def bow_kf_frame(self, desc_kf, node_kf, valid_kf, angle_kf, desc_f, node_f, angle_f):
+        dk, nk, vk, ak = _a(desc_kf, np.uint8), _a(node_kf, np.int32), _a(valid_kf, np.uint8), _a(angle_kf, np.float32)
+        df, nf, af = _a(desc_f, np.uint8), _a(node_f, np.int32), _a(angle_f, np.float32)
+        mf = np.full(max(len(nf), 1), -1, np.int32)
+        nm = self.L.rm_search_bow_kf_frame(len(nk), dk.ctypes.data, nk.ctypes.data, vk.ctypes.data, ak.ctypes.data, len(nf),
+                                           df.ctypes.data, nf.ctypes.data, af.ctypes.data, self.nnratio, self.ori, mf.ctypes.data)
+        return nm, mf[:len(nf)]
+
+    def bow_kf_kf(self, d1, n1, v1, a1, d2, n2, v2, a2):
+        d1, n1, v1, a1 = _a(d1, np.uint8), _a(n1, np.int32), _a(v1, np.uint8), _a(a1, np.float32)
+        d2, n2, v2, a2 = _a(d2, np.uint8), _a(n2, np.int32), _a(v2, np.uint8), _a(a2, np.float32)
+        m12 = np.full(max(len(n1), 1), -1, np.int32)
+        nm = self.L.rm_search_bow_kf_kf(len(n1), d1.ctypes.data, n1.ctypes.data, v1.ctypes.data, a1.ctypes.data, len(n2),
+                                        d2.ctypes.data, n2.ctypes.data, v2.ctypes.data, a2.ctypes.data, self.nnratio, self.ori,
+                                        m12.ctypes.data)
+        return nm, m12[:len(n1)]
+
+    def search_for_initialization(self, desc1, octave1, angle1, prev_xy, F2, windowSize):
+        d1, o1, a1 = _a(desc1, np.uint8), _a(octave1, np.int32), _a(angle1, np.float32)
+        m12 = np.full(max(len(o1), 1), -1, np.int32)
+        nm = self.L.rm_search_for_initialization(len(o1), d1.ctypes.data, o1.ctypes.data, a1.ctypes.data, prev_xy.ctypes.data,
+                                                 F2.h, int(windowSize), self.nnratio, self.ori, m12.ctypes.data)
+        return nm, m12[:len(o1)]

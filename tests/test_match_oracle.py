@@ -1,9 +1,7 @@
 """CPU: the matcher oracle (oracle/match_oracle.cpp) against independent numpy restatements of the arithmetic it
 rests on — SWAR popcount == bit count, GetFeaturesInArea == brute-force window filter in grid order, all-pairs
 best-2 == argmin/partition — and hand-built known-answer cases of the greedy rules of cslam/src/ORBmatcher.cpp.
-PARITY NOTE: the reference ships no tests or golden vectors for ORBmatcher, and ORBmatcher.cpp is
-welded to Frame/KeyFrame/MapPoint, so unlike the extractor it is not compiled here: the matcher oracle is pinned by
-these known-answer cases only ("parity unpinned" against reference outputs)."""
+The oracle is additionally pinned to the reference's own ORBmatcher.cpp compiled unmodified: tests/test_match_oracle_vs_ref.py."""
 import numpy as np
 
 from _oracle import OracleFrame, OracleMatcher
