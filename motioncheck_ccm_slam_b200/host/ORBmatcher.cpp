@@ -1,0 +1,332 @@
+// Drop-in replacement bodies for cslam/src/ORBmatcher.cpp of taiyaki-go/motioncheck_ccm_slam: the SAME class declaration
+// (this file includes the reference's own, unmodified <cslam/ORBmatcher.h>); each search keeps the host-side geometry
+// the reference performs before its candidate loop (so u, v, radius and level are bit-identical), packs one
+// ccm_window_query per loop iteration that reaches GetFeaturesInArea, and lets the CUDA library (include/ccm_match.h)
+// run the candidate loops, including their greedy order and the rotation-histogram pruning. The state the reference
+// loop would have left (F.mvpMapPoints, vpMatched, vnMatches12, ...) is written back from the returned arrays.
+//
+// Converted here: DescriptorDistance, SearchByProjection(Frame, MapPoints), SearchByProjection(Frame, LastFrame),
+// SearchByProjection(KeyFrame, Scw), SearchByBoW(KeyFrame, Frame), SearchByBoW(KeyFrame, KeyFrame),
+// SearchForInitialization. SearchBySim3 / Fuse (distance phase = CCM_WIN_BEST) and
+// SearchForTriangulation keep their upstream bodies this round. A CUDA failure throws estd::infrastructure_ex (the
+// reference's fatal-error convention, estd.h:74); there is no CPU fallback.
+#include <cslam/ORBmatcher.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+#include "ccm_match.h"
+
+namespace {
+
+struct Device {
+    ccm_matcher* m = nullptr;
+    std::mutex mu;
+};
+
+Device& device() {
+    static Device d;
+    if (!d.m) {
+        const char* e = std::getenv("CCM_ORB_DEVICE");       // agent -> GPU pinning, same variable as the extractor
+        if (ccm_matcher_create(e ? std::atoi(e) : 0, &d.m) != CCM_OK) throw estd::infrastructure_ex();
+    }
+    return d;
+}
+
+// Device copy of what the matcher reads of a Frame / KeyFrame. Built per call here; a production build caches it on the
+// object (one upload per Frame / KeyFrame) as INTEGRATION.md describes.
+struct Pack {
+    ccm_frame_pack* p = nullptr;
+    Pack(ccm_matcher* m, int n, const cv::Mat& desc, const std::vector<cv::KeyPoint>& keysUn, float minX, float minY, float invW,
+         float invH, int cols, int rows) {
+        const int cap = n > 0 ? n : 1;
+        if (ccm_frame_pack_create(m, cap, &p) != CCM_OK) throw estd::infrastructure_ex();
+        std::vector<float> x(cap), y(cap), ang(cap);
+        std::vector<int> oct(cap);
+        std::vector<uint8_t> d((size_t)cap * 32);
+        for (int i = 0; i < n; i++) {
+            x[i] = keysUn[i].pt.x; y[i] = keysUn[i].pt.y; ang[i] = keysUn[i].angle; oct[i] = keysUn[i].octave;
+            std::memcpy(&d[(size_t)32 * i], desc.ptr(i), 32);
+        }
+        ccm_grid_params g = {minX, minY, invW, invH, cols, rows};
+        if (ccm_frame_pack_upload(p, &g, n, d.data(), x.data(), y.data(), oct.data(), ang.data()) != CCM_OK) {
+            ccm_frame_pack_destroy(p);
+            throw estd::infrastructure_ex();
+        }
+    }
+    ~Pack() { ccm_frame_pack_destroy(p); }
+    Pack(const Pack&) = delete;
+    Pack& operator=(const Pack&) = delete;
+};
+
+inline ccm_window_query no_query() { ccm_window_query q; std::memset(&q, 0, sizeof(q)); return q; }
+
+void run_window(ccm_matcher* m, ccm_frame_pack* pack, int mode, float nnratio, int th_dist, bool ori, std::vector<ccm_window_query>& q,
+                std::vector<uint8_t>& qd, int* holder, ccm_match_result* res, int& nmatches) {
+    ccm_window_params prm;
+    prm.mode = mode; prm.nnratio = nnratio; prm.th_dist = th_dist; prm.check_orientation = ori ? 1 : 0;
+    prm.inv_sigma2 = nullptr; prm.n_levels = 0;
+    nmatches = 0;
+    if (q.empty()) return;
+    if (ccm_search_window(m, pack, &prm, (int)q.size(), q.data(), qd.data(), holder, res, &nmatches) != CCM_OK)
+        throw estd::infrastructure_ex();
+}
+
+// FeatureVector (node id -> feature indices) as one node id per feature, -1 = not in the vector
+std::vector<int> node_ids(const DBoW2::FeatureVector& fv, int n) {
+    std::vector<int> node(n > 0 ? n : 1, -1);
+    for (DBoW2::FeatureVector::const_iterator it = fv.begin(); it != fv.end(); ++it)
+        for (size_t k = 0; k < it->second.size(); k++)
+            if ((int)it->second[k] < n) node[it->second[k]] = (int)it->first;
+    return node;
+}
+
+}  // namespace
+
+namespace cslam {
+
+const int ORBmatcher::TH_HIGH = 100;
+const int ORBmatcher::TH_LOW = 50;
+const int ORBmatcher::HISTO_LENGTH = 30;
+
+ORBmatcher::ORBmatcher(float nnratio, bool checkOri) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+// ORBmatcher.cpp:150-156
+float ORBmatcher::RadiusByViewingCos(const float &viewCos) {
+    if (viewCos > 0.998) return 2.5;
+    return 4.0;
+}
+
+// ORBmatcher.cpp:1653-1669 — single pairs stay on the host (called from MapPoint.cpp:645,968 and Tracking.cpp:491);
+// batches go through ccm_descriptor_distance.
+int ORBmatcher::DescriptorDistance(const cv::Mat &a, const cv::Mat &b) {
+    const uint32_t* pa = a.ptr<uint32_t>();
+    const uint32_t* pb = b.ptr<uint32_t>();
+    int dist = 0;
+    for (int i = 0; i < 8; i++) dist += __builtin_popcount(pa[i] ^ pb[i]);
+    return dist;
+}
+
+// ORBmatcher.cpp:71-148
+int ORBmatcher::SearchByProjection(Frame &F, const vector<mpptr> &vpMapPoints, const float th) {
+    const bool bFactor = th != 1.0;
+    const int nq = (int)vpMapPoints.size();
+    std::vector<ccm_window_query> q(nq, no_query());
+    std::vector<uint8_t> qd((size_t)nq * 32 + 32);
+    for (int i = 0; i < nq; i++) {
+        mpptr pMP = vpMapPoints[i];
+        if (!pMP->mbTrackInView) continue;
+        if (pMP->isBad()) continue;
+        const int lvl = pMP->mnTrackScaleLevel;
+        float r = RadiusByViewingCos(pMP->mTrackViewCos);
+        if (bFactor) r *= th;
+        q[i].u = pMP->mTrackProjX; q[i].v = pMP->mTrackProjY; q[i].r = r * F.mvScaleFactors[lvl];
+        q[i].min_level = (int16_t)(lvl - 1); q[i].max_level = (int16_t)lvl;
+        q[i].flags = CCM_Q_VALID | (pMP->Observations() > 0 ? CCM_Q_OBS : 0u);
+        std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+    }
+    std::vector<int> holder(F.N > 0 ? F.N : 1, -1);
+    for (int k = 0; k < F.N; k++)
+        if (F.mvpMapPoints[k]) holder[k] = F.mvpMapPoints[k]->Observations() > 0 ? -2 : -3;
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    Pack pack(D.m, F.N, F.mDescriptors, F.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+              Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
+    int nmatches = 0;
+    run_window(D.m, pack.p, CCM_WIN_PROJ_MAPPOINTS, mfNNratio, TH_HIGH, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
+    for (int k = 0; k < F.N; k++)
+        if (holder[k] >= 0) F.mvpMapPoints[k] = vpMapPoints[holder[k]];
+    return nmatches;
+}
+
+// ORBmatcher.cpp:1350-1476
+int ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, const float th) {
+    const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+    const int nq = LastFrame.N;
+    std::vector<ccm_window_query> q(nq, no_query());
+    std::vector<uint8_t> qd((size_t)nq * 32 + 32);
+    for (int i = 0; i < nq; i++) {
+        mpptr pMP = LastFrame.mvpMapPoints[i];
+        if (!pMP || LastFrame.mvbOutlier[i]) continue;
+        cv::Mat x3Dw = pMP->GetWorldPos();
+        cv::Mat x3Dc = Rcw * x3Dw + tcw;
+        const float xc = x3Dc.at<float>(0), yc = x3Dc.at<float>(1);
+        const float invzc = 1.0 / x3Dc.at<float>(2);
+        if (invzc < 0) continue;
+        const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        const int nLastOctave = LastFrame.mvKeys[i].octave;
+        q[i].u = u; q[i].v = v; q[i].r = th * CurrentFrame.mvScaleFactors[nLastOctave];
+        q[i].angle = LastFrame.mvKeysUn[i].angle;
+        q[i].min_level = (int16_t)(nLastOctave - 1); q[i].max_level = (int16_t)(nLastOctave + 1);
+        q[i].flags = CCM_Q_VALID | (pMP->Observations() > 0 ? CCM_Q_OBS : 0u);
+        std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+    }
+    const int N = CurrentFrame.N;
+    std::vector<int> holder(N > 0 ? N : 1, -1);
+    for (int k = 0; k < N; k++)
+        if (CurrentFrame.mvpMapPoints[k]) holder[k] = CurrentFrame.mvpMapPoints[k]->Observations() > 0 ? -2 : -3;
+    const std::vector<int> before = holder;
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    Pack pack(D.m, N, CurrentFrame.mDescriptors, CurrentFrame.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+              Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
+    int nmatches = 0;
+    run_window(D.m, pack.p, CCM_WIN_PROJ_LASTFRAME, mfNNratio, TH_HIGH, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
+    for (int k = 0; k < N; k++) {
+        if (holder[k] >= 0) CurrentFrame.mvpMapPoints[k] = LastFrame.mvpMapPoints[holder[k]];
+        else if (holder[k] == -1 && before[k] != -1) CurrentFrame.mvpMapPoints[k] = mpptr();   // pruned by the rotation histogram (:1461)
+    }
+    return nmatches;
+}
+
+// ORBmatcher.cpp:308-446
+int ORBmatcher::SearchByProjection(kfptr pKF, cv::Mat Scw, const vector<mpptr> &vpPoints, vector<mpptr> &vpMatched, int th) {
+    const float &fx = pKF->fx, &fy = pKF->fy, &cx = pKF->cx, &cy = pKF->cy;
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    set<mpptr> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+    spAlreadyFound.erase(nullptr);
+    const int nq = (int)vpPoints.size();
+    std::vector<ccm_window_query> q(nq, no_query());
+    std::vector<uint8_t> qd((size_t)nq * 32 + 32);
+    for (int i = 0; i < nq; i++) {
+        mpptr pMP = vpPoints[i];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.at<float>(2) < 0.0) continue;
+        const float invz = 1 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz, y = p3Dc.at<float>(1) * invz;
+        const float u = fx * x + cx, v = fy * y + cy;
+        if (!pKF->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        cv::Mat PO = p3Dw - Ow;
+        const float dist = cv::norm(PO);
+        if (dist < minDistance || dist > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (PO.dot(Pn) < 0.5 * dist) continue;
+        const int lvl = pMP->PredictScale(dist, pKF);
+        q[i].u = u; q[i].v = v; q[i].r = th * pKF->mvScaleFactors[lvl];
+        q[i].min_level = (int16_t)(lvl - 1); q[i].max_level = (int16_t)lvl;
+        q[i].flags = CCM_Q_VALID | (pMP->GetIndexInKeyFrame(pKF) == -1 ? CCM_Q_CLAIMS : 0u);
+        std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+    }
+    const int N = pKF->N;
+    std::vector<int> holder(N > 0 ? N : 1, -1);
+    for (int k = 0; k < N; k++) if (vpMatched[k]) holder[k] = -2;
+    std::vector<ccm_match_result> res(nq > 0 ? nq : 1);
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    Pack pack(D.m, N, pKF->mDescriptors, pKF->mvKeysUn, (float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv,
+              pKF->mfGridElementHeightInv, pKF->mnGridCols, pKF->mnGridRows);
+    int nmatches = 0;
+    run_window(D.m, pack.p, CCM_WIN_PROJ_KF_SIM3, mfNNratio, TH_LOW, mbCheckOrientation, q, qd, holder.data(), res.data(), nmatches);
+    for (int i = 0; i < nq; i++) {
+        if (!res[i].accepted) continue;
+        mpptr pMP = vpPoints[i];
+        const int bestIdx = res[i].best_idx, bestDist = res[i].best_dist;
+        const int existing_idx = pMP->GetIndexInKeyFrame(pKF);
+        if (existing_idx != -1) {
+            // the key frame already observes this point: move the observation unless the feature's own descriptor is
+            // closer to the point than the match found (:414-433; dist_newplace is the distance to the same feature)
+            bool bDoNotReplace = false;
+            if (pKF->GetMapPoint(bestIdx)) {
+                const int dist_newplace = DescriptorDistance(pMP->GetDescriptor(), pKF->mDescriptors.row(bestIdx));
+                if (dist_newplace < bestDist) bDoNotReplace = true;
+            }
+            if (!bDoNotReplace) pKF->RemapMapPointMatch(pMP, existing_idx, bestIdx);
+        } else {
+            vpMatched[bestIdx] = pMP;
+        }
+    }
+    return nmatches;
+}
+
+// ORBmatcher.cpp:178-306
+int ORBmatcher::SearchByBoW(kfptr pKF, Frame &F, vector<mpptr> &vpMapPointMatches) {
+    const vector<mpptr> vpMapPointsKF = pKF->GetMapPointMatches();
+    vpMapPointMatches = vector<mpptr>(F.N, static_cast<mpptr>(NULL));
+    const int nKF = (int)vpMapPointsKF.size(), nF = F.N;
+    std::vector<uint8_t> valid(nKF > 0 ? nKF : 1, 0);
+    std::vector<float> angKF(nKF > 0 ? nKF : 1), angF(nF > 0 ? nF : 1);
+    for (int i = 0; i < nKF; i++) {
+        valid[i] = (vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad()) ? 1 : 0;
+        angKF[i] = pKF->mvKeysUn[i].angle;
+    }
+    for (int i = 0; i < nF; i++) angF[i] = F.mvKeys[i].angle;
+    const std::vector<int> nodeKF = node_ids(pKF->mFeatVec, nKF), nodeF = node_ids(F.mFeatVec, nF);
+    std::vector<int> match_f(nF > 0 ? nF : 1, -1);
+    int nmatches = 0;
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    if (ccm_search_bow(D.m, CCM_BOW_KF_FRAME, mfNNratio, mbCheckOrientation ? 1 : 0, nKF, pKF->mDescriptors.ptr(0), nodeKF.data(),
+                       valid.data(), angKF.data(), nF, F.mDescriptors.ptr(0), nodeF.data(), nullptr, angF.data(), nullptr,
+                       match_f.data(), nullptr, &nmatches) != CCM_OK)
+        throw estd::infrastructure_ex();
+    for (int i = 0; i < nF; i++)
+        if (match_f[i] >= 0) vpMapPointMatches[i] = vpMapPointsKF[match_f[i]];
+    return nmatches;
+}
+
+// ORBmatcher.cpp:565-698
+int ORBmatcher::SearchByBoW(kfptr pKF1, kfptr pKF2, vector<mpptr> &vpMatches12) {
+    const vector<mpptr> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int n1 = (int)vpMapPoints1.size(), n2 = (int)vpMapPoints2.size();
+    vpMatches12 = vector<mpptr>(n1, static_cast<mpptr>(NULL));
+    std::vector<uint8_t> v1(n1 > 0 ? n1 : 1, 0), v2(n2 > 0 ? n2 : 1, 0);
+    std::vector<float> a1(n1 > 0 ? n1 : 1), a2(n2 > 0 ? n2 : 1);
+    for (int i = 0; i < n1; i++) { v1[i] = (vpMapPoints1[i] && !vpMapPoints1[i]->isBad()) ? 1 : 0; a1[i] = pKF1->mvKeysUn[i].angle; }
+    for (int i = 0; i < n2; i++) { v2[i] = (vpMapPoints2[i] && !vpMapPoints2[i]->isBad()) ? 1 : 0; a2[i] = pKF2->mvKeysUn[i].angle; }
+    const std::vector<int> node1 = node_ids(pKF1->mFeatVec, n1), node2 = node_ids(pKF2->mFeatVec, n2);
+    std::vector<int> m12(n1 > 0 ? n1 : 1, -1);
+    int nmatches = 0;
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    if (ccm_search_bow(D.m, CCM_BOW_KF_KF, mfNNratio, mbCheckOrientation ? 1 : 0, n1, pKF1->mDescriptors.ptr(0), node1.data(), v1.data(),
+                       a1.data(), n2, pKF2->mDescriptors.ptr(0), node2.data(), v2.data(), a2.data(), m12.data(), nullptr, nullptr,
+                       &nmatches) != CCM_OK)
+        throw estd::infrastructure_ex();
+    for (int i = 0; i < n1; i++)
+        if (m12[i] >= 0) vpMatches12[i] = vpMapPoints2[m12[i]];
+    return nmatches;
+}
+
+// ORBmatcher.cpp:448-563
+int ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f> &vbPrevMatched, vector<int> &vnMatches12, int windowSize) {
+    const int n1 = (int)F1.mvKeysUn.size(), n2 = (int)F2.mvKeysUn.size();
+    vnMatches12 = vector<int>(n1, -1);
+    std::vector<ccm_window_query> q(n1, no_query());
+    std::vector<uint8_t> qd((size_t)n1 * 32 + 32);
+    for (int i1 = 0; i1 < n1; i1++) {
+        const cv::KeyPoint &kp1 = F1.mvKeysUn[i1];
+        const int level1 = kp1.octave;
+        std::memcpy(&qd[(size_t)32 * i1], F1.mDescriptors.ptr(i1), 32);
+        if (level1 > 0) continue;
+        q[i1].u = vbPrevMatched[i1].x; q[i1].v = vbPrevMatched[i1].y; q[i1].r = (float)windowSize;
+        q[i1].angle = kp1.angle;
+        q[i1].min_level = (int16_t)level1; q[i1].max_level = (int16_t)level1;
+        q[i1].flags = CCM_Q_VALID;
+    }
+    std::vector<int> holder(n2 > 0 ? n2 : 1, -1);           // vnMatches21, output only
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    Pack pack(D.m, n2, F2.mDescriptors, F2.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+              Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
+    int nmatches = 0;
+    run_window(D.m, pack.p, CCM_WIN_INIT, mfNNratio, TH_LOW, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
+    for (int i2 = 0; i2 < n2; i2++)
+        if (holder[i2] >= 0) vnMatches12[holder[i2]] = i2;
+    for (int i1 = 0; i1 < n1; i1++)
+        if (vnMatches12[i1] >= 0) vbPrevMatched[i1] = F2.mvKeysUn[vnMatches12[i1]].pt;   // :558-560
+    return nmatches;
+}
+
+}  // namespace cslam

@@ -125,6 +125,10 @@ void* mo_frame_create(int n, const uint8_t* desc, const float* x, const float* y
 }
 void mo_frame_destroy(void* f) { delete (MoFrame*)f; }
 
+void mo_frame_params(const void* fp, float* min_x, float* min_y, float* inv_w, float* inv_h, int* cols, int* rows) {
+    const MoFrame* f = (const MoFrame*)fp;
+    *min_x = f->min_x; *min_y = f->min_y; *inv_w = f->inv_w; *inv_h = f->inv_h; *cols = f->cols; *rows = f->rows;
+}
 /* read-only view of a frame's arrays (used by oracle/ref_match_glue.cpp to build the mock Frame / KeyFrame) */
 void mo_frame_view(const void* fp, int* n, const uint8_t** desc, const float** x, const float** y, const int** octave, const float** angle) {
     const MoFrame* f = (const MoFrame*)fp;

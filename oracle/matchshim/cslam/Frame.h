@@ -10,6 +10,9 @@
 #include <thirdparty/DBoW2/DBoW2/FeatureVector.h>
 #include <cslam/MapPoint.h>
 
+#define FRAME_GRID_ROWS 48
+#define FRAME_GRID_COLS 75
+
 extern "C" int mo_features_in_area(const void* fp, float x, float y, float r, int minLevel, int maxLevel, int kf_variant, int* out, int cap);
 
 namespace cslam {
@@ -35,5 +38,6 @@ public:
     cv::Mat mTcw;
     std::vector<float> mvScaleFactors;
     static float mnMinX, mnMaxX, mnMinY, mnMaxY;
+    static float mfGridElementWidthInv, mfGridElementHeightInv;   /* Frame.h:147-148 */
 };
 }

@@ -15,7 +15,10 @@ public:
     void* grid = nullptr;
     int N = 0;
     float fx = 1, fy = 1, cx = 0, cy = 0;
-    float minX = 0, maxX = 0, minY = 0, maxY = 0;
+    float minX = 0, maxX = 0, minY = 0, maxY = 0;       /* IsInImage bounds of the mock */
+    int mnMinX = 0, mnMinY = 0, mnMaxX = 0, mnMaxY = 0;   /* KeyFrame.h:345-348 (int upstream) */
+    int mnGridCols = 75, mnGridRows = 48;
+    float mfGridElementWidthInv = 0, mfGridElementHeightInv = 0;   /* KeyFrame.h:289-290 */
     std::vector<cv::KeyPoint> mvKeysUn;
     cv::Mat mDescriptors;
     DBoW2::FeatureVector mFeatVec;

@@ -11,11 +11,13 @@
 #include <cstring>
 #include <limits>
 
+extern "C" void mo_frame_params(const void* fp, float* min_x, float* min_y, float* inv_w, float* inv_h, int* cols, int* rows);
 extern "C" void mo_frame_view(const void* fp, int* n, const uint8_t** desc, const float** x, const float** y, const int** octave, const float** angle);
 
 namespace cslam {
 float Frame::fx = 1.f, Frame::fy = 1.f, Frame::cx = 0.f, Frame::cy = 0.f;
 float Frame::mnMinX = -1e30f, Frame::mnMaxX = 1e30f, Frame::mnMinY = -1e30f, Frame::mnMaxY = 1e30f;
+float Frame::mfGridElementWidthInv = 0.f, Frame::mfGridElementHeightInv = 0.f;
 }
 
 namespace {
@@ -43,6 +45,12 @@ void make_frame(Frame& F, const void* fp, const float* sf, int nlevels) {
     fill_common(fp, F.N, F.mvKeysUn, F.mDescriptors);
     F.mvKeys = F.mvKeysUn;
     F.grid = const_cast<void*>(fp);
+    {   /* static image bounds / grid pitch as Frame.cpp:80-88 would set them for this grid */
+        float mx, my, iw, ih; int gc, gr;
+        mo_frame_params(fp, &mx, &my, &iw, &ih, &gc, &gr);
+        Frame::mnMinX = mx; Frame::mnMinY = my; Frame::mnMaxX = mx + (float)gc / iw; Frame::mnMaxY = my + (float)gr / ih;
+        Frame::mfGridElementWidthInv = iw; Frame::mfGridElementHeightInv = ih;
+    }
     F.mvpMapPoints.assign(F.N, mpptr());
     F.mvbOutlier.assign(F.N, false);
     F.mTcw = cv::Mat::eye(4, 4, CV_32F);
@@ -54,6 +62,12 @@ kfptr make_kf(const void* fp, const float* sf, int nlevels) {
     fill_common(fp, K->N, K->mvKeysUn, K->mDescriptors);
     K->grid = const_cast<void*>(fp);
     K->mvpMapPoints.assign(K->N, mpptr());
+    {
+        float mx, my, iw, ih; int gc, gr;
+        mo_frame_params(fp, &mx, &my, &iw, &ih, &gc, &gr);
+        K->mnMinX = (int)mx; K->mnMinY = (int)my; K->mnMaxX = (int)(mx + (float)gc / iw); K->mnMaxY = (int)(my + (float)gr / ih);
+        K->mnGridCols = gc; K->mnGridRows = gr; K->mfGridElementWidthInv = iw; K->mfGridElementHeightInv = ih;
+    }
     K->minX = K->minY = -1e30f; K->maxX = K->maxY = 1e30f;
     K->R = cv::Mat::eye(3, 3, CV_32F); K->t = vec3(0, 0, 0); K->C = vec3(0, 0, 0);
     if (sf) K->mvScaleFactors.assign(sf, sf + nlevels);

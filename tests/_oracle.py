@@ -305,12 +305,17 @@ def ref_match_available():
     return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_match.so"))
 
 
+def dropin_match_available():
+    """oracle/_ref/libdropin_match.so: the product's drop-in ORBmatcher bodies behind the reference glue."""
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libdropin_match.so"))
+
+
 class RefMatcher:
     """Same array interface as OracleMatcher, executed by the reference's ORBmatcher methods. `F` arguments are
     OracleFrame objects whose handles must come from the SAME library (pass lib=self.L to OracleFrame)."""
 
-    def __init__(self, nnratio=0.6, checkOri=True):
-        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", "libref_match.so"))
+    def __init__(self, nnratio=0.6, checkOri=True, lib="libref_match.so"):
+        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", lib))
         L.mo_frame_create.restype = _vp
         L.mo_frame_create.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _c.c_float, _c.c_float, _i, _i]
         L.mo_frame_destroy.argtypes = [_vp]

@@ -326,3 +326,79 @@ def test_extractor_to_matcher_zero_copy_batch(gm):
         assert nm[j] == nm_c and np.array_equal(holder[j, :n[j + 1]], hc)
         assert nm_c > 300, nm_c        # consecutive frames of the stream really match
     ex.close()
+
+
+def test_dropin_cpp_matcher_matches_reference_class(cuda_lib):
+    """The drop-in C++ ORBmatcher bodies (motioncheck_ccm_slam_b200/host/ORBmatcher.cpp, compiled against the
+    reference's own <cslam/ORBmatcher.h>) and the reference's ORBmatcher.cpp, both driven through the same glue with
+    Frame / KeyFrame / MapPoint objects: identical object state after every converted method. Built only where
+    /root/reference exists; the prebuilt libraries travel to the GPU box."""
+    import _oracle
+    if not (_oracle.dropin_match_available() and _oracle.ref_match_available()):
+        pytest.skip("oracle/_ref/libdropin_match.so not built (needs the reference headers at build time)")
+    from motioncheck_ccm_slam_b200.matcher import frame_grid
+    from motioncheck_ccm_slam_b200.synth import bow_node_ids
+    grid = frame_grid(W, H)
+
+    def pair(nnratio, ori):
+        return _oracle.RefMatcher(nnratio, ori, lib="libdropin_match.so"), _oracle.RefMatcher(nnratio, ori)
+
+    def inb(u, v, valid):
+        return valid & ((u >= 0) & (u <= W) & (v >= 0) & (v <= H)).astype(np.uint8)
+
+    for seed, th, nnratio in [(21, 1.0, 0.8), (22, 5.0, 0.8), (24, 12.0, 0.9)]:
+        rng = np.random.default_rng(seed)
+        a, b, src = _frames(seed)
+        valid, u, v, level, obs = _projection_inputs(a, b, src, rng)
+        viewcos = rng.choice([0.9, 0.9985, 0.998, 0.99801], len(u)).astype(np.float32)
+        holder0 = rng.choice([-1, -1, -1, -2, -3], len(b["x"])).astype(np.int32)
+        D, R = pair(nnratio, True)
+        hd, hr = holder0.copy(), holder0.copy()
+        nd = D.projection_mappoints(D.frame(b, grid), valid, u, v, level, viewcos, a["desc"], obs, th, SF, hd)
+        nr = R.projection_mappoints(R.frame(b, grid), valid, u, v, level, viewcos, a["desc"], obs, th, SF, hr)
+        assert nd == nr > 200 and np.array_equal(hd, hr)
+    for seed, th, ori in [(31, 7.0, True), (32, 14.0, True), (33, 7.0, False)]:
+        rng = np.random.default_rng(seed)
+        a, b, src = _frames(seed)
+        valid, u, v, _, obs = _projection_inputs(a, b, src, rng)
+        valid = inb(u, v, valid)
+        holder0 = rng.choice([-1, -1, -1, -1, -2, -3], len(b["x"])).astype(np.int32)
+        D, R = pair(0.9, ori)
+        hd, hr = holder0.copy(), holder0.copy()
+        nd = D.projection_lastframe(D.frame(b, grid), valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hd)
+        nr = R.projection_lastframe(R.frame(b, grid), valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hr)
+        assert nd == nr > 200 and np.array_equal(hd, hr)
+    for seed, th in [(41, 10), (42, 4)]:
+        rng = np.random.default_rng(seed)
+        a, b, src = _frames(seed, n=3000)
+        valid, u, v, level, claims = _projection_inputs(a, b, src, rng)
+        holder0 = rng.choice([-1, -1, -1, -2], len(b["x"])).astype(np.int32)
+        D, R = pair(0.75, True)
+        hd, hr = holder0.copy(), holder0.copy()
+        nd = D.projection_kf_sim3(D.frame(b, grid), valid, u, v, level, a["desc"], claims, th, SF, hd)
+        nr = R.projection_kf_sim3(R.frame(b, grid), valid, u, v, level, a["desc"], claims, th, SF, hr)
+        assert nd == nr > 100 and np.array_equal(hd, hr)
+    for seed, window, ori in [(71, 100, True), (73, 100, False)]:
+        a, b, src = _frames(seed, n=2000, motion=(6.0, -3.0))
+        D, R = pair(0.9, ori)
+        pd_, pr = np.stack([a["x"], a["y"]], 1).astype(np.float32).copy(), np.stack([a["x"], a["y"]], 1).astype(np.float32).copy()
+        nd, md = D.search_for_initialization(a["desc"], a["octave"], a["angle"], pd_, D.frame(b, grid), window)
+        nr, mr = R.search_for_initialization(a["desc"], a["octave"], a["angle"], pr, R.frame(b, grid), window)
+        assert nd == nr > 50 and np.array_equal(md, mr) and np.array_equal(pd_, pr)
+    for seed, nnratio, ori, n_nodes in [(81, 0.7, True, 1000), (82, 0.75, False, 100)]:
+        rng = np.random.default_rng(seed)
+        a, b, src = _frames(seed, flip_prob=0.03)
+        na, nb = bow_node_ids(a["desc"], n_nodes), bow_node_ids(b["desc"], n_nodes)
+        na[rng.random(len(na)) < 0.05] = -1; nb[rng.random(len(nb)) < 0.05] = -1
+        va = (rng.random(len(na)) < 0.8).astype(np.uint8); vb = (rng.random(len(nb)) < 0.8).astype(np.uint8)
+        D, R = pair(nnratio, ori)
+        nd, md = D.bow_kf_frame(a["desc"], na, va, a["angle"], b["desc"], nb, b["angle"])
+        nr, mr = R.bow_kf_frame(a["desc"], na, va, a["angle"], b["desc"], nb, b["angle"])
+        assert nd == nr > 20 and np.array_equal(md, mr)
+        nd, md = D.bow_kf_kf(a["desc"], na, va, a["angle"], b["desc"], nb, vb, b["angle"])
+        nr, mr = R.bow_kf_kf(a["desc"], na, va, a["angle"], b["desc"], nb, vb, b["angle"])
+        assert nd == nr > 10 and np.array_equal(md, mr)
+    rng = np.random.default_rng(5)
+    x = rng.integers(0, 256, (64, 32), dtype=np.uint8); y = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    D, R = pair(0.6, True)
+    assert np.array_equal(D.descriptor_distance(x, y), R.descriptor_distance(x, y))

@@ -32,6 +32,8 @@ def _inputs(a, b, src, rng):
     level = np.where(inv >= 0, b["octave"][np.maximum(inv, 0)], a["octave"]).astype(np.int32)
     level = np.clip(level + rng.choice([0, 0, 0, 1], n), 0, 7).astype(np.int32)
     valid = (rng.random(n) < 0.9).astype(np.uint8)
+    # projections outside the image bounds are host-side `continue`s of the reference (ORBmatcher.cpp:1393-1396): not valid
+    valid &= ((u >= 0) & (u <= W) & (v >= 0) & (v <= H)).astype(np.uint8)
     obs = (rng.random(n) < 0.8).astype(np.uint8)
     return valid, u, v, level, obs
 
