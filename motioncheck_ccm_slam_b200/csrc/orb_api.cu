@@ -37,7 +37,8 @@ struct ccm_orb {
     ccm_keypoint* h_kp = nullptr; uint8_t* h_desc = nullptr; int* h_n = nullptr;
     cudaStream_t stream = nullptr;
     // host entry point: copy-in / compute / copy-out overlap over sub-batches ("chunks") of one call
-    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaStream_t s_in = nullptr, s_out = nullptr, s_aux = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_in[CCM_MAX_CHUNKS] = {}, ev_done[CCM_MAX_CHUNKS] = {}, ev_out[CCM_MAX_CHUNKS] = {};
     long long launches = 0;
     // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
@@ -235,15 +236,25 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         h->launches++;
     }
     if (st) CK(cudaEventRecord(h->ev[1], s));
+    // The blur depends only on the pyramid. Outside stage-timing mode it runs on a side stream next to FAST + quadtree
+    // (all three are latency/ALU-bound and leave issue slots free) and joins before the descriptor stage.
+    const bool fork = !st;
+    if (fork) {
+        CK(cudaEventRecord(h->ev_fork, s));
+        CK(cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
+        k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, h->s_aux>>>(T);
+        CK(cudaEventRecord(h->ev_join, h->s_aux));
+    }
     k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_cell_info, A.corners, A.corner_count);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[2], s));
-    k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+    if (!fork) k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[3], s));
     k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, A.corners, A.corner_count, A.node_of,
                                                           A.level_kps, A.level_kp_count);
     h->launches++;
+    if (fork) CK(cudaStreamWaitEvent(s, h->ev_join, 0));
     if (st) CK(cudaEventRecord(h->ev[4], s));
     k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, A.level_kps, A.level_kp_count,
                                                                         (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
@@ -291,7 +302,10 @@ int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
     if ((e = cudaSetDevice(cfg->device)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     if ((e = cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+        (e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&h->s_aux, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     for (int i = 0; i < CCM_MAX_CHUNKS; i++)
         if ((e = cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)) != cudaSuccess ||
             (e = cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming)) != cudaSuccess ||
@@ -313,6 +327,9 @@ void ccm_orb_destroy(ccm_orb* h) {
         if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
         if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
     }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    if (h->s_aux) cudaStreamDestroy(h->s_aux);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->stream) cudaStreamDestroy(h->stream);
