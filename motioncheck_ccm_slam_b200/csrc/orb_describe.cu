@@ -96,7 +96,10 @@ struct BriefPattern { signed char v[256][4]; };
 __constant__ BriefPattern c_pattern_init = {{
 #include "brief_pattern.inc"
 }};
-__constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};   // :623-638 for HALF_PATCH_SIZE 15
+// umax[v] of the 15-px orientation patch, ORBextractor.cpp:623-638: {15,15,15,15,14,14,14,13,13,12,11,10,9,8,6,3}
+__host__ __device__ constexpr int umax_of(int v) {
+    return v <= 3 ? 15 : v <= 6 ? 14 : v <= 8 ? 13 : v == 9 ? 12 : v == 10 ? 11 : v == 11 ? 10 : v == 12 ? 9 : v == 13 ? 8 : v == 14 ? 6 : 3;
+}
 
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     // OpenCV atan2_p1..p7: float(coef) * float(180/pi), evaluated in float
@@ -153,14 +156,18 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
 
     // --- orientation ---
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride + (size_t)ky * L.img_pitch + kx;
+    // rows +v and -v share |u| <= umax[v] (:80-92); fully unrolled so that all 31 row loads of a lane are in flight at once
     int m10 = 0, m01 = 0;
     const int u = lane - CCM_HALF_PATCH;
-#pragma unroll 1
-    for (int v = -CCM_HALF_PATCH; v <= CCM_HALF_PATCH; v++) {
-        if (lane < 31 && abs(u) <= c_umax[abs(v)]) {
-            const int val = img[v * L.img_pitch + u];
-            m10 += u * val;
-            m01 += v * val;
+    const int au = abs(u);
+    const uint8_t* __restrict__ pc = img + u;
+    if (lane < 31) m10 = u * (int)pc[0];
+#pragma unroll
+    for (int v = 1; v <= CCM_HALF_PATCH; v++) {
+        if (lane < 31 && au <= umax_of(v)) {
+            const int vp = pc[v * L.img_pitch], vm = pc[-v * L.img_pitch];
+            m10 += u * (vp + vm);
+            m01 += v * (vp - vm);
         }
     }
 #pragma unroll
