@@ -271,13 +271,17 @@ static int fill_params(ccm_matcher* m, const ccm_window_params* prm, WindowParam
 }
 
 // scratch of one job, carved from MB_SCRATCH: head[cap] claim0[qs] claim1[qs] qbest[3*qs]
-static size_t job_scratch_ints(int cap, int qs) { return (size_t)cap + 5 * (size_t)qs + 16; }
+static size_t job_scratch_ints(int cap, int qs) { return (size_t)cap + (7 + 2 * WIN_TOPK) * (size_t)qs + 32; }
 
 static void carve_job(WindowJob& J, int* s, int cap, int qs) {
     J.head = s; s += cap;
     J.claim[0] = s; s += qs;
     J.claim[1] = s; s += qs;
-    J.qbest = s;
+    J.qbest = s; s += 3 * (size_t)qs;
+    J.total = s; s += qs;
+    J.fb = s; s += qs;
+    s += ((uintptr_t)s & 4) ? 1 : 0;            // 8-byte alignment for the keys
+    J.keys = (unsigned long long*)s;
 }
 
 int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs, int n_jobs, const ccm_window_params* prm,
@@ -315,7 +319,11 @@ int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs,
     }
     // pageable -> device copy is staged by the runtime before it returns, so `jobs` may die at scope exit
     MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(WindowJob) * n_jobs, cudaMemcpyHostToDevice, m->stream));
-    k_window_search<<<n_jobs, WIN_THREADS, 0, m->stream>>>(djobs, P);
+    if (P.mode != CCM_WIN_INIT) {
+        k_window_eval<<<dim3((q_stride + 7) / 8, n_jobs), 256, 0, m->stream>>>(djobs, P);
+        m->launches++;
+    }
+    k_window_resolve<<<n_jobs, WIN_THREADS, 0, m->stream>>>(djobs, P);
     m->launches++;
     MCK(cudaGetLastError());
     return CCM_OK;

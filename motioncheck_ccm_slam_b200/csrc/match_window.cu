@@ -15,6 +15,11 @@
 // map in parallel until the claim vector stops changing (after k rounds the first k queries are final, in practice
 // 2-3 rounds because conflicts are rare). SearchForInitialization's steal-back rule (:487-513) compares distances of
 // earlier claims and is run in query order by one warp instead (it is called a handful of times per session).
+//
+// Two kernels per search: k_window_eval walks the grid ONCE per query, fully parallel over (job, query) warps, under the
+// filters that do not depend on other queries, and keeps the WIN_TOPK best candidate keys plus the candidate count;
+// k_window_resolve (one CTA per job) runs the fixpoint on those keys alone, one thread per query. Only a query that
+// finds too few unblocked keys among a truncated list re-walks the grid (exact, rare).
 #include "match_common.cuh"
 
 #define WIN_THREADS 1024
@@ -26,6 +31,7 @@
 #define WQ_VALID 1u
 #define WQ_BLOCKS 2u
 #define KEY_NONE 0xffffffffffffffffull
+#define WIN_TOPK 4
 
 // ---- frame pack construction ----------------------------------------------------------------------------------
 // ccm_keypoint (AoS, extractor output) -> pack SoA, one CTA per pack; xy_un overrides the positions (mvKeysUn of a
@@ -159,6 +165,64 @@ __device__ __forceinline__ WinEval eval_query(const PackDev& P, const WindowPara
     return e;
 }
 
+// static pass: candidates under the query-independent filters (window, levels, gate, the holder state the call
+// started with), best WIN_TOPK keys in keys[] (ascending, KEY_NONE padded) and the number of candidates that passed
+template <int MODE>
+__device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowParamsDev& prm, const WindowQueryDev& q,
+                                                const uint4 qd0, const uint4 qd1, const int* __restrict__ holder, int lane,
+                                                unsigned long long (&keys)[WIN_TOPK], int& total) {
+    unsigned long long k0 = KEY_NONE, k1 = KEY_NONE, k2 = KEY_NONE, k3 = KEY_NONE;
+    int cnt = 0;
+    const float fx = __fsub_rn(q.u, P.min_x), fy = __fsub_rn(q.v, P.min_y);
+    const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(fx, q.r), P.inv_w)));
+    const int maxCX = min(P.cols - 1, (int)ceilf(__fmul_rn(__fadd_rn(fx, q.r), P.inv_w)));
+    const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(fy, q.r), P.inv_h)));
+    const int maxCY = min(P.rows - 1, (int)ceilf(__fmul_rn(__fadd_rn(fy, q.r), P.inv_h)));
+    if (minCX < P.cols && maxCX >= 0 && minCY < P.rows && maxCY >= 0) {
+        const uint4* __restrict__ desc = reinterpret_cast<const uint4*>(P.desc);
+        int pos_base = 0;
+        for (int ix = minCX; ix <= maxCX; ix++) {
+            const int s = P.cell_start[ix * P.rows + minCY], t = P.cell_start[ix * P.rows + maxCY + 1];
+            for (int p = s + lane; p < t; p += 32) {
+                const int k = P.items[p];
+                const int oct = P.octave[k];
+                if (oct < q.min_level) continue;
+                if (q.max_level >= 0 && oct > q.max_level) continue;
+                const float dx = __fsub_rn(P.x[k], q.u), dy = __fsub_rn(P.y[k], q.v);
+                if (!(fabsf(dx) < q.r && fabsf(dy) < q.r)) continue;
+                if (MODE == WIN_MODE_BEST && prm.use_gate) {
+                    const float ex = __fsub_rn(q.u, P.x[k]), ey = __fsub_rn(q.v, P.y[k]);
+                    const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                    if ((double)__fmul_rn(e2, prm.inv_sigma2[oct]) > 5.99) continue;
+                }
+                if (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) { if (holder[k] == -2) continue; }
+                else if (MODE == WIN_MODE_KF_SIM3) { if (holder[k] != -1) continue; }
+                const int dist = hamming256(qd0, qd1, desc[2 * (size_t)k], desc[2 * (size_t)k + 1]);
+                unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned long long)(pos_base + p - s) << 16) | (unsigned)k;
+                cnt++;
+                if (key < k3) {
+                    k3 = key;
+                    if (k3 < k2) { const unsigned long long t2 = k2; k2 = k3; k3 = t2; }
+                    if (k2 < k1) { const unsigned long long t1 = k1; k1 = k2; k2 = t1; }
+                    if (k1 < k0) { const unsigned long long t0 = k0; k0 = k1; k1 = t0; }
+                }
+            }
+            pos_base += t - s;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < WIN_TOPK; r++) {
+        unsigned long long m = k0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+        keys[r] = m;
+        if (k0 == m && m != KEY_NONE) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY_NONE; }   // keys are unique: one lane pops
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    total = cnt;
+}
+
 template <int MODE>
 __device__ __forceinline__ bool accept_rule(const PackDev& P, const WindowParamsDev& prm, const WinEval& e, int& bestIdx,
                                             int& bestDist, int& bestDist2) {
@@ -186,7 +250,7 @@ __device__ __forceinline__ bool accept_rule(const PackDev& P, const WindowParams
 
 template <int MODE>
 __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
-    __shared__ int s_changed, s_nm, s_hist[32], s_keep[3];
+    __shared__ int s_nfb, s_nm, s_hist[32], s_keep[3];
     const PackDev& P = J.pack;
     const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
     const int n = min(*P.n, P.cap);
@@ -215,15 +279,44 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
             __syncthreads();
         }
         int changed = 0;
-        for (int i = wid; i < nq; i += nw) {
+        if (threadIdx.x == 0) s_nfb = 0;
+        __syncthreads();
+        // one thread per query, from the keys k_window_eval stored
+        for (int i = threadIdx.x; i < nq; i += blockDim.x) {
+            const WindowQueryDev q = J.q[i];
+            WinEval e; e.b1 = KEY_NONE; e.b2 = KEY_NONE;
+            bool fallback = false;
+            if (q.flags & WQ_VALID) {
+                const int total = J.total[i];
+                const int have = min(total, WIN_TOPK);
+                int found = 0;
+                for (int r = 0; r < have; r++) {
+                    const unsigned long long key = J.keys[(size_t)WIN_TOPK * i + r];
+                    if (stateful && minclaim[(int)(key & 0xffff)] < i) continue;
+                    if (found == 0) e.b1 = key; else { e.b2 = key; }
+                    if (++found == 2) break;
+                }
+                const int need = (MODE == WIN_MODE_MAPPOINTS) ? 2 : 1;
+                fallback = found < need && total > WIN_TOPK;
+            }
+            if (fallback) { J.fb[atomicAdd(&s_nfb, 1)] = i; continue; }
+            int bestIdx, bestDist, bestDist2;
+            const bool acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
+            const int c = acc ? bestIdx : -1;
+            if (c != J.claim[prev][i]) changed = 1;
+            J.claim[cur][i] = c;
+            J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist;
+            J.qbest[3 * i + 2] = (MODE == WIN_MODE_MAPPOINTS) ? bestDist2 : 256;
+        }
+        __syncthreads();
+        // truncated key lists that ran dry: exact re-walk of the grid, one warp per query
+        const int nfb = s_nfb;
+        for (int j = wid; j < nfb; j += nw) {
+            const int i = J.fb[j];
             const WindowQueryDev q = J.q[i];
             int bestIdx = -1, bestDist = 256, bestDist2 = 256;
-            bool acc = false;
-            if (q.flags & WQ_VALID) {
-                const WinEval e = eval_query<MODE>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i, J.holder,
-                                                   minclaim, nullptr, lane);
-                acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
-            }
+            const WinEval e = eval_query<MODE>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i, J.holder, minclaim, nullptr, lane);
+            const bool acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
             if (lane == 0) {
                 const int c = acc ? bestIdx : -1;
                 if (c != J.claim[prev][i]) changed = 1;
@@ -336,7 +429,38 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
     if (threadIdx.x == 0) *J.nmatches = s_nm;
 }
 
-__global__ void __launch_bounds__(WIN_THREADS) k_window_search(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
+template <int MODE>
+__device__ __forceinline__ void window_eval_job(const WindowJob& J, const WindowParamsDev& prm, int i, int lane) {
+    const WindowQueryDev q = J.q[i];
+    unsigned long long keys[WIN_TOPK];
+    int total = 0;
+    if (q.flags & WQ_VALID) {
+        const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
+        eval_query_topk<MODE>(J.pack, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], J.holder, lane, keys, total);
+    } else {
+#pragma unroll
+        for (int r = 0; r < WIN_TOPK; r++) keys[r] = KEY_NONE;
+    }
+#pragma unroll
+    for (int r = 0; r < WIN_TOPK; r++) if (lane == r) J.keys[(size_t)WIN_TOPK * i + r] = keys[r];
+    if (lane == 0) J.total[i] = total;
+}
+
+// grid (query groups of 8, jobs); warp = one query of one job. Not used by CCM_WIN_INIT.
+__global__ void __launch_bounds__(256) k_window_eval(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
+    const WindowJob& J = jobs[blockIdx.y];
+    const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= nq) return;
+    switch (prm.mode) {
+        case WIN_MODE_MAPPOINTS: window_eval_job<WIN_MODE_MAPPOINTS>(J, prm, i, lane); break;
+        case WIN_MODE_LASTFRAME: window_eval_job<WIN_MODE_LASTFRAME>(J, prm, i, lane); break;
+        case WIN_MODE_KF_SIM3: window_eval_job<WIN_MODE_KF_SIM3>(J, prm, i, lane); break;
+        default: window_eval_job<WIN_MODE_BEST>(J, prm, i, lane); break;
+    }
+}
+
+__global__ void __launch_bounds__(WIN_THREADS) k_window_resolve(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
     const WindowJob J = jobs[blockIdx.x];
     switch (prm.mode) {
         case WIN_MODE_MAPPOINTS: window_job<WIN_MODE_MAPPOINTS>(J, prm); break;
