@@ -39,6 +39,7 @@ struct ccm_orb {
     // host entry point: copy-in / compute / copy-out overlap over sub-batches ("chunks") of one call
     cudaStream_t s_in = nullptr, s_out = nullptr, s_aux = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    uint8_t* d_stage = nullptr; size_t stage_bytes = 0;   // host entry point: staging for rows that are not 4-byte multiples
     cudaEvent_t ev_in[CCM_MAX_CHUNKS] = {}, ev_done[CCM_MAX_CHUNKS] = {}, ev_out[CCM_MAX_CHUNKS] = {};
     long long launches = 0;
     // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
@@ -327,6 +328,7 @@ void ccm_orb_destroy(ccm_orb* h) {
         if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
         if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
     }
+    if (h->d_stage) cudaFree(h->d_stage);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->s_aux) cudaStreamDestroy(h->s_aux);
@@ -410,6 +412,14 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     const size_t budget = (size_t)align_up(cols, 32);
     const bool flat = (step % 4 == 0) && step <= budget;
     const size_t pitch = flat ? step : budget, stride = budget * rows;
+    const size_t frame_bytes = step * (size_t)rows;
+    if (!flat && h->stage_bytes < frame_bytes * h->cfg.max_batch) {
+        CK(cudaStreamSynchronize(h->s_in));
+        if (h->d_stage) cudaFree(h->d_stage);
+        h->d_stage = nullptr; h->stage_bytes = 0;
+        CK(cudaMalloc((void**)&h->d_stage, frame_bytes * h->cfg.max_batch));
+        h->stage_bytes = frame_bytes * h->cfg.max_batch;
+    }
     const int cap = h->max_kps;
     int n_chunks = n <= 8 ? 1 : std::min(CCM_MAX_CHUNKS, std::min(4, n / 4));
     const int per = (n + n_chunks - 1) / n_chunks;
@@ -420,7 +430,13 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
         const int f0 = c * per, m = std::min(per, n - f0);
         for (int f = f0; f < f0 + m; f++) {
             if (flat) CK(cudaMemcpyAsync(l0 + f * stride, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
-            else CK(cudaMemcpy2DAsync(l0 + f * stride, pitch, imgs[f], step, cols, rows, cudaMemcpyHostToDevice, h->s_in));
+            else {
+                // rows that are not 4-byte multiples: one contiguous host->device copy into a staging area, then a
+                // device-side pitched copy (a pitched host->device copy runs at a fraction of the link rate)
+                uint8_t* st = h->d_stage + (size_t)f * frame_bytes;
+                CK(cudaMemcpyAsync(st, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
+                CK(cudaMemcpy2DAsync(l0 + f * stride, pitch, st, step, cols, rows, cudaMemcpyDeviceToDevice, h->s_in));
+            }
         }
         CK(cudaEventRecord(h->ev_in[c], h->s_in));
         CK(cudaStreamWaitEvent(h->stream, h->ev_in[c], 0));

@@ -27,7 +27,9 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint3
     uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
     if (lane == 0 && x0 > 0) prev = *reinterpret_cast<const uint32_t*>(row + x - 4);
     if (lane == 31 && x + 4 < w) next = *reinterpret_cast<const uint32_t*>(row + x + 4);
-    if ((x - 3 < 0 || x + 6 >= w) && x < w) {          // lanes touching the reflected border: gather bytes x-4..x+7
+    if (x == 0 && 10 <= w) {
+        prev = __byte_perm(own, 0u, 0x1230);          // reflect-101 on the left: pixels -3,-2,-1 are pixels 3,2,1 of this word
+    } else if ((x - 3 < 0 || x + 6 >= w) && x < w) {   // lanes touching the right border: gather bytes x-4..x+7
         uint32_t wd[3] = {0u, 0u, 0u};
 #pragma unroll
         for (int k = 0; k < 12; k++) wd[k >> 2] |= (uint32_t)row[ccm_reflect101(min(x - 4 + k, w + 2), w)] << (8 * (k & 3));
