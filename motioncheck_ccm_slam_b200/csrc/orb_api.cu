@@ -237,24 +237,27 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         h->launches++;
     }
     if (st) CK(cudaEventRecord(h->ev[1], s));
-    // The blur depends only on the pyramid. Outside stage-timing mode it runs on a side stream next to FAST + quadtree
-    // (all three are latency/ALU-bound and leave issue slots free) and joins before the descriptor stage.
+    // The blur depends only on the pyramid; the quadtree is one small CTA per (frame, level) and latency-bound. Outside
+    // stage-timing mode the blur runs on a side stream next to the quadtree and joins before the descriptor stage.
     const bool fork = !st;
-    if (fork) {
-        CK(cudaEventRecord(h->ev_fork, s));
-        CK(cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
-        k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, h->s_aux>>>(T);
-        CK(cudaEventRecord(h->ev_join, h->s_aux));
-    }
     k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_cell_info, A.corners, A.corner_count);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[2], s));
-    if (!fork) k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
-    h->launches++;
+    if (fork) CK(cudaEventRecord(h->ev_fork, s));
+    if (!fork) {
+        k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+        h->launches++;
+    }
     if (st) CK(cudaEventRecord(h->ev[3], s));
     k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, A.corners, A.corner_count, A.node_of,
                                                           A.level_kps, A.level_kp_count);
     h->launches++;
+    if (fork) {
+        CK(cudaStreamWaitEvent(h->s_aux, h->ev_fork, 0));
+        k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, h->s_aux>>>(T);
+        h->launches++;
+        CK(cudaEventRecord(h->ev_join, h->s_aux));
+    }
     if (fork) CK(cudaStreamWaitEvent(s, h->ev_join, 0));
     if (st) CK(cudaEventRecord(h->ev[4], s));
     k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, A.level_kps, A.level_kp_count,
