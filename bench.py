@@ -455,7 +455,9 @@ def run_ours(args, wl, rank, world, local_rank):
     tp = os.path.join(ROOT, "profiles", "traffic.json")   # dram bytes per launch from the committed ncu --set full capture
     if os.path.exists(tp):
         with open(tp) as f:
-            traffic = json.load(f).get(STAGES[dom])
+            tj = json.load(f)
+        if tj.get("workload") == args.workload and tj.get("frames_per_launch") == B:   # only for the captured configuration
+            traffic = tj["bytes"].get(STAGES[dom])
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,

@@ -7,8 +7,9 @@
 //
 // Converted here: DescriptorDistance, SearchByProjection(Frame, MapPoints), SearchByProjection(Frame, LastFrame),
 // SearchByProjection(KeyFrame, Scw), SearchByBoW(KeyFrame, Frame), SearchByBoW(KeyFrame, KeyFrame),
-// SearchForInitialization. SearchBySim3 / Fuse (distance phase = CCM_WIN_BEST) and
-// SearchForTriangulation keep their upstream bodies this round. A CUDA failure throws estd::infrastructure_ex (the
+// SearchForInitialization, SearchBySim3 and both Fuse overloads (candidate search on the device, CCM_WIN_BEST; the map
+// mutations are replayed on the host in the reference's order). SearchForTriangulation and the caller-less
+// relocalisation SearchByProjection keep their upstream bodies this round. A CUDA failure throws estd::infrastructure_ex (the
 // reference's fatal-error convention, estd.h:74); there is no CPU fallback.
 #include <cslam/ORBmatcher.h>
 
@@ -63,10 +64,10 @@ struct Pack {
 inline ccm_window_query no_query() { ccm_window_query q; std::memset(&q, 0, sizeof(q)); return q; }
 
 void run_window(ccm_matcher* m, ccm_frame_pack* pack, int mode, float nnratio, int th_dist, bool ori, std::vector<ccm_window_query>& q,
-                std::vector<uint8_t>& qd, int* holder, ccm_match_result* res, int& nmatches) {
+                std::vector<uint8_t>& qd, int* holder, ccm_match_result* res, int& nmatches, const std::vector<float>* inv_sigma2 = nullptr) {
     ccm_window_params prm;
     prm.mode = mode; prm.nnratio = nnratio; prm.th_dist = th_dist; prm.check_orientation = ori ? 1 : 0;
-    prm.inv_sigma2 = nullptr; prm.n_levels = 0;
+    prm.inv_sigma2 = inv_sigma2 ? inv_sigma2->data() : nullptr; prm.n_levels = inv_sigma2 ? (int)inv_sigma2->size() : 0;
     nmatches = 0;
     if (q.empty()) return;
     if (ccm_search_window(m, pack, &prm, (int)q.size(), q.data(), qd.data(), holder, res, &nmatches) != CCM_OK)
@@ -327,6 +328,210 @@ int ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f
     for (int i1 = 0; i1 < n1; i1++)
         if (vnMatches12[i1] >= 0) vbPrevMatched[i1] = F2.mvKeysUn[vnMatches12[i1]].pt;   // :558-560
     return nmatches;
+}
+
+}  // namespace cslam
+
+// ---------------------------------------------------------------------------------------------------------------
+// Fuse and SearchBySim3: the candidate search of every map point is independent of the map mutations the reference
+// interleaves with it (the distance loops never consult map points), so all searches of a call run as one
+// CCM_WIN_BEST batch and the mutations are replayed afterwards in the reference's order, re-checking the conditions a
+// mutation can change (isBad, IsInKeyFrame) at replay time.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+struct KfPack {
+    Pack pack;
+    KfPack(ccm_matcher* m, const boost::shared_ptr<cslam::KeyFrame>& k)
+        : pack(m, k->N, k->mDescriptors, k->mvKeysUn, (float)k->mnMinX, (float)k->mnMinY, k->mfGridElementWidthInv,
+               k->mfGridElementHeightInv, k->mnGridCols, k->mnGridRows) {}
+};
+inline void set_query(ccm_window_query& q, float u, float v, float r, int lvl) {
+    q.u = u; q.v = v; q.r = r; q.min_level = (int16_t)(lvl - 1); q.max_level = (int16_t)lvl; q.flags = CCM_Q_VALID;
+}
+}  // namespace
+
+namespace cslam {
+
+// ORBmatcher.cpp:854-993
+int ORBmatcher::Fuse(kfptr pKF, const vector<mpptr> &vpMapPoints, const float th) {
+    cv::Mat Rcw = pKF->GetRotation(), tcw = pKF->GetTranslation();
+    const float &fx = pKF->fx, &fy = pKF->fy, &cx = pKF->cx, &cy = pKF->cy;
+    cv::Mat Ow = pKF->GetCameraCenter();
+    const int nMPs = (int)vpMapPoints.size();
+    std::vector<ccm_window_query> q(nMPs, no_query());
+    std::vector<uint8_t> qd((size_t)nMPs * 32 + 32);
+    for (int i = 0; i < nMPs; i++) {
+        mpptr pMP = vpMapPoints[i];
+        if (!pMP) continue;
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+        if (pMP->mbDoNotReplace) continue;
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.at<float>(2) < 0.0f) continue;
+        const float invz = 1 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz, y = p3Dc.at<float>(1) * invz;
+        const float u = fx * x + cx, v = fy * y + cy;
+        if (!pKF->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        cv::Mat PO = p3Dw - Ow;
+        const float dist3D = cv::norm(PO);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (PO.dot(Pn) < 0.5 * dist3D) continue;
+        const int lvl = pMP->PredictScale(dist3D, pKF);
+        set_query(q[i], u, v, th * pKF->mvScaleFactors[lvl], lvl);
+        std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+    }
+    std::vector<ccm_match_result> res(nMPs > 0 ? nMPs : 1);
+    {
+        Device& D = device();
+        std::lock_guard<std::mutex> g(D.mu);
+        KfPack kp(D.m, pKF);
+        int n_acc = 0;
+        run_window(D.m, kp.pack.p, CCM_WIN_BEST, mfNNratio, TH_LOW, false, q, qd, nullptr, res.data(), n_acc, &pKF->mvInvLevelSigma2);
+    }
+    int nFused = 0;
+    for (int i = 0; i < nMPs; i++) {
+        if (!(q[i].flags & CCM_Q_VALID) || !res[i].accepted) continue;
+        mpptr pMP = vpMapPoints[i];
+        if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;      // an earlier replacement / observation of this call
+        const int bestIdx = res[i].best_idx;
+        mpptr pMPinKF = pKF->GetMapPoint(bestIdx);
+        if (pMPinKF) {
+            if (!pMPinKF->isBad() && !pMPinKF->mbDoNotReplace) {
+                if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                else pMPinKF->Replace(pMP);
+            }
+        } else {
+            pMP->AddObservation(pKF, bestIdx);
+            pKF->AddMapPoint(pMP, bestIdx);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
+// ORBmatcher.cpp:995-1122
+int ORBmatcher::Fuse(kfptr pKF, cv::Mat Scw, const vector<mpptr> &vpPoints, float th, vector<mpptr> &vpReplacePoint) {
+    const float &fx = pKF->fx, &fy = pKF->fy, &cx = pKF->cx, &cy = pKF->cy;
+    cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+    const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+    cv::Mat Rcw = sRcw / scw;
+    cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+    cv::Mat Ow = -Rcw.t() * tcw;
+    const set<mpptr> spAlreadyFound = pKF->GetMapPoints();
+    const int nPoints = (int)vpPoints.size();
+    std::vector<ccm_window_query> q(nPoints, no_query());
+    std::vector<uint8_t> qd((size_t)nPoints * 32 + 32);
+    for (int i = 0; i < nPoints; i++) {
+        mpptr pMP = vpPoints[i];
+        if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+        cv::Mat p3Dw = pMP->GetWorldPos();
+        cv::Mat p3Dc = Rcw * p3Dw + tcw;
+        if (p3Dc.at<float>(2) < 0.0f) continue;
+        const float invz = 1.0 / p3Dc.at<float>(2);
+        const float x = p3Dc.at<float>(0) * invz, y = p3Dc.at<float>(1) * invz;
+        const float u = fx * x + cx, v = fy * y + cy;
+        if (!pKF->IsInImage(u, v)) continue;
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        cv::Mat PO = p3Dw - Ow;
+        const float dist3D = cv::norm(PO);
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        cv::Mat Pn = pMP->GetNormal();
+        if (PO.dot(Pn) < 0.5 * dist3D) continue;
+        const int lvl = pMP->PredictScale(dist3D, pKF);
+        set_query(q[i], u, v, th * pKF->mvScaleFactors[lvl], lvl);
+        std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+    }
+    std::vector<ccm_match_result> res(nPoints > 0 ? nPoints : 1);
+    {
+        Device& D = device();
+        std::lock_guard<std::mutex> g(D.mu);
+        KfPack kp(D.m, pKF);
+        int n_acc = 0;
+        run_window(D.m, kp.pack.p, CCM_WIN_BEST, mfNNratio, TH_LOW, false, q, qd, nullptr, res.data(), n_acc);
+    }
+    int nFused = 0;
+    for (int i = 0; i < nPoints; i++) {
+        if (!(q[i].flags & CCM_Q_VALID) || !res[i].accepted) continue;
+        mpptr pMP = vpPoints[i];
+        const int bestIdx = res[i].best_idx;
+        mpptr pMPinKF = pKF->GetMapPoint(bestIdx);
+        if (pMPinKF) {
+            if (!pMPinKF->isBad()) vpReplacePoint[i] = pMPinKF;
+        } else {
+            pMP->AddObservation(pKF, bestIdx);
+            pKF->AddMapPoint(pMP, bestIdx);
+        }
+        nFused++;
+    }
+    return nFused;
+}
+
+// ORBmatcher.cpp:1124-1348
+int ORBmatcher::SearchBySim3(kfptr pKF1, kfptr pKF2, vector<mpptr> &vpMatches12, const float &s12, const cv::Mat &R12,
+                             const cv::Mat &t12, const float th) {
+    const float &fx = pKF1->fx, &fy = pKF1->fy, &cx = pKF1->cx, &cy = pKF1->cy;
+    cv::Mat R1w = pKF1->GetRotation(), t1w = pKF1->GetTranslation();
+    cv::Mat R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+    cv::Mat sR12 = s12 * R12;
+    cv::Mat sR21 = (1.0 / s12) * R12.t();
+    cv::Mat t21 = -sR21 * t12;
+    const vector<mpptr> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+    const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+    vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+    for (int i = 0; i < N1; i++) {
+        mpptr pMP = vpMatches12[i];
+        if (pMP) {
+            vbAlreadyMatched1[i] = true;
+            const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+            if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+        }
+    }
+    // one projection pass per direction: points of `from` through (Rw, tw) then (sR, t) into `to`
+    struct Dir { const vector<mpptr>* pts; const vector<bool>* done; cv::Mat Rw, tw, sR, t; kfptr to; int n; };
+    Dir dirs[2] = {{&vpMapPoints1, &vbAlreadyMatched1, R1w, t1w, sR21, t21, pKF2, N1},
+                   {&vpMapPoints2, &vbAlreadyMatched2, R2w, t2w, sR12, t12, pKF1, N2}};
+    std::vector<int> vnMatch[2];
+    for (int d = 0; d < 2; d++) {
+        const Dir& X = dirs[d];
+        std::vector<ccm_window_query> q(X.n, no_query());
+        std::vector<uint8_t> qd((size_t)X.n * 32 + 32);
+        for (int i = 0; i < X.n; i++) {
+            mpptr pMP = (*X.pts)[i];
+            if (!pMP || (*X.done)[i]) continue;
+            if (pMP->isBad()) continue;
+            cv::Mat p3Dw = pMP->GetWorldPos();
+            cv::Mat pa = X.Rw * p3Dw + X.tw;
+            cv::Mat pb = X.sR * pa + X.t;
+            if (pb.at<float>(2) < 0.0) continue;
+            const float invz = 1.0 / pb.at<float>(2);
+            const float x = pb.at<float>(0) * invz, y = pb.at<float>(1) * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!X.to->IsInImage(u, v)) continue;
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            const float dist3D = cv::norm(pb);
+            if (dist3D < minDistance || dist3D > maxDistance) continue;
+            const int lvl = pMP->PredictScale(dist3D, X.to);
+            set_query(q[i], u, v, th * X.to->mvScaleFactors[lvl], lvl);
+            std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+        }
+        std::vector<ccm_match_result> res(X.n > 0 ? X.n : 1);
+        Device& D = device();
+        std::lock_guard<std::mutex> g(D.mu);
+        KfPack kp(D.m, X.to);
+        int n_acc = 0;
+        run_window(D.m, kp.pack.p, CCM_WIN_BEST, mfNNratio, TH_HIGH, false, q, qd, nullptr, res.data(), n_acc);
+        vnMatch[d].assign(X.n, -1);
+        for (int i = 0; i < X.n; i++)
+            if ((q[i].flags & CCM_Q_VALID) && res[i].accepted) vnMatch[d][i] = res[i].best_idx;
+    }
+    int nFound = 0;
+    for (int i1 = 0; i1 < N1; i1++) {
+        const int idx2 = vnMatch[0][i1];
+        if (idx2 >= 0 && vnMatch[1][idx2] == i1) { vpMatches12[i1] = vpMapPoints2[idx2]; nFound++; }
+    }
+    return nFound;
 }
 
 }  // namespace cslam

@@ -33,7 +33,10 @@ public:
     cv::Mat GetCameraCenter() { return C.clone(); }
     cv::Mat GetRotation() { return R.clone(); }
     cv::Mat GetTranslation() { return t.clone(); }
-    void AddMapPoint(mpptr pMP, const size_t& idx, bool = false) { if (added.size() < (size_t)N) added.assign(N, -1); added[idx] = pMP->id; }
+    void AddMapPoint(mpptr pMP, const size_t& idx, bool = false) {      /* KeyFrame.cpp: mvpMapPoints[idx] = pMP */
+        if (added.size() < (size_t)N) added.assign(N, -1);
+        added[idx] = pMP->id; mvpMapPoints[idx] = pMP;
+    }
     std::set<mpptr> GetMapPoints() { std::set<mpptr> s; for (auto& p : mvpMapPoints) if (p) s.insert(p); return s; }
     std::vector<mpptr> GetMapPointMatches() { return mvpMapPoints; }
     mpptr GetMapPoint(const size_t& idx) { return mvpMapPoints[idx]; }
@@ -45,4 +48,14 @@ public:
     }
     bool IsInImage(const float& x, const float& y) const { return (x >= minX && x < maxX && y >= minY && y < maxY); }
 };
+inline void MapPoint::Replace(mpptr pMP, bool) {
+    if (pMP->id == id) return;
+    replacedBy = pMP->id; bad = true;
+    std::map<KeyFrame*, int> obs; obs.swap(indexInKF);
+    for (auto& o : obs) {
+        if (pMP->indexInKF.count(o.first)) continue;
+        if (o.second >= 0 && o.second < (int)o.first->mvpMapPoints.size()) o.first->mvpMapPoints[o.second] = pMP;
+        pMP->indexInKF[o.first] = o.second; pMP->nObs++;
+    }
+}
 }

@@ -1,5 +1,8 @@
 /* TEST INFRASTRUCTURE — mock of cslam::MapPoint with the members cslam/src/ORBmatcher.cpp reads (MapPoint.h:134-228).
- * Plain data set by the test glue; graph mutations (AddObservation, Replace) are recorded, not performed. */
+ * Plain data set by the test glue; AddObservation and Replace record their argument and leave the state the real
+ * class leaves that ORBmatcher.cpp can observe afterwards (MapPoint.cpp:417 AddObservation makes IsInKeyFrame true and
+ * counts the observation; MapPoint.cpp:583-612 Replace marks the replaced point bad and moves its observations, and
+ * the keyframes' slots, to the survivor — the common branch where the survivor does not observe that keyframe yet). */
 #pragma once
 #include <map>
 #include <memory>
@@ -40,7 +43,7 @@ public:
     int PredictScale(const float&, frameptr) { return predictedLevel; }
     int GetIndexInKeyFrame(kfptr pKF, bool = false) { auto it = indexInKF.find(pKF.get()); return it == indexInKF.end() ? -1 : it->second; }
     bool IsInKeyFrame(kfptr pKF) { return indexInKF.count(pKF.get()) != 0; }
-    void AddObservation(kfptr, size_t idx, bool = false) { addedObsIdx = (int)idx; }
-    void Replace(mpptr pMP, bool = false) { replacedBy = pMP->id; }
+    void AddObservation(kfptr pKF, size_t idx, bool = false) { addedObsIdx = (int)idx; indexInKF[pKF.get()] = (int)idx; nObs++; }
+    void Replace(mpptr pMP, bool = false);     /* defined in the mock KeyFrame.h (needs the complete KeyFrame) */
 };
 }

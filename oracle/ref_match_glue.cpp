@@ -244,4 +244,107 @@ int rm_search_for_initialization(int n1, const uint8_t* desc1, const int* octave
     return nm;
 }
 
+/* Occupants of a keyframe's feature slots for the Fuse cases: occ_obs[k] < 0 = empty, else a map point with id
+ * OCC_ID + k, that many observations, observed by K at slot k; occ_flags bit0 = bad, bit1 = mbDoNotReplace. */
+static const int OCC_ID = 100000;
+static void make_occupants(kfptr K, const int* occ_obs, const uint8_t* occ_flags) {
+    for (int k = 0; k < K->N; k++) {
+        if (occ_obs[k] < 0) continue;
+        mpptr o = make_mp(OCC_ID + k, nullptr, occ_obs[k]);
+        o->bad = occ_flags[k] & 1; o->mbDoNotReplace = (occ_flags[k] & 2) != 0;
+        o->indexInKF[K.get()] = k;
+        K->mvpMapPoints[k] = o;
+    }
+}
+/* query points: q_alias[i] = j < i shares point j (the same map point listed twice), q_alias[i] = -(k+2) is the
+ * occupant of slot k (a candidate the keyframe already holds), -1 = a fresh point. q_flags bit1 = mbDoNotReplace. */
+static void make_points(kfptr K, int nq, const uint8_t* q_valid, const float* q_u, const float* q_v, const int* q_level,
+                        const uint8_t* q_desc, const int* q_obs, const uint8_t* q_flags, const int* q_alias, std::vector<mpptr>& pts) {
+    pts.resize(nq);
+    for (int i = 0; i < nq; i++) {
+        if (q_alias[i] >= 0 && q_alias[i] < i) { pts[i] = pts[q_alias[i]]; continue; }
+        if (q_alias[i] <= -2 && K->mvpMapPoints[-q_alias[i] - 2]) pts[i] = K->mvpMapPoints[-q_alias[i] - 2];
+        else pts[i] = make_mp(i, nullptr, q_obs[i]);
+        pts[i]->descriptor = desc_mat(q_desc + (size_t)32 * i, 1);
+        if (!q_valid[i]) pts[i]->bad = true;
+        pts[i]->mbDoNotReplace = pts[i]->mbDoNotReplace || (q_flags[i] & 2) != 0;
+        pts[i]->predictedLevel = q_level[i];
+        set_world(pts[i], q_u[i], q_v[i]);
+    }
+}
+static void export_slots(kfptr K, int* slot_id, int* slot_bad) {
+    for (int k = 0; k < K->N; k++) {
+        slot_id[k] = K->mvpMapPoints[k] ? K->mvpMapPoints[k]->id : -1;
+        slot_bad[k] = K->mvpMapPoints[k] ? (int)K->mvpMapPoints[k]->bad : 0;
+    }
+}
+
+/* ORBmatcher::Fuse(kfptr, vpMapPoints, th), ORBmatcher.cpp:854-993. Outputs per query: replaced_by (id of the point it was
+ * replaced by, -1), added_idx (slot it was added to, -1), bad; per slot: id of the final occupant and whether it is bad. */
+int rm_fuse(const void* fp, int nq, const uint8_t* q_valid, const float* q_u, const float* q_v, const int* q_level,
+            const uint8_t* q_desc, const int* q_obs, const uint8_t* q_flags, const int* q_alias, float th,
+            const float* scale_factors, const float* inv_sigma2, const int* occ_obs, const uint8_t* occ_flags,
+            int* replaced_by, int* added_idx, int* q_bad, int* slot_id, int* slot_bad, int* occ_replaced_by) {
+    kfptr K = make_kf(fp, scale_factors, NLEV);
+    K->mvInvLevelSigma2.assign(inv_sigma2, inv_sigma2 + NLEV);
+    make_occupants(K, occ_obs, occ_flags);
+    std::vector<mpptr> occ = K->mvpMapPoints, pts;
+    make_points(K, nq, q_valid, q_u, q_v, q_level, q_desc, q_obs, q_flags, q_alias, pts);
+    ORBmatcher m(0.6f, true);
+    const int nFused = m.Fuse(K, pts, th);
+    for (int i = 0; i < nq; i++) { replaced_by[i] = pts[i]->replacedBy; added_idx[i] = pts[i]->addedObsIdx; q_bad[i] = pts[i]->bad; }
+    export_slots(K, slot_id, slot_bad);
+    for (int k = 0; k < K->N; k++) occ_replaced_by[k] = occ[k] ? occ[k]->replacedBy : -1;
+    return nFused;
+}
+
+/* ORBmatcher::Fuse(kfptr, Scw, vpPoints, th, vpReplacePoint), ORBmatcher.cpp:995-1122 (Scw = identity) */
+int rm_fuse_sim3(const void* fp, int nq, const uint8_t* q_valid, const float* q_u, const float* q_v, const int* q_level,
+                 const uint8_t* q_desc, const int* q_obs, const uint8_t* q_flags, const int* q_alias, float th,
+                 const float* scale_factors, const int* occ_obs, const uint8_t* occ_flags,
+                 int* replace_point, int* added_idx, int* slot_id, int* slot_bad) {
+    kfptr K = make_kf(fp, scale_factors, NLEV);
+    make_occupants(K, occ_obs, occ_flags);
+    std::vector<mpptr> pts, rep(nq);
+    make_points(K, nq, q_valid, q_u, q_v, q_level, q_desc, q_obs, q_flags, q_alias, pts);
+    ORBmatcher m(0.8f, true);
+    const int nFused = m.Fuse(K, cv::Mat::eye(4, 4, CV_32F), pts, th, rep);
+    for (int i = 0; i < nq; i++) { replace_point[i] = rep[i] ? rep[i]->id : -1; added_idx[i] = pts[i]->addedObsIdx; }
+    export_slots(K, slot_id, slot_bad);
+    return nFused;
+}
+
+/* ORBmatcher::SearchBySim3(pKF1, pKF2, vpMatches12, s12 = 1, R12 = I, t12 = 0, th), ORBmatcher.cpp:1124-1348.
+ * mpX_state[i]: 0 = no map point at slot i, 1 = map point, 2 = bad map point; (u, v) = where it projects in the OTHER
+ * keyframe. prior12[i] >= 0: vpMatches12[i] = map point of KF2's slot prior12[i] on entry; -2 = a point KF2 does not
+ * hold. matches12 out: slot of KF2 whose map point vpMatches12[i] is on return, -1 none, -2 foreign. */
+int rm_search_by_sim3(const void* fp1, const void* fp2, const uint8_t* mp1_state, const float* mp1_u, const float* mp1_v,
+                      const int* mp1_level, const uint8_t* mp1_desc, const uint8_t* mp2_state, const float* mp2_u,
+                      const float* mp2_v, const int* mp2_level, const uint8_t* mp2_desc, const int* prior12, float th,
+                      const float* scale_factors, int* matches12) {
+    kfptr K1 = make_kf(fp1, scale_factors, NLEV), K2 = make_kf(fp2, scale_factors, NLEV);
+    const int ID2 = 1000000;
+    struct Side { kfptr K; const uint8_t* st; const float *u, *v; const int* lvl; const uint8_t* d; int base; };
+    Side side[2] = {{K1, mp1_state, mp1_u, mp1_v, mp1_level, mp1_desc, 0}, {K2, mp2_state, mp2_u, mp2_v, mp2_level, mp2_desc, ID2}};
+    for (Side& S : side)
+        for (int i = 0; i < S.K->N; i++) {
+            if (!S.st[i]) continue;
+            mpptr p = make_mp(S.base + i, S.d + (size_t)32 * i, 1);
+            p->bad = S.st[i] == 2; p->predictedLevel = S.lvl[i];
+            set_world(p, S.u[i], S.v[i]);
+            p->indexInKF[S.K.get()] = i;
+            S.K->mvpMapPoints[i] = p;
+        }
+    std::vector<mpptr> m12(K1->N);
+    mpptr foreign = make_mp(-2, nullptr, 1);
+    for (int i = 0; i < K1->N; i++) {
+        if (prior12[i] >= 0 && K2->mvpMapPoints[prior12[i]]) m12[i] = K2->mvpMapPoints[prior12[i]];
+        else if (prior12[i] == -2) m12[i] = foreign;
+    }
+    ORBmatcher m(0.75f, true);
+    const int nFound = m.SearchBySim3(K1, K2, m12, 1.0f, cv::Mat::eye(3, 3, CV_32F), vec3(0, 0, 0), th);
+    for (int i = 0; i < K1->N; i++) matches12[i] = !m12[i] ? -1 : (m12[i]->id >= ID2 ? m12[i]->id - ID2 : -2);
+    return nFound;
+}
+
 }  // extern "C"

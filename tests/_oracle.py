@@ -326,6 +326,9 @@ class RefMatcher:
         L.rm_search_bow_kf_frame.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _c.c_float, _i, _vp]
         L.rm_search_bow_kf_kf.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _c.c_float, _i, _vp]
         L.rm_search_for_initialization.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _i, _c.c_float, _i, _vp]
+        L.rm_fuse.argtypes = [_vp, _i] + [_vp] * 8 + [_c.c_float] + [_vp] * 10
+        L.rm_fuse_sim3.argtypes = [_vp, _i] + [_vp] * 8 + [_c.c_float] + [_vp] * 7
+        L.rm_search_by_sim3.argtypes = [_vp, _vp] + [_vp] * 11 + [_c.c_float, _vp, _vp]
         self.L = L
         self.nnratio = float(np.float32(nnratio))
         self.ori = 1 if checkOri else 0
@@ -388,3 +391,37 @@ class RefMatcher:
         nm = self.L.rm_search_for_initialization(len(o1), d1.ctypes.data, o1.ctypes.data, a1.ctypes.data, prev_xy.ctypes.data,
                                                  F2.h, int(windowSize), self.nnratio, self.ori, m12.ctypes.data)
         return nm, m12[:len(o1)]
+
+    def fuse(self, F, c, th, sf, inv_sigma2):
+        """c: a tests/_fuse_cases.fuse_case dict. Returns the state ORBmatcher::Fuse(pKF, vpMapPoints, th) leaves."""
+        n, nb = len(c["q_u"]), F.n
+        a = [_a(c[k], t) for k, t in (("q_valid", np.uint8), ("q_u", np.float32), ("q_v", np.float32), ("q_level", np.int32),
+                                      ("q_desc", np.uint8), ("q_obs", np.int32), ("q_flags", np.uint8), ("q_alias", np.int32))]
+        s, g = _a(sf, np.float32), _a(inv_sigma2, np.float32)
+        oo, of = _a(c["occ_obs"], np.int32), _a(c["occ_flags"], np.uint8)
+        out = {k: np.full(m, -7, np.int32) for k, m in (("replaced_by", n), ("added_idx", n), ("q_bad", n), ("slot_id", nb),
+                                                         ("slot_bad", nb), ("occ_replaced_by", nb))}
+        out["n"] = self.L.rm_fuse(F.h, n, *[x.ctypes.data for x in a], th, s.ctypes.data, g.ctypes.data, oo.ctypes.data,
+                                  of.ctypes.data, *[out[k].ctypes.data for k in ("replaced_by", "added_idx", "q_bad", "slot_id",
+                                                                                "slot_bad", "occ_replaced_by")])
+        return out
+
+    def fuse_sim3(self, F, c, th, sf):
+        n, nb = len(c["q_u"]), F.n
+        a = [_a(c[k], t) for k, t in (("q_valid", np.uint8), ("q_u", np.float32), ("q_v", np.float32), ("q_level", np.int32),
+                                      ("q_desc", np.uint8), ("q_obs", np.int32), ("q_flags", np.uint8), ("q_alias", np.int32))]
+        s = _a(sf, np.float32)
+        oo, of = _a(c["occ_obs"], np.int32), _a(c["occ_flags"], np.uint8)
+        out = {k: np.full(m, -7, np.int32) for k, m in (("replace_point", n), ("added_idx", n), ("slot_id", nb), ("slot_bad", nb))}
+        out["n"] = self.L.rm_fuse_sim3(F.h, n, *[x.ctypes.data for x in a], th, s.ctypes.data, oo.ctypes.data, of.ctypes.data,
+                                       *[out[k].ctypes.data for k in ("replace_point", "added_idx", "slot_id", "slot_bad")])
+        return out
+
+    def search_by_sim3(self, F1, F2, c, th, sf):
+        a = [_a(c[k], t) for k, t in (("st1", np.uint8), ("u1", np.float32), ("v1", np.float32), ("l1", np.int32), ("d1", np.uint8),
+                                      ("st2", np.uint8), ("u2", np.float32), ("v2", np.float32), ("l2", np.int32), ("d2", np.uint8),
+                                      ("prior", np.int32))]
+        s = _a(sf, np.float32)
+        m12 = np.full(max(F1.n, 1), -7, np.int32)
+        n = self.L.rm_search_by_sim3(F1.h, F2.h, *[x.ctypes.data for x in a], th, s.ctypes.data, m12.ctypes.data)
+        return n, m12[:F1.n]

@@ -402,3 +402,36 @@ def test_dropin_cpp_matcher_matches_reference_class(cuda_lib):
     x = rng.integers(0, 256, (64, 32), dtype=np.uint8); y = rng.integers(0, 256, (64, 32), dtype=np.uint8)
     D, R = pair(0.6, True)
     assert np.array_equal(D.descriptor_distance(x, y), R.descriptor_distance(x, y))
+
+
+def test_dropin_cpp_fuse_and_sim3_match_reference_class(cuda_lib):
+    """Drop-in Fuse (both overloads) and SearchBySim3 — candidate search on the device (CCM_WIN_BEST), map mutations
+    replayed on the host — against the reference's own bodies (ORBmatcher.cpp:854-1348) through the same glue: the same
+    Replace / AddObservation / AddMapPoint / vpReplacePoint / vpMatches12 state, including map points listed twice,
+    occupied slots, bad and mbDoNotReplace points."""
+    import _oracle
+    import _fuse_cases as fc
+    if not (_oracle.dropin_match_available() and _oracle.ref_match_available()):
+        pytest.skip("oracle/_ref/libdropin_match.so not built (needs the reference headers at build time)")
+    from motioncheck_ccm_slam_b200.matcher import frame_grid
+    grid = frame_grid(W, H)
+    for seed, th in [(301, 3.0), (302, 8.0), (303, 2.5)]:
+        c = fc.fuse_case(seed)
+        D, R = _oracle.RefMatcher(0.6, True, lib="libdropin_match.so"), _oracle.RefMatcher(0.6, True)
+        d, r = D.fuse(D.frame(c["kf"], grid), c, th, fc.SF, fc.INV_SIGMA2), R.fuse(R.frame(c["kf"], grid), c, th, fc.SF, fc.INV_SIGMA2)
+        assert d["n"] == r["n"] > 150
+        for k in ("replaced_by", "added_idx", "q_bad", "slot_id", "slot_bad", "occ_replaced_by"):
+            assert np.array_equal(d[k], r[k]), k
+    for seed, th in [(311, 4.0), (312, 10.0)]:
+        c = fc.fuse_case(seed)
+        D, R = _oracle.RefMatcher(0.8, True, lib="libdropin_match.so"), _oracle.RefMatcher(0.8, True)
+        d, r = D.fuse_sim3(D.frame(c["kf"], grid), c, th, fc.SF), R.fuse_sim3(R.frame(c["kf"], grid), c, th, fc.SF)
+        assert d["n"] == r["n"] > 150
+        for k in ("replace_point", "added_idx", "slot_id", "slot_bad"):
+            assert np.array_equal(d[k], r[k]), k
+    for seed, th in [(321, 7.5), (322, 15.0)]:
+        c = fc.sim3_case(seed)
+        D, R = _oracle.RefMatcher(0.75, True, lib="libdropin_match.so"), _oracle.RefMatcher(0.75, True)
+        nd, md = D.search_by_sim3(D.frame(c["kf1"], grid), D.frame(c["kf2"], grid), c, th, fc.SF)
+        nr, mr = R.search_by_sim3(R.frame(c["kf1"], grid), R.frame(c["kf2"], grid), c, th, fc.SF)
+        assert nd == nr > 150 and np.array_equal(md, mr)

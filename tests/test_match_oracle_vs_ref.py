@@ -145,3 +145,58 @@ def test_search_by_bow(seed, nnratio, ori, n_nodes):
     nm_c, m_c, _ = c.bow_kf_kf(a["desc"], na, va, a["angle"], b["desc"], nb, vb, b["angle"])
     nm_r, m_r = R.bow_kf_kf(a["desc"], na, va, a["angle"], b["desc"], nb, vb, b["angle"])
     assert nm_c == nm_r > 10 and np.array_equal(m_c, m_r)
+
+
+# ---- Fuse / SearchBySim3: the reference methods against the oracle's best-in-window search + the host replay ----
+import _fuse_cases as fc
+
+
+def _best(of, nnratio, valid, c_u, c_v, c_level, c_desc, th, th_dist, inv_sigma2=None):
+    radius = (np.float32(th) * fc.SF[c_level]).astype(np.float32)
+    _, res = OracleMatcher(nnratio, True).best_in_window(of, valid.astype(np.uint8), c_u, c_v, radius, c_level, c_desc, th_dist, inv_sigma2)
+    return res["accepted"], res["best_idx"]
+
+
+@pytest.mark.parametrize("seed,th", [(301, 3.0), (302, 8.0), (303, 2.5)])
+def test_fuse(seed, th):
+    c = fc.fuse_case(seed)
+    of, grid = _both(c["kf"])
+    R = _oracle.RefMatcher(0.6, True)
+    ref = R.fuse(R.frame(c["kf"], grid), c, th, fc.SF, fc.INV_SIGMA2)
+    rows, searched = fc.effective_rows(c), fc.searched_fuse(c, first=True)
+    acc, best = _best(of, 0.6, searched, c["q_u"][rows], c["q_v"][rows], c["q_level"][rows], c["q_desc"][rows], th, 50, fc.INV_SIGMA2)
+    mine = fc.replay_fuse(c, searched, acc, best)
+    assert mine["n"] == ref["n"] > 150
+    for k in ("replaced_by", "added_idx", "q_bad", "slot_id", "slot_bad", "occ_replaced_by"):
+        assert np.array_equal(mine[k], ref[k]), k
+    assert (ref["replaced_by"] >= 0).sum() > 10 and (ref["occ_replaced_by"] >= 0).sum() > 10 and (ref["added_idx"] >= 0).sum() > 50
+
+
+@pytest.mark.parametrize("seed,th", [(311, 4.0), (312, 10.0)])
+def test_fuse_sim3(seed, th):
+    c = fc.fuse_case(seed)
+    of, grid = _both(c["kf"])
+    R = _oracle.RefMatcher(0.8, True)
+    ref = R.fuse_sim3(R.frame(c["kf"], grid), c, th, fc.SF)
+    rows, searched = fc.effective_rows(c), fc.searched_fuse(c, first=False)
+    acc, best = _best(of, 0.8, searched, c["q_u"][rows], c["q_v"][rows], c["q_level"][rows], c["q_desc"][rows], th, 50)
+    mine = fc.replay_fuse_sim3(c, searched, acc, best)
+    assert mine["n"] == ref["n"] > 150
+    for k in ("replace_point", "added_idx", "slot_id", "slot_bad"):
+        assert np.array_equal(mine[k], ref[k]), k
+    assert (ref["replace_point"] >= 0).sum() > 30 and (ref["added_idx"] >= 0).sum() > 50
+
+
+@pytest.mark.parametrize("seed,th", [(321, 7.5), (322, 15.0)])
+def test_search_by_sim3(seed, th):
+    c = fc.sim3_case(seed)
+    grid = frame_grid(W, H)
+    o1 = OracleFrame(*(c["kf1"][k] for k in ("desc", "x", "y", "octave", "angle")), grid)
+    o2 = OracleFrame(*(c["kf2"][k] for k in ("desc", "x", "y", "octave", "angle")), grid)
+    R = _oracle.RefMatcher(0.75, True)
+    n_ref, m_ref = R.search_by_sim3(R.frame(c["kf1"], grid), R.frame(c["kf2"], grid), c, th, fc.SF)
+    m1, m2 = fc.sim3_masks(c)
+    a1, b1 = _best(o2, 0.75, m1, c["u1"], c["v1"], c["l1"], c["d1"], th, 100)
+    a2, b2 = _best(o1, 0.75, m2, c["u2"], c["v2"], c["l2"], c["d2"], th, 100)
+    n_mine, m_mine = fc.replay_sim3(c, a1, b1, a2, b2, m1, m2)
+    assert n_mine == n_ref > 150 and np.array_equal(m_mine, m_ref)
