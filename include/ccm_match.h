@@ -127,6 +127,24 @@ int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientatio
                    int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* valid_b, const float* angle_b,
                    int* match_a, int* match_b, ccm_match_result* res_a, int* nmatches);
 
+/* SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs), ORBmatcher.cpp:700-852 with CheckDistEpipolarLine :159-176.
+ * Same FeatureVector convention; free_a / free_b = the feature holds NO map point (:741-744, :758-762). The epipole
+ * (:707-714) and F12 are host geometry and come in as numbers. match_a [n_a]: pKF2 feature index or -1 (vMatches12;
+ * vMatchedPairs = its non-negative entries in index order); *nmatches = the return value. A pKF2 feature can be matched
+ * by several pKF1 features (upstream never sets vbMatched2). */
+typedef struct ccm_epipolar_geom {
+    float f12[9];                  /* F12, row-major */
+    float ex, ey;                  /* epipole: pKF1's camera centre projected into pKF2 */
+    const float* scale_factors;    /* pKF2->mvScaleFactors  (HOST, n_levels) */
+    const float* level_sigma2;     /* pKF2->mvLevelSigma2   (HOST, n_levels) */
+    int n_levels;                  /* <= 16 */
+} ccm_epipolar_geom;
+int ccm_search_triangulation(ccm_matcher* m, int check_orientation, const ccm_epipolar_geom* g,
+                             int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* free_a, const float* x_a,
+                             const float* y_a, const float* angle_a,
+                             int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* free_b, const float* x_b,
+                             const float* y_b, const int* octave_b, const float* angle_b, int* match_a, int* nmatches);
+
 /* ---- server keyframe-database search (BASELINE.json configs[4]) --------------------------------------------
  * Best and second-best Hamming distance of every query descriptor over a (shard of a) target descriptor database,
  * first-wins on ties: the inner loop of SearchByBoW(KF,KF) (:607-637) with one all-inclusive node. */

@@ -50,6 +50,12 @@ class GridParams(ctypes.Structure):
                 ("cols", ctypes.c_int), ("rows", ctypes.c_int)]
 
 
+class EpipolarGeom(ctypes.Structure):
+    _fields_ = [("f12", ctypes.c_float * 9), ("ex", ctypes.c_float), ("ey", ctypes.c_float),
+                ("scale_factors", ctypes.POINTER(ctypes.c_float)), ("level_sigma2", ctypes.POINTER(ctypes.c_float)),
+                ("n_levels", ctypes.c_int)]
+
+
 class WindowQuery(ctypes.Structure):
     _fields_ = [("u", ctypes.c_float), ("v", ctypes.c_float), ("r", ctypes.c_float), ("angle", ctypes.c_float),
                 ("min_level", ctypes.c_int16), ("max_level", ctypes.c_int16), ("flags", ctypes.c_uint32)]
@@ -82,6 +88,7 @@ SIGNATURES.update({
     "ccm_search_window": (_i, [_vp, _vp, _wp, _i, _vp, _vp, _vp, _vp, _ip]),
     "ccm_search_window_batch_device": (_i, [_vp, _c.POINTER(_vp), _i, _wp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "ccm_search_bow": (_i, [_vp, _i, _f, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ip]),
+    "ccm_search_triangulation": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ip]),
     "ccm_match_allpairs_best2_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
     "ccm_match_allpairs_merge_device": (_i, [_vp, _vp, _i, _i, _f, _vp, _vp]),
     "ccm_match_allpairs_best2": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),

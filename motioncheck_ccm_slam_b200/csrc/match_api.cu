@@ -1,6 +1,7 @@
 // Host side of the matcher C ABI (include/ccm_match.h): frame packs, scratch arena, launches.
 // Compiled as part of the single translation unit ccm_orb_cuda.cu after match_allpairs.cu, match_window.cu, match_bow.cu.
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -371,13 +372,16 @@ static void feature_vector_order(int n, const int* node, std::vector<int>& order
     std::stable_sort(order.begin(), order.end(), [node](int a, int b) { return node[a] < node[b]; });
 }
 
-int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientation,
-                   int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* valid_a, const float* angle_a,
-                   int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* valid_b, const float* angle_b,
-                   int* match_a, int* match_b, ccm_match_result* res_a, int* nmatches) {
-    if (!m || (mode != CCM_BOW_KF_FRAME && mode != CCM_BOW_KF_KF) || n_a < 0 || n_b < 0 || n_a > 65535 || n_b > 65535) return CCM_E_BADARG;
+// extra per-feature inputs of SearchForTriangulation (host pointers)
+struct TriHost { const ccm_epipolar_geom* g; const float *x_a, *y_a, *x_b, *y_b; const int* oct_b; };
+
+static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_orientation,
+                           int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* valid_a, const float* angle_a,
+                           int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* valid_b, const float* angle_b,
+                           int* match_a, int* match_b, ccm_match_result* res_a, int* nmatches, const TriHost* tri) {
+    if (!m || n_a < 0 || n_b < 0 || n_a > 65535 || n_b > 65535) return CCM_E_BADARG;
     if ((n_a > 0 && (!desc_a || !node_a || !valid_a || !angle_a)) || (n_b > 0 && (!desc_b || !node_b || !angle_b))) return CCM_E_BADARG;
-    if (mode == CCM_BOW_KF_KF && n_b > 0 && !valid_b) return CCM_E_BADARG;
+    if (mode != CCM_BOW_KF_FRAME && n_b > 0 && !valid_b) return CCM_E_BADARG;
     if (nmatches) *nmatches = 0;
     if (n_a == 0 || n_b == 0) {
         if (match_a) for (int i = 0; i < n_a; i++) match_a[i] = -1;
@@ -407,10 +411,12 @@ int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientatio
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     const size_t A = (size_t)n_a, B = (size_t)n_b;
     // side A blob: desc | valid | angle | order | match | res ; side B blob: desc | valid | angle | order | match
+    // (triangulation adds x | y | node index per order position to A and x | y | octave to B)
     const size_t a_desc = 0, a_val = a_desc + up(A * 32), a_ang = a_val + up(A), a_ord = a_ang + up(A * 4), a_mat = a_ord + up(A * 4),
-                 a_res = a_mat + up(A * 4), a_tot = a_res + up(A * 16);
+                 a_res = a_mat + up(A * 4), a_x = a_res + up(A * 16), a_y = a_x + up(A * 4), a_nod = a_y + up(A * 4),
+                 a_tot = tri ? a_nod + up(A * 4) : a_x;
     const size_t b_desc = 0, b_val = b_desc + up(B * 32), b_ang = b_val + up(B), b_ord = b_ang + up(B * 4), b_mat = b_ord + up(B * 4),
-                 b_tot = b_mat + up(B * 4);
+                 b_x = b_mat + up(B * 4), b_y = b_x + up(B * 4), b_oct = b_y + up(B * 4), b_tot = tri ? b_oct + up(B * 4) : b_x;
     if ((rc = mbuf(m, MB_A, a_tot, &blob_a))) return rc;
     if ((rc = mbuf(m, MB_B, b_tot, &blob_b))) return rc;
     if ((rc = mbuf(m, MB_C, nodes.size() + 1, &dn))) return rc;
@@ -433,7 +439,33 @@ int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientatio
     J.match_a = dma; J.match_b = dmb; J.res_a = res_a ? dres : nullptr; J.nmatches = dnm;
     J.mode = mode; J.nnratio = nnratio; J.th_low = CCM_TH_LOW; J.check_orientation = check_orientation;
     k_bow_init<<<(std::max(n_a, n_b) + 255) / 256, 256, 0, m->stream>>>(J);
-    if (J.n_nodes > 0) k_bow_search<<<(J.n_nodes + 7) / 8, 256, 0, m->stream>>>(J);
+    if (tri) {
+        TriGeom G;
+        G.x_a = (const float*)(blob_a + a_x); G.y_a = (const float*)(blob_a + a_y);
+        G.x_b = (const float*)(blob_b + b_x); G.y_b = (const float*)(blob_b + b_y); G.oct_b = (const int*)(blob_b + b_oct);
+        std::memcpy(G.f, tri->g->f12, sizeof(G.f));
+        G.ex = tri->g->ex; G.ey = tri->g->ey;
+        for (int l = 0; l < 16; l++) {
+            const bool in = l < tri->g->n_levels;
+            G.epipole_th[l] = in ? 100 * tri->g->scale_factors[l] : 0.f;                       // :777, int * float
+            const double t = in ? 3.84 * tri->g->level_sigma2[l] : 0.0;                          // :175, double * float
+            float tf = (float)t;                                                                 // float d: (double)d < t  <=>  d < tf
+            if ((double)tf < t) tf = std::nextafterf(tf, INFINITY);
+            G.line_th[l] = tf;
+        }
+        // position in order_a -> index of its shared node (-1: the node does not occur in pKF2's vector)
+        std::vector<int> a_node(oa.size() ? oa.size() : 1, -1);
+        for (size_t k = 0; k < nodes.size(); k++) for (int i = nodes[k].a0; i < nodes[k].a1; i++) a_node[i] = (int)k;
+        MCK(cudaMemcpyAsync(blob_a + a_nod, a_node.data(), a_node.size() * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(blob_a + a_x, tri->x_a, A * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(blob_a + a_y, tri->y_a, A * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(blob_b + b_x, tri->x_b, B * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(blob_b + b_y, tri->y_b, B * 4, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(blob_b + b_oct, tri->oct_b, B * 4, cudaMemcpyHostToDevice, m->stream));
+        J.n_a = (int)oa.size();                       // the search walks order_a positions
+        if (J.n_nodes > 0 && J.n_a > 0) k_tri_search<<<(J.n_a + 7) / 8, 256, 0, m->stream>>>(J, G, (const int*)(blob_a + a_nod));
+        J.n_a = n_a;
+    } else if (J.n_nodes > 0) k_bow_search<<<(J.n_nodes + 7) / 8, 256, 0, m->stream>>>(J);
     k_bow_finish<<<1, 1024, 0, m->stream>>>(J);
     m->launches += J.n_nodes > 0 ? 3 : 2;
     MCK(cudaGetLastError());
@@ -445,6 +477,28 @@ int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientatio
     MCK(cudaStreamSynchronize(m->stream));
     if (nmatches) *nmatches = nm;
     return CCM_OK;
+}
+
+int ccm_search_bow(ccm_matcher* m, int mode, float nnratio, int check_orientation,
+                   int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* valid_a, const float* angle_a,
+                   int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* valid_b, const float* angle_b,
+                   int* match_a, int* match_b, ccm_match_result* res_a, int* nmatches) {
+    if (mode != CCM_BOW_KF_FRAME && mode != CCM_BOW_KF_KF) return CCM_E_BADARG;
+    return bow_search_impl(m, mode, nnratio, check_orientation, n_a, desc_a, node_a, valid_a, angle_a, n_b, desc_b, node_b, valid_b,
+                           angle_b, match_a, match_b, res_a, nmatches, nullptr);
+}
+
+int ccm_search_triangulation(ccm_matcher* m, int check_orientation, const ccm_epipolar_geom* g,
+                             int n_a, const uint8_t* desc_a, const int* node_a, const uint8_t* free_a, const float* x_a,
+                             const float* y_a, const float* angle_a,
+                             int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* free_b, const float* x_b,
+                             const float* y_b, const int* octave_b, const float* angle_b, int* match_a, int* nmatches) {
+    if (!g || !g->scale_factors || !g->level_sigma2 || g->n_levels < 1 || g->n_levels > 16) return CCM_E_BADARG;
+    if ((n_a > 0 && (!x_a || !y_a)) || (n_b > 0 && (!x_b || !y_b || !octave_b))) return CCM_E_BADARG;
+    for (int i = 0; i < n_b; i++) if (octave_b[i] < 0 || octave_b[i] >= g->n_levels) return CCM_E_BADARG;
+    TriHost t = {g, x_a, y_a, x_b, y_b, octave_b};
+    return bow_search_impl(m, BOW_MODE_TRIANGULATION, 0.f, check_orientation, n_a, desc_a, node_a, free_a, angle_a, n_b, desc_b,
+                           node_b, free_b, angle_b, match_a, nullptr, nullptr, nmatches, &t);
 }
 
 /* ---- server keyframe-database search ---------------------------------------------------------------------- */

@@ -12,6 +12,17 @@
 
 #define BOW_MODE_KF_FRAME 0
 #define BOW_MODE_KF_KF 1
+#define BOW_MODE_TRIANGULATION 2
+
+// SearchForTriangulation's geometric predicates (ORBmatcher.cpp:159-176, :773-778), thresholds folded per level by the host
+struct TriGeom {
+    const float* x_a; const float* y_a;                    // mvKeysUn of pKF1
+    const float* x_b; const float* y_b; const int* oct_b;  // mvKeysUn of pKF2
+    float f[9];                                            // F12 row-major
+    float ex, ey;                                          // epipole in pKF2 (:707-714)
+    float epipole_th[16];                                  // 100 * mvScaleFactors[l]                         (:777)
+    float line_th[16];                                     // smallest float >= 3.84 * mvLevelSigma2[l] (double) (:175)
+};
 
 struct BowNode { int a0, a1, b0, b1; };   // ranges into order_a / order_b
 
@@ -99,4 +110,51 @@ __global__ void __launch_bounds__(1024) k_bow_finish(BowJob J) {
         __syncthreads();
     }
     if (threadIdx.x == 0) *J.nmatches = s_nm;
+}
+
+// SearchForTriangulation (ORBmatcher.cpp:700-852). vbMatched2 is never set upstream, so the pKF1 features are
+// independent: one warp per (shared node, pKF1 feature), lanes over the node's pKF2 features. The running
+// `dist > bestDist` test (:768) only ever compares against candidates that passed both geometric gates, so the loop
+// returns the gated candidate of minimum distance, the LAST one among equals: key = dist << 16 | (0xffff - position).
+// Float expressions keep the reference's operation order with explicit round-to-nearest mul/add (no FMA contraction).
+__global__ void __launch_bounds__(256) k_tri_search(BowJob J, TriGeom G, const int* __restrict__ a_node) {
+    const int lane = threadIdx.x & 31;
+    const int ia = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);      // position in order_a
+    if (ia >= J.n_a) return;
+    const int ni = a_node[ia];
+    if (ni < 0) return;                                                     // node not shared with pKF2
+    const int a = J.order_a[ia];
+    if (!J.valid_a[a]) return;                                              // pKF1 feature holds a map point, :741-744
+    const BowNode N = J.nodes[ni];
+    const uint4* __restrict__ da = reinterpret_cast<const uint4*>(J.desc_a);
+    const uint4* __restrict__ db = reinterpret_cast<const uint4*>(J.desc_b);
+    const uint4 q0 = da[2 * (size_t)a], q1 = da[2 * (size_t)a + 1];
+    const float x1 = G.x_a[a], y1 = G.y_a[a];
+    const float la = __fadd_rn(__fadd_rn(__fmul_rn(x1, G.f[0]), __fmul_rn(y1, G.f[3])), G.f[6]);
+    const float lb = __fadd_rn(__fadd_rn(__fmul_rn(x1, G.f[1]), __fmul_rn(y1, G.f[4])), G.f[7]);
+    const float lc = __fadd_rn(__fadd_rn(__fmul_rn(x1, G.f[2]), __fmul_rn(y1, G.f[5])), G.f[8]);
+    const float den = __fadd_rn(__fmul_rn(la, la), __fmul_rn(lb, lb));
+    uint32_t best = 0xffffffffu;
+    if (den != 0.f) {
+        for (int ib = N.b0 + lane; ib < N.b1; ib += 32) {
+            const int b = J.order_b[ib];
+            if (!J.valid_b[b]) continue;                                    // pKF2 feature holds a map point, :758-762
+            const int dist = hamming256(q0, q1, db[2 * (size_t)b], db[2 * (size_t)b + 1]);
+            if (dist > J.th_low) continue;
+            const float x2 = G.x_b[b], y2 = G.y_b[b];
+            const int o = G.oct_b[b];
+            const float dex = __fsub_rn(G.ex, x2), dey = __fsub_rn(G.ey, y2);
+            if (__fadd_rn(__fmul_rn(dex, dex), __fmul_rn(dey, dey)) < G.epipole_th[o]) continue;
+            const float num = __fadd_rn(__fadd_rn(__fmul_rn(la, x2), __fmul_rn(lb, y2)), lc);
+            const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+            if (!(dsqr < G.line_th[o])) continue;
+            best = min(best, ((uint32_t)dist << 16) | (uint32_t)(0xffff - (ib - N.b0)));
+        }
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (lane == 0 && best != 0xffffffffu) {
+        const int b = J.order_b[N.b0 + (0xffff - (int)(best & 0xffff))];
+        J.match_a[a] = b;
+        if (J.res_a) { MatchResultDev r; r.best_idx = b; r.best_dist = (int)(best >> 16); r.best_dist2 = 256; r.accepted = 1; J.res_a[a] = r; }
+    }
 }

@@ -7,12 +7,13 @@
 //
 // Converted here: DescriptorDistance, SearchByProjection(Frame, MapPoints), SearchByProjection(Frame, LastFrame),
 // SearchByProjection(KeyFrame, Scw), SearchByBoW(KeyFrame, Frame), SearchByBoW(KeyFrame, KeyFrame),
-// SearchForInitialization, SearchBySim3 and both Fuse overloads (candidate search on the device, CCM_WIN_BEST; the map
-// mutations are replayed on the host in the reference's order). SearchForTriangulation and the caller-less
-// relocalisation SearchByProjection keep their upstream bodies this round. A CUDA failure throws estd::infrastructure_ex (the
+// SearchForInitialization, SearchForTriangulation, SearchBySim3 and both Fuse overloads (candidate search on the device,
+// CCM_WIN_BEST; the map mutations are replayed on the host in the reference's order). The caller-less relocalisation
+// SearchByProjection (:1478-1605) keeps its upstream body. A CUDA failure throws estd::infrastructure_ex (the
 // reference's fatal-error convention, estd.h:74); there is no CPU fallback.
 #include <cslam/ORBmatcher.h>
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -297,6 +298,66 @@ int ORBmatcher::SearchByBoW(kfptr pKF1, kfptr pKF2, vector<mpptr> &vpMatches12) 
         throw estd::infrastructure_ex();
     for (int i = 0; i < n1; i++)
         if (m12[i] >= 0) vpMatches12[i] = vpMapPoints2[m12[i]];
+    return nmatches;
+}
+
+// ORBmatcher.cpp:159-176 (scalar helper; the device evaluates the same expression inside ccm_search_triangulation)
+bool ORBmatcher::CheckDistEpipolarLine(const cv::KeyPoint &kp1, const cv::KeyPoint &kp2, const cv::Mat &F12, const kfptr pKF2) {
+    const float a = kp1.pt.x * F12.at<float>(0, 0) + kp1.pt.y * F12.at<float>(1, 0) + F12.at<float>(2, 0);
+    const float b = kp1.pt.x * F12.at<float>(0, 1) + kp1.pt.y * F12.at<float>(1, 1) + F12.at<float>(2, 1);
+    const float c = kp1.pt.x * F12.at<float>(0, 2) + kp1.pt.y * F12.at<float>(1, 2) + F12.at<float>(2, 2);
+    const float num = a * kp2.pt.x + b * kp2.pt.y + c;
+    const float den = a * a + b * b;
+    if (den == 0) return false;
+    const float dsqr = num * num / den;
+    return dsqr < 3.84 * pKF2->mvLevelSigma2[kp2.octave];
+}
+
+// ORBmatcher.cpp:700-852
+int ORBmatcher::SearchForTriangulation(kfptr pKF1, kfptr pKF2, cv::Mat F12, vector<pair<size_t, size_t> > &vMatchedPairs) {
+    // epipole in the second image, :707-714
+    cv::Mat Cw = pKF1->GetCameraCenter();
+    cv::Mat R2w = pKF2->GetRotation();
+    cv::Mat t2w = pKF2->GetTranslation();
+    cv::Mat C2 = R2w * Cw + t2w;
+    const float invz = 1.0f / C2.at<float>(2);
+    ccm_epipolar_geom geo;
+    geo.ex = pKF2->fx * C2.at<float>(0) * invz + pKF2->cx;
+    geo.ey = pKF2->fy * C2.at<float>(1) * invz + pKF2->cy;
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) geo.f12[3 * r + c] = F12.at<float>(r, c);
+    geo.scale_factors = pKF2->mvScaleFactors.data();
+    geo.level_sigma2 = pKF2->mvLevelSigma2.data();
+    geo.n_levels = (int)std::min(pKF2->mvScaleFactors.size(), pKF2->mvLevelSigma2.size());
+    const int n1 = pKF1->N, n2 = pKF2->N;
+    struct Side { std::vector<uint8_t> free_; std::vector<float> x, y, ang; std::vector<int> oct; };
+    Side S[2];
+    kfptr K[2] = {pKF1, pKF2};
+    for (int s = 0; s < 2; s++) {
+        const int n = K[s]->N, cap = n > 0 ? n : 1;
+        S[s].free_.assign(cap, 0); S[s].x.resize(cap); S[s].y.resize(cap); S[s].ang.resize(cap); S[s].oct.assign(cap, 0);
+        for (int i = 0; i < n; i++) {
+            const cv::KeyPoint &kp = K[s]->mvKeysUn[i];
+            S[s].free_[i] = K[s]->GetMapPoint(i) ? 0 : 1;             // :741-744, :758-762
+            S[s].x[i] = kp.pt.x; S[s].y[i] = kp.pt.y; S[s].ang[i] = kp.angle; S[s].oct[i] = kp.octave;
+        }
+    }
+    const std::vector<int> node1 = node_ids(pKF1->mFeatVec, n1), node2 = node_ids(pKF2->mFeatVec, n2);
+    std::vector<int> m12(n1 > 0 ? n1 : 1, -1);
+    int nmatches = 0;
+    {
+        Device& D = device();
+        std::lock_guard<std::mutex> g(D.mu);
+        if (ccm_search_triangulation(D.m, mbCheckOrientation ? 1 : 0, &geo, n1, pKF1->mDescriptors.ptr(0), node1.data(), S[0].free_.data(),
+                                     S[0].x.data(), S[0].y.data(), S[0].ang.data(), n2, pKF2->mDescriptors.ptr(0), node2.data(),
+                                     S[1].free_.data(), S[1].x.data(), S[1].y.data(), S[1].oct.data(), S[1].ang.data(), m12.data(),
+                                     &nmatches) != CCM_OK)
+            throw estd::infrastructure_ex();
+    }
+    vMatchedPairs.clear();
+    vMatchedPairs.reserve(nmatches);
+    for (int i = 0; i < n1; i++)
+        if (m12[i] >= 0) vMatchedPairs.push_back(make_pair((size_t)i, (size_t)m12[i]));
     return nmatches;
 }
 

@@ -266,6 +266,31 @@ class ORBmatcher:
         nm, ma, _, res = self._search_bow(BOW_KF_KF, desc1, node1, valid1, angle1, desc2, node2, valid2, angle2)
         return nm, ma, res
 
+    # SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs), ORBmatcher.cpp:700-852 -> (nmatches, match12);
+    # vMatchedPairs = [(i, match12[i]) for i where match12[i] >= 0]. free* = the feature holds no map point.
+    def SearchForTriangulation(self, desc1, node1, free1, x1, y1, angle1, desc2, node2, free2, x2, y2, octave2, angle2,
+                               F12, ex, ey, scale_factors, level_sigma2):
+        from ._lib import EpipolarGeom
+        c = np.ascontiguousarray
+        desc1 = c(desc1, np.uint8).reshape(-1, 32); desc2 = c(desc2, np.uint8).reshape(-1, 32)
+        n1, n2 = len(desc1), len(desc2)
+        a = [c(node1, np.int32), c(free1, np.uint8), c(x1, np.float32), c(y1, np.float32), c(angle1, np.float32)]
+        b = [c(node2, np.int32), c(free2, np.uint8), c(x2, np.float32), c(y2, np.float32), c(octave2, np.int32), c(angle2, np.float32)]
+        sf, ls = c(scale_factors, np.float32), c(level_sigma2, np.float32)
+        g = EpipolarGeom()
+        g.f12[:] = [float(v) for v in c(F12, np.float32).reshape(-1)]
+        g.ex, g.ey = float(ex), float(ey)
+        g.scale_factors = sf.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+        g.level_sigma2 = ls.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+        g.n_levels = len(sf)
+        m12 = np.full(max(n1, 1), -1, np.int32)
+        nm = ctypes.c_int()
+        self.m._check(self.m._lib.ccm_search_triangulation(
+            self.m._h, 1 if self.mbCheckOrientation else 0, ctypes.byref(g),
+            n1, desc1.ctypes.data, *[v.ctypes.data for v in a], n2, desc2.ctypes.data, *[v.ctypes.data for v in b],
+            m12.ctypes.data, ctypes.byref(nm)))
+        return nm.value, m12[:n1]
+
 
 # ---- device-resident batch path (extractor output -> packs -> searches, no host round trip) ----------------------
 def packs_from_extractor_batch_device(packs, grid, d_kp, d_desc, d_n, kp_stride, d_xy_un=None):

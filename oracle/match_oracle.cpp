@@ -446,6 +446,65 @@ int mo_search_bow_kf_kf(int n1, const uint8_t* desc1, const int* node1, const ui
     return nmatches;
 }
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs), ORBmatcher.cpp:700-852, with
+ * CheckDistEpipolarLine :159-176. free1/free2 = the feature holds NO map point (:739-744, :758-762); f12 = F12 row-major;
+ * (ex, ey) = the epipole the reference computes at :707-714 (host geometry, an input here). vbMatched2 is never set
+ * upstream, so a KF2 feature may be matched by several KF1 features. match12[n1] out: KF2 feature index or -1
+ * (vMatches12; vMatchedPairs = its non-negative entries in index order). Float expressions keep the reference's
+ * operation order; the oracle is built with -ffp-contract=off. */
+int mo_search_for_triangulation(int n1, const uint8_t* desc1, const int* node1, const uint8_t* free1, const float* x1,
+                                const float* y1, const float* angle1, int n2, const uint8_t* desc2, const int* node2,
+                                const uint8_t* free2, const float* x2, const float* y2, const int* octave2,
+                                const float* angle2, const float* f12, float ex, float ey, const float* scale_factors,
+                                const float* level_sigma2, int check_orientation, int* match12) {
+    for (int i = 0; i < n1; i++) match12[i] = -1;
+    const NodeLists A = build_feature_vector(n1, node1), B = build_feature_vector(n2, node2);
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    size_t a = 0, b = 0;
+    while (a < A.ids.size() && b < B.ids.size()) {
+        if (A.ids[a] == B.ids[b]) {
+            for (int idx1 : A.items[a]) {
+                if (!free1[idx1]) continue;
+                const uint8_t* d1 = desc1 + (size_t)idx1 * 32;
+                int bestDist = TH_LOW, bestIdx2 = -1;
+                for (int idx2 : B.items[b]) {
+                    if (!free2[idx2]) continue;
+                    const int dist = descriptor_distance(d1, desc2 + (size_t)idx2 * 32);
+                    if (dist > TH_LOW || dist > bestDist) continue;                   /* :768: ties move to the later one */
+                    const float distex = ex - x2[idx2], distey = ey - y2[idx2];
+                    if (distex * distex + distey * distey < 100 * scale_factors[octave2[idx2]]) continue;   /* :777 */
+                    /* CheckDistEpipolarLine :159-176 */
+                    const float la = x1[idx1] * f12[0] + y1[idx1] * f12[3] + f12[6];
+                    const float lb = x1[idx1] * f12[1] + y1[idx1] * f12[4] + f12[7];
+                    const float lc = x1[idx1] * f12[2] + y1[idx1] * f12[5] + f12[8];
+                    const float num = la * x2[idx2] + lb * y2[idx2] + lc;
+                    const float den = la * la + lb * lb;
+                    if (den == 0) continue;
+                    const float dsqr = num * num / den;
+                    if (dsqr < 3.84 * level_sigma2[octave2[idx2]]) { bestIdx2 = idx2; bestDist = dist; }
+                }
+                if (bestIdx2 >= 0) {
+                    match12[idx1] = bestIdx2;
+                    nmatches++;
+                    if (check_orientation) rotHist[rot_bin(angle1[idx1], angle2[bestIdx2])].push_back(idx1);
+                }
+            }
+            a++; b++;
+        } else if (A.ids[a] < B.ids[b]) a++;
+        else b++;
+    }
+    if (check_orientation) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        compute_three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : rotHist[i]) { match12[idx] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), ORBmatcher.cpp:448-563.
  * f2 = grid of F2; F1 is given by its arrays. prev_xy[2*n1] in/out (vbPrevMatched). */
 int mo_search_for_initialization(int n1, const uint8_t* desc1, const int* octave1, const float* angle1, float* prev_xy,

@@ -347,4 +347,41 @@ int rm_search_by_sim3(const void* fp1, const void* fp2, const uint8_t* mp1_state
     return nFound;
 }
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs), ORBmatcher.cpp:700-852. Plain keyframes from
+ * arrays (no grid needed); KF2 has identity pose and unit intrinsics and KF1's camera centre is (ex, ey, 1), so the
+ * reference's own epipole code (:707-714) yields exactly (ex, ey). */
+int rm_search_for_triangulation(int n1, const uint8_t* desc1, const int* node1, const uint8_t* free1, const float* x1,
+                                const float* y1, const float* angle1, int n2, const uint8_t* desc2, const int* node2,
+                                const uint8_t* free2, const float* x2, const float* y2, const int* octave2,
+                                const float* angle2, const float* f12, float ex, float ey, const float* scale_factors,
+                                const float* level_sigma2, int check_orientation, int* match12) {
+    kfptr K1(new KeyFrame()), K2(new KeyFrame());
+    struct Side { kfptr K; int n; const uint8_t* d; const int* node; const uint8_t* fr; const float *x, *y, *ang; const int* oct; };
+    Side side[2] = {{K1, n1, desc1, node1, free1, x1, y1, angle1, nullptr}, {K2, n2, desc2, node2, free2, x2, y2, angle2, octave2}};
+    for (Side& S : side) {
+        S.K->N = S.n;
+        S.K->mDescriptors = desc_mat(S.d, S.n);
+        S.K->mvKeysUn.resize(S.n);
+        S.K->mvpMapPoints.assign(S.n, mpptr());
+        for (int i = 0; i < S.n; i++) {
+            S.K->mvKeysUn[i] = cv::KeyPoint(S.x[i], S.y[i], 31.f, S.ang[i], 0.f, S.oct ? S.oct[i] : 0);
+            if (!S.fr[i]) S.K->mvpMapPoints[i] = make_mp(i, nullptr, 1);
+        }
+        S.K->mFeatVec = feat_vec(S.n, S.node);
+        S.K->R = cv::Mat::eye(3, 3, CV_32F); S.K->t = vec3(0, 0, 0); S.K->C = vec3(0, 0, 0);
+        S.K->mvScaleFactors.assign(scale_factors, scale_factors + NLEV);
+        S.K->mvLevelSigma2.assign(level_sigma2, level_sigma2 + NLEV);
+    }
+    K1->C = vec3(ex, ey, 1.f);
+    cv::Mat F12(3, 3, CV_32F);
+    for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) F12.at<float>(r, c) = f12[3 * r + c];
+    std::vector<std::pair<size_t, size_t> > pairs;
+    ORBmatcher m(0.6f, check_orientation != 0);
+    const int nm = m.SearchForTriangulation(K1, K2, F12, pairs);
+    for (int i = 0; i < n1; i++) match12[i] = -1;
+    for (size_t k = 0; k < pairs.size(); k++) match12[pairs[k].first] = (int)pairs[k].second;
+    if ((int)pairs.size() != nm) return -1000 - nm;      /* the pair list and the return value must agree */
+    return nm;
+}
+
 }  // extern "C"

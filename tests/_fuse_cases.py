@@ -219,3 +219,40 @@ def replay_sim3(c, acc1, best1, acc2, best2, m1, m2):
         if j >= 0 and vn2[j] == i:
             out[i] = j; found += 1
     return found, out
+
+
+LEVEL_SIGMA2 = (SF * SF).astype(np.float32)
+
+
+def tri_case(seed, n=1000, n_nodes=120, motion=(9.0, 4.0)):
+    """Two keyframes related by an image translation: F12 = [t]x makes the epipolar line of a KF1 feature the line
+    through it along the motion. To make every predicate of the loop decide something: a third of KF2's features are
+    pushed off their epipolar line (3.84 sigma2 gate, :159-176), 150 look-alikes (same vocabulary node, 0-5 flipped bits,
+    0 = an exact tie, which the reference resolves to the LATER feature, :768) are placed along the lines, and the
+    epipole sits on a feature cluster of KF2 (:777 gate)."""
+    from motioncheck_ccm_slam_b200.synth import bow_node_ids
+    rng = np.random.default_rng(seed)
+    a = make_feature_frame(seed, n, W, H)
+    b, src = make_next_frame(seed + 1, a, W, H, motion=motion)
+    tx, ty = np.float32(motion[0]), np.float32(motion[1])
+    tn = float(np.hypot(tx, ty))
+    off = rng.random(len(b["x"])) < 0.33
+    perp = rng.normal(0, 3.0, len(b["x"])) * off
+    b["x"] = (b["x"] - perp * ty / tn).astype(np.float32)
+    b["y"] = (b["y"] + perp * tx / tn).astype(np.float32)
+    cand = np.nonzero(src >= 0)[0]
+    twins = rng.choice(cand, min(150, len(cand) // 3), replace=False)
+    sl = rng.uniform(-40, 40, len(twins))
+    td = b["desc"][twins].copy()
+    for k, row in enumerate(td):
+        for bit in rng.integers(16, 256, int(rng.choice([0, 0, 1, 2, 5]))):
+            row[bit >> 3] ^= np.uint8(1 << (bit & 7))
+    b = {"desc": np.concatenate([b["desc"], td]), "x": np.concatenate([b["x"], (b["x"][twins] + sl * tx / tn).astype(np.float32)]),
+         "y": np.concatenate([b["y"], (b["y"][twins] + sl * ty / tn).astype(np.float32)]),
+         "octave": np.concatenate([b["octave"], b["octave"][twins]]), "angle": np.concatenate([b["angle"], b["angle"][twins]])}
+    f12 = np.array([[0, 0, ty], [0, 0, -tx], [-ty, tx, 0]], np.float32) * np.float32(0.37)
+    free1 = (rng.random(len(a["x"])) < 0.7).astype(np.uint8)
+    free2 = (rng.random(len(b["x"])) < 0.7).astype(np.uint8)
+    return {"kf1": a, "kf2": b, "node1": bow_node_ids(a["desc"], n_nodes), "node2": bow_node_ids(b["desc"], n_nodes),
+            "free1": free1, "free2": free2, "f12": np.ascontiguousarray(f12.reshape(-1)),
+            "ex": float(b["x"][5]), "ey": float(b["y"][5])}

@@ -291,6 +291,9 @@ class OracleMatcher:
                                                  F2.h, int(windowSize), self.nnratio, self.ori, m12.ctypes.data)
         return nm, m12[:len(o1)]
 
+    def search_for_triangulation(self, c, sf, level_sigma2, ori):
+        return _triangulation(self.L, self.L.mo_search_for_triangulation, c, sf, level_sigma2, ori)
+
     def allpairs_best2(self, q, t):
         q = _a(q, np.uint8).reshape(-1, 32); t = _a(t, np.uint8).reshape(-1, 32)
         res = np.zeros(max(len(q), 1), RESULT_DTYPE)
@@ -301,6 +304,24 @@ class OracleMatcher:
 # ---------------------------------------------------------------------------------------------------------------
 # the reference's own ORBmatcher.cpp, compiled unmodified over mock Frame/KeyFrame/MapPoint (oracle/_ref/libref_match.so)
 # ---------------------------------------------------------------------------------------------------------------
+def _triangulation(L, fn, c, sf, level_sigma2, ori):
+    """SearchForTriangulation through `fn` (mo_* of the oracle or rm_* of a reference/drop-in build): c is a
+    tests/_fuse_cases.tri_case dict. Returns (nmatches, match12)."""
+    a, b = c["kf1"], c["kf2"]
+    arrs = [_a(a["desc"], np.uint8), _a(c["node1"], np.int32), _a(c["free1"], np.uint8), _a(a["x"], np.float32), _a(a["y"], np.float32),
+            _a(a["angle"], np.float32)]
+    brrs = [_a(b["desc"], np.uint8), _a(c["node2"], np.int32), _a(c["free2"], np.uint8), _a(b["x"], np.float32), _a(b["y"], np.float32),
+            _a(b["octave"], np.int32), _a(b["angle"], np.float32)]
+    f12, s, g = _a(c["f12"], np.float32), _a(sf, np.float32), _a(level_sigma2, np.float32)
+    n1, n2 = len(arrs[1]), len(brrs[1])
+    m12 = np.full(max(n1, 1), -7, np.int32)
+    fn.restype = _i
+    fn.argtypes = [_i] + [_vp] * 6 + [_i] + [_vp] * 7 + [_vp, _c.c_float, _c.c_float, _vp, _vp, _i, _vp]
+    nm = fn(n1, *[x.ctypes.data for x in arrs], n2, *[x.ctypes.data for x in brrs], f12.ctypes.data, c["ex"], c["ey"],
+            s.ctypes.data, g.ctypes.data, int(ori), m12.ctypes.data)
+    return nm, m12[:n1]
+
+
 def ref_match_available():
     return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_match.so"))
 
@@ -425,3 +446,6 @@ class RefMatcher:
         m12 = np.full(max(F1.n, 1), -7, np.int32)
         n = self.L.rm_search_by_sim3(F1.h, F2.h, *[x.ctypes.data for x in a], th, s.ctypes.data, m12.ctypes.data)
         return n, m12[:F1.n]
+
+    def search_for_triangulation(self, c, sf, level_sigma2, ori):
+        return _triangulation(self.L, self.L.rm_search_for_triangulation, c, sf, level_sigma2, ori)

@@ -435,3 +435,63 @@ def test_dropin_cpp_fuse_and_sim3_match_reference_class(cuda_lib):
         nd, md = D.search_by_sim3(D.frame(c["kf1"], grid), D.frame(c["kf2"], grid), c, th, fc.SF)
         nr, mr = R.search_by_sim3(R.frame(c["kf1"], grid), R.frame(c["kf2"], grid), c, th, fc.SF)
         assert nd == nr > 150 and np.array_equal(md, mr)
+
+
+@pytest.mark.parametrize("seed,ori,nodes", [(331, False, 120), (332, True, 120), (333, False, 12), (334, False, 1000), (335, True, 1)])
+def test_search_for_triangulation(gm, seed, ori, nodes):
+    """ccm_search_triangulation vs the oracle (itself identical to the reference's SearchForTriangulation on these
+    seeds, tests/test_match_oracle_vs_ref.py): epipole gate, epipolar-line gate with the double-precision threshold
+    folded to a float bound, last-wins ties, features without node, rotation histogram."""
+    import _fuse_cases as fc
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    c = fc.tri_case(seed, n_nodes=nodes)
+    rng = np.random.default_rng(seed)
+    c["node1"][rng.random(len(c["node1"])) < 0.05] = -1
+    c["node2"][rng.random(len(c["node2"])) < 0.05] = -1
+    a, b = c["kf1"], c["kf2"]
+    nm_g, m_g = ORBmatcher(gm, 0.6, ori).SearchForTriangulation(
+        a["desc"], c["node1"], c["free1"], a["x"], a["y"], a["angle"], b["desc"], c["node2"], c["free2"], b["x"], b["y"],
+        b["octave"], b["angle"], c["f12"], c["ex"], c["ey"], fc.SF, fc.LEVEL_SIGMA2)
+    nm_c, m_c = OracleMatcher(0.6, ori).search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
+    assert nm_g == nm_c and np.array_equal(m_g, m_c)
+    assert nm_c > (20 if nodes == 1000 else 100)
+
+
+def test_search_for_triangulation_edges(gm):
+    import _fuse_cases as fc
+    from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+    c = fc.tri_case(340, n=64, n_nodes=4)
+    a, b = c["kf1"], c["kf2"]
+    g = ORBmatcher(gm, 0.6, False)
+
+    def run(cc):
+        aa, bb = cc["kf1"], cc["kf2"]
+        got = g.SearchForTriangulation(aa["desc"], cc["node1"], cc["free1"], aa["x"], aa["y"], aa["angle"], bb["desc"], cc["node2"],
+                                       cc["free2"], bb["x"], bb["y"], bb["octave"], bb["angle"], cc["f12"], cc["ex"], cc["ey"],
+                                       fc.SF, fc.LEVEL_SIGMA2)
+        want = OracleMatcher(0.6, False).search_for_triangulation(cc, fc.SF, fc.LEVEL_SIGMA2, False)
+        assert got[0] == want[0] and np.array_equal(got[1], want[1])
+        return got[0]
+
+    # degenerate F12 (den == 0 for every feature, :170-171): nothing matches
+    assert run(dict(c, f12=np.zeros(9, np.float32))) == 0
+    # no free feature on one side
+    assert run(dict(c, free2=np.zeros_like(c["free2"]))) == 0
+    # disjoint vocabularies
+    assert run(dict(c, node2=c["node2"] + 100)) == 0
+    # empty keyframe
+    empty = {k: v[:0] for k, v in b.items()}
+    assert run(dict(c, kf2=empty, node2=c["node2"][:0], free2=c["free2"][:0])) == 0
+    assert run(c) > 5
+
+
+def test_dropin_cpp_triangulation_matches_reference_class(cuda_lib):
+    import _oracle
+    import _fuse_cases as fc
+    if not (_oracle.dropin_match_available() and _oracle.ref_match_available()):
+        pytest.skip("oracle/_ref/libdropin_match.so not built (needs the reference headers at build time)")
+    for seed, ori, nodes in [(331, False, 120), (332, True, 120), (333, False, 12)]:
+        c = fc.tri_case(seed, n_nodes=nodes)
+        nd, md = _oracle.RefMatcher(0.6, ori, lib="libdropin_match.so").search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
+        nr, mr = _oracle.RefMatcher(0.6, ori).search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
+        assert nd == nr > 100 and np.array_equal(md, mr)

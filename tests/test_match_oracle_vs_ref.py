@@ -200,3 +200,16 @@ def test_search_by_sim3(seed, th):
     a2, b2 = _best(o1, 0.75, m2, c["u2"], c["v2"], c["l2"], c["d2"], th, 100)
     n_mine, m_mine = fc.replay_sim3(c, a1, b1, a2, b2, m1, m2)
     assert n_mine == n_ref > 150 and np.array_equal(m_mine, m_ref)
+
+
+@pytest.mark.parametrize("seed,ori,nodes", [(331, False, 120), (332, True, 120), (333, False, 12), (334, False, 1000)])
+def test_search_for_triangulation(seed, ori, nodes):
+    c = fc.tri_case(seed, n_nodes=nodes)
+    n_ref, m_ref = _oracle.RefMatcher(0.6, ori).search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
+    n_mine, m_mine = OracleMatcher(0.6, ori).search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
+    assert n_mine == n_ref and np.array_equal(m_mine, m_ref)
+    assert n_ref > (20 if nodes == 1000 else 100), n_ref
+    # every gate decides something: opening the epipolar gate, or moving the epipole away, changes the result
+    n_line, m_line = OracleMatcher(0.6, ori).search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2 * 1e6, ori)
+    n_epi, m_epi = OracleMatcher(0.6, ori).search_for_triangulation(dict(c, ex=-1e6, ey=-1e6), fc.SF, fc.LEVEL_SIGMA2, ori)
+    assert n_line > n_ref and not np.array_equal(m_epi, m_ref)
