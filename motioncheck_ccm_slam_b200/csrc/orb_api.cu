@@ -30,6 +30,7 @@ struct ccm_orb {
     // device arena
     std::vector<void*> allocs;
     uint4* d_cell_info = nullptr;
+    FastSmem fast_smem = {};
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
     ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
@@ -114,6 +115,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
     int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0;
     std::vector<uint4> cell_info;
+    int max_cw = 1, max_ch = 1;
     for (int l = 0; l < L; l++) {
         LevelDesc& D = T.l[l];
         D.w = (int)lrintf((float)cols * h->isf[l]);
@@ -138,7 +140,15 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
                 const int x0 = CCM_EDGE + j * D.wCell, y0 = CCM_EDGE + i * D.hCell;
                 const int cw = std::min(x0 + D.wCell, D.w - CCM_EDGE) - x0, ch = std::min(y0 + D.hCell, D.h - CCM_EDGE) - y0;
                 if (cw > 0 && ch > 0) cc += ((cw + 1) / 2) * ((ch + 1) / 2);
-                cell_info.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l, 0u));
+                // tile geometry of k_fast_cells: x0-3 = word-aligned gxa + shift; wpr words per tile row; the cell's pixels
+                // lie in aligned words [g0, g0+ngx) of a tile row; magic multipliers m with (i*m)>>20 == i/d for i < 4096
+                const int cwp = std::max(cw, 1), shift = (x0 - 3) & 3, wpr = (shift + cwp + 6 + 3) >> 2;
+                const int g0 = (3 + shift) >> 2, ngx = ((cwp + 2 + shift) >> 2) - g0 + 1;
+                auto magic = [](int d) { return (0x100000u + (uint32_t)d - 1) / (uint32_t)d; };
+                cell_info.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l,
+                                               (uint32_t)shift | ((uint32_t)wpr << 8) | ((uint32_t)g0 << 16) | ((uint32_t)ngx << 24)));
+                cell_info.push_back(make_uint4(magic(wpr), magic(cwp), magic(ngx), 0u));
+                max_cw = std::max(max_cw, cw); max_ch = std::max(max_ch, ch);
             }
         D.corner_cap = std::max(cc, 1); D.corner_off = corners; corners += align_up(D.corner_cap, 4);
         if (D.corner_cap > 0x7FFFF) { h->err = "image too large (corner capacity per level exceeds 2^19)"; return CCM_E_BADARG; }
@@ -178,6 +188,8 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         }
     }
     int rc;
+    h->fast_smem = fast_smem_layout(max_cw, max_ch);
+    CK(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if ((rc = dev_alloc(h, &h->d_cell_info, cell_info.size()))) return rc;
     CK(cudaMemcpy(h->d_cell_info, cell_info.data(), cell_info.size() * sizeof(uint4), cudaMemcpyHostToDevice));
     if ((rc = dev_alloc(h, &h->d_corners, (size_t)corners * B))) return rc;
@@ -244,7 +256,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
     // The blur depends only on the pyramid; the quadtree is one small CTA per (frame, level) and latency-bound. Outside
     // stage-timing mode the blur runs on a side stream next to the quadtree and joins before the descriptor stage.
     const bool fork = !st;
-    k_fast_cells<<<dim3(T.total_cells, n), 256, 0, s>>>(T, h->d_cell_info, A.corners, A.corner_count);
+    k_fast_cells<<<dim3(T.total_cells, n), FAST_THREADS, h->fast_smem.total, s>>>(T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem);
     h->launches++;
     if (st) CK(cudaEventRecord(h->ev[2], s));
     if (fork) CK(cudaEventRecord(LN.fork, s));

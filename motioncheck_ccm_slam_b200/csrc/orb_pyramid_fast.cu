@@ -99,19 +99,36 @@ __device__ __forceinline__ void list_append(bool pred, uint16_t val, uint16_t* l
     if (pred) list[base + __popc(ballot & ((1u << lane) - 1))] = val;
 }
 
-__global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ LevelTable T,
-                                                    const uint4* __restrict__ cell_info,  // per cell: x0|y0<<16, cw|ch<<16, level, 0
+#define FAST_THREADS 128
+// Dynamic shared memory, sized by the host for the largest cell of the configured shape (fast_smem_layout):
+// tile [max_ch + 6][FAST_TS] | score [max_ch + 2][FAST_SS] | cand [max_px] u16 | corn [max_px] u16
+struct FastSmem { int score_off, cand_off, corn_off, total; };
+static inline FastSmem fast_smem_layout(int max_cw, int max_ch) {
+    FastSmem m;
+    const int tile_bytes = ((max_ch + 6) * FAST_TS + 15) / 16 * 16;
+    const int score_bytes = ((max_ch + 2) * FAST_SS + 15) / 16 * 16;
+    const int list_bytes = (max_cw * max_ch * 2 + 15) / 16 * 16;
+    m.score_off = tile_bytes; m.cand_off = m.score_off + score_bytes; m.corn_off = m.cand_off + list_bytes;
+    m.total = m.corn_off + list_bytes;
+    return m;
+}
+
+__global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_constant__ LevelTable T,
+                                                    const uint4* __restrict__ cell_info,  // per cell 2 x uint4, see configure_shape
                                                     uint32_t* __restrict__ corners,      // [frames][corners_per_frame]
-                                                    int* __restrict__ corner_count) {    // [frames][CCM_MAX_LEVELS]
-    __shared__ __align__(16) uint8_t tile[FAST_TILE][FAST_TS];
-    __shared__ __align__(16) uint8_t score[FAST_SCORE_BYTES];   // [cell + 1-px zero ring][FAST_SS]
-    __shared__ uint16_t cand[FAST_MAX_CELL * FAST_MAX_CELL];
-    __shared__ uint16_t corn[FAST_MAX_CELL * FAST_MAX_CELL];
+                                                    int* __restrict__ corner_count,      // [frames][CCM_MAX_LEVELS]
+                                                    const FastSmem M) {
+    extern __shared__ __align__(16) uint8_t fast_smem[];
+    uint8_t* const tile = fast_smem;                                   // [ch + 6][FAST_TS]
+    uint8_t* const score = fast_smem + M.score_off;                    // [cell + 1-px zero ring][FAST_SS]
+    uint16_t* const cand = reinterpret_cast<uint16_t*>(fast_smem + M.cand_off);
+    uint16_t* const corn = reinterpret_cast<uint16_t*>(fast_smem + M.corn_off);
     __shared__ int n_cand, n_corn;
 
     const int f = blockIdx.y;
-    // detection block of this cell in level coordinates (host-built table: configure_shape, orb_api.cu)
-    const uint4 ci = __ldg(cell_info + blockIdx.x);
+    // detection block of this cell in level coordinates and the index-arithmetic constants of its tile
+    // (host-built table: configure_shape, orb_api.cu)
+    const uint4 ci = __ldg(cell_info + 2 * blockIdx.x), cj = __ldg(cell_info + 2 * blockIdx.x + 1);
     const int x0 = (int)(ci.x & 0xffff), y0 = (int)(ci.x >> 16), cw = (int)(ci.y & 0xffff), ch = (int)(ci.y >> 16), lvl = (int)ci.z;
     if (cw <= 0 || ch <= 0) return;          // clipped-away cell (the :962/:971 `continue`s)
     const LevelDesc& L = T.l[lvl];
@@ -119,30 +136,31 @@ __global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ L
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int tid = threadIdx.x;
     // (A) tile = cell + 3-px ring, loaded as aligned 32-bit words (rows are 32-B aligned, pitch a multiple of 32)
-    const int gx = x0 - 3, gxa = gx & ~3, shift = gx - gxa;
-    const int wpr = (shift + cw + 6 + 3) >> 2, th = ch + 6;           // words per tile row
-    const uint32_t wmagic = (0x100000u + wpr - 1) / wpr;              // i / wpr for i < 4096
-    for (int i = tid; i < wpr * th; i += 256) {
-        const int ty = (int)(((uint32_t)i * wmagic) >> 20), tx = i - ty * wpr;
-        const uint32_t v = *reinterpret_cast<const uint32_t*>(img + (size_t)(y0 - 3 + ty) * L.img_pitch + gxa + 4 * tx);
-        *reinterpret_cast<uint32_t*>(&tile[ty][4 * tx]) = v;
+    const int shift = (int)(ci.w & 3), wpr = (int)(ci.w >> 8) & 0xff;       // x0-3 = word-aligned gxa + shift; words per tile row
+    const int g0 = (int)(ci.w >> 16) & 0xff, ngx = (int)(ci.w >> 24);       // aligned 4-px words covering the cell: [g0, g0 + ngx)
+    const uint32_t wmagic = cj.x, cmagic = cj.y, gmagic = cj.z;             // i / wpr, i / cw, i / ngx for i < 4096
+    const int gxa = x0 - 3 - shift, th = ch + 6;
+    {
+        const uint8_t* src = img + (size_t)(y0 - 3) * L.img_pitch + gxa;
+        for (int i = tid; i < wpr * th; i += FAST_THREADS) {
+            const int ty = (int)(((uint32_t)i * wmagic) >> 20), tx = i - ty * wpr;
+            const uint32_t v = *reinterpret_cast<const uint32_t*>(src + ty * L.img_pitch + 4 * tx);
+            *reinterpret_cast<uint32_t*>(tile + ty * FAST_TS + 4 * tx) = v;
+        }
     }
-    for (int i = tid; i < FAST_SCORE_BYTES / 16; i += 256) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < ((ch + 2) * FAST_SS + 15) / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) { n_cand = 0; n_corn = 0; }
     __syncthreads();
 
-    const int npx = cw * ch;
-    const uint32_t cmagic = (0x100000u + cw - 1) / cw;                 // i / cw for i < 4096
     const int S = FAST_TS;
-    const int g0 = (3 + shift) >> 2, ngx = ((cw + 2 + shift) >> 2) - g0 + 1, ngrp = ngx * ch;   // aligned 4-px words covering the cell
-    const uint32_t gmagic = (0x100000u + ngx - 1) / ngx;              // i / ngx for i < 4096
+    const int ngrp = ngx * ch;
     int threshold = T.ini_th;
 #pragma unroll 1
     for (int pass = 0; pass < 2; pass++) {
         // (B) opposite-pair test on 4 pixels per thread (a 9-arc of the ring contains one pixel of every diametral pair,
         //     so |v-p0|<=t && |v-p8|<=t, or the same for p4/p12, rules a pixel out): aligned 32-bit tile words, byte SIMD
         const uint32_t t4 = (uint32_t)threshold * 0x01010101u;
-        for (int base = 0; base < ngrp; base += 256) {
+        for (int base = 0; base < ngrp; base += FAST_THREADS) {
             const int gi = base + tid;
             uint32_t nib = 0;
             int py = 0, pxb = 0;
@@ -150,7 +168,7 @@ __global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ L
                 py = (int)(((uint32_t)gi * gmagic) >> 20);
                 const int g = g0 + gi - py * ngx;
                 pxb = 4 * g - 3 - shift;                                      // pixel of byte 0 of this word
-                const uint32_t* rowc = reinterpret_cast<const uint32_t*>(&tile[py + 3][0]) + g;
+                const uint32_t* rowc = reinterpret_cast<const uint32_t*>(tile + (py + 3) * FAST_TS) + g;
                 const uint32_t cen = rowc[0], lft = rowc[-1], rgt = rowc[1];
                 const uint32_t up = rowc[-3 * (FAST_TS / 4)], dn = rowc[3 * (FAST_TS / 4)];
                 const uint32_t p4 = __funnelshift_r(cen, rgt, 24), p12 = __funnelshift_r(lft, cen, 8);
@@ -181,14 +199,14 @@ __global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ L
         __syncthreads();
         // (C) full FAST-9/16 segment test on the candidates
         const int nc = n_cand;
-        for (int base = 0; base < nc; base += 256) {
+        for (int base = 0; base < nc; base += FAST_THREADS) {
             const int j = base + tid;
             bool is_corner = false;
             int i = 0;
             if (j < nc) {
                 i = cand[j];
                 const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-                const uint8_t* c = &tile[py + 3][px + 3 + shift];
+                const uint8_t* c = tile + (py + 3) * FAST_TS + px + 3 + shift;
                 const int v = c[0], hi = v + threshold, lo = v - threshold;
                 int r[16];
                 r[0] = c[3 * S];       r[1] = c[3 * S + 1];   r[2] = c[2 * S + 2];   r[3] = c[S + 3];
@@ -205,10 +223,10 @@ __global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ L
         __syncthreads();
         // (D) cornerScore of the corners -> score map
         const int nk = n_corn;
-        for (int j = tid; j < nk; j += 256) {
+        for (int j = tid; j < nk; j += FAST_THREADS) {
             const int i = corn[j];
             const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-            const uint8_t* c = &tile[py + 3][px + 3 + shift];
+            const uint8_t* c = tile + (py + 3) * FAST_TS + px + 3 + shift;
             const int v = c[0];
             int d[16];
             d[0] = v - c[3 * S];       d[1] = v - c[3 * S + 1];   d[2] = v - c[2 * S + 2];   d[3] = v - c[S + 3];
@@ -220,7 +238,7 @@ __global__ void __launch_bounds__(256, 8) k_fast_cells(const __grid_constant__ L
         __syncthreads();
         // (E) non-maximum suppression over the corners, append survivors
         int found = 0;
-        for (int base = 0; base < nk; base += 256) {     // uniform trip count: ballots below need whole warps
+        for (int base = 0; base < nk; base += FAST_THREADS) {     // uniform trip count: ballots below need whole warps
             const int j = base + tid;
             bool keep = false;
             int px = 0, py = 0, s = 0;
