@@ -3,6 +3,9 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -245,41 +248,45 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
     cudaStream_t s = LN.s;
     const bool st = h->stage_timing && allow_timing && lane_id == 0;
     if (st) { int rc = collect_stage_times(h); if (rc != CCM_OK) return rc; }
-    CK(cudaMemsetAsync(A.corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
-    if (st) CK(cudaEventRecord(h->ev[0], s));
-    for (int l = 1; l < T.nlevels; l++) {
-        dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
-        k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
-        h->launches++;
-    }
-    if (st) CK(cudaEventRecord(h->ev[1], s));
     // The blur depends only on the pyramid; the quadtree is one small CTA per (frame, level) and latency-bound. Outside
     // stage-timing mode the blur runs on a side stream next to the quadtree and joins before the descriptor stage.
     const bool fork = !st;
-    k_fast_cells<<<dim3(T.total_cells, n), FAST_THREADS, h->fast_smem.total, s>>>(T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem);
-    h->launches++;
-    if (st) CK(cudaEventRecord(h->ev[2], s));
-    if (fork) CK(cudaEventRecord(LN.fork, s));
-    if (!fork) {
-        k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+    {
+        CK(cudaMemsetAsync(A.corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
+        if (st) CK(cudaEventRecord(h->ev[0], s));
+        for (int l = 1; l < T.nlevels; l++) {
+            dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
+            k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
+            h->launches++;
+        }
+        if (st) CK(cudaEventRecord(h->ev[1], s));
+        k_fast_cells<<<dim3(T.total_cells, n), FAST_THREADS, h->fast_smem.total, s>>>(T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem);
         h->launches++;
+        if (st) CK(cudaEventRecord(h->ev[2], s));
+        if (fork) CK(cudaEventRecord(LN.fork, s));
+        if (!fork) {
+            k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+            h->launches++;
+        }
+        if (st) CK(cudaEventRecord(h->ev[3], s));
     }
-    if (st) CK(cudaEventRecord(h->ev[3], s));
-    k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, A.corners, A.corner_count, A.node_of,
-                                                          A.level_kps, A.level_kp_count);
-    h->launches++;
-    if (fork) {
-        CK(cudaStreamWaitEvent(LN.aux, LN.fork, 0));
-        k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, LN.aux>>>(T);
+    {
+        k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, A.corners, A.corner_count, A.node_of,
+                                                              A.level_kps, A.level_kp_count);
         h->launches++;
-        CK(cudaEventRecord(LN.join, LN.aux));
+        if (fork) {
+            CK(cudaStreamWaitEvent(LN.aux, LN.fork, 0));
+            k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, LN.aux>>>(T);
+            h->launches++;
+            CK(cudaEventRecord(LN.join, LN.aux));
+            CK(cudaStreamWaitEvent(s, LN.join, 0));
+        }
+        if (st) CK(cudaEventRecord(h->ev[4], s));
+        k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, A.level_kps, A.level_kp_count,
+                                                                            (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
+        h->launches++;
+        if (st) { CK(cudaEventRecord(h->ev[5], s)); h->stage_pending = true; }
     }
-    if (fork) CK(cudaStreamWaitEvent(s, LN.join, 0));
-    if (st) CK(cudaEventRecord(h->ev[4], s));
-    k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, A.level_kps, A.level_kp_count,
-                                                                        (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
-    h->launches++;
-    if (st) { CK(cudaEventRecord(h->ev[5], s)); h->stage_pending = true; }
     CK(cudaGetLastError());
     return CCM_OK;
 }
@@ -430,6 +437,7 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     if (rows == 0 || cols == 0) { for (int f = 0; f < n; f++) out_n[f] = 0; return CCM_OK; }
     if (rows < 0 || cols < 0 || step < (size_t)cols) { h->err = "bad image geometry"; return CCM_E_BADARG; }
     if (n > h->cfg.max_batch) { h->err = "batch larger than max_batch"; return CCM_E_CAPACITY; }
+    const double t_call = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
     CK(cudaSetDevice(h->cfg.device));
     int rc = configure_shape(h, rows, cols);
     if (rc != CCM_OK) return rc;
@@ -441,8 +449,12 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     uint8_t* l0 = (uint8_t*)h->allocs[0];
     const size_t budget = (size_t)align_up(cols, 32);
     const bool flat = (step % 4 == 0) && step <= budget;
-    const size_t pitch = flat ? step : budget, stride = budget * rows;
     const size_t frame_bytes = step * (size_t)rows;
+    // frames that follow each other in host memory (a [n][rows][step] array) keep that layout on the device, so a whole
+    // sub-batch is ONE copy instead of one per frame
+    bool packed = flat && n > 1;
+    for (int f = 1; packed && f < n; f++) packed = imgs[f] == imgs[f - 1] + frame_bytes;
+    const size_t pitch = flat ? step : budget, stride = packed ? frame_bytes : budget * rows;
     if (!flat && h->stage_bytes < frame_bytes * h->cfg.max_batch) {
         CK(cudaStreamSynchronize(h->s_in));
         if (h->d_stage) cudaFree(h->d_stage);
@@ -451,14 +463,40 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
         h->stage_bytes = frame_bytes * h->cfg.max_batch;
     }
     const int cap = h->max_kps;
+    // sub-batch plan: first[c] .. first[c+1]
+    int first[CCM_MAX_CHUNKS + 1];
     int n_chunks = n <= 8 ? 1 : std::min(CCM_MAX_CHUNKS, std::min(4, n / 4));
-    const int per = (n + n_chunks - 1) / n_chunks;
-    n_chunks = (n + per - 1) / per;
+    if (const char* e = std::getenv("CCM_ORB_CHUNKS")) n_chunks = std::max(1, std::min(std::min(CCM_MAX_CHUNKS, n), std::atoi(e)));   // tuning knob
+    {
+        const int per = (n + n_chunks - 1) / n_chunks;
+        n_chunks = (n + per - 1) / per;
+        for (int c = 0; c <= n_chunks; c++) first[c] = std::min(c * per, n);
+    }
+    if (const char* e = std::getenv("CCM_ORB_CHUNK_PLAN")) {            // tuning knob: comma-separated sub-batch sizes
+        int c = 0, at = 0;
+        first[0] = 0;
+        while (*e && c < CCM_MAX_CHUNKS - 1 && at < n) {
+            const int v = std::atoi(e);
+            if (v <= 0) break;
+            at = std::min(n, at + v); first[++c] = at;
+            while (*e && *e != ',') e++;
+            if (*e == ',') e++;
+        }
+        if (at < n) first[++c] = n;
+        n_chunks = c;
+    }
     for (int f = 0; f < n; f++)
         if (!imgs[f]) { h->err = "null image in batch"; return CCM_E_BADARG; }
+    static const bool trace = std::getenv("CCM_ORB_TRACE") != nullptr;
+    static cudaEvent_t tev[1 + 3 * CCM_MAX_CHUNKS] = {};
+    if (trace) {
+        if (!tev[0]) for (auto& e : tev) cudaEventCreate(&e);
+        CK(cudaEventRecord(tev[0], h->s_in));
+    }
     for (int c = 0; c < n_chunks; c++) {
-        const int f0 = c * per, m = std::min(per, n - f0);
-        for (int f = f0; f < f0 + m; f++) {
+        const int f0 = first[c], m = first[c + 1] - f0;
+        if (packed) CK(cudaMemcpyAsync(l0 + f0 * stride, imgs[f0], frame_bytes * (size_t)(m - 1) + step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
+        for (int f = f0; f < f0 + m && !packed; f++) {
             if (flat) CK(cudaMemcpyAsync(l0 + f * stride, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
             else {
                 // rows that are not 4-byte multiples: one contiguous host->device copy into a staging area, then a
@@ -469,20 +507,29 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
             }
         }
         CK(cudaEventRecord(h->ev_in[c], h->s_in));
+        if (trace) CK(cudaEventRecord(tev[1 + 3 * c], h->s_in));
         const int ln = n_chunks > 1 ? (c & 1) : 0;
         CK(cudaStreamWaitEvent(h->lane[ln].s, h->ev_in[c], 0));
         rc = run_pipeline(h, m, l0, pitch, stride, h->d_kp + (size_t)f0 * cap, h->d_desc + (size_t)f0 * cap * 32, h->d_n + f0, cap, f0, n_chunks == 1, ln);
         if (rc != CCM_OK) return rc;
         CK(cudaEventRecord(h->ev_done[c], h->lane[ln].s));
+        if (trace) CK(cudaEventRecord(tev[2 + 3 * c], h->lane[ln].s));
         CK(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
         CK(cudaMemcpyAsync(h->h_n + f0, h->d_n + f0, sizeof(int) * m, cudaMemcpyDeviceToHost, h->s_out));
         CK(cudaMemcpyAsync(h->h_kp + (size_t)f0 * cap, h->d_kp + (size_t)f0 * cap, sizeof(ccm_keypoint) * (size_t)cap * m, cudaMemcpyDeviceToHost, h->s_out));
         CK(cudaMemcpyAsync(h->h_desc + (size_t)f0 * cap * 32, h->d_desc + (size_t)f0 * cap * 32, (size_t)32 * cap * m, cudaMemcpyDeviceToHost, h->s_out));
         CK(cudaEventRecord(h->ev_out[c], h->s_out));
+        if (trace) CK(cudaEventRecord(tev[3 + 3 * c], h->s_out));
     }
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_enq = trace ? now() : 0.0;
+    double t_wait = 0, t_copy = 0;
     for (int c = 0; c < n_chunks; c++) {
-        const int f0 = c * per, m = std::min(per, n - f0);
+        const int f0 = first[c], m = first[c + 1] - f0;
+        const double ta = trace ? now() : 0.0;
         CK(cudaEventSynchronize(h->ev_out[c]));
+        const double tb = trace ? now() : 0.0;
+        t_wait += tb - ta;
         for (int f = f0; f < f0 + m; f++) {
             const int cnt = h->h_n[f];
             out_n[f] = cnt;
@@ -496,6 +543,19 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     // the next call's copy-in must not overtake this call's kernels (they read the level-0 buffer)
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->lane[1].s));
+    if (trace) {
+        const double t_end = now();
+        fprintf(stderr, "[ccm_orb trace] enqueue %.3f ms, wait %.3f ms, scatter %.3f ms, total %.3f ms | device (ms after first copy starts):", t_enq - t_call, t_wait,
+                t_end - t_enq - t_wait, t_end - t_call);
+        for (int c = 0; c < n_chunks; c++) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, tev[0], tev[1 + 3 * c]); cudaEventElapsedTime(&b, tev[0], tev[2 + 3 * c]);
+            cudaEventElapsedTime(&d, tev[0], tev[3 + 3 * c]);
+            fprintf(stderr, " [in %.3f done %.3f out %.3f]", a, b, d);
+        }
+        fprintf(stderr, "\n");
+    }
+    (void)t_copy;
     return CCM_OK;
 }
 
