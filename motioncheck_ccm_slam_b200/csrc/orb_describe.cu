@@ -21,15 +21,28 @@ __device__ __forceinline__ uint32_t blur_load(const uint8_t* __restrict__ row, i
 }
 
 // four horizontal 7-tap sums of pixels x..x+3 from the words holding pixels x-4..x+7: eight unaligned 4-byte windows
-// (PRMT) and eight IDP4A with the packed 8.8 coefficients {18,34,48,56 | 48,34,18,0}
+// (PRMT) and eight IDP4A with the packed 8.8 coefficients {18,34,48,56 | 48,34,18,0}.
+// Right border (reflect-101): the taps reach at most pixels w..w+2 = pixels w-2, w-3, w-4. The row's last aligned word
+// (at wa = (w-1) & ~3, holding e = w - wa valid pixels) followed by those three pixels forms an 8-byte tail; the lane that
+// owns word wa takes (own, next) from it and the lane before takes next. Rows narrower than 16 px use a per-byte gather.
 __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint32_t own, int x, int x0, int w, int lane, uint32_t (&hs)[4]) {
     uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
     uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
     if (lane == 0 && x0 > 0) prev = *reinterpret_cast<const uint32_t*>(row + x - 4);
     if (lane == 31 && x + 4 < w) next = *reinterpret_cast<const uint32_t*>(row + x + 4);
-    if (x == 0 && 10 <= w) {
-        prev = __byte_perm(own, 0u, 0x1230);          // reflect-101 on the left: pixels -3,-2,-1 are pixels 3,2,1 of this word
-    } else if ((x - 3 < 0 || x + 6 >= w) && x < w) {   // lanes touching the right border: gather bytes x-4..x+7
+    const int wa = (w - 1) & ~3;
+    if (w >= 16) {
+        if (x == 0) prev = __byte_perm(own, 0u, 0x1230);   // reflect-101 on the left: pixels -3,-2,-1 are pixels 3,2,1 of this word
+        if (x + 4 >= wa && x <= wa) {                       // the two lanes whose windows reach past the last pixel
+            const int e = w - wa;                           // 1..4 valid pixels in the last word
+            const uint32_t last = *reinterpret_cast<const uint32_t*>(row + wa);
+            const uint32_t ext = (uint32_t)row[w - 2] | ((uint32_t)row[w - 3] << 8) | ((uint32_t)row[w - 4] << 16);
+            const unsigned long long tail = (e == 4 ? (unsigned long long)last : (unsigned long long)(last & ((1u << (8 * e)) - 1u))) |
+                                            ((unsigned long long)ext << (8 * e));
+            if (x == wa) { own = (uint32_t)tail; next = (uint32_t)(tail >> 32); }
+            else next = (uint32_t)tail;
+        }
+    } else if (x < w) {                                     // tiny rows: gather bytes x-4..x+7
         uint32_t wd[3] = {0u, 0u, 0u};
 #pragma unroll
         for (int k = 0; k < 12; k++) wd[k >> 2] |= (uint32_t)row[ccm_reflect101(min(x - 4 + k, w + 2), w)] << (8 * (k & 3));
@@ -44,7 +57,7 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint3
     hs[3] = __dp4a(own, C1, __dp4a(next, C2, 0u));
 }
 
-__global__ void __launch_bounds__(256, 4) k_blur_levels(const __grid_constant__ LevelTable T) {
+__global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ LevelTable T) {
     int lvl = 0;
 #pragma unroll 1
     while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].blur_tile_base) lvl++;
@@ -58,14 +71,17 @@ __global__ void __launch_bounds__(256, 4) k_blur_levels(const __grid_constant__ 
     const int w = L.w, h = L.h;
     if (wy0 >= h) return;                                    // warp-uniform
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
-    uint8_t* __restrict__ out = L.blur + (size_t)f * L.blur_stride;
+    const int pitch = L.img_pitch;
+    uint8_t* __restrict__ outp = L.blur + (size_t)f * L.blur_stride + (size_t)wy0 * L.blur_pitch + x;
     uint32_t ring[7][4];
-    // source row of window row r is wy0 + r - 3 (rows past the bottom only feed outputs that are never stored)
-    const uint8_t* row = img + (size_t)ccm_reflect101(min(wy0 - 3, h + 2), h) * L.img_pitch;
+    // source row of window row r is wy0 + r - 3 (rows past the bottom only feed outputs that are never stored).
+    // Strips that touch neither the top nor the bottom border step the row pointer; the others reflect per row.
+    const bool inner = wy0 >= 3 && wy0 + BLUR_RPW + 3 <= h;   // warp-uniform
+    const uint8_t* row = img + (size_t)ccm_reflect101(min(wy0 - 3, h + 2), h) * pitch;
     uint32_t own = blur_load(row, x, w);
 #pragma unroll
     for (int r = 0; r < BLUR_RPW + 6; r++) {
-        const uint8_t* row_n = img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * L.img_pitch;
+        const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
         const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
         blur_hrow(row, own, x, x0, w, lane, ring[r % 7]);
         row = row_n; own = own_n;
@@ -78,7 +94,8 @@ __global__ void __launch_bounds__(256, 4) k_blur_levels(const __grid_constant__ 
                                      48 * (ring[(r - 4) % 7][k] + ring[(r - 2) % 7][k]) + 56 * ring[(r - 3) % 7][k];
                 packed |= ((acc + 32768u) >> 16) << (8 * k);
             }
-            if (oy < h && x < w) *reinterpret_cast<uint32_t*>(out + (size_t)oy * L.blur_pitch + x) = packed;   // pitch multiple of 32: in-bounds
+            if (oy < h && x < w) *reinterpret_cast<uint32_t*>(outp) = packed;   // pitch multiple of 32: in-bounds
+            outp += L.blur_pitch;
         }
     }
 }
