@@ -39,6 +39,7 @@ struct LevelDesc {
     // resize tables for (l-1) -> l, device pointers (null for level 0)
     const int* xofs; const short* xcoef;   // w entries, 2 coefs each
     const int* yofs; const short* ycoef;   // h entries
+    const uint4* xgrp;                     // per group of 4 outputs, 2 x uint4 (k_resize_level); null: use the generic kernel
 };
 
 struct LevelTable {

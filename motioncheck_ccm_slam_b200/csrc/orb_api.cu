@@ -104,6 +104,28 @@ static void linear_table(int ssize, int dsize, std::vector<int>& ofs, std::vecto
     }
 }
 
+// k_resize_level's table for groups of 4 adjacent outputs: the taps of a group start at source pixel s0 = ofs[4g]; entry
+// = {s0 & ~3, 8 * (s0 & 3), 4 selector bytes (tap0 - s0) | (tap1 - s0) << 4, 0} {4 x (a0 | a1 << 16)}. Outputs past
+// the row end repeat the last pixel. Returns false when some group's taps do not fit in 8 bytes (scale factor > 2).
+static bool resize_group_table(int ssize, int dsize, const std::vector<int>& ofs, const std::vector<short>& coef, std::vector<uint4>& out) {
+    const int groups = (dsize + 3) / 4;
+    out.resize(2 * (size_t)groups);
+    for (int g = 0; g < groups; g++) {
+        const int s0 = ofs[4 * g];
+        uint32_t sel = 0, c[4];
+        for (int i = 0; i < 4; i++) {
+            const int x = std::min(4 * g + i, dsize - 1);
+            const int t0 = ofs[x] - s0, t1 = std::min(ofs[x] + 1, ssize - 1) - s0;
+            if (t0 < 0 || t1 < 0 || t0 > 7 || t1 > 7) return false;
+            sel |= (uint32_t)(t0 | (t1 << 4)) << (8 * i);
+            c[i] = (uint32_t)(uint16_t)coef[2 * x] | ((uint32_t)(uint16_t)coef[2 * x + 1] << 16);
+        }
+        out[2 * g] = make_uint4((uint32_t)(s0 & ~3), (uint32_t)(8 * (s0 & 3)), sel, 0u);
+        out[2 * g + 1] = make_uint4(c[0], c[1], c[2], c[3]);
+    }
+    return true;
+}
+
 // Level geometry for one image shape, following ComputePyramid (:1284-1286), ComputeKeyPointsOctTree (:941-955)
 // and DistributeOctTree (:711-713). Allocates the arena for cfg.max_batch frames of this shape.
 static int configure_shape(ccm_orb* h, int rows, int cols) {
@@ -188,6 +210,14 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
             CK(cudaMemcpy(dxa, xa.data(), xa.size() * sizeof(short), cudaMemcpyHostToDevice));
             CK(cudaMemcpy(dya, ya.data(), ya.size() * sizeof(short), cudaMemcpyHostToDevice));
             D.xofs = dxo; D.yofs = dyo; D.xcoef = dxa; D.ycoef = dya;
+            std::vector<uint4> grp;
+            D.xgrp = nullptr;
+            if (resize_group_table(T.l[l - 1].w, D.w, xo, xa, grp)) {
+                uint4* dg;
+                if ((rc = dev_alloc(h, &dg, grp.size()))) return rc;
+                CK(cudaMemcpy(dg, grp.data(), grp.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+                D.xgrp = dg;
+            }
         }
     }
     int rc;
@@ -256,7 +286,8 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[0], s));
         for (int l = 1; l < T.nlevels; l++) {
             dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
-            k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
+            if (T.l[l].xgrp) k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
+            else k_resize_level_generic<<<g, dim3(32, 8), 0, s>>>(T, l);
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[1], s));
@@ -422,6 +453,7 @@ int ccm_orb_extract_batch_device(ccm_orb* h, const uint8_t* d_imgs, int n, int r
                                  ccm_keypoint* d_kp, uint8_t* d_desc, int capacity, int* d_n) {
     if (!h) return CCM_E_BADARG;
     if (!d_imgs || !d_kp || !d_desc || !d_n || n < 1 || rows < 1 || cols < 1 || capacity < 1 || pitch < (size_t)cols) { h->err = "bad argument"; return CCM_E_BADARG; }
+    if (((uintptr_t)d_imgs | pitch | frame_stride) & 3) { h->err = "device images: base, pitch and frame stride must be multiples of 4 bytes"; return CCM_E_BADARG; }
     if (n > h->cfg.max_batch) { h->err = "batch larger than max_batch"; return CCM_E_CAPACITY; }
     CK(cudaSetDevice(h->cfg.device));
     int rc = configure_shape(h, rows, cols);

@@ -7,8 +7,49 @@
 // cslam/src/ORBextractor.cpp:1293 (ComputePyramid :1280-1304). Bit-exact 8U fixed-point bilinear:
 // horizontal taps scaled by 2048 into int32, vertical (((b0*(r0>>4))>>16)+((b1*(r1>>4))>>16)+2)>>2.
 // Each thread produces 4 horizontally adjacent pixels and stores one 32-bit word; a warp writes 128 B.
+// For scale factors <= 2 the source pixels of the 4 outputs span at most 8 bytes: the thread loads three aligned
+// words per source row, funnel-shifts them to the first tap, picks each output's two taps with one PRMT (selector
+// from the host-built group table) and forms a0*p0 + a1*p1 with one IDP2A. k_resize_level_generic (byte loads) covers
+// larger factors.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_resize_level(const __grid_constant__ LevelTable T, int lvl) {
+    const LevelDesc& D = T.l[lvl];
+    const LevelDesc& S = T.l[lvl - 1];
+    const int f = blockIdx.z;
+    const int g = blockIdx.x * 32 + threadIdx.x, x4 = g * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    if (y >= D.h || x4 >= D.w) return;
+    const uint8_t* __restrict__ src = S.img + (size_t)f * S.img_stride;
+    // group table (resize_group_table, orb_api.cu): {first tap's aligned byte offset, bit shift to the first tap,
+    // 4 x (tap0 | tap1 << 4) byte selectors, -} {4 x (a0 | a1 << 16)}
+    const uint4 ga = __ldg(D.xgrp + 2 * g), gc = __ldg(D.xgrp + 2 * g + 1);
+    const int base = (int)ga.x, wlim = S.w;                   // words starting at or beyond the row's last pixel are not read
+    const int sy0 = __ldg(D.yofs + y);
+    const int sy1 = min(sy0 + 1, S.h - 1);
+    const uint32_t b0 = (uint32_t)__ldg(D.ycoef + 2 * y), b1 = (uint32_t)__ldg(D.ycoef + 2 * y + 1);
+    const uint8_t* r0p = src + (size_t)sy0 * S.img_pitch + base;
+    const uint8_t* r1p = src + (size_t)sy1 * S.img_pitch + base;
+    const bool in1 = base + 4 < wlim, in2 = base + 8 < wlim;
+    const uint32_t u0 = *reinterpret_cast<const uint32_t*>(r0p), v0 = *reinterpret_cast<const uint32_t*>(r1p);
+    const uint32_t u1 = in1 ? *reinterpret_cast<const uint32_t*>(r0p + 4) : 0u, v1 = in1 ? *reinterpret_cast<const uint32_t*>(r1p + 4) : 0u;
+    const uint32_t u2 = in2 ? *reinterpret_cast<const uint32_t*>(r0p + 8) : 0u, v2 = in2 ? *reinterpret_cast<const uint32_t*>(r1p + 8) : 0u;
+    const uint32_t lo0 = __funnelshift_r(u0, u1, ga.y), hi0 = __funnelshift_r(u1, u2, ga.y);
+    const uint32_t lo1 = __funnelshift_r(v0, v1, ga.y), hi1 = __funnelshift_r(v1, v2, ga.y);
+    const uint32_t coef[4] = {gc.x, gc.y, gc.z, gc.w};
+    uint32_t packed = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const uint32_t sel = (ga.z >> (8 * i)) & 0xffu;
+        const uint32_t r0 = __dp2a_lo(coef[i], __byte_perm(lo0, hi0, sel), 0u);
+        const uint32_t r1 = __dp2a_lo(coef[i], __byte_perm(lo1, hi1, sel), 0u);
+        const uint32_t v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
+        packed |= (v & 255u) << (8 * i);
+    }
+    uint8_t* __restrict__ dst = D.img + (size_t)f * D.img_stride;
+    *reinterpret_cast<uint32_t*>(dst + (size_t)y * D.img_pitch + x4) = packed;   // pitch is a multiple of 32: in-bounds
+}
+
+__global__ void __launch_bounds__(256) k_resize_level_generic(const __grid_constant__ LevelTable T, int lvl) {
     const LevelDesc& D = T.l[lvl];
     const LevelDesc& S = T.l[lvl - 1];
     const int f = blockIdx.z;
