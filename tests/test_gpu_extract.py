@@ -69,7 +69,8 @@ def test_shapes_and_quotas(cuda_lib, w, h, nf, nl, seed):
 
 def test_other_scale_and_thresholds(cuda_lib):
     img = make_frame(23, 640, 480)
-    for args in [(800, 1.5, 4, 20, 7), (800, 1.1, 10, 30, 10), (800, 1.2, 8, 12, 12), (300, 2.0, 3, 40, 5)]:
+    for args in [(800, 1.5, 4, 20, 7), (800, 1.1, 10, 30, 10), (800, 1.2, 8, 12, 12), (300, 2.0, 3, 40, 5),
+                 (300, 2.6, 3, 20, 7), (400, 3.0, 2, 20, 7)]:      # factors > 2 take the generic resize kernel
         kp, desc = make(cuda_lib, *args, max_width=640, max_height=480)(img)
         ko, do = OracleExtractor(*args)(img)
         assert_same(kp, desc, ko, do, args)
