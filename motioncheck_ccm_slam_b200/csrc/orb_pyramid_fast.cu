@@ -130,14 +130,27 @@ __device__ __forceinline__ int fast_score16(const int (&d)[16]) {
 #define FAST_SS (FAST_MAX_CELL + 4)            // score row stride
 #define FAST_SCORE_BYTES (((FAST_MAX_CELL + 2) * FAST_SS + 15) / 16 * 16)
 
-__device__ __forceinline__ void list_append(bool pred, uint16_t val, uint16_t* list, int* count) {
+// Shared-memory list plumbing written as PTX on 32-bit shared addresses: one ATOMS per warp (nvcc otherwise wraps every
+// atomicAdd in its own warp-aggregation sequence) and predicated 16-bit stores instead of a branch per store.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t atoms_add(uint32_t saddr, uint32_t v) {
+    uint32_t r;
+    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(saddr), "r"(v) : "memory");
+    return r;
+}
+__device__ __forceinline__ void sts_u16_if(uint32_t pred, uint32_t saddr, uint32_t val) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.shared.u16 [%1], %2;\n\t}" ::"r"(pred), "r"(saddr), "h"((unsigned short)val) : "memory");
+}
+__device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
+
+// append val to a shared u16 list (byte address list_s, counter at count_s) for the lanes with pred set
+__device__ __forceinline__ void list_append(bool pred, uint32_t val, uint32_t list_s, uint32_t count_s) {
     const uint32_t ballot = __ballot_sync(0xffffffffu, pred);
     if (!ballot) return;
-    const int lane = threadIdx.x & 31;
-    int base = 0;
-    if (lane == 0) base = atomicAdd(count, __popc(ballot));
+    uint32_t base = 0;
+    if ((threadIdx.x & 31) == 0) base = atoms_add(count_s, __popc(ballot));
     base = __shfl_sync(0xffffffffu, base, 0);
-    if (pred) list[base + __popc(ballot & ((1u << lane) - 1))] = val;
+    sts_u16_if(pred, list_s + 2 * (base + __popc(ballot & lanemask_lt())), val);
 }
 
 #define FAST_THREADS 128
@@ -182,16 +195,22 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
     const uint32_t wmagic = cj.x, cmagic = cj.y, gmagic = cj.z;             // i / wpr, i / cw, i / ngx for i < 4096
     const int gxa = x0 - 3 - shift, th = ch + 6;
     {
-        const uint8_t* src = img + (size_t)(y0 - 3) * L.img_pitch + gxa;
-        for (int i = tid; i < wpr * th; i += FAST_THREADS) {
-            const int ty = (int)(((uint32_t)i * wmagic) >> 20), tx = i - ty * wpr;
-            const uint32_t v = *reinterpret_cast<const uint32_t*>(src + ty * L.img_pitch + 4 * tx);
-            *reinterpret_cast<uint32_t*>(tile + ty * FAST_TS + 4 * tx) = v;
+        // FAST_THREADS / wpr tile rows per sweep, one word per thread, pointers stepped by whole sweeps
+        const int rps = (int)((FAST_THREADS * wmagic) >> 20);
+        const int ty0 = (int)(((uint32_t)tid * wmagic) >> 20), tx = tid - ty0 * wpr;
+        if (ty0 < rps) {
+            const uint8_t* src = img + (size_t)(y0 - 3 + ty0) * L.img_pitch + gxa + 4 * tx;
+            uint8_t* dst = tile + ty0 * FAST_TS + 4 * tx;
+            const size_t sstep = (size_t)rps * L.img_pitch;
+            const int dstep = rps * FAST_TS;
+            for (int ty = ty0; ty < th; ty += rps, src += sstep, dst += dstep)
+                *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(src);
         }
     }
     for (int i = tid; i < ((ch + 2) * FAST_SS + 15) / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) { n_cand = 0; n_corn = 0; }
     __syncthreads();
+    const uint32_t cand_s = smem_addr(cand), corn_s = smem_addr(corn), ncand_s = smem_addr(&n_cand), ncorn_s = smem_addr(&n_corn);
 
     const int S = FAST_TS;
     const int ngrp = ngx * ch;
@@ -224,17 +243,17 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
             const uint32_t b0 = __ballot_sync(0xffffffffu, nib & 1u), b1 = __ballot_sync(0xffffffffu, nib & 2u);
             const uint32_t b2 = __ballot_sync(0xffffffffu, nib & 4u), b3 = __ballot_sync(0xffffffffu, nib & 8u);
             if (b0 | b1 | b2 | b3) {
-                const int lane = tid & 31;
-                const uint32_t lt = (1u << lane) - 1;
-                const int c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
-                int slot = 0;
-                if (lane == 0) slot = atomicAdd(&n_cand, c0 + c1 + c2 + c3);
+                const uint32_t lt = lanemask_lt();
+                const uint32_t c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
+                uint32_t slot = 0;
+                if ((tid & 31) == 0) slot = atoms_add(ncand_s, c0 + c1 + c2 + c3);
                 slot = __shfl_sync(0xffffffffu, slot, 0);
-                const int pi = py * cw + pxb;
-                if (nib & 1u) cand[slot + __popc(b0 & lt)] = (uint16_t)pi;
-                if (nib & 2u) cand[slot + c0 + __popc(b1 & lt)] = (uint16_t)(pi + 1);
-                if (nib & 4u) cand[slot + c0 + c1 + __popc(b2 & lt)] = (uint16_t)(pi + 2);
-                if (nib & 8u) cand[slot + c0 + c1 + c2 + __popc(b3 & lt)] = (uint16_t)(pi + 3);
+                const uint32_t a = cand_s + 2 * slot;
+                const uint32_t pi = (uint32_t)(py * cw + pxb);
+                sts_u16_if(nib & 1u, a + 2 * __popc(b0 & lt), pi);
+                sts_u16_if(nib & 2u, a + 2 * (c0 + __popc(b1 & lt)), pi + 1);
+                sts_u16_if(nib & 4u, a + 2 * (c0 + c1 + __popc(b2 & lt)), pi + 2);
+                sts_u16_if(nib & 8u, a + 2 * (c0 + c1 + c2 + __popc(b3 & lt)), pi + 3);
             }
         }
         __syncthreads();
@@ -259,7 +278,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
                 for (int k = 0; k < 16; k++) { dark |= (uint32_t)(r[k] < lo) << k; bright |= (uint32_t)(r[k] > hi) << k; }
                 is_corner = has_run9(dark) || has_run9(bright);
             }
-            list_append(is_corner, (uint16_t)i, corn, &n_corn);
+            list_append(is_corner, (uint32_t)i, corn_s, ncorn_s);
         }
         __syncthreads();
         // (D) cornerScore of the corners -> score map
