@@ -145,6 +145,25 @@ int ccm_search_triangulation(ccm_matcher* m, int check_orientation, const ccm_ep
                              int n_b, const uint8_t* desc_b, const int* node_b, const uint8_t* free_b, const float* x_b,
                              const float* y_b, const int* octave_b, const float* angle_b, int* match_a, int* nmatches);
 
+/* ---- vocabulary transform: the per-feature half of Frame::ComputeBoW (cslam/src/Frame.cpp:268-275) ----------
+ * mpORBvocabulary->transform(descriptors, mBowVec, mFeatVec, 4) descends the DBoW2 tree once per descriptor
+ * (thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1261: child at the smallest FORB::distance, first child on ties) and
+ * files the result in two std::maps. The descent runs here; the maps (double weights, :1143-1168) stay on the host.
+ * The tree is given as loadFromTextFile numbers it (:1338-1420): node 0 = root, child_start [n_nodes + 1] / child_ids
+ * [n_nodes - 1] = each node's children in file order, node_desc [n_nodes][32], node_word [n_nodes] = word id of a
+ * leaf (-1 otherwise), depth_levels = m_L. All HOST arrays, copied. */
+typedef struct ccm_vocabulary ccm_vocabulary;
+int ccm_vocabulary_create(ccm_matcher* m, int n_nodes, const int* child_start, const int* child_ids, const uint8_t* node_desc,
+                          const int* node_word, int depth_levels, ccm_vocabulary** out);
+void ccm_vocabulary_destroy(ccm_vocabulary* v);
+/* word [n] = word id of feature i, node [n] = the node `levelsup` levels above the leaves on its path (0 = root when
+ * depth_levels - levelsup <= 0, and when the path ends above that level, which upstream leaves undefined). */
+int ccm_vocabulary_transform(ccm_matcher* m, const ccm_vocabulary* v, int n, const uint8_t* desc, int levelsup, int* word, int* node);
+/* device-resident and asynchronous on the matcher's stream: d_desc [n][32] (16-byte aligned, e.g. the extractor's
+ * descriptor rows of a whole batch), d_word / d_node [n]. d_node is what ccm_search_bow takes as node_a / node_b. */
+int ccm_vocabulary_transform_device(ccm_matcher* m, const ccm_vocabulary* v, int n, const uint8_t* d_desc, int levelsup,
+                                    int* d_word, int* d_node);
+
 /* ---- server keyframe-database search (BASELINE.json configs[4]) --------------------------------------------
  * Best and second-best Hamming distance of every query descriptor over a (shard of a) target descriptor database,
  * first-wins on ties: the inner loop of SearchByBoW(KF,KF) (:607-637) with one all-inclusive node. */

@@ -88,6 +88,10 @@ SIGNATURES.update({
     "ccm_search_window": (_i, [_vp, _vp, _wp, _i, _vp, _vp, _vp, _vp, _ip]),
     "ccm_search_window_batch_device": (_i, [_vp, _c.POINTER(_vp), _i, _wp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "ccm_search_bow": (_i, [_vp, _i, _f, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ip]),
+    "ccm_vocabulary_create": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _c.POINTER(_vp)]),
+    "ccm_vocabulary_destroy": (None, [_vp]),
+    "ccm_vocabulary_transform": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
+    "ccm_vocabulary_transform_device": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
     "ccm_search_triangulation": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ip]),
     "ccm_match_allpairs_best2_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
     "ccm_match_allpairs_merge_device": (_i, [_vp, _vp, _i, _i, _f, _vp, _vp]),

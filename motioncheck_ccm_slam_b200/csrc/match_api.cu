@@ -501,6 +501,86 @@ int ccm_search_triangulation(ccm_matcher* m, int check_orientation, const ccm_ep
                            node_b, free_b, angle_b, match_a, nullptr, nullptr, nmatches, &t);
 }
 
+/* ---- vocabulary transform ------------------------------------------------------------------------------------ */
+struct ccm_vocabulary {
+    ccm_matcher* m = nullptr;
+    int n_nodes = 0, depth = 0;
+    void* base = nullptr;
+    VocabDev dev = {};
+};
+
+int ccm_vocabulary_create(ccm_matcher* m, int n_nodes, const int* child_start, const int* child_ids, const uint8_t* node_desc,
+                          const int* node_word, int depth_levels, ccm_vocabulary** out) {
+    if (!m || !out || n_nodes < 2 || !child_start || !child_ids || !node_desc || !node_word || depth_levels < 1) return CCM_E_BADARG;
+    *out = nullptr;
+    const int n_edges = n_nodes - 1;
+    if (child_start[0] != 0 || child_start[n_nodes] != n_edges || child_start[1] == 0) { m->err = "vocabulary: child lists must cover nodes 1..n-1 and the root must have children"; return CCM_E_BADARG; }
+    for (int i = 0; i < n_nodes; i++)
+        if (child_start[i + 1] < child_start[i] || child_start[i + 1] - child_start[i] > 65535) { m->err = "vocabulary: bad child_start"; return CCM_E_BADARG; }
+    for (int p = 0; p < n_edges; p++)
+        if (child_ids[p] < 1 || child_ids[p] >= n_nodes) { m->err = "vocabulary: child id out of range"; return CCM_E_BADARG; }
+    cudaSetDevice(m->device);
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_cs = 0, o_id = o_cs + up((size_t)(n_nodes + 1) * 4), o_desc = o_id + up((size_t)n_edges * 4),
+                 o_word = o_desc + up((size_t)n_edges * 32), total = o_word + up((size_t)n_nodes * 4);
+    std::vector<uint8_t> cdesc((size_t)n_edges * 32);
+    for (int p = 0; p < n_edges; p++) std::memcpy(&cdesc[(size_t)32 * p], node_desc + (size_t)32 * child_ids[p], 32);   // CSR order
+    ccm_vocabulary* v = new ccm_vocabulary();
+    v->m = m; v->n_nodes = n_nodes; v->depth = depth_levels;
+    cudaError_t e = cudaMalloc(&v->base, total);
+    if (e != cudaSuccess) { m->err = std::string("cudaMalloc(vocabulary): ") + cudaGetErrorString(e); delete v; return CCM_E_CUDA; }
+    uint8_t* b = (uint8_t*)v->base;
+    if ((e = cudaMemcpy(b + o_cs, child_start, (size_t)(n_nodes + 1) * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(b + o_id, child_ids, (size_t)n_edges * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(b + o_desc, cdesc.data(), cdesc.size(), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (e = cudaMemcpy(b + o_word, node_word, (size_t)n_nodes * 4, cudaMemcpyHostToDevice)) != cudaSuccess) {
+        m->err = std::string("cudaMemcpy(vocabulary): ") + cudaGetErrorString(e);
+        cudaFree(v->base); delete v;
+        return CCM_E_CUDA;
+    }
+    v->dev.child_start = (const int*)(b + o_cs); v->dev.child_id = (const int*)(b + o_id);
+    v->dev.child_desc = (const uint4*)(b + o_desc); v->dev.node_word = (const int*)(b + o_word);
+    *out = v;
+    return CCM_OK;
+}
+
+void ccm_vocabulary_destroy(ccm_vocabulary* v) {
+    if (!v) return;
+    cudaSetDevice(v->m->device);
+    cudaStreamSynchronize(v->m->stream);
+    cudaFree(v->base);
+    delete v;
+}
+
+int ccm_vocabulary_transform_device(ccm_matcher* m, const ccm_vocabulary* v, int n, const uint8_t* d_desc, int levelsup,
+                                    int* d_word, int* d_node) {
+    if (!m || !v || v->m != m || n < 0 || levelsup < 0 || (n > 0 && (!d_desc || !d_word || !d_node))) return CCM_E_BADARG;
+    if (n == 0) return CCM_OK;
+    if ((uintptr_t)d_desc & 15) { m->err = "descriptor array must be 16-byte aligned"; return CCM_E_BADARG; }
+    cudaSetDevice(m->device);
+    k_vocab_transform<<<(n + 7) / 8, 256, 0, m->stream>>>(v->dev, v->depth - levelsup, n, (const uint4*)d_desc, d_word, d_node);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_vocabulary_transform(ccm_matcher* m, const ccm_vocabulary* v, int n, const uint8_t* desc, int levelsup, int* word, int* node) {
+    if (!m || !v || v->m != m || n < 0 || levelsup < 0 || (n > 0 && (!desc || !word || !node))) return CCM_E_BADARG;
+    if (n == 0) return CCM_OK;
+    cudaSetDevice(m->device);
+    uint8_t* dd; int *dw, *dn;
+    int rc;
+    if ((rc = mbuf(m, MB_A, (size_t)n * 32, &dd))) return rc;
+    if ((rc = mbuf(m, MB_B, (size_t)n, &dw))) return rc;
+    if ((rc = mbuf(m, MB_C, (size_t)n, &dn))) return rc;
+    MCK(cudaMemcpyAsync(dd, desc, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+    if ((rc = ccm_vocabulary_transform_device(m, v, n, dd, levelsup, dw, dn))) return rc;
+    MCK(cudaMemcpyAsync(word, dw, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaMemcpyAsync(node, dn, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
 /* ---- server keyframe-database search ---------------------------------------------------------------------- */
 int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
                                     uint32_t index_base, ccm_best2* d_out) {

@@ -158,3 +158,39 @@ __global__ void __launch_bounds__(256) k_tri_search(BowJob J, TriGeom G, const i
         if (J.res_a) { MatchResultDev r; r.best_idx = b; r.best_dist = (int)(best >> 16); r.best_dist2 = 256; r.accepted = 1; J.res_a[a] = r; }
     }
 }
+
+// Vocabulary descent of Frame::ComputeBoW (cslam/src/Frame.cpp:268-275 -> DBoW2 TemplatedVocabulary::transform,
+// thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1261): per feature, from the root to a leaf through the child at the
+// smallest Hamming distance (first child wins ties), remembering the node passed at level nid_level = L - levelsup.
+// One warp per feature; the children of a node are stored contiguously (CSR order), lane c takes child c, so a level is
+// one coalesced read of k x 32 B and one warp min over (distance << 16 | child position). A k = 10, L = 6 vocabulary is
+// 35 MB: resident in the 126 MB L2 after the first batch.
+struct VocabDev {
+    const int* child_start;      // [n_nodes + 1]
+    const int* child_id;         // [n_nodes - 1] node id per CSR position
+    const uint4* child_desc;     // [n_nodes - 1][2] descriptor per CSR position
+    const int* node_word;        // [n_nodes] word id of a leaf, -1 for inner nodes
+};
+
+__global__ void __launch_bounds__(256) k_vocab_transform(VocabDev V, int nid_level, int n, const uint4* __restrict__ desc,
+                                                         int* __restrict__ word, int* __restrict__ node_out) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= n) return;
+    const uint4 q0 = __ldg(desc + 2 * (size_t)i), q1 = __ldg(desc + 2 * (size_t)i + 1);
+    int node = 0, nid = 0, level = 0;
+    for (;;) {
+        const int c0 = __ldg(V.child_start + node), c1 = __ldg(V.child_start + node + 1);
+        if (c1 == c0) break;                                                   // a node without children is a word (:1256)
+        ++level;
+        uint32_t best = 0xffffffffu;
+        for (int p = c0 + lane; p < c1; p += 32) {
+            const int d = hamming256(q0, q1, __ldg(V.child_desc + 2 * (size_t)p), __ldg(V.child_desc + 2 * (size_t)p + 1));
+            best = min(best, ((uint32_t)d << 16) | (uint32_t)min(p - c0, 0xffff));
+        }
+        best = __reduce_min_sync(0xffffffffu, best);
+        node = __ldg(V.child_id + c0 + (int)(best & 0xffffu));
+        if (level == nid_level) nid = node;
+    }
+    if (lane == 0) { word[i] = __ldg(V.node_word + node); node_out[i] = nid; }
+}

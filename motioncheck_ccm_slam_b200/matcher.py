@@ -292,6 +292,68 @@ class ORBmatcher:
         return nm.value, m12[:n1]
 
 
+class Vocabulary:
+    """Device copy of a DBoW2 vocabulary tree for the per-feature half of Frame::ComputeBoW (cslam/src/Frame.cpp:268-275).
+    `voc` = dict(child_start, child_ids, desc, word, weight, L) in loadFromTextFile's node numbering (synth.make_vocabulary
+    builds a seeded one; the ORBvoc.txt blob is absent from the reference checkout)."""
+
+    def __init__(self, matcher, voc):
+        c = np.ascontiguousarray
+        self.m = matcher
+        self.weight = c(voc["weight"], np.float64)
+        cs, ci, nd, wd = c(voc["child_start"], np.int32), c(voc["child_ids"], np.int32), c(voc["desc"], np.uint8), c(voc["word"], np.int32)
+        self.n_nodes = len(wd)
+        self._h = ctypes.c_void_p()
+        matcher._check(matcher._lib.ccm_vocabulary_create(matcher._h, self.n_nodes, cs.ctypes.data, ci.ctypes.data, nd.ctypes.data,
+                                                          wd.ctypes.data, int(voc["L"]), ctypes.byref(self._h)))
+        self.word_weight = np.zeros(int(wd.max()) + 1, np.float64)
+        self.word_weight[wd[wd >= 0]] = self.weight[wd >= 0]
+
+    def close(self):
+        if self._h:
+            self.m._lib.ccm_vocabulary_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def transform_features(self, desc, levelsup=4):
+        """-> (word [n], node [n]) per descriptor (TemplatedVocabulary.h:1218-1261)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(d)
+        word, node = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.int32)
+        self.m._check(self.m._lib.ccm_vocabulary_transform(self.m._h, self._h, n, d.ctypes.data, int(levelsup), word.ctypes.data, node.ctypes.data))
+        return word[:n], node[:n]
+
+    def transform_device(self, n, d_desc, d_word, d_node, levelsup=4):
+        """Raw device pointers; asynchronous on the matcher's stream."""
+        self.m._check(self.m._lib.ccm_vocabulary_transform_device(self.m._h, self._h, int(n), d_desc, int(levelsup), d_word, d_node))
+
+    def ComputeBoW(self, desc, levelsup=4):
+        """Frame::ComputeBoW: -> (bow_words, bow_values, fv_node per feature (-1: stopped word), fv_order). The descent runs
+        on the device; the two containers are filled on the host exactly as TemplatedVocabulary.h:1143-1168 does for the ORB
+        vocabulary's L1 / TF-IDF setting: weights added per word in feature order, then divided by the L1 norm summed in
+        word order (BowVector.cpp:28-41, 62-84)."""
+        word, node = self.transform_features(desc, levelsup)
+        wt = self.word_weight[word] if len(word) else np.zeros(0)
+        acc = {}
+        for i in range(len(word)):
+            if wt[i] > 0:
+                w = int(word[i])
+                acc[w] = acc[w] + float(wt[i]) if w in acc else float(wt[i])
+        words = sorted(acc)
+        norm = 0.0
+        for w in words:
+            norm += abs(acc[w])
+        vals = [acc[w] / norm if norm > 0.0 else acc[w] for w in words]
+        fv_node = np.where(wt > 0, node, -1).astype(np.int32)
+        order = [i for nd in sorted(set(fv_node[fv_node >= 0].tolist())) for i in np.nonzero(fv_node == nd)[0].tolist()]
+        return np.array(words, np.uint32), np.array(vals, np.float64), fv_node, np.array(order, np.int32)
+
+
 # ---- device-resident batch path (extractor output -> packs -> searches, no host round trip) ----------------------
 def packs_from_extractor_batch_device(packs, grid, d_kp, d_desc, d_n, kp_stride, d_xy_un=None):
     """packs[j] takes frame j of ORBextractor.extract_batch_device's output (raw device pointers); asynchronous."""

@@ -114,3 +114,52 @@ def bow_node_ids(desc, n_nodes=1000):
     SURVEY.md §8c): node = first 13 descriptor bits mod n_nodes, the same rule on both sides."""
     d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
     return (((d[:, 0].astype(np.int32) << 5) | (d[:, 1].astype(np.int32) >> 3)) % n_nodes).astype(np.int32)
+
+
+def make_vocabulary(seed, k=10, L=4, ragged=0.0, stop=0.02):
+    """A seeded stand-in for the ORB vocabulary (cslam/conf/ORBvoc.txt.zip is a missing blob): a k-ary tree
+    of depth L in the node numbering loadFromTextFile produces (TemplatedVocabulary.h:1338-1420: root = 0, nodes 1.. in file
+    order, word ids in file order of the leaves). A child descriptor is its parent's with a level-dependent number of bits
+    flipped, so descents are decided by small distance differences and ties occur. `ragged` = probability that an inner
+    node is cut short into a leaf or gets fewer than k children; `stop` = fraction of words with weight 0 (stopped words).
+    Returns dict(k, L, parent [n], is_leaf [n], desc [n][32], weight [n], word [n], child_start [n+1], child_ids) with n
+    counting the root (index 0; its descriptor and weight are unused)."""
+    rng = np.random.default_rng(seed)
+    parent, is_leaf, desc, level = [0], [0], [np.zeros(32, np.uint8)], [0]
+    frontier = [0]
+    root_desc = rng.integers(0, 256, 32, dtype=np.uint8)
+    for lvl in range(1, L + 1):
+        nxt = []
+        flips = max(256 >> (lvl + 1), 3)
+        for p in frontier:
+            base = root_desc if p == 0 else desc[p]
+            nk = k if (p == 0 or rng.random() >= ragged) else int(rng.integers(1, k + 1))
+            for _ in range(nk):
+                d = np.unpackbits(base).copy()
+                d[rng.choice(256, flips, replace=False)] ^= 1
+                leaf = lvl == L or (lvl > 1 and rng.random() < ragged * 0.5)
+                parent.append(p); is_leaf.append(int(leaf)); desc.append(np.packbits(d)); level.append(lvl)
+                if not leaf:
+                    nxt.append(len(parent) - 1)
+        frontier = nxt
+    n = len(parent)
+    parent = np.array(parent, np.int32); is_leaf = np.array(is_leaf, np.uint8); desc = np.stack(desc).astype(np.uint8)
+    weight = np.where(is_leaf > 0, rng.uniform(0.5, 9.0, n), 0.0)
+    weight[(is_leaf > 0) & (rng.random(n) < stop)] = 0.0
+    word = np.full(n, -1, np.int32)
+    word[is_leaf > 0] = np.arange(int(is_leaf.sum()), dtype=np.int32)
+    order = np.argsort(parent[1:], kind="stable") + 1          # children of a node in file order
+    counts = np.bincount(parent[1:], minlength=n)
+    child_start = np.zeros(n + 1, np.int32); child_start[1:] = np.cumsum(counts)
+    return dict(k=k, L=L, parent=parent, is_leaf=is_leaf, desc=desc, weight=weight, word=word,
+                child_start=child_start, child_ids=order.astype(np.int32), level=np.array(level, np.int32))
+
+
+def write_vocabulary_text(voc, path):
+    """ORB-SLAM's vocabulary text format (TemplatedVocabulary.h:1338-1420, 1423-1447): 'k L scoring weighting', then one line
+    per node 'parent isLeaf b0 .. b31 weight'. No newline after the last node: the loader's while(!eof) loop would otherwise
+    parse one more, empty, node. Scoring 0 = L1_NORM, weighting 0 = TF_IDF (the ORB vocabulary's header)."""
+    with open(path, "w") as f:
+        f.write("%d %d 0 0" % (voc["k"], voc["L"]))
+        for i in range(1, len(voc["parent"])):
+            f.write("\n%d %d %s %r" % (voc["parent"][i], voc["is_leaf"][i], " ".join(str(int(b)) for b in voc["desc"][i]), float(voc["weight"][i])))

@@ -505,6 +505,36 @@ int mo_search_for_triangulation(int n1, const uint8_t* desc1, const int* node1, 
     return nmatches;
 }
 
+/* DBoW2 TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup), thirdparty/DBoW2/DBoW2/
+ * TemplatedVocabulary.h:1218-1261 — the per-feature half of Frame::ComputeBoW (cslam/src/Frame.cpp:268-275, levelsup 4):
+ * from the root, move to the child at the smallest FORB::distance (Hamming, FORB.cpp:103-121; the FIRST child wins ties)
+ * until a node without children; nid = the node reached at level L - levelsup (0 = root if that level is <= 0). If the
+ * descent ends ABOVE that level upstream never assigns nid (the batch caller then reads an uninitialised local, :1150-1154:
+ * undefined, and impossible with the complete ORB vocabulary); 0 is returned here. The tree comes as CSR children lists in file order
+ * (loadFromTextFile, :1338-1420). */
+void mo_vocab_transform(const int* child_start, const int* child_ids, const uint8_t* node_desc, const double* node_weight,
+                        const int* node_word, int L, int n, const uint8_t* desc, int levelsup, int* word, double* weight, int* node) {
+    const int nid_level = L - levelsup;
+    for (int i = 0; i < n; i++) {
+        const uint8_t* f = desc + (size_t)32 * i;
+        int nid = 0, final_id = 0, current_level = 0;
+        do {
+            ++current_level;
+            const int c0 = child_start[final_id], c1 = child_start[final_id + 1];
+            int best = child_ids[c0];
+            int best_d = descriptor_distance(f, node_desc + (size_t)32 * best);
+            for (int c = c0 + 1; c < c1; c++) {
+                const int id = child_ids[c];
+                const int d = descriptor_distance(f, node_desc + (size_t)32 * id);
+                if (d < best_d) { best_d = d; best = id; }
+            }
+            final_id = best;
+            if (current_level == nid_level) nid = final_id;
+        } while (child_start[final_id + 1] > child_start[final_id]);
+        word[i] = node_word[final_id]; weight[i] = node_weight[final_id]; node[i] = nid;
+    }
+}
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), ORBmatcher.cpp:448-563.
  * f2 = grid of F2; F1 is given by its arrays. prev_xy[2*n1] in/out (vbPrevMatched). */
 int mo_search_for_initialization(int n1, const uint8_t* desc1, const int* octave1, const float* angle1, float* prev_xy,

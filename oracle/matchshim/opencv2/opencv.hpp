@@ -43,6 +43,7 @@ public:
         buf = std::make_shared<std::vector<unsigned char>>((size_t)r * step, 0);
         data = buf->data();
     }
+    void release() { rows = cols = 0; step = 0; data = nullptr; buf.reset(); }
     static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }
     static Mat eye(int r, int c, int type) { Mat m(r, c, type); for (int i = 0; i < r && i < c; i++) m.at<float>(i, i) = 1.f; return m; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }

@@ -449,3 +449,80 @@ class RefMatcher:
 
     def search_for_triangulation(self, c, sf, level_sigma2, ori):
         return _triangulation(self.L, self.L.rm_search_for_triangulation, c, sf, level_sigma2, ori)
+
+
+# ---- vocabulary transform (Frame::ComputeBoW) ------------------------------------------------------------------------
+def ref_vocab_available():
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_vocab.so"))
+
+
+class RefVocabulary:
+    """The vendored DBoW2 (oracle/_ref/libref_vocab.so) loaded from a vocabulary text file."""
+
+    def __init__(self, path):
+        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", "libref_vocab.so"))
+        L.rv_load.restype = _vp; L.rv_load.argtypes = [_c.c_char_p]
+        L.rv_free.argtypes = [_vp]; L.rv_words.argtypes = [_vp]
+        L.rv_transform.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp]
+        L.rv_transform_features.argtypes = [_vp, _i, _vp, _i, _vp, _vp, _vp]
+        self.L = L
+        self.h = L.rv_load(path.encode())
+        if not self.h:
+            raise RuntimeError("reference vocabulary failed to load " + path)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.rv_free(self.h); self.h = None
+
+    def words(self):
+        return self.L.rv_words(self.h)
+
+    def transform(self, desc, levelsup=4):
+        """-> (bow_words, bow_values, fv_node per feature, fv_order)"""
+        d = _a(desc, np.uint8).reshape(-1, 32); n = len(d)
+        nb, nf = _c.c_int(), _c.c_int()
+        bw, bv = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64)
+        node, order = np.full(max(n, 1), -7, np.int32), np.zeros(max(n, 1), np.int32)
+        self.L.rv_transform(self.h, n, d.ctypes.data, levelsup, _c.byref(nb), bw.ctypes.data, bv.ctypes.data, node.ctypes.data,
+                            _c.byref(nf), order.ctypes.data)
+        return bw[:nb.value], bv[:nb.value], node[:n], order[:nf.value]
+
+    def transform_features(self, desc, levelsup=4):
+        d = _a(desc, np.uint8).reshape(-1, 32); n = len(d)
+        w, wt, nd = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64), np.zeros(max(n, 1), np.uint32)
+        self.L.rv_transform_features(self.h, n, d.ctypes.data, levelsup, w.ctypes.data, wt.ctypes.data, nd.ctypes.data)
+        return w[:n].astype(np.int32), wt[:n], nd[:n].astype(np.int32)
+
+
+def oracle_vocab_transform(voc, desc, levelsup=4):
+    """oracle/match_oracle.cpp mo_vocab_transform on a synth.make_vocabulary dict -> (word, weight, node) per feature."""
+    L = match_lib()
+    d = _a(desc, np.uint8).reshape(-1, 32); n = len(d)
+    cs, ci, nd, nw, wd = (_a(voc["child_start"], np.int32), _a(voc["child_ids"], np.int32), _a(voc["desc"], np.uint8),
+                          _a(voc["weight"], np.float64), _a(voc["word"], np.int32))
+    word, weight, node = np.zeros(max(n, 1), np.int32), np.zeros(max(n, 1), np.float64), np.zeros(max(n, 1), np.int32)
+    L.mo_vocab_transform.argtypes = [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _vp, _vp, _vp]
+    L.mo_vocab_transform.restype = None
+    L.mo_vocab_transform(cs.ctypes.data, ci.ctypes.data, nd.ctypes.data, nw.ctypes.data, wd.ctypes.data, int(voc["L"]), n, d.ctypes.data,
+                         int(levelsup), word.ctypes.data, weight.ctypes.data, node.ctypes.data)
+    return word[:n], weight[:n], node[:n]
+
+
+def assemble_bow(word, weight, node):
+    """The container half of TemplatedVocabulary::transform(features, BowVector, FeatureVector, levelsup) for L1 / TF-IDF
+    (TemplatedVocabulary.h:1143-1168, BowVector.cpp:28-41, 60-84): features with weight > 0 add their weight to their word
+    in feature order (repeated double additions), then the vector is divided by its L1 norm accumulated in word order;
+    the FeatureVector lists those features per node."""
+    acc = {}
+    for i in range(len(word)):
+        if weight[i] > 0:
+            w = int(word[i])
+            acc[w] = acc[w] + float(weight[i]) if w in acc else float(weight[i])
+    words = sorted(acc)
+    norm = 0.0
+    for w in words:
+        norm += abs(acc[w])
+    vals = [acc[w] / norm if norm > 0.0 else acc[w] for w in words]
+    fv_node = np.where(np.asarray(weight) > 0, node, -1).astype(np.int32)
+    order = [i for nd in sorted(set(fv_node[fv_node >= 0].tolist())) for i in np.nonzero(fv_node == nd)[0].tolist()]
+    return np.array(words, np.uint32), np.array(vals, np.float64), fv_node, np.array(order, np.int32)

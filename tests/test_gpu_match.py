@@ -495,3 +495,49 @@ def test_dropin_cpp_triangulation_matches_reference_class(cuda_lib):
         nd, md = _oracle.RefMatcher(0.6, ori, lib="libdropin_match.so").search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
         nr, mr = _oracle.RefMatcher(0.6, ori).search_for_triangulation(c, fc.SF, fc.LEVEL_SIGMA2, ori)
         assert nd == nr > 100 and np.array_equal(md, mr)
+
+
+@pytest.mark.parametrize("seed,k,L,ragged,levelsup", [(1, 10, 4, 0.0, 2), (2, 10, 3, 0.15, 4), (3, 6, 5, 0.1, 4), (4, 10, 4, 0.0, 0),
+                                                      (5, 3, 6, 0.2, 4), (6, 10, 2, 0.0, 1), (7, 20, 3, 0.0, 1), (8, 40, 2, 0.3, 1)])
+def test_vocabulary_transform(gm, seed, k, L, ragged, levelsup):
+    """ccm_vocabulary_transform vs the oracle (identical to the vendored DBoW2 on seeds 1-6, tests/test_vocab_oracle_vs_ref.py):
+    word and node ids per feature, then the BowVector / FeatureVector Frame::ComputeBoW fills, bit for bit."""
+    import _oracle
+    from motioncheck_ccm_slam_b200.matcher import Vocabulary
+    from motioncheck_ccm_slam_b200.synth import make_vocabulary, perturb_descriptors
+    voc = make_vocabulary(seed, k, L, ragged)
+    rng = np.random.default_rng(seed + 100)
+    leaves = np.nonzero(voc["is_leaf"])[0]
+    desc = perturb_descriptors(rng, voc["desc"][rng.choice(leaves, 1500)], 0.04)
+    desc[:150] = rng.integers(0, 256, (150, 32), dtype=np.uint8)
+    V = Vocabulary(gm, voc)
+    w_g, n_g = V.transform_features(desc, levelsup)
+    w_o, wt_o, n_o = _oracle.oracle_vocab_transform(voc, desc, levelsup)
+    assert np.array_equal(w_g, w_o) and np.array_equal(n_g, n_o)
+    bw_g, bv_g, fn_g, fo_g = V.ComputeBoW(desc, levelsup)
+    bw_o, bv_o, fn_o, fo_o = _oracle.assemble_bow(w_o, wt_o, n_o)
+    assert np.array_equal(bw_g, bw_o) and np.array_equal(bv_g.view(np.uint64), bv_o.view(np.uint64))
+    assert np.array_equal(fn_g, fn_o) and np.array_equal(fo_g, fo_o)
+    assert len(V.transform_features(desc[:0], levelsup)[0]) == 0
+    V.close()
+
+
+def test_vocabulary_transform_vs_reference_dbow2(gm, tmp_path):
+    """Straight against the reference's own DBoW2 (compiled unmodified, oracle/_ref/libref_vocab.so) where it was built."""
+    import _oracle
+    if not _oracle.ref_vocab_available():
+        pytest.skip("oracle/_ref/libref_vocab.so not built")
+    from motioncheck_ccm_slam_b200.matcher import Vocabulary
+    from motioncheck_ccm_slam_b200.synth import make_vocabulary, perturb_descriptors, write_vocabulary_text
+    voc = make_vocabulary(21, 10, 4)
+    path = str(tmp_path / "voc.txt")
+    write_vocabulary_text(voc, path)
+    R = _oracle.RefVocabulary(path)
+    rng = np.random.default_rng(5)
+    desc = perturb_descriptors(rng, voc["desc"][rng.choice(np.nonzero(voc["is_leaf"])[0], 2000)], 0.05)
+    V = Vocabulary(gm, voc)
+    bw_g, bv_g, fn_g, fo_g = V.ComputeBoW(desc, 2)
+    bw_r, bv_r, fn_r, fo_r = R.transform(desc, 2)
+    assert np.array_equal(bw_g, bw_r) and np.array_equal(bv_g.view(np.uint64), bv_r.view(np.uint64))
+    assert np.array_equal(fn_g, fn_r) and np.array_equal(fo_g, fo_r) and len(bw_r) > 500
+    V.close()
