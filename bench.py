@@ -291,6 +291,35 @@ def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d
                        "matches_per_frame_lastframe": float(nm[0, 1:].mean()), "matches_per_frame_mappoints": float(nm[1, 2:].mean()),
                        "matcher_launches_per_step": (m.launch_count() - l0) / args.steps}
     out["_launches"] = ap_launches + (m.launch_count() - l0)
+
+    # ---- (3) Frame::ComputeBoW's vocabulary descent on the last batch's descriptor rows, in place ----
+    from motioncheck_ccm_slam_b200.matcher import Vocabulary
+    from motioncheck_ccm_slam_b200.synth import make_vocabulary_complete
+    voc = make_vocabulary_complete(77, 10, 6)           # the ORB vocabulary's shape (k = 10, L = 6); the blob itself is missing
+    V = Vocabulary(m, voc)
+    d_word = torch.zeros((B * cap,), dtype=torch.int32, device=dev)
+    d_node = torch.zeros((B * cap,), dtype=torch.int32, device=dev)
+    n_feat = int(d_n.sum().item())
+    for _ in range(3):
+        V.transform_device(B * cap, d_desc.data_ptr(), d_word.data_ptr(), d_node.data_ptr(), 4)
+    m.sync(); barrier()
+    l0 = m.launch_count()
+    with torch.cuda.stream(ms):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(ksteps):
+            V.transform_device(B * cap, d_desc.data_ptr(), d_word.data_ptr(), d_node.data_ptr(), 4)
+        e1.record()
+    m.sync(); barrier()
+    bow_ms = e0.elapsed_time(e1) / ksteps
+    out["_launches"] += m.launch_count() - l0
+    out["bow_transform"] = {"what": "DBoW2 transform(levelsup 4) descent of every descriptor row of a %d-frame batch (%d rows, %d keypoints), "
+                                    "descriptors read in place from the extractor's output" % (B, B * cap, n_feat),
+                            "vocabulary": "synthetic k=10 L=6, %d nodes, %.1f MB of node descriptors (L2-resident)" % (len(voc["word"]), (len(voc["word"]) - 1) * 32 / 1e6),
+                            "ms_per_step": bow_ms, "descriptors_per_s": B * cap * world / (bow_ms * 1e-3),
+                            "distances_per_s": B * cap * world * 60 / (bow_ms * 1e-3)}
+    out["_voc"] = voc
+    V.close()
     for p in packs:
         p.close()
     m.close()
@@ -498,6 +527,14 @@ def run_ours(args, wl, rank, world, local_rank):
         line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                                 "sample": "%d threads x %d frames of the same stream, %.1f s" % (cores, fpt, dt)}
         if ham:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            from _oracle import oracle_vocab_transform
+            rngb = np.random.default_rng(3)
+            db = rngb.integers(0, 256, (20000, 32), dtype=np.uint8)
+            t0 = time.perf_counter()
+            oracle_vocab_transform(ham["_voc"], db, 4)
+            line["cpu_baseline"]["bow_transform"] = {"descriptors_per_s": len(db) / (time.perf_counter() - t0), "cores": 1, "kind": "port",
+                                                     "sample": "20000 uniform descriptors through the same vocabulary"}
             pps, nmm = cpu_matcher_baseline(frames[0], nf, nl)
             line["cpu_baseline"]["matcher"] = {
                 "tracking_searches_frame_pairs_per_s": pps, "matches_per_pair": nmm, "allpairs_gpairs_per_s": cpu_allpairs_baseline(),

@@ -163,3 +163,37 @@ def write_vocabulary_text(voc, path):
         f.write("%d %d 0 0" % (voc["k"], voc["L"]))
         for i in range(1, len(voc["parent"])):
             f.write("\n%d %d %s %r" % (voc["parent"][i], voc["is_leaf"][i], " ".join(str(int(b)) for b in voc["desc"][i]), float(voc["weight"][i])))
+
+
+def make_vocabulary_complete(seed, k=10, L=6):
+    """make_vocabulary's complete-tree case, vectorised per level (a k = 10, L = 6 tree has 1.1 M nodes): the same node
+    numbering (level by level, children of a node adjacent), word ids in node order of the leaves, weights in [0.5, 9)."""
+    rng = np.random.default_rng(seed)
+    descs = [np.zeros((1, 32), np.uint8)]
+    parents = [np.zeros(1, np.int32)]
+    cur = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+    first = 0                                     # node id of cur[0]
+    n_total = 1
+    for lvl in range(1, L + 1):
+        flips = max(256 >> (lvl + 1), 3)
+        n = len(cur) * k
+        child = np.repeat(cur, k, axis=0)
+        for c0 in range(0, n, 1 << 16):
+            c1 = min(n, c0 + (1 << 16))
+            bits = np.zeros((c1 - c0, 256), np.uint8)
+            np.put_along_axis(bits, rng.integers(0, 256, (c1 - c0, flips)), 1, axis=1)
+            child[c0:c1] ^= np.packbits(bits, axis=1)
+        parents.append(np.repeat(np.arange(first, first + len(cur), dtype=np.int32), k))
+        descs.append(child)
+        first, cur = n_total, child
+        n_total += n
+    desc = np.concatenate(descs); parent = np.concatenate(parents)
+    n = len(parent)
+    is_leaf = np.zeros(n, np.uint8); is_leaf[first:] = 1
+    weight = np.zeros(n); weight[first:] = rng.uniform(0.5, 9.0, n - first)
+    word = np.full(n, -1, np.int32); word[first:] = np.arange(n - first, dtype=np.int32)
+    child_start = np.zeros(n + 1, np.int32)
+    child_start[1:first + 1] = (np.arange(first, dtype=np.int64) + 1) * k
+    child_start[first + 1:] = n - 1
+    return dict(k=k, L=L, parent=parent, is_leaf=is_leaf, desc=desc, weight=weight, word=word, child_start=child_start,
+                child_ids=np.arange(1, n, dtype=np.int32))
