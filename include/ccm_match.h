@@ -164,6 +164,13 @@ int ccm_vocabulary_transform(ccm_matcher* m, const ccm_vocabulary* v, int n, con
 int ccm_vocabulary_transform_device(ccm_matcher* m, const ccm_vocabulary* v, int n, const uint8_t* d_desc, int levelsup,
                                     int* d_word, int* d_node);
 
+/* ---- MapPoint::ComputeDistinctiveDescriptors (cslam/src/MapPoint.cpp:929-994), batched ----------------------
+ * Map point p owns descriptor rows [start[p], start[p+1]) of desc (the descriptors of its observations in the
+ * caller's iteration order; at most 65535 per point). best[p] = index within its rows of the descriptor with the
+ * least median distance to the others (the sorted row's element at int(0.5*(N-1)), self-distance included, first
+ * minimum wins), -1 for a point without rows; best_median[p] = that median (may be NULL). HOST arrays. */
+int ccm_distinctive_descriptors(ccm_matcher* m, int n_points, const int* start, const uint8_t* desc, int* best, int* best_median);
+
 /* ---- server keyframe-database search (BASELINE.json configs[4]) --------------------------------------------
  * Best and second-best Hamming distance of every query descriptor over a (shard of a) target descriptor database,
  * first-wins on ties: the inner loop of SearchByBoW(KF,KF) (:607-637) with one all-inclusive node. */

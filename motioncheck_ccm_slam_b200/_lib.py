@@ -92,6 +92,7 @@ SIGNATURES.update({
     "ccm_vocabulary_destroy": (None, [_vp]),
     "ccm_vocabulary_transform": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
     "ccm_vocabulary_transform_device": (_i, [_vp, _vp, _i, _vp, _i, _vp, _vp]),
+    "ccm_distinctive_descriptors": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "ccm_search_triangulation": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ip]),
     "ccm_match_allpairs_best2_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
     "ccm_match_allpairs_merge_device": (_i, [_vp, _vp, _i, _i, _f, _vp, _vp]),

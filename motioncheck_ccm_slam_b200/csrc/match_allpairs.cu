@@ -136,3 +136,33 @@ __global__ void k_descriptor_distance(const uint4* __restrict__ a, const uint4* 
     if (i >= n) return;
     out[i] = hamming256(a[2 * (size_t)i], a[2 * (size_t)i + 1], b[2 * (size_t)i], b[2 * (size_t)i + 1]);
 }
+
+// MapPoint::ComputeDistinctiveDescriptors (cslam/src/MapPoint.cpp:929-994), batched over map points: among the
+// descriptors of a point's observations, the one whose sorted row of Hamming distances to all of them (its own 0
+// included) has the least element at index int(0.5 * (N - 1)); the first such row wins. One warp per map point, one lane
+// per row (strided for N > 32). The k-th smallest of a row is found by bisection on the value range [0, 256]: 9 counting
+// passes over the point's descriptors, which every lane reads at the same address (one broadcast transaction), so no
+// distance matrix is stored.
+__global__ void __launch_bounds__(256) k_distinctive(const int* __restrict__ start, const uint4* __restrict__ desc, int n_points,
+                                                     int* __restrict__ best, int* __restrict__ best_median) {
+    const int lane = threadIdx.x & 31;
+    const int p = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (p >= n_points) return;
+    const int r0 = start[p], N = start[p + 1] - r0;
+    if (N <= 0) { if (lane == 0) { best[p] = -1; best_median[p] = 0; } return; }
+    const int k = (int)(0.5 * (N - 1));
+    uint32_t key = 0xffffffffu;
+    for (int i = lane; i < N; i += 32) {
+        const uint4 q0 = desc[2 * (size_t)(r0 + i)], q1 = desc[2 * (size_t)(r0 + i) + 1];
+        int lo = 0, hi = 256;                                   // smallest v with #{j : d_ij <= v} >= k + 1
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = 0; j < N; j++) cnt += hamming256(q0, q1, desc[2 * (size_t)(r0 + j)], desc[2 * (size_t)(r0 + j) + 1]) <= mid;
+            if (cnt >= k + 1) hi = mid; else lo = mid + 1;
+        }
+        key = min(key, ((uint32_t)lo << 16) | (uint32_t)min(i, 0xffff));
+    }
+    key = __reduce_min_sync(0xffffffffu, key);
+    if (lane == 0) { best[p] = (int)(key & 0xffffu); best_median[p] = (int)(key >> 16); }
+}

@@ -581,6 +581,33 @@ int ccm_vocabulary_transform(ccm_matcher* m, const ccm_vocabulary* v, int n, con
     return CCM_OK;
 }
 
+/* ---- distinctive descriptors ---------------------------------------------------------------------------------- */
+int ccm_distinctive_descriptors(ccm_matcher* m, int n_points, const int* start, const uint8_t* desc, int* best, int* best_median) {
+    if (!m || n_points < 0 || (n_points > 0 && (!start || !best))) return CCM_E_BADARG;
+    if (n_points == 0) return CCM_OK;
+    if (start[0] != 0) { m->err = "start[0] must be 0"; return CCM_E_BADARG; }
+    for (int p = 0; p < n_points; p++)
+        if (start[p + 1] < start[p] || start[p + 1] - start[p] > 65535) { m->err = "start must be non-decreasing with at most 65535 rows per point"; return CCM_E_BADARG; }
+    const size_t rows = (size_t)start[n_points];
+    if (rows > 0 && !desc) return CCM_E_BADARG;
+    cudaSetDevice(m->device);
+    int *ds, *db, *dm; uint8_t* dd;
+    int rc;
+    if ((rc = mbuf(m, MB_A, rows * 32, &dd))) return rc;
+    if ((rc = mbuf(m, MB_B, (size_t)n_points + 1, &ds))) return rc;
+    if ((rc = mbuf(m, MB_C, (size_t)n_points, &db))) return rc;
+    if ((rc = mbuf(m, MB_D, (size_t)n_points, &dm))) return rc;
+    if (rows) MCK(cudaMemcpyAsync(dd, desc, rows * 32, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(ds, start, ((size_t)n_points + 1) * 4, cudaMemcpyHostToDevice, m->stream));
+    k_distinctive<<<(n_points + 7) / 8, 256, 0, m->stream>>>(ds, (const uint4*)dd, n_points, db, dm);
+    m->launches++;
+    MCK(cudaGetLastError());
+    MCK(cudaMemcpyAsync(best, db, (size_t)n_points * 4, cudaMemcpyDeviceToHost, m->stream));
+    if (best_median) MCK(cudaMemcpyAsync(best_median, dm, (size_t)n_points * 4, cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
 /* ---- server keyframe-database search ---------------------------------------------------------------------- */
 int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
                                     uint32_t index_base, ccm_best2* d_out) {

@@ -292,6 +292,18 @@ class ORBmatcher:
         return nm.value, m12[:n1]
 
 
+def distinctive_descriptors(matcher, start, desc):
+    """MapPoint::ComputeDistinctiveDescriptors (cslam/src/MapPoint.cpp:929-994) for a batch of map points: point p owns
+    rows start[p]:start[p+1] of desc. -> (best row index within each point, -1 if it has none; its median distance)."""
+    st = np.ascontiguousarray(start, np.int32)
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = len(st) - 1
+    best, med = np.full(max(n, 1), -1, np.int32), np.zeros(max(n, 1), np.int32)
+    matcher._check(matcher._lib.ccm_distinctive_descriptors(matcher._h, n, st.ctypes.data, d.ctypes.data if len(d) else None,
+                                                            best.ctypes.data, med.ctypes.data))
+    return best[:n], med[:n]
+
+
 class Vocabulary:
     """Device copy of a DBoW2 vocabulary tree for the per-feature half of Frame::ComputeBoW (cslam/src/Frame.cpp:268-275).
     `voc` = dict(child_start, child_ids, desc, word, weight, L) in loadFromTextFile's node numbering (synth.make_vocabulary

@@ -535,6 +535,34 @@ void mo_vocab_transform(const int* child_start, const int* child_ids, const uint
     }
 }
 
+/* MapPoint::ComputeDistinctiveDescriptors, cslam/src/MapPoint.cpp:929-994, for map points given as CSR row ranges of one
+ * descriptor array (rows of a point in the order the reference's observation map would iterate them). PARITY UNPINNED:
+ * MapPoint.cpp does not compile outside the ROS workspace (ccmslam_msgs, Map, Communicator), so this restatement is checked
+ * only against a numpy median in tests/test_match_oracle.py. Keeps the float distance matrix, the sort and the
+ * vDists[0.5*(N-1)] index of the original. */
+void mo_distinctive_descriptors(int n_points, const int* start, const uint8_t* desc, int* best, int* best_median) {
+    for (int p = 0; p < n_points; p++) {
+        const int r0 = start[p], N = start[p + 1] - r0;
+        if (N <= 0) { best[p] = -1; if (best_median) best_median[p] = 0; continue; }
+        std::vector<float> D((size_t)N * N);
+        for (int i = 0; i < N; i++) {
+            D[(size_t)i * N + i] = 0;
+            for (int j = i + 1; j < N; j++) {
+                const int d = descriptor_distance(desc + (size_t)32 * (r0 + i), desc + (size_t)32 * (r0 + j));
+                D[(size_t)i * N + j] = (float)d; D[(size_t)j * N + i] = (float)d;
+            }
+        }
+        int BestMedian = INT_MAX, BestIdx = 0;
+        for (int i = 0; i < N; i++) {
+            std::vector<int> vDists(D.begin() + (size_t)i * N, D.begin() + (size_t)(i + 1) * N);
+            std::sort(vDists.begin(), vDists.end());
+            const int median = vDists[(size_t)(0.5 * (N - 1))];
+            if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+        }
+        best[p] = BestIdx; if (best_median) best_median[p] = BestMedian;
+    }
+}
+
 /* ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize), ORBmatcher.cpp:448-563.
  * f2 = grid of F2; F1 is given by its arrays. prev_xy[2*n1] in/out (vbPrevMatched). */
 int mo_search_for_initialization(int n1, const uint8_t* desc1, const int* octave1, const float* angle1, float* prev_xy,

@@ -526,3 +526,34 @@ def assemble_bow(word, weight, node):
     fv_node = np.where(np.asarray(weight) > 0, node, -1).astype(np.int32)
     order = [i for nd in sorted(set(fv_node[fv_node >= 0].tolist())) for i in np.nonzero(fv_node == nd)[0].tolist()]
     return np.array(words, np.uint32), np.array(vals, np.float64), fv_node, np.array(order, np.int32)
+
+
+def oracle_distinctive_descriptors(start, desc):
+    L = match_lib()
+    st, d = _a(start, np.int32), _a(desc, np.uint8).reshape(-1, 32)
+    n = len(st) - 1
+    best, med = np.full(max(n, 1), -1, np.int32), np.zeros(max(n, 1), np.int32)
+    L.mo_distinctive_descriptors.argtypes = [_i, _vp, _vp, _vp, _vp]
+    L.mo_distinctive_descriptors.restype = None
+    L.mo_distinctive_descriptors(n, st.ctypes.data, d.ctypes.data, best.ctypes.data, med.ctypes.data)
+    return best[:n], med[:n]
+
+
+def distinctive_case(seed, n_points=400, max_obs=40):
+    """Map points with 0..max_obs observations: each point's rows are one random descriptor seen again with 0-12 % of
+    its bits flipped (so medians tie often), plus a few outliers."""
+    from motioncheck_ccm_slam_b200.synth import perturb_descriptors
+    rng = np.random.default_rng(seed)
+    counts = rng.integers(0, max_obs + 1, n_points)
+    counts[:8] = [0, 1, 2, 3, 33, 64, 65, max_obs]
+    start = np.zeros(n_points + 1, np.int32); start[1:] = np.cumsum(counts)
+    desc = np.zeros((int(start[-1]), 32), np.uint8)
+    for p in range(n_points):
+        if counts[p] == 0:
+            continue
+        base = rng.integers(0, 256, (1, 32), dtype=np.uint8)
+        rows = perturb_descriptors(rng, np.repeat(base, counts[p], 0), rng.choice([0.0, 0.02, 0.06, 0.12]))
+        out = rng.random(counts[p]) < 0.1
+        rows[out] = rng.integers(0, 256, (int(out.sum()), 32), dtype=np.uint8)
+        desc[start[p]:start[p + 1]] = rows
+    return start, desc

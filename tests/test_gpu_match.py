@@ -541,3 +541,16 @@ def test_vocabulary_transform_vs_reference_dbow2(gm, tmp_path):
     assert np.array_equal(bw_g, bw_r) and np.array_equal(bv_g.view(np.uint64), bv_r.view(np.uint64))
     assert np.array_equal(fn_g, fn_r) and np.array_equal(fo_g, fo_r) and len(bw_r) > 500
     V.close()
+
+
+@pytest.mark.parametrize("seed,n_points,max_obs", [(5, 400, 40), (6, 50, 300), (7, 3000, 12)])
+def test_distinctive_descriptors(gm, seed, n_points, max_obs):
+    from _oracle import distinctive_case, oracle_distinctive_descriptors
+    from motioncheck_ccm_slam_b200.matcher import distinctive_descriptors
+    start, desc = distinctive_case(seed, n_points, max_obs)
+    bg, mg = distinctive_descriptors(gm, start, desc)
+    bo, mo = oracle_distinctive_descriptors(start, desc)
+    assert np.array_equal(bg, bo) and np.array_equal(mg, mo)
+    assert (bo == -1).any() and (bo > 0).sum() > n_points // 4
+    b0, _ = distinctive_descriptors(gm, np.zeros(1, np.int32), np.zeros((0, 32), np.uint8))
+    assert len(b0) == 0

@@ -132,3 +132,20 @@ def test_rotation_histogram_quirk():
     nm, res = OracleMatcher(0.9, True).projection_lastframe(F, np.ones(n), xs, ys, [0] * n, ang, np.array(descs), np.ones(n), 3.0, sf, h)
     assert res["accepted"].sum() == n
     assert nm == n - 2 and list(np.nonzero(h < 0)[0]) == [34, 35]
+
+
+def test_distinctive_descriptors_vs_numpy():
+    """mo_distinctive_descriptors (MapPoint.cpp:929-994 restated; the reference file does not build here, so this row's
+    parity is unpinned) against an independent numpy statement: argmin over rows of sorted(row)[int(0.5*(N-1))]."""
+    from _oracle import distinctive_case, oracle_distinctive_descriptors
+    start, desc = distinctive_case(5)
+    best, med = oracle_distinctive_descriptors(start, desc)
+    bits = np.unpackbits(desc, axis=1).astype(np.int32)
+    for p in range(len(start) - 1):
+        b = bits[start[p]:start[p + 1]]
+        if len(b) == 0:
+            assert best[p] == -1
+            continue
+        D = (b[:, None, :] != b[None, :, :]).sum(2)
+        m = np.sort(D, axis=1)[:, int(0.5 * (len(b) - 1))]
+        assert best[p] == int(np.argmin(m)) and med[p] == int(m.min())
