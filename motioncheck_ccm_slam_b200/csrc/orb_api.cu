@@ -28,6 +28,7 @@ struct ccm_orb {
     int rows = 0, cols = 0;
     LevelTable T;
     int qt_cap = 0;           // quadtree node capacity (power of two)
+    int qt_ccap = 0;          // corners per (frame, level) the quadtree keeps in shared memory
     size_t qt_smem = 0;
     int max_kps = 0;          // == T.kps_per_frame
     // device arena
@@ -188,7 +189,8 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     h->max_kps = kps;
     int cap = 32; while (cap < max_node_cap) cap <<= 1;
     h->qt_cap = cap;
-    h->qt_smem = (size_t)cap * 60 + (512 + 1) * sizeof(int);
+    h->qt_ccap = 4096;                                   // corners per (frame, level) cached in shared memory: 24 KB
+    h->qt_smem = (size_t)cap * 60 + 32 * sizeof(int) + (size_t)h->qt_ccap * 6;
     CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
 
     for (int l = 0; l < L; l++) {
@@ -302,7 +304,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[3], s));
     }
     {
-        k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, A.corners, A.corner_count, A.node_of,
+        k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, h->qt_ccap, A.corners, A.corner_count, A.node_of,
                                                               A.level_kps, A.level_kp_count);
         h->launches++;
         if (fork) {

@@ -20,31 +20,28 @@ namespace {
 
 struct QNode { short ulx, uly, brx, bry; int cnt; };
 
-// exclusive prefix sum of v[0..n) in place (block-wide); returns the total. scratch: blockDim.x ints.
+// exclusive prefix sum of v[0..n) in place (block-wide, QT_THREADS threads); returns the total. scratch: 32 ints.
+// Each thread owns a contiguous run of ceil(n / QT_THREADS) elements; the per-thread sums are scanned inside every warp
+// at once and the 16 warp totals by every warp redundantly, so the call costs two barriers and ten shuffle steps.
+#define QT_THREADS 512
 __device__ int block_exclusive_scan(int* v, int n, int* scratch) {
-    const int T = blockDim.x, tid = threadIdx.x;
-    const int per = (n + T - 1) / T;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (n + QT_THREADS - 1) / QT_THREADS;
     const int b = min(tid * per, n), e = min(b + per, n);
     int s = 0;
     for (int i = b; i < e; i++) s += v[i];
-    scratch[tid] = s;
-    __syncthreads();
-    if (tid < 32) {      // T <= 1024: one warp scans the per-thread totals
-        int carry = 0;
-        for (int base = 0; base < T; base += 32) {
-            int x = scratch[base + tid];
-            int inc = x;
+    int inc = s;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, inc, o); if (tid >= o) inc += y; }
-            scratch[base + tid] = carry + inc - x;
-            carry += __shfl_sync(0xffffffffu, inc, 31);
-        }
-        if (tid == 0) scratch[T] = carry;
-    }
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+    if (lane == 31) scratch[warp] = inc;
     __syncthreads();
-    int run = scratch[tid];
-    for (int i = b; i < e; i++) { int x = v[i]; v[i] = run; run += x; }
-    const int total = scratch[T];
+    const int wt = lane < QT_THREADS / 32 ? scratch[lane] : 0;
+    int winc = wt;
+#pragma unroll
+    for (int o = 1; o < QT_THREADS / 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += y; }
+    const int total = __shfl_sync(0xffffffffu, winc, QT_THREADS / 32 - 1);
+    int run = __shfl_sync(0xffffffffu, winc - wt, warp) + inc - s;
+    for (int i = b; i < e; i++) { const int x = v[i]; v[i] = run; run += x; }
     __syncthreads();
     return total;
 }
@@ -65,8 +62,10 @@ __device__ __forceinline__ int quadrant(const QNode& p, int x, int y) {
 
 // dynamic smem layout (cap = node capacity rounded up to a power of two, >= 32):
 //   QNode A[cap], B[cap]; int cc[4*cap]; int key[cap]; int aux[cap]; int newpos[cap]; short childpos[4*cap];
-//   int scratch[blockDim+1]
-__global__ void __launch_bounds__(512) k_quadtree(const __grid_constant__ LevelTable T, int cap,
+//   int scratch[32]; uint32_t corner_cache[ccap]; uint16_t node_cache[ccap]
+// A (frame, level) with at most ccap corners keeps its corner list and the corner -> node map in shared memory for the
+// whole run (every round walks both twice); larger ones work on the global arrays.
+__global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap,
                                                   const uint32_t* __restrict__ corners, const int* __restrict__ corner_count,
                                                   uint16_t* __restrict__ node_of,          // [frames][corners_per_frame]
                                                   uint32_t* __restrict__ level_kps,        // [frames][kps_per_frame] packed x|y<<12|score<<24
@@ -89,6 +88,12 @@ __global__ void __launch_bounds__(512) k_quadtree(const __grid_constant__ LevelT
     const int nC = min(corner_count[f * CCM_MAX_LEVELS + lvl], L.corner_cap);
     const uint32_t* ck = corners + (size_t)f * T.corners_per_frame + L.corner_off;
     uint16_t* nof = node_of + (size_t)f * T.corners_per_frame + L.corner_off;
+    if (nC <= ccap) {
+        uint32_t* sck = reinterpret_cast<uint32_t*>(scratch + 32);
+        for (int k = tid; k < nC; k += NT) sck[k] = ck[k];
+        ck = sck;
+        nof = reinterpret_cast<uint16_t*>(sck + ccap);
+    }
     const int N = L.quota;
     const int H = L.h - 2 * CCM_MIN_BORDER;   // maxY-minY
 
@@ -146,21 +151,24 @@ __global__ void __launch_bounds__(512) k_quadtree(const __grid_constant__ LevelT
             for (int i = tid; i < n; i += NT) if (A[i].cnt > 1) key[aux[i]] = i;
             __syncthreads();
         } else {
-            // sort descending by (count, earlier list position first): bitonic over `cap` keys
-            for (int i = tid; i < cap; i += NT) key[i] = (i < n && A[i].cnt > 1) ? ((min(A[i].cnt, 0x7FFFF) << 12) | (4095 - i)) : 0;
+            // sort descending by (count, earlier list position first). Keys are distinct (the position is part of the
+            // key), so a candidate's place is the number of larger keys: one pass of broadcast reads, no barrier ladder
+            for (int i = tid; i < cap; i += NT) {
+                key[i] = (i < n && A[i].cnt > 1) ? ((min(A[i].cnt, 0x7FFFF) << 12) | (4095 - i)) : 0;
+                newpos[i] = 0;
+            }
             __syncthreads();
-            for (int k2 = 2; k2 <= cap; k2 <<= 1)
-                for (int j = k2 >> 1; j > 0; j >>= 1) {
-                    for (int i = tid; i < cap; i += NT) {
-                        const int ixj = i ^ j;
-                        if (ixj > i) {
-                            const int a = key[i], b = key[ixj];
-                            const bool desc = (i & k2) == 0;
-                            if (desc ? (a < b) : (a > b)) { key[i] = b; key[ixj] = a; }
-                        }
-                    }
-                    __syncthreads();
+            for (int i = tid; i < n; i += NT) {
+                const int k = key[i];
+                if (k) {
+                    int r = 0;
+                    for (int j = 0; j < n; j++) r += key[j] > k;
+                    newpos[r] = k;
                 }
+            }
+            __syncthreads();
+            for (int i = tid; i < cap; i += NT) key[i] = newpos[i];
+            __syncthreads();
             // aux[r] = growth of the list when the r-th candidate is split (children - 1); prefix -> cut (:895-896)
             for (int r = tid; r < cap; r += NT) {
                 int g = 0;
