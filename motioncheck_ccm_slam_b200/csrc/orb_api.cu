@@ -46,7 +46,6 @@ struct ccm_orb {
     // two pipeline lanes: lane 0 runs on `stream`, lane 1 on its own stream; each has a side stream for the blur. Half
     // batches on the two lanes fill each other's latency-bound stages (quadtree, small pyramid levels).
     struct Lane { cudaStream_t s = nullptr, aux = nullptr; cudaEvent_t fork = nullptr, join = nullptr; } lane[2];
-    cudaEvent_t ev_l1_start = nullptr, ev_l1_done = nullptr;
     uint8_t* d_stage = nullptr; size_t stage_bytes = 0;   // host entry point: staging for rows that are not 4-byte multiples
     cudaEvent_t ev_in[CCM_MAX_CHUNKS] = {}, ev_done[CCM_MAX_CHUNKS] = {}, ev_out[CCM_MAX_CHUNKS] = {};
     long long launches = 0;
@@ -363,9 +362,7 @@ int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
     if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     if ((e = cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaStreamCreateWithFlags(&h->lane[1].s, cudaStreamNonBlocking)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&h->ev_l1_start, cudaEventDisableTiming)) != cudaSuccess ||
-        (e = cudaEventCreateWithFlags(&h->ev_l1_done, cudaEventDisableTiming)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+        (e = cudaStreamCreateWithFlags(&h->lane[1].s, cudaStreamNonBlocking)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     h->lane[0].s = h->stream;
     for (int i = 0; i < 2; i++)
         if ((e = cudaStreamCreateWithFlags(&h->lane[i].aux, cudaStreamNonBlocking)) != cudaSuccess ||
@@ -399,8 +396,6 @@ void ccm_orb_destroy(ccm_orb* h) {
         if (h->lane[i].aux) cudaStreamDestroy(h->lane[i].aux);
     }
     if (h->lane[1].s) cudaStreamDestroy(h->lane[1].s);
-    if (h->ev_l1_start) cudaEventDestroy(h->ev_l1_start);
-    if (h->ev_l1_done) cudaEventDestroy(h->ev_l1_done);
     if (h->s_in) cudaStreamDestroy(h->s_in);
     if (h->s_out) cudaStreamDestroy(h->s_out);
     if (h->stream) cudaStreamDestroy(h->stream);
