@@ -67,6 +67,32 @@ int ccm_frame_pack_from_extractor_batch_device(ccm_frame_pack* const* packs, int
 int ccm_frame_pack_get_grid(ccm_frame_pack* p, int* cell_start, int* items, int* n_items);
 int ccm_frame_pack_count(ccm_frame_pack* p, int* n);
 
+/* ---- Frame::UndistortKeyPoints / ComputeImageBounds (Frame.cpp:277-343) ---------------------------------------
+ * cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK): five fixed-point iterations of the inverse
+ * Brown-Conrady model per point, in double, every operation separately rounded (no FMA contraction), result
+ * rounded to float — bit-identical to OpenCV 4.13.0 (tests/golden/undistort.npz). */
+typedef struct ccm_camera {
+    float fx, fy, cx, cy;      /* mK (Tracking.cpp:38-43) */
+    float dist[5];             /* mDistCoef = k1 k2 p1 p2 [k3] (Tracking.cpp:47-58) */
+    int n_dist;                /* 4 or 5 */
+} ccm_camera;
+
+/* host in/out: xy_out[i] = undistorted xy_in[i] ([n][2] floats). As Frame.cpp:279-283, dist[0] == 0 copies the input. */
+int ccm_undistort_points(ccm_matcher* m, const ccm_camera* cam, int n, const float* xy_in, float* xy_out);
+/* device, batched over an extractor batch: frame j's d_n[j] keypoints (d_kp + j*kp_stride) -> d_xy_un [n_frames][kp_stride][2],
+ * the array the pack builders take as d_xy_un; enqueued on the matcher's stream */
+int ccm_undistort_keypoints_batch_device(ccm_matcher* m, const ccm_camera* cam, int n_frames, const ccm_keypoint* d_kp,
+                                         const int* d_n, int kp_stride, float* d_xy_un);
+/* Frame::ComputeImageBounds + the grid constants of the Frame constructor (Frame.cpp:85-88, 309-343): fills
+ * g->min_x, min_y, inv_w, inv_h for a cols x rows image (g->cols, g->rows as given); bounds[4] = mnMinX, mnMaxX,
+ * mnMinY, mnMaxY (may be NULL) */
+int ccm_image_bounds(ccm_matcher* m, const ccm_camera* cam, int img_cols, int img_rows, ccm_grid_params* g, float* bounds);
+/* ccm_frame_pack_from_extractor_batch_device with the undistortion fused into the pack fill (no d_xy_un round trip):
+ * pack positions = mvKeysUn of a camera with distortion */
+int ccm_frame_pack_from_extractor_batch_device_cam(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g,
+                                                   const ccm_camera* cam, const ccm_keypoint* d_kp, const uint8_t* d_desc,
+                                                   const int* d_n, int kp_stride);
+
 /* ---- windowed searches (GetFeaturesInArea candidates) -------------------------------------------------------
  * One query per map point / feature the reference loop reaches; the loop's host-side early `continue`s are the
  * valid flag. Query order is the reference's loop order: results are those of the sequential greedy loop. */

@@ -50,6 +50,12 @@ class GridParams(ctypes.Structure):
                 ("cols", ctypes.c_int), ("rows", ctypes.c_int)]
 
 
+class Camera(ctypes.Structure):
+    """ccm_camera: mK and mDistCoef of a Frame (Tracking.cpp:38-58)"""
+    _fields_ = [("fx", ctypes.c_float), ("fy", ctypes.c_float), ("cx", ctypes.c_float), ("cy", ctypes.c_float),
+                ("dist", ctypes.c_float * 5), ("n_dist", ctypes.c_int)]
+
+
 class EpipolarGeom(ctypes.Structure):
     _fields_ = [("f12", ctypes.c_float * 9), ("ex", ctypes.c_float), ("ey", ctypes.c_float),
                 ("scale_factors", ctypes.POINTER(ctypes.c_float)), ("level_sigma2", ctypes.POINTER(ctypes.c_float)),
@@ -67,7 +73,7 @@ class WindowParams(ctypes.Structure):
 
 
 _ll, _u32, _f = _c.c_longlong, _c.c_uint32, _c.c_float
-_gp, _wp = _c.POINTER(GridParams), _c.POINTER(WindowParams)
+_gp, _wp, _cp = _c.POINTER(GridParams), _c.POINTER(WindowParams), _c.POINTER(Camera)
 
 # every symbol include/ccm_match.h declares
 SIGNATURES.update({
@@ -83,6 +89,10 @@ SIGNATURES.update({
     "ccm_frame_pack_upload": (_i, [_vp, _gp, _i, _vp, _vp, _vp, _vp, _vp]),
     "ccm_frame_pack_from_extractor_device": (_i, [_vp, _gp, _vp, _vp, _vp, _vp]),
     "ccm_frame_pack_from_extractor_batch_device": (_i, [_c.POINTER(_vp), _i, _gp, _vp, _vp, _vp, _i, _vp]),
+    "ccm_frame_pack_from_extractor_batch_device_cam": (_i, [_c.POINTER(_vp), _i, _gp, _cp, _vp, _vp, _vp, _i]),
+    "ccm_undistort_points": (_i, [_vp, _cp, _i, _vp, _vp]),
+    "ccm_undistort_keypoints_batch_device": (_i, [_vp, _cp, _i, _vp, _vp, _i, _vp]),
+    "ccm_image_bounds": (_i, [_vp, _cp, _i, _i, _gp, _vp]),
     "ccm_frame_pack_get_grid": (_i, [_vp, _vp, _vp, _ip]),
     "ccm_frame_pack_count": (_i, [_vp, _ip]),
     "ccm_search_window": (_i, [_vp, _vp, _wp, _i, _vp, _vp, _vp, _vp, _ip]),

@@ -199,13 +199,90 @@ int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, co
     return CCM_OK;
 }
 
+static int camera_dev(ccm_matcher* m, const ccm_camera* cam, CameraDev* c) {
+    std::memset(c, 0, sizeof(*c));
+    if (!cam) return CCM_OK;                                     // no camera: mvKeysUn = mvKeys
+    if (cam->n_dist < 4 || cam->n_dist > 5 || !(cam->fx != 0.0f) || !(cam->fy != 0.0f)) { m->err = "camera: n_dist must be 4 or 5 and fx, fy non-zero"; return CCM_E_BADARG; }
+    c->fx = cam->fx; c->fy = cam->fy; c->cx = cam->cx; c->cy = cam->cy;
+    c->ifx = 1. / c->fx; c->ify = 1. / c->fy;                    // double reciprocals of the float intrinsics, as cvUndistortPointsInternal
+    c->k0 = cam->dist[0]; c->k1 = cam->dist[1]; c->k2 = cam->dist[2]; c->k3 = cam->dist[3]; c->k4 = cam->n_dist > 4 ? cam->dist[4] : 0.0;
+    c->distorted = cam->dist[0] != 0.0f;                         // Frame.cpp:279: only k1 is looked at
+    return CCM_OK;
+}
+
+static int pack_from_extractor(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g, const ccm_camera* cam,
+                               const ccm_keypoint* d_kp, const uint8_t* d_desc, const int* d_n, int kp_stride, const float* d_xy_un);
+
 int ccm_frame_pack_from_extractor_batch_device(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g,
                                                const ccm_keypoint* d_kp, const uint8_t* d_desc, const int* d_n, int kp_stride,
                                                const float* d_xy_un) {
+    return pack_from_extractor(packs, n_packs, g, nullptr, d_kp, d_desc, d_n, kp_stride, d_xy_un);
+}
+
+int ccm_frame_pack_from_extractor_batch_device_cam(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g,
+                                                   const ccm_camera* cam, const ccm_keypoint* d_kp, const uint8_t* d_desc,
+                                                   const int* d_n, int kp_stride) {
+    if (!cam) return CCM_E_BADARG;
+    return pack_from_extractor(packs, n_packs, g, cam, d_kp, d_desc, d_n, kp_stride, nullptr);
+}
+
+int ccm_undistort_points(ccm_matcher* m, const ccm_camera* cam, int n, const float* xy_in, float* xy_out) {
+    if (!m || !cam || n < 0 || (n > 0 && (!xy_in || !xy_out))) return CCM_E_BADARG;
+    CameraDev c;
+    int rc = camera_dev(m, cam, &c);
+    if (rc || n == 0) return rc;
+    cudaSetDevice(m->device);
+    float2 *din, *dout;
+    if ((rc = mbuf(m, MB_A, (size_t)n, &din))) return rc;
+    if ((rc = mbuf(m, MB_B, (size_t)n, &dout))) return rc;
+    MCK(cudaMemcpyAsync(din, xy_in, (size_t)n * sizeof(float2), cudaMemcpyHostToDevice, m->stream));
+    k_undistort_points<<<(n + 255) / 256, 256, 0, m->stream>>>(c, n, din, dout);
+    m->launches++;
+    MCK(cudaGetLastError());
+    MCK(cudaMemcpyAsync(xy_out, dout, (size_t)n * sizeof(float2), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
+int ccm_undistort_keypoints_batch_device(ccm_matcher* m, const ccm_camera* cam, int n_frames, const ccm_keypoint* d_kp,
+                                         const int* d_n, int kp_stride, float* d_xy_un) {
+    if (!m || !cam || n_frames <= 0 || !d_kp || !d_n || kp_stride <= 0 || !d_xy_un) return CCM_E_BADARG;
+    CameraDev c;
+    int rc = camera_dev(m, cam, &c);
+    if (rc) return rc;
+    cudaSetDevice(m->device);
+    k_undistort_keypoints<<<dim3((kp_stride + 255) / 256, n_frames), 256, 0, m->stream>>>(c, (const ccm_keypoint_dev*)d_kp, d_n, kp_stride, (float2*)d_xy_un);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_image_bounds(ccm_matcher* m, const ccm_camera* cam, int img_cols, int img_rows, ccm_grid_params* g, float* bounds) {
+    if (!m || !cam || !g || img_cols <= 0 || img_rows <= 0 || g->cols <= 0 || g->rows <= 0) return CCM_E_BADARG;
+    float mn_x = 0.0f, mx_x = (float)img_cols, mn_y = 0.0f, mx_y = (float)img_rows;                // Frame.cpp:336-341
+    if (cam->dist[0] != 0.0f) {                                                                     // :311
+        const float in[8] = {0.0f, 0.0f, (float)img_cols, 0.0f, 0.0f, (float)img_rows, (float)img_cols, (float)img_rows};   // :313-317
+        float un[8];
+        const int rc = ccm_undistort_points(m, cam, 4, in, un);
+        if (rc) return rc;
+        mn_x = std::min(un[0], un[4]); mx_x = std::max(un[2], un[6]);                               // :324-327
+        mn_y = std::min(un[1], un[3]); mx_y = std::max(un[5], un[7]);
+    }
+    g->min_x = mn_x; g->min_y = mn_y;
+    g->inv_w = (float)g->cols / (mx_x - mn_x);                                                     // :87-88
+    g->inv_h = (float)g->rows / (mx_y - mn_y);
+    if (bounds) { bounds[0] = mn_x; bounds[1] = mx_x; bounds[2] = mn_y; bounds[3] = mx_y; }
+    return CCM_OK;
+}
+
+static int pack_from_extractor(ccm_frame_pack* const* packs, int n_packs, const ccm_grid_params* g, const ccm_camera* cam,
+                               const ccm_keypoint* d_kp, const uint8_t* d_desc, const int* d_n, int kp_stride, const float* d_xy_un) {
     if (!packs || n_packs <= 0 || !packs[0] || !d_kp || !d_desc || !d_n || kp_stride <= 0) return CCM_E_BADARG;
     ccm_matcher* m = packs[0]->m;
     int rc = check_grid(m, g);
     if (rc) return rc;
+    CameraDev c;
+    if ((rc = camera_dev(m, cam, &c))) return rc;
     cudaSetDevice(m->device);
     std::vector<PackFill> fills(n_packs);
     for (int j = 0; j < n_packs; j++) {
@@ -218,7 +295,7 @@ int ccm_frame_pack_from_extractor_batch_device(ccm_frame_pack* const* packs, int
     PackFill* dfills;
     if ((rc = mbuf(m, MB_D, (size_t)n_packs, &dfills))) return rc;
     MCK(cudaMemcpyAsync(dfills, fills.data(), sizeof(PackFill) * n_packs, cudaMemcpyHostToDevice, m->stream));
-    k_pack_from_keypoints<<<n_packs, 256, 0, m->stream>>>(dfills, (const ccm_keypoint_dev*)d_kp, d_xy_un, d_n, kp_stride);
+    k_pack_from_keypoints<<<n_packs, 256, 0, m->stream>>>(dfills, (const ccm_keypoint_dev*)d_kp, d_xy_un, d_n, kp_stride, c);
     m->launches++;
     MCK(cudaGetLastError());
     return launch_build_grid(m, packs, n_packs);

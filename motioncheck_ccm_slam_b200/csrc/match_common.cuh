@@ -117,3 +117,35 @@ __device__ __forceinline__ void warp_top2(unsigned long long& b1, unsigned long 
         merge_top2(b1, b2, o1, o2);
     }
 }
+
+// cv::undistortPoints for one point (OpenCV 4.13.0 cvUndistortPointsInternal, default 5 iterations, R = I, P = K), the
+// arithmetic of Frame::UndistortKeyPoints (Frame.cpp:295). Doubles with explicit round-to-nearest intrinsics so that
+// nvcc cannot contract a multiply-add: the host library is built without FMA and the results must be identical.
+// k[5..11] are 0 for the reference's 4/5-coefficient models; the terms they multiply are kept where a zero product
+// still takes part in a rounding (x + 0 is exact, so they are dropped only where they add an exact zero).
+struct CameraDev { double fx, fy, cx, cy, ifx, ify, k0, k1, k2, k3, k4; int distorted; };
+__device__ __forceinline__ float2 undistort_point(const CameraDev& C, float xf, float yf) {
+    if (!C.distorted) return make_float2(xf, yf);
+    const double u = (double)xf, v = (double)yf;
+    double x = __dmul_rn(__dsub_rn(u, C.cx), C.ifx), y = __dmul_rn(__dsub_rn(v, C.cy), C.ify);
+    const double x0 = x, y0 = y;
+    const double two_k2 = __dmul_rn(2.0, C.k2), two_k3 = __dmul_rn(2.0, C.k3);
+#pragma unroll 1
+    for (int j = 0; j < 5; j++) {
+        const double xx = __dmul_rn(x, x), yy = __dmul_rn(y, y);
+        const double r2 = __dadd_rn(xx, yy);
+        // (1 + ((k7*r2 + k6)*r2 + k5)*r2) with k5..k7 = 0: ((0*r2 + 0)*r2 + 0)*r2 = 0 for finite r2, 1 + 0 = 1
+        const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(C.k4, r2), C.k1), r2), C.k0), r2));
+        const double icdist = __ddiv_rn(1.0, den);
+        if (icdist < 0) { x = x0; y = y0; break; }
+        // deltaX = 2*k2*x*y + k3*(r2 + 2*x*x) + k8*r2 + k9*r2*r2, left to right; the k8..k11 terms add exact zeros
+        const double dx = __dadd_rn(__dmul_rn(__dmul_rn(two_k2, x), y), __dmul_rn(C.k3, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
+        const double dy = __dadd_rn(__dmul_rn(C.k2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y))), __dmul_rn(__dmul_rn(two_k3, x), y));
+        x = __dmul_rn(__dsub_rn(x0, dx), icdist);
+        y = __dmul_rn(__dsub_rn(y0, dy), icdist);
+    }
+    // RR = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1/(0*x + 0*y + 1) = 1
+    const double ox = __dadd_rn(__dadd_rn(__dmul_rn(C.fx, x), __dmul_rn(0.0, y)), C.cx);
+    const double oy = __dadd_rn(__dadd_rn(__dmul_rn(0.0, x), __dmul_rn(C.fy, y)), C.cy);
+    return make_float2(__double2float_rn(ox), __double2float_rn(oy));
+}

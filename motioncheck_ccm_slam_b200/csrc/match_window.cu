@@ -38,7 +38,8 @@
 // distorted camera). Pack j reads frame j of the extractor's batch output (kp_stride keypoints apart).
 struct PackFill { float* x; float* y; float* angle; int* octave; int* n; int cap; };
 __global__ void __launch_bounds__(256) k_pack_from_keypoints(const PackFill* __restrict__ fills, const ccm_keypoint_dev* __restrict__ kp,
-                                                             const float* __restrict__ xy_un, const int* __restrict__ n_ptr, int kp_stride) {
+                                                             const float* __restrict__ xy_un, const int* __restrict__ n_ptr, int kp_stride,
+                                                             const CameraDev cam) {
     const PackFill F = fills[blockIdx.x];
     kp += (size_t)blockIdx.x * kp_stride;
     if (xy_un) xy_un += (size_t)blockIdx.x * kp_stride * 2;
@@ -46,11 +47,24 @@ __global__ void __launch_bounds__(256) k_pack_from_keypoints(const PackFill* __r
     if (threadIdx.x == 0) *F.n = n;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         const ccm_keypoint_dev k = kp[i];
-        F.x[i] = xy_un ? xy_un[2 * i] : k.x;
-        F.y[i] = xy_un ? xy_un[2 * i + 1] : k.y;
+        const float2 un = xy_un ? make_float2(xy_un[2 * i], xy_un[2 * i + 1]) : undistort_point(cam, k.x, k.y);   // mvKeysUn[i].pt
+        F.x[i] = un.x;
+        F.y[i] = un.y;
         F.angle[i] = k.angle;
         F.octave[i] = k.octave;
     }
+}
+
+// Frame::UndistortKeyPoints (Frame.cpp:277-307) for flat point arrays and for an extractor batch (frame = blockIdx.y)
+__global__ void __launch_bounds__(256) k_undistort_points(const CameraDev cam, int n, const float2* __restrict__ in, float2* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const float2 p = in[i]; out[i] = undistort_point(cam, p.x, p.y); }
+}
+__global__ void __launch_bounds__(256) k_undistort_keypoints(const CameraDev cam, const ccm_keypoint_dev* __restrict__ kp, const int* __restrict__ n_ptr,
+                                                             int kp_stride, float2* __restrict__ out) {
+    const int f = blockIdx.y, n = min(n_ptr[f], kp_stride);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const ccm_keypoint_dev k = kp[(size_t)f * kp_stride + i]; out[(size_t)f * kp_stride + i] = undistort_point(cam, k.x, k.y); }
 }
 
 // Frame::AssignFeaturesToGrid + PosInGrid (Frame.cpp:103-118, 255-265; note round(), not floor()): one CTA per pack.

@@ -8,7 +8,7 @@ import ctypes
 import numpy as np
 
 from . import _lib
-from ._lib import CcmError, GridParams, WindowParams, WindowQuery
+from ._lib import Camera, CcmError, GridParams, WindowParams, WindowQuery
 
 TH_HIGH, TH_LOW, HISTO_LENGTH = 100, 50, 30          # ORBmatcher.cpp:63-65
 FRAME_GRID_COLS, FRAME_GRID_ROWS = 75, 48            # Frame.h:51-52
@@ -30,6 +30,14 @@ def frame_grid(width, height, min_x=0.0, min_y=0.0, cols=FRAME_GRID_COLS, rows=F
     inv_w = np.float32(cols) / (max_x - np.float32(min_x))
     inv_h = np.float32(rows) / (max_y - np.float32(min_y))
     return GridParams(float(min_x), float(min_y), float(inv_w), float(inv_h), cols, rows)
+
+
+def make_camera(fx, fy, cx, cy, dist):
+    """mK + mDistCoef (k1 k2 p1 p2 [k3]) as floats, the way Tracking.cpp:38-58 reads them from the settings file."""
+    dist = [float(np.float32(d)) for d in dist]
+    assert len(dist) in (4, 5)
+    return Camera(float(np.float32(fx)), float(np.float32(fy)), float(np.float32(cx)), float(np.float32(cy)),
+                  (ctypes.c_float * 5)(*(dist + [0.0] * (5 - len(dist)))), len(dist))
 
 
 class Matcher:
@@ -76,6 +84,24 @@ class Matcher:
         return out
 
     # ---- server keyframe-database search (BASELINE.json configs[4]) ----
+    def UndistortKeyPoints(self, cam, xy):
+        """Frame::UndistortKeyPoints (Frame.cpp:277-307) on an [n][2] float array of keypoint positions."""
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        out = np.empty_like(xy)
+        self._check(self._lib.ccm_undistort_points(self._h, ctypes.byref(cam), len(xy), xy.ctypes.data, out.ctypes.data))
+        return out
+
+    def undistort_keypoints_batch_device(self, cam, n_frames, d_kp, d_n, kp_stride, d_xy_un):
+        self._check(self._lib.ccm_undistort_keypoints_batch_device(self._h, ctypes.byref(cam), int(n_frames), d_kp, d_n,
+                                                                   int(kp_stride), d_xy_un))
+
+    def ComputeImageBounds(self, cam, width, height, cols=FRAME_GRID_COLS, rows=FRAME_GRID_ROWS):
+        """Frame::ComputeImageBounds + the grid constants (Frame.cpp:85-88, 309-343) -> (GridParams, [minX, maxX, minY, maxY])."""
+        g = GridParams(0.0, 0.0, 0.0, 0.0, cols, rows)
+        b = np.zeros(4, np.float32)
+        self._check(self._lib.ccm_image_bounds(self._h, ctypes.byref(cam), int(width), int(height), ctypes.byref(g), b.ctypes.data))
+        return g, b
+
     def match_allpairs_best2(self, q, targets, index_base=0):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
         t = np.ascontiguousarray(targets, np.uint8).reshape(-1, 32)
@@ -367,12 +393,18 @@ class Vocabulary:
 
 
 # ---- device-resident batch path (extractor output -> packs -> searches, no host round trip) ----------------------
-def packs_from_extractor_batch_device(packs, grid, d_kp, d_desc, d_n, kp_stride, d_xy_un=None):
-    """packs[j] takes frame j of ORBextractor.extract_batch_device's output (raw device pointers); asynchronous."""
+def packs_from_extractor_batch_device(packs, grid, d_kp, d_desc, d_n, kp_stride, d_xy_un=None, cam=None):
+    """packs[j] takes frame j of ORBextractor.extract_batch_device's output (raw device pointers); asynchronous.
+    cam: undistort the keypoints inside the pack fill (mvKeysUn of a distorted camera)."""
     m = packs[0].m
     arr = (ctypes.c_void_p * len(packs))(*[p._h.value for p in packs])
     for p in packs:
         p.grid = grid
+    if cam is not None:
+        assert d_xy_un is None
+        m._check(m._lib.ccm_frame_pack_from_extractor_batch_device_cam(arr, len(packs), ctypes.byref(grid), ctypes.byref(cam), d_kp,
+                                                                       d_desc, d_n, int(kp_stride)))
+        return
     m._check(m._lib.ccm_frame_pack_from_extractor_batch_device(arr, len(packs), ctypes.byref(grid), d_kp, d_desc, d_n,
                                                                int(kp_stride), d_xy_un))
 

@@ -209,4 +209,46 @@ int ocv_fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, i
     return n;
 }
 
+/* cv::undistortPoints(src, dst, K, distCoeffs, noArray(), P) on CV_32FC2 points, OpenCV 4.13.0
+ * calib3d/src/undistort.dispatch.cpp cvUndistortPointsInternal with the 4-argument overload's default
+ * TermCriteria(MAX_ITER, 5, 0.01): five fixed-point iterations in double, no early exit (the EPS bit is not set).
+ * Call sites: Frame::UndistortKeyPoints cslam/src/Frame.cpp:295, Frame::ComputeImageBounds :321 (K = P = mK, float;
+ * distCoeffs = (k1,k2,p1,p2[,k3]) float, Tracking.cpp:47-58). k[5..13] (rational, thin-prism, tilt) are 0 for the
+ * 4/5-coefficient models the reference loads, so the tilt matrices are the identity; the zero terms are kept where
+ * they take part in the arithmetic so the rounding sequence is OpenCV's. Every operation is a separately rounded
+ * double operation (this file is built with -ffp-contract=off). */
+void ocv_undistort_points_f32(const float* src_xy, float* dst_xy, int n, const float K[9], const float* dist, int n_dist,
+                              const float P[9]) {
+    double k[14] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int i = 0; i < n_dist && i < 14; i++) k[i] = (double)dist[i];
+    double RR[3][3];
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++) RR[r][c] = (double)P[3 * r + c];          /* PP * I */
+    const double fx = (double)K[0], fy = (double)K[4], ifx = 1. / fx, ify = 1. / fy, cx = (double)K[2], cy = (double)K[5];
+    for (int i = 0; i < n; i++) {
+        double x = (double)src_xy[2 * i], y = (double)src_xy[2 * i + 1];
+        const double u = x, v = y;
+        x = (x - cx) * ifx;
+        y = (y - cy) * ify;
+        if (dist) {
+            /* invMatTilt = I: vecUntilt = (x*1 + y*0 + 1*0, ..., 1); invProj = 1 */
+            const double x0 = x, y0 = y;
+            for (int j = 0; j < 5; j++) {
+                const double r2 = x * x + y * y;
+                const double icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+                if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+                const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2;
+                const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2;
+                x = (x0 - deltaX) * icdist;
+                y = (y0 - deltaY) * icdist;
+            }
+        }
+        const double xx = RR[0][0] * x + RR[0][1] * y + RR[0][2];
+        const double yy = RR[1][0] * x + RR[1][1] * y + RR[1][2];
+        const double ww = 1. / (RR[2][0] * x + RR[2][1] * y + RR[2][2]);
+        dst_xy[2 * i] = (float)(xx * ww);
+        dst_xy[2 * i + 1] = (float)(yy * ww);
+    }
+}
+
 }  // extern "C"

@@ -12,6 +12,7 @@
  *   cv::FAST(img, kps, th, true)        cslam/src/ORBextractor.cpp:978,983
  *   cv::GaussianBlur(7x7, s=2, R101)    cslam/src/ORBextractor.cpp:1259
  *   cv::fastAtan2                       cslam/src/ORBextractor.cpp:94
+ *   cv::undistortPoints                 cslam/src/Frame.cpp:295,321
  *   cvRound                             cslam/src/ORBextractor.cpp:72,107,111-124,611,629,1285
  */
 #ifndef CCM_ORACLE_CV_PRIMITIVES_H_
@@ -54,6 +55,11 @@ int ocv_fast_score_9_16(const uint8_t* p, size_t step);
  * cap; only the first cap are written), in raster order, exactly as cv::FAST lists them. */
 int ocv_fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, int nonmax,
                  ocv_corner* out, int cap);
+
+/* cv::undistortPoints(src, dst, K, dist, noArray(), P) for CV_32FC2 points, float K/dist/P, default 5 iterations;
+ * dist may be NULL (no distortion model). Frame.cpp:295, :321 */
+void ocv_undistort_points_f32(const float* src_xy, float* dst_xy, int n, const float K[9], const float* dist, int n_dist,
+                              const float P[9]);
 
 #ifdef __cplusplus
 }

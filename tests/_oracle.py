@@ -91,6 +91,32 @@ class OracleExtractor:
         return kp[:n].copy()
 
 
+def oracle_undistort(xy, K, dist):
+    """oracle/cv_primitives.cpp ocv_undistort_points_f32: cv::undistortPoints(xy, K, dist, None, K) as Frame.cpp:295 calls it."""
+    L = oracle_lib()
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    K = np.ascontiguousarray(K, np.float32).reshape(9)
+    d = np.ascontiguousarray(dist, np.float32).ravel()
+    out = np.empty_like(xy)
+    vp = ctypes.c_void_p
+    L.ocv_undistort_points_f32.argtypes = [vp, vp, ctypes.c_int, vp, vp, ctypes.c_int, vp]
+    L.ocv_undistort_points_f32.restype = None
+    L.ocv_undistort_points_f32(xy.ctypes.data, out.ctypes.data, len(xy), K.ctypes.data, d.ctypes.data, d.size, K.ctypes.data)
+    return out
+
+
+def oracle_image_bounds(K, dist, w, h, cols=75, rows=48):
+    """Frame::ComputeImageBounds + Frame.cpp:87-88 -> (minX, maxX, minY, maxY, invW, invH) as float32."""
+    f = np.float32
+    if f(dist[0]) == 0:
+        mn_x, mx_x, mn_y, mx_y = f(0), f(w), f(0), f(h)
+    else:
+        c = oracle_undistort(np.array([[0, 0], [w, 0], [0, h], [w, h]], np.float32), K, dist)
+        mn_x, mx_x = min(c[0, 0], c[2, 0]), max(c[1, 0], c[3, 0])
+        mn_y, mx_y = min(c[0, 1], c[1, 1]), max(c[2, 1], c[3, 1])
+    return np.array([mn_x, mx_x, mn_y, mx_y, f(cols) / (mx_x - mn_x), f(rows) / (mx_y - mn_y)], np.float32)
+
+
 def ref_available(mono=True):
     return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_orb_mono.so" if mono else "libref_orb.so"))
 

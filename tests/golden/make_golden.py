@@ -1,6 +1,8 @@
 """Generates the committed golden fixtures. Run in the build container (needs cv2 4.13.0 and /root/reference):
     python tests/golden/make_golden.py
 * cv_primitives.npz  — inputs and cv2 4.13.0 outputs for resize / GaussianBlur / copyMakeBorder / FAST / fastAtan2
+* undistort.npz      — cv2 4.13.0 cv::undistortPoints(pts, K, D, None, K) on keypoint-like points for four camera models
+                       (EuRoC vi_euroc.yaml, a 5-coefficient one, barrel, strong pincushion) + their image-corner bounds
 * ref_extract.npz    — keypoints + descriptors from the reference's own ORBextractor.cpp compiled unmodified
                        (oracle/_ref/libref_orb_mono.so, monotone allocator; see DESIGN.md quadtree tie rule)
 Seeds are fixed; re-running reproduces the files bit for bit."""
@@ -60,6 +62,37 @@ def cv_fixtures():
     np.savez_compressed(os.path.join(HERE, "cv_primitives.npz"), **out)
 
 
+UNDISTORT_CAMERAS = [
+    # fx, fy, cx, cy, dist, image (w, h)
+    ("euroc", 458.654, 457.296, 367.215, 248.375, [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], (752, 480)),   # conf/vi_euroc.yaml
+    ("k3", 458.654, 457.296, 367.215, 248.375, [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05, 0.013], (752, 480)),
+    ("barrel", 718.856, 718.856, 607.1928, 185.2157, [0.11, -0.23, 0.0012, -0.0021], (1241, 376)),
+    ("strong", 300.0, 310.0, 320.5, 239.5, [-0.9, 0.5, 0.01, 0.01, 0.3], (640, 480)),                                    # drives icdist < 0 at the rim
+]
+
+
+def undistort_fixtures():
+    import cv2
+    assert cv2.__version__ == "4.13.0", cv2.__version__
+    rng = np.random.default_rng(77)
+    out = {}
+    for name, fx, fy, cx, cy, dist, (w, h) in UNDISTORT_CAMERAS:
+        K = np.array([[fx, 0, cx], [0, fy, cy], [0, 0, 1]], np.float32)
+        D = np.array(dist, np.float32).reshape(-1, 1)
+        # keypoint-like positions: integer level-0 pixels, higher-level pixels times a scale factor, and a few out-of-image points
+        pts = np.concatenate([rng.integers(0, [w, h], (1500, 2)).astype(np.float32),
+                              (rng.integers(0, [w // 2, h // 2], (1500, 2)) * np.float32(1.2) ** rng.integers(1, 8, (1500, 1))).astype(np.float32),
+                              rng.uniform(-60, [w + 60, h + 60], (200, 2)).astype(np.float32)])
+        corners = np.array([[0, 0], [w, 0], [0, h], [w, h]], np.float32)          # Frame::ComputeImageBounds, Frame.cpp:313-317
+        out[name + "_K"] = K
+        out[name + "_D"] = D.ravel()
+        out[name + "_wh"] = np.array([w, h], np.int32)
+        out[name + "_pts"] = pts
+        out[name + "_und"] = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, D, None, K).reshape(-1, 2)
+        out[name + "_corners_und"] = cv2.undistortPoints(corners.reshape(-1, 1, 2), K, D, None, K).reshape(-1, 2)
+    np.savez_compressed(os.path.join(HERE, "undistort.npz"), **out)
+
+
 def ref_fixtures():
     from _oracle import RefExtractor
     from motioncheck_ccm_slam_b200.synth import make_frame
@@ -76,6 +109,7 @@ def ref_fixtures():
 
 if __name__ == "__main__":
     cv_fixtures()
+    undistort_fixtures()
     ref_fixtures()
-    for f in ("cv_primitives.npz", "ref_extract.npz"):
+    for f in ("cv_primitives.npz", "undistort.npz", "ref_extract.npz"):
         print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

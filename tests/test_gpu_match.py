@@ -554,3 +554,102 @@ def test_distinctive_descriptors(gm, seed, n_points, max_obs):
     assert (bo == -1).any() and (bo > 0).sum() > n_points // 4
     b0, _ = distinctive_descriptors(gm, np.zeros(1, np.int32), np.zeros((0, 32), np.uint8))
     assert len(b0) == 0
+
+
+# ---- Frame::UndistortKeyPoints / ComputeImageBounds (Frame.cpp:277-343) ----------------------------------------------------
+_UND_CAMERAS = ("euroc", "k3", "barrel", "strong")
+
+
+def _und_golden():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "undistort.npz"))
+
+
+def _camera(U, cam):
+    from motioncheck_ccm_slam_b200.matcher import make_camera
+    K = U[cam + "_K"]
+    return make_camera(K[0, 0], K[1, 1], K[0, 2], K[1, 2], list(U[cam + "_D"]))
+
+
+@pytest.mark.parametrize("cam", _UND_CAMERAS)
+def test_undistort_keypoints(gm, cam):
+    """cv::undistortPoints on the device: bit-identical to the cv2 4.13.0 golden vectors and, on 200k random points, to the
+    oracle restatement (doubles, no FMA contraction, five iterations, the icdist < 0 bail-out of the 'strong' camera)."""
+    from _oracle import oracle_image_bounds, oracle_undistort
+    U = _und_golden()
+    c = _camera(U, cam)
+    got = gm.UndistortKeyPoints(c, U[cam + "_pts"])
+    assert np.array_equal(got.view(np.uint32), U[cam + "_und"].view(np.uint32))
+    w, h = U[cam + "_wh"]
+    rng = np.random.default_rng(5)
+    pts = np.concatenate([rng.uniform(-80, [w + 80, h + 80], (200000, 2)), rng.integers(0, [w, h], (50000, 2))]).astype(np.float32)
+    assert np.array_equal(gm.UndistortKeyPoints(c, pts).view(np.uint32), oracle_undistort(pts, U[cam + "_K"], U[cam + "_D"]).view(np.uint32))
+    assert gm.UndistortKeyPoints(c, np.zeros((0, 2), np.float32)).shape == (0, 2)
+    # ComputeImageBounds + grid constants
+    g, b = gm.ComputeImageBounds(c, w, h)
+    ob = oracle_image_bounds(U[cam + "_K"], U[cam + "_D"], w, h)
+    cu = U[cam + "_corners_und"]
+    assert np.array_equal(b, np.array([min(cu[0, 0], cu[2, 0]), max(cu[1, 0], cu[3, 0]), min(cu[0, 1], cu[1, 1]), max(cu[2, 1], cu[3, 1])], np.float32))
+    assert np.array_equal(np.array([g.min_x, b[1], g.min_y, b[3], g.inv_w, g.inv_h], np.float32), ob)
+
+
+def test_undistort_zero_k1_is_a_copy(gm):
+    """Frame.cpp:279-283 / :311: only k1 is tested; with k1 == 0 the keypoints are copied and the bounds are the image."""
+    from motioncheck_ccm_slam_b200.matcher import make_camera
+    c = make_camera(458.654, 457.296, 367.215, 248.375, [0.0, 0.07, 0.001, 0.002])
+    pts = np.random.default_rng(1).uniform(0, 700, (1000, 2)).astype(np.float32)
+    assert np.array_equal(gm.UndistortKeyPoints(c, pts), pts)
+    g, b = gm.ComputeImageBounds(c, 752, 480)
+    assert np.array_equal(b, np.array([0, 752, 0, 480], np.float32))
+    assert g.inv_w == np.float32(75) / np.float32(752) and g.inv_h == np.float32(48) / np.float32(480)
+    with pytest.raises(Exception):
+        gm.UndistortKeyPoints(make_camera(0.0, 1.0, 0.0, 0.0, [0.1, 0, 0, 0]), pts)
+
+
+def test_extractor_to_packs_with_distorted_camera(gm):
+    """ExtractORB -> UndistortKeyPoints -> AssignFeaturesToGrid without leaving HBM: the undistortion fused into the pack
+    fill and the stand-alone batched kernel both give mvKeysUn, and the grid built from them, of the oracle."""
+    torch = pytest.importorskip("torch")
+    from _oracle import oracle_undistort
+    from motioncheck_ccm_slam_b200 import ORBextractor
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    from motioncheck_ccm_slam_b200.matcher import FramePack, packs_from_extractor_batch_device
+    from motioncheck_ccm_slam_b200.synth import make_stream
+    U = _und_golden()
+    cam = _camera(U, "euroc")
+    B, w, h = 3, 752, 480
+    frames = make_stream(777, B, w, h)
+    ex = ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B, device=0)
+    cap = ex.max_keypoints()
+    dev = torch.device("cuda", 0)
+    d_img = torch.from_numpy(frames).to(dev)
+    d_kp = torch.zeros((B, cap, 6), dtype=torch.float32, device=dev)
+    d_desc = torch.zeros((B, cap, 32), dtype=torch.uint8, device=dev)
+    d_n = torch.zeros((B,), dtype=torch.int32, device=dev)
+    d_un = torch.full((B, cap, 2), -1.0, dtype=torch.float32, device=dev)
+    torch.cuda.synchronize()
+    ex.extract_batch_device(d_img.data_ptr(), B, h, w, w, w * h, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+    ex.sync()
+    kp = d_kp.cpu().numpy().view(KP_DTYPE).reshape(B, cap)
+    desc, n = d_desc.cpu().numpy(), d_n.cpu().numpy()
+    grid, bounds = gm.ComputeImageBounds(cam, w, h)
+    assert bounds[0] < 0 and bounds[1] > w                       # barrel distortion: the undistorted image is larger
+    gm.undistort_keypoints_batch_device(cam, B, d_kp.data_ptr(), d_n.data_ptr(), cap, d_un.data_ptr())
+    fused = [FramePack(gm, cap) for _ in range(B)]
+    staged = [FramePack(gm, cap) for _ in range(B)]
+    packs_from_extractor_batch_device(fused, grid, d_kp.data_ptr(), d_desc.data_ptr(), d_n.data_ptr(), cap, cam=cam)
+    packs_from_extractor_batch_device(staged, grid, d_kp.data_ptr(), d_desc.data_ptr(), d_n.data_ptr(), cap, d_xy_un=d_un.data_ptr())
+    gm.sync()
+    un = d_un.cpu().numpy()
+    for j in range(B):
+        k = kp[j, :n[j]]
+        want = oracle_undistort(np.stack([k["x"], k["y"]], 1), U["euroc_K"], U["euroc_D"])
+        assert np.array_equal(un[j, :n[j]].view(np.uint32), want.view(np.uint32))
+        assert (un[j, n[j]:] == -1).all()                                           # rows past the count are not touched
+        of = OracleFrame(desc[j, :n[j]], want[:, 0], want[:, 1], k["octave"], k["angle"], grid)
+        ocs, oitems = of.csr()
+        for p in (fused[j], staged[j]):
+            cs, items = p.get_grid()
+            assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
+            assert p.count() == n[j]
+    ex.close()

@@ -6,7 +6,7 @@ import os
 import numpy as np
 import pytest
 
-from _oracle import oracle_lib
+from _oracle import oracle_image_bounds, oracle_lib, oracle_undistort
 
 G = np.load(os.path.join(os.path.dirname(__file__), "golden", "cv_primitives.npz"))
 u8p = ctypes.c_void_p
@@ -91,6 +91,33 @@ def test_atan_golden(L):
     true = np.degrees(np.arctan2(G["atan_yx"][:, 0].astype(np.float64), G["atan_yx"][:, 1].astype(np.float64))) % 360
     err = np.abs((got - true + 180) % 360 - 180)
     assert err.max() < 0.02   # fastAtan2 is an approximation (up to ~1.7e-4 rad off true atan2): replicate it, don't "fix" it
+
+
+U = np.load(os.path.join(os.path.dirname(__file__), "golden", "undistort.npz"))
+UNDISTORT_CAMERAS = ("euroc", "k3", "barrel", "strong")
+
+
+@pytest.mark.parametrize("cam", UNDISTORT_CAMERAS)
+def test_undistort_golden(cam):
+    """cv::undistortPoints as Frame::UndistortKeyPoints / ComputeImageBounds call it (Frame.cpp:295, :321), bit for bit."""
+    got = oracle_undistort(U[cam + "_pts"], U[cam + "_K"], U[cam + "_D"])
+    assert np.array_equal(got.view(np.uint32), U[cam + "_und"].view(np.uint32))
+    assert np.abs(got - U[cam + "_pts"]).max() > 1.0          # the model does move points
+    w, h = U[cam + "_wh"]
+    c = U[cam + "_corners_und"]
+    b = oracle_image_bounds(U[cam + "_K"], U[cam + "_D"], w, h)
+    assert np.array_equal(b[:4], np.array([min(c[0, 0], c[2, 0]), max(c[1, 0], c[3, 0]), min(c[0, 1], c[1, 1]), max(c[2, 1], c[3, 1])], np.float32))
+
+
+def test_undistort_live_against_cv2():
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(11)
+    for cam in UNDISTORT_CAMERAS:
+        K, D = U[cam + "_K"], U[cam + "_D"]
+        w, h = U[cam + "_wh"]
+        pts = rng.uniform(-40, [w + 40, h + 40], (50000, 2)).astype(np.float32)
+        ref = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, D.reshape(-1, 1), None, K).reshape(-1, 2)
+        assert np.array_equal(oracle_undistort(pts, K, D).view(np.uint32), ref.view(np.uint32))
 
 
 def test_live_against_cv2(L):
