@@ -197,6 +197,29 @@ int ccm_vocabulary_transform_device(ccm_matcher* m, const ccm_vocabulary* v, int
  * minimum wins), -1 for a point without rows; best_median[p] = that median (may be NULL). HOST arrays. */
 int ccm_distinctive_descriptors(ccm_matcher* m, int n_points, const int* start, const uint8_t* desc, int* best, int* best_median);
 
+/* ---- keyframe wire format: the CvKeyPoint[] / Descriptor[] arrays of ccmslam_msgs/KF ----------------------------
+ * ROS 1 serialisation of what KeyFrame::ConvertToMessage fills (KeyFrame.cpp:1462-1472, Converter.cc:166-179):
+ *   kp_bytes   = u32 n | n x { f32 x, f32 y, u8 size, f32 angle, u8 response, i8 octave }   (CCM_WIRE_KP_BYTES each)
+ *   desc_bytes = u32 n | n x u8[32]
+ * size / response truncate to u8 and octave to i8 on the wire, as (u_int8_t)kp.size does. Buffers are little-endian
+ * byte strings of CCM_WIRE_KP_LEN(n) / CCM_WIRE_DESC_LEN(n) bytes; allocate them rounded up to a multiple of 4. */
+#define CCM_WIRE_KP_BYTES 15
+#define CCM_WIRE_KP_LEN(n) (4 + (size_t)CCM_WIRE_KP_BYTES * (size_t)(n))
+#define CCM_WIRE_DESC_LEN(n) (4 + (size_t)32 * (size_t)(n))
+/* client side, device-resident and asynchronous: n keypoints / descriptor rows of the extractor's output (d_xy_un
+ * [n][2] overrides the positions with mvKeysUn, or NULL) -> d_kp_bytes, d_desc_bytes (device, 4-byte aligned) */
+int ccm_wire_encode_keyframe_device(ccm_matcher* m, const ccm_keypoint* d_kp, const float* d_xy_un, const uint8_t* d_desc,
+                                    int n, uint8_t* d_kp_bytes, uint8_t* d_desc_bytes);
+/* host convenience: upload, encode, download; synchronous */
+int ccm_wire_encode_keyframe(ccm_matcher* m, const ccm_keypoint* kp, const float* xy_un, const uint8_t* desc, int n,
+                             uint8_t* kp_bytes, uint8_t* desc_bytes);
+/* server side, KeyFrame::WriteMembersFromMessage (KeyFrame.cpp:1689-1702, Converter.cc:181-193): the two received byte
+ * strings (HOST) go up as they are and are decoded on the device straight into a frame pack (positions, octaves,
+ * angles, descriptors, feature grid). kp_out [n] (HOST, may be NULL) receives the decoded mvKeysUn. Returns
+ * CCM_E_BADARG when the counts and lengths disagree, CCM_E_CAPACITY when the pack is too small. */
+int ccm_frame_pack_from_wire(ccm_frame_pack* p, const ccm_grid_params* g, const uint8_t* kp_bytes, size_t kp_len,
+                             const uint8_t* desc_bytes, size_t desc_len, ccm_keypoint* kp_out);
+
 /* ---- server keyframe-database search (BASELINE.json configs[4]) --------------------------------------------
  * Best and second-best Hamming distance of every query descriptor over a (shard of a) target descriptor database,
  * first-wins on ties: the inner loop of SearchByBoW(KF,KF) (:607-637) with one all-inclusive node. */

@@ -93,6 +93,9 @@ SIGNATURES.update({
     "ccm_undistort_points": (_i, [_vp, _cp, _i, _vp, _vp]),
     "ccm_undistort_keypoints_batch_device": (_i, [_vp, _cp, _i, _vp, _vp, _i, _vp]),
     "ccm_image_bounds": (_i, [_vp, _cp, _i, _i, _gp, _vp]),
+    "ccm_wire_encode_keyframe_device": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ccm_wire_encode_keyframe": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ccm_frame_pack_from_wire": (_i, [_vp, _gp, _vp, _sz, _vp, _sz, _vp]),
     "ccm_frame_pack_get_grid": (_i, [_vp, _vp, _vp, _ip]),
     "ccm_frame_pack_count": (_i, [_vp, _ip]),
     "ccm_search_window": (_i, [_vp, _vp, _wp, _i, _vp, _vp, _vp, _vp, _ip]),

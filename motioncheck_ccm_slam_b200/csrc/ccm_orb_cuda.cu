@@ -7,4 +7,5 @@
 #include "match_allpairs.cu"
 #include "match_window.cu"
 #include "match_bow.cu"
+#include "match_wire.cu"
 #include "match_api.cu"

@@ -334,6 +334,70 @@ int ccm_frame_pack_get_grid(ccm_frame_pack* p, int* cell_start, int* items, int*
     return CCM_OK;
 }
 
+/* ---- keyframe wire format ---------------------------------------------------------------------------------- */
+int ccm_wire_encode_keyframe_device(ccm_matcher* m, const ccm_keypoint* d_kp, const float* d_xy_un, const uint8_t* d_desc,
+                                    int n, uint8_t* d_kp_bytes, uint8_t* d_desc_bytes) {
+    if (!m || n < 0 || !d_kp_bytes || !d_desc_bytes || (n > 0 && (!d_kp || !d_desc))) return CCM_E_BADARG;
+    if (((uintptr_t)d_kp_bytes | (uintptr_t)d_desc_bytes | (uintptr_t)d_desc) & 3) { m->err = "wire buffers and descriptor rows must be 4-byte aligned"; return CCM_E_BADARG; }
+    cudaSetDevice(m->device);
+    k_wire_encode<<<std::max(1, (n + WIRE_CTA - 1) / WIRE_CTA), WIRE_CTA, 0, m->stream>>>((const ccm_keypoint_dev*)d_kp, (const float2*)d_xy_un, (const uint32_t*)d_desc, n,
+                                                                                            (uint32_t*)d_kp_bytes, (uint32_t*)d_desc_bytes);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+int ccm_wire_encode_keyframe(ccm_matcher* m, const ccm_keypoint* kp, const float* xy_un, const uint8_t* desc, int n,
+                             uint8_t* kp_bytes, uint8_t* desc_bytes) {
+    if (!m || n < 0 || !kp_bytes || !desc_bytes || (n > 0 && (!kp || !desc))) return CCM_E_BADARG;
+    cudaSetDevice(m->device);
+    ccm_keypoint* dkp; float* dxy; uint8_t *ddesc, *dkb, *ddb;
+    int rc;
+    const size_t nn = std::max(n, 1);
+    if ((rc = mbuf(m, MB_A, nn, &dkp)) || (rc = mbuf(m, MB_B, nn * 2, &dxy)) || (rc = mbuf(m, MB_C, nn * 32, &ddesc)) ||
+        (rc = mbuf(m, MB_D, CCM_WIRE_KP_LEN(n) + 4, &dkb)) || (rc = mbuf(m, MB_E, CCM_WIRE_DESC_LEN(n) + 4, &ddb))) return rc;
+    if (n > 0) {
+        MCK(cudaMemcpyAsync(dkp, kp, (size_t)n * sizeof(ccm_keypoint), cudaMemcpyHostToDevice, m->stream));
+        if (xy_un) MCK(cudaMemcpyAsync(dxy, xy_un, (size_t)n * 8, cudaMemcpyHostToDevice, m->stream));
+        MCK(cudaMemcpyAsync(ddesc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+    }
+    if ((rc = ccm_wire_encode_keyframe_device(m, dkp, xy_un ? dxy : nullptr, ddesc, n, dkb, ddb))) return rc;
+    MCK(cudaMemcpyAsync(kp_bytes, dkb, CCM_WIRE_KP_LEN(n), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaMemcpyAsync(desc_bytes, ddb, CCM_WIRE_DESC_LEN(n), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
+int ccm_frame_pack_from_wire(ccm_frame_pack* p, const ccm_grid_params* g, const uint8_t* kp_bytes, size_t kp_len,
+                             const uint8_t* desc_bytes, size_t desc_len, ccm_keypoint* kp_out) {
+    if (!p || !kp_bytes || !desc_bytes || kp_len < 4 || desc_len < 4) return CCM_E_BADARG;
+    ccm_matcher* m = p->m;
+    uint32_t n_kp, n_desc;
+    std::memcpy(&n_kp, kp_bytes, 4); std::memcpy(&n_desc, desc_bytes, 4);           // little-endian host (x86-64 / aarch64)
+    if (n_kp != n_desc || kp_len != CCM_WIRE_KP_LEN(n_kp) || desc_len != CCM_WIRE_DESC_LEN(n_desc)) {
+        m->err = "wire arrays: counts and byte lengths disagree";
+        return CCM_E_BADARG;
+    }
+    const int n = (int)n_kp;
+    if (n > p->cap) { m->err = "frame pack capacity too small"; return CCM_E_CAPACITY; }
+    int rc = check_grid(m, g);
+    if (rc) return rc;
+    cudaSetDevice(m->device);
+    uint8_t *dkb, *ddb; ccm_keypoint* dkp;
+    if ((rc = mbuf(m, MB_D, kp_len + 4, &dkb)) || (rc = mbuf(m, MB_F, desc_len + 4, &ddb)) || (rc = mbuf(m, MB_A, (size_t)std::max(n, 1), &dkp))) return rc;
+    MCK(cudaMemcpyAsync(dkb, kp_bytes, kp_len, cudaMemcpyHostToDevice, m->stream));
+    MCK(cudaMemcpyAsync(ddb, desc_bytes, desc_len, cudaMemcpyHostToDevice, m->stream));
+    p->g = *g; p->n_host = n; p->desc_view = p->desc;
+    WireDecodeOut O{p->x, p->y, p->angle, p->octave, (uint32_t*)p->desc, kp_out ? (ccm_keypoint_dev*)dkp : nullptr, p->n};
+    k_wire_decode<<<std::max(1, (n + WIRE_CTA - 1) / WIRE_CTA), WIRE_CTA, 0, m->stream>>>((const uint32_t*)dkb, (const uint32_t*)ddb, n, O);
+    m->launches++;
+    MCK(cudaGetLastError());
+    if ((rc = launch_build_grid(m, &p, 1))) return rc;
+    if (kp_out && n > 0) MCK(cudaMemcpyAsync(kp_out, dkp, (size_t)n * sizeof(ccm_keypoint), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaStreamSynchronize(m->stream));
+    return CCM_OK;
+}
+
 /* ---- windowed searches ------------------------------------------------------------------------------------ */
 static int fill_params(ccm_matcher* m, const ccm_window_params* prm, WindowParamsDev* d) {
     if (!prm || prm->mode < CCM_WIN_PROJ_MAPPOINTS || prm->mode > CCM_WIN_INIT) { m->err = "bad window mode"; return CCM_E_BADARG; }

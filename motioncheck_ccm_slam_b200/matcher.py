@@ -102,6 +102,22 @@ class Matcher:
         self._check(self._lib.ccm_image_bounds(self._h, ctypes.byref(cam), int(width), int(height), ctypes.byref(g), b.ctypes.data))
         return g, b
 
+    def wire_encode_keyframe(self, kp, desc, xy_un=None):
+        """The CvKeyPoint[] / Descriptor[] arrays of KeyFrame::ConvertToMessage (KeyFrame.cpp:1462-1472) as ROS 1 serialises
+        them -> (kp_bytes, desc_bytes). kp: extractor.KP_DTYPE records; xy_un [n][2] overrides the positions (mvKeysUn)."""
+        kp = np.ascontiguousarray(kp)
+        n = len(kp)
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(n, 32)
+        xy = None if xy_un is None else np.ascontiguousarray(xy_un, np.float32).reshape(n, 2)
+        kb = np.zeros((4 + 15 * n + 3) // 4 * 4, np.uint8)
+        db = np.zeros(4 + 32 * n, np.uint8)
+        self._check(self._lib.ccm_wire_encode_keyframe(self._h, kp.ctypes.data, None if xy is None else xy.ctypes.data, desc.ctypes.data, n,
+                                                       kb.ctypes.data, db.ctypes.data))
+        return kb[:4 + 15 * n].tobytes(), db.tobytes()
+
+    def wire_encode_keyframe_device(self, d_kp, d_xy_un, d_desc, n, d_kp_bytes, d_desc_bytes):
+        self._check(self._lib.ccm_wire_encode_keyframe_device(self._h, d_kp, d_xy_un, d_desc, int(n), d_kp_bytes, d_desc_bytes))
+
     def match_allpairs_best2(self, q, targets, index_base=0):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
         t = np.ascontiguousarray(targets, np.uint8).reshape(-1, 32)
@@ -147,6 +163,19 @@ class FramePack:
         self.m._check(self.m._lib.ccm_frame_pack_upload(self._h, ctypes.byref(grid), n, desc.ctypes.data, x.ctypes.data,
                                                         y.ctypes.data, octave.ctypes.data, angle.ctypes.data))
         return self
+
+    def from_wire(self, grid, kp_bytes, desc_bytes, want_keypoints=True):
+        """KeyFrame::WriteMembersFromMessage (KeyFrame.cpp:1689-1702): the CvKeyPoint[] / Descriptor[] byte strings of a
+        received ccmslam_msgs/KF -> this pack; returns the decoded mvKeysUn (extractor.KP_DTYPE) or None."""
+        from .extractor import KP_DTYPE
+        kb = np.frombuffer(bytes(kp_bytes), np.uint8)
+        db = np.frombuffer(bytes(desc_bytes), np.uint8)
+        n = int(kb[:4].view("<u4")[0]) if len(kb) >= 4 else 0
+        out = np.zeros(max(n, 1), KP_DTYPE) if want_keypoints else None
+        self.grid = grid
+        self.m._check(self.m._lib.ccm_frame_pack_from_wire(self._h, ctypes.byref(grid), kb.ctypes.data, len(kb), db.ctypes.data, len(db),
+                                                           out.ctypes.data if want_keypoints else None))
+        return out[:n] if want_keypoints else None
 
     def from_extractor_device(self, grid, d_kp, d_desc, d_n, d_xy_un=None):
         self.grid = grid

@@ -630,4 +630,44 @@ void mo_match_allpairs_best2(int nq, const uint8_t* q_desc, long long nt, const 
     }
 }
 
+/* Keyframe wire format — PARITY UNPINNED: cslam/src/Converter.cc needs Eigen and g2o and ccmslam_msgs needs ROS genmsg,
+ * none of which exist in this image, so the two conversions are restated here and checked only against an independent
+ * numpy packing (tests/test_match_oracle.py). KeyFrame::ConvertToMessage (cslam/src/KeyFrame.cpp:1462-1472) pushes
+ * Converter::toCvKeyPointMsg(mvKeysUn[i]) (Converter.cc:166-179: x, y, angle copied; octave to int8; response and size
+ * through (u_int8_t)float) and one Descriptor per row; ROS 1 serialises CvKeyPoint[] / Descriptor[] (cslam_msgs/msg) as a
+ * u32 count followed by the unpadded little-endian fields in declaration order:
+ * fPoint2f_x, fPoint2f_y, size, angle, response, octave = 15 bytes; uint8[32] = 32 bytes. */
+void mo_wire_encode_keyframe(int n, const float* x, const float* y, const float* size, const float* angle, const float* response,
+                             const int* octave, const uint8_t* desc, uint8_t* kp_bytes, uint8_t* desc_bytes) {
+    const uint32_t cnt = (uint32_t)n;
+    std::memcpy(kp_bytes, &cnt, 4);
+    std::memcpy(desc_bytes, &cnt, 4);
+    for (int i = 0; i < n; i++) {
+        uint8_t* r = kp_bytes + 4 + (size_t)15 * i;
+        const uint8_t sz = (uint8_t)size[i], rs = (uint8_t)response[i];     /* (u_int8_t)kp.size, (u_int8_t)kp.response */
+        const int8_t oc = (int8_t)octave[i];                                /* Msg.octave = kp.octave (int8) */
+        std::memcpy(r, &x[i], 4); std::memcpy(r + 4, &y[i], 4); r[8] = sz; std::memcpy(r + 9, &angle[i], 4); r[13] = rs;
+        std::memcpy(r + 14, &oc, 1);
+        for (int b = 0; b < 32; b++) desc_bytes[4 + (size_t)32 * i + b] = desc[(size_t)32 * i + b];   /* KeyFrame.cpp:1464-1471 */
+    }
+}
+
+/* KeyFrame::WriteMembersFromMessage, KeyFrame.cpp:1689-1702 + Converter::fromCvKeyPointMsg, Converter.cc:181-193.
+ * Returns n, or -1 when the two counts disagree. */
+int mo_wire_decode_keyframe(const uint8_t* kp_bytes, const uint8_t* desc_bytes, int cap, float* x, float* y, float* size, float* angle,
+                            float* response, int* octave, uint8_t* desc) {
+    uint32_t n, nd;
+    std::memcpy(&n, kp_bytes, 4);
+    std::memcpy(&nd, desc_bytes, 4);
+    if (n != nd || (int)n > cap) return -1;
+    for (uint32_t i = 0; i < n; i++) {
+        const uint8_t* r = kp_bytes + 4 + (size_t)15 * i;
+        int8_t oc;
+        std::memcpy(&x[i], r, 4); std::memcpy(&y[i], r + 4, 4); std::memcpy(&angle[i], r + 9, 4); std::memcpy(&oc, r + 14, 1);
+        size[i] = (float)r[8]; response[i] = (float)r[13]; octave[i] = oc;
+        std::memcpy(desc + (size_t)32 * i, desc_bytes + 4 + (size_t)32 * i, 32);
+    }
+    return (int)n;
+}
+
 }  // extern "C"

@@ -117,6 +117,36 @@ def oracle_image_bounds(K, dist, w, h, cols=75, rows=48):
     return np.array([mn_x, mx_x, mn_y, mx_y, f(cols) / (mx_x - mn_x), f(rows) / (mx_y - mn_y)], np.float32)
 
 
+def oracle_wire_encode(kp, desc):
+    """oracle/match_oracle.cpp mo_wire_encode_keyframe on KP_DTYPE-like records -> (kp_bytes, desc_bytes)."""
+    L = match_lib()
+    n = len(kp)
+    a = {k: np.ascontiguousarray(kp[k], np.int32 if k == "octave" else np.float32) for k in ("x", "y", "size", "angle", "response", "octave")}
+    d = np.ascontiguousarray(desc, np.uint8).reshape(n, 32)
+    kb, db = np.zeros(4 + 15 * n, np.uint8), np.zeros(4 + 32 * n, np.uint8)
+    L.mo_wire_encode_keyframe.restype = None
+    L.mo_wire_encode_keyframe.argtypes = [ctypes.c_int] + [ctypes.c_void_p] * 9
+    L.mo_wire_encode_keyframe(n, *[a[k].ctypes.data for k in ("x", "y", "size", "angle", "response", "octave")], d.ctypes.data, kb.ctypes.data, db.ctypes.data)
+    return kb.tobytes(), db.tobytes()
+
+
+def oracle_wire_decode(kp_bytes, desc_bytes, cap=1 << 16):
+    """mo_wire_decode_keyframe -> (dict of x, y, size, angle, response, octave; desc [n][32]) or None when the counts disagree."""
+    L = match_lib()
+    kb, db = np.frombuffer(kp_bytes, np.uint8), np.frombuffer(desc_bytes, np.uint8)
+    f = {k: np.zeros(cap, np.float32) for k in ("x", "y", "size", "angle", "response")}
+    oc, d = np.zeros(cap, np.int32), np.zeros((cap, 32), np.uint8)
+    L.mo_wire_decode_keyframe.restype = ctypes.c_int
+    L.mo_wire_decode_keyframe.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 7
+    n = L.mo_wire_decode_keyframe(kb.ctypes.data, db.ctypes.data, cap, f["x"].ctypes.data, f["y"].ctypes.data, f["size"].ctypes.data,
+                                  f["angle"].ctypes.data, f["response"].ctypes.data, oc.ctypes.data, d.ctypes.data)
+    if n < 0:
+        return None
+    out = {k: v[:n] for k, v in f.items()}
+    out["octave"] = oc[:n]
+    return out, d[:n]
+
+
 def ref_available(mono=True):
     return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_orb_mono.so" if mono else "libref_orb.so"))
 

@@ -653,3 +653,47 @@ def test_extractor_to_packs_with_distorted_camera(gm):
             assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
             assert p.count() == n[j]
     ex.close()
+
+
+# ---- keyframe wire format (KeyFrame.cpp:1462-1472, 1689-1702; Converter.cc:166-193) --------------------------------------
+@pytest.mark.parametrize("seed,n", [(1, 1000), (2, 1), (3, 0), (4, 257), (5, 256), (6, 5000)])
+def test_wire_format_encode_decode(gm, seed, n):
+    """Client-side encode and server-side decode-into-a-pack on the device against the oracle restatement: byte strings
+    identical, decoded keypoints (lossy u8 size / response, i8 octave) identical, the pack's grid that of the decoded frame."""
+    from _oracle import oracle_wire_decode, oracle_wire_encode
+    from test_match_oracle import _wire_keypoints
+    from motioncheck_ccm_slam_b200.matcher import FramePack, frame_grid
+    kp, desc = _wire_keypoints(seed, n)
+    kb, db = gm.wire_encode_keyframe(kp, desc)
+    okb, odb = oracle_wire_encode(kp, desc)
+    assert kb == okb and db == odb
+    grid = frame_grid(W, H, min_x=-20.0, min_y=-20.0)
+    p = FramePack(gm, max(n, 1) + 3)
+    got = p.from_wire(grid, kb, db)
+    back, d2 = oracle_wire_decode(okb, odb)
+    for k in ("x", "y", "size", "angle", "response", "octave"):
+        assert np.array_equal(got[k], back[k]), k
+    assert p.count() == n
+    of = OracleFrame(d2, back["x"], back["y"], back["octave"], back["angle"], grid)
+    cs, items = p.get_grid()
+    ocs, oitems = of.csr()
+    assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
+    if n >= 256:    # the descriptors landed in the pack: a query equal to row 7 finds row 7 at distance 0
+        from motioncheck_ccm_slam_b200.matcher import ORBmatcher
+        _, res = ORBmatcher(gm).SearchBestInWindow(p, np.ones(1, np.uint8), back["x"][7:8], back["y"][7:8], np.full(1, 3.0, np.float32),
+                                                back["octave"][7:8].astype(np.int32), d2[7:8], 256)
+        assert res["best_dist"][0] == 0
+    with pytest.raises(Exception):
+        p.from_wire(grid, kb, db + b"\0")                                  # length does not match the count
+    p.close()
+
+
+def test_wire_format_mvkeysun_override(gm):
+    """ConvertToMessage sends mvKeysUn: the encoder takes the undistorted positions from the d_xy_un array."""
+    from _oracle import oracle_wire_encode
+    from test_match_oracle import _wire_keypoints
+    kp, desc = _wire_keypoints(9, 777)
+    xy = np.random.default_rng(9).uniform(0, 700, (777, 2)).astype(np.float32)
+    kb, db = gm.wire_encode_keyframe(kp, desc, xy_un=xy)
+    kp2 = kp.copy(); kp2["x"] = xy[:, 0]; kp2["y"] = xy[:, 1]
+    assert (kb, db) == oracle_wire_encode(kp2, desc)

@@ -149,3 +149,47 @@ def test_distinctive_descriptors_vs_numpy():
         D = (b[:, None, :] != b[None, :, :]).sum(2)
         m = np.sort(D, axis=1)[:, int(0.5 * (len(b) - 1))]
         assert best[p] == int(np.argmin(m)) and med[p] == int(m.min())
+
+
+def _wire_keypoints(seed, n):
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    rng = np.random.default_rng(seed)
+    kp = np.zeros(n, KP_DTYPE)
+    kp["octave"] = rng.integers(0, 8, n)
+    kp["x"] = rng.uniform(-20, 780, n).astype(np.float32)
+    kp["y"] = rng.uniform(-20, 500, n).astype(np.float32)
+    kp["size"] = (31 * np.float32(1.2) ** kp["octave"]).astype(np.int32)          # (int)(31 * scale), up to 111
+    kp["angle"] = rng.uniform(0, 360, n).astype(np.float32)
+    kp["response"] = rng.integers(7, 256, n)
+    if n > 4:
+        kp["response"][:2] = [37.75, 255.0]                                         # fractional values truncate
+        kp["size"][2] = 300.5                                                       # out of u8 range: low byte of the integer part
+        kp["octave"][3] = -1
+    return kp, rng.integers(0, 256, (n, 32), dtype=np.uint8)
+
+
+def test_wire_format_vs_numpy_packing():
+    """Keyframe wire arrays (KeyFrame.cpp:1462-1472, Converter.cc:166-193) — parity unpinned, see oracle/match_oracle.cpp:
+    the restatement against an independent numpy structured-dtype packing of the .msg definitions, and the round trip."""
+    from _oracle import oracle_wire_decode, oracle_wire_encode
+    msg = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "u1"), ("angle", "<f4"), ("response", "u1"), ("octave", "i1")])
+    assert msg.itemsize == 15
+    for seed, n in [(1, 1000), (2, 1), (3, 0), (4, 257)]:
+        kp, desc = _wire_keypoints(seed, n)
+        kb, db = oracle_wire_encode(kp, desc)
+        rec = np.zeros(n, msg)
+        for k in ("x", "y", "angle"):
+            rec[k] = kp[k]
+        rec["size"] = kp["size"].astype(np.int64) & 255
+        rec["response"] = kp["response"].astype(np.int64) & 255
+        rec["octave"] = kp["octave"].astype(np.int8)
+        assert kb == np.uint32(n).tobytes() + rec.tobytes()
+        assert db == np.uint32(n).tobytes() + desc.tobytes()
+        back, d2 = oracle_wire_decode(kb, db)
+        assert np.array_equal(d2, desc)
+        for k in ("x", "y", "angle"):
+            assert np.array_equal(back[k], kp[k])
+        assert np.array_equal(back["size"], rec["size"].astype(np.float32)) and np.array_equal(back["response"], rec["response"].astype(np.float32))
+        assert np.array_equal(back["octave"], rec["octave"].astype(np.int32))
+    kb, db = oracle_wire_encode(*_wire_keypoints(5, 10))
+    assert oracle_wire_decode(kb, db[:4 + 32 * 9].replace(db[:4], np.uint32(9).tobytes(), 1)) is None     # counts disagree
