@@ -71,6 +71,19 @@ int ccm_orb_extract(ccm_orb* h, const uint8_t* img, int rows, int cols, size_t s
 int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n_imgs, int rows, int cols, size_t step,
                           ccm_keypoint* out_kp, uint8_t* out_desc, int capacity, int* out_n);
 
+/* The same call as an asynchronous pair, for a stream of batches: submit enqueues copy-in, kernels and copy-out and
+ * returns a ticket; wait blocks until that batch's results are in out_kp / out_desc / out_n. Two batches may be in
+ * flight (submit k+1, then wait k): the copy-in of one overlaps the kernels of the other, so the link and the SMs
+ * work at the same time. The frames in flight together must fit max_batch (each batch occupies its own frame slots
+ * of the arena), the image shape must not change while a batch is in flight, imgs and the output arrays must stay
+ * valid until wait returns, and batches complete in submission order. When out_kp / out_desc are pinned host memory
+ * and capacity == ccm_orb_max_keypoints(h), results are copied straight into them (whole rows; only the first
+ * out_n[f] entries of a row are meaningful). ccm_orb_extract_batch == submit + wait. Do not interleave with
+ * ccm_orb_extract_batch_device on the same handle while a ticket is open. */
+int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n_imgs, int rows, int cols, size_t step,
+                                 ccm_keypoint* out_kp, uint8_t* out_desc, int capacity, int* out_n, int* ticket);
+int ccm_orb_extract_batch_wait(ccm_orb* h, int ticket);
+
 /* Device-resident variant: images already in HBM at d_imgs + f*frame_stride (row pitch `pitch`, both multiples
  * of 4 bytes); results stay in HBM (d_kp [n][capacity], d_desc [n][capacity][32], d_n [n]) so the matcher can
  * consume them without a host round trip. Asynchronous on the handle's stream; pair with ccm_orb_sync. */

@@ -32,6 +32,8 @@ SIGNATURES = {
     "ccm_orb_max_keypoints": (_i, [_vp]),
     "ccm_orb_extract": (_i, [_vp, _vp, _i, _i, _sz, _vp, _vp, _i, _ip]),
     "ccm_orb_extract_batch": (_i, [_vp, _c.POINTER(_vp), _i, _i, _i, _sz, _vp, _vp, _i, _ip]),
+    "ccm_orb_extract_batch_submit": (_i, [_vp, _c.POINTER(_vp), _i, _i, _i, _sz, _vp, _vp, _i, _ip, _ip]),
+    "ccm_orb_extract_batch_wait": (_i, [_vp, _i]),
     "ccm_orb_extract_batch_device": (_i, [_vp, _vp, _i, _i, _i, _sz, _sz, _vp, _vp, _i, _vp]),
     "ccm_orb_sync": (_i, [_vp]),
     "ccm_orb_stream": (_vp, [_vp]),

@@ -17,6 +17,7 @@
 // orb_pyramid_fast.cu, orb_quadtree.cu and orb_describe.cu.
 
 #define CCM_MAX_CHUNKS 8
+#define CCM_MAX_TICKETS 2
 static thread_local std::string g_create_error = "";
 
 struct ccm_orb {
@@ -47,7 +48,17 @@ struct ccm_orb {
     // batches on the two lanes fill each other's latency-bound stages (quadtree, small pyramid levels).
     struct Lane { cudaStream_t s = nullptr, aux = nullptr; cudaEvent_t fork = nullptr, join = nullptr; } lane[2];
     uint8_t* d_stage = nullptr; size_t stage_bytes = 0;   // host entry point: staging for rows that are not 4-byte multiples
-    cudaEvent_t ev_in[CCM_MAX_CHUNKS] = {}, ev_done[CCM_MAX_CHUNKS] = {}, ev_out[CCM_MAX_CHUNKS] = {};
+    cudaEvent_t ev_in[CCM_MAX_TICKETS][CCM_MAX_CHUNKS] = {}, ev_done[CCM_MAX_TICKETS][CCM_MAX_CHUNKS] = {}, ev_out[CCM_MAX_TICKETS][CCM_MAX_CHUNKS] = {};
+    // batches in flight through the asynchronous host entry point (ccm_orb_extract_batch_submit / _wait)
+    struct Ticket {
+        bool active = false, empty = false, direct = false, trace = false;
+        int n = 0, slot0 = 0, n_chunks = 0, capacity = 0;
+        int first[CCM_MAX_CHUNKS + 1] = {};
+        ccm_keypoint* out_kp = nullptr; uint8_t* out_desc = nullptr; int* out_n = nullptr;
+        double t_call = 0, t_enq = 0;
+        cudaEvent_t tev[1 + 3 * CCM_MAX_CHUNKS] = {};
+    } tk[CCM_MAX_TICKETS];
+    int next_slot = 0, next_lane = 0;
     long long launches = 0;
     // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
     bool stage_timing = false;
@@ -368,10 +379,11 @@ int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
         if ((e = cudaStreamCreateWithFlags(&h->lane[i].aux, cudaStreamNonBlocking)) != cudaSuccess ||
             (e = cudaEventCreateWithFlags(&h->lane[i].fork, cudaEventDisableTiming)) != cudaSuccess ||
             (e = cudaEventCreateWithFlags(&h->lane[i].join, cudaEventDisableTiming)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
-    for (int i = 0; i < CCM_MAX_CHUNKS; i++)
-        if ((e = cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming)) != cudaSuccess ||
-            (e = cudaEventCreateWithFlags(&h->ev_done[i], cudaEventDisableTiming)) != cudaSuccess ||
-            (e = cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
+    for (int t = 0; t < CCM_MAX_TICKETS; t++)
+        for (int i = 0; i < CCM_MAX_CHUNKS; i++)
+            if ((e = cudaEventCreateWithFlags(&h->ev_in[t][i], cudaEventDisableTiming)) != cudaSuccess ||
+                (e = cudaEventCreateWithFlags(&h->ev_done[t][i], cudaEventDisableTiming)) != cudaSuccess ||
+                (e = cudaEventCreateWithFlags(&h->ev_out[t][i], cudaEventDisableTiming)) != cudaSuccess) { h->err = cudaGetErrorString(e); return fail(CCM_E_CUDA); }
     int rc = configure_shape(h, cfg->max_height, cfg->max_width);
     if (rc != CCM_OK) return fail(rc);
     *out = h;
@@ -381,13 +393,16 @@ int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
 void ccm_orb_destroy(ccm_orb* h) {
     if (!h) return;
     cudaSetDevice(h->cfg.device);
-    if (h->stream) cudaStreamSynchronize(h->stream);
+    for (cudaStream_t st : {h->s_in, h->stream, h->lane[1].s, h->lane[0].aux, h->lane[1].aux, h->s_out}) if (st) cudaStreamSynchronize(st);
     free_arena(h);
     for (int i = 0; i <= CCM_N_STAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
-    for (int i = 0; i < CCM_MAX_CHUNKS; i++) {
-        if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
-        if (h->ev_done[i]) cudaEventDestroy(h->ev_done[i]);
-        if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
+    for (int t = 0; t < CCM_MAX_TICKETS; t++) {
+        for (int i = 0; i < CCM_MAX_CHUNKS; i++) {
+            if (h->ev_in[t][i]) cudaEventDestroy(h->ev_in[t][i]);
+            if (h->ev_done[t][i]) cudaEventDestroy(h->ev_done[t][i]);
+            if (h->ev_out[t][i]) cudaEventDestroy(h->ev_out[t][i]);
+        }
+        for (auto& e : h->tk[t].tev) if (e) cudaEventDestroy(e);
     }
     if (h->d_stage) cudaFree(h->d_stage);
     for (int i = 0; i < 2; i++) {
@@ -459,22 +474,57 @@ int ccm_orb_extract_batch_device(ccm_orb* h, const uint8_t* d_imgs, int n, int r
     return run_pipeline(h, n, d_imgs, pitch, frame_stride, d_kp, d_desc, d_n, capacity);
 }
 
-int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int rows, int cols, size_t step,
-                          ccm_keypoint* out_kp, uint8_t* out_desc, int capacity, int* out_n) {
+// Host entry point, asynchronous pair. submit enqueues copy-in, kernels and copy-out of one batch and returns; wait blocks
+// until that batch's results are in the caller's arrays. Every batch takes a contiguous range of the arena's frame slots
+// (ring allocation over max_batch), so a second batch can be submitted while the first is still on the device: its
+// copy-in overlaps the first one's kernels and the link and the SMs are busy at the same time across calls.
+static double now_ms() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+static bool is_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n, int rows, int cols, size_t step,
+                                 ccm_keypoint* out_kp, uint8_t* out_desc, int capacity, int* out_n, int* ticket) {
     if (!h) return CCM_E_BADARG;
-    if (!imgs || !out_n || n < 1 || capacity < 0 || (capacity > 0 && (!out_kp || !out_desc))) { h->err = "bad argument"; return CCM_E_BADARG; }
-    if (rows == 0 || cols == 0) { for (int f = 0; f < n; f++) out_n[f] = 0; return CCM_OK; }
-    if (rows < 0 || cols < 0 || step < (size_t)cols) { h->err = "bad image geometry"; return CCM_E_BADARG; }
+    if (!imgs || !out_n || !ticket || n < 1 || capacity < 0 || (capacity > 0 && (!out_kp || !out_desc))) { h->err = "bad argument"; return CCM_E_BADARG; }
+    if (rows < 0 || cols < 0 || (rows > 0 && cols > 0 && step < (size_t)cols)) { h->err = "bad image geometry"; return CCM_E_BADARG; }
     if (n > h->cfg.max_batch) { h->err = "batch larger than max_batch"; return CCM_E_CAPACITY; }
-    const double t_call = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    int tk = -1, in_flight = 0;
+    for (int i = 0; i < CCM_MAX_TICKETS; i++) { if (h->tk[i].active) in_flight++; else if (tk < 0) tk = i; }
+    if (tk < 0) { h->err = "two batches are already in flight: wait for one first"; return CCM_E_CAPACITY; }
+    ccm_orb::Ticket& K = h->tk[tk];
+    {
+        cudaEvent_t keep[1 + 3 * CCM_MAX_CHUNKS];
+        std::memcpy(keep, K.tev, sizeof(keep));
+        K = ccm_orb::Ticket();
+        std::memcpy(K.tev, keep, sizeof(keep));
+    }
+    K.n = n; K.out_kp = out_kp; K.out_desc = out_desc; K.out_n = out_n; K.capacity = capacity; K.t_call = now_ms();
+    if (rows == 0 || cols == 0) { K.active = true; K.empty = true; *ticket = tk; return CCM_OK; }          // ORBextractor.cpp:1219-1220
+    for (int f = 0; f < n; f++)
+        if (!imgs[f]) { h->err = "null image in batch"; return CCM_E_BADARG; }
     CK(cudaSetDevice(h->cfg.device));
+    if ((rows != h->rows || cols != h->cols) && in_flight) { h->err = "image shape changed while a batch is in flight"; return CCM_E_BADARG; }
     int rc = configure_shape(h, rows, cols);
     if (rc != CCM_OK) return rc;
+    // frame slots: a synchronous caller (nothing in flight) always starts at slot 0, which the debug taps rely on
+    if (!in_flight) { h->next_slot = 0; h->next_lane = 0; }
+    int s0 = h->next_slot;
+    if (s0 + n > h->cfg.max_batch) s0 = 0;
+    for (int i = 0; i < CCM_MAX_TICKETS; i++)
+        if (h->tk[i].active && !h->tk[i].empty && s0 < h->tk[i].slot0 + h->tk[i].n && h->tk[i].slot0 < s0 + n) {
+            h->err = "frames in flight exceed max_batch: create the handle with max_batch >= the two batches together";
+            return CCM_E_CAPACITY;
+        }
+    K.slot0 = s0;
+    h->next_slot = s0 + n;
     // Level 0 lives in the handle's own level-0 buffer. When the caller's rows are 4-byte multiples that fit the
     // buffer's row budget the device pitch equals the host step and a frame is ONE contiguous copy; otherwise a
-    // pitched 2-D copy. The call is cut into up to CCM_MAX_CHUNKS sub-batches: copy-in (s_in), kernels (stream) and
-    // copy-out (s_out) of different sub-batches overlap, and the host-side scatter into the caller's arrays runs
-    // while later sub-batches are still on the device.
+    // pitched 2-D copy. The call is cut into up to CCM_MAX_CHUNKS sub-batches: copy-in (s_in), kernels (lanes) and
+    // copy-out (s_out) of different sub-batches overlap.
     uint8_t* l0 = (uint8_t*)h->allocs[0];
     const size_t budget = (size_t)align_up(cols, 32);
     const bool flat = (step % 4 == 0) && step <= budget;
@@ -485,6 +535,7 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     for (int f = 1; packed && f < n; f++) packed = imgs[f] == imgs[f - 1] + frame_bytes;
     const size_t pitch = flat ? step : budget, stride = packed ? frame_bytes : budget * rows;
     if (!flat && h->stage_bytes < frame_bytes * h->cfg.max_batch) {
+        if (in_flight) { h->err = "staging buffer must grow while a batch is in flight"; return CCM_E_BADARG; }
         CK(cudaStreamSynchronize(h->s_in));
         if (h->d_stage) cudaFree(h->d_stage);
         h->d_stage = nullptr; h->stage_bytes = 0;
@@ -492,9 +543,10 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
         h->stage_bytes = frame_bytes * h->cfg.max_batch;
     }
     const int cap = h->max_kps;
-    // sub-batch plan: first[c] .. first[c+1]
-    int first[CCM_MAX_CHUNKS + 1];
-    int n_chunks = n <= 8 ? 1 : std::min(CCM_MAX_CHUNKS, std::min(4, n / 4));
+    // sub-batch plan: first[c] .. first[c+1]. With another batch already on the device the copy-in of this one is hidden
+    // behind that batch's kernels, so fewer, larger sub-batches (better kernel efficiency) are the better cut.
+    int* first = K.first;
+    int n_chunks = n <= 8 ? 1 : std::min(CCM_MAX_CHUNKS, std::min(in_flight ? 2 : 4, n / 4));
     if (const char* e = std::getenv("CCM_ORB_CHUNKS")) n_chunks = std::max(1, std::min(std::min(CCM_MAX_CHUNKS, n), std::atoi(e)));   // tuning knob
     {
         const int per = (n + n_chunks - 1) / n_chunks;
@@ -514,78 +566,102 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
         if (at < n) first[++c] = n;
         n_chunks = c;
     }
-    for (int f = 0; f < n; f++)
-        if (!imgs[f]) { h->err = "null image in batch"; return CCM_E_BADARG; }
+    K.n_chunks = n_chunks;
+    // results go straight into the caller's arrays when those are pinned and laid out like the arena's ([n][max_kps]);
+    // otherwise through the handle's pinned staging and a host-side scatter in wait
+    K.direct = capacity == cap && is_pinned(out_kp) && is_pinned(out_desc);
     static const bool trace = std::getenv("CCM_ORB_TRACE") != nullptr;
-    static cudaEvent_t tev[1 + 3 * CCM_MAX_CHUNKS] = {};
+    K.trace = trace;
     if (trace) {
-        if (!tev[0]) for (auto& e : tev) cudaEventCreate(&e);
-        CK(cudaEventRecord(tev[0], h->s_in));
+        for (auto& e : K.tev) if (!e) CK(cudaEventCreate(&e));
+        CK(cudaEventRecord(K.tev[0], h->s_in));
     }
     for (int c = 0; c < n_chunks; c++) {
-        const int f0 = first[c], m = first[c + 1] - f0;
-        if (packed) CK(cudaMemcpyAsync(l0 + f0 * stride, imgs[f0], frame_bytes * (size_t)(m - 1) + step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
+        const int f0 = first[c], m = first[c + 1] - f0, g0 = s0 + f0;        // g0: first arena slot of this sub-batch
+        if (packed) CK(cudaMemcpyAsync(l0 + g0 * stride, imgs[f0], frame_bytes * (size_t)(m - 1) + step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
         for (int f = f0; f < f0 + m && !packed; f++) {
-            if (flat) CK(cudaMemcpyAsync(l0 + f * stride, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
+            if (flat) CK(cudaMemcpyAsync(l0 + (s0 + f) * stride, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
             else {
                 // rows that are not 4-byte multiples: one contiguous host->device copy into a staging area, then a
                 // device-side pitched copy (a pitched host->device copy runs at a fraction of the link rate)
-                uint8_t* st = h->d_stage + (size_t)f * frame_bytes;
+                uint8_t* st = h->d_stage + (size_t)(s0 + f) * frame_bytes;
                 CK(cudaMemcpyAsync(st, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
-                CK(cudaMemcpy2DAsync(l0 + f * stride, pitch, st, step, cols, rows, cudaMemcpyDeviceToDevice, h->s_in));
+                CK(cudaMemcpy2DAsync(l0 + (s0 + f) * stride, pitch, st, step, cols, rows, cudaMemcpyDeviceToDevice, h->s_in));
             }
         }
-        CK(cudaEventRecord(h->ev_in[c], h->s_in));
-        if (trace) CK(cudaEventRecord(tev[1 + 3 * c], h->s_in));
-        const int ln = n_chunks > 1 ? (c & 1) : 0;
-        CK(cudaStreamWaitEvent(h->lane[ln].s, h->ev_in[c], 0));
-        rc = run_pipeline(h, m, l0, pitch, stride, h->d_kp + (size_t)f0 * cap, h->d_desc + (size_t)f0 * cap * 32, h->d_n + f0, cap, f0, n_chunks == 1, ln);
+        cudaEvent_t ev_in = h->ev_in[tk][c], ev_done = h->ev_done[tk][c], ev_out = h->ev_out[tk][c];
+        CK(cudaEventRecord(ev_in, h->s_in));
+        if (trace) CK(cudaEventRecord(K.tev[1 + 3 * c], h->s_in));
+        const int ln = h->next_lane;
+        h->next_lane ^= 1;
+        CK(cudaStreamWaitEvent(h->lane[ln].s, ev_in, 0));
+        rc = run_pipeline(h, m, l0, pitch, stride, h->d_kp + (size_t)g0 * cap, h->d_desc + (size_t)g0 * cap * 32, h->d_n + g0, cap, g0,
+                          n_chunks == 1 && !in_flight, ln);
         if (rc != CCM_OK) return rc;
-        CK(cudaEventRecord(h->ev_done[c], h->lane[ln].s));
-        if (trace) CK(cudaEventRecord(tev[2 + 3 * c], h->lane[ln].s));
-        CK(cudaStreamWaitEvent(h->s_out, h->ev_done[c], 0));
-        CK(cudaMemcpyAsync(h->h_n + f0, h->d_n + f0, sizeof(int) * m, cudaMemcpyDeviceToHost, h->s_out));
-        CK(cudaMemcpyAsync(h->h_kp + (size_t)f0 * cap, h->d_kp + (size_t)f0 * cap, sizeof(ccm_keypoint) * (size_t)cap * m, cudaMemcpyDeviceToHost, h->s_out));
-        CK(cudaMemcpyAsync(h->h_desc + (size_t)f0 * cap * 32, h->d_desc + (size_t)f0 * cap * 32, (size_t)32 * cap * m, cudaMemcpyDeviceToHost, h->s_out));
-        CK(cudaEventRecord(h->ev_out[c], h->s_out));
-        if (trace) CK(cudaEventRecord(tev[3 + 3 * c], h->s_out));
+        CK(cudaEventRecord(ev_done, h->lane[ln].s));
+        if (trace) CK(cudaEventRecord(K.tev[2 + 3 * c], h->lane[ln].s));
+        CK(cudaStreamWaitEvent(h->s_out, ev_done, 0));
+        CK(cudaMemcpyAsync(h->h_n + g0, h->d_n + g0, sizeof(int) * m, cudaMemcpyDeviceToHost, h->s_out));
+        ccm_keypoint* dst_kp = K.direct ? out_kp + (size_t)f0 * cap : h->h_kp + (size_t)g0 * cap;
+        uint8_t* dst_desc = K.direct ? out_desc + (size_t)f0 * cap * 32 : h->h_desc + (size_t)g0 * cap * 32;
+        CK(cudaMemcpyAsync(dst_kp, h->d_kp + (size_t)g0 * cap, sizeof(ccm_keypoint) * (size_t)cap * m, cudaMemcpyDeviceToHost, h->s_out));
+        CK(cudaMemcpyAsync(dst_desc, h->d_desc + (size_t)g0 * cap * 32, (size_t)32 * cap * m, cudaMemcpyDeviceToHost, h->s_out));
+        CK(cudaEventRecord(ev_out, h->s_out));
+        if (trace) CK(cudaEventRecord(K.tev[3 + 3 * c], h->s_out));
     }
-    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    const double t_enq = trace ? now() : 0.0;
-    double t_wait = 0, t_copy = 0;
-    for (int c = 0; c < n_chunks; c++) {
-        const int f0 = first[c], m = first[c + 1] - f0;
-        const double ta = trace ? now() : 0.0;
-        CK(cudaEventSynchronize(h->ev_out[c]));
-        const double tb = trace ? now() : 0.0;
-        t_wait += tb - ta;
+    K.t_enq = now_ms();
+    K.active = true;
+    *ticket = tk;
+    return CCM_OK;
+}
+
+int ccm_orb_extract_batch_wait(ccm_orb* h, int ticket) {
+    if (!h) return CCM_E_BADARG;
+    if (ticket < 0 || ticket >= CCM_MAX_TICKETS || !h->tk[ticket].active) { h->err = "no such batch in flight"; return CCM_E_BADARG; }
+    ccm_orb::Ticket& K = h->tk[ticket];
+    if (K.empty) { for (int f = 0; f < K.n; f++) K.out_n[f] = 0; K.active = false; return CCM_OK; }
+    CK(cudaSetDevice(h->cfg.device));
+    const int cap = h->max_kps;
+    const double t0 = K.trace ? now_ms() : 0.0;
+    double t_wait = 0;
+    for (int c = 0; c < K.n_chunks; c++) {
+        const int f0 = K.first[c], m = K.first[c + 1] - f0;
+        const double ta = K.trace ? now_ms() : 0.0;
+        cudaError_t e = cudaEventSynchronize(h->ev_out[ticket][c]);
+        if (e != cudaSuccess) { K.active = false; h->err = std::string("cudaEventSynchronize: ") + cudaGetErrorString(e); return CCM_E_CUDA; }
+        if (K.trace) t_wait += now_ms() - ta;
         for (int f = f0; f < f0 + m; f++) {
-            const int cnt = h->h_n[f];
-            out_n[f] = cnt;
-            const int k = std::min(std::min(cnt, capacity), cap);
-            if (k > 0) {
-                std::memcpy(out_kp + (size_t)f * capacity, h->h_kp + (size_t)f * cap, sizeof(ccm_keypoint) * k);
-                std::memcpy(out_desc + (size_t)f * capacity * 32, h->h_desc + (size_t)f * cap * 32, (size_t)32 * k);
+            const int g = K.slot0 + f, cnt = h->h_n[g];
+            K.out_n[f] = cnt;
+            const int k = std::min(std::min(cnt, K.capacity), cap);
+            if (k > 0 && !K.direct) {
+                std::memcpy(K.out_kp + (size_t)f * K.capacity, h->h_kp + (size_t)g * cap, sizeof(ccm_keypoint) * k);
+                std::memcpy(K.out_desc + (size_t)f * K.capacity * 32, h->h_desc + (size_t)g * cap * 32, (size_t)32 * k);
             }
         }
     }
-    // the next call's copy-in must not overtake this call's kernels (they read the level-0 buffer)
-    CK(cudaStreamSynchronize(h->stream));
-    CK(cudaStreamSynchronize(h->lane[1].s));
-    if (trace) {
-        const double t_end = now();
-        fprintf(stderr, "[ccm_orb trace] enqueue %.3f ms, wait %.3f ms, scatter %.3f ms, total %.3f ms | device (ms after first copy starts):", t_enq - t_call, t_wait,
-                t_end - t_enq - t_wait, t_end - t_call);
-        for (int c = 0; c < n_chunks; c++) {
+    K.active = false;
+    if (K.trace) {
+        const double t_end = now_ms();
+        fprintf(stderr, "[ccm_orb trace] ticket %d slots %d..%d%s: enqueue %.3f ms, submit->wait %.3f ms, wait %.3f ms, scatter %.3f ms | device (ms after first copy starts):",
+                ticket, K.slot0, K.slot0 + K.n, K.direct ? " direct" : "", K.t_enq - K.t_call, t0 - K.t_enq, t_wait, t_end - t0 - t_wait);
+        for (int c = 0; c < K.n_chunks; c++) {
             float a = 0, b = 0, d = 0;
-            cudaEventElapsedTime(&a, tev[0], tev[1 + 3 * c]); cudaEventElapsedTime(&b, tev[0], tev[2 + 3 * c]);
-            cudaEventElapsedTime(&d, tev[0], tev[3 + 3 * c]);
+            cudaEventElapsedTime(&a, K.tev[0], K.tev[1 + 3 * c]); cudaEventElapsedTime(&b, K.tev[0], K.tev[2 + 3 * c]);
+            cudaEventElapsedTime(&d, K.tev[0], K.tev[3 + 3 * c]);
             fprintf(stderr, " [in %.3f done %.3f out %.3f]", a, b, d);
         }
         fprintf(stderr, "\n");
     }
-    (void)t_copy;
     return CCM_OK;
+}
+
+int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int rows, int cols, size_t step,
+                          ccm_keypoint* out_kp, uint8_t* out_desc, int capacity, int* out_n) {
+    int ticket = -1;
+    const int rc = ccm_orb_extract_batch_submit(h, imgs, n, rows, cols, step, out_kp, out_desc, capacity, out_n, &ticket);
+    if (rc != CCM_OK) return rc;
+    return ccm_orb_extract_batch_wait(h, ticket);
 }
 
 int ccm_orb_extract(ccm_orb* h, const uint8_t* img, int rows, int cols, size_t step, ccm_keypoint* out_kp, uint8_t* out_desc,

@@ -120,6 +120,17 @@ class ORBextractor:
         self._check(self._lib.ccm_orb_extract_batch(self._h, img_ptrs, n, rows, cols, step, out_kp_ptr, out_desc_ptr,
                                                     capacity, out_n))
 
+    def extract_batch_submit(self, img_ptrs, n, rows, cols, step, out_kp_ptr, out_desc_ptr, capacity, out_n):
+        """ccm_orb_extract_batch_submit: enqueue one batch and return its ticket; the buffers stay owned by the caller
+        until extract_batch_wait(ticket) returns. Two batches may be in flight (their frames together <= max_batch)."""
+        t = ctypes.c_int(-1)
+        self._check(self._lib.ccm_orb_extract_batch_submit(self._h, img_ptrs, n, rows, cols, step, out_kp_ptr, out_desc_ptr,
+                                                           capacity, out_n, ctypes.byref(t)))
+        return t.value
+
+    def extract_batch_wait(self, ticket):
+        self._check(self._lib.ccm_orb_extract_batch_wait(self._h, int(ticket)))
+
     def set_stage_timing(self, on):
         self._check(self._lib.ccm_orb_set_stage_timing(self._h, 1 if on else 0))
 

@@ -212,3 +212,66 @@ def test_dropin_cpp_class_matches_reference_class(cuda_lib):
     kd, dd = drop(np.ascontiguousarray(roi))
     kr, dr = ref(np.ascontiguousarray(roi))
     assert len(kd) == len(kr) and np.array_equal(kd["x"], kr["x"]) and np.array_equal(kd["angle"], kr["angle"])
+
+
+def test_async_submit_wait_pipeline(cuda_lib):
+    """ccm_orb_extract_batch_submit / _wait: two batches in flight on alternating frame slots of the arena, results equal to
+    the synchronous call for every batch of a stream (pinned outputs in the arena layout take the direct copy-out path,
+    pageable ones of another capacity the staged one), slot overflow and a third ticket are refused."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200._lib import CCM_E_CAPACITY, CcmError
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    w, h, B, NB = 640, 400, 6, 5
+    frames = make_stream(4321, B * NB, w, h).reshape(NB, B, h, w)
+    ex = make(cuda_lib, 600, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=2 * B + 1)
+    cap = ex.max_keypoints()
+    want = [ex.extract_batch(list(frames[b])) for b in range(NB)]
+    for pinned, capacity in ((True, cap), (False, cap - 5), (True, 100)):
+        pin = torch.from_numpy(frames.copy()).pin_memory() if pinned else torch.from_numpy(frames.copy())
+        base = pin.numpy()
+        mk = (lambda *s, dt: torch.zeros(s, dtype=dt).pin_memory()) if pinned else (lambda *s, dt: torch.zeros(s, dtype=dt))
+        out_kp = [mk(B, capacity, 6, dt=torch.float32) for _ in range(2)]
+        out_desc = [mk(B, capacity, 32, dt=torch.uint8) for _ in range(2)]
+        out_n = [(ctypes.c_int * B)() for _ in range(2)]
+        ptrs = [(ctypes.c_void_p * B)(*[base[b, f].ctypes.data for f in range(B)]) for b in range(NB)]
+
+        def check(b):
+            s = b & 1
+            kp = out_kp[s].numpy().view(KP_DTYPE).reshape(B, capacity)
+            for f in range(B):
+                n = out_n[s][f]
+                assert n == len(want[b][0][f])
+                k = min(n, capacity)
+                assert np.array_equal(kp[f, :k], want[b][0][f][:k]) and np.array_equal(out_desc[s].numpy()[f, :k], want[b][1][f][:k])
+
+        tickets = {}
+        for b in range(NB):
+            s = b & 1
+            tickets[b] = ex.extract_batch_submit(ptrs[b], B, h, w, w, out_kp[s].data_ptr(), out_desc[s].data_ptr(), capacity, out_n[s])
+            if b >= 1:
+                ex.extract_batch_wait(tickets[b - 1])
+                check(b - 1)
+        # both slots busy? no: one ticket open. A second fits, a third does not; nor does a batch larger than the free slots.
+        t2 = ex.extract_batch_submit(ptrs[0], B, h, w, w, out_kp[NB & 1].data_ptr(), out_desc[NB & 1].data_ptr(), capacity, out_n[NB & 1])
+        with pytest.raises(CcmError) as e:
+            ex.extract_batch_submit(ptrs[1], 1, h, w, w, out_kp[0].data_ptr(), out_desc[0].data_ptr(), capacity, out_n[0])
+        assert e.value.code == CCM_E_CAPACITY
+        ex.extract_batch_wait(tickets[NB - 1])
+        check(NB - 1)
+        ex.extract_batch_wait(t2)
+        with pytest.raises(CcmError):
+            ex.extract_batch_wait(t2)                                       # already collected
+    # frames in flight must fit max_batch
+    small = make(cuda_lib, 600, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B + 2)
+    o_kp, o_d, o_n = np.zeros((2, B, cap), KP_DTYPE), np.zeros((2, B, cap, 32), np.uint8), [(ctypes.c_int * B)() for _ in range(2)]
+    fr = np.ascontiguousarray(frames[0])
+    p0 = (ctypes.c_void_p * B)(*[fr[f].ctypes.data for f in range(B)])
+    t = small.extract_batch_submit(p0, B, h, w, w, o_kp[0].ctypes.data, o_d[0].ctypes.data, cap, o_n[0])
+    with pytest.raises(CcmError) as e:
+        small.extract_batch_submit(p0, B, h, w, w, o_kp[1].ctypes.data, o_d[1].ctypes.data, cap, o_n[1])
+    assert e.value.code == CCM_E_CAPACITY
+    small.extract_batch_wait(t)
+    assert [o_n[0][f] for f in range(B)] == [len(k) for k in want[0][0]]
+    # a synchronous call afterwards still works and the stage taps still see frame 0 in slot 0
+    k, d = small.extract_batch(list(frames[1]))
+    assert all(np.array_equal(k[f], want[1][0][f]) for f in range(B))
