@@ -36,6 +36,12 @@ struct ccm_orb {
     std::vector<void*> allocs;
     uint4* d_cell_info = nullptr;
     FastSmem fast_smem = {};
+    // TMA variant of the FAST tile load: its own cell table (tile column 0 = pixel x0-3) and one tensor map per level
+    uint4* d_cell_info_tma = nullptr;
+    FastSmem fast_smem_tma = {};
+    int fast_ts = 0;                                   // tile row stride of the TMA variant (48 / 64 / 80), 0 = TMA unavailable
+    FastTma tmaps = {};
+    void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
     ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
@@ -137,6 +143,28 @@ static bool resize_group_table(int ssize, int dsize, const std::vector<int>& ofs
     return true;
 }
 
+// ---- TMA descriptors for k_fast_cells<TS, true> ----
+typedef CUresult (*ccm_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                        const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+// u8 tensor [frames][rows][pitch] at base, box [1][box_rows][ts]; out-of-range parts of a box are zero-filled (never read)
+static bool encode_level_map(ccm_orb* h, CUtensorMap* out, const void* base, size_t pitch, int rows, size_t frame_stride, int frames,
+                             int ts, int box_rows) {
+    if (!h->encode_tiled || ((uintptr_t)base & 15) || (pitch & 15) || (frame_stride & 15) || pitch == 0 || frames < 1) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)rows, (cuuint64_t)frames};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame_stride};
+    const cuuint32_t box[3] = {(cuuint32_t)ts, (cuuint32_t)box_rows, 1u}, estr[3] = {1u, 1u, 1u};
+    return ((ccm_encode_tiled_fn)h->encode_tiled)(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<void*>(base), dims, strides, box, estr,
+                                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int TS, bool TMA>
+static void launch_fast(cudaStream_t s, dim3 grid, const LevelTable& T, const uint4* cell_info, uint32_t* corners, int* corner_count,
+                        const FastSmem& M, int frame0, const FastTma& tm) {
+    k_fast_cells<TS, TMA><<<grid, FAST_THREADS, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
+}
+
 // Level geometry for one image shape, following ComputePyramid (:1284-1286), ComputeKeyPointsOctTree (:941-955)
 // and DistributeOctTree (:711-713). Allocates the arena for cfg.max_batch frames of this shape.
 static int configure_shape(ccm_orb* h, int rows, int cols) {
@@ -150,7 +178,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     const int L = h->cfg.nlevels, B = h->cfg.max_batch;
     T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
     int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0;
-    std::vector<uint4> cell_info;
+    std::vector<uint4> cell_info, cell_info_tma;
     int max_cw = 1, max_ch = 1;
     for (int l = 0; l < L; l++) {
         LevelDesc& D = T.l[l];
@@ -184,6 +212,11 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
                 cell_info.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l,
                                                (uint32_t)shift | ((uint32_t)wpr << 8) | ((uint32_t)g0 << 16) | ((uint32_t)ngx << 24)));
                 cell_info.push_back(make_uint4(magic(wpr), magic(cwp), magic(ngx), 0u));
+                // TMA variant: the box starts at the 16-byte aligned column below x0-3 (tools/tma_probe.cu), shift = 0..15
+                const int shift_t = (x0 - 3) & 15, g0_t = (3 + shift_t) >> 2, ngx_t = ((cwp + 2 + shift_t) >> 2) - g0_t + 1;
+                cell_info_tma.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l,
+                                                   (uint32_t)shift_t | (1u << 8) | ((uint32_t)g0_t << 16) | ((uint32_t)ngx_t << 24)));
+                cell_info_tma.push_back(make_uint4(magic(1), magic(cwp), magic(ngx_t), 0u));
                 max_cw = std::max(max_cw, cw); max_ch = std::max(max_ch, ch);
             }
         D.corner_cap = std::max(cc, 1); D.corner_off = corners; corners += align_up(D.corner_cap, 4);
@@ -234,9 +267,31 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     }
     int rc;
     h->fast_smem = fast_smem_layout(max_cw, max_ch);
-    CK(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_fast_cells<FAST_TS, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_fast_cells<96, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_fast_cells<64, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(cudaFuncSetAttribute(k_fast_cells<80, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if ((rc = dev_alloc(h, &h->d_cell_info, cell_info.size()))) return rc;
     CK(cudaMemcpy(h->d_cell_info, cell_info.data(), cell_info.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+    if ((rc = dev_alloc(h, &h->d_cell_info_tma, cell_info_tma.size()))) return rc;
+    CK(cudaMemcpy(h->d_cell_info_tma, cell_info_tma.data(), cell_info_tma.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+    // TMA tile load: row stride = box width = a multiple of 16 bytes that holds the widest cell + ring; descriptors of the
+    // arena levels are encoded once per shape, level 0 (the caller's buffer) per call (run_pipeline)
+    h->fast_ts = 0;
+    if (!std::getenv("CCM_ORB_NO_TMA")) {
+        if (!h->encode_tiled) {
+            cudaDriverEntryPointQueryResult q;
+            void* fn = nullptr;
+            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) h->encode_tiled = fn;
+            else cudaGetLastError();
+        }
+        const int need = 15 + max_cw + 6, ts = need <= 64 ? 64 : need <= 80 ? 80 : 96;
+        h->fast_smem_tma = fast_smem_layout(max_cw, max_ch, ts);
+        bool ok = h->encode_tiled != nullptr;
+        for (int l = 1; l < L && ok; l++)
+            ok = encode_level_map(h, &h->tmaps.m[l], T.l[l].img, (size_t)T.l[l].img_pitch, T.l[l].h, T.l[l].img_stride, B, ts, h->fast_smem_tma.tile_rows);
+        if (ok) h->fast_ts = ts;
+    }
     if ((rc = dev_alloc(h, &h->d_corners, (size_t)corners * B))) return rc;
     if ((rc = dev_alloc(h, &h->d_node_of, (size_t)corners * B))) return rc;
     if ((rc = dev_alloc(h, &h->d_corner_count, (size_t)CCM_MAX_LEVELS * B))) return rc;
@@ -303,8 +358,18 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[1], s));
-        k_fast_cells<<<dim3(T.total_cells, n), FAST_THREADS, h->fast_smem.total, s>>>(T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem);
-        h->launches++;
+        {
+            // level 0 is the caller's buffer: its descriptor is encoded per call; a base / pitch / stride that TMA cannot address
+            // (not 16-byte multiples) takes the word-load variant of the kernel for this call
+            const dim3 grid(T.total_cells, n);
+            FastTma tm = h->tmaps;
+            const bool tma = h->fast_ts && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, h->fast_ts, h->fast_smem_tma.tile_rows);
+            if (tma && h->fast_ts == 64) launch_fast<64, true>(s, grid, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
+            else if (tma && h->fast_ts == 80) launch_fast<80, true>(s, grid, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
+            else if (tma) launch_fast<96, true>(s, grid, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
+            else launch_fast<FAST_TS, false>(s, grid, T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem, f0, tm);
+            h->launches++;
+        }
         if (st) CK(cudaEventRecord(h->ev[2], s));
         if (fork) CK(cudaEventRecord(LN.fork, s));
         if (!fork) {

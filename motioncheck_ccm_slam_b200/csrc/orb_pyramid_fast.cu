@@ -1,5 +1,6 @@
 // K1 (pyramid level) and K2+K3 (per-cell FAST-9/16 + NMS + threshold fallback + compaction), sm_100a.
 // Integer/byte work bounded by HBM/L2 bandwidth and the ALU pipe; no tensor cores by design.
+#include <cuda.h>   // CUtensorMap (types only; the encoder is fetched with cudaGetDriverEntryPoint, libcuda is not linked)
 #include "ccm_common.cuh"
 
 // ---------------------------------------------------------------------------------------------
@@ -155,29 +156,53 @@ __device__ __forceinline__ void list_append(bool pred, uint32_t val, uint32_t li
 
 #define FAST_THREADS 128
 // Dynamic shared memory, sized by the host for the largest cell of the configured shape (fast_smem_layout):
-// tile [max_ch + 6][FAST_TS] | score [max_ch + 2][FAST_SS] | cand [max_px] u16 | corn [max_px] u16
-struct FastSmem { int score_off, cand_off, corn_off, total; };
-static inline FastSmem fast_smem_layout(int max_cw, int max_ch) {
+// tile [max_ch + 6][ts] | score [max_ch + 2][FAST_SS] | cand [max_px] u16 | corn [max_px] u16
+struct FastSmem { int score_off, cand_off, corn_off, total, ts, tile_rows; };
+static inline FastSmem fast_smem_layout(int max_cw, int max_ch, int ts = FAST_TS) {
     FastSmem m;
-    const int tile_bytes = ((max_ch + 6) * FAST_TS + 15) / 16 * 16;
+    const int tile_bytes = ((max_ch + 6) * ts + 127) / 128 * 128;
     const int score_bytes = ((max_ch + 2) * FAST_SS + 15) / 16 * 16;
     const int list_bytes = (max_cw * max_ch * 2 + 15) / 16 * 16;
     m.score_off = tile_bytes; m.cand_off = m.score_off + score_bytes; m.corn_off = m.cand_off + list_bytes;
     m.total = m.corn_off + list_bytes;
+    m.ts = ts; m.tile_rows = max_ch + 6;
     return m;
 }
 
+// TMA tile load (cp.async.bulk.tensor, sm_90+): one elected thread asks the copy engine for the (cell + 3-px ring) box of
+// its level image; the bytes land in shared memory and complete an mbarrier transaction count. One descriptor per level
+// (u8 tensor [frames][h][pitch], box = [1][tile_rows][TS]), passed by value as a __grid_constant__ parameter.
+struct alignas(64) FastTma { CUtensorMap m[CCM_MAX_LEVELS]; };
+__device__ __forceinline__ void mbar_init(uint32_t bar_s, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar_s), "r"(count) : "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");            // the init must be visible to the async (TMA) proxy
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar_s, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_s, const CUtensorMap* map, int x, int y, int z, uint32_t bar_s) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                 ::"r"(dst_s), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar_s) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar_s, uint32_t parity) {
+    asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}"
+                 ::"r"(bar_s), "r"(parity) : "memory");
+}
+
+template <int TS, bool TMA>
 __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_constant__ LevelTable T,
                                                     const uint4* __restrict__ cell_info,  // per cell 2 x uint4, see configure_shape
                                                     uint32_t* __restrict__ corners,      // [frames][corners_per_frame]
                                                     int* __restrict__ corner_count,      // [frames][CCM_MAX_LEVELS]
-                                                    const FastSmem M) {
-    extern __shared__ __align__(16) uint8_t fast_smem[];
-    uint8_t* const tile = fast_smem;                                   // [ch + 6][FAST_TS]
+                                                    const FastSmem M, int frame0,        // arena slot of frame 0 (TMA z coordinate)
+                                                    const __grid_constant__ FastTma tm) {
+    extern __shared__ __align__(128) uint8_t fast_smem[];
+    uint8_t* const tile = fast_smem;                                   // [ch + 6][TS]
     uint8_t* const score = fast_smem + M.score_off;                    // [cell + 1-px zero ring][FAST_SS]
     uint16_t* const cand = reinterpret_cast<uint16_t*>(fast_smem + M.cand_off);
     uint16_t* const corn = reinterpret_cast<uint16_t*>(fast_smem + M.corn_off);
     __shared__ int n_cand, n_corn;
+    __shared__ __align__(8) unsigned long long tile_bar;
 
     const int f = blockIdx.y;
     // detection block of this cell in level coordinates and the index-arithmetic constants of its tile
@@ -189,20 +214,30 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
 
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int tid = threadIdx.x;
-    // (A) tile = cell + 3-px ring, loaded as aligned 32-bit words (rows are 32-B aligned, pitch a multiple of 32)
-    const int shift = (int)(ci.w & 3), wpr = (int)(ci.w >> 8) & 0xff;       // x0-3 = word-aligned gxa + shift; words per tile row
+    // (A) tile = cell + 3-px ring. TMA: one thread asks for the box whose corner is (gxa, y0-3) of frame f — the innermost start
+    //     coordinate of a tiled TMA load must be a multiple of 16 bytes (measured: tools/tma_probe.cu; x = 13 raises an illegal
+    //     instruction), so gxa = (x0-3) & ~15 and pixel x0-3 is tile column `shift`; otherwise aligned 32-bit words (rows are
+    //     32-B aligned, pitch a multiple of 32).
+    const int shift = (int)(ci.w & 0xff), wpr = (int)(ci.w >> 8) & 0xff;    // x0-3 = aligned gxa + shift (word-aligned: 0..3, TMA: 16-byte aligned, 0..15); words per tile row
     const int g0 = (int)(ci.w >> 16) & 0xff, ngx = (int)(ci.w >> 24);       // aligned 4-px words covering the cell: [g0, g0 + ngx)
     const uint32_t wmagic = cj.x, cmagic = cj.y, gmagic = cj.z;             // i / wpr, i / cw, i / ngx for i < 4096
     const int gxa = x0 - 3 - shift, th = ch + 6;
-    {
+    if (TMA) {
+        if (tid == 0) {
+            const uint32_t bar_s = smem_addr(&tile_bar);
+            mbar_init(bar_s, 1);
+            mbar_expect_tx(bar_s, (uint32_t)(M.tile_rows * TS));
+            tma_load_3d(smem_addr(tile), &tm.m[lvl], gxa, y0 - 3, frame0 + f, bar_s);
+        }
+    } else {
         // FAST_THREADS / wpr tile rows per sweep, one word per thread, pointers stepped by whole sweeps
         const int rps = (int)((FAST_THREADS * wmagic) >> 20);
         const int ty0 = (int)(((uint32_t)tid * wmagic) >> 20), tx = tid - ty0 * wpr;
         if (ty0 < rps) {
             const uint8_t* src = img + (size_t)(y0 - 3 + ty0) * L.img_pitch + gxa + 4 * tx;
-            uint8_t* dst = tile + ty0 * FAST_TS + 4 * tx;
+            uint8_t* dst = tile + ty0 * TS + 4 * tx;
             const size_t sstep = (size_t)rps * L.img_pitch;
-            const int dstep = rps * FAST_TS;
+            const int dstep = rps * TS;
             for (int ty = ty0; ty < th; ty += rps, src += sstep, dst += dstep)
                 *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(src);
         }
@@ -210,9 +245,10 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
     for (int i = tid; i < ((ch + 2) * FAST_SS + 15) / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) { n_cand = 0; n_corn = 0; }
     __syncthreads();
+    if (TMA) mbar_wait(smem_addr(&tile_bar), 0);     // every thread observes the completed transaction: the tile is visible
     const uint32_t cand_s = smem_addr(cand), corn_s = smem_addr(corn), ncand_s = smem_addr(&n_cand), ncorn_s = smem_addr(&n_corn);
 
-    const int S = FAST_TS;
+    const int S = TS;
     const int ngrp = ngx * ch;
     int threshold = T.ini_th;
 #pragma unroll 1
@@ -228,9 +264,9 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
                 py = (int)(((uint32_t)gi * gmagic) >> 20);
                 const int g = g0 + gi - py * ngx;
                 pxb = 4 * g - 3 - shift;                                      // pixel of byte 0 of this word
-                const uint32_t* rowc = reinterpret_cast<const uint32_t*>(tile + (py + 3) * FAST_TS) + g;
+                const uint32_t* rowc = reinterpret_cast<const uint32_t*>(tile + (py + 3) * TS) + g;
                 const uint32_t cen = rowc[0], lft = rowc[-1], rgt = rowc[1];
-                const uint32_t up = rowc[-3 * (FAST_TS / 4)], dn = rowc[3 * (FAST_TS / 4)];
+                const uint32_t up = rowc[-3 * (TS / 4)], dn = rowc[3 * (TS / 4)];
                 const uint32_t p4 = __funnelshift_r(cen, rgt, 24), p12 = __funnelshift_r(lft, cen, 8);
                 const uint32_t m = (__vcmpgtu4(__vabsdiffu4(cen, dn), t4) | __vcmpgtu4(__vabsdiffu4(cen, up), t4)) &
                                    (__vcmpgtu4(__vabsdiffu4(cen, p4), t4) | __vcmpgtu4(__vabsdiffu4(cen, p12), t4));
@@ -266,7 +302,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
             if (j < nc) {
                 i = cand[j];
                 const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-                const uint8_t* c = tile + (py + 3) * FAST_TS + px + 3 + shift;
+                const uint8_t* c = tile + (py + 3) * TS + px + 3 + shift;
                 const int v = c[0], hi = v + threshold, lo = v - threshold;
                 int r[16];
                 r[0] = c[3 * S];       r[1] = c[3 * S + 1];   r[2] = c[2 * S + 2];   r[3] = c[S + 3];
@@ -286,7 +322,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
         for (int j = tid; j < nk; j += FAST_THREADS) {
             const int i = corn[j];
             const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-            const uint8_t* c = tile + (py + 3) * FAST_TS + px + 3 + shift;
+            const uint8_t* c = tile + (py + 3) * TS + px + 3 + shift;
             const int v = c[0];
             int d[16];
             d[0] = v - c[3 * S];       d[1] = v - c[3 * S + 1];   d[2] = v - c[2 * S + 2];   d[3] = v - c[S + 3];
