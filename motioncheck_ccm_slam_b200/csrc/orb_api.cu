@@ -39,6 +39,7 @@ struct ccm_orb {
     // TMA variant of the FAST tile load: its own cell table (tile column 0 = pixel x0-3) and one tensor map per level
     uint4* d_cell_info_tma = nullptr;
     FastSmem fast_smem_tma = {};
+    int fast_nt = 128, fast_nt_tma = 128;              // CTA sizes picked for the two cell tables
     int fast_ts = 0;                                   // tile row stride of the TMA variant (48 / 64 / 80), 0 = TMA unavailable
     FastTma tmaps = {};
     void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
@@ -160,9 +161,35 @@ static bool encode_level_map(ccm_orb* h, CUtensorMap* out, const void* base, siz
 }
 
 template <int TS, bool TMA>
-static void launch_fast(cudaStream_t s, dim3 grid, const LevelTable& T, const uint4* cell_info, uint32_t* corners, int* corner_count,
+static void launch_fast(cudaStream_t s, dim3 grid, int nt, const LevelTable& T, const uint4* cell_info, uint32_t* corners, int* corner_count,
                         const FastSmem& M, int frame0, const FastTma& tm) {
-    k_fast_cells<TS, TMA><<<grid, FAST_THREADS, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
+    if (nt == 96) k_fast_cells<TS, TMA, 96><<<grid, 96, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
+    else if (nt == 160) k_fast_cells<TS, TMA, 160><<<grid, 160, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
+    else k_fast_cells<TS, TMA, 128><<<grid, 128, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
+}
+template <int TS, bool TMA>
+static cudaError_t fast_set_carveout() {
+    cudaError_t e = cudaFuncSetAttribute(k_fast_cells<TS, TMA, 96>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fast_cells<TS, TMA, 128>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fast_cells<TS, TMA, 160>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    return e;
+}
+// CTA size of k_fast_cells for a cell table: warp-sweeps over the 4-pixel groups of every cell (the dominant loop) plus a
+// per-warp share for the stages whose cost does not depend on the cell size
+static int fast_pick_threads(const std::vector<uint4>& cell_info) {
+    int best = 128;
+    double best_cost = 1e300;
+    for (int nt : {96, 128, 160}) {
+        double cost = 0;
+        for (size_t c = 0; c + 1 < cell_info.size(); c += 2) {
+            const int ch = (int)(cell_info[c].y >> 16), ngx = (int)(cell_info[c].w >> 24), ngrp = ngx * ch;
+            if (ch <= 0) continue;
+            cost += (double)((ngrp + nt - 1) / nt) * (nt / 32) + 1.5 * (nt / 32);
+        }
+        if (cost < best_cost) { best_cost = cost; best = nt; }
+    }
+    if (const char* e = std::getenv("CCM_ORB_FAST_THREADS")) { const int v = std::atoi(e); if (v == 96 || v == 128 || v == 160) best = v; }   // tuning knob
+    return best;
 }
 
 // Level geometry for one image shape, following ComputePyramid (:1284-1286), ComputeKeyPointsOctTree (:941-955)
@@ -267,10 +294,12 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     }
     int rc;
     h->fast_smem = fast_smem_layout(max_cw, max_ch);
-    CK(cudaFuncSetAttribute(k_fast_cells<FAST_TS, false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(k_fast_cells<96, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(k_fast_cells<64, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CK(cudaFuncSetAttribute(k_fast_cells<80, true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK((fast_set_carveout<FAST_TS, false>()));
+    CK((fast_set_carveout<64, true>()));
+    CK((fast_set_carveout<80, true>()));
+    CK((fast_set_carveout<96, true>()));
+    h->fast_nt = fast_pick_threads(cell_info);
+    h->fast_nt_tma = fast_pick_threads(cell_info_tma);
     if ((rc = dev_alloc(h, &h->d_cell_info, cell_info.size()))) return rc;
     CK(cudaMemcpy(h->d_cell_info, cell_info.data(), cell_info.size() * sizeof(uint4), cudaMemcpyHostToDevice));
     if ((rc = dev_alloc(h, &h->d_cell_info_tma, cell_info_tma.size()))) return rc;
@@ -364,10 +393,10 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
             const dim3 grid(T.total_cells, n);
             FastTma tm = h->tmaps;
             const bool tma = h->fast_ts && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, h->fast_ts, h->fast_smem_tma.tile_rows);
-            if (tma && h->fast_ts == 64) launch_fast<64, true>(s, grid, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
-            else if (tma && h->fast_ts == 80) launch_fast<80, true>(s, grid, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
-            else if (tma) launch_fast<96, true>(s, grid, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
-            else launch_fast<FAST_TS, false>(s, grid, T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem, f0, tm);
+            if (tma && h->fast_ts == 64) launch_fast<64, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
+            else if (tma && h->fast_ts == 80) launch_fast<80, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
+            else if (tma) launch_fast<96, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
+            else launch_fast<FAST_TS, false>(s, grid, h->fast_nt, T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem, f0, tm);
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[2], s));
@@ -596,8 +625,9 @@ int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n, 
     const size_t frame_bytes = step * (size_t)rows;
     // frames that follow each other in host memory (a [n][rows][step] array) keep that layout on the device, so a whole
     // sub-batch is ONE copy instead of one per frame
-    bool packed = flat && n > 1;
-    for (int f = 1; packed && f < n; f++) packed = imgs[f] == imgs[f - 1] + frame_bytes;
+    bool contiguous = n > 1;
+    for (int f = 1; contiguous && f < n; f++) contiguous = imgs[f] == imgs[f - 1] + frame_bytes;
+    const bool packed = flat && contiguous;
     const size_t pitch = flat ? step : budget, stride = packed ? frame_bytes : budget * rows;
     if (!flat && h->stage_bytes < frame_bytes * h->cfg.max_batch) {
         if (in_flight) { h->err = "staging buffer must grow while a batch is in flight"; return CCM_E_BADARG; }
@@ -644,7 +674,14 @@ int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n, 
     for (int c = 0; c < n_chunks; c++) {
         const int f0 = first[c], m = first[c + 1] - f0, g0 = s0 + f0;        // g0: first arena slot of this sub-batch
         if (packed) CK(cudaMemcpyAsync(l0 + g0 * stride, imgs[f0], frame_bytes * (size_t)(m - 1) + step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
-        for (int f = f0; f < f0 + m && !packed; f++) {
+        else if (contiguous) {
+            // rows that are not 4-byte multiples, frames adjacent in host memory: the sub-batch goes up as ONE copy into the
+            // staging area and is re-pitched by ONE device-side 2-D copy (the frames are m * rows consecutive rows on both sides)
+            uint8_t* st = h->d_stage + (size_t)g0 * frame_bytes;
+            CK(cudaMemcpyAsync(st, imgs[f0], frame_bytes * (size_t)(m - 1) + step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
+            CK(cudaMemcpy2DAsync(l0 + g0 * stride, pitch, st, step, cols, (size_t)rows * m, cudaMemcpyDeviceToDevice, h->s_in));
+        }
+        for (int f = f0; f < f0 + m && !packed && !contiguous; f++) {
             if (flat) CK(cudaMemcpyAsync(l0 + (s0 + f) * stride, imgs[f], step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
             else {
                 // rows that are not 4-byte multiples: one contiguous host->device copy into a staging area, then a

@@ -128,8 +128,6 @@ __device__ __forceinline__ int fast_score16(const int (&d)[16]) {
 // list; (C) full 16-ring FAST-9 test on candidates -> corner list; (D) cornerScore on corners -> score map;
 // (E) 3x3 NMS on corners only -> warp-aggregated append to the (frame, level) corner list in HBM.
 #define FAST_TS 76                             // tile row stride: 64 + 6 halo + up to 3 bytes of word-alignment shift
-#define FAST_SS (FAST_MAX_CELL + 4)            // score row stride
-#define FAST_SCORE_BYTES (((FAST_MAX_CELL + 2) * FAST_SS + 15) / 16 * 16)
 
 // Shared-memory list plumbing written as PTX on 32-bit shared addresses: one ATOMS per warp (nvcc otherwise wraps every
 // atomicAdd in its own warp-aggregation sequence) and predicated 16-bit stores instead of a branch per store.
@@ -154,14 +152,16 @@ __device__ __forceinline__ void list_append(bool pred, uint32_t val, uint32_t li
     sts_u16_if(pred, list_s + 2 * (base + __popc(ballot & lanemask_lt())), val);
 }
 
-#define FAST_THREADS 128
+// CTA size NT is a template parameter (96 / 128 / 160 threads): a cell is ngx x ch 4-pixel groups (~290 at the reference's 30-px
+// cells) and the host picks the NT that wastes the fewest lanes in the sweeps over them (fast_pick_threads, orb_api.cu)
 // Dynamic shared memory, sized by the host for the largest cell of the configured shape (fast_smem_layout):
-// tile [max_ch + 6][ts] | score [max_ch + 2][FAST_SS] | cand [max_px] u16 | corn [max_px] u16
-struct FastSmem { int score_off, cand_off, corn_off, total, ts, tile_rows; };
+// tile [max_ch + 6][ts] | score [max_ch + 2][ss] | cand [max_px] u16 | corn [max_px] u16
+struct FastSmem { int score_off, cand_off, corn_off, total, ts, tile_rows, ss; };
 static inline FastSmem fast_smem_layout(int max_cw, int max_ch, int ts = FAST_TS) {
     FastSmem m;
     const int tile_bytes = ((max_ch + 6) * ts + 127) / 128 * 128;
-    const int score_bytes = ((max_ch + 2) * FAST_SS + 15) / 16 * 16;
+    m.ss = (max_cw + 2 + 3) / 4 * 4;                                 // score row stride: widest cell + its 1-px zero ring
+    const int score_bytes = ((max_ch + 2) * m.ss + 15) / 16 * 16;
     const int list_bytes = (max_cw * max_ch * 2 + 15) / 16 * 16;
     m.score_off = tile_bytes; m.cand_off = m.score_off + score_bytes; m.corn_off = m.cand_off + list_bytes;
     m.total = m.corn_off + list_bytes;
@@ -189,8 +189,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar_s, uint32_t parity) {
                  ::"r"(bar_s), "r"(parity) : "memory");
 }
 
-template <int TS, bool TMA>
-__global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_constant__ LevelTable T,
+#ifndef FAST_RESIDENT_THREADS
+#define FAST_RESIDENT_THREADS 2048          // threads per SM the register budget is sized for (32 registers per thread)
+#endif
+template <int TS, bool TMA, int NT>
+__global__ void __launch_bounds__(NT, FAST_RESIDENT_THREADS / NT) k_fast_cells(const __grid_constant__ LevelTable T,
                                                     const uint4* __restrict__ cell_info,  // per cell 2 x uint4, see configure_shape
                                                     uint32_t* __restrict__ corners,      // [frames][corners_per_frame]
                                                     int* __restrict__ corner_count,      // [frames][CCM_MAX_LEVELS]
@@ -198,7 +201,8 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
                                                     const __grid_constant__ FastTma tm) {
     extern __shared__ __align__(128) uint8_t fast_smem[];
     uint8_t* const tile = fast_smem;                                   // [ch + 6][TS]
-    uint8_t* const score = fast_smem + M.score_off;                    // [cell + 1-px zero ring][FAST_SS]
+    uint8_t* const score = fast_smem + M.score_off;                    // [cell + 1-px zero ring][SS]
+    const int SS = M.ss;
     uint16_t* const cand = reinterpret_cast<uint16_t*>(fast_smem + M.cand_off);
     uint16_t* const corn = reinterpret_cast<uint16_t*>(fast_smem + M.corn_off);
     __shared__ int n_cand, n_corn;
@@ -230,8 +234,8 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
             tma_load_3d(smem_addr(tile), &tm.m[lvl], gxa, y0 - 3, frame0 + f, bar_s);
         }
     } else {
-        // FAST_THREADS / wpr tile rows per sweep, one word per thread, pointers stepped by whole sweeps
-        const int rps = (int)((FAST_THREADS * wmagic) >> 20);
+        // NT / wpr tile rows per sweep, one word per thread, pointers stepped by whole sweeps
+        const int rps = (int)((NT * wmagic) >> 20);
         const int ty0 = (int)(((uint32_t)tid * wmagic) >> 20), tx = tid - ty0 * wpr;
         if (ty0 < rps) {
             const uint8_t* src = img + (size_t)(y0 - 3 + ty0) * L.img_pitch + gxa + 4 * tx;
@@ -242,7 +246,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
                 *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(src);
         }
     }
-    for (int i = tid; i < ((ch + 2) * FAST_SS + 15) / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
+    for (int i = tid; i < ((ch + 2) * SS + 15) / 16; i += NT) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
     if (tid == 0) { n_cand = 0; n_corn = 0; }
     __syncthreads();
     if (TMA) mbar_wait(smem_addr(&tile_bar), 0);     // every thread observes the completed transaction: the tile is visible
@@ -256,7 +260,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
         // (B) opposite-pair test on 4 pixels per thread (a 9-arc of the ring contains one pixel of every diametral pair,
         //     so |v-p0|<=t && |v-p8|<=t, or the same for p4/p12, rules a pixel out): aligned 32-bit tile words, byte SIMD
         const uint32_t t4 = (uint32_t)threshold * 0x01010101u;
-        for (int base = 0; base < ngrp; base += FAST_THREADS) {
+        for (int base = 0; base < ngrp; base += NT) {
             const int gi = base + tid;
             uint32_t nib = 0;
             int py = 0, pxb = 0;
@@ -295,7 +299,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
         __syncthreads();
         // (C) full FAST-9/16 segment test on the candidates
         const int nc = n_cand;
-        for (int base = 0; base < nc; base += FAST_THREADS) {
+        for (int base = 0; base < nc; base += NT) {
             const int j = base + tid;
             bool is_corner = false;
             int i = 0;
@@ -319,7 +323,7 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
         __syncthreads();
         // (D) cornerScore of the corners -> score map
         const int nk = n_corn;
-        for (int j = tid; j < nk; j += FAST_THREADS) {
+        for (int j = tid; j < nk; j += NT) {
             const int i = corn[j];
             const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
             const uint8_t* c = tile + (py + 3) * TS + px + 3 + shift;
@@ -329,22 +333,22 @@ __global__ void __launch_bounds__(FAST_THREADS, 16) k_fast_cells(const __grid_co
             d[4] = v - c[3];           d[5] = v - c[-S + 3];      d[6] = v - c[-2 * S + 2];  d[7] = v - c[-3 * S + 1];
             d[8] = v - c[-3 * S];      d[9] = v - c[-3 * S - 1];  d[10] = v - c[-2 * S - 2]; d[11] = v - c[-S - 3];
             d[12] = v - c[-3];         d[13] = v - c[S - 3];      d[14] = v - c[2 * S - 2];  d[15] = v - c[3 * S - 1];
-            score[(py + 1) * FAST_SS + px + 1] = (uint8_t)fast_score16(d);   // >= threshold > 0 (threshold >= 1 enforced at create)
+            score[(py + 1) * SS + px + 1] = (uint8_t)fast_score16(d);   // >= threshold > 0 (threshold >= 1 enforced at create)
         }
         __syncthreads();
         // (E) non-maximum suppression over the corners, append survivors
         int found = 0;
-        for (int base = 0; base < nk; base += FAST_THREADS) {     // uniform trip count: ballots below need whole warps
+        for (int base = 0; base < nk; base += NT) {     // uniform trip count: ballots below need whole warps
             const int j = base + tid;
             bool keep = false;
             int px = 0, py = 0, s = 0;
             if (j < nk) {
                 const int i = corn[j];
                 py = (int)(((uint32_t)i * cmagic) >> 20); px = i - py * cw;
-                const uint8_t* sc = &score[(py + 1) * FAST_SS + px + 1];
+                const uint8_t* sc = &score[(py + 1) * SS + px + 1];
                 s = sc[0];
-                keep = s > sc[-FAST_SS - 1] && s > sc[-FAST_SS] && s > sc[-FAST_SS + 1] && s > sc[-1] && s > sc[1] &&
-                       s > sc[FAST_SS - 1] && s > sc[FAST_SS] && s > sc[FAST_SS + 1];
+                const uint8_t *su = sc - SS, *sd = sc + SS;
+                keep = s > su[-1] && s > su[0] && s > su[1] && s > sc[-1] && s > sc[1] && s > sd[-1] && s > sd[0] && s > sd[1];
             }
             const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
             if (ballot) {
