@@ -60,3 +60,10 @@ __device__ __forceinline__ int ccm_reflect101(int p, int len) {
     if (p >= len) p = 2 * (len - 1) - p;
     return p;
 }
+
+// Programmatic dependent launch (sm_90+): a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start
+// while its predecessor on the stream is still draining; pdl_wait() blocks until that predecessor has completed and its writes
+// are visible, pdl_launch() lets the successor's CTAs take the SM slots this grid no longer needs. Both are no-ops for a
+// normal launch. Everything a kernel reads before pdl_wait() must be data no earlier kernel of the chain writes (host tables).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }

@@ -160,12 +160,25 @@ static bool encode_level_map(ccm_orb* h, CUtensorMap* out, const void* base, siz
                                                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// launch with the programmatic-stream-serialization attribute (see pdl_wait / pdl_launch, ccm_common.cuh)
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    static const bool off = std::getenv("CCM_ORB_NO_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = off ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 template <int TS, bool TMA>
 static void launch_fast(cudaStream_t s, dim3 grid, int nt, const LevelTable& T, const uint4* cell_info, uint32_t* corners, int* corner_count,
                         const FastSmem& M, int frame0, const FastTma& tm) {
-    if (nt == 96) k_fast_cells<TS, TMA, 96><<<grid, 96, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
-    else if (nt == 160) k_fast_cells<TS, TMA, 160><<<grid, 160, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
-    else k_fast_cells<TS, TMA, 128><<<grid, 128, M.total, s>>>(T, cell_info, corners, corner_count, M, frame0, tm);
+    if (nt == 96) launch_pdl(k_fast_cells<TS, TMA, 96>, grid, dim3(96), (size_t)M.total, s, T, cell_info, corners, corner_count, M, frame0, tm);
+    else if (nt == 160) launch_pdl(k_fast_cells<TS, TMA, 160>, grid, dim3(160), (size_t)M.total, s, T, cell_info, corners, corner_count, M, frame0, tm);
+    else launch_pdl(k_fast_cells<TS, TMA, 128>, grid, dim3(128), (size_t)M.total, s, T, cell_info, corners, corner_count, M, frame0, tm);
 }
 template <int TS, bool TMA>
 static cudaError_t fast_set_carveout() {
@@ -382,7 +395,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[0], s));
         for (int l = 1; l < T.nlevels; l++) {
             dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
-            if (T.l[l].xgrp) k_resize_level<<<g, dim3(32, 8), 0, s>>>(T, l);
+            if (T.l[l].xgrp) launch_pdl(k_resize_level, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l);
             else k_resize_level_generic<<<g, dim3(32, 8), 0, s>>>(T, l);
             h->launches++;
         }
@@ -408,8 +421,8 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[3], s));
     }
     {
-        k_quadtree<<<dim3(T.nlevels, n), 512, h->qt_smem, s>>>(T, h->qt_cap, h->qt_ccap, A.corners, A.corner_count, A.node_of,
-                                                              A.level_kps, A.level_kp_count);
+        launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(512), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, (const uint32_t*)A.corners,
+                   (const int*)A.corner_count, A.node_of, A.level_kps, A.level_kp_count);
         h->launches++;
         if (fork) {
             CK(cudaStreamWaitEvent(LN.aux, LN.fork, 0));

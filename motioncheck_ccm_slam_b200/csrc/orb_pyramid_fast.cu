@@ -13,41 +13,69 @@
 // from the host-built group table) and forms a0*p0 + a1*p1 with one IDP2A. k_resize_level_generic (byte loads) covers
 // larger factors.
 // ---------------------------------------------------------------------------------------------
+// A thread walks RESIZE_ROWS consecutive output rows of its 4-pixel column: the horizontal pass of a source row is kept in
+// registers and reused when the next output row starts on it (at scale 1.2 an output row's lower source row is the next
+// row's upper one four times out of five), and the column's table entries are loaded once.
+#define RESIZE_ROWS 4
+__device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ rp, bool in1, bool in2, uint32_t shift, uint32_t sel4,
+                                            const uint32_t (&coef)[4], uint32_t (&r)[4]) {
+    const uint32_t u0 = *reinterpret_cast<const uint32_t*>(rp);
+    const uint32_t u1 = in1 ? *reinterpret_cast<const uint32_t*>(rp + 4) : 0u;
+    const uint32_t u2 = in2 ? *reinterpret_cast<const uint32_t*>(rp + 8) : 0u;
+    const uint32_t lo = __funnelshift_r(u0, u1, shift), hi = __funnelshift_r(u1, u2, shift);
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = __dp2a_lo(coef[i], __byte_perm(lo, hi, (sel4 >> (8 * i)) & 0xffu), 0u) >> 4;
+}
+
 __global__ void __launch_bounds__(256) k_resize_level(const __grid_constant__ LevelTable T, int lvl) {
     const LevelDesc& D = T.l[lvl];
     const LevelDesc& S = T.l[lvl - 1];
     const int f = blockIdx.z;
     const int g = blockIdx.x * 32 + threadIdx.x, x4 = g * 4;
-    const int y = blockIdx.y * 8 + threadIdx.y;
-    if (y >= D.h || x4 >= D.w) return;
-    const uint8_t* __restrict__ src = S.img + (size_t)f * S.img_stride;
+    const int y0 = (blockIdx.y * 8 + threadIdx.y) * RESIZE_ROWS;
+    pdl_launch();
+    if (y0 >= D.h || x4 >= D.w) { pdl_wait(); return; }      // no CTA leaves before its predecessor is complete (the chain is transitive)
     // group table (resize_group_table, orb_api.cu): {first tap's aligned byte offset, bit shift to the first tap,
     // 4 x (tap0 | tap1 << 4) byte selectors, -} {4 x (a0 | a1 << 16)}
     const uint4 ga = __ldg(D.xgrp + 2 * g), gc = __ldg(D.xgrp + 2 * g + 1);
     const int base = (int)ga.x, wlim = S.w;                   // words starting at or beyond the row's last pixel are not read
-    const int sy0 = __ldg(D.yofs + y);
-    const int sy1 = min(sy0 + 1, S.h - 1);
-    const uint32_t b0 = (uint32_t)__ldg(D.ycoef + 2 * y), b1 = (uint32_t)__ldg(D.ycoef + 2 * y + 1);
-    const uint8_t* r0p = src + (size_t)sy0 * S.img_pitch + base;
-    const uint8_t* r1p = src + (size_t)sy1 * S.img_pitch + base;
     const bool in1 = base + 4 < wlim, in2 = base + 8 < wlim;
-    const uint32_t u0 = *reinterpret_cast<const uint32_t*>(r0p), v0 = *reinterpret_cast<const uint32_t*>(r1p);
-    const uint32_t u1 = in1 ? *reinterpret_cast<const uint32_t*>(r0p + 4) : 0u, v1 = in1 ? *reinterpret_cast<const uint32_t*>(r1p + 4) : 0u;
-    const uint32_t u2 = in2 ? *reinterpret_cast<const uint32_t*>(r0p + 8) : 0u, v2 = in2 ? *reinterpret_cast<const uint32_t*>(r1p + 8) : 0u;
-    const uint32_t lo0 = __funnelshift_r(u0, u1, ga.y), hi0 = __funnelshift_r(u1, u2, ga.y);
-    const uint32_t lo1 = __funnelshift_r(v0, v1, ga.y), hi1 = __funnelshift_r(v1, v2, ga.y);
     const uint32_t coef[4] = {gc.x, gc.y, gc.z, gc.w};
-    uint32_t packed = 0;
+    const uint8_t* __restrict__ src = S.img + (size_t)f * S.img_stride + base;
+    uint8_t* __restrict__ dst = D.img + (size_t)f * D.img_stride + (size_t)y0 * D.img_pitch + x4;
+    const int pitch = S.img_pitch, last = S.h - 1, ny = min(RESIZE_ROWS, D.h - y0);
+    int cached = -1;
+    uint32_t hc[4] = {0u, 0u, 0u, 0u};                        // horizontal pass of source row `cached`
+    const int sy_first = __ldg(D.yofs + y0);                  // host tables: loaded before the previous level is waited for
+    (void)sy_first;
+    pdl_wait();                                               // level lvl-1 is complete
 #pragma unroll
-    for (int i = 0; i < 4; i++) {
-        const uint32_t sel = (ga.z >> (8 * i)) & 0xffu;
-        const uint32_t r0 = __dp2a_lo(coef[i], __byte_perm(lo0, hi0, sel), 0u);
-        const uint32_t r1 = __dp2a_lo(coef[i], __byte_perm(lo1, hi1, sel), 0u);
-        const uint32_t v = (((b0 * (r0 >> 4)) >> 16) + ((b1 * (r1 >> 4)) >> 16) + 2) >> 2;
-        packed |= (v & 255u) << (8 * i);
+    for (int j = 0; j < RESIZE_ROWS; j++) {
+        if (j < ny) {                                         // warp-uniform (a warp is one row strip)
+            const int y = y0 + j;
+            const int sy0 = __ldg(D.yofs + y), sy1 = min(sy0 + 1, last);
+            const uint32_t b0 = (uint32_t)__ldg(D.ycoef + 2 * y), b1 = (uint32_t)__ldg(D.ycoef + 2 * y + 1);
+            uint32_t h0[4], h1[4];
+            if (sy0 == cached) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) h0[i] = hc[i];
+            } else resize_hrow(src + (size_t)sy0 * pitch, in1, in2, ga.y, ga.z, coef, h0);
+            if (sy1 == sy0) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) h1[i] = h0[i];
+            } else resize_hrow(src + (size_t)sy1 * pitch, in1, in2, ga.y, ga.z, coef, h1);
+            uint32_t packed = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t v = (((b0 * h0[i]) >> 16) + ((b1 * h1[i]) >> 16) + 2) >> 2;
+                packed |= (v & 255u) << (8 * i);
+                hc[i] = h1[i];
+            }
+            cached = sy1;
+            *reinterpret_cast<uint32_t*>(dst) = packed;       // pitch is a multiple of 32: in-bounds
+            dst += D.img_pitch;
+        }
     }
-    uint8_t* __restrict__ dst = D.img + (size_t)f * D.img_stride;
-    *reinterpret_cast<uint32_t*>(dst + (size_t)y * D.img_pitch + x4) = packed;   // pitch is a multiple of 32: in-bounds
 }
 
 __global__ void __launch_bounds__(256) k_resize_level_generic(const __grid_constant__ LevelTable T, int lvl) {
@@ -213,6 +241,8 @@ __global__ void __launch_bounds__(NT, FAST_RESIDENT_THREADS / NT) k_fast_cells(c
     // (host-built table: configure_shape, orb_api.cu)
     const uint4 ci = __ldg(cell_info + 2 * blockIdx.x), cj = __ldg(cell_info + 2 * blockIdx.x + 1);
     const int x0 = (int)(ci.x & 0xffff), y0 = (int)(ci.x >> 16), cw = (int)(ci.y & 0xffff), ch = (int)(ci.y >> 16), lvl = (int)ci.z;
+    pdl_launch();
+    pdl_wait();                              // the pyramid (previous kernels of the chain) is complete
     if (cw <= 0 || ch <= 0) return;          // clipped-away cell (the :962/:971 `continue`s)
     const LevelDesc& L = T.l[lvl];
 

@@ -66,7 +66,7 @@ __device__ __forceinline__ int quadrant(const QNode& p, int x, int y) {
 // A (frame, level) with at most ccap corners keeps its corner list and the corner -> node map in shared memory for the
 // whole run (every round walks both twice); larger ones work on the global arrays.
 __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap,
-                                                  const uint32_t* __restrict__ corners, const int* __restrict__ corner_count,
+                                                  const uint32_t* corners, const int* corner_count,   // written by the PDL predecessor: no __restrict__, so these are coherent loads the compiler cannot hoist above pdl_wait()
                                                   uint16_t* __restrict__ node_of,          // [frames][corners_per_frame]
                                                   uint32_t* __restrict__ level_kps,        // [frames][kps_per_frame] packed x|y<<12|score<<24
                                                   int* __restrict__ level_kp_count) {      // [frames][CCM_MAX_LEVELS]
@@ -74,6 +74,8 @@ __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constan
     const int lvl = blockIdx.x, f = blockIdx.y;
     const LevelDesc& L = T.l[lvl];
     const int tid = threadIdx.x, NT = blockDim.x;
+    pdl_launch();
+    pdl_wait();                              // the corner lists of k_fast_cells are complete
 
     QNode* A = reinterpret_cast<QNode*>(smem_raw);
     QNode* B = A + cap;
