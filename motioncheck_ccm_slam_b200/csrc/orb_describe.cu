@@ -111,6 +111,12 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
 //   Output: ccm_keypoint with pt scaled by mvScaleFactor[level] for level != 0 (:1268-1274), descriptor as two
 //   16-byte stores per keypoint.
 // ---------------------------------------------------------------------------------------------
+#ifndef DESC_LVL_PARALLEL
+#define DESC_LVL_PARALLEL 0          // measured slower (0.118 vs 0.109 ms): the divergent constant-bank reads serialise
+#endif
+#ifndef DESC_SINCOS
+#define DESC_SINCOS 1
+#endif
 struct BriefPattern { signed char v[256][4]; };
 __constant__ BriefPattern c_pattern_init = {{
 #include "brief_pattern.inc"
@@ -146,27 +152,38 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
                                                          uint8_t* __restrict__ out_desc,             // [frames][capacity][32]
                                                          int* __restrict__ out_count,                // [frames]
                                                          int capacity) {
-    __shared__ int pat[8][32][2];     // pat[k][lane] = packed taps of test 8*lane+k (conflict-free per k)
+    __shared__ float4 pat[8][32];     // pat[k][lane] = (x1, y1, x2, y2) of test 8*lane+k as floats: one LDS.128, no conversions in the loop
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 256; i += 256) {
-        const signed char* p = c_pattern_init.v[i];
-        pat[i & 7][i >> 3][0] = ((int)p[0] & 0xFFFF) | ((int)p[1] << 16);
-        pat[i & 7][i >> 3][1] = ((int)p[2] & 0xFFFF) | ((int)p[3] << 16);
+    {
+        const signed char* p = c_pattern_init.v[tid];
+        pat[tid & 7][tid >> 3] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
     }
     __syncthreads();
 
     const int f = blockIdx.y;
     const int slot = blockIdx.x * 8 + warp;
     if (slot >= T.kps_per_frame) return;
+#if DESC_LVL_PARALLEL
+    // level of this slot and the number of keypoints in front of it, lane l looking at level l: the level is the last one
+    // whose slot range starts at or before `slot`, `before` the keypoints of the lower levels, `total` all of them
+    const int my_off = lane < T.nlevels ? T.l[lane].kp_off : 0x7fffffff;
+    const int my_cnt = lane < T.nlevels ? level_kp_count[f * CCM_MAX_LEVELS + lane] : 0;
+    const int lvl = __popc(__ballot_sync(0xffffffffu, slot >= my_off)) - 1;
+    const int total = __reduce_add_sync(0xffffffffu, my_cnt);
+    const int before = __reduce_add_sync(0xffffffffu, lane < lvl ? my_cnt : 0);
+    const int cnt_lvl = __shfl_sync(0xffffffffu, my_cnt, lvl);
+#else
     int lvl = 0;
     while (lvl + 1 < T.nlevels && slot >= T.l[lvl + 1].kp_off) lvl++;
-    const LevelDesc& L = T.l[lvl];
-    const int pos = slot - L.kp_off;
     const int* cnt = level_kp_count + f * CCM_MAX_LEVELS;
     int before = 0, total = 0;
     for (int l = 0; l < T.nlevels; l++) { const int c = cnt[l]; if (l < lvl) before += c; total += c; }
+    const int cnt_lvl = cnt[lvl];
+#endif
+    const LevelDesc& L = T.l[lvl];
+    const int pos = slot - L.kp_off;
     if (slot == 0 && lane == 0) out_count[f] = total;
-    if (pos >= cnt[lvl]) return;
+    if (pos >= cnt_lvl) return;
     const int oi = before + pos;
     if (oi >= capacity) return;
 
@@ -195,19 +212,28 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
 
     // --- descriptor ---
     const float rad = __fmul_rn(angle, 0x1.1df46ap-6f);      // factorPI = (float)(CV_PI/180.f)
+#if DESC_SINCOS
+    double sd, cd;
+    sincos((double)rad, &sd, &cd);
+    const float a = (float)cd, b = (float)sd;
+#else
     const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+#endif
     const uint8_t* __restrict__ bl = L.blur + (size_t)f * L.blur_stride + (size_t)ky * L.blur_pitch + kx;
+    // cvRound of the steered tap (:107, :111-124) without the quarter-rate F2I: v + 1.5 * 2^23 rounds v to the nearest-even integer
+    // in the low mantissa bits (|v| < 2^22), so int(v) = bits - 0x4B400000. The two constants of row * pitch + col are folded
+    // into one (32-bit modular arithmetic: the true offset is small).
+    const float MAGIC = 12582912.0f;
+    const uint32_t pitch = (uint32_t)L.blur_pitch, kfold = 0x4B400000u * (pitch + 1u);
     uint32_t byte = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
-        const int p0 = pat[k][lane][0], p1 = pat[k][lane][1];
-        const float x1 = (float)(short)(p0 & 0xFFFF), y1 = (float)(p0 >> 16);
-        const float x2 = (float)(short)(p1 & 0xFFFF), y2 = (float)(p1 >> 16);
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int r2 = __float2int_rn(__fadd_rn(__fmul_rn(x2, b), __fmul_rn(y2, a)));
-        const int c2 = __float2int_rn(__fsub_rn(__fmul_rn(x2, a), __fmul_rn(y2, b)));
-        const int t0 = bl[r1 * L.blur_pitch + c1], t1 = bl[r2 * L.blur_pitch + c2];
+        const float4 p = pat[k][lane];
+        const uint32_t r1 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)), MAGIC));
+        const uint32_t c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)), MAGIC));
+        const uint32_t r2 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)), MAGIC));
+        const uint32_t c2 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)), MAGIC));
+        const int t0 = bl[(int)(r1 * pitch + c1 - kfold)], t1 = bl[(int)(r2 * pitch + c2 - kfold)];
         byte |= (uint32_t)(t0 < t1) << k;
     }
     uint32_t w = byte << (8 * (lane & 3));
