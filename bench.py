@@ -363,6 +363,36 @@ def cpu_allpairs_baseline(nq=64, nt=200000):
     return nq * nt / (time.perf_counter() - t0) / 1e9
 
 
+def bind_to_gpu_numa(local_rank):
+    """Agent-to-GPU pinning on the host side: run this rank (and first-touch its pinned buffers) on the CPUs of the NUMA node
+    its GPU hangs off, so that 8 ranks do not push their copies across the socket link. Best effort; returns the node or None."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local_rank]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else local_rank
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(idx)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]
+        with open("/sys/bus/pci/devices/%s/numa_node" % bus) as f:
+            node = int(f.read())
+        if node < 0:
+            return None
+        with open("/sys/devices/system/node/node%d/cpulist" % node) as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 # ----------------------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------------------
@@ -375,6 +405,7 @@ def run_ours(args, wl, rank, world, local_rank):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU baseline)")
+    numa_node = bind_to_gpu_numa(local_rank) if world > 1 else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -524,7 +555,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": B * w * h,
                 "d2h_bytes_per_step": B * cap * 56 + 4 * B, "keypoints_per_frame": n_kp_host / B,
                 "api": "ccm_orb_extract_batch_submit / _wait, two batches in flight (copy-in of batch i+1 overlaps the kernels of batch i)",
-                "synchronous_call_frames_per_s": B * args.steps / e2e_sync_s},
+                "synchronous_call_frames_per_s": B * args.steps / e2e_sync_s, "host_numa_node_rank0": numa_node},
         "gpu_launches": int(launches),
         "clocks": clocks,
     }
