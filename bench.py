@@ -574,7 +574,7 @@ def run_ours(args, wl, rank, world, local_rank):
         line["gpu_launches"] += int(ham["_launches"])
     if not args.no_cpu and world == 1:
         cores = os.cpu_count() or 1
-        fpt = 24
+        fpt = 48                                             # ~15 s of CPU work on 16 threads
         fps, dt, kind = cpu_reference_fps(frames[0], nf, nl, cores, fpt)
         line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                                 "sample": "%d threads x %d frames of the same stream, %.1f s" % (cores, fpt, dt)}

@@ -183,6 +183,32 @@ def test_device_resident_path_matches_host_path(cuda_lib):
         assert np.array_equal(d_desc[f, :n[f]].cpu().numpy(), dh[f])
 
 
+def test_device_buffers_tma_cannot_address_take_the_word_load_kernel(cuda_lib):
+    """Level 0 is read in place from the caller's buffer. A pitch that is not a 16-byte multiple (756) or a base 4 bytes off a
+    16-byte boundary cannot be described to TMA: those calls run k_fast_cells<.., TMA = false> and must give the same frames."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    frames = make_stream(3100, 3)
+    ex = make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=3)
+    kh, dh = ex.extract_batch(list(frames))
+    cap = ex.max_keypoints()
+    for pitch, lead in ((756, 0), (768, 4), (752, 0)):
+        buf = torch.zeros(lead + 3 * 480 * pitch + 64, dtype=torch.uint8, device="cuda")
+        view = buf[lead:lead + 3 * 480 * pitch].view(3, 480, pitch)
+        view[:, :, :752] = torch.from_numpy(frames).cuda()
+        d_kp = torch.zeros((3, cap, 6), dtype=torch.float32, device="cuda")
+        d_desc = torch.zeros((3, cap, 32), dtype=torch.uint8, device="cuda")
+        d_n = torch.zeros(3, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        ex.extract_batch_device(buf.data_ptr() + lead, 3, 480, 752, pitch, pitch * 480, d_kp.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+        ex.sync()
+        n = d_n.cpu().numpy()
+        for f in range(3):
+            assert n[f] == len(kh[f]), (pitch, lead, f)
+            kp = d_kp[f, :n[f]].cpu().numpy().view(np.uint8).reshape(-1).view(KP_DTYPE)
+            assert np.array_equal(kp, kh[f]) and np.array_equal(d_desc[f, :n[f]].cpu().numpy(), dh[f]), (pitch, lead, f)
+
+
 def test_dropin_cpp_class_matches_reference_class(cuda_lib):
     """The drop-in C++ class (motioncheck_ccm_slam_b200/host/ORBextractor.cpp, compiled against the reference's own
     <cslam/ORBextractor.h>) and the reference's ORBextractor.cpp, both driven through the same glue
