@@ -194,10 +194,29 @@ __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowPa
     const int maxCY = min(P.rows - 1, (int)ceilf(__fmul_rn(__fadd_rn(fy, q.r), P.inv_h)));
     if (minCX < P.cols && maxCX >= 0 && minCY < P.rows && maxCY >= 0) {
         const uint4* __restrict__ desc = reinterpret_cast<const uint4*>(P.desc);
+        // The window's grid columns are walked as ONE flattened candidate list (GetFeaturesInArea order: column by column,
+        // cells top to bottom, features in index order): lane j fetches the CSR range of column cx0 + j, an inclusive scan gives
+        // every column's first position, and the lanes then stride over all candidates of up to 32 columns at once. The
+        // dependent load chain (range -> item -> fields -> descriptor) is paid once per 32 candidates, not once per column.
         int pos_base = 0;
-        for (int ix = minCX; ix <= maxCX; ix++) {
-            const int s = P.cell_start[ix * P.rows + minCY], t = P.cell_start[ix * P.rows + maxCY + 1];
-            for (int p = s + lane; p < t; p += 32) {
+        for (int cx0 = minCX; cx0 <= maxCX; cx0 += 32) {
+            const int ix = cx0 + lane;
+            int s = 0, n = 0;
+            if (ix <= maxCX) { s = P.cell_start[ix * P.rows + minCY]; n = P.cell_start[ix * P.rows + maxCY + 1] - s; }
+            int inc = n;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
+            const int tot = __shfl_sync(0xffffffffu, inc, 31);
+            const int exc = inc - n;                       // position of this column's first candidate
+            for (int c0 = 0; c0 < tot; c0 += 32) {         // warp-uniform trip count: the shuffles below need all lanes
+                const int c = c0 + lane;
+                // column of candidate c = the first lane whose inclusive count exceeds c (binary search over the lanes by shuffle)
+                int lo = 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) { const int v = __shfl_sync(0xffffffffu, inc, lo + o - 1); if (v <= c) lo += o; }
+                const int s_j = __shfl_sync(0xffffffffu, s, lo), exc_j = __shfl_sync(0xffffffffu, exc, lo);
+                if (c >= tot) continue;
+                const int p = s_j + (c - exc_j);
                 const int k = P.items[p];
                 const int oct = P.octave[k];
                 if (oct < q.min_level) continue;
@@ -212,7 +231,7 @@ __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowPa
                 if (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) { if (holder[k] == -2) continue; }
                 else if (MODE == WIN_MODE_KF_SIM3) { if (holder[k] != -1) continue; }
                 const int dist = hamming256(qd0, qd1, desc[2 * (size_t)k], desc[2 * (size_t)k + 1]);
-                unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned long long)(pos_base + p - s) << 16) | (unsigned)k;
+                unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned long long)(pos_base + c) << 16) | (unsigned)k;
                 cnt++;
                 if (key < k3) {
                     k3 = key;
@@ -221,7 +240,7 @@ __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowPa
                     if (k1 < k0) { const unsigned long long t0 = k0; k0 = k1; k1 = t0; }
                 }
             }
-            pos_base += t - s;
+            pos_base += tot;
         }
     }
 #pragma unroll
@@ -461,7 +480,10 @@ __device__ __forceinline__ void window_eval_job(const WindowJob& J, const Window
 }
 
 // grid (query groups of 8, jobs); warp = one query of one job. Not used by CCM_WIN_INIT.
-__global__ void __launch_bounds__(256) k_window_eval(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
+#ifndef WIN_EVAL_MIN_CTAS
+#define WIN_EVAL_MIN_CTAS 6
+#endif
+__global__ void __launch_bounds__(256, WIN_EVAL_MIN_CTAS) k_window_eval(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
     const WindowJob& J = jobs[blockIdx.y];
     const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
     const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
