@@ -301,3 +301,62 @@ def test_async_submit_wait_pipeline(cuda_lib):
     # a synchronous call afterwards still works and the stage taps still see frame 0 in slot 0
     k, d = small.extract_batch(list(frames[1]))
     assert all(np.array_equal(k[f], want[1][0][f]) for f in range(B))
+
+
+def test_four_agents_share_one_gpu(cuda_lib):
+    """BASELINE configs[3] on one GPU: four agent streams (seeds 1000..4000), one extractor handle and one host thread per agent
+    (ClientSystem = one process per agent upstream), all running at once through the asynchronous pair. Every agent's output
+    must be what its handle gives when it runs alone, and agent 0's first frame what the oracle gives."""
+    import threading
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
+    w, h, B, NB, A = 752, 480, 4, 3, 4
+    streams = [make_stream(1000 * (a + 1), B * NB, w, h).reshape(NB, B, h, w) for a in range(A)]
+    exs = [make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=2 * B) for _ in range(A)]
+    cap = exs[0].max_keypoints()
+    alone = [[exs[a].extract_batch(list(streams[a][b])) for b in range(NB)] for a in range(A)]
+    got = [[None] * NB for _ in range(A)]
+    errs = []
+
+    def agent(a):
+        try:
+            pin = torch.from_numpy(streams[a].copy()).pin_memory()
+            base = pin.numpy()
+            okp = [torch.zeros((B, cap, 6), dtype=torch.float32).pin_memory() for _ in range(2)]
+            ode = [torch.zeros((B, cap, 32), dtype=torch.uint8).pin_memory() for _ in range(2)]
+            on = [(ctypes.c_int * B)() for _ in range(2)]
+            ptrs = [(ctypes.c_void_p * B)(*[base[b, f].ctypes.data for f in range(B)]) for b in range(NB)]
+
+            def collect(b):
+                s = b & 1
+                kp = okp[s].numpy().view(KP_DTYPE).reshape(B, cap)
+                got[a][b] = ([kp[f, :on[s][f]].copy() for f in range(B)], [ode[s].numpy()[f, :on[s][f]].copy() for f in range(B)])
+
+            for rep in range(3):                                   # keep the GPU shared for a while
+                t_prev = None
+                for b in range(NB):
+                    s = b & 1
+                    t = exs[a].extract_batch_submit(ptrs[b], B, h, w, w, okp[s].data_ptr(), ode[s].data_ptr(), cap, on[s])
+                    if t_prev is not None:
+                        exs[a].extract_batch_wait(t_prev)
+                        collect(b - 1)
+                    t_prev = t
+                exs[a].extract_batch_wait(t_prev)
+                collect(NB - 1)
+        except Exception as e:                                     # noqa: BLE001
+            errs.append((a, repr(e)))
+
+    ths = [threading.Thread(target=agent, args=(a,)) for a in range(A)]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    assert not errs, errs
+    for a in range(A):
+        for b in range(NB):
+            for f in range(B):
+                assert np.array_equal(got[a][b][0][f], alone[a][b][0][f]) and np.array_equal(got[a][b][1][f], alone[a][b][1][f]), (a, b, f)
+    ko, do = OracleExtractor(1000, 1.2, 8, 20, 7)(streams[0][0, 0])
+    assert_same(got[0][0][0][0], got[0][0][1][0], ko, do, "agent 0 frame 0")
+    for e in exs:
+        e.close()
