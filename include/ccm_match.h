@@ -235,6 +235,25 @@ int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, 
  * reference accept rule (best < TH_LOW and (float)best < nnratio*(float)best2, :641-643) -> d_accept [nq] (may be NULL) */
 int ccm_match_allpairs_merge_device(ccm_matcher* m, const ccm_best2* d_parts, int n_parts, int nq, float nnratio,
                                     ccm_best2* d_out, uint8_t* d_accept);
+/* ---- fused fold + exchange + merge over peer memory (NVLink), the multi-GPU form of the two calls above ----------
+ * One context per rank owns an exchange buffer in device memory that every other rank of the box maps (CUDA IPC across
+ * processes, or plain peer access inside one process). ccm_match_allpairs_best2_exchange_device then does the whole sharded
+ * search in two launches: the per-chunk search and ONE kernel that folds the chunks, stores the rank's best-2 records into
+ * every rank's buffer, flags them, waits for the other ranks' records of the same queries and merges (accept rule
+ * included). No NCCL call, no host synchronisation; every rank must make the same sequence of calls. */
+typedef struct ccm_exchange ccm_exchange;
+#define CCM_IPC_HANDLE_BYTES 64
+#define CCM_EXCHANGE_MAX_WORLD 16
+/* handle_out (may be NULL) receives the cudaIpcMemHandle_t of this rank's buffer, to be all-gathered by the caller */
+int ccm_exchange_create(ccm_matcher* m, int rank, int world, int nq_cap, ccm_exchange** out, uint8_t* handle_out);
+/* handles [world][CCM_IPC_HANDLE_BYTES] in rank order (entry `rank` is ignored): opens the peers' buffers */
+int ccm_exchange_connect_ipc(ccm_exchange* x, const uint8_t* handles);
+/* same-process variant: device pointers of all ranks' buffers (ccm_exchange_buffer) in rank order; enables peer access */
+int ccm_exchange_connect_ptrs(ccm_exchange* x, void* const* peer_buffers);
+void* ccm_exchange_buffer(ccm_exchange* x);
+void ccm_exchange_destroy(ccm_exchange* x);
+int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, const uint8_t* d_q, int nq, const uint8_t* d_targets,
+                                             long long nt, uint32_t index_base, float nnratio, ccm_best2* d_out, uint8_t* d_accept);
 /* host convenience: upload, search one shard, download */
 int ccm_match_allpairs_best2(ccm_matcher* m, const uint8_t* q, int nq, const uint8_t* targets, long long nt,
                              uint32_t index_base, ccm_best2* out);

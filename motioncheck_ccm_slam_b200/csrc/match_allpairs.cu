@@ -166,3 +166,87 @@ __global__ void __launch_bounds__(256) k_distinctive(const int* __restrict__ sta
     key = __reduce_min_sync(0xffffffffu, key);
     if (lane == 0) { best[p] = (int)(key & 0xffffu); best_median[p] = (int)(key >> 16); }
 }
+
+// ---------------------------------------------------------------------------------------------
+// Fused fold + exchange + merge for the sharded keyframe-database search (BASELINE.json configs[4]): the one path with a
+// real exchange step. Instead of fold -> NCCL all_gather -> merge (three launches and a collective whose 8 KB payload is
+// pure latency), ONE kernel per rank
+//   1. folds the rank's chunk records into its per-query best-2 (as k_allpairs_merge does),
+//   2. stores that record straight into slot [rank] of EVERY rank's exchange buffer over NVLink (peer memory, plain
+//      8-byte stores: a CTA writes 2 KB per peer, coalesced), fences at system scope and raises the CTA's flag on
+//      every peer,
+//   3. waits until the same CTA index of every other rank has raised its flag in the local buffer (the records it needs
+//      are exactly those that CTA wrote: no grid-wide or cross-GPU barrier), and
+//   4. merges the `world` records per query and applies the accept rule (ORBmatcher.cpp:641-643).
+// Records and flags are double-buffered by the parity of a per-context epoch: a rank can run at most one call ahead of
+// a peer (its call e+1 needs the peer's e+1 flags, which the peer raises only after its own call e has finished), so
+// the set of parity e&1 is never overwritten while somebody still merges call e.
+// Buffer of one rank: Best2Dev rec[2][world][nq_cap] | uint32_t flag[2][world][ctas_cap].
+// ---------------------------------------------------------------------------------------------
+#define EX_MAX_WORLD 16
+#define EX_THREADS 256
+struct ExPeers { unsigned char* p[EX_MAX_WORLD]; };
+
+__device__ __forceinline__ unsigned long long ld_sys_u64(const void* p) {
+    unsigned long long v;
+    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const void* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(void* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(EX_THREADS) k_allpairs_exchange(const Best2Dev* __restrict__ parts, int n_parts, int nq, float nnratio, int th_low,
+                                                                  const ExPeers peers, int rank, int world, int nq_cap, int ctas_cap, uint32_t epoch,
+                                                                  Best2Dev* __restrict__ out, uint8_t* __restrict__ accept) {
+    const int qi = blockIdx.x * EX_THREADS + threadIdx.x;
+    const uint32_t par = epoch & 1u;
+    const size_t rec_bytes = (size_t)2 * world * nq_cap * sizeof(Best2Dev);
+    // 1. fold this rank's chunks
+    uint32_t bd = 256, bi = 0xffffffffu, sd = 256;
+    if (qi < nq) {
+        for (int p = 0; p < n_parts; p++) {
+            const Best2Dev r = parts[(size_t)p * nq + qi];
+            if (r.d1 < bd || (r.d1 == bd && r.idx < bi)) { sd = min(sd, bd); bd = r.d1; bi = r.idx; }
+            else sd = min(sd, (uint32_t)r.d1);
+            sd = min(sd, (uint32_t)r.d2);
+        }
+        // 2. publish into slot [par][rank] of every rank's buffer (own included)
+        const unsigned long long packed = (unsigned long long)bi | ((unsigned long long)bd << 32) | ((unsigned long long)sd << 48);   // == Best2Dev {idx, d1, d2}
+        for (int t = 0; t < world; t++) {
+            unsigned long long* dst = reinterpret_cast<unsigned long long*>(peers.p[t]) + ((size_t)par * world + rank) * nq_cap + qi;
+            *dst = packed;
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x < world) {
+        uint32_t* flag = reinterpret_cast<uint32_t*>(peers.p[threadIdx.x] + rec_bytes) + ((size_t)par * world + rank) * ctas_cap + blockIdx.x;
+        st_release_sys_u32(flag, epoch);
+    }
+    // 3. wait for the same CTA of every rank (flags live in the local buffer)
+    if (threadIdx.x < world) {
+        const uint32_t* flag = reinterpret_cast<const uint32_t*>(peers.p[rank] + rec_bytes) + ((size_t)par * world + threadIdx.x) * ctas_cap + blockIdx.x;
+        while (ld_acquire_sys_u32(flag) != epoch) __nanosleep(100);
+    }
+    __syncthreads();
+    // 4. merge across ranks
+    if (qi >= nq) return;
+    bd = 256; bi = 0xffffffffu; sd = 256;
+    const unsigned long long* mine = reinterpret_cast<const unsigned long long*>(peers.p[rank]) + (size_t)par * world * nq_cap + qi;
+    for (int t = 0; t < world; t++) {
+        const unsigned long long v = ld_sys_u64(mine + (size_t)t * nq_cap);
+        const uint32_t idx = (uint32_t)v, d1 = (uint32_t)(v >> 32) & 0xffffu, d2 = (uint32_t)(v >> 48);
+        if (d1 < bd || (d1 == bd && idx < bi)) { sd = min(sd, bd); bd = d1; bi = idx; }
+        else sd = min(sd, d1);
+        sd = min(sd, d2);
+    }
+    Best2Dev o; o.idx = bi; o.d1 = (uint16_t)bd; o.d2 = (uint16_t)sd;
+    out[qi] = o;
+    if (accept) accept[qi] = ((int)bd < th_low && (float)bd < __fmul_rn(nnratio, (float)sd)) ? 1 : 0;
+}

@@ -750,10 +750,9 @@ int ccm_distinctive_descriptors(ccm_matcher* m, int n_points, const int* start, 
 }
 
 /* ---- server keyframe-database search ---------------------------------------------------------------------- */
-int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
-                                    uint32_t index_base, ccm_best2* d_out) {
-    if (!m || nq < 0 || nt < 0 || !d_out || (nq > 0 && !d_q) || (nt > 0 && !d_targets)) return CCM_E_BADARG;
-    if (nq == 0) return CCM_OK;
+// per-chunk best-2 of d_q over one shard: *parts_out [n_chunks][nq] in the matcher's arena
+static int allpairs_chunks(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt, uint32_t index_base,
+                           Best2Dev** parts_out, int* n_chunks_out) {
     if (((uintptr_t)d_q | (uintptr_t)d_targets) & 15) { m->err = "descriptor arrays must be 16-byte aligned"; return CCM_E_BADARG; }
     cudaSetDevice(m->device);
     // queries per thread: as many as keep (almost) every thread of a query tile busy
@@ -773,8 +772,116 @@ int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, 
     if (Q == 4) k_allpairs_best2<4><<<grid, AP_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_targets, nt, (int)chunk, index_base, parts);
     else if (Q == 2) k_allpairs_best2<2><<<grid, AP_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_targets, nt, (int)chunk, index_base, parts);
     else k_allpairs_best2<1><<<grid, AP_THREADS, 0, m->stream>>>((const uint4*)d_q, nq, (const uint4*)d_targets, nt, (int)chunk, index_base, parts);
-    k_allpairs_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>(parts, (int)n_chunks, nq, 0.f, CCM_TH_LOW, (Best2Dev*)d_out, nullptr);
-    m->launches += 2;
+    m->launches++;
+    *parts_out = parts; *n_chunks_out = (int)n_chunks;
+    return CCM_OK;
+}
+
+int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
+                                    uint32_t index_base, ccm_best2* d_out) {
+    if (!m || nq < 0 || nt < 0 || !d_out || (nq > 0 && !d_q) || (nt > 0 && !d_targets)) return CCM_E_BADARG;
+    if (nq == 0) return CCM_OK;
+    Best2Dev* parts; int n_chunks;
+    int rc = allpairs_chunks(m, d_q, nq, d_targets, nt, index_base, &parts, &n_chunks);
+    if (rc) return rc;
+    k_allpairs_merge<<<(nq + 255) / 256, 256, 0, m->stream>>>(parts, n_chunks, nq, 0.f, CCM_TH_LOW, (Best2Dev*)d_out, nullptr);
+    m->launches++;
+    MCK(cudaGetLastError());
+    return CCM_OK;
+}
+
+/* ---- peer-memory exchange context ------------------------------------------------------------------------- */
+struct ccm_exchange {
+    ccm_matcher* m = nullptr;
+    int rank = 0, world = 1, nq_cap = 0, ctas_cap = 0;
+    size_t bytes = 0;
+    unsigned char* buf = nullptr;                       // this rank's buffer
+    unsigned char* peer[EX_MAX_WORLD] = {};             // every rank's buffer as seen from this device
+    bool ipc_opened[EX_MAX_WORLD] = {};
+    bool connected = false;
+    uint32_t epoch = 0;
+};
+
+int ccm_exchange_create(ccm_matcher* m, int rank, int world, int nq_cap, ccm_exchange** out, uint8_t* handle_out) {
+    if (!m || !out || world < 1 || world > EX_MAX_WORLD || rank < 0 || rank >= world || nq_cap < 1) return CCM_E_BADARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == CCM_IPC_HANDLE_BYTES, "ipc handle size");
+    static_assert(EX_MAX_WORLD == CCM_EXCHANGE_MAX_WORLD, "exchange world limit");
+    *out = nullptr;
+    cudaSetDevice(m->device);
+    ccm_exchange* x = new ccm_exchange();
+    x->m = m; x->rank = rank; x->world = world; x->nq_cap = nq_cap; x->ctas_cap = (nq_cap + EX_THREADS - 1) / EX_THREADS;
+    x->bytes = (size_t)2 * world * nq_cap * sizeof(Best2Dev) + (size_t)2 * world * x->ctas_cap * sizeof(uint32_t);
+    cudaError_t e = cudaMalloc((void**)&x->buf, x->bytes);
+    if (e == cudaSuccess) e = cudaMemset(x->buf, 0, x->bytes);               // flags start at epoch 0 = "nothing published"
+    if (e == cudaSuccess && handle_out) e = cudaIpcGetMemHandle((cudaIpcMemHandle_t*)handle_out, x->buf);
+    if (e != cudaSuccess) { m->err = std::string("exchange buffer: ") + cudaGetErrorString(e); if (x->buf) cudaFree(x->buf); delete x; return CCM_E_CUDA; }
+    x->peer[rank] = x->buf;
+    x->connected = world == 1;
+    *out = x;
+    return CCM_OK;
+}
+
+int ccm_exchange_connect_ipc(ccm_exchange* x, const uint8_t* handles) {
+    if (!x || !handles) return CCM_E_BADARG;
+    ccm_matcher* m = x->m;
+    cudaSetDevice(m->device);
+    for (int r = 0; r < x->world; r++) {
+        if (r == x->rank) continue;
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + (size_t)r * CCM_IPC_HANDLE_BYTES, sizeof(h));
+        void* p = nullptr;
+        MCK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        x->peer[r] = (unsigned char*)p; x->ipc_opened[r] = true;
+    }
+    x->connected = true;
+    return CCM_OK;
+}
+
+int ccm_exchange_connect_ptrs(ccm_exchange* x, void* const* peer_buffers) {
+    if (!x || !peer_buffers) return CCM_E_BADARG;
+    ccm_matcher* m = x->m;
+    cudaSetDevice(m->device);
+    for (int r = 0; r < x->world; r++) {
+        if (r == x->rank) continue;
+        if (!peer_buffers[r]) { m->err = "null peer buffer"; return CCM_E_BADARG; }
+        cudaPointerAttributes a;
+        MCK(cudaPointerGetAttributes(&a, peer_buffers[r]));
+        if (a.device != m->device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(a.device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else if (e != cudaSuccess) { m->err = std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e); return CCM_E_CUDA; }
+        }
+        x->peer[r] = (unsigned char*)peer_buffers[r];
+    }
+    x->connected = true;
+    return CCM_OK;
+}
+
+void* ccm_exchange_buffer(ccm_exchange* x) { return x ? (void*)x->buf : nullptr; }
+
+void ccm_exchange_destroy(ccm_exchange* x) {
+    if (!x) return;
+    cudaSetDevice(x->m->device);
+    cudaStreamSynchronize(x->m->stream);
+    for (int r = 0; r < x->world; r++) if (x->ipc_opened[r]) cudaIpcCloseMemHandle(x->peer[r]);
+    if (x->buf) cudaFree(x->buf);
+    delete x;
+}
+
+int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, const uint8_t* d_q, int nq, const uint8_t* d_targets,
+                                             long long nt, uint32_t index_base, float nnratio, ccm_best2* d_out, uint8_t* d_accept) {
+    if (!m || !x || x->m != m || nq < 1 || nt < 0 || !d_out || !d_q || (nt > 0 && !d_targets)) return CCM_E_BADARG;
+    if (!x->connected) { m->err = "exchange context is not connected to its peers"; return CCM_E_BADARG; }
+    if (nq > x->nq_cap) { m->err = "more queries than the exchange context was created for"; return CCM_E_CAPACITY; }
+    Best2Dev* parts; int n_chunks;
+    int rc = allpairs_chunks(m, d_q, nq, d_targets, nt, index_base, &parts, &n_chunks);
+    if (rc) return rc;
+    ExPeers P;
+    for (int r = 0; r < EX_MAX_WORLD; r++) P.p[r] = r < x->world ? x->peer[r] : nullptr;
+    x->epoch++;
+    k_allpairs_exchange<<<(nq + EX_THREADS - 1) / EX_THREADS, EX_THREADS, 0, m->stream>>>(parts, n_chunks, nq, nnratio, CCM_TH_LOW, P, x->rank, x->world,
+                                                                                           x->nq_cap, x->ctas_cap, x->epoch, (Best2Dev*)d_out, d_accept);
+    m->launches++;
     MCK(cudaGetLastError());
     return CCM_OK;
 }

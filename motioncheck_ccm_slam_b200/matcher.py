@@ -133,6 +133,44 @@ class Matcher:
         self._check(self._lib.ccm_match_allpairs_merge_device(self._h, d_parts, n_parts, nq, nnratio, d_out, d_accept))
 
 
+class Exchange:
+    """Peer-memory exchange context of the sharded keyframe-database search (ccm_exchange_*): one per rank."""
+
+    def __init__(self, matcher, rank, world, nq_cap):
+        self.m, self.rank, self.world = matcher, rank, world
+        self._h = ctypes.c_void_p()
+        self.handle = np.zeros(64, np.uint8)             # cudaIpcMemHandle_t of this rank's buffer
+        matcher._check(matcher._lib.ccm_exchange_create(matcher._h, rank, world, int(nq_cap), ctypes.byref(self._h), self.handle.ctypes.data))
+
+    def buffer(self):
+        return self.m._lib.ccm_exchange_buffer(self._h)
+
+    def connect_ipc(self, handles):
+        """handles: [world][64] uint8, all ranks' `handle` arrays in rank order (other processes of the same box)."""
+        hs = np.ascontiguousarray(handles, np.uint8).reshape(self.world, 64)
+        self.m._check(self.m._lib.ccm_exchange_connect_ipc(self._h, hs.ctypes.data))
+
+    def connect_ptrs(self, buffers):
+        """buffers: every rank's Exchange.buffer() in rank order (contexts of the same process on different devices)."""
+        arr = (ctypes.c_void_p * self.world)(*buffers)
+        self.m._check(self.m._lib.ccm_exchange_connect_ptrs(self._h, arr))
+
+    def allpairs_best2_device(self, d_q, nq, d_targets, nt, index_base, nnratio, d_out, d_accept=None):
+        self.m._check(self.m._lib.ccm_match_allpairs_best2_exchange_device(self.m._h, self._h, d_q, int(nq), d_targets, int(nt), int(index_base),
+                                                                           float(nnratio), d_out, d_accept))
+
+    def close(self):
+        if self._h:
+            self.m._lib.ccm_exchange_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class FramePack:
     """Device copy of what the matcher reads of a Frame / KeyFrame: mDescriptors, mvKeysUn, mGrid (Frame.h:128-149)."""
 

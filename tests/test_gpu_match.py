@@ -697,3 +697,75 @@ def test_wire_format_mvkeysun_override(gm):
     kb, db = gm.wire_encode_keyframe(kp, desc, xy_un=xy)
     kp2 = kp.copy(); kp2["x"] = xy[:, 0]; kp2["y"] = xy[:, 1]
     assert (kb, db) == oracle_wire_encode(kp2, desc)
+
+
+# ---- fused fold + exchange + merge over peer memory (ccm_exchange_*) --------------------------------------------------
+def test_allpairs_exchange_world1_equals_merge(gm):
+    """One rank: the fused kernel publishes into its own buffer and merges: identical to search + merge, over several calls
+    (epoch parity), with fewer queries than the context's capacity and an empty shard."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200.matcher import BEST2_DTYPE, Exchange
+    rng = np.random.default_rng(21)
+    x = Exchange(gm, 0, 1, 1000)
+    for call, (nq, nt) in enumerate([(1000, 50000), (1000, 50000), (300, 7000), (1, 1), (513, 0)]):
+        q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+        t = rng.integers(0, 256, (max(nt, 1), 32), dtype=np.uint8)
+        if nt:
+            t[rng.integers(0, nt, min(nq, nt) // 2)] = q[: min(nq, nt) // 2]          # exact duplicates: distance 0, index ties
+        d_q, d_t = torch.from_numpy(q).cuda(), torch.from_numpy(t).cuda()
+        d_out = torch.zeros((nq, 8), dtype=torch.uint8, device="cuda")
+        d_acc = torch.zeros(nq, dtype=torch.uint8, device="cuda")
+        d_ref = torch.zeros((nq, 8), dtype=torch.uint8, device="cuda")
+        d_ref2 = torch.zeros((nq, 8), dtype=torch.uint8, device="cuda")
+        d_acc2 = torch.zeros(nq, dtype=torch.uint8, device="cuda")
+        torch.cuda.synchronize()
+        x.allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), nt, 1000 * call, 0.6, d_out.data_ptr(), d_acc.data_ptr())
+        gm.match_allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), nt, 1000 * call, d_ref.data_ptr())
+        gm.match_allpairs_merge_device(d_ref.data_ptr(), 1, nq, 0.6, d_ref2.data_ptr(), d_acc2.data_ptr())
+        gm.sync()
+        assert np.array_equal(d_out.cpu().numpy().view(BEST2_DTYPE), d_ref2.cpu().numpy().view(BEST2_DTYPE)), call
+        assert np.array_equal(d_acc.cpu().numpy(), d_acc2.cpu().numpy())
+    x.close()
+
+
+def test_allpairs_exchange_two_gpus(cuda_lib):
+    """Two ranks on two devices of one process (peer access): every rank ends with the result of the unsharded search."""
+    torch = pytest.importorskip("torch")
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from motioncheck_ccm_slam_b200.matcher import BEST2_DTYPE, Exchange, Matcher
+    rng = np.random.default_rng(22)
+    nq, nt = 1000, 300000
+    q = rng.integers(0, 256, (nq, 32), dtype=np.uint8)
+    t = rng.integers(0, 256, (nt, 32), dtype=np.uint8)
+    t[rng.integers(0, nt, 400)] = q[:400]
+    ms = [Matcher(0), Matcher(1)]
+    xs = [Exchange(ms[r], r, 2, nq) for r in range(2)]
+    bufs = [x.buffer() for x in xs]
+    for x in xs:
+        x.connect_ptrs(bufs)
+    want = ms[0].match_allpairs_best2(q, t)
+    half = nt // 2 + 37
+    outs = []
+    ins = []
+    for r in range(2):
+        dev = torch.device("cuda", r)
+        lo, hi = (0, half) if r == 0 else (half, nt)
+        ins.append((torch.from_numpy(q).to(dev), torch.from_numpy(t[lo:hi]).to(dev), torch.zeros((nq, 8), dtype=torch.uint8, device=dev), lo, hi))
+        torch.cuda.synchronize(dev)
+    for rep in range(3):
+        outs = []
+        for r in range(2):                                   # both launches are asynchronous: rank 0 waits on the device for rank 1
+            d_q, d_t, d_out, lo, hi = ins[r]
+            xs[r].allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), hi - lo, lo, 0.6, d_out.data_ptr())
+            outs.append((d_q, d_t, d_out))
+        for r in range(2):
+            ms[r].sync()
+        for r in range(2):
+            got = outs[r][2].cpu().numpy().view(BEST2_DTYPE).reshape(-1)
+            for f in ("idx", "d1", "d2"):
+                assert np.array_equal(got[f], want[f]), (rep, r, f)
+    for x in xs:
+        x.close()
+    for m in ms:
+        m.close()
