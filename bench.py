@@ -179,7 +179,7 @@ def int_pipe_peak_gpairs(sms, sm_mhz):
 
 def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d_desc, d_n, cap, w, h, pitch, barrier):
     from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
-    from motioncheck_ccm_slam_b200.matcher import (FramePack, Matcher, QUERY_DTYPE, Q_OBS, Q_VALID, WIN_PROJ_LASTFRAME,
+    from motioncheck_ccm_slam_b200.matcher import (Exchange, FramePack, Matcher, QUERY_DTYPE, Q_OBS, Q_VALID, WIN_PROJ_LASTFRAME,
                                                    WIN_PROJ_MAPPOINTS, frame_grid, packs_from_extractor_batch_device,
                                                    search_window_batch_device)
     out = {}
@@ -201,33 +201,61 @@ def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d
     d_acc = torch.zeros((nq,), dtype=torch.uint8, device=dev)
     torch.cuda.synchronize()
 
-    def ap_step():
+    def ap_step_nccl():
         m.match_allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), hi - lo, lo, d_part.data_ptr())
         if world > 1:
             with torch.cuda.stream(ms):
-                dist.all_gather_into_tensor(d_all, d_part)       # 8 KB per rank: the only data-path collective
+                dist.all_gather_into_tensor(d_all, d_part)       # 8 KB per rank
             m.match_allpairs_merge_device(d_all.data_ptr(), world, nq, 0.75, d_best.data_ptr(), d_acc.data_ptr())
         else:
             m.match_allpairs_merge_device(d_part.data_ptr(), 1, nq, 0.75, d_best.data_ptr(), d_acc.data_ptr())
 
+    # world > 1: the search, the exchange of the per-shard best-two records (stores into every peer's buffer over
+    # NVLink, release/acquire flags) and the merge are ONE kernel; the NCCL all_gather + merge pair is timed beside it
+    xch = None
+    if world > 1:
+        xch = Exchange(m, rank, world, nq)
+        hs = [None] * world
+        dist.all_gather_object(hs, xch.handle.tobytes())
+        xch.connect_ipc(np.frombuffer(b"".join(hs), np.uint8).reshape(world, 64))
+        d_best_x = torch.zeros_like(d_best); d_acc_x = torch.zeros_like(d_acc)
+        barrier()
+
+    def ap_step_fused():
+        xch.allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), hi - lo, lo, 0.75, d_best_x.data_ptr(), d_acc_x.data_ptr())
+
+    def time_ap(step):
+        for _ in range(3):
+            step()
+        m.sync(); barrier()
+        l0 = m.launch_count()
+        with torch.cuda.stream(ms):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(ksteps):
+                step()
+            e1.record()
+        m.sync(); barrier()
+        return e0.elapsed_time(e1) / ksteps, m.launch_count() - l0
+
     ksteps = max(3, min(args.steps, 10))
-    for _ in range(3):
-        ap_step()
-    m.sync(); barrier()
-    l0 = m.launch_count()
-    with torch.cuda.stream(ms):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(ksteps):
-            ap_step()
-        e1.record()
-    m.sync(); barrier()
-    ap_ms = e0.elapsed_time(e1) / ksteps
-    ap_launches = m.launch_count() - l0
+    ap_ms, ap_launches = time_ap(ap_step_nccl)
+    collective = "none (1 shard)"
+    if world > 1:
+        nccl_ms = ap_ms
+        ap_ms, ap_launches = time_ap(ap_step_fused)
+        same = bool(torch.equal(d_best, d_best_x) and torch.equal(d_acc, d_acc_x))
+        if not same:
+            raise SystemExit("fused exchange search differs from all_gather + merge on rank %d" % rank)
+        collective = ("fused in the search kernel: %d B per rank stored into every peer's buffer over NVLink + flags; "
+                      "nccl all_gather + merge kernel beside it: %.4f ms on rank 0 (identical result)" % (nq * 8, nccl_ms))
+        out["_ap_nccl_ms"] = nccl_ms
     out["_ap_ms"] = ap_ms
     out["allpairs"] = {"nq": nq, "nt_total": nt_total, "nt_per_gpu": hi - lo, "steps": ksteps,
-                       "collective": "nccl all_gather of %d B per rank + merge kernel" % (nq * 8) if world > 1 else "none (1 shard)",
+                       "collective": collective,
                        "l2": "target shard %.0f MB streamed once per step" % ((hi - lo) * 32 / 1e6)}
+    if world > 1:
+        out["allpairs"]["nccl_allgather_merge_ms_rank0"] = nccl_ms
 
     # ---- (2) tracking-side searches on the extractor's output: pack build + LastFrame(th 7) + MapPoints(th 1) ----
     R = min(d_frames.shape[0], 2)
@@ -322,6 +350,9 @@ def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d
     V.close()
     for p in packs:
         p.close()
+    if xch is not None:
+        barrier()                                         # no peer may still be storing into this rank's buffer
+        xch.close()
     m.close()
     return out
 

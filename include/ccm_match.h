@@ -251,6 +251,8 @@ int ccm_exchange_connect_ipc(ccm_exchange* x, const uint8_t* handles);
 /* same-process variant: device pointers of all ranks' buffers (ccm_exchange_buffer) in rank order; enables peer access */
 int ccm_exchange_connect_ptrs(ccm_exchange* x, void* const* peer_buffers);
 void* ccm_exchange_buffer(ccm_exchange* x);
+/* synchronises the device, closes the peer mappings and frees the buffer. Call it when no peer can still be inside a
+ * search on this context (a barrier of the caller's), and before or after ccm_matcher_destroy - it does not touch m. */
 void ccm_exchange_destroy(ccm_exchange* x);
 int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, const uint8_t* d_q, int nq, const uint8_t* d_targets,
                                              long long nt, uint32_t index_base, float nnratio, ccm_best2* d_out, uint8_t* d_accept);

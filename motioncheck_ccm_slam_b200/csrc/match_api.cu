@@ -793,7 +793,7 @@ int ccm_match_allpairs_best2_device(ccm_matcher* m, const uint8_t* d_q, int nq, 
 /* ---- peer-memory exchange context ------------------------------------------------------------------------- */
 struct ccm_exchange {
     ccm_matcher* m = nullptr;
-    int rank = 0, world = 1, nq_cap = 0, ctas_cap = 0;
+    int device = 0, rank = 0, world = 1, nq_cap = 0, ctas_cap = 0;
     size_t bytes = 0;
     unsigned char* buf = nullptr;                       // this rank's buffer
     unsigned char* peer[EX_MAX_WORLD] = {};             // every rank's buffer as seen from this device
@@ -809,7 +809,7 @@ int ccm_exchange_create(ccm_matcher* m, int rank, int world, int nq_cap, ccm_exc
     *out = nullptr;
     cudaSetDevice(m->device);
     ccm_exchange* x = new ccm_exchange();
-    x->m = m; x->rank = rank; x->world = world; x->nq_cap = nq_cap; x->ctas_cap = (nq_cap + EX_THREADS - 1) / EX_THREADS;
+    x->m = m; x->device = m->device; x->rank = rank; x->world = world; x->nq_cap = nq_cap; x->ctas_cap = (nq_cap + EX_THREADS - 1) / EX_THREADS;
     x->bytes = (size_t)2 * world * nq_cap * sizeof(Best2Dev) + (size_t)2 * world * x->ctas_cap * sizeof(uint32_t);
     cudaError_t e = cudaMalloc((void**)&x->buf, x->bytes);
     if (e == cudaSuccess) e = cudaMemset(x->buf, 0, x->bytes);               // flags start at epoch 0 = "nothing published"
@@ -861,8 +861,8 @@ void* ccm_exchange_buffer(ccm_exchange* x) { return x ? (void*)x->buf : nullptr;
 
 void ccm_exchange_destroy(ccm_exchange* x) {
     if (!x) return;
-    cudaSetDevice(x->m->device);
-    cudaStreamSynchronize(x->m->stream);
+    cudaSetDevice(x->device);
+    cudaDeviceSynchronize();                            // not the matcher's stream: the matcher may be gone already
     for (int r = 0; r < x->world; r++) if (x->ipc_opened[r]) cudaIpcCloseMemHandle(x->peer[r]);
     if (x->buf) cudaFree(x->buf);
     delete x;
