@@ -40,6 +40,7 @@ struct LevelDesc {
     const int* xofs; const short* xcoef;   // w entries, 2 coefs each
     const int* yofs; const short* ycoef;   // h entries
     const uint4* xgrp;                     // per group of 4 outputs, 2 x uint4 (k_resize_level); null: use the generic kernel
+    int resize_mlp;                        // 1: every 4-row strip taps rows s..s+5 with row j starting at s+j or s+j+1 (k_resize_level_mlp)
 };
 
 struct LevelTable {

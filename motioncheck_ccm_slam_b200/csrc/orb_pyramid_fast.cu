@@ -17,6 +17,16 @@
 // registers and reused when the next output row starts on it (at scale 1.2 an output row's lower source row is the next
 // row's upper one four times out of five), and the column's table entries are loaded once.
 #define RESIZE_ROWS 4
+// vertical pass of 4 outputs: v = (((b0 * h0) >> 16) + ((b1 * h1) >> 16) + 2) >> 2, v <= 255 (b0 + b1 = 2048, h <= 32640).
+// With b pre-shifted by 16 each product-shift is one IMAD.HI (the +2 and the second product ride on its addend); two
+// sums share a register (s0 + s1 << 16: both < 1024) for the final shift, and one PRMT gathers the four bytes.
+__device__ __forceinline__ uint32_t resize_vpack(uint32_t b0s, uint32_t b1s, const uint32_t (&h0)[4], const uint32_t (&h1)[4]) {
+    uint32_t t[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) t[k] = __umulhi(b1s, h1[k]) + (__umulhi(b0s, h0[k]) + 2u);
+    const uint32_t q01 = (t[0] + (t[1] << 16)) >> 2, q23 = (t[2] + (t[3] << 16)) >> 2;
+    return __byte_perm(q01, q23, 0x6420);
+}
 __device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ rp, bool in1, bool in2, uint32_t shift, uint32_t sel4,
                                             const uint32_t (&coef)[4], uint32_t (&r)[4]) {
     const uint32_t u0 = *reinterpret_cast<const uint32_t*>(rp);
@@ -24,7 +34,7 @@ __device__ __forceinline__ void resize_hrow(const uint8_t* __restrict__ rp, bool
     const uint32_t u2 = in2 ? *reinterpret_cast<const uint32_t*>(rp + 8) : 0u;
     const uint32_t lo = __funnelshift_r(u0, u1, shift), hi = __funnelshift_r(u1, u2, shift);
 #pragma unroll
-    for (int i = 0; i < 4; i++) r[i] = __dp2a_lo(coef[i], __byte_perm(lo, hi, (sel4 >> (8 * i)) & 0xffu), 0u) >> 4;
+    for (int i = 0; i < 4; i++) r[i] = __dp2a_lo(coef[i], __byte_perm(lo, hi, sel4 >> (8 * i)), 0u) >> 4;   // IDP2A reads result bytes 0,1 only: selector nibbles 2,3 are don't-care (all < 8)
 }
 
 __global__ void __launch_bounds__(256) k_resize_level(const __grid_constant__ LevelTable T, int lvl) {
@@ -64,15 +74,72 @@ __global__ void __launch_bounds__(256) k_resize_level(const __grid_constant__ Le
 #pragma unroll
                 for (int i = 0; i < 4; i++) h1[i] = h0[i];
             } else resize_hrow(src + (size_t)sy1 * pitch, in1, in2, ga.y, ga.z, coef, h1);
-            uint32_t packed = 0;
+            const uint32_t packed = resize_vpack(b0 << 16, b1 << 16, h0, h1);
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const uint32_t v = (((b0 * h0[i]) >> 16) + ((b1 * h1[i]) >> 16) + 2) >> 2;
-                packed |= (v & 255u) << (8 * i);
-                hc[i] = h1[i];
-            }
+            for (int i = 0; i < 4; i++) hc[i] = h1[i];
             cached = sy1;
             *reinterpret_cast<uint32_t*>(dst) = packed;       // pitch is a multiple of 32: in-bounds
+            dst += D.img_pitch;
+        }
+    }
+}
+
+// Loads-first variant for scale factors where RESIZE_ROWS output rows tap at most RESIZE_SRC_ROWS source rows (the host
+// checks the y table; 6 rows at ORB-SLAM's 1.2). k_resize_level interleaves each source row's loads with its arithmetic,
+// so a thread has 3-6 loads in flight and the kernel waits on HBM/L2 latency (ncu: long-scoreboard 7.4 per issue at IPC
+// 2.0); here the strip's RESIZE_SRC_ROWS x 3 words are all requested before the first is used.
+#define RESIZE_SRC_ROWS 6
+__global__ void __launch_bounds__(256) k_resize_level_mlp(const __grid_constant__ LevelTable T, int lvl) {
+    const LevelDesc& D = T.l[lvl];
+    const LevelDesc& S = T.l[lvl - 1];
+    const int f = blockIdx.z;
+    const int g = blockIdx.x * 32 + threadIdx.x, x4 = g * 4;
+    const int y0 = (blockIdx.y * 8 + threadIdx.y) * RESIZE_ROWS;
+    pdl_launch();
+    if (y0 >= D.h || x4 >= D.w) { pdl_wait(); return; }
+    const uint4 ga = __ldg(D.xgrp + 2 * g), gc = __ldg(D.xgrp + 2 * g + 1);
+    const int base = (int)ga.x, wlim = S.w;
+    const bool in1 = base + 4 < wlim, in2 = base + 8 < wlim;
+    const uint32_t coef[4] = {gc.x, gc.y, gc.z, gc.w};
+    const int pitch = S.img_pitch, last = S.h - 1, ny = min(RESIZE_ROWS, D.h - y0);
+    int off[RESIZE_ROWS]; uint32_t bb[RESIZE_ROWS];
+    const int s_first = __ldg(D.yofs + y0);
+#pragma unroll
+    for (int j = 0; j < RESIZE_ROWS; j++) {
+        const int y = min(y0 + j, D.h - 1);
+        off[j] = __ldg(D.yofs + y) - s_first;                                          // j or j + 1 ... checked on the host: off[j] + 1 < RESIZE_SRC_ROWS
+        bb[j] = __ldg(reinterpret_cast<const uint32_t*>(D.ycoef) + y);                 // b0 | b1 << 16
+    }
+    const uint8_t* src = S.img + (size_t)f * S.img_stride + base;
+    uint8_t* dst = D.img + (size_t)f * D.img_stride + (size_t)y0 * D.img_pitch + x4;
+    pdl_wait();                                               // level lvl-1 is complete
+    uint32_t u[RESIZE_SRC_ROWS][3];
+#pragma unroll
+    for (int k = 0; k < RESIZE_SRC_ROWS; k++) {
+        const uint8_t* rp = src + (size_t)min(s_first + k, last) * pitch;
+        u[k][0] = *reinterpret_cast<const uint32_t*>(rp);
+        u[k][1] = in1 ? *reinterpret_cast<const uint32_t*>(rp + 4) : 0u;
+        u[k][2] = in2 ? *reinterpret_cast<const uint32_t*>(rp + 8) : 0u;
+    }
+    uint32_t H[RESIZE_SRC_ROWS][4];
+#pragma unroll
+    for (int k = 0; k < RESIZE_SRC_ROWS; k++) {
+        const uint32_t lo = __funnelshift_r(u[k][0], u[k][1], ga.y), hi = __funnelshift_r(u[k][1], u[k][2], ga.y);
+#pragma unroll
+        for (int i = 0; i < 4; i++) H[k][i] = __dp2a_lo(coef[i], __byte_perm(lo, hi, ga.z >> (8 * i)), 0u) >> 4;
+    }
+#pragma unroll
+    for (int j = 0; j < RESIZE_ROWS; j++) {
+        if (j < ny) {
+            // row j starts at source row s_first + off[j], off[j] in [j, j + 2) for scale factors below 4/3: a warp-uniform select
+            uint32_t h0[4], h1[4];
+            const bool up = off[j] != j;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                h0[i] = up ? H[j + 1][i] : H[j][i];
+                h1[i] = up ? H[min(j + 2, RESIZE_SRC_ROWS - 1)][i] : H[j + 1][i];
+            }
+            *reinterpret_cast<uint32_t*>(dst) = resize_vpack(bb[j] << 16, bb[j] & 0xffff0000u, h0, h1);
             dst += D.img_pitch;
         }
     }
@@ -105,6 +172,124 @@ __global__ void __launch_bounds__(256) k_resize_level_generic(const __grid_const
         packed |= (uint32_t)(v & 255) << (8 * i);
     }
     *reinterpret_cast<uint32_t*>(dst + (size_t)y * D.img_pitch + x4) = packed;   // pitch is a multiple of 32: in-bounds
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1f: the whole pyramid chain (levels 1..L-1) of one image tile in ONE launch. ComputePyramid (:1280-1304) resizes level
+// l from level l-1, so the chain is sequential per pixel neighbourhood but independent between tiles: a CTA owns one
+// tile of every level (a partition of each level, x bounds multiples of 4), keeps the previous level's rectangle in
+// shared memory (two ping-pong buffers), computes the next level's rectangle from it with the same fixed-point taps
+// as k_resize_level (same group table, same instructions: bit-identical, pad bytes included) and stores the words it
+// owns to HBM. A level's rectangle = what the tile owns U what the next level's rectangle reads (host table
+// pyr_tile_rects, orb_api.cu), so tiles recompute a halo (about 25 % of the pixels at 4 x 8 tiles of 752 x 480)
+// instead of waiting for each other. Replaces 7 dependent launches whose small levels are launch-latency bound.
+// ---------------------------------------------------------------------------------------------
+struct PyrRect { short nx0, nx1, ny0, ny1, ox0, ox1, oy0, oy1; };    // computed rectangle, owned rectangle (x multiples of 4)
+#define PYR_THREADS 256
+#define PYR_PAD 8                                                    // bytes a group's three word loads may run past the rectangle
+
+__device__ __forceinline__ void pyr_hrow(const uint8_t* rp, uint32_t shift, uint32_t sel4, const uint32_t (&coef)[4], uint32_t (&r)[4]) {
+    const uint32_t u0 = *reinterpret_cast<const uint32_t*>(rp);
+    const uint32_t u1 = *reinterpret_cast<const uint32_t*>(rp + 4);
+    const uint32_t u2 = *reinterpret_cast<const uint32_t*>(rp + 8);
+    const uint32_t lo = __funnelshift_r(u0, u1, shift), hi = __funnelshift_r(u1, u2, shift);
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = __dp2a_lo(coef[i], __byte_perm(lo, hi, sel4 >> (8 * i)), 0u) >> 4;   // IDP2A reads result bytes 0,1 only: selector nibbles 2,3 are don't-care (all < 8)
+}
+
+#ifndef PYR_ROWS
+#define PYR_ROWS 2                                                   // output rows per work item (k_resize_level walks 4; here parallelism matters more)
+#endif
+#ifndef PYR_MIN_CTAS
+#define PYR_MIN_CTAS 5
+#endif
+__global__ void __launch_bounds__(PYR_THREADS, PYR_MIN_CTAS) k_pyramid_fused(const __grid_constant__ LevelTable T, const PyrRect* rects, int buf_a_bytes,
+                                                                              int buf_b_bytes, int xg_cap) {
+    extern __shared__ __align__(16) uint8_t pyr_smem[];
+    __shared__ PyrRect R[CCM_MAX_LEVELS];
+    const int tile = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, L = T.nlevels;
+    uint4* xg = reinterpret_cast<uint4*>(pyr_smem + buf_a_bytes + buf_b_bytes);       // group-table slices of levels 1..L-1, back to back
+    uint2* yt = reinterpret_cast<uint2*>(xg + xg_cap);                                 // {yofs, b0 | b1 << 16} per computed row, back to back
+    pdl_launch();
+    if (tid < L) R[tid] = rects[tile * CCM_MAX_LEVELS + tid];         // host tables: not produced by a predecessor
+    __syncthreads();
+    {
+        int xb = 0, yb = 0;
+        for (int l = 1; l < L; l++) {
+            const PyrRect d = R[l];
+            const LevelDesc& D = T.l[l];
+            const int nx = max(0, (d.nx1 - d.nx0) >> 1), ny = max(0, d.ny1 - d.ny0);   // 2 uint4 per group
+            for (int i = tid; i < nx; i += PYR_THREADS) xg[xb + i] = __ldg(D.xgrp + 2 * (d.nx0 >> 2) + i);
+            for (int i = tid; i < ny; i += PYR_THREADS)
+                yt[yb + i] = make_uint2((uint32_t)__ldg(D.yofs + d.ny0 + i), __ldg(reinterpret_cast<const uint32_t*>(D.ycoef) + d.ny0 + i));
+            xb += nx; yb += ny;
+        }
+    }
+    pdl_wait();
+    {   // level 0 rectangle, 32-bit words (rows are 4-byte aligned, as k_resize_level assumes)
+        const PyrRect r = R[0];
+        const int words = (r.nx1 - r.nx0) >> 2, rows = r.ny1 - r.ny0, sp = (r.nx1 - r.nx0) + PYR_PAD;
+        if (words > 0 && rows > 0) {
+            const uint8_t* src = T.l[0].img + (size_t)f * T.l[0].img_stride + (size_t)r.ny0 * T.l[0].img_pitch + r.nx0;
+            const int pitch = T.l[0].img_pitch;
+            for (int i = tid; i < words * rows; i += PYR_THREADS) {
+                const int y = i / words, x = i - y * words;
+                *reinterpret_cast<uint32_t*>(pyr_smem + y * sp + 4 * x) = *reinterpret_cast<const uint32_t*>(src + (size_t)y * pitch + 4 * x);
+            }
+        }
+    }
+    __syncthreads();
+    int xb = 0, yb = 0;
+    for (int l = 1; l < L; l++) {
+        const LevelDesc& D = T.l[l];
+        const PyrRect s = R[l - 1], d = R[l];
+        const int gx = (d.nx1 - d.nx0) >> 2, ny = d.ny1 - d.ny0;
+        if (gx > 0 && ny > 0) {
+            const int sp = (s.nx1 - s.nx0) + PYR_PAD, dp = (d.nx1 - d.nx0) + PYR_PAD;
+            const uint8_t* sb = pyr_smem + ((l & 1) ? 0 : buf_a_bytes);      // level l-1: even levels in buffer A
+            uint8_t* db = pyr_smem + ((l & 1) ? buf_a_bytes : 0);
+            const int strips = (ny + PYR_ROWS - 1) / PYR_ROWS, last = T.l[l - 1].h - 1;
+            uint8_t* gdst = D.img + (size_t)f * D.img_stride;
+            for (int i = tid; i < gx * strips; i += PYR_THREADS) {
+                const int st = i / gx, gl = i - st * gx;
+                const int x4 = d.nx0 + 4 * gl;
+                const uint4 ga = xg[xb + 2 * gl], gc = xg[xb + 2 * gl + 1];
+                const uint32_t coef[4] = {gc.x, gc.y, gc.z, gc.w};
+                const uint8_t* scol = sb + ((int)ga.x - s.nx0);
+                const bool own_x = x4 >= d.ox0 && x4 < d.ox1;
+                const int y0 = d.ny0 + st * PYR_ROWS, rows = min(PYR_ROWS, d.ny1 - y0);
+                int cached = -1;
+                uint32_t hc[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+                for (int j = 0; j < PYR_ROWS; j++) {
+                    if (j < rows) {
+                        const int y = y0 + j;
+                        const uint2 ye = yt[yb + (y - d.ny0)];
+                        const int sy0 = (int)ye.x, sy1 = min(sy0 + 1, last);
+                        const uint32_t b0s = ye.y << 16, b1s = ye.y & 0xffff0000u;
+                        uint32_t h0[4], h1[4];
+                        if (sy0 == cached) {
+#pragma unroll
+                            for (int k = 0; k < 4; k++) h0[k] = hc[k];
+                        } else pyr_hrow(scol + (sy0 - s.ny0) * sp, ga.y, ga.z, coef, h0);
+                        if (sy1 == sy0) {
+#pragma unroll
+                            for (int k = 0; k < 4; k++) h1[k] = h0[k];
+                        } else pyr_hrow(scol + (sy1 - s.ny0) * sp, ga.y, ga.z, coef, h1);
+                        const uint32_t packed = resize_vpack(b0s, b1s, h0, h1);
+#pragma unroll
+                        for (int k = 0; k < 4; k++) hc[k] = h1[k];
+                        cached = sy1;
+                        *reinterpret_cast<uint32_t*>(db + (y - d.ny0) * dp + 4 * gl) = packed;
+                        if (own_x && y >= d.oy0 && y < d.oy1)
+                            *reinterpret_cast<uint32_t*>(gdst + (size_t)y * D.img_pitch + x4) = packed;   // pitch is a multiple of 32: in-bounds
+                    }
+                }
+            }
+        }
+        xb += max(0, (d.nx1 - d.nx0) >> 1); yb += max(0, ny);
+        __syncthreads();
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
