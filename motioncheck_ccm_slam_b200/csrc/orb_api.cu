@@ -43,8 +43,6 @@ struct ccm_orb {
     int fast_ts = 0;                                   // tile row stride of the TMA variant (48 / 64 / 80), 0 = TMA unavailable
     FastTma tmaps = {};
     void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
-    // fused pyramid chain (k_pyramid_fused): per-tile rectangles of every level, ping-pong buffer sizes; 0 tiles = per-level launches
-    PyrRect* d_pyr_rects = nullptr; int pyr_tiles = 0, pyr_buf_a = 0, pyr_buf_b = 0, pyr_xg_cap = 0; size_t pyr_smem = 0;
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
     ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
@@ -144,55 +142,6 @@ static bool resize_group_table(int ssize, int dsize, const std::vector<int>& ofs
         out[2 * g + 1] = make_uint4(c[0], c[1], c[2], c[3]);
     }
     return true;
-}
-
-// k_pyramid_fused's table. Every level is partitioned into ntx x nty owned rectangles (x bounds multiples of 4, the last
-// one running to the padded row end like k_resize_level's last word). A tile's computed rectangle of level l is its owned
-// rectangle united with the source rows / columns the computed rectangle of level l+1 taps (first tap's aligned word to
-// last tap), rounded out to whole 4-pixel groups; level 0 is only read. Returns the two ping-pong buffer sizes.
-static void pyr_tile_rects(const LevelTable& T, const std::vector<int>* xofs, const std::vector<int>* yofs, int ntx, int nty,
-                           std::vector<PyrRect>& out, int& buf_a, int& buf_b, int& xg_cap, int& y_cap) {
-    const int L = T.nlevels;
-    auto bound = [](int n, int k, int i, int al, int nmax) {
-        if (i >= k) return nmax;
-        const int b = (int)std::lround((double)i * n / k);
-        return std::min(nmax, (b + al - 1) / al * al);
-    };
-    out.assign((size_t)ntx * nty * CCM_MAX_LEVELS, PyrRect{0, 0, 0, 0, 0, 0, 0, 0});
-    buf_a = buf_b = 16; xg_cap = y_cap = 0;
-    for (int iy = 0; iy < nty; iy++)
-        for (int ix = 0; ix < ntx; ix++) {
-            PyrRect* R = &out[(size_t)(iy * ntx + ix) * CCM_MAX_LEVELS];
-            int xg = 0, yr = 0;
-            for (int l = L - 1; l >= 0; l--) {
-                const int w = T.l[l].w, h = T.l[l].h, w4 = (w + 3) / 4 * 4;
-                PyrRect r;
-                r.ox0 = (short)bound(w, ntx, ix, 4, w4); r.ox1 = (short)bound(w, ntx, ix + 1, 4, w4);
-                r.oy0 = (short)bound(h, nty, iy, 1, h);  r.oy1 = (short)bound(h, nty, iy + 1, 1, h);
-                int x0 = r.ox0, x1 = r.ox1, y0 = r.oy0, y1 = r.oy1;
-                if (l == 0 || x1 <= x0 || y1 <= y0) { x0 = x1 = y0 = y1 = 0; r.ox0 = r.ox1 = r.oy0 = r.oy1 = 0; }
-                if (l + 1 < L) {
-                    const PyrRect& u = R[l + 1];
-                    if (u.nx1 > u.nx0 && u.ny1 > u.ny0) {
-                        const std::vector<int>& xo = xofs[l + 1]; const std::vector<int>& yo = yofs[l + 1];
-                        const int wu = T.l[l + 1].w;
-                        const int sx0 = xo[std::min((int)u.nx0, wu - 1)] & ~3;
-                        const int sx1 = std::min(xo[std::min((int)u.nx1, wu) - 1] + 2, w);
-                        const int sy0 = yo[u.ny0], sy1 = std::min(yo[u.ny1 - 1] + 2, h);
-                        if (x1 <= x0) { x0 = sx0; x1 = sx1; y0 = sy0; y1 = sy1; }
-                        else { x0 = std::min(x0, sx0); x1 = std::max(x1, sx1); y0 = std::min(y0, sy0); y1 = std::max(y1, sy1); }
-                    }
-                }
-                x1 = std::min((x1 + 3) / 4 * 4, w4);
-                r.nx0 = (short)x0; r.nx1 = (short)x1; r.ny0 = (short)y0; r.ny1 = (short)y1;
-                R[l] = r;
-                const int bytes = ((x1 - x0) + PYR_PAD) * (y1 - y0) + 16;
-                if (l & 1) buf_b = std::max(buf_b, bytes); else buf_a = std::max(buf_a, bytes);
-                if (l > 0) { xg += (x1 - x0) / 2; yr += y1 - y0; }
-            }
-            xg_cap = std::max(xg_cap, xg); y_cap = std::max(y_cap, yr);
-        }
-    buf_a = (buf_a + 15) / 16 * 16; buf_b = (buf_b + 15) / 16 * 16;
 }
 
 // ---- TMA descriptors for k_fast_cells<TS, true> ----
@@ -327,8 +276,6 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     h->qt_smem = (size_t)cap * 60 + 32 * sizeof(int) + (size_t)h->qt_ccap * 6;
     CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
 
-    std::vector<int> xofs_h[CCM_MAX_LEVELS], yofs_h[CCM_MAX_LEVELS];
-    bool all_grouped = true;
     for (int l = 0; l < L; l++) {
         LevelDesc& D = T.l[l];
         int rc;
@@ -355,8 +302,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
                 if ((rc = dev_alloc(h, &dg, grp.size()))) return rc;
                 CK(cudaMemcpy(dg, grp.data(), grp.size() * sizeof(uint4), cudaMemcpyHostToDevice));
                 D.xgrp = dg;
-            } else all_grouped = false;
-            xofs_h[l] = xo; yofs_h[l] = yo;
+            }
             D.resize_mlp = D.xgrp != nullptr && !std::getenv("CCM_ORB_NO_RESIZE_MLP");
             for (int y0 = 0; y0 < D.h && D.resize_mlp; y0 += RESIZE_ROWS)
                 for (int j = 0; j < RESIZE_ROWS && y0 + j < D.h; j++) {
@@ -366,22 +312,6 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         }
     }
     int rc;
-    // fused pyramid chain: 4 x 8 tiles per frame unless the image is small (a tile of the last level at least 16 x 8 pixels)
-    h->pyr_tiles = 0;
-    if (L > 1 && all_grouped && std::getenv("CCM_ORB_FUSED_PYRAMID")) {      // measured slower than the per-level launches: opt-in
-        int ntx = std::max(1, std::min(4, T.l[L - 1].w / 16)), nty = std::max(1, std::min(8, T.l[L - 1].h / 8));
-        if (const char* e = std::getenv("CCM_ORB_PYR_TILES")) { int a = 0, b = 0; if (std::sscanf(e, "%dx%d", &a, &b) == 2 && a > 0 && b > 0 && a <= 64 && b <= 64) { ntx = a; nty = b; } }   // tuning knob
-        std::vector<PyrRect> rects; int ba, bb, xc, yc;
-        pyr_tile_rects(T, xofs_h, yofs_h, ntx, nty, rects, ba, bb, xc, yc);
-        const size_t smem = (size_t)ba + bb + (size_t)xc * sizeof(uint4) + (size_t)yc * sizeof(uint2);
-        if (smem <= 200 * 1024) {
-            if ((rc = dev_alloc(h, &h->d_pyr_rects, rects.size()))) return rc;
-            CK(cudaMemcpy(h->d_pyr_rects, rects.data(), rects.size() * sizeof(PyrRect), cudaMemcpyHostToDevice));
-            h->pyr_tiles = ntx * nty; h->pyr_buf_a = ba; h->pyr_buf_b = bb; h->pyr_xg_cap = xc; h->pyr_smem = smem;
-            CK(cudaFuncSetAttribute(k_pyramid_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->pyr_smem));
-            CK(cudaFuncSetAttribute(k_pyramid_fused, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        }
-    }
     h->fast_smem = fast_smem_layout(max_cw, max_ch);
     CK((fast_set_carveout<FAST_TS, false>()));
     CK((fast_set_carveout<64, true>()));
@@ -471,10 +401,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
     {
         CK(cudaMemsetAsync(A.corner_count, 0, sizeof(int) * CCM_MAX_LEVELS * n, s));
         if (st) CK(cudaEventRecord(h->ev[0], s));
-        if (h->pyr_tiles) {
-            launch_pdl(k_pyramid_fused, dim3(h->pyr_tiles, n), dim3(PYR_THREADS), h->pyr_smem, s, T, (const PyrRect*)h->d_pyr_rects, h->pyr_buf_a, h->pyr_buf_b, h->pyr_xg_cap);
-            h->launches++;
-        } else for (int l = 1; l < T.nlevels; l++) {
+        for (int l = 1; l < T.nlevels; l++) {
             dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
             if (T.l[l].resize_mlp) launch_pdl(k_resize_level_mlp, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l);
             else if (T.l[l].xgrp) launch_pdl(k_resize_level, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l);

@@ -89,7 +89,10 @@ __global__ void __launch_bounds__(256) k_resize_level(const __grid_constant__ Le
 // so a thread has 3-6 loads in flight and the kernel waits on HBM/L2 latency (ncu: long-scoreboard 7.4 per issue at IPC
 // 2.0); here the strip's RESIZE_SRC_ROWS x 3 words are all requested before the first is used.
 #define RESIZE_SRC_ROWS 6
-__global__ void __launch_bounds__(256) k_resize_level_mlp(const __grid_constant__ LevelTable T, int lvl) {
+#ifndef RESIZE_MLP_CTAS
+#define RESIZE_MLP_CTAS 4
+#endif
+__global__ void __launch_bounds__(256, RESIZE_MLP_CTAS) k_resize_level_mlp(const __grid_constant__ LevelTable T, int lvl) {
     const LevelDesc& D = T.l[lvl];
     const LevelDesc& S = T.l[lvl - 1];
     const int f = blockIdx.z;
@@ -131,15 +134,11 @@ __global__ void __launch_bounds__(256) k_resize_level_mlp(const __grid_constant_
 #pragma unroll
     for (int j = 0; j < RESIZE_ROWS; j++) {
         if (j < ny) {
-            // row j starts at source row s_first + off[j], off[j] in [j, j + 2) for scale factors below 4/3: a warp-uniform select
-            uint32_t h0[4], h1[4];
-            const bool up = off[j] != j;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                h0[i] = up ? H[j + 1][i] : H[j][i];
-                h1[i] = up ? H[min(j + 2, RESIZE_SRC_ROWS - 1)][i] : H[j + 1][i];
-            }
-            *reinterpret_cast<uint32_t*>(dst) = resize_vpack(bb[j] << 16, bb[j] & 0xffff0000u, h0, h1);
+            // row j starts at source row s_first + off[j], off[j] in [j, j + 2) for scale factors below 4/3: a warp-uniform branch
+            uint32_t packed;
+            if (off[j] != j) packed = resize_vpack(bb[j] << 16, bb[j] & 0xffff0000u, H[j + 1], H[j + 2 < RESIZE_SRC_ROWS ? j + 2 : RESIZE_SRC_ROWS - 1]);
+            else packed = resize_vpack(bb[j] << 16, bb[j] & 0xffff0000u, H[j], H[j + 1]);
+            *reinterpret_cast<uint32_t*>(dst) = packed;
             dst += D.img_pitch;
         }
     }
@@ -172,124 +171,6 @@ __global__ void __launch_bounds__(256) k_resize_level_generic(const __grid_const
         packed |= (uint32_t)(v & 255) << (8 * i);
     }
     *reinterpret_cast<uint32_t*>(dst + (size_t)y * D.img_pitch + x4) = packed;   // pitch is a multiple of 32: in-bounds
-}
-
-// ---------------------------------------------------------------------------------------------
-// K1f: the whole pyramid chain (levels 1..L-1) of one image tile in ONE launch. ComputePyramid (:1280-1304) resizes level
-// l from level l-1, so the chain is sequential per pixel neighbourhood but independent between tiles: a CTA owns one
-// tile of every level (a partition of each level, x bounds multiples of 4), keeps the previous level's rectangle in
-// shared memory (two ping-pong buffers), computes the next level's rectangle from it with the same fixed-point taps
-// as k_resize_level (same group table, same instructions: bit-identical, pad bytes included) and stores the words it
-// owns to HBM. A level's rectangle = what the tile owns U what the next level's rectangle reads (host table
-// pyr_tile_rects, orb_api.cu), so tiles recompute a halo (about 25 % of the pixels at 4 x 8 tiles of 752 x 480)
-// instead of waiting for each other. Replaces 7 dependent launches whose small levels are launch-latency bound.
-// ---------------------------------------------------------------------------------------------
-struct PyrRect { short nx0, nx1, ny0, ny1, ox0, ox1, oy0, oy1; };    // computed rectangle, owned rectangle (x multiples of 4)
-#define PYR_THREADS 256
-#define PYR_PAD 8                                                    // bytes a group's three word loads may run past the rectangle
-
-__device__ __forceinline__ void pyr_hrow(const uint8_t* rp, uint32_t shift, uint32_t sel4, const uint32_t (&coef)[4], uint32_t (&r)[4]) {
-    const uint32_t u0 = *reinterpret_cast<const uint32_t*>(rp);
-    const uint32_t u1 = *reinterpret_cast<const uint32_t*>(rp + 4);
-    const uint32_t u2 = *reinterpret_cast<const uint32_t*>(rp + 8);
-    const uint32_t lo = __funnelshift_r(u0, u1, shift), hi = __funnelshift_r(u1, u2, shift);
-#pragma unroll
-    for (int i = 0; i < 4; i++) r[i] = __dp2a_lo(coef[i], __byte_perm(lo, hi, sel4 >> (8 * i)), 0u) >> 4;   // IDP2A reads result bytes 0,1 only: selector nibbles 2,3 are don't-care (all < 8)
-}
-
-#ifndef PYR_ROWS
-#define PYR_ROWS 2                                                   // output rows per work item (k_resize_level walks 4; here parallelism matters more)
-#endif
-#ifndef PYR_MIN_CTAS
-#define PYR_MIN_CTAS 5
-#endif
-__global__ void __launch_bounds__(PYR_THREADS, PYR_MIN_CTAS) k_pyramid_fused(const __grid_constant__ LevelTable T, const PyrRect* rects, int buf_a_bytes,
-                                                                              int buf_b_bytes, int xg_cap) {
-    extern __shared__ __align__(16) uint8_t pyr_smem[];
-    __shared__ PyrRect R[CCM_MAX_LEVELS];
-    const int tile = blockIdx.x, f = blockIdx.y, tid = threadIdx.x, L = T.nlevels;
-    uint4* xg = reinterpret_cast<uint4*>(pyr_smem + buf_a_bytes + buf_b_bytes);       // group-table slices of levels 1..L-1, back to back
-    uint2* yt = reinterpret_cast<uint2*>(xg + xg_cap);                                 // {yofs, b0 | b1 << 16} per computed row, back to back
-    pdl_launch();
-    if (tid < L) R[tid] = rects[tile * CCM_MAX_LEVELS + tid];         // host tables: not produced by a predecessor
-    __syncthreads();
-    {
-        int xb = 0, yb = 0;
-        for (int l = 1; l < L; l++) {
-            const PyrRect d = R[l];
-            const LevelDesc& D = T.l[l];
-            const int nx = max(0, (d.nx1 - d.nx0) >> 1), ny = max(0, d.ny1 - d.ny0);   // 2 uint4 per group
-            for (int i = tid; i < nx; i += PYR_THREADS) xg[xb + i] = __ldg(D.xgrp + 2 * (d.nx0 >> 2) + i);
-            for (int i = tid; i < ny; i += PYR_THREADS)
-                yt[yb + i] = make_uint2((uint32_t)__ldg(D.yofs + d.ny0 + i), __ldg(reinterpret_cast<const uint32_t*>(D.ycoef) + d.ny0 + i));
-            xb += nx; yb += ny;
-        }
-    }
-    pdl_wait();
-    {   // level 0 rectangle, 32-bit words (rows are 4-byte aligned, as k_resize_level assumes)
-        const PyrRect r = R[0];
-        const int words = (r.nx1 - r.nx0) >> 2, rows = r.ny1 - r.ny0, sp = (r.nx1 - r.nx0) + PYR_PAD;
-        if (words > 0 && rows > 0) {
-            const uint8_t* src = T.l[0].img + (size_t)f * T.l[0].img_stride + (size_t)r.ny0 * T.l[0].img_pitch + r.nx0;
-            const int pitch = T.l[0].img_pitch;
-            for (int i = tid; i < words * rows; i += PYR_THREADS) {
-                const int y = i / words, x = i - y * words;
-                *reinterpret_cast<uint32_t*>(pyr_smem + y * sp + 4 * x) = *reinterpret_cast<const uint32_t*>(src + (size_t)y * pitch + 4 * x);
-            }
-        }
-    }
-    __syncthreads();
-    int xb = 0, yb = 0;
-    for (int l = 1; l < L; l++) {
-        const LevelDesc& D = T.l[l];
-        const PyrRect s = R[l - 1], d = R[l];
-        const int gx = (d.nx1 - d.nx0) >> 2, ny = d.ny1 - d.ny0;
-        if (gx > 0 && ny > 0) {
-            const int sp = (s.nx1 - s.nx0) + PYR_PAD, dp = (d.nx1 - d.nx0) + PYR_PAD;
-            const uint8_t* sb = pyr_smem + ((l & 1) ? 0 : buf_a_bytes);      // level l-1: even levels in buffer A
-            uint8_t* db = pyr_smem + ((l & 1) ? buf_a_bytes : 0);
-            const int strips = (ny + PYR_ROWS - 1) / PYR_ROWS, last = T.l[l - 1].h - 1;
-            uint8_t* gdst = D.img + (size_t)f * D.img_stride;
-            for (int i = tid; i < gx * strips; i += PYR_THREADS) {
-                const int st = i / gx, gl = i - st * gx;
-                const int x4 = d.nx0 + 4 * gl;
-                const uint4 ga = xg[xb + 2 * gl], gc = xg[xb + 2 * gl + 1];
-                const uint32_t coef[4] = {gc.x, gc.y, gc.z, gc.w};
-                const uint8_t* scol = sb + ((int)ga.x - s.nx0);
-                const bool own_x = x4 >= d.ox0 && x4 < d.ox1;
-                const int y0 = d.ny0 + st * PYR_ROWS, rows = min(PYR_ROWS, d.ny1 - y0);
-                int cached = -1;
-                uint32_t hc[4] = {0u, 0u, 0u, 0u};
-#pragma unroll
-                for (int j = 0; j < PYR_ROWS; j++) {
-                    if (j < rows) {
-                        const int y = y0 + j;
-                        const uint2 ye = yt[yb + (y - d.ny0)];
-                        const int sy0 = (int)ye.x, sy1 = min(sy0 + 1, last);
-                        const uint32_t b0s = ye.y << 16, b1s = ye.y & 0xffff0000u;
-                        uint32_t h0[4], h1[4];
-                        if (sy0 == cached) {
-#pragma unroll
-                            for (int k = 0; k < 4; k++) h0[k] = hc[k];
-                        } else pyr_hrow(scol + (sy0 - s.ny0) * sp, ga.y, ga.z, coef, h0);
-                        if (sy1 == sy0) {
-#pragma unroll
-                            for (int k = 0; k < 4; k++) h1[k] = h0[k];
-                        } else pyr_hrow(scol + (sy1 - s.ny0) * sp, ga.y, ga.z, coef, h1);
-                        const uint32_t packed = resize_vpack(b0s, b1s, h0, h1);
-#pragma unroll
-                        for (int k = 0; k < 4; k++) hc[k] = h1[k];
-                        cached = sy1;
-                        *reinterpret_cast<uint32_t*>(db + (y - d.ny0) * dp + 4 * gl) = packed;
-                        if (own_x && y >= d.oy0 && y < d.oy1)
-                            *reinterpret_cast<uint32_t*>(gdst + (size_t)y * D.img_pitch + x4) = packed;   // pitch is a multiple of 32: in-bounds
-                    }
-                }
-            }
-        }
-        xb += max(0, (d.nx1 - d.nx0) >> 1); yb += max(0, ny);
-        __syncthreads();
-    }
 }
 
 // ---------------------------------------------------------------------------------------------
