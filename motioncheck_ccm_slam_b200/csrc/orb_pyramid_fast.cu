@@ -411,7 +411,10 @@ __global__ void __launch_bounds__(NT, FAST_RESIDENT_THREADS / NT) k_fast_cells(c
                 r[12] = c[-3];         r[13] = c[S - 3];      r[14] = c[2 * S - 2];  r[15] = c[3 * S - 1];
                 uint32_t dark = 0, bright = 0;      // ring darker than v-t  /  brighter than v+t
 #pragma unroll
-                for (int k = 0; k < 16; k++) { dark |= (uint32_t)(r[k] < lo) << k; bright |= (uint32_t)(r[k] > hi) << k; }
+                for (int k = 0; k < 16; k++) {      // sign of the difference shifted in from the right: IADD + SHF per test; bit 15-k = ring pixel k
+                    dark = __funnelshift_l((uint32_t)(r[k] - lo), dark, 1);       // (the run test is circular: the reversed order is as good)
+                    bright = __funnelshift_l((uint32_t)(hi - r[k]), bright, 1);
+                }
                 is_corner = has_run9(dark) || has_run9(bright);
             }
             list_append(is_corner, (uint32_t)i, corn_s, ncorn_s);
