@@ -194,27 +194,25 @@ __device__ __forceinline__ bool has_run9(uint32_t m16) {
 }
 
 // cornerScore<16> (OpenCV fast_score.cpp): max over the 16 arcs of 9 ring pixels of min(d) and of min(-d), minus 1.
-// Written with min-only arc reductions over d and over nd = -d (materialised through an opaque asm so the negation
-// cannot be folded into a 3-input min/max): ptxas 12.9 -O1+ for sm_100a miscompiles max(max(x,-y),max(z,-w))
-// (VIMNMX3 with negated operands; reproduced on B200, see DESIGN.md "toolchain notes").
+// d and -d (|d| <= 255) travel as the two signed halves of one register, so each step of the arc reduction is one
+// VIMNMX.S16x2 / VIMNMX3.S16x2 for both polarities: min over 2, over 4, then min3(4-run, 4-run, 9th pixel) and a max3
+// over pairs of arcs - 56 packed min/max instead of 160 scalar ones. (The scalar form also had to keep -d behind an opaque
+// asm: ptxas 12.9 for sm_100a miscompiles max(max(x,-y),max(z,-w)) into a VIMNMX3 with negated operands, DESIGN.md
+// "toolchain notes"; nothing is negated inside a min/max here.)
 __device__ __forceinline__ int fast_score16(const int (&d)[16]) {
-    int nd[16];
+    uint32_t p[16], m2[16], m4[16], a9[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) { nd[k] = -d[k]; asm volatile("" : "+r"(nd[k])); }
-    int a2[16], b2[16];
+    for (int k = 0; k < 16; k++) p[k] = __byte_perm((uint32_t)d[k], (uint32_t)(-d[k]), 0x5410);   // lo = d, hi = -d
 #pragma unroll
-    for (int k = 0; k < 16; k++) { a2[k] = min(d[k], d[(k + 1) & 15]); b2[k] = min(nd[k], nd[(k + 1) & 15]); }
-    int a4[16], b4[16];
+    for (int k = 0; k < 16; k++) m2[k] = __vmins2(p[k], p[(k + 1) & 15]);
 #pragma unroll
-    for (int k = 0; k < 16; k++) { a4[k] = min(a2[k], a2[(k + 2) & 15]); b4[k] = min(b2[k], b2[(k + 2) & 15]); }
-    int best = -1000;
+    for (int k = 0; k < 16; k++) m4[k] = __vmins2(m2[k], m2[(k + 2) & 15]);
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        const int a9 = min(min(a4[k], a4[(k + 4) & 15]), d[(k + 8) & 15]);
-        const int b9 = min(min(b4[k], b4[(k + 4) & 15]), nd[(k + 8) & 15]);
-        best = max(best, max(a9, b9));
-    }
-    return best - 1;
+    for (int k = 0; k < 16; k++) a9[k] = __vimin3_s16x2(m4[k], m4[(k + 4) & 15], p[(k + 8) & 15]);
+    uint32_t best = __vmaxs2(a9[0], a9[1]);
+#pragma unroll
+    for (int k = 2; k < 16; k += 2) best = __vimax3_s16x2(best, a9[k], a9[k + 1]);
+    return max((int)(short)(best & 0xffffu), (int)(short)(best >> 16)) - 1;
 }
 
 // Work is staged through shared-memory lists so that the expensive steps only run on pixels that need them, with all
