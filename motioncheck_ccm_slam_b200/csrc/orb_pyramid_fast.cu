@@ -193,16 +193,20 @@ __device__ __forceinline__ bool has_run9(uint32_t m16) {
     return x != 0;
 }
 
-// cornerScore<16> (OpenCV fast_score.cpp): max over the 16 arcs of 9 ring pixels of min(d) and of min(-d), minus 1.
-// d and -d (|d| <= 255) travel as the two signed halves of one register, so each step of the arc reduction is one
-// VIMNMX.S16x2 / VIMNMX3.S16x2 for both polarities: min over 2, over 4, then min3(4-run, 4-run, 9th pixel) and a max3
-// over pairs of arcs - 56 packed min/max instead of 160 scalar ones. (The scalar form also had to keep -d behind an opaque
-// asm: ptxas 12.9 for sm_100a miscompiles max(max(x,-y),max(z,-w)) into a VIMNMX3 with negated operands, DESIGN.md
-// "toolchain notes"; nothing is negated inside a min/max here.)
-__device__ __forceinline__ int fast_score16(const int (&d)[16]) {
+// cornerScore<16> (OpenCV fast_score.cpp): max over the 16 arcs of 9 ring pixels of min(d) and of min(-d), minus 1, with
+// d = v - ring pixel. d + 256 and 256 - d (both in [1, 511]) travel as the two halves of one register - one IMAD per ring
+// pixel, r * 65535 + ((v + 256) * (1 - 65536) + (512 << 16)), no borrow between the halves - so each step of the arc
+// reduction is one VIMNMX.S16x2 / VIMNMX3.S16x2 for both polarities: min over 2, over 4, then min3(4-run, 4-run, 9th
+// pixel) and a max3 over pairs of arcs: 56 packed min/max instead of 160 scalar ones. (The scalar form also had to keep -d
+// behind an opaque asm: ptxas 12.9 for sm_100a miscompiles max(max(x,-y),max(z,-w)) into a VIMNMX3 with negated operands,
+// DESIGN.md "toolchain notes"; nothing is negated inside a min/max here.)
+// A pixel is a FAST-9 corner at threshold t exactly when this score is >= t (some arc has every |d| > t, same sign), so
+// the segment test and the score are one computation.
+__device__ __forceinline__ int fast_score16(int v, const uint32_t (&r)[16]) {
+    const uint32_t bias = (uint32_t)(v + 256) * 0xFFFF0001u + (512u << 16);
     uint32_t p[16], m2[16], m4[16], a9[16];
 #pragma unroll
-    for (int k = 0; k < 16; k++) p[k] = __byte_perm((uint32_t)d[k], (uint32_t)(-d[k]), 0x5410);   // lo = d, hi = -d
+    for (int k = 0; k < 16; k++) p[k] = r[k] * 65535u + bias;            // lo = d + 256, hi = 256 - d
 #pragma unroll
     for (int k = 0; k < 16; k++) m2[k] = __vmins2(p[k], p[(k + 1) & 15]);
 #pragma unroll
@@ -212,7 +216,7 @@ __device__ __forceinline__ int fast_score16(const int (&d)[16]) {
     uint32_t best = __vmaxs2(a9[0], a9[1]);
 #pragma unroll
     for (int k = 2; k < 16; k += 2) best = __vimax3_s16x2(best, a9[k], a9[k + 1]);
-    return max((int)(short)(best & 0xffffu), (int)(short)(best >> 16)) - 1;
+    return (int)max(best & 0xffffu, best >> 16) - 257;
 }
 
 // Work is staged through shared-memory lists so that the expensive steps only run on pixels that need them, with all
@@ -391,7 +395,7 @@ __global__ void __launch_bounds__(NT, FAST_RESIDENT_THREADS / NT) k_fast_cells(c
             }
         }
         __syncthreads();
-        // (C) full FAST-9/16 segment test on the candidates
+        // (C) FAST-9/16 on the candidates: the corner score decides (score >= threshold) and goes into the score map
         const int nc = n_cand;
         for (int base = 0; base < nc; base += NT) {
             const int j = base + tid;
@@ -401,38 +405,19 @@ __global__ void __launch_bounds__(NT, FAST_RESIDENT_THREADS / NT) k_fast_cells(c
                 i = cand[j];
                 const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
                 const uint8_t* c = tile + (py + 3) * TS + px + 3 + shift;
-                const int v = c[0], hi = v + threshold, lo = v - threshold;
-                int r[16];
+                uint32_t r[16];
                 r[0] = c[3 * S];       r[1] = c[3 * S + 1];   r[2] = c[2 * S + 2];   r[3] = c[S + 3];
                 r[4] = c[3];           r[5] = c[-S + 3];      r[6] = c[-2 * S + 2];  r[7] = c[-3 * S + 1];
                 r[8] = c[-3 * S];      r[9] = c[-3 * S - 1];  r[10] = c[-2 * S - 2]; r[11] = c[-S - 3];
                 r[12] = c[-3];         r[13] = c[S - 3];      r[14] = c[2 * S - 2];  r[15] = c[3 * S - 1];
-                uint32_t dark = 0, bright = 0;      // ring darker than v-t  /  brighter than v+t
-#pragma unroll
-                for (int k = 0; k < 16; k++) {      // sign of the difference shifted in from the right: IADD + SHF per test; bit 15-k = ring pixel k
-                    dark = __funnelshift_l((uint32_t)(r[k] - lo), dark, 1);       // (the run test is circular: the reversed order is as good)
-                    bright = __funnelshift_l((uint32_t)(hi - r[k]), bright, 1);
-                }
-                is_corner = has_run9(dark) || has_run9(bright);
+                const int sc = fast_score16((int)c[0], r);
+                is_corner = sc >= threshold;                  // threshold >= 1 (enforced at create): a corner's score is never 0
+                if (is_corner) score[(py + 1) * SS + px + 1] = (uint8_t)sc;
             }
             list_append(is_corner, (uint32_t)i, corn_s, ncorn_s);
         }
         __syncthreads();
-        // (D) cornerScore of the corners -> score map
         const int nk = n_corn;
-        for (int j = tid; j < nk; j += NT) {
-            const int i = corn[j];
-            const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-            const uint8_t* c = tile + (py + 3) * TS + px + 3 + shift;
-            const int v = c[0];
-            int d[16];
-            d[0] = v - c[3 * S];       d[1] = v - c[3 * S + 1];   d[2] = v - c[2 * S + 2];   d[3] = v - c[S + 3];
-            d[4] = v - c[3];           d[5] = v - c[-S + 3];      d[6] = v - c[-2 * S + 2];  d[7] = v - c[-3 * S + 1];
-            d[8] = v - c[-3 * S];      d[9] = v - c[-3 * S - 1];  d[10] = v - c[-2 * S - 2]; d[11] = v - c[-S - 3];
-            d[12] = v - c[-3];         d[13] = v - c[S - 3];      d[14] = v - c[2 * S - 2];  d[15] = v - c[3 * S - 1];
-            score[(py + 1) * SS + px + 1] = (uint8_t)fast_score16(d);   // >= threshold > 0 (threshold >= 1 enforced at create)
-        }
-        __syncthreads();
         // (E) non-maximum suppression over the corners, append survivors
         int found = 0;
         for (int base = 0; base < nk; base += NT) {     // uniform trip count: ballots below need whole warps
