@@ -34,6 +34,7 @@ struct LevelDesc {
     int corner_off;          // into the per-frame corner array (u32 units)
     int corner_cap;
     int kp_off;              // into the per-frame level-keypoint slot list
+    int desc_block_base;     // first CTA of this level in k_orient_describe's grid (8 slots per CTA, a CTA never spans two levels)
     float scale;             // mvScaleFactor[l]
     float kp_size;           // (float)(int)(31*mvScaleFactor[l]), :1006
     // resize tables for (l-1) -> l, device pointers (null for level 0)
@@ -48,6 +49,7 @@ struct LevelTable {
     int nlevels;
     int total_cells;
     int total_blur_tiles;
+    int total_desc_blocks;
     int corners_per_frame;   // u32 units
     int kps_per_frame;       // slot-list length per frame (sum of node_cap)
     int ini_th, min_th;

@@ -42,6 +42,7 @@ struct ccm_orb {
     int fast_nt = 128, fast_nt_tma = 128;              // CTA sizes picked for the two cell tables
     int fast_ts = 0;                                   // tile row stride of the TMA variant (48 / 64 / 80), 0 = TMA unavailable
     FastTma tmaps = {};
+    float4* d_pat = nullptr;                           // k_orient_describe's test pattern table
     void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
@@ -217,7 +218,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     std::memset(&T, 0, sizeof(T));
     const int L = h->cfg.nlevels, B = h->cfg.max_batch;
     T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
-    int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0;
+    int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0, desc_blocks = 0;
     std::vector<uint4> cell_info, cell_info_tma;
     int max_cw = 1, max_ch = 1;
     for (int l = 0; l < L; l++) {
@@ -262,13 +263,14 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         D.corner_cap = std::max(cc, 1); D.corner_off = corners; corners += align_up(D.corner_cap, 4);
         if (D.corner_cap > 0x7FFFF) { h->err = "image too large (corner capacity per level exceeds 2^19)"; return CCM_E_BADARG; }
         D.kp_off = kps; kps += D.node_cap;
+        D.desc_block_base = desc_blocks; desc_blocks += (D.node_cap + 7) / 8;
         D.scale = h->sf[l];
         D.kp_size = (float)(int)(31 * h->sf[l]);
         D.img_pitch = D.blur_pitch = align_up(D.w, 32);
         D.img_stride = D.blur_stride = (size_t)D.img_pitch * D.h;
     }
     if (max_node_cap > 2048) { h->err = "nfeatures too large: more than 2045 features on one level"; return CCM_E_BADARG; }
-    T.total_cells = cells; T.total_blur_tiles = blur_tiles; T.corners_per_frame = corners; T.kps_per_frame = kps;
+    T.total_cells = cells; T.total_blur_tiles = blur_tiles; T.total_desc_blocks = desc_blocks; T.corners_per_frame = corners; T.kps_per_frame = kps;
     h->max_kps = kps;
     int cap = 32; while (cap < max_node_cap) cap <<= 1;
     h->qt_cap = cap;
@@ -312,6 +314,12 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         }
     }
     int rc;
+    {
+        float4 pt[256];
+        orb_pattern_table(pt);
+        if ((rc = dev_alloc(h, &h->d_pat, 256))) return rc;
+        CK(cudaMemcpy(h->d_pat, pt, sizeof(pt), cudaMemcpyHostToDevice));
+    }
     h->fast_smem = fast_smem_layout(max_cw, max_ch);
     CK((fast_set_carveout<FAST_TS, false>()));
     CK((fast_set_carveout<64, true>()));
@@ -441,7 +449,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
             CK(cudaStreamWaitEvent(s, LN.join, 0));
         }
         if (st) CK(cudaEventRecord(h->ev[4], s));
-        k_orient_describe<<<dim3((T.kps_per_frame + 7) / 8, n), 256, 0, s>>>(T, A.level_kps, A.level_kp_count,
+        k_orient_describe<<<dim3(T.total_desc_blocks, n), 256, 0, s>>>(T, h->d_pat, A.level_kps, A.level_kp_count,
                                                                             (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
         h->launches++;
         if (st) { CK(cudaEventRecord(h->ev[5], s)); h->stage_pending = true; }

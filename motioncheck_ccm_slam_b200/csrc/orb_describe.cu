@@ -111,16 +111,18 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
 //   Output: ccm_keypoint with pt scaled by mvScaleFactor[level] for level != 0 (:1268-1274), descriptor as two
 //   16-byte stores per keypoint.
 // ---------------------------------------------------------------------------------------------
-#ifndef DESC_LVL_PARALLEL
-#define DESC_LVL_PARALLEL 0          // measured slower (0.118 vs 0.109 ms): the divergent constant-bank reads serialise
-#endif
 #ifndef DESC_SINCOS
 #define DESC_SINCOS 1
 #endif
-struct BriefPattern { signed char v[256][4]; };
-__constant__ BriefPattern c_pattern_init = {{
+// rBRIEF test pattern (bit_pattern_31_, ORBextractor.cpp:320-577) as it sits in the source; the kernel reads the float4 table
+// orb_pattern_table() builds from it once per handle: entry [k][lane] = (x1, y1, x2, y2) of test 8 * lane + k
+static const signed char h_brief_pattern[256][4] = {
 #include "brief_pattern.inc"
-}};
+};
+static void orb_pattern_table(float4 (&out)[256]) {
+    for (int t = 0; t < 256; t++)
+        out[(t & 7) * 32 + (t >> 3)] = make_float4((float)h_brief_pattern[t][0], (float)h_brief_pattern[t][1], (float)h_brief_pattern[t][2], (float)h_brief_pattern[t][3]);
+}
 // umax[v] of the 15-px orientation patch, ORBextractor.cpp:623-638: {15,15,15,15,14,14,14,13,13,12,11,10,9,8,6,3}
 __host__ __device__ constexpr int umax_of(int v) {
     return v <= 3 ? 15 : v <= 6 ? 14 : v <= 8 ? 13 : v == 9 ? 12 : v == 10 ? 11 : v == 11 ? 10 : v == 12 ? 9 : v == 13 ? 8 : v == 14 ? 6 : 3;
@@ -146,6 +148,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ LevelTable T,
+                                                         const float4* __restrict__ pat_table,       // [8][32], see below (host-built)
                                                          const uint32_t* __restrict__ level_kps,     // [frames][kps_per_frame]
                                                          const int* __restrict__ level_kp_count,     // [frames][CCM_MAX_LEVELS]
                                                          ccm_keypoint_dev* __restrict__ out_kp,      // [frames][capacity]
@@ -153,55 +156,46 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
                                                          int* __restrict__ out_count,                // [frames]
                                                          int capacity) {
     __shared__ float4 pat[8][32];     // pat[k][lane] = (x1, y1, x2, y2) of test 8*lane+k as floats: one LDS.128, no conversions in the loop
+    __shared__ int s_cnt[CCM_MAX_LEVELS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    {
-        const signed char* p = c_pattern_init.v[tid];
-        pat[tid & 7][tid >> 3] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
-    }
-    __syncthreads();
-
     const int f = blockIdx.y;
-    const int slot = blockIdx.x * 8 + warp;
-    if (slot >= T.kps_per_frame) return;
-#if DESC_LVL_PARALLEL
-    // level of this slot and the number of keypoints in front of it, lane l looking at level l: the level is the last one
-    // whose slot range starts at or before `slot`, `before` the keypoints of the lower levels, `total` all of them
-    const int my_off = lane < T.nlevels ? T.l[lane].kp_off : 0x7fffffff;
-    const int my_cnt = lane < T.nlevels ? level_kp_count[f * CCM_MAX_LEVELS + lane] : 0;
-    const int lvl = __popc(__ballot_sync(0xffffffffu, slot >= my_off)) - 1;
-    const int total = __reduce_add_sync(0xffffffffu, my_cnt);
-    const int before = __reduce_add_sync(0xffffffffu, lane < lvl ? my_cnt : 0);
-    const int cnt_lvl = __shfl_sync(0xffffffffu, my_cnt, lvl);
-#else
+    reinterpret_cast<float4*>(&pat[0][0])[tid] = __ldg(pat_table + tid);
+    if (tid < CCM_MAX_LEVELS) s_cnt[tid] = tid < T.nlevels ? level_kp_count[f * CCM_MAX_LEVELS + tid] : 0;
+    // A CTA's 8 slots belong to one level (host grid: desc_block_base), so the level, its image bases and pitches are
+    // CTA-uniform: they live in uniform registers and every pixel load below is [uniform base + 32-bit offset].
     int lvl = 0;
-    while (lvl + 1 < T.nlevels && slot >= T.l[lvl + 1].kp_off) lvl++;
-    const int* cnt = level_kp_count + f * CCM_MAX_LEVELS;
-    int before = 0, total = 0;
-    for (int l = 0; l < T.nlevels; l++) { const int c = cnt[l]; if (l < lvl) before += c; total += c; }
-    const int cnt_lvl = cnt[lvl];
-#endif
+#pragma unroll 1
+    while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].desc_block_base) lvl++;
     const LevelDesc& L = T.l[lvl];
-    const int pos = slot - L.kp_off;
-    if (slot == 0 && lane == 0) out_count[f] = total;
+    __syncthreads();
+    // keypoints of the lower levels come first in the output (:1239-1276): lane l holds level l's count
+    const int c = lane < CCM_MAX_LEVELS ? s_cnt[lane] : 0;
+    const int total = __reduce_add_sync(0xffffffffu, c);
+    const int before = __reduce_add_sync(0xffffffffu, lane < lvl ? c : 0);
+    const int cnt_lvl = s_cnt[lvl];
+    if (blockIdx.x == 0 && tid == 0) out_count[f] = total;
+    const int pos = ((int)blockIdx.x - L.desc_block_base) * 8 + warp;
     if (pos >= cnt_lvl) return;
     const int oi = before + pos;
     if (oi >= capacity) return;
+    const int slot = L.kp_off + pos;
 
     const uint32_t pk = level_kps[(size_t)f * T.kps_per_frame + slot];
     const int kx = (int)(pk & 4095u), ky = (int)((pk >> 12) & 4095u), score = (int)(pk >> 24);
 
     // --- orientation ---
-    const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride + (size_t)ky * L.img_pitch + kx;
+    const uint8_t* __restrict__ imgf = L.img + (size_t)f * L.img_stride;      // uniform
+    const int ipitch = L.img_pitch;
     // rows +v and -v share |u| <= umax[v] (:80-92); fully unrolled so that all 31 row loads of a lane are in flight at once
     int m10 = 0, m01 = 0;
     const int u = lane - CCM_HALF_PATCH;
     const int au = abs(u);
-    const uint8_t* __restrict__ pc = img + u;
-    if (lane < 31) m10 = u * (int)pc[0];
+    const int o0 = ky * ipitch + kx + u;
+    if (lane < 31) m10 = u * (int)imgf[o0];
 #pragma unroll
     for (int v = 1; v <= CCM_HALF_PATCH; v++) {
         if (lane < 31 && au <= umax_of(v)) {
-            const int vp = pc[v * L.img_pitch], vm = pc[-v * L.img_pitch];
+            const int vp = imgf[o0 + v * ipitch], vm = imgf[o0 - v * ipitch];
             m10 += u * (vp + vm);
             m01 += v * (vp - vm);
         }
@@ -219,12 +213,12 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
 #else
     const float a = (float)cos((double)rad), b = (float)sin((double)rad);
 #endif
-    const uint8_t* __restrict__ bl = L.blur + (size_t)f * L.blur_stride + (size_t)ky * L.blur_pitch + kx;
+    const uint8_t* __restrict__ blf = L.blur + (size_t)f * L.blur_stride;     // uniform
     // cvRound of the steered tap (:107, :111-124) without the quarter-rate F2I: v + 1.5 * 2^23 rounds v to the nearest-even integer
     // in the low mantissa bits (|v| < 2^22), so int(v) = bits - 0x4B400000. The two constants of row * pitch + col are folded
     // into one (32-bit modular arithmetic: the true offset is small).
     const float MAGIC = 12582912.0f;
-    const uint32_t pitch = (uint32_t)L.blur_pitch, kfold = 0x4B400000u * (pitch + 1u);
+    const uint32_t pitch = (uint32_t)L.blur_pitch, koff = (uint32_t)ky * pitch + (uint32_t)kx - 0x4B400000u * (pitch + 1u);
     uint32_t byte = 0;
 #pragma unroll
     for (int k = 0; k < 8; k++) {
@@ -233,7 +227,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
         const uint32_t c1 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)), MAGIC));
         const uint32_t r2 = __float_as_uint(__fadd_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)), MAGIC));
         const uint32_t c2 = __float_as_uint(__fadd_rn(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)), MAGIC));
-        const int t0 = bl[(int)(r1 * pitch + c1 - kfold)], t1 = bl[(int)(r2 * pitch + c2 - kfold)];
+        const int t0 = blf[(int)(r1 * pitch + c1 + koff)], t1 = blf[(int)(r2 * pitch + c2 + koff)];
         byte |= (uint32_t)(t0 < t1) << k;
     }
     uint32_t w = byte << (8 * (lane & 3));
