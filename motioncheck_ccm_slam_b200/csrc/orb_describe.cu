@@ -22,32 +22,30 @@ __device__ __forceinline__ uint32_t blur_load(const uint8_t* __restrict__ row, i
 
 // four horizontal 7-tap sums of pixels x..x+3 from the words holding pixels x-4..x+7: eight unaligned 4-byte windows
 // (PRMT) and eight IDP4A with the packed 8.8 coefficients {18,34,48,56 | 48,34,18,0}.
-// Right border (reflect-101): the taps reach at most pixels w..w+2 = pixels w-2, w-3, w-4. The row's last aligned word
-// (at wa = (w-1) & ~3, holding e = w - wa valid pixels) followed by those three pixels forms an 8-byte tail; the lane that
-// owns word wa takes (own, next) from it and the lane before takes next. Rows narrower than 16 px use a per-byte gather.
-__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint32_t own, int x, int x0, int w, int lane, uint32_t (&hs)[4]) {
+// Right border (reflect-101): the taps reach at most pixels w..w+2 = pixels w-2, w-3, w-4. With wa = (w-1) & ~3 the row's
+// last aligned word and e = w - wa its valid pixels, the 8 bytes "pixels wa..w-1, then w-2, w-3, w-4" are a byte permutation
+// of the two words at wa-4 and wa, which the two lanes concerned already hold: two PRMT with selectors that depend only
+// on e (blur_tail_selectors), no extra loads. The lane that owns word wa takes (own, next) from them, the lane before
+// takes next. Levels narrower than 16 px never get here (blur_small_level).
+__device__ __forceinline__ void blur_tail_selectors(int w, uint32_t& sel_lo, uint32_t& sel_hi) {
+    const int e = w - ((w - 1) & ~3);                       // 1..4
+    // byte j of the tail is pixel wa + j for j < e (index 4 + j of the word pair) and pixel w - 2 - (j - e) after it (index 2e + 2 - j)
+    sel_lo = (uint32_t)(0x7654565434541234ull >> (16 * (e - 1))) & 0xffffu;     // e = 1: 0x1234, 2: 0x3454, 3: 0x5654, 4: 0x7654
+    sel_hi = (uint32_t)(0x3456123400120000ull >> (16 * (e - 1))) & 0xffffu;     // e = 1: 0x0000, 2: 0x0012, 3: 0x1234, 4: 0x3456
+}
+
+__device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint32_t own, int x, int x0, int w, int lane,
+                                          uint32_t sel_lo, uint32_t sel_hi, uint32_t (&hs)[4]) {
     uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
     uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
     if (lane == 0 && x0 > 0) prev = *reinterpret_cast<const uint32_t*>(row + x - 4);
     if (lane == 31 && x + 4 < w) next = *reinterpret_cast<const uint32_t*>(row + x + 4);
     const int wa = (w - 1) & ~3;
-    if (w >= 16) {
-        if (x == 0) prev = __byte_perm(own, 0u, 0x1230);   // reflect-101 on the left: pixels -3,-2,-1 are pixels 3,2,1 of this word
-        if (x + 4 >= wa && x <= wa) {                       // the two lanes whose windows reach past the last pixel
-            const int e = w - wa;                           // 1..4 valid pixels in the last word
-            const uint32_t last = *reinterpret_cast<const uint32_t*>(row + wa);
-            const uint32_t ext = (uint32_t)row[w - 2] | ((uint32_t)row[w - 3] << 8) | ((uint32_t)row[w - 4] << 16);
-            const unsigned long long tail = (e == 4 ? (unsigned long long)last : (unsigned long long)(last & ((1u << (8 * e)) - 1u))) |
-                                            ((unsigned long long)ext << (8 * e));
-            if (x == wa) { own = (uint32_t)tail; next = (uint32_t)(tail >> 32); }
-            else next = (uint32_t)tail;
-        }
-    } else if (x < w) {                                     // tiny rows: gather bytes x-4..x+7
-        uint32_t wd[3] = {0u, 0u, 0u};
-#pragma unroll
-        for (int k = 0; k < 12; k++) wd[k >> 2] |= (uint32_t)row[ccm_reflect101(min(x - 4 + k, w + 2), w)] << (8 * (k & 3));
-        prev = wd[0]; own = wd[1]; next = wd[2];
-    }
+    if (x == 0) prev = __byte_perm(own, 0u, 0x1230);       // reflect-101 on the left: pixels -3,-2,-1 are pixels 3,2,1 of this word
+    if (x == wa) {                                          // the two lanes whose windows reach past the last pixel
+        const uint32_t lo = __byte_perm(prev, own, sel_lo), hi = __byte_perm(prev, own, sel_hi);
+        own = lo; next = hi;
+    } else if (x == wa - 4) next = __byte_perm(own, next, sel_lo);
     const uint32_t C1 = 18u | (34u << 8) | (48u << 16) | (56u << 24), C2 = 48u | (34u << 8) | (18u << 16);
     const uint32_t wm3 = __byte_perm(prev, own, 0x4321), wm2 = __byte_perm(prev, own, 0x5432), wm1 = __byte_perm(prev, own, 0x6543);
     const uint32_t wp1 = __byte_perm(own, next, 0x4321), wp2 = __byte_perm(own, next, 0x5432), wp3 = __byte_perm(own, next, 0x6543);
@@ -55,6 +53,34 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint3
     hs[1] = __dp4a(wm2, C1, __dp4a(wp2, C2, 0u));
     hs[2] = __dp4a(wm1, C1, __dp4a(wp3, C2, 0u));
     hs[3] = __dp4a(own, C1, __dp4a(next, C2, 0u));
+}
+
+// Levels narrower than 16 px (the last levels of very small images): the word tricks of blur_hrow do not apply, and such a
+// level is a few hundred pixels - each lane evaluates its 4 outputs tap by tap with reflect-101 (same integers: the
+// horizontal sums are exact, the vertical pass rounds once). Out of line so that the unrolled main loop stays small.
+__device__ __noinline__ void blur_small_level(const uint8_t* __restrict__ img, int pitch, uint8_t* __restrict__ out, int opitch,
+                                              int w, int h, int x, int wy0) {
+    const int cf[7] = {18, 34, 48, 56, 48, 34, 18};
+#pragma unroll 1
+    for (int oy = wy0; oy < min(wy0 + BLUR_RPW, h); oy++) {
+        if (x >= w) continue;
+        uint32_t packed = 0;
+#pragma unroll 1
+        for (int i = 0; i < 4; i++) {
+            const int px = min(x + i, w - 1);
+            uint32_t acc = 0;
+#pragma unroll 1
+            for (int dy = -3; dy <= 3; dy++) {
+                const uint8_t* row = img + (size_t)ccm_reflect101(oy + dy, h) * pitch;
+                uint32_t hs = 0;
+#pragma unroll 1
+                for (int dx = -3; dx <= 3; dx++) hs += (uint32_t)cf[dx + 3] * row[ccm_reflect101(px + dx, w)];
+                acc += (uint32_t)cf[dy + 3] * hs;
+            }
+            packed |= ((acc + 32768u) >> 16) << (8 * i);
+        }
+        *reinterpret_cast<uint32_t*>(out + (size_t)oy * opitch + x) = packed;
+    }
 }
 
 __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ LevelTable T) {
@@ -73,7 +99,10 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int pitch = L.img_pitch;
     uint8_t* __restrict__ outp = L.blur + (size_t)f * L.blur_stride + (size_t)wy0 * L.blur_pitch + x;
+    if (w < 16) { blur_small_level(img, pitch, L.blur + (size_t)f * L.blur_stride, L.blur_pitch, w, h, x, wy0); return; }   // warp-uniform
     uint32_t ring[7][4];
+    uint32_t sel_lo, sel_hi;
+    blur_tail_selectors(w, sel_lo, sel_hi);
     // source row of window row r is wy0 + r - 3 (rows past the bottom only feed outputs that are never stored).
     // Strips that touch neither the top nor the bottom border step the row pointer; the others reflect per row.
     const bool inner = wy0 >= 3 && wy0 + BLUR_RPW + 3 <= h;   // warp-uniform
@@ -83,7 +112,7 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     for (int r = 0; r < BLUR_RPW + 6; r++) {
         const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
         const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
-        blur_hrow(row, own, x, x0, w, lane, ring[r % 7]);
+        blur_hrow(row, own, x, x0, w, lane, sel_lo, sel_hi, ring[r % 7]);
         row = row_n; own = own_n;
         if (r >= 6) {
             const int oy = wy0 + r - 6;
