@@ -11,13 +11,16 @@
 // vertical pass: no shared memory, every source byte is loaded once per strip (22 rows for 16 outputs), the output
 // is one coalesced 32-bit store per lane. Reflect-101 borders take a per-byte path only in the lanes that touch them.
 // ---------------------------------------------------------------------------------------------
-#define BLUR_TW 128
+#ifndef BLUR_OVERLAP
+#define BLUR_OVERLAP 1                  // warps overlap by one word on each side: lanes 0 / 31 only feed their neighbours, no edge loads
+#endif
+#define BLUR_TW (BLUR_OVERLAP ? 120 : 128)   // output pixels per warp row
 #define BLUR_RPW 16                      // output rows per warp
 #define BLUR_TH (8 * BLUR_RPW)           // rows per CTA (8 warps)
 
 // own word of this lane for one source row (0 beyond the row); issued one row ahead of its use
 __device__ __forceinline__ uint32_t blur_load(const uint8_t* __restrict__ row, int x, int w) {
-    return x < w ? *reinterpret_cast<const uint32_t*>(row + x) : 0u;
+    return (unsigned)x < (unsigned)w ? *reinterpret_cast<const uint32_t*>(row + x) : 0u;   // x = -4 for lane 0 of the first tile (overlap mode)
 }
 
 // four horizontal 7-tap sums of pixels x..x+3 from the words holding pixels x-4..x+7: eight unaligned 4-byte windows
@@ -38,8 +41,10 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint3
                                           uint32_t sel_lo, uint32_t sel_hi, uint32_t (&hs)[4]) {
     uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
     uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
+#if !BLUR_OVERLAP
     if (lane == 0 && x0 > 0) prev = *reinterpret_cast<const uint32_t*>(row + x - 4);
     if (lane == 31 && x + 4 < w) next = *reinterpret_cast<const uint32_t*>(row + x + 4);
+#endif
     const int wa = (w - 1) & ~3;
     if (x == 0) prev = __byte_perm(own, 0u, 0x1230);       // reflect-101 on the left: pixels -3,-2,-1 are pixels 3,2,1 of this word
     if (x == wa) {                                          // the two lanes whose windows reach past the last pixel
@@ -92,14 +97,15 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const int tyi = tile / L.blur_tiles_x, txi = tile - tyi * L.blur_tiles_x;
     const int f = blockIdx.y;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x0 = txi * BLUR_TW, x = x0 + 4 * lane;
+    const int x0 = txi * BLUR_TW - (BLUR_OVERLAP ? 4 : 0), x = x0 + 4 * lane;
+    const bool out_lane = !BLUR_OVERLAP || (lane >= 1 && lane <= 30);
     const int wy0 = tyi * BLUR_TH + warp * BLUR_RPW;
     const int w = L.w, h = L.h;
     if (wy0 >= h) return;                                    // warp-uniform
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int pitch = L.img_pitch;
     uint8_t* __restrict__ outp = L.blur + (size_t)f * L.blur_stride + (size_t)wy0 * L.blur_pitch + x;
-    if (w < 16) { blur_small_level(img, pitch, L.blur + (size_t)f * L.blur_stride, L.blur_pitch, w, h, x, wy0); return; }   // warp-uniform
+    if (w < 16) { blur_small_level(img, pitch, L.blur + (size_t)f * L.blur_stride, L.blur_pitch, w, h, out_lane ? x : w, wy0); return; }   // warp-uniform
     uint32_t ring[7][4];
     uint32_t sel_lo, sel_hi;
     blur_tail_selectors(w, sel_lo, sel_hi);
@@ -123,7 +129,7 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
                                      48 * (ring[(r - 4) % 7][k] + ring[(r - 2) % 7][k]) + 56 * ring[(r - 3) % 7][k];
                 packed |= ((acc + 32768u) >> 16) << (8 * k);
             }
-            if (oy < h && x < w) *reinterpret_cast<uint32_t*>(outp) = packed;   // pitch multiple of 32: in-bounds
+            if (out_lane && oy < h && x < w) *reinterpret_cast<uint32_t*>(outp) = packed;   // pitch multiple of 32: in-bounds
             outp += L.blur_pitch;
         }
     }
