@@ -260,6 +260,21 @@ int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, co
 int ccm_match_allpairs_best2(ccm_matcher* m, const uint8_t* q, int nq, const uint8_t* targets, long long nt,
                              uint32_t index_base, ccm_best2* out);
 
+/* ---- allocation-free database search -----------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it). Same result as
+ * ccm_match_allpairs_best2_device (d_out [nq] = best-2 of d_q [nq][32] over d_targets [nt][32], device pointers,
+ * 16-byte aligned), but it takes no matcher handle and allocates nothing: the per-chunk partial records live in a
+ * fixed 4 MiB `static __device__` array inside the library (every GPU that loads the library holds its copy until
+ * the process exits). Runs on the CURRENT device, on `stream` (a cudaStream_t; NULL = the default stream),
+ * asynchronously. Limits: nq <= CCM_NOALLOC_MAX_QUERIES and nt <= floor(524288 / nq) * 2^23, else CCM_E_CAPACITY;
+ * the message is read with ccm_matcher_last_error(NULL). All calls on one GPU share the array: calls that overlap
+ * on the GPU (different streams or host threads) race; calls ordered on one stream are safe. The first call on a
+ * device resolves the array's device address (cudaGetSymbolAddress) - make it outside stream capture. */
+#define CCM_NOALLOC_MAX_QUERIES 4096
+int ccm_match_allpairs_best2_noalloc_device(void* stream, const uint8_t* d_q, int nq, const uint8_t* d_targets, long long nt,
+                                            uint32_t index_base, ccm_best2* d_out);
+
 #ifdef __cplusplus
 }
 #endif

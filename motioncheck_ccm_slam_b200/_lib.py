@@ -118,6 +118,7 @@ SIGNATURES.update({
     "ccm_match_allpairs_best2_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
     "ccm_match_allpairs_merge_device": (_i, [_vp, _vp, _i, _i, _f, _vp, _vp]),
     "ccm_match_allpairs_best2": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
+    "ccm_match_allpairs_best2_noalloc_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
 })
 
 _lib = None

@@ -9,3 +9,4 @@
 #include "match_bow.cu"
 #include "match_wire.cu"
 #include "match_api.cu"
+#include "match_noalloc.cu"
