@@ -42,6 +42,11 @@ struct ccm_orb {
     int fast_nt = 128, fast_nt_tma = 128;              // CTA sizes picked for the two cell tables
     int fast_ts = 0;                                   // tile row stride of the TMA variant (48 / 64 / 80), 0 = TMA unavailable
     FastTma tmaps = {};
+    // k_fast_chunks: one warp per chunk of whole cells (orb_fast_chunks.cu)
+    uint4* d_chunks = nullptr; int n_chunks = 0;
+    FastChunkSmem fc_smem = {};
+    bool fc_tma = false;                               // tensor maps of the arena levels are encoded (box FC_TW x tile_rows)
+    FastTma fc_tmaps = {};
     float4* d_pat = nullptr;                           // k_orient_describe's test pattern table
     void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
@@ -210,6 +215,36 @@ static int fast_pick_threads(const std::vector<uint4>& cell_info) {
     return best;
 }
 
+// k_fast_chunks' work list: every cell row of every level cut into chunks of whole cells that one warp covers with its 32
+// aligned 4-pixel words (lane 0's word holds x_c0 - 3, the last valid pixel lies in lane 30's word or before).
+// Entry = {x_c0 | y0 << 16, wc | ch << 16, level | ncells << 8 | wCell << 16, xw0} {magic(wCell), 0, 0, 0}.
+static void fast_chunk_table(const LevelTable& T, std::vector<uint4>& out, int* max_ch) {
+    auto magic = [](int d) { return (0x100000u + (uint32_t)d - 1) / (uint32_t)d; };
+    *max_ch = 1;
+    for (int l = 0; l < T.nlevels; l++) {
+        const LevelDesc& D = T.l[l];
+        for (int i = 0; i < D.nRows; i++) {
+            const int y0 = CCM_EDGE + i * D.hCell, ch = std::min(y0 + D.hCell, D.h - CCM_EDGE) - y0;
+            if (ch <= 0) continue;
+            *max_ch = std::max(*max_ch, ch);
+            for (int j = 0; j < D.nCols;) {
+                const int x_c0 = CCM_EDGE + j * D.wCell, xw0 = (x_c0 - 3) & ~3;
+                int wc = 0, n = 0;
+                while (j + n < D.nCols) {
+                    const int x = x_c0 + wc, cw = std::min(x + D.wCell, D.w - CCM_EDGE) - x;
+                    if (cw <= 0 || (n > 0 && x + cw - 1 > xw0 + FC_MAX_SPAN)) break;
+                    wc += cw; n++;
+                }
+                if (n == 0) break;                               // the rest of the row is clipped away (:971)
+                out.push_back(make_uint4((uint32_t)x_c0 | ((uint32_t)y0 << 16), (uint32_t)wc | ((uint32_t)ch << 16),
+                                         (uint32_t)l | ((uint32_t)n << 8) | ((uint32_t)D.wCell << 16), (uint32_t)xw0));
+                out.push_back(make_uint4(magic(D.wCell), 0u, 0u, 0u));
+                j += n;
+            }
+        }
+    }
+}
+
 // Level geometry for one image shape, following ComputePyramid (:1284-1286), ComputeKeyPointsOctTree (:941-955)
 // and DistributeOctTree (:711-713). Allocates the arena for cfg.max_batch frames of this shape.
 static int configure_shape(ccm_orb* h, int rows, int cols) {
@@ -354,6 +389,22 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
             ok = encode_level_map(h, &h->tmaps.m[l], T.l[l].img, (size_t)T.l[l].img_pitch, T.l[l].h, T.l[l].img_stride, B, ts, h->fast_smem_tma.tile_rows);
         if (ok) h->fast_ts = ts;
     }
+    {
+        std::vector<uint4> chunks;
+        int fc_max_ch = 1;
+        fast_chunk_table(T, chunks, &fc_max_ch);
+        h->n_chunks = (int)(chunks.size() / 2);
+        h->fc_smem = fast_chunk_smem(fc_max_ch);
+        if ((rc = dev_alloc(h, &h->d_chunks, chunks.size()))) return rc;
+        CK(cudaMemcpy(h->d_chunks, chunks.data(), chunks.size() * sizeof(uint4), cudaMemcpyHostToDevice));
+        CK(cudaFuncSetAttribute(k_fast_chunks<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CK(cudaFuncSetAttribute(k_fast_chunks<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CK(cudaFuncSetAttribute(k_fast_chunks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fc_smem.total));
+        CK(cudaFuncSetAttribute(k_fast_chunks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fc_smem.total));
+        h->fc_tma = h->fast_ts != 0;
+        for (int l = 1; l < L && h->fc_tma; l++)
+            h->fc_tma = encode_level_map(h, &h->fc_tmaps.m[l], T.l[l].img, (size_t)T.l[l].img_pitch, T.l[l].h, T.l[l].img_stride, B, FC_TW, h->fc_smem.tile_rows);
+    }
     if ((rc = dev_alloc(h, &h->d_corners, (size_t)corners * B))) return rc;
     if ((rc = dev_alloc(h, &h->d_node_of, (size_t)corners * B))) return rc;
     if ((rc = dev_alloc(h, &h->d_corner_count, (size_t)CCM_MAX_LEVELS * B))) return rc;
@@ -426,6 +477,14 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         {
             // level 0 is the caller's buffer: its descriptor is encoded per call; a base / pitch / stride that TMA cannot address
             // (not 16-byte multiples) takes the word-load variant of the kernel for this call
+            static const bool use_cells = std::getenv("CCM_ORB_FAST_CELLS") != nullptr;     // A/B against the per-cell kernel
+            if (!use_cells) {
+                FastTma tm = h->fc_tmaps;
+                const bool tma = h->fc_tma && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, FC_TW, h->fc_smem.tile_rows);
+                const dim3 grid(h->n_chunks, n);
+                if (tma) launch_pdl(k_fast_chunks<true>, grid, dim3(32), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
+                else launch_pdl(k_fast_chunks<false>, grid, dim3(32), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
+            } else {
             const dim3 grid(T.total_cells, n);
             FastTma tm = h->tmaps;
             const bool tma = h->fast_ts && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, h->fast_ts, h->fast_smem_tma.tile_rows);
@@ -433,6 +492,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
             else if (tma && h->fast_ts == 80) launch_fast<80, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
             else if (tma) launch_fast<96, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
             else launch_fast<FAST_TS, false>(s, grid, h->fast_nt, T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem, f0, tm);
+            }
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[2], s));
