@@ -482,8 +482,8 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
                 FastTma tm = h->fc_tmaps;
                 const bool tma = h->fc_tma && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, FC_TW, h->fc_smem.tile_rows);
                 const dim3 grid(h->n_chunks, n);
-                if (tma) launch_pdl(k_fast_chunks<true>, grid, dim3(32), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
-                else launch_pdl(k_fast_chunks<false>, grid, dim3(32), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
+                if (tma) launch_pdl(k_fast_chunks<true>, grid, dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
+                else launch_pdl(k_fast_chunks<false>, grid, dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
             } else {
             const dim3 grid(T.total_cells, n);
             FastTma tm = h->tmaps;
