@@ -203,7 +203,8 @@ __device__ __forceinline__ bool has_run9(uint32_t m16) {
 // A pixel is a FAST-9 corner at threshold t exactly when this score is >= t (some arc has every |d| > t, same sign), so
 // the segment test and the score are one computation.
 __device__ __forceinline__ int fast_score16(int v, const uint32_t (&r)[16]) {
-    const uint32_t bias = (uint32_t)(v + 256) * 0xFFFF0001u + (512u << 16);
+    uint32_t bias = (uint32_t)(v + 256) * 0xFFFF0001u + (512u << 16);
+    asm("" : "+r"(bias));      // opaque: otherwise the compiler rewrites r * 65535 + bias as (r - v) * 65535 + const, two instructions per ring pixel
     uint32_t p[16], m2[16], m4[16], a9[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) p[k] = r[k] * 65535u + bias;            // lo = d + 256, hi = 256 - d

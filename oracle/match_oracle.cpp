@@ -536,10 +536,11 @@ void mo_vocab_transform(const int* child_start, const int* child_ids, const uint
 }
 
 /* MapPoint::ComputeDistinctiveDescriptors, cslam/src/MapPoint.cpp:929-994, for map points given as CSR row ranges of one
- * descriptor array (rows of a point in the order the reference's observation map would iterate them). PARITY UNPINNED:
- * MapPoint.cpp does not compile outside the ROS workspace (ccmslam_msgs, Map, Communicator), so this restatement is checked
- * only against a numpy median in tests/test_match_oracle.py. Keeps the float distance matrix, the sort and the
- * vDists[0.5*(N-1)] index of the original. */
+ * descriptor array (rows of a point in the order the reference's observation map would iterate them). PINNED: MapPoint.cpp
+ * does not compile outside the ROS workspace (ccmslam_msgs, Map, Communicator), so oracle/Makefile cuts lines 929-994 out
+ * of it and compiles them as they are over oracle/pinshim (oracle/_ref/libref_pin.so); tests/test_pin_oracle_vs_ref.py
+ * holds this restatement against that, tests/test_match_oracle.py against a numpy median. Keeps the float distance
+ * matrix, the sort and the vDists[0.5*(N-1)] index of the original. */
 void mo_distinctive_descriptors(int n_points, const int* start, const uint8_t* desc, int* best, int* best_median) {
     for (int p = 0; p < n_points; p++) {
         const int r0 = start[p], N = start[p + 1] - r0;
@@ -630,9 +631,11 @@ void mo_match_allpairs_best2(int nq, const uint8_t* q_desc, long long nt, const 
     }
 }
 
-/* Keyframe wire format — PARITY UNPINNED: cslam/src/Converter.cc needs Eigen and g2o and ccmslam_msgs needs ROS genmsg,
- * none of which exist in this image, so the two conversions are restated here and checked only against an independent
- * numpy packing (tests/test_match_oracle.py). KeyFrame::ConvertToMessage (cslam/src/KeyFrame.cpp:1462-1472) pushes
+/* Keyframe wire format — PINNED to the reference's own conversion statements: cslam/src/Converter.cc needs Eigen and g2o and
+ * ccmslam_msgs needs ROS genmsg, none of which exist in this image, so oracle/Makefile cuts Converter.cc:166-193 and
+ * KeyFrame.cpp:1462-1472 / 1688-1704 out of the reference and compiles them as they are over message structs with the .msg
+ * fields (oracle/_ref/libref_pin.so; tests/test_pin_oracle_vs_ref.py); the ROS 1 byte layout itself (no generated
+ * serialiser in the repository) is also checked against an independent numpy packing (tests/test_match_oracle.py). KeyFrame::ConvertToMessage (cslam/src/KeyFrame.cpp:1462-1472) pushes
  * Converter::toCvKeyPointMsg(mvKeysUn[i]) (Converter.cc:166-179: x, y, angle copied; octave to int8; response and size
  * through (u_int8_t)float) and one Descriptor per row; ROS 1 serialises CvKeyPoint[] / Descriptor[] (cslam_msgs/msg) as a
  * u32 count followed by the unpadded little-endian fields in declaration order:

@@ -613,3 +613,58 @@ def distinctive_case(seed, n_points=400, max_obs=40):
         rows[out] = rng.integers(0, 256, (int(out.sum()), 32), dtype=np.uint8)
         desc[start[p]:start[p + 1]] = rows
     return start, desc
+
+
+# line ranges of MapPoint.cpp / Converter.cc / KeyFrame.cpp compiled as they are (oracle/_ref/libref_pin.so, oracle/Makefile)
+def ref_pin_available():
+    return os.path.exists(os.path.join(ORACLE_DIR, "_ref", "libref_pin.so"))
+
+
+_pin = None
+
+
+def ref_pin_lib():
+    global _pin
+    if _pin is None:
+        L = ctypes.CDLL(os.path.join(ORACLE_DIR, "_ref", "libref_pin.so"))
+        L.pin_distinctive_descriptors.restype = None
+        L.pin_distinctive_descriptors.argtypes = [ctypes.c_int] + [ctypes.c_void_p] * 5
+        L.pin_wire_encode.restype = None
+        L.pin_wire_encode.argtypes = [ctypes.c_int] + [ctypes.c_void_p] * 9
+        L.pin_wire_decode.restype = ctypes.c_int
+        L.pin_wire_decode.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 7
+        _pin = L
+    return _pin
+
+
+def ref_distinctive_descriptors(start, desc, kf_bad=None):
+    """The reference's MapPoint::ComputeDistinctiveDescriptors per map point -> (chosen descriptor [n][32], assigned [n])."""
+    L = ref_pin_lib()
+    st, d = _a(start, np.int32), _a(desc, np.uint8).reshape(-1, 32)
+    n = len(st) - 1
+    out, has = np.zeros((max(n, 1), 32), np.uint8), np.zeros(max(n, 1), np.int32)
+    bad = None if kf_bad is None else _a(kf_bad, np.uint8)
+    L.pin_distinctive_descriptors(n, st.ctypes.data, d.ctypes.data, None if bad is None else bad.ctypes.data, out.ctypes.data, has.ctypes.data)
+    return out[:n], has[:n]
+
+
+def ref_wire_encode(kp, desc):
+    L = ref_pin_lib()
+    n = len(kp)
+    a = {k: np.ascontiguousarray(kp[k], np.int32 if k == "octave" else np.float32) for k in ("x", "y", "size", "angle", "response", "octave")}
+    d = _a(desc, np.uint8).reshape(-1, 32)
+    kb, db = np.zeros(4 + 15 * n + 4, np.uint8), np.zeros(4 + 32 * n + 4, np.uint8)
+    L.pin_wire_encode(n, *[a[k].ctypes.data for k in ("x", "y", "size", "angle", "response", "octave")], d.ctypes.data, kb.ctypes.data, db.ctypes.data)
+    return kb[:4 + 15 * n].tobytes(), db[:4 + 32 * n].tobytes()
+
+
+def ref_wire_decode(kp_bytes, desc_bytes, cap=1 << 16):
+    L = ref_pin_lib()
+    kb, db = np.frombuffer(kp_bytes, np.uint8).copy(), np.frombuffer(desc_bytes, np.uint8).copy()
+    n0 = int(np.frombuffer(kp_bytes[:4], np.uint32)[0])
+    f = {k: np.zeros(max(n0, 1), np.int32 if k == "octave" else np.float32) for k in ("x", "y", "size", "angle", "response", "octave")}
+    d = np.zeros((max(n0, 1), 32), np.uint8)
+    n = L.pin_wire_decode(kb.ctypes.data, db.ctypes.data, cap, *[f[k].ctypes.data for k in ("x", "y", "size", "angle", "response", "octave")], d.ctypes.data)
+    if n < 0:
+        return None
+    return {k: v[:n] for k, v in f.items()}, d[:n]

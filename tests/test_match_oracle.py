@@ -135,8 +135,8 @@ def test_rotation_histogram_quirk():
 
 
 def test_distinctive_descriptors_vs_numpy():
-    """mo_distinctive_descriptors (MapPoint.cpp:929-994 restated; the reference file does not build here, so this row's
-    parity is unpinned) against an independent numpy statement: argmin over rows of sorted(row)[int(0.5*(N-1))]."""
+    """mo_distinctive_descriptors (MapPoint.cpp:929-994 restated; pinned to the reference's own lines in
+    tests/test_pin_oracle_vs_ref.py) against an independent numpy statement: argmin over rows of sorted(row)[int(0.5*(N-1))]."""
     from _oracle import distinctive_case, oracle_distinctive_descriptors
     start, desc = distinctive_case(5)
     best, med = oracle_distinctive_descriptors(start, desc)
@@ -169,7 +169,8 @@ def _wire_keypoints(seed, n):
 
 
 def test_wire_format_vs_numpy_packing():
-    """Keyframe wire arrays (KeyFrame.cpp:1462-1472, Converter.cc:166-193) — parity unpinned, see oracle/match_oracle.cpp:
+    """Keyframe wire arrays (KeyFrame.cpp:1462-1472, Converter.cc:166-193; pinned to the reference's statements in
+    tests/test_pin_oracle_vs_ref.py):
     the restatement against an independent numpy structured-dtype packing of the .msg definitions, and the round trip."""
     from _oracle import oracle_wire_decode, oracle_wire_encode
     msg = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "u1"), ("angle", "<f4"), ("response", "u1"), ("octave", "i1")])
