@@ -256,6 +256,12 @@ void* ccm_exchange_buffer(ccm_exchange* x);
 void ccm_exchange_destroy(ccm_exchange* x);
 int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, const uint8_t* d_q, int nq, const uint8_t* d_targets,
                                              long long nt, uint32_t index_base, float nnratio, ccm_best2* d_out, uint8_t* d_accept);
+/* All ranks must make the same sequence of exchange calls with the same nq (lockstep). A rank whose peer never launches
+ * (its call failed, its process died) does not spin forever: after CCM_EXCHANGE_TIMEOUT_MS (environment, default 2000)
+ * the kernel gives up, writes "no match" records and raises a status word. ccm_exchange_check synchronises the matcher's
+ * stream and returns CCM_E_CUDA if that happened since the context was created; the context is then out of step with
+ * its peers and must be destroyed and recreated on every rank. */
+int ccm_exchange_check(ccm_exchange* x);
 /* host convenience: upload, search one shard, download */
 int ccm_match_allpairs_best2(ccm_matcher* m, const uint8_t* q, int nq, const uint8_t* targets, long long nt,
                              uint32_t index_base, ccm_best2* out);

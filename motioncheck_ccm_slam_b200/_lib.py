@@ -114,6 +114,7 @@ SIGNATURES.update({
     "ccm_exchange_connect_ptrs": (_i, [_vp, _c.POINTER(_vp)]),
     "ccm_exchange_buffer": (_vp, [_vp]),
     "ccm_exchange_destroy": (None, [_vp]),
+    "ccm_exchange_check": (_i, [_vp]),
     "ccm_match_allpairs_best2_exchange_device": (_i, [_vp, _vp, _vp, _i, _vp, _ll, _u32, _f, _vp, _vp]),
     "ccm_match_allpairs_best2_device": (_i, [_vp, _vp, _i, _vp, _ll, _u32, _vp]),
     "ccm_match_allpairs_merge_device": (_i, [_vp, _vp, _i, _i, _f, _vp, _vp]),

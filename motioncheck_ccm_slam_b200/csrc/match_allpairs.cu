@@ -201,9 +201,20 @@ __device__ __forceinline__ void st_release_sys_u32(void* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// status (device word of the exchange context): set to 1 by a CTA whose wait ran past timeout_ns. A peer that never
+// launches (its call failed or its process died) would otherwise leave this kernel spinning with no way to cancel it.
 __global__ void __launch_bounds__(EX_THREADS) k_allpairs_exchange(const Best2Dev* __restrict__ parts, int n_parts, int nq, float nnratio, int th_low,
                                                                   const ExPeers peers, int rank, int world, int nq_cap, int ctas_cap, uint32_t epoch,
-                                                                  Best2Dev* __restrict__ out, uint8_t* __restrict__ accept) {
+                                                                  Best2Dev* __restrict__ out, uint8_t* __restrict__ accept,
+                                                                  unsigned long long timeout_ns, uint32_t* __restrict__ status) {
+    __shared__ int timed_out;
+    if (threadIdx.x == 0) timed_out = 0;
     const int qi = blockIdx.x * EX_THREADS + threadIdx.x;
     const uint32_t par = epoch & 1u;
     const size_t rec_bytes = (size_t)2 * world * nq_cap * sizeof(Best2Dev);
@@ -232,11 +243,21 @@ __global__ void __launch_bounds__(EX_THREADS) k_allpairs_exchange(const Best2Dev
     // 3. wait for the same CTA of every rank (flags live in the local buffer)
     if (threadIdx.x < world) {
         const uint32_t* flag = reinterpret_cast<const uint32_t*>(peers.p[rank] + rec_bytes) + ((size_t)par * world + threadIdx.x) * ctas_cap + blockIdx.x;
-        while (ld_acquire_sys_u32(flag) != epoch) __nanosleep(100);
+        const unsigned long long t0 = globaltimer_ns();
+        while (ld_acquire_sys_u32(flag) != epoch) {
+            __nanosleep(100);
+            if (globaltimer_ns() - t0 > timeout_ns) { timed_out = 1; atomicExch(status, 1u); break; }
+        }
     }
     __syncthreads();
     // 4. merge across ranks
     if (qi >= nq) return;
+    if (timed_out) {                                     // a peer never published: no result, the host reports CCM_E_CUDA
+        Best2Dev o; o.idx = 0xffffffffu; o.d1 = 256; o.d2 = 256;
+        out[qi] = o;
+        if (accept) accept[qi] = 0;
+        return;
+    }
     bd = 256; bi = 0xffffffffu; sd = 256;
     const unsigned long long* mine = reinterpret_cast<const unsigned long long*>(peers.p[rank]) + (size_t)par * world * nq_cap + qi;
     for (int t = 0; t < world; t++) {

@@ -2,6 +2,7 @@
 // Compiled as part of the single translation unit ccm_orb_cuda.cu after match_allpairs.cu, match_window.cu, match_bow.cu.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -800,6 +801,8 @@ struct ccm_exchange {
     bool ipc_opened[EX_MAX_WORLD] = {};
     bool connected = false;
     uint32_t epoch = 0;
+    uint32_t* d_status = nullptr;                       // set by k_allpairs_exchange when a wait for a peer timed out
+    unsigned long long timeout_ns = 2000000000ull;      // CCM_EXCHANGE_TIMEOUT_MS
 };
 
 int ccm_exchange_create(ccm_matcher* m, int rank, int world, int nq_cap, ccm_exchange** out, uint8_t* handle_out) {
@@ -814,7 +817,10 @@ int ccm_exchange_create(ccm_matcher* m, int rank, int world, int nq_cap, ccm_exc
     cudaError_t e = cudaMalloc((void**)&x->buf, x->bytes);
     if (e == cudaSuccess) e = cudaMemset(x->buf, 0, x->bytes);               // flags start at epoch 0 = "nothing published"
     if (e == cudaSuccess && handle_out) e = cudaIpcGetMemHandle((cudaIpcMemHandle_t*)handle_out, x->buf);
-    if (e != cudaSuccess) { m->err = std::string("exchange buffer: ") + cudaGetErrorString(e); if (x->buf) cudaFree(x->buf); delete x; return CCM_E_CUDA; }
+    if (e == cudaSuccess) e = cudaMalloc((void**)&x->d_status, 256);
+    if (e == cudaSuccess) e = cudaMemset(x->d_status, 0, 256);
+    if (e != cudaSuccess) { m->err = std::string("exchange buffer: ") + cudaGetErrorString(e); if (x->buf) cudaFree(x->buf); if (x->d_status) cudaFree(x->d_status); delete x; return CCM_E_CUDA; }
+    if (const char* t = std::getenv("CCM_EXCHANGE_TIMEOUT_MS")) { const long long v = std::atoll(t); if (v > 0) x->timeout_ns = (unsigned long long)v * 1000000ull; }
     x->peer[rank] = x->buf;
     x->connected = world == 1;
     *out = x;
@@ -865,7 +871,23 @@ void ccm_exchange_destroy(ccm_exchange* x) {
     cudaDeviceSynchronize();                            // not the matcher's stream: the matcher may be gone already
     for (int r = 0; r < x->world; r++) if (x->ipc_opened[r]) cudaIpcCloseMemHandle(x->peer[r]);
     if (x->buf) cudaFree(x->buf);
+    if (x->d_status) cudaFree(x->d_status);
     delete x;
+}
+
+int ccm_exchange_check(ccm_exchange* x) {
+    if (!x) return CCM_E_BADARG;
+    ccm_matcher* m = x->m;
+    cudaSetDevice(x->device);
+    MCK(cudaStreamSynchronize(m->stream));
+    uint32_t st = 0;
+    MCK(cudaMemcpy(&st, x->d_status, sizeof(st), cudaMemcpyDeviceToHost));
+    if (st) {
+        m->err = "sharded search: a peer rank did not publish its records within the timeout (CCM_EXCHANGE_TIMEOUT_MS); "
+                 "the exchange context is out of step with its peers and must be recreated on every rank";
+        return CCM_E_CUDA;
+    }
+    return CCM_OK;
 }
 
 int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, const uint8_t* d_q, int nq, const uint8_t* d_targets,
@@ -878,11 +900,13 @@ int ccm_match_allpairs_best2_exchange_device(ccm_matcher* m, ccm_exchange* x, co
     if (rc) return rc;
     ExPeers P;
     for (int r = 0; r < EX_MAX_WORLD; r++) P.p[r] = r < x->world ? x->peer[r] : nullptr;
-    x->epoch++;
+    // the epoch advances only once the launch is known to be enqueued: a failed call leaves the context in step with its peers
     k_allpairs_exchange<<<(nq + EX_THREADS - 1) / EX_THREADS, EX_THREADS, 0, m->stream>>>(parts, n_chunks, nq, nnratio, CCM_TH_LOW, P, x->rank, x->world,
-                                                                                           x->nq_cap, x->ctas_cap, x->epoch, (Best2Dev*)d_out, d_accept);
-    m->launches++;
+                                                                                           x->nq_cap, x->ctas_cap, x->epoch + 1, (Best2Dev*)d_out, d_accept,
+                                                                                           x->timeout_ns, x->d_status);
     MCK(cudaGetLastError());
+    x->epoch++;
+    m->launches++;
     return CCM_OK;
 }
 

@@ -34,21 +34,13 @@ struct ccm_orb {
     int max_kps = 0;          // == T.kps_per_frame
     // device arena
     std::vector<void*> allocs;
-    uint4* d_cell_info = nullptr;
-    FastSmem fast_smem = {};
-    // TMA variant of the FAST tile load: its own cell table (tile column 0 = pixel x0-3) and one tensor map per level
-    uint4* d_cell_info_tma = nullptr;
-    FastSmem fast_smem_tma = {};
-    int fast_nt = 128, fast_nt_tma = 128;              // CTA sizes picked for the two cell tables
-    int fast_ts = 0;                                   // tile row stride of the TMA variant (48 / 64 / 80), 0 = TMA unavailable
-    FastTma tmaps = {};
-    // k_fast_chunks: one warp per chunk of whole cells (orb_fast_chunks.cu)
+    void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
+    // k_fast_chunks: two warps per chunk of whole cells (orb_fast_chunks.cu)
     uint4* d_chunks = nullptr; int n_chunks = 0;
     FastChunkSmem fc_smem = {};
     bool fc_tma = false;                               // tensor maps of the arena levels are encoded (box FC_TW x tile_rows)
     FastTma fc_tmaps = {};
     float4* d_pat = nullptr;                           // k_orient_describe's test pattern table
-    void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
     ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
@@ -89,6 +81,17 @@ struct ccm_orb {
         cudaError_t e_ = (call);                                                                         \
         if (e_ != cudaSuccess) {                                                                         \
             h->err = std::string(#call) + ": " + cudaGetErrorString(e_);                                 \
+            return CCM_E_CUDA;                                                                           \
+        }                                                                                                \
+    } while (0)
+
+// launch check that names the kernel: a failed launch is reported where it happened, not at the end of the batch
+#define CKL(name, expr)                                                                                  \
+    do {                                                                                                 \
+        cudaError_t e_ = (expr);                                                                         \
+        if (e_ == cudaSuccess) e_ = cudaGetLastError();                                                  \
+        if (e_ != cudaSuccess) {                                                                         \
+            h->err = std::string("launch of " name ": ") + cudaGetErrorString(e_);                       \
             return CCM_E_CUDA;                                                                           \
         }                                                                                                \
     } while (0)
@@ -150,7 +153,7 @@ static bool resize_group_table(int ssize, int dsize, const std::vector<int>& ofs
     return true;
 }
 
-// ---- TMA descriptors for k_fast_cells<TS, true> ----
+// ---- TMA descriptors for k_fast_chunks<true> ----
 typedef CUresult (*ccm_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                         const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                         CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -181,38 +184,6 @@ static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = (off || !tl_pdl) ? 0 : 1;
     return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
-}
-
-template <int TS, bool TMA>
-static void launch_fast(cudaStream_t s, dim3 grid, int nt, const LevelTable& T, const uint4* cell_info, uint32_t* corners, int* corner_count,
-                        const FastSmem& M, int frame0, const FastTma& tm) {
-    if (nt == 96) launch_pdl(k_fast_cells<TS, TMA, 96>, grid, dim3(96), (size_t)M.total, s, T, cell_info, corners, corner_count, M, frame0, tm);
-    else if (nt == 160) launch_pdl(k_fast_cells<TS, TMA, 160>, grid, dim3(160), (size_t)M.total, s, T, cell_info, corners, corner_count, M, frame0, tm);
-    else launch_pdl(k_fast_cells<TS, TMA, 128>, grid, dim3(128), (size_t)M.total, s, T, cell_info, corners, corner_count, M, frame0, tm);
-}
-template <int TS, bool TMA>
-static cudaError_t fast_set_carveout() {
-    cudaError_t e = cudaFuncSetAttribute(k_fast_cells<TS, TMA, 96>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fast_cells<TS, TMA, 128>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_fast_cells<TS, TMA, 160>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    return e;
-}
-// CTA size of k_fast_cells for a cell table: warp-sweeps over the 4-pixel groups of every cell (the dominant loop) plus a
-// per-warp share for the stages whose cost does not depend on the cell size
-static int fast_pick_threads(const std::vector<uint4>& cell_info) {
-    int best = 128;
-    double best_cost = 1e300;
-    for (int nt : {96, 128, 160}) {
-        double cost = 0;
-        for (size_t c = 0; c + 1 < cell_info.size(); c += 2) {
-            const int ch = (int)(cell_info[c].y >> 16), ngx = (int)(cell_info[c].w >> 24), ngrp = ngx * ch;
-            if (ch <= 0) continue;
-            cost += (double)((ngrp + nt - 1) / nt) * (nt / 32) + 1.5 * (nt / 32);
-        }
-        if (cost < best_cost) { best_cost = cost; best = nt; }
-    }
-    if (const char* e = std::getenv("CCM_ORB_FAST_THREADS")) { const int v = std::atoi(e); if (v == 96 || v == 128 || v == 160) best = v; }   // tuning knob
-    return best;
 }
 
 // k_fast_chunks' work list: every cell row of every level cut into chunks of whole cells that one warp covers with its 32
@@ -258,8 +229,6 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     const int L = h->cfg.nlevels, B = h->cfg.max_batch;
     T.nlevels = L; T.ini_th = h->cfg.ini_th_fast; T.min_th = h->cfg.min_th_fast;
     int cells = 0, corners = 0, kps = 0, max_node_cap = 0, blur_tiles = 0, desc_blocks = 0;
-    std::vector<uint4> cell_info, cell_info_tma;
-    int max_cw = 1, max_ch = 1;
     for (int l = 0; l < L; l++) {
         LevelDesc& D = T.l[l];
         D.w = (int)lrintf((float)cols * h->isf[l]);
@@ -284,20 +253,6 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
                 const int x0 = CCM_EDGE + j * D.wCell, y0 = CCM_EDGE + i * D.hCell;
                 const int cw = std::min(x0 + D.wCell, D.w - CCM_EDGE) - x0, ch = std::min(y0 + D.hCell, D.h - CCM_EDGE) - y0;
                 if (cw > 0 && ch > 0) cc += ((cw + 1) / 2) * ((ch + 1) / 2);
-                // tile geometry of k_fast_cells: x0-3 = word-aligned gxa + shift; wpr words per tile row; the cell's pixels
-                // lie in aligned words [g0, g0+ngx) of a tile row; magic multipliers m with (i*m)>>20 == i/d for i < 4096
-                const int cwp = std::max(cw, 1), shift = (x0 - 3) & 3, wpr = (shift + cwp + 6 + 3) >> 2;
-                const int g0 = (3 + shift) >> 2, ngx = ((cwp + 2 + shift) >> 2) - g0 + 1;
-                auto magic = [](int d) { return (0x100000u + (uint32_t)d - 1) / (uint32_t)d; };
-                cell_info.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l,
-                                               (uint32_t)shift | ((uint32_t)wpr << 8) | ((uint32_t)g0 << 16) | ((uint32_t)ngx << 24)));
-                cell_info.push_back(make_uint4(magic(wpr), magic(cwp), magic(ngx), 0u));
-                // TMA variant: the box starts at the 16-byte aligned column below x0-3 (tools/tma_probe.cu), shift = 0..15
-                const int shift_t = (x0 - 3) & 15, g0_t = (3 + shift_t) >> 2, ngx_t = ((cwp + 2 + shift_t) >> 2) - g0_t + 1;
-                cell_info_tma.push_back(make_uint4((uint32_t)x0 | ((uint32_t)y0 << 16), (uint32_t)std::max(cw, 0) | ((uint32_t)std::max(ch, 0) << 16), (uint32_t)l,
-                                                   (uint32_t)shift_t | (1u << 8) | ((uint32_t)g0_t << 16) | ((uint32_t)ngx_t << 24)));
-                cell_info_tma.push_back(make_uint4(magic(1), magic(cwp), magic(ngx_t), 0u));
-                max_cw = std::max(max_cw, cw); max_ch = std::max(max_ch, ch);
             }
         D.corner_cap = std::max(cc, 1); D.corner_off = corners; corners += align_up(D.corner_cap, 4);
         if (D.corner_cap > 0x7FFFF) { h->err = "image too large (corner capacity per level exceeds 2^19)"; return CCM_E_BADARG; }
@@ -359,35 +314,11 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         if ((rc = dev_alloc(h, &h->d_pat, 256))) return rc;
         CK(cudaMemcpy(h->d_pat, pt, sizeof(pt), cudaMemcpyHostToDevice));
     }
-    h->fast_smem = fast_smem_layout(max_cw, max_ch);
-    CK((fast_set_carveout<FAST_TS, false>()));
-    CK((fast_set_carveout<64, true>()));
-    CK((fast_set_carveout<80, true>()));
-    CK((fast_set_carveout<96, true>()));
-    h->fast_nt = fast_pick_threads(cell_info);
-    h->fast_nt_tma = fast_pick_threads(cell_info_tma);
-    if ((rc = dev_alloc(h, &h->d_cell_info, cell_info.size()))) return rc;
-    CK(cudaMemcpy(h->d_cell_info, cell_info.data(), cell_info.size() * sizeof(uint4), cudaMemcpyHostToDevice));
-    if ((rc = dev_alloc(h, &h->d_cell_info_tma, cell_info_tma.size()))) return rc;
-    CK(cudaMemcpy(h->d_cell_info_tma, cell_info_tma.data(), cell_info_tma.size() * sizeof(uint4), cudaMemcpyHostToDevice));
-    // TMA tile load: row stride = box width = a multiple of 16 bytes that holds the widest cell + ring; descriptors of the
-    // arena levels are encoded once per shape, level 0 (the caller's buffer) per call (run_pipeline)
-    h->fast_ts = 0;
-    if (!std::getenv("CCM_ORB_NO_TMA")) {
-        if (!h->encode_tiled) {
-            cudaDriverEntryPointQueryResult q;
-            void* fn = nullptr;
-            if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) h->encode_tiled = fn;
-            else cudaGetLastError();
-        }
-        const int need = 15 + max_cw + 6;
-        int ts = need <= 80 ? 80 : 96;      // 64 fits the 30-px cells but a 16-word row stride makes rows r and r+2 share banks (0.220 vs 0.216 ms)
-        if (const char* e = std::getenv("CCM_ORB_FAST_TS")) { const int v = std::atoi(e); if ((v == 64 || v == 80 || v == 96) && v >= need) ts = v; }   // tuning knob
-        h->fast_smem_tma = fast_smem_layout(max_cw, max_ch, ts);
-        bool ok = h->encode_tiled != nullptr;
-        for (int l = 1; l < L && ok; l++)
-            ok = encode_level_map(h, &h->tmaps.m[l], T.l[l].img, (size_t)T.l[l].img_pitch, T.l[l].h, T.l[l].img_stride, B, ts, h->fast_smem_tma.tile_rows);
-        if (ok) h->fast_ts = ts;
+    if (!h->encode_tiled && !std::getenv("CCM_ORB_NO_TMA")) {
+        cudaDriverEntryPointQueryResult q;
+        void* fn = nullptr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) h->encode_tiled = fn;
+        else cudaGetLastError();
     }
     {
         std::vector<uint4> chunks;
@@ -401,7 +332,9 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         CK(cudaFuncSetAttribute(k_fast_chunks<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         CK(cudaFuncSetAttribute(k_fast_chunks<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fc_smem.total));
         CK(cudaFuncSetAttribute(k_fast_chunks<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->fc_smem.total));
-        h->fc_tma = h->fast_ts != 0;
+        // TMA tile load: one descriptor per level, box = FC_TW x tile_rows; the arena levels are encoded once per shape,
+        // level 0 (the caller's buffer) per call (run_pipeline). CCM_ORB_NO_TMA=1 forces the word-load variant.
+        h->fc_tma = h->encode_tiled != nullptr;
         for (int l = 1; l < L && h->fc_tma; l++)
             h->fc_tma = encode_level_map(h, &h->fc_tmaps.m[l], T.l[l].img, (size_t)T.l[l].img_pitch, T.l[l].h, T.l[l].img_stride, B, FC_TW, h->fc_smem.tile_rows);
     }
@@ -468,48 +401,39 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[0], s));
         for (int l = 1; l < T.nlevels; l++) {
             dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, n);
-            if (T.l[l].resize_mlp) launch_pdl(k_resize_level_mlp, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l);
-            else if (T.l[l].xgrp) launch_pdl(k_resize_level, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l);
-            else k_resize_level_generic<<<g, dim3(32, 8), 0, s>>>(T, l);
+            if (T.l[l].resize_mlp) CKL("k_resize_level_mlp", launch_pdl(k_resize_level_mlp, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l));
+            else if (T.l[l].xgrp) CKL("k_resize_level", launch_pdl(k_resize_level, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), n), dim3(32, 8), 0, s, T, l));
+            else { k_resize_level_generic<<<g, dim3(32, 8), 0, s>>>(T, l); CKL("k_resize_level_generic", cudaSuccess); }
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[1], s));
         {
             // level 0 is the caller's buffer: its descriptor is encoded per call; a base / pitch / stride that TMA cannot address
             // (not 16-byte multiples) takes the word-load variant of the kernel for this call
-            static const bool use_cells = std::getenv("CCM_ORB_FAST_CELLS") != nullptr;     // A/B against the per-cell kernel
-            if (!use_cells) {
-                FastTma tm = h->fc_tmaps;
-                const bool tma = h->fc_tma && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, FC_TW, h->fc_smem.tile_rows);
-                const dim3 grid(h->n_chunks, n);
-                if (tma) launch_pdl(k_fast_chunks<true>, grid, dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
-                else launch_pdl(k_fast_chunks<false>, grid, dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm);
-            } else {
-            const dim3 grid(T.total_cells, n);
-            FastTma tm = h->tmaps;
-            const bool tma = h->fast_ts && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, h->fast_ts, h->fast_smem_tma.tile_rows);
-            if (tma && h->fast_ts == 64) launch_fast<64, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
-            else if (tma && h->fast_ts == 80) launch_fast<80, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
-            else if (tma) launch_fast<96, true>(s, grid, h->fast_nt_tma, T, h->d_cell_info_tma, A.corners, A.corner_count, h->fast_smem_tma, f0, tm);
-            else launch_fast<FAST_TS, false>(s, grid, h->fast_nt, T, h->d_cell_info, A.corners, A.corner_count, h->fast_smem, f0, tm);
-            }
+            FastTma tm = h->fc_tmaps;
+            const bool tma = h->fc_tma && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, f0 + n, FC_TW, h->fc_smem.tile_rows);
+            const dim3 grid(h->n_chunks, n);
+            if (tma) CKL("k_fast_chunks<TMA>", launch_pdl(k_fast_chunks<true>, grid, dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm));
+            else CKL("k_fast_chunks<words>", launch_pdl(k_fast_chunks<false>, grid, dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, s, T, h->d_chunks, A.corners, A.corner_count, h->fc_smem, f0, tm));
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[2], s));
         if (fork) CK(cudaEventRecord(LN.fork, s));
         if (!fork) {
             k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+            CKL("k_blur_levels", cudaSuccess);
             h->launches++;
         }
         if (st) CK(cudaEventRecord(h->ev[3], s));
     }
     {
-        launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(512), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, (const uint32_t*)A.corners,
-                   (const int*)A.corner_count, A.node_of, A.level_kps, A.level_kp_count);
+        CKL("k_quadtree", launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(512), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, (const uint32_t*)A.corners,
+                                     (const int*)A.corner_count, A.node_of, A.level_kps, A.level_kp_count));
         h->launches++;
         if (fork) {
             CK(cudaStreamWaitEvent(LN.aux, LN.fork, 0));
             k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, LN.aux>>>(T);
+            CKL("k_blur_levels", cudaSuccess);
             h->launches++;
             CK(cudaEventRecord(LN.join, LN.aux));
             CK(cudaStreamWaitEvent(s, LN.join, 0));
@@ -517,6 +441,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[4], s));
         k_orient_describe<<<dim3(T.total_desc_blocks, n), 256, 0, s>>>(T, h->d_pat, A.level_kps, A.level_kp_count,
                                                                             (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
+        CKL("k_orient_describe", cudaSuccess);
         h->launches++;
         if (st) { CK(cudaEventRecord(h->ev[5], s)); h->stage_pending = true; }
     }
@@ -657,6 +582,8 @@ int ccm_orb_extract_batch_device(ccm_orb* h, const uint8_t* d_imgs, int n, int r
     if (!d_imgs || !d_kp || !d_desc || !d_n || n < 1 || rows < 1 || cols < 1 || capacity < 1 || pitch < (size_t)cols) { h->err = "bad argument"; return CCM_E_BADARG; }
     if (((uintptr_t)d_imgs | pitch | frame_stride) & 3) { h->err = "device images: base, pitch and frame stride must be multiples of 4 bytes"; return CCM_E_BADARG; }
     if (n > h->cfg.max_batch) { h->err = "batch larger than max_batch"; return CCM_E_CAPACITY; }
+    for (int i = 0; i < CCM_MAX_TICKETS; i++)
+        if (h->tk[i].active) { h->err = "ccm_orb_extract_batch_device while a submitted batch is in flight: wait for it first (both use the arena's frame slots)"; return CCM_E_BADARG; }
     CK(cudaSetDevice(h->cfg.device));
     int rc = configure_shape(h, rows, cols);
     if (rc != CCM_OK) return rc;
@@ -738,13 +665,15 @@ int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n, 
     // behind that batch's kernels, so fewer, larger sub-batches (better kernel efficiency) are the better cut.
     int* first = K.first;
     int n_chunks = n <= 8 ? 1 : std::min(CCM_MAX_CHUNKS, std::min(in_flight ? 2 : 4, n / 4));
-    if (const char* e = std::getenv("CCM_ORB_CHUNKS")) n_chunks = std::max(1, std::min(std::min(CCM_MAX_CHUNKS, n), std::atoi(e)));   // tuning knob
+    static const char* const env_chunks = std::getenv("CCM_ORB_CHUNKS");
+    static const char* const env_plan = std::getenv("CCM_ORB_CHUNK_PLAN");
+    if (const char* e = env_chunks) n_chunks = std::max(1, std::min(std::min(CCM_MAX_CHUNKS, n), std::atoi(e)));   // tuning knob
     {
         const int per = (n + n_chunks - 1) / n_chunks;
         n_chunks = (n + per - 1) / per;
         for (int c = 0; c <= n_chunks; c++) first[c] = std::min(c * per, n);
     }
-    if (const char* e = std::getenv("CCM_ORB_CHUNK_PLAN")) {            // tuning knob: comma-separated sub-batch sizes
+    if (const char* e = env_plan) {                                      // tuning knob: comma-separated sub-batch sizes
         int c = 0, at = 0;
         first[0] = 0;
         while (*e && c < CCM_MAX_CHUNKS - 1 && at < n) {
@@ -767,6 +696,7 @@ int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n, 
         for (auto& e : K.tev) if (!e) CK(cudaEventCreate(&e));
         CK(cudaEventRecord(K.tev[0], h->s_in));
     }
+    auto enqueue = [&]() -> int {
     for (int c = 0; c < n_chunks; c++) {
         const int f0 = first[c], m = first[c + 1] - f0, g0 = s0 + f0;        // g0: first arena slot of this sub-batch
         if (packed) CK(cudaMemcpyAsync(l0 + g0 * stride, imgs[f0], frame_bytes * (size_t)(m - 1) + step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, h->s_in));
@@ -806,6 +736,20 @@ int ccm_orb_extract_batch_submit(ccm_orb* h, const uint8_t* const* imgs, int n, 
         CK(cudaMemcpyAsync(dst_desc, h->d_desc + (size_t)g0 * cap * 32, (size_t)32 * cap * m, cudaMemcpyDeviceToHost, h->s_out));
         CK(cudaEventRecord(ev_out, h->s_out));
         if (trace) CK(cudaEventRecord(K.tev[3 + 3 * c], h->s_out));
+    }
+    return CCM_OK;
+    };
+    rc = enqueue();
+    if (rc != CCM_OK) {
+        // part of the batch may be enqueued and still writing into the caller's arrays: nothing of it may be in flight
+        // when the error returns, because the ticket stays inactive and cannot be waited on
+        const std::string err = h->err;
+        cudaStreamSynchronize(h->s_in);
+        for (int i = 0; i < 2; i++) { cudaStreamSynchronize(h->lane[i].s); cudaStreamSynchronize(h->lane[i].aux); }
+        cudaStreamSynchronize(h->s_out);
+        cudaGetLastError();
+        h->err = err;
+        return rc;
     }
     K.t_enq = now_ms();
     K.active = true;

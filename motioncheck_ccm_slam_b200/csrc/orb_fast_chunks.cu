@@ -1,8 +1,8 @@
 // K2+K3, second form: FAST-9/16 + per-cell NMS + per-cell threshold fallback with TWO WARPS per chunk of whole cells.
 // Replaces the cell loop of ComputeKeyPointsOctTree, cslam/src/ORBextractor.cpp:957-998 (cv::FAST(cell, iniThFAST, nms) and
-// the minThFAST rerun when the cell came out empty, :978-985). Same results as k_fast_cells (orb_pyramid_fast.cu), which
-// spends ~300 warp instructions per 128 pixels: a per-cell CTA with five barriers per pass, a 4-word prefilter that
-// recomputes every difference twice, and four ballots per 128 pixels for the candidate list.
+// the minThFAST rerun when the cell came out empty, :978-985). Successor of the round-1 kernel
+// (one CTA per cell: ~300 warp instructions per 128 pixels, five barriers per pass, a 4-word prefilter that recomputed
+// every difference twice, four ballots per 128 pixels for the candidate list; 167 M warp instructions per 64 frames).
 //
 // A chunk = up to four horizontally adjacent cells of one cell row (<= 121 px wide): lane l owns the aligned 4-pixel word
 // xw0 + 4l of every row of the chunk's tile (128 px + ring; one TMA box or one word-copy loop per CTA). The two warps of

@@ -174,25 +174,12 @@ __global__ void __launch_bounds__(256) k_resize_level_generic(const __grid_const
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2+K3: FAST-9/16 per 30-px cell. Replaces the cell loop of ComputeKeyPointsOctTree,
-// cslam/src/ORBextractor.cpp:957-998 (cv::FAST(cell, iniTh, nms) and the minTh rerun when the cell is empty).
-// One CTA per (cell, frame). The cell's detection range is its (wCell x hCell) block of [19,w-19)x[19,h-19);
-// NMS neighbours outside that block count as 0 exactly as in a per-cell cv::FAST call.
-// Survivors are appended to the (frame, level) corner list with a warp-aggregated atomic; list order is not
-// significant (the quadtree's only order dependence is re-derived from coordinates, see orb_quadtree.cu).
+// K2+K3 building blocks: the FAST-9/16 corner score and the TMA / mbarrier helpers of the tile load. The kernel itself is
+// k_fast_chunks (orb_fast_chunks.cu). A cell's detection range is its (wCell x hCell) block of [19,w-19)x[19,h-19);
+// NMS neighbours outside that block count as 0 exactly as in a per-cell cv::FAST call. Survivors are
+// appended to the (frame, level) corner list; list order is not significant (the quadtree's only order dependence is
+// re-derived from coordinates, see orb_quadtree.cu).
 // ---------------------------------------------------------------------------------------------
-#define FAST_MAX_CELL 64                       // wCell,hCell <= 60 (width/nCols with nCols=floor(width/30))
-#define FAST_TILE (FAST_MAX_CELL + 6)
-
-__device__ __forceinline__ bool has_run9(uint32_t m16) {
-    uint32_t x = m16 | (m16 << 16);
-    x &= x >> 1;   // runs >= 2
-    x &= x >> 2;   // runs >= 4
-    x &= x >> 4;   // runs >= 8
-    x &= x >> 1;   // runs >= 9
-    return x != 0;
-}
-
 // cornerScore<16> (OpenCV fast_score.cpp): max over the 16 arcs of 9 ring pixels of min(d) and of min(-d), minus 1, with
 // d = v - ring pixel. d + 256 and 256 - d (both in [1, 511]) travel as the two halves of one register - one IMAD per ring
 // pixel, r * 65535 + ((v + 256) * (1 - 65536) + (512 << 16)), no borrow between the halves - so each step of the arc
@@ -220,51 +207,8 @@ __device__ __forceinline__ int fast_score16(int v, const uint32_t (&r)[16]) {
     return (int)max(best & 0xffffu, best >> 16) - 257;
 }
 
-// Work is staged through shared-memory lists so that the expensive steps only run on pixels that need them, with all
-// lanes busy: (B) 4-point compass test on every pixel (a 9-arc always holds two adjacent compass points) -> candidate
-// list; (C) full 16-ring FAST-9 test on candidates -> corner list; (D) cornerScore on corners -> score map;
-// (E) 3x3 NMS on corners only -> warp-aggregated append to the (frame, level) corner list in HBM.
-#define FAST_TS 76                             // tile row stride: 64 + 6 halo + up to 3 bytes of word-alignment shift
-
-// Shared-memory list plumbing written as PTX on 32-bit shared addresses: one ATOMS per warp (nvcc otherwise wraps every
-// atomicAdd in its own warp-aggregation sequence) and predicated 16-bit stores instead of a branch per store.
+// 32-bit shared-memory address of a generic pointer (PTX operands of the mbarrier / TMA / st.shared helpers)
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ uint32_t atoms_add(uint32_t saddr, uint32_t v) {
-    uint32_t r;
-    asm volatile("atom.shared.add.u32 %0, [%1], %2;" : "=r"(r) : "r"(saddr), "r"(v) : "memory");
-    return r;
-}
-__device__ __forceinline__ void sts_u16_if(uint32_t pred, uint32_t saddr, uint32_t val) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %0, 0;\n\t@p st.shared.u16 [%1], %2;\n\t}" ::"r"(pred), "r"(saddr), "h"((unsigned short)val) : "memory");
-}
-__device__ __forceinline__ uint32_t lanemask_lt() { uint32_t m; asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m)); return m; }
-
-// append val to a shared u16 list (byte address list_s, counter at count_s) for the lanes with pred set
-__device__ __forceinline__ void list_append(bool pred, uint32_t val, uint32_t list_s, uint32_t count_s) {
-    const uint32_t ballot = __ballot_sync(0xffffffffu, pred);
-    if (!ballot) return;
-    uint32_t base = 0;
-    if ((threadIdx.x & 31) == 0) base = atoms_add(count_s, __popc(ballot));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    sts_u16_if(pred, list_s + 2 * (base + __popc(ballot & lanemask_lt())), val);
-}
-
-// CTA size NT is a template parameter (96 / 128 / 160 threads): a cell is ngx x ch 4-pixel groups (~290 at the reference's 30-px
-// cells) and the host picks the NT that wastes the fewest lanes in the sweeps over them (fast_pick_threads, orb_api.cu)
-// Dynamic shared memory, sized by the host for the largest cell of the configured shape (fast_smem_layout):
-// tile [max_ch + 6][ts] | score [max_ch + 2][ss] | cand [max_px] u16 | corn [max_px] u16
-struct FastSmem { int score_off, cand_off, corn_off, total, ts, tile_rows, ss; };
-static inline FastSmem fast_smem_layout(int max_cw, int max_ch, int ts = FAST_TS) {
-    FastSmem m;
-    const int tile_bytes = ((max_ch + 6) * ts + 127) / 128 * 128;
-    m.ss = (max_cw + 2 + 3) / 4 * 4;                                 // score row stride: widest cell + its 1-px zero ring
-    const int score_bytes = ((max_ch + 2) * m.ss + 15) / 16 * 16;
-    const int list_bytes = (max_cw * max_ch * 2 + 15) / 16 * 16;
-    m.score_off = tile_bytes; m.cand_off = m.score_off + score_bytes; m.corn_off = m.cand_off + list_bytes;
-    m.total = m.corn_off + list_bytes;
-    m.ts = ts; m.tile_rows = max_ch + 6;
-    return m;
-}
 
 // TMA tile load (cp.async.bulk.tensor, sm_90+): one elected thread asks the copy engine for the (cell + 3-px ring) box of
 // its level image; the bytes land in shared memory and complete an mbarrier transaction count. One descriptor per level
@@ -284,173 +228,4 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst_s, const CUtensorMap* m
 __device__ __forceinline__ void mbar_wait(uint32_t bar_s, uint32_t parity) {
     asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}"
                  ::"r"(bar_s), "r"(parity) : "memory");
-}
-
-#ifndef FAST_RESIDENT_THREADS
-#define FAST_RESIDENT_THREADS 2048          // threads per SM the register budget is sized for (32 registers per thread)
-#endif
-template <int TS, bool TMA, int NT>
-__global__ void __launch_bounds__(NT, FAST_RESIDENT_THREADS / NT) k_fast_cells(const __grid_constant__ LevelTable T,
-                                                    const uint4* __restrict__ cell_info,  // per cell 2 x uint4, see configure_shape
-                                                    uint32_t* __restrict__ corners,      // [frames][corners_per_frame]
-                                                    int* __restrict__ corner_count,      // [frames][CCM_MAX_LEVELS]
-                                                    const FastSmem M, int frame0,        // arena slot of frame 0 (TMA z coordinate)
-                                                    const __grid_constant__ FastTma tm) {
-    extern __shared__ __align__(128) uint8_t fast_smem[];
-    uint8_t* const tile = fast_smem;                                   // [ch + 6][TS]
-    uint8_t* const score = fast_smem + M.score_off;                    // [cell + 1-px zero ring][SS]
-    const int SS = M.ss;
-    uint16_t* const cand = reinterpret_cast<uint16_t*>(fast_smem + M.cand_off);
-    uint16_t* const corn = reinterpret_cast<uint16_t*>(fast_smem + M.corn_off);
-    __shared__ int n_cand, n_corn;
-    __shared__ __align__(8) unsigned long long tile_bar;
-
-    const int f = blockIdx.y;
-    // detection block of this cell in level coordinates and the index-arithmetic constants of its tile
-    // (host-built table: configure_shape, orb_api.cu)
-    const uint4 ci = __ldg(cell_info + 2 * blockIdx.x), cj = __ldg(cell_info + 2 * blockIdx.x + 1);
-    const int x0 = (int)(ci.x & 0xffff), y0 = (int)(ci.x >> 16), cw = (int)(ci.y & 0xffff), ch = (int)(ci.y >> 16), lvl = (int)ci.z;
-    pdl_launch();
-    pdl_wait();                              // the pyramid (previous kernels of the chain) is complete
-    if (cw <= 0 || ch <= 0) return;          // clipped-away cell (the :962/:971 `continue`s)
-    const LevelDesc& L = T.l[lvl];
-
-    const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
-    const int tid = threadIdx.x;
-    // (A) tile = cell + 3-px ring. TMA: one thread asks for the box whose corner is (gxa, y0-3) of frame f — the innermost start
-    //     coordinate of a tiled TMA load must be a multiple of 16 bytes (measured: tools/tma_probe.cu; x = 13 raises an illegal
-    //     instruction), so gxa = (x0-3) & ~15 and pixel x0-3 is tile column `shift`; otherwise aligned 32-bit words (rows are
-    //     32-B aligned, pitch a multiple of 32).
-    const int shift = (int)(ci.w & 0xff), wpr = (int)(ci.w >> 8) & 0xff;    // x0-3 = aligned gxa + shift (word-aligned: 0..3, TMA: 16-byte aligned, 0..15); words per tile row
-    const int g0 = (int)(ci.w >> 16) & 0xff, ngx = (int)(ci.w >> 24);       // aligned 4-px words covering the cell: [g0, g0 + ngx)
-    const uint32_t wmagic = cj.x, cmagic = cj.y, gmagic = cj.z;             // i / wpr, i / cw, i / ngx for i < 4096
-    const int gxa = x0 - 3 - shift, th = ch + 6;
-    if (TMA) {
-        if (tid == 0) {
-            const uint32_t bar_s = smem_addr(&tile_bar);
-            mbar_init(bar_s, 1);
-            mbar_expect_tx(bar_s, (uint32_t)(M.tile_rows * TS));
-            tma_load_3d(smem_addr(tile), &tm.m[lvl], gxa, y0 - 3, frame0 + f, bar_s);
-        }
-    } else {
-        // NT / wpr tile rows per sweep, one word per thread, pointers stepped by whole sweeps
-        const int rps = (int)((NT * wmagic) >> 20);
-        const int ty0 = (int)(((uint32_t)tid * wmagic) >> 20), tx = tid - ty0 * wpr;
-        if (ty0 < rps) {
-            const uint8_t* src = img + (size_t)(y0 - 3 + ty0) * L.img_pitch + gxa + 4 * tx;
-            uint8_t* dst = tile + ty0 * TS + 4 * tx;
-            const size_t sstep = (size_t)rps * L.img_pitch;
-            const int dstep = rps * TS;
-            for (int ty = ty0; ty < th; ty += rps, src += sstep, dst += dstep)
-                *reinterpret_cast<uint32_t*>(dst) = *reinterpret_cast<const uint32_t*>(src);
-        }
-    }
-    for (int i = tid; i < ((ch + 2) * SS + 15) / 16; i += NT) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
-    if (tid == 0) { n_cand = 0; n_corn = 0; }
-    __syncthreads();
-    if (TMA) mbar_wait(smem_addr(&tile_bar), 0);     // every thread observes the completed transaction: the tile is visible
-    const uint32_t cand_s = smem_addr(cand), corn_s = smem_addr(corn), ncand_s = smem_addr(&n_cand), ncorn_s = smem_addr(&n_corn);
-
-    const int S = TS;
-    const int ngrp = ngx * ch;
-    int threshold = T.ini_th;
-#pragma unroll 1
-    for (int pass = 0; pass < 2; pass++) {
-        // (B) opposite-pair test on 4 pixels per thread (a 9-arc of the ring contains one pixel of every diametral pair,
-        //     so |v-p0|<=t && |v-p8|<=t, or the same for p4/p12, rules a pixel out): aligned 32-bit tile words, byte SIMD
-        const uint32_t t4 = (uint32_t)threshold * 0x01010101u;
-        for (int base = 0; base < ngrp; base += NT) {
-            const int gi = base + tid;
-            uint32_t nib = 0;
-            int py = 0, pxb = 0;
-            if (gi < ngrp) {
-                py = (int)(((uint32_t)gi * gmagic) >> 20);
-                const int g = g0 + gi - py * ngx;
-                pxb = 4 * g - 3 - shift;                                      // pixel of byte 0 of this word
-                const uint32_t* rowc = reinterpret_cast<const uint32_t*>(tile + (py + 3) * TS) + g;
-                const uint32_t cen = rowc[0], lft = rowc[-1], rgt = rowc[1];
-                const uint32_t up = rowc[-3 * (TS / 4)], dn = rowc[3 * (TS / 4)];
-                const uint32_t p4 = __funnelshift_r(cen, rgt, 24), p12 = __funnelshift_r(lft, cen, 8);
-                const uint32_t m = (__vcmpgtu4(__vabsdiffu4(cen, dn), t4) | __vcmpgtu4(__vabsdiffu4(cen, up), t4)) &
-                                   (__vcmpgtu4(__vabsdiffu4(cen, p4), t4) | __vcmpgtu4(__vabsdiffu4(cen, p12), t4));
-                nib = (((m & 0x01010101u) * 0x01020408u) >> 24) & 15u;
-                // keep the bytes that are pixels of this cell: 0 <= pxb + k < cw
-                const uint32_t lo_ok = pxb >= 0 ? 15u : (15u << (-pxb)) & 15u;
-                const uint32_t hi_ok = pxb + 3 < cw ? 15u : 15u >> (pxb + 4 - cw);
-                nib &= lo_ok & hi_ok;
-            }
-            const uint32_t b0 = __ballot_sync(0xffffffffu, nib & 1u), b1 = __ballot_sync(0xffffffffu, nib & 2u);
-            const uint32_t b2 = __ballot_sync(0xffffffffu, nib & 4u), b3 = __ballot_sync(0xffffffffu, nib & 8u);
-            if (b0 | b1 | b2 | b3) {
-                const uint32_t lt = lanemask_lt();
-                const uint32_t c0 = __popc(b0), c1 = __popc(b1), c2 = __popc(b2), c3 = __popc(b3);
-                uint32_t slot = 0;
-                if ((tid & 31) == 0) slot = atoms_add(ncand_s, c0 + c1 + c2 + c3);
-                slot = __shfl_sync(0xffffffffu, slot, 0);
-                const uint32_t a = cand_s + 2 * slot;
-                const uint32_t pi = (uint32_t)(py * cw + pxb);
-                sts_u16_if(nib & 1u, a + 2 * __popc(b0 & lt), pi);
-                sts_u16_if(nib & 2u, a + 2 * (c0 + __popc(b1 & lt)), pi + 1);
-                sts_u16_if(nib & 4u, a + 2 * (c0 + c1 + __popc(b2 & lt)), pi + 2);
-                sts_u16_if(nib & 8u, a + 2 * (c0 + c1 + c2 + __popc(b3 & lt)), pi + 3);
-            }
-        }
-        __syncthreads();
-        // (C) FAST-9/16 on the candidates: the corner score decides (score >= threshold) and goes into the score map
-        const int nc = n_cand;
-        for (int base = 0; base < nc; base += NT) {
-            const int j = base + tid;
-            bool is_corner = false;
-            int i = 0;
-            if (j < nc) {
-                i = cand[j];
-                const int py = (int)(((uint32_t)i * cmagic) >> 20), px = i - py * cw;
-                const uint8_t* c = tile + (py + 3) * TS + px + 3 + shift;
-                uint32_t r[16];
-                r[0] = c[3 * S];       r[1] = c[3 * S + 1];   r[2] = c[2 * S + 2];   r[3] = c[S + 3];
-                r[4] = c[3];           r[5] = c[-S + 3];      r[6] = c[-2 * S + 2];  r[7] = c[-3 * S + 1];
-                r[8] = c[-3 * S];      r[9] = c[-3 * S - 1];  r[10] = c[-2 * S - 2]; r[11] = c[-S - 3];
-                r[12] = c[-3];         r[13] = c[S - 3];      r[14] = c[2 * S - 2];  r[15] = c[3 * S - 1];
-                const int sc = fast_score16((int)c[0], r);
-                is_corner = sc >= threshold;                  // threshold >= 1 (enforced at create): a corner's score is never 0
-                if (is_corner) score[(py + 1) * SS + px + 1] = (uint8_t)sc;
-            }
-            list_append(is_corner, (uint32_t)i, corn_s, ncorn_s);
-        }
-        __syncthreads();
-        const int nk = n_corn;
-        // (E) non-maximum suppression over the corners, append survivors
-        int found = 0;
-        for (int base = 0; base < nk; base += NT) {     // uniform trip count: ballots below need whole warps
-            const int j = base + tid;
-            bool keep = false;
-            int px = 0, py = 0, s = 0;
-            if (j < nk) {
-                const int i = corn[j];
-                py = (int)(((uint32_t)i * cmagic) >> 20); px = i - py * cw;
-                const uint8_t* sc = &score[(py + 1) * SS + px + 1];
-                s = sc[0];
-                const uint8_t *su = sc - SS, *sd = sc + SS;
-                keep = s > su[-1] && s > su[0] && s > su[1] && s > sc[-1] && s > sc[1] && s > sd[-1] && s > sd[0] && s > sd[1];
-            }
-            const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
-            if (ballot) {
-                const int lane = tid & 31;
-                int slot = 0;
-                if (lane == 0) slot = atomicAdd(&corner_count[f * CCM_MAX_LEVELS + lvl], __popc(ballot));
-                slot = __shfl_sync(0xffffffffu, slot, 0);
-                if (keep) {
-                    const int idx = slot + __popc(ballot & ((1u << lane) - 1));
-                    if (idx < L.corner_cap)
-                        corners[(size_t)f * T.corners_per_frame + L.corner_off + idx] =
-                            (uint32_t)(x0 + px) | ((uint32_t)(y0 + py) << 12) | ((uint32_t)s << 24);
-                }
-                found = 1;
-            }
-        }
-        if (__syncthreads_or(found) || threshold == T.min_th) break;
-        threshold = T.min_th;     // cell empty at iniThFAST -> rerun at minThFAST (:981-985)
-        if (tid == 0) { n_cand = 0; n_corn = 0; }
-        __syncthreads();
-    }
 }

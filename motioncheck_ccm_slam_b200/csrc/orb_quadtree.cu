@@ -75,7 +75,7 @@ __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constan
     const LevelDesc& L = T.l[lvl];
     const int tid = threadIdx.x, NT = blockDim.x;
     pdl_launch();
-    pdl_wait();                              // the corner lists of k_fast_cells are complete
+    pdl_wait();                              // the corner lists of k_fast_chunks are complete
 
     QNode* A = reinterpret_cast<QNode*>(smem_raw);
     QNode* B = A + cap;

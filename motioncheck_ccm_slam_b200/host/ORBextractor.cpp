@@ -5,16 +5,18 @@
 //
 // The reference class has no spare member for a handle and its destructor is inline in the header, and the object is
 // copied into every Frame (Frame.cpp:37,56), so the device handle lives in a process-wide registry keyed by the
-// constructor arguments + device: copies of an extractor share one handle, the normal and the "ini" (2x features)
-// extractor get one each (they are never used concurrently, Tracking.cpp:75,115), and handles live until process exit.
-// A CUDA failure throws (the reference's fatal-error convention, estd.h:74) — there is no CPU fallback.
+// constructor arguments + device + image shape: copies of an extractor share one handle, the normal and the "ini" (2x
+// features) extractor get one each (they are never used concurrently, Tracking.cpp:75,115), a process that alternates two
+// image sizes keeps one arena per size instead of re-allocating per frame, and handles live until process exit.
+// A CUDA failure prints the library's message and throws estd::infrastructure_ex (the reference's fatal-error convention,
+// estd.h:66-74, as KILLSYS does) — there is no CPU fallback.
 #include <cslam/ORBextractor.h>
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
 #include <mutex>
-#include <stdexcept>
 #include <string>
 #include <tuple>
 
@@ -27,38 +29,38 @@ struct Shared {
     std::mutex mu;                       // the reference extractor is not re-entrant either (it mutates mvImagePyramid)
     std::vector<ccm_keypoint> kp;
     std::vector<unsigned char> desc;
-    int max_w = 0, max_h = 0;
 };
 
-typedef std::tuple<int, float, int, int, int, int> Key;
+[[noreturn]] void fatal(const char* what, const ccm_orb* h) {
+    std::fprintf(stderr, "ORBextractor (CUDA): %s: %s\n", what, ccm_last_error(h));
+    throw estd::infrastructure_ex();
+}
+
+typedef std::tuple<int, float, int, int, int, int, int, int> Key;
 
 int device_from_env() {                  // agent -> GPU pinning: CCM_ORB_DEVICE, default 0
     const char* e = std::getenv("CCM_ORB_DEVICE");
     return e ? std::atoi(e) : 0;
 }
 
-Shared& shared_for(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST) {
+Shared& shared_for(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int rows, int cols) {
     static std::mutex reg_mu;
     static std::map<Key, Shared*> reg;
     std::lock_guard<std::mutex> g(reg_mu);
-    Shared*& s = reg[Key(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device_from_env())];
+    Shared*& s = reg[Key(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, device_from_env(), rows, cols)];
     if (!s) s = new Shared();
     return *s;
 }
 
-// (re)create the handle when the first image arrives or a larger one shows up
+// create the handle of this (configuration, shape) when its first image arrives
 void ensure_handle(Shared& s, int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST, int rows, int cols) {
-    if (s.h && rows <= s.max_h && cols <= s.max_w) return;
-    if (s.h) ccm_orb_destroy(s.h);
-    s.h = nullptr;
+    if (s.h) return;
     ccm_orb_config cfg;
     cfg.nfeatures = nfeatures; cfg.scale_factor = scaleFactor; cfg.nlevels = nlevels;
     cfg.ini_th_fast = iniThFAST; cfg.min_th_fast = minThFAST;
-    cfg.max_width = std::max(cols, s.max_w); cfg.max_height = std::max(rows, s.max_h);
+    cfg.max_width = cols; cfg.max_height = rows;
     cfg.max_batch = 1; cfg.device = device_from_env();
-    if (ccm_orb_create(&cfg, &s.h) != CCM_OK)
-        throw std::runtime_error(std::string("ccm_orb_create: ") + ccm_last_error(nullptr));
-    s.max_w = cfg.max_width; s.max_h = cfg.max_height;
+    if (ccm_orb_create(&cfg, &s.h) != CCM_OK) fatal("ccm_orb_create", nullptr);
     const int cap = ccm_orb_max_keypoints(s.h);
     s.kp.resize(cap);
     s.desc.resize((size_t)cap * 32);
@@ -117,14 +119,14 @@ void ORBextractor::operator()(InputArray _image, InputArray /*_mask: ignored ups
     if (_image.empty()) return;                                        // :1219-1220, outputs untouched
     Mat image = _image.getMat();
     assert(image.type() == CV_8UC1);                                   // :1223
-    Shared& s = shared_for(nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST);
+    Shared& s = shared_for(nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, image.rows, image.cols);
     std::lock_guard<std::mutex> g(s.mu);
     ensure_handle(s, nfeatures, (float)scaleFactor, nlevels, iniThFAST, minThFAST, image.rows, image.cols);
     int n = 0;
     const int cap = (int)s.kp.size();
     if (ccm_orb_extract(s.h, image.data, image.rows, image.cols, (size_t)image.step, s.kp.data(), s.desc.data(), cap, &n) != CCM_OK)
-        throw std::runtime_error(std::string("ccm_orb_extract: ") + ccm_last_error(s.h));
-    n = std::min(n, cap);
+        fatal("ccm_orb_extract", s.h);
+    if (n > cap) fatal("more keypoints than ccm_orb_max_keypoints (internal)", s.h);      // never truncate silently
     _keypoints.clear();
     _keypoints.reserve(n);
     if (n == 0) {
@@ -148,7 +150,7 @@ void ORBextractor::operator()(InputArray _image, InputArray /*_mask: ignored ups
             Mat temp(h + 38, w + 38, CV_8UC1);
             int ow = 0, oh = 0;
             if (ccm_orb_get_pyramid_level(s.h, 0, level, 1, temp.data, (size_t)temp.step, &ow, &oh) != CCM_OK)
-                throw std::runtime_error(std::string("ccm_orb_get_pyramid_level: ") + ccm_last_error(s.h));
+                fatal("ccm_orb_get_pyramid_level", s.h);
             mvImagePyramid[level] = temp(Rect(19, 19, w, h));
         }
     }

@@ -8,8 +8,8 @@
 // Converted here: DescriptorDistance, SearchByProjection(Frame, MapPoints), SearchByProjection(Frame, LastFrame),
 // SearchByProjection(KeyFrame, Scw), SearchByBoW(KeyFrame, Frame), SearchByBoW(KeyFrame, KeyFrame),
 // SearchForInitialization, SearchForTriangulation, SearchBySim3 and both Fuse overloads (candidate search on the device,
-// CCM_WIN_BEST; the map mutations are replayed on the host in the reference's order). The caller-less relocalisation
-// SearchByProjection (:1478-1605) keeps its upstream body. A CUDA failure throws estd::infrastructure_ex (the
+// CCM_WIN_BEST; the map mutations are replayed on the host in the reference's order), and the relocalisation
+// SearchByProjection (:1478-1605, no caller upstream) on the entry point of the LastFrame search. A CUDA failure throws estd::infrastructure_ex (the
 // reference's fatal-error convention, estd.h:74); there is no CPU fallback.
 #include <cslam/ORBmatcher.h>
 
@@ -29,10 +29,11 @@ struct Device {
 
 Device& device() {
     static Device d;
-    if (!d.m) {
+    static std::once_flag once;
+    std::call_once(once, [] {                                 // a failed create throws and leaves the flag unset: the next call retries
         const char* e = std::getenv("CCM_ORB_DEVICE");       // agent -> GPU pinning, same variable as the extractor
         if (ccm_matcher_create(e ? std::atoi(e) : 0, &d.m) != CCM_OK) throw estd::infrastructure_ex();
-    }
+    });
     return d;
 }
 
@@ -183,6 +184,55 @@ int ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, 
         if (holder[k] >= 0) CurrentFrame.mvpMapPoints[k] = LastFrame.mvpMapPoints[holder[k]];
         else if (holder[k] == -1 && before[k] != -1) CurrentFrame.mvpMapPoints[k] = mpptr();   // pruned by the rotation histogram (:1461)
     }
+    return nmatches;
+}
+
+// ORBmatcher.cpp:1478-1605 — relocalisation: the key frame's map points projected with the current pose. The candidate
+// loop is the one of the LastFrame search (best only, levels [l-1, l+1], rotation histogram) with two changes that fit
+// the same entry point: every occupied feature blocks (:1545, no Observations() test) = holder -2, and the bound is
+// ORBdist instead of TH_HIGH (:1559) = th_dist.
+int ORBmatcher::SearchByProjection(Frame &CurrentFrame, kfptr pKF, const set<mpptr> &sAlreadyFound, const float th, const int ORBdist) {
+    const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3);
+    const cv::Mat tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+    const cv::Mat Ow = -Rcw.t() * tcw;
+    const vector<mpptr> vpMPs = pKF->GetMapPointMatches();
+    const int nq = (int)vpMPs.size();
+    std::vector<ccm_window_query> q(nq, no_query());
+    std::vector<uint8_t> qd((size_t)nq * 32 + 32);
+    for (int i = 0; i < nq; i++) {
+        mpptr pMP = vpMPs[i];
+        if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+        cv::Mat x3Dw = pMP->GetWorldPos();
+        cv::Mat x3Dc = Rcw * x3Dw + tcw;
+        const float xc = x3Dc.at<float>(0), yc = x3Dc.at<float>(1);
+        const float invzc = 1.0 / x3Dc.at<float>(2);
+        const float u = CurrentFrame.fx * xc * invzc + CurrentFrame.cx;
+        const float v = CurrentFrame.fy * yc * invzc + CurrentFrame.cy;
+        if (u < CurrentFrame.mnMinX || u > CurrentFrame.mnMaxX) continue;
+        if (v < CurrentFrame.mnMinY || v > CurrentFrame.mnMaxY) continue;
+        cv::Mat PO = x3Dw - Ow;
+        float dist3D = cv::norm(PO);
+        const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+        if (dist3D < minDistance || dist3D > maxDistance) continue;
+        const int lvl = pMP->PredictScale(dist3D, CurrentFrame.shared_from_this());
+        q[i].u = u; q[i].v = v; q[i].r = th * CurrentFrame.mvScaleFactors[lvl];
+        q[i].angle = pKF->mvKeysUn[i].angle;
+        q[i].min_level = (int16_t)(lvl - 1); q[i].max_level = (int16_t)(lvl + 1);
+        q[i].flags = CCM_Q_VALID | CCM_Q_OBS;                    // every accepted match blocks the feature for later points
+        std::memcpy(&qd[(size_t)32 * i], pMP->GetDescriptor().ptr(0), 32);
+    }
+    const int N = CurrentFrame.N;
+    std::vector<int> holder(N > 0 ? N : 1, -1);
+    for (int k = 0; k < N; k++)
+        if (CurrentFrame.mvpMapPoints[k]) holder[k] = -2;
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    Pack pack(D.m, N, CurrentFrame.mDescriptors, CurrentFrame.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+              Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
+    int nmatches = 0;
+    run_window(D.m, pack.p, CCM_WIN_PROJ_LASTFRAME, mfNNratio, ORBdist, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
+    for (int k = 0; k < N; k++)
+        if (holder[k] >= 0) CurrentFrame.mvpMapPoints[k] = vpMPs[holder[k]];
     return nmatches;
 }
 

@@ -159,6 +159,10 @@ class Exchange:
         self.m._check(self.m._lib.ccm_match_allpairs_best2_exchange_device(self.m._h, self._h, d_q, int(nq), d_targets, int(nt), int(index_base),
                                                                            float(nnratio), d_out, d_accept))
 
+    def check(self):
+        """Synchronises the stream; raises CcmError(CCM_E_CUDA) if a wait for a peer timed out (CCM_EXCHANGE_TIMEOUT_MS)."""
+        self.m._check(self.m._lib.ccm_exchange_check(self._h))
+
     def close(self):
         if self._h:
             self.m._lib.ccm_exchange_destroy(self._h)

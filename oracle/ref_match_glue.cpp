@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstring>
 #include <limits>
+#include <set>
 
 extern "C" void mo_frame_params(const void* fp, float* min_x, float* min_y, float* inv_w, float* inv_h, int* cols, int* rows);
 extern "C" void mo_frame_view(const void* fp, int* n, const uint8_t** desc, const float** x, const float** y, const int** octave, const float** angle);
@@ -153,6 +154,36 @@ int rm_search_projection_lastframe(const void* fp, int nq, const uint8_t* q_vali
     }
     ORBmatcher m(0.9f, check_orientation != 0);
     const int nm = m.SearchByProjection(*Cur, Last, th);
+    points_to_holder(Cur->mvpMapPoints, holder);
+    return nm;
+}
+
+/* ORBmatcher::SearchByProjection(Frame& Current, kfptr pKF, sAlreadyFound, th, ORBdist), ORBmatcher.cpp:1478-1605
+ * (relocalisation; no caller upstream). q_state: 0 = pKF has no map point at this feature, 1 = a good point, 2 = a bad
+ * point, 3 = a good point that is in sAlreadyFound. */
+int rm_search_projection_reloc(const void* fp, int nq, const uint8_t* q_state, const float* q_u, const float* q_v, const int* q_level,
+                               const float* q_angle, const uint8_t* q_desc, float th, int orb_dist, const float* scale_factors,
+                               int check_orientation, int* holder) {
+    boost::shared_ptr<Frame> Cur(new Frame());
+    make_frame(*Cur, fp, scale_factors, NLEV);
+    holder_to_points(holder, Cur->N, Cur->mvpMapPoints);
+    kfptr K(new KeyFrame());
+    K->N = nq;
+    K->mvKeysUn.resize(nq);
+    K->mvpMapPoints.assign(nq, mpptr());
+    std::set<mpptr> found;
+    for (int i = 0; i < nq; i++) {
+        K->mvKeysUn[i] = cv::KeyPoint(q_u[i], q_v[i], 31.f, q_angle[i], 0.f, q_level[i]);
+        if (!q_state[i]) continue;
+        mpptr p = make_mp(i, q_desc + (size_t)32 * i, 1);
+        p->bad = q_state[i] == 2;
+        p->predictedLevel = q_level[i];
+        set_world(p, q_u[i], q_v[i]);
+        if (q_state[i] == 3) found.insert(p);
+        K->mvpMapPoints[i] = p;
+    }
+    ORBmatcher m(0.9f, check_orientation != 0);
+    const int nm = m.SearchByProjection(*Cur, K, found, th, orb_dist);
     points_to_holder(Cur->mvpMapPoints, holder);
     return nm;
 }

@@ -299,6 +299,13 @@ class OracleMatcher:
                                                    holder.ctypes.data, res.ctypes.data)
         return nm, res
 
+    def projection_reloc(self, F, q_state, q_u, q_v, q_level, q_angle, q_desc, th, orb_dist, sf, holder):
+        """SearchByProjection(Frame&, kfptr, sAlreadyFound, th, ORBdist), ORBmatcher.cpp:1478-1605"""
+        st, u_, v_, l, a, d, s = (_a(q_state, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
+                                  _a(q_angle, np.float32), _a(q_desc, np.uint8), _a(sf, np.float32))
+        return self.L.rm_search_projection_reloc(F.h, len(u_), st.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data, a.ctypes.data,
+                                                 d.ctypes.data, th, int(orb_dist), s.ctypes.data, self.ori, holder.ctypes.data)
+
     def projection_kf_sim3(self, F, q_valid, q_u, q_v, q_level, q_desc, q_claims, th, sf, holder):
         n = len(q_u)
         res = np.zeros(n, RESULT_DTYPE)
@@ -400,6 +407,7 @@ class RefMatcher:
         L.rm_search_projection_mappoints.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _c.c_float, _vp, _vp]
         L.rm_search_projection_lastframe.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _vp, _i, _vp]
         L.rm_search_projection_kf_sim3.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp]
+        L.rm_search_projection_reloc.argtypes = [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _c.c_float, _i, _vp, _i, _vp]
         L.rm_search_bow_kf_frame.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _c.c_float, _i, _vp]
         L.rm_search_bow_kf_kf.argtypes = [_i, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp, _c.c_float, _i, _vp]
         L.rm_search_for_initialization.argtypes = [_i, _vp, _vp, _vp, _vp, _vp, _i, _c.c_float, _i, _vp]
@@ -438,6 +446,13 @@ class RefMatcher:
         return self.L.rm_search_projection_lastframe(F.h, len(u_), v.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data,
                                                      a.ctypes.data, d.ctypes.data, o.ctypes.data, th, s.ctypes.data, self.ori,
                                                      holder.ctypes.data)
+
+    def projection_reloc(self, F, q_state, q_u, q_v, q_level, q_angle, q_desc, th, orb_dist, sf, holder):
+        """SearchByProjection(Frame&, kfptr, sAlreadyFound, th, ORBdist), ORBmatcher.cpp:1478-1605"""
+        st, u_, v_, l, a, d, s = (_a(q_state, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
+                                  _a(q_angle, np.float32), _a(q_desc, np.uint8), _a(sf, np.float32))
+        return self.L.rm_search_projection_reloc(F.h, len(u_), st.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data, a.ctypes.data,
+                                                 d.ctypes.data, th, int(orb_dist), s.ctypes.data, self.ori, holder.ctypes.data)
 
     def projection_kf_sim3(self, F, q_valid, q_u, q_v, q_level, q_desc, q_claims, th, sf, holder):
         v, u_, v_, l, d, c, s = (_a(q_valid, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),

@@ -185,7 +185,7 @@ def test_device_resident_path_matches_host_path(cuda_lib):
 
 def test_device_buffers_tma_cannot_address_take_the_word_load_kernel(cuda_lib):
     """Level 0 is read in place from the caller's buffer. A pitch that is not a 16-byte multiple (756) or a base 4 bytes off a
-    16-byte boundary cannot be described to TMA: those calls run k_fast_cells<.., TMA = false> and must give the same frames."""
+    16-byte boundary cannot be described to TMA: those calls run k_fast_chunks<false> (word loads) and must give the same frames."""
     torch = pytest.importorskip("torch")
     from motioncheck_ccm_slam_b200.extractor import KP_DTYPE
     frames = make_stream(3100, 3)

@@ -368,6 +368,19 @@ def test_dropin_cpp_matcher_matches_reference_class(cuda_lib):
         nd = D.projection_lastframe(D.frame(b, grid), valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hd)
         nr = R.projection_lastframe(R.frame(b, grid), valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hr)
         assert nd == nr > 200 and np.array_equal(hd, hr)
+    # relocalisation overload (:1478-1605): every occupied feature blocks, bound = ORBdist, levels [l-1, l+1]
+    for seed, th, orb_dist, ori in [(51, 10.0, 100, True), (52, 3.0, 64, True), (53, 10.0, 100, False)]:
+        rng = np.random.default_rng(seed)
+        a, b, src = _frames(seed)
+        valid, u, v, level, _ = _projection_inputs(a, b, src, rng)
+        valid = inb(u, v, valid)
+        state = np.where(valid > 0, rng.choice([1, 1, 1, 1, 1, 1, 2, 3], len(u)), 0).astype(np.uint8)
+        holder0 = rng.choice([-1, -1, -1, -1, -2, -3], len(b["x"])).astype(np.int32)
+        D, R = pair(0.9, ori)
+        hd, hr = holder0.copy(), holder0.copy()
+        nd = D.projection_reloc(D.frame(b, grid), state, u, v, level, a["angle"], a["desc"], th, orb_dist, SF, hd)
+        nr = R.projection_reloc(R.frame(b, grid), state, u, v, level, a["angle"], a["desc"], th, orb_dist, SF, hr)
+        assert nd == nr > 150 and np.array_equal(hd, hr), (seed, nd, nr)
     for seed, th in [(41, 10), (42, 4)]:
         rng = np.random.default_rng(seed)
         a, b, src = _frames(seed, n=3000)
@@ -726,6 +739,38 @@ def test_allpairs_exchange_world1_equals_merge(gm):
         assert np.array_equal(d_out.cpu().numpy().view(BEST2_DTYPE), d_ref2.cpu().numpy().view(BEST2_DTYPE)), call
         assert np.array_equal(d_acc.cpu().numpy(), d_acc2.cpu().numpy())
     x.close()
+
+
+def test_allpairs_exchange_missing_peer_times_out(cuda_lib, monkeypatch):
+    """A rank whose peer never launches must not spin forever (the kernel cannot be cancelled from the host): the wait is
+    bounded, the call's results are "no match", and ccm_exchange_check reports CCM_E_CUDA."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200._lib import CCM_E_CUDA, CcmError
+    from motioncheck_ccm_slam_b200.matcher import BEST2_DTYPE, Exchange, Matcher
+    monkeypatch.setenv("CCM_EXCHANGE_TIMEOUT_MS", "50")
+    ms = [Matcher(0), Matcher(0)]                       # two ranks' contexts on one device: rank 1 never calls
+    xs = [Exchange(ms[r], r, 2, 512) for r in range(2)]
+    bufs = [x.buffer() for x in xs]
+    for x in xs:
+        x.connect_ptrs(bufs)
+    rng = np.random.default_rng(1)
+    nq, nt = 300, 5000
+    d_q = torch.from_numpy(rng.integers(0, 256, (nq, 32), dtype=np.uint8)).cuda()
+    d_t = torch.from_numpy(rng.integers(0, 256, (nt, 32), dtype=np.uint8)).cuda()
+    d_out = torch.zeros((nq, 8), dtype=torch.uint8, device="cuda")
+    d_acc = torch.ones(nq, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    xs[0].check()                                       # nothing happened yet
+    xs[0].allpairs_best2_device(d_q.data_ptr(), nq, d_t.data_ptr(), nt, 0, 0.6, d_out.data_ptr(), d_acc.data_ptr())
+    with pytest.raises(CcmError) as e:
+        xs[0].check()
+    assert e.value.code == CCM_E_CUDA and "peer rank did not publish" in str(e.value)
+    out = d_out.cpu().numpy().view(BEST2_DTYPE).reshape(-1)
+    assert np.all(out["idx"] == 0xFFFFFFFF) and np.all(out["d1"] == 256) and not d_acc.cpu().numpy().any()
+    for x in xs:
+        x.close()
+    for m in ms:
+        m.close()
 
 
 def test_allpairs_exchange_two_gpus(cuda_lib):
