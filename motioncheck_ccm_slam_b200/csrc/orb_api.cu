@@ -65,6 +65,12 @@ struct ccm_orb {
     } tk[CCM_MAX_TICKETS];
     int next_slot = 0, next_lane = 0;
     long long launches = 0;
+    // single-frame call (ccm_orb_extract, the call Frame::ExtractORB makes): the whole kernel sequence of one frame in arena
+    // slot 0 plus the copy-out into the pinned staging is ONE CUDA graph per (shape, level-0 pitch)
+    cudaGraphExec_t graph1 = nullptr;
+    size_t graph1_pitch = 0;
+    long long graph1_launches = 0;
+    bool graph1_failed = false;
     // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
     bool stage_timing = false;
     cudaEvent_t ev[CCM_N_STAGES + 1] = {};
@@ -223,6 +229,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     if (rows > h->cfg.max_height || cols > h->cfg.max_width) { h->err = "image larger than max_width x max_height of the handle"; return CCM_E_CAPACITY; }
     CK(cudaStreamSynchronize(h->stream));
     free_arena(h);
+    if (h->graph1) { cudaGraphExecDestroy(h->graph1); h->graph1 = nullptr; }
     h->rows = h->cols = 0;
     LevelTable& T = h->T;
     std::memset(&T, 0, sizeof(T));
@@ -510,6 +517,7 @@ void ccm_orb_destroy(ccm_orb* h) {
     cudaSetDevice(h->cfg.device);
     for (cudaStream_t st : {h->s_in, h->stream, h->lane[1].s, h->lane[0].aux, h->lane[1].aux, h->s_out}) if (st) cudaStreamSynchronize(st);
     free_arena(h);
+    if (h->graph1) cudaGraphExecDestroy(h->graph1);
     for (int i = 0; i <= CCM_N_STAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int t = 0; t < CCM_MAX_TICKETS; t++) {
         for (int i = 0; i < CCM_MAX_CHUNKS; i++) {
@@ -806,11 +814,79 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     return ccm_orb_extract_batch_wait(h, ticket);
 }
 
+// One frame, synchronously, as Frame::ExtractORB calls the extractor (cslam/src/Frame.cpp:120-123): copy-in, ONE graph launch
+// (memset, 7 resize levels, FAST, quadtree next to the blur, orientation + descriptors, copy-out of slot 0 into the pinned
+// staging), wait, hand the results over. The graph is captured from run_pipeline itself on first use, so it is the same
+// kernel sequence with the same arguments; every pointer in it is an arena address, which only changes with the shape.
+// Returns 1 when the fast path cannot be used (a batch in flight, capture unavailable): the caller takes the general path.
+static int extract_single_graph(ccm_orb* h, const uint8_t* img, int rows, int cols, size_t step, ccm_keypoint* out_kp, uint8_t* out_desc,
+                                int capacity, int* out_n) {
+    static const bool off = std::getenv("CCM_ORB_NO_GRAPH") != nullptr;
+    if (off || h->graph1_failed || h->stage_timing) return 1;
+    for (int i = 0; i < CCM_MAX_TICKETS; i++) if (h->tk[i].active) return 1;
+    if (capacity < 0 || (capacity > 0 && (!out_kp || !out_desc)) || step < (size_t)cols) { h->err = "bad argument"; return CCM_E_BADARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    int rc = configure_shape(h, rows, cols);
+    if (rc != CCM_OK) return rc;
+    uint8_t* l0 = (uint8_t*)h->allocs[0];
+    const size_t budget = (size_t)align_up(cols, 32);
+    const bool flat = (step % 4 == 0) && step <= budget;
+    const size_t pitch = flat ? step : budget;
+    cudaStream_t s = h->stream;
+    const int cap = h->max_kps;
+    if (!h->graph1 || h->graph1_pitch != pitch) {
+        if (h->graph1) { cudaGraphExecDestroy(h->graph1); h->graph1 = nullptr; }
+        CK(cudaStreamSynchronize(s));
+        const long long l_before = h->launches;
+        cudaGraph_t g = nullptr;
+        cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+        if (e == cudaSuccess) {
+            rc = run_pipeline(h, 1, l0, pitch, pitch * (size_t)rows, h->d_kp, h->d_desc, h->d_n, cap, 0, false, 0, true);
+            if (rc == CCM_OK) {
+                cudaMemcpyAsync(h->h_n, h->d_n, sizeof(int), cudaMemcpyDeviceToHost, s);
+                cudaMemcpyAsync(h->h_kp, h->d_kp, sizeof(ccm_keypoint) * (size_t)cap, cudaMemcpyDeviceToHost, s);
+                cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * cap, cudaMemcpyDeviceToHost, s);
+            }
+            e = cudaStreamEndCapture(s, &g);
+            if (e == cudaSuccess && rc == CCM_OK) e = cudaGraphInstantiate(&h->graph1, g, 0);
+            if (g) cudaGraphDestroy(g);
+        }
+        if (e != cudaSuccess || rc != CCM_OK || !h->graph1) {       // no graph on this driver / configuration: general path from now on
+            cudaGetLastError();
+            h->graph1 = nullptr; h->graph1_failed = true; h->launches = l_before;
+            return 1;
+        }
+        h->graph1_pitch = pitch;
+        h->graph1_launches = h->launches - l_before;
+        h->launches = l_before;
+    }
+    if (flat) CK(cudaMemcpyAsync(l0, img, step * (size_t)(rows - 1) + cols, cudaMemcpyHostToDevice, s));
+    else CK(cudaMemcpy2DAsync(l0, pitch, img, step, cols, rows, cudaMemcpyHostToDevice, s));
+    CK(cudaGraphLaunch(h->graph1, s));
+    h->launches += h->graph1_launches;
+    h->last_l0 = l0; h->last_l0_pitch = pitch; h->last_l0_stride = pitch * (size_t)rows; h->last_frames = 1;
+    h->T.l[0].img = l0; h->T.l[0].img_pitch = (int)pitch; h->T.l[0].img_stride = pitch * (size_t)rows;
+    h->next_slot = 0; h->next_lane = 0;
+    CK(cudaStreamSynchronize(s));
+    const int cnt = h->h_n[0];
+    *out_n = cnt;
+    const int k = std::min(std::min(cnt, capacity), cap);
+    if (k > 0) {
+        std::memcpy(out_kp, h->h_kp, sizeof(ccm_keypoint) * (size_t)k);
+        std::memcpy(out_desc, h->h_desc, (size_t)32 * k);
+    }
+    return CCM_OK;
+}
+
 int ccm_orb_extract(ccm_orb* h, const uint8_t* img, int rows, int cols, size_t step, ccm_keypoint* out_kp, uint8_t* out_desc,
                     int capacity, int* out_n) {
     if (!h) return CCM_E_BADARG;
     if (!out_n) { h->err = "bad argument"; return CCM_E_BADARG; }
     if (!img || rows == 0 || cols == 0) { *out_n = 0; return CCM_OK; }   // ORBextractor.cpp:1219-1220
+    if (rows > 0 && cols > 0) {
+        const int rc = extract_single_graph(h, img, rows, cols, step, out_kp, out_desc, capacity, out_n);
+        if (rc != 1) return rc;
+    }
     const uint8_t* one[1] = {img};
     return ccm_orb_extract_batch(h, one, 1, rows, cols, step, out_kp, out_desc, capacity, out_n);
 }

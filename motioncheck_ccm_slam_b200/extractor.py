@@ -79,8 +79,25 @@ class ORBextractor:
     # -- operator() (ORBextractor.cpp:1216-1278). mask is ignored, as in the reference (ORBextractor.h:109-111) --
     def __call__(self, image, mask=None):
         """image: uint8 [H, W] (any row stride). Returns (keypoints structured array, descriptors uint8 [N, 32])."""
-        kps, descs = self.extract_batch([image])
-        return kps[0], descs[0]
+        im = np.asarray(image)
+        if im.dtype != np.uint8 or im.ndim != 2:
+            raise TypeError("images must be 2-D uint8 (CV_8UC1), as ORBextractor.cpp:1223 asserts")
+        rows, cols = im.shape
+        if rows == 0 or cols == 0:      # ORBextractor.cpp:1219-1220: empty image, outputs untouched
+            return np.zeros(0, KP_DTYPE), np.zeros((0, 32), np.uint8)
+        if im.strides[1] != 1:
+            raise ValueError("unit pixel stride expected")
+        cap = self.max_keypoints_for(rows, cols)
+        kp = np.zeros(cap, dtype=KP_DTYPE)
+        desc = np.zeros((cap, 32), dtype=np.uint8)
+        cnt = ctypes.c_int()
+        self._check(self._lib.ccm_orb_extract(self._h, im.ctypes.data, rows, cols, im.strides[0], kp.ctypes.data, desc.ctypes.data, cap,
+                                              ctypes.byref(cnt)))
+        return kp[:cnt.value].copy(), desc[:cnt.value].copy()
+
+    def extract_raw(self, img_ptr, rows, cols, step, out_kp_ptr, out_desc_ptr, capacity, out_n):
+        """ccm_orb_extract (one frame, synchronous: the call Frame::ExtractORB makes) with caller-owned host buffers."""
+        self._check(self._lib.ccm_orb_extract(self._h, img_ptr, rows, cols, step, out_kp_ptr, out_desc_ptr, capacity, out_n))
 
     def extract_batch(self, images):
         """images: sequence of uint8 [H, W] arrays of one size (or one [B, H, W] array). Host in, host out."""

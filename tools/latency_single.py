@@ -21,12 +21,14 @@ for mb in (1, 8):
     ode = torch.zeros((1, cap, 32), dtype=torch.uint8).pin_memory()
     on = (ctypes.c_int * 1)()
     ptrs = [(ctypes.c_void_p * 1)(pn[f].ctypes.data) for f in range(16)]
-    for i in range(20):
-        ex.extract_batch_raw(ptrs[i % 16], 1, h, w, w, okp.data_ptr(), ode.data_ptr(), cap, on)
-    t0 = time.perf_counter()
     N = 300
-    for i in range(N):
-        ex.extract_batch_raw(ptrs[i % 16], 1, h, w, w, okp.data_ptr(), ode.data_ptr(), cap, on)
-    dt = time.perf_counter() - t0
-    print("max_batch %d: %.1f us per frame, %.0f frames/s, %d keypoints" % (mb, 1e6 * dt / N, N / dt, on[0]))
+    for name, call in (("ccm_orb_extract (graph)", lambda i: ex.extract_raw(pn[i % 16].ctypes.data, h, w, w, okp.data_ptr(), ode.data_ptr(), cap, on)),
+                       ("ccm_orb_extract_batch n=1", lambda i: ex.extract_batch_raw(ptrs[i % 16], 1, h, w, w, okp.data_ptr(), ode.data_ptr(), cap, on))):
+        for i in range(20):
+            call(i)
+        t0 = time.perf_counter()
+        for i in range(N):
+            call(i)
+        dt = time.perf_counter() - t0
+        print("max_batch %d, %s: %.1f us per frame, %.0f frames/s, %d keypoints" % (mb, name, 1e6 * dt / N, N / dt, on[0]))
     ex.close()
