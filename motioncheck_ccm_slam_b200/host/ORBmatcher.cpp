@@ -16,7 +16,9 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <mutex>
+#include <tuple>
 
 #include "ccm_match.h"
 
@@ -37,12 +39,49 @@ Device& device() {
     return d;
 }
 
-// Device copy of what the matcher reads of a Frame / KeyFrame. Built per call here; a production build caches it on the
-// object (one upload per Frame / KeyFrame) as INTEGRATION.md describes.
+// Device copy of what the matcher reads of a Frame / KeyFrame (descriptors, undistorted keypoints, the feature grid).
+// Tracking searches the same Frame two or three times per image and LoopFinder / MapMatcher hit the same KeyFrame many
+// times, so packs live in a small LRU side table keyed by the object's identity: Frame::mId / KeyFrame::mId
+// (Frame.h:156, KeyFrame.h:282; copies of a Frame share the id and the features), the feature count and a checksum of a
+// few descriptor rows and keypoints. A hit costs no upload and no grid build. CCM_ORB_PACK_CACHE = entries (default 16,
+// 0 = one pack per call as before); ccm_dropin_pack_cache_clear() drops everything (e.g. from a map reset).
+struct PackKey {
+    int kind; size_t id0, id1; int n; uint64_t sum;
+    bool operator<(const PackKey& o) const {
+        return std::tie(kind, id0, id1, n, sum) < std::tie(o.kind, o.id0, o.id1, o.n, o.sum);
+    }
+};
+struct PackEntry { ccm_frame_pack* p = nullptr; unsigned long long used = 0; };
+struct PackCache {
+    std::map<PackKey, PackEntry> m;
+    unsigned long long tick = 0, hits = 0, misses = 0;
+    int capacity = -1;
+};
+PackCache& pack_cache() { static PackCache c; return c; }
+
+uint64_t fnv(uint64_t h, const void* p, size_t n) {
+    const unsigned char* b = (const unsigned char*)p;
+    for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+    return h;
+}
+
 struct Pack {
     ccm_frame_pack* p = nullptr;
-    Pack(ccm_matcher* m, int n, const cv::Mat& desc, const std::vector<cv::KeyPoint>& keysUn, float minX, float minY, float invW,
-         float invH, int cols, int rows) {
+    bool owned = true;
+    // kind: 0 Frame, 1 KeyFrame; id: the object's mId
+    Pack(ccm_matcher* m, int kind, const std::pair<size_t, size_t>& id, int n, const cv::Mat& desc, const std::vector<cv::KeyPoint>& keysUn,
+         float minX, float minY, float invW, float invH, int cols, int rows) {
+        PackCache& C = pack_cache();
+        if (C.capacity < 0) { const char* e = std::getenv("CCM_ORB_PACK_CACHE"); C.capacity = e ? std::max(0, std::atoi(e)) : 16; }
+        PackKey key = {kind, id.first, id.second, n, 0};
+        if (C.capacity > 0 && n > 0) {
+            uint64_t h = 1469598103934665603ull;
+            for (int r : {0, n / 2, n - 1}) { h = fnv(h, desc.ptr(r), 32); h = fnv(h, &keysUn[r].pt, sizeof(keysUn[r].pt)); h = fnv(h, &keysUn[r].octave, sizeof(int)); }
+            const float gp[4] = {minX, minY, invW, invH};
+            key.sum = fnv(h, gp, sizeof(gp));
+            std::map<PackKey, PackEntry>::iterator it = C.m.find(key);
+            if (it != C.m.end()) { it->second.used = ++C.tick; C.hits++; p = it->second.p; owned = false; return; }
+        }
         const int cap = n > 0 ? n : 1;
         if (ccm_frame_pack_create(m, cap, &p) != CCM_OK) throw estd::infrastructure_ex();
         std::vector<float> x(cap), y(cap), ang(cap);
@@ -57,8 +96,20 @@ struct Pack {
             ccm_frame_pack_destroy(p);
             throw estd::infrastructure_ex();
         }
+        if (C.capacity > 0 && n > 0) {
+            C.misses++;
+            if ((int)C.m.size() >= C.capacity) {                      // evict the least recently used pack
+                std::map<PackKey, PackEntry>::iterator lru = C.m.begin();
+                for (std::map<PackKey, PackEntry>::iterator it = C.m.begin(); it != C.m.end(); ++it) if (it->second.used < lru->second.used) lru = it;
+                ccm_frame_pack_destroy(lru->second.p);
+                C.m.erase(lru);
+            }
+            PackEntry e; e.p = p; e.used = ++C.tick;
+            C.m[key] = e;
+            owned = false;
+        }
     }
-    ~Pack() { ccm_frame_pack_destroy(p); }
+    ~Pack() { if (owned && p) ccm_frame_pack_destroy(p); }
     Pack(const Pack&) = delete;
     Pack& operator=(const Pack&) = delete;
 };
@@ -134,7 +185,7 @@ int ORBmatcher::SearchByProjection(Frame &F, const vector<mpptr> &vpMapPoints, c
         if (F.mvpMapPoints[k]) holder[k] = F.mvpMapPoints[k]->Observations() > 0 ? -2 : -3;
     Device& D = device();
     std::lock_guard<std::mutex> g(D.mu);
-    Pack pack(D.m, F.N, F.mDescriptors, F.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+    Pack pack(D.m, 0, F.mId, F.N, F.mDescriptors, F.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
               Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
     int nmatches = 0;
     run_window(D.m, pack.p, CCM_WIN_PROJ_MAPPOINTS, mfNNratio, TH_HIGH, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
@@ -176,7 +227,7 @@ int ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, 
     const std::vector<int> before = holder;
     Device& D = device();
     std::lock_guard<std::mutex> g(D.mu);
-    Pack pack(D.m, N, CurrentFrame.mDescriptors, CurrentFrame.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+    Pack pack(D.m, 0, CurrentFrame.mId, N, CurrentFrame.mDescriptors, CurrentFrame.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
               Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
     int nmatches = 0;
     run_window(D.m, pack.p, CCM_WIN_PROJ_LASTFRAME, mfNNratio, TH_HIGH, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
@@ -227,7 +278,7 @@ int ORBmatcher::SearchByProjection(Frame &CurrentFrame, kfptr pKF, const set<mpp
         if (CurrentFrame.mvpMapPoints[k]) holder[k] = -2;
     Device& D = device();
     std::lock_guard<std::mutex> g(D.mu);
-    Pack pack(D.m, N, CurrentFrame.mDescriptors, CurrentFrame.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+    Pack pack(D.m, 0, CurrentFrame.mId, N, CurrentFrame.mDescriptors, CurrentFrame.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
               Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
     int nmatches = 0;
     run_window(D.m, pack.p, CCM_WIN_PROJ_LASTFRAME, mfNNratio, ORBdist, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
@@ -277,7 +328,7 @@ int ORBmatcher::SearchByProjection(kfptr pKF, cv::Mat Scw, const vector<mpptr> &
     std::vector<ccm_match_result> res(nq > 0 ? nq : 1);
     Device& D = device();
     std::lock_guard<std::mutex> g(D.mu);
-    Pack pack(D.m, N, pKF->mDescriptors, pKF->mvKeysUn, (float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv,
+    Pack pack(D.m, 1, pKF->mId, N, pKF->mDescriptors, pKF->mvKeysUn, (float)pKF->mnMinX, (float)pKF->mnMinY, pKF->mfGridElementWidthInv,
               pKF->mfGridElementHeightInv, pKF->mnGridCols, pKF->mnGridRows);
     int nmatches = 0;
     run_window(D.m, pack.p, CCM_WIN_PROJ_KF_SIM3, mfNNratio, TH_LOW, mbCheckOrientation, q, qd, holder.data(), res.data(), nmatches);
@@ -430,7 +481,7 @@ int ORBmatcher::SearchForInitialization(Frame &F1, Frame &F2, vector<cv::Point2f
     std::vector<int> holder(n2 > 0 ? n2 : 1, -1);           // vnMatches21, output only
     Device& D = device();
     std::lock_guard<std::mutex> g(D.mu);
-    Pack pack(D.m, n2, F2.mDescriptors, F2.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
+    Pack pack(D.m, 0, F2.mId, n2, F2.mDescriptors, F2.mvKeysUn, Frame::mnMinX, Frame::mnMinY, Frame::mfGridElementWidthInv,
               Frame::mfGridElementHeightInv, FRAME_GRID_COLS, FRAME_GRID_ROWS);
     int nmatches = 0;
     run_window(D.m, pack.p, CCM_WIN_INIT, mfNNratio, TH_LOW, mbCheckOrientation, q, qd, holder.data(), nullptr, nmatches);
@@ -453,7 +504,7 @@ namespace {
 struct KfPack {
     Pack pack;
     KfPack(ccm_matcher* m, const boost::shared_ptr<cslam::KeyFrame>& k)
-        : pack(m, k->N, k->mDescriptors, k->mvKeysUn, (float)k->mnMinX, (float)k->mnMinY, k->mfGridElementWidthInv,
+        : pack(m, 1, k->mId, k->N, k->mDescriptors, k->mvKeysUn, (float)k->mnMinX, (float)k->mnMinY, k->mfGridElementWidthInv,
                k->mfGridElementHeightInv, k->mnGridCols, k->mnGridRows) {}
 };
 inline void set_query(ccm_window_query& q, float u, float v, float r, int lvl) {
@@ -646,3 +697,16 @@ int ORBmatcher::SearchBySim3(kfptr pKF1, kfptr pKF2, vector<mpptr> &vpMatches12,
 }
 
 }  // namespace cslam
+
+// Drops every cached frame pack (call it on a map reset, or from ~Frame / ~KeyFrame if device memory is tight), and
+// reports the cache's hit / miss counters since the last clear.
+extern "C" void ccm_dropin_pack_cache_clear(unsigned long long* hits, unsigned long long* misses) {
+    Device& D = device();
+    std::lock_guard<std::mutex> g(D.mu);
+    PackCache& C = pack_cache();
+    if (hits) *hits = C.hits;
+    if (misses) *misses = C.misses;
+    for (std::map<PackKey, PackEntry>::iterator it = C.m.begin(); it != C.m.end(); ++it) ccm_frame_pack_destroy(it->second.p);
+    C.m.clear();
+    C.hits = C.misses = 0;
+}

@@ -23,6 +23,7 @@ public:
     typedef boost::shared_ptr<MapPoint> mpptr;
     typedef boost::shared_ptr<KeyFrame> kfptr;
     void* grid = nullptr;                    /* MoFrame of oracle/match_oracle.cpp */
+    std::pair<size_t, size_t> mId = {0, 0};  /* idpair mId, Frame.h:156 */
     std::vector<size_t> GetFeaturesInArea(const float& x, const float& y, const float& r, const int minLevel = -1, const int maxLevel = -1) const {
         std::vector<int> tmp(N > 0 ? N : 1);
         const int k = mo_features_in_area(grid, x, y, r, minLevel, maxLevel, 0, tmp.data(), (int)tmp.size());

@@ -13,6 +13,7 @@ class KeyFrame {
 public:
     typedef boost::shared_ptr<MapPoint> mpptr;
     void* grid = nullptr;
+    std::pair<size_t, size_t> mId = {0, 0};  /* idpair mId, KeyFrame.h:282 */
     int N = 0;
     float fx = 1, fy = 1, cx = 0, cy = 0;
     float minX = 0, maxX = 0, minY = 0, maxY = 0;       /* IsInImage bounds of the mock */

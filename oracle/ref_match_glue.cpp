@@ -42,8 +42,17 @@ void fill_common(const void* fp, int& N, std::vector<cv::KeyPoint>& keysUn, cv::
     desc = desc_mat(d, N);
 }
 
+/* Identity of the objects built from one frame handle: the same handle searched again is the same Frame / KeyFrame
+ * (the drop-in keys its device packs on mId). rm_set_unique_ids(1) gives every object its own id instead. */
+static bool g_unique_ids = false;
+static size_t g_next_id = 1;
+std::pair<size_t, size_t> object_id(const void* fp, size_t kind) {
+    return g_unique_ids ? std::make_pair(g_next_id++, (size_t)99) : std::make_pair((size_t)(uintptr_t)fp, kind);
+}
+
 void make_frame(Frame& F, const void* fp, const float* sf, int nlevels) {
     fill_common(fp, F.N, F.mvKeysUn, F.mDescriptors);
+    F.mId = object_id(fp, 1);
     F.mvKeys = F.mvKeysUn;
     F.grid = const_cast<void*>(fp);
     {   /* static image bounds / grid pitch as Frame.cpp:80-88 would set them for this grid */
@@ -61,6 +70,7 @@ void make_frame(Frame& F, const void* fp, const float* sf, int nlevels) {
 kfptr make_kf(const void* fp, const float* sf, int nlevels) {
     kfptr K(new KeyFrame());
     fill_common(fp, K->N, K->mvKeysUn, K->mDescriptors);
+    K->mId = object_id(fp, 2);
     K->grid = const_cast<void*>(fp);
     K->mvpMapPoints.assign(K->N, mpptr());
     {
@@ -109,6 +119,8 @@ const int NLEV = 8;
 }  // namespace
 
 extern "C" {
+
+void rm_set_unique_ids(int on) { g_unique_ids = on != 0; }
 
 int rm_descriptor_distance(const uint8_t* a, const uint8_t* b) { return ORBmatcher::DescriptorDistance(desc_mat(a, 1), desc_mat(b, 1)); }
 

@@ -417,6 +417,42 @@ def test_dropin_cpp_matcher_matches_reference_class(cuda_lib):
     assert np.array_equal(D.descriptor_distance(x, y), R.descriptor_distance(x, y))
 
 
+def test_dropin_cpp_frame_pack_cache(cuda_lib):
+    """The drop-in keeps the device pack of a Frame / KeyFrame in an LRU side table keyed by mId: a frame searched three
+    times is uploaded once, different frames never share a pack, and every result still equals the reference class."""
+    import ctypes
+    import _oracle
+    if not (_oracle.dropin_match_available() and _oracle.ref_match_available()):
+        pytest.skip("oracle/_ref/libdropin_match.so not built (needs the reference headers at build time)")
+    from motioncheck_ccm_slam_b200.matcher import frame_grid
+    grid = frame_grid(W, H)
+    D, R = _oracle.RefMatcher(0.9, True, lib="libdropin_match.so"), _oracle.RefMatcher(0.9, True)
+    hits, misses = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    D.L.ccm_dropin_pack_cache_clear(ctypes.byref(hits), ctypes.byref(misses))
+    frames = []
+    for seed in (31, 32):
+        rng = np.random.default_rng(seed)
+        a, b, src = _frames(seed)
+        valid, u, v, level, obs = _projection_inputs(a, b, src, rng)
+        valid &= ((u >= 0) & (u <= W) & (v >= 0) & (v <= H)).astype(np.uint8)
+        frames.append((a, D.frame(b, grid), R.frame(b, grid), valid, u, v, level, obs, len(b["x"])))
+    for rep in range(3):                                   # the same two frames again: hits from the second round on
+        for a, fd, fr, valid, u, v, level, obs, nb in frames:
+            for th in (7.0, 14.0):
+                hd, hr = np.full(nb, -1, np.int32), np.full(nb, -1, np.int32)
+                nd = D.projection_lastframe(fd, valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hd)
+                nr = R.projection_lastframe(fr, valid, u, v, a["octave"], a["angle"], a["desc"], obs, th, SF, hr)
+                assert nd == nr > 200 and np.array_equal(hd, hr), (rep, th)
+            viewcos = np.full(len(u), 0.9, np.float32)
+            hd, hr = np.full(nb, -1, np.int32), np.full(nb, -1, np.int32)
+            D.nnratio = R.nnratio = float(np.float32(0.8))
+            nd = D.projection_mappoints(fd, valid, u, v, level, viewcos, a["desc"], obs, 1.0, SF, hd)
+            nr = R.projection_mappoints(fr, valid, u, v, level, viewcos, a["desc"], obs, 1.0, SF, hr)
+            assert nd == nr and np.array_equal(hd, hr)
+    D.L.ccm_dropin_pack_cache_clear(ctypes.byref(hits), ctypes.byref(misses))
+    assert misses.value == 2 and hits.value == 3 * 2 * 3 - 2, (hits.value, misses.value)
+
+
 def test_dropin_cpp_fuse_and_sim3_match_reference_class(cuda_lib):
     """Drop-in Fuse (both overloads) and SearchBySim3 — candidate search on the device (CCM_WIN_BEST), map mutations
     replayed on the host — against the reference's own bodies (ORBmatcher.cpp:854-1348) through the same glue: the same
