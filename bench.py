@@ -63,6 +63,33 @@ def algorithmic_bytes(w, h, nfeatures, nlevels):
     return per, pipeline
 
 
+def issue_roofline(workload, B, stage_ms, sms, w, h, nl):
+    """The roofline the kernels actually live under: warp instructions per launch (from the committed ncu --set full capture,
+    profiles/issue.json) / (SMs x 4 schedulers x SM clock x the stage's live event time)."""
+    p = os.path.join(ROOT, "profiles", "issue.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        ij = json.load(f)
+    if ij.get("workload") != workload or ij.get("frames_per_launch") != B:
+        return None
+    px = sum(a * b for a, b in level_sizes(w, h, nl)) * B
+    mhz = float(ij.get("sm_mhz", 1965.0))
+    out = {"source": ij.get("source"), "unit": "fraction of issue slots (SMs x 4 x %.0f MHz)" % mhz, "stages": {}}
+    tot_i = tot_slots = 0.0
+    for st, wi in ij["warp_instructions"].items():
+        ms = stage_ms.get(st, 0.0)
+        if ms <= 0:
+            continue
+        slots = sms * 4 * mhz * 1e6 * ms * 1e-3
+        out["stages"][st] = {"warp_instructions": wi, "frac": wi / slots, "thread_instructions_per_pixel": 32.0 * wi / px}
+        tot_i += wi; tot_slots += slots
+    out["warp_instructions_per_step"] = tot_i
+    out["frac"] = tot_i / tot_slots if tot_slots else None
+    out["budget"] = ij.get("budget")
+    return out
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -247,8 +274,9 @@ def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d
         same = bool(torch.equal(d_best, d_best_x) and torch.equal(d_acc, d_acc_x))
         if not same:
             raise SystemExit("fused exchange search differs from all_gather + merge on rank %d" % rank)
-        collective = ("fused in the search kernel: %d B per rank stored into every peer's buffer over NVLink + flags; "
-                      "nccl all_gather + merge kernel beside it: %.4f ms on rank 0 (identical result)" % (nq * 8, nccl_ms))
+        xch.check()                                       # raises if a wait for a peer ever timed out
+        collective = ("chunk fold + peer-memory exchange + merge in ONE kernel after the search launches: %d B per rank stored into every "
+                      "peer's buffer over NVLink + flags; nccl all_gather + merge kernel beside it: %.4f ms on rank 0 (identical result)" % (nq * 8, nccl_ms))
         out["_ap_nccl_ms"] = nccl_ms
     out["_ap_ms"] = ap_ms
     out["allpairs"] = {"nq": nq, "nt_total": nt_total, "nt_per_gpu": hi - lo, "steps": ksteps,
@@ -357,8 +385,10 @@ def hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d
     return out
 
 
-def cpu_matcher_baseline(frames, nf, nl, n_pairs=6):
-    """Oracle port of the two tracking-side searches, single thread, on consecutive frames of the same stream."""
+def cpu_matcher_baseline(frames, nf, nl, n_frames=8):
+    """The two tracking-side searches of the GPU leg on the reference's own ORBmatcher.cpp (oracle/_ref/libref_match.so), one
+    thread, SAME queries as hamming_legs: frame t searched with frame t-1's points moved by (-2,-1) (LastFrame, th 7) and with
+    frame t-2's points moved by (-4,-2) (MapPoints, th 1). Falls back to the oracle port when the library is not built."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle
     from motioncheck_ccm_slam_b200.matcher import frame_grid
@@ -366,20 +396,27 @@ def cpu_matcher_baseline(frames, nf, nl, n_pairs=6):
     ex = _oracle.OracleExtractor(nf, SCALE, nl, INI_TH, MIN_TH)
     sf = ex.tables()[0][0]
     grid = frame_grid(w, h)
-    ext = [ex(frames[i]) for i in range(n_pairs + 1)]
-    om = _oracle.OracleMatcher(0.9, True)
+    ext = [ex(frames[i]) for i in range(n_frames)]
+    ref = _oracle.ref_match_available()
+    M9, M8 = (_oracle.RefMatcher(0.9, True), _oracle.RefMatcher(0.8, True)) if ref else (_oracle.OracleMatcher(0.9, True), _oracle.OracleMatcher(0.8, True))
+    mk = (lambda k, d: M9.frame(dict(desc=d, x=k["x"], y=k["y"], octave=k["octave"], angle=k["angle"]), grid)) if ref else \
+         (lambda k, d: _oracle.OracleFrame(d, k["x"], k["y"], k["octave"], k["angle"], grid))
+    Fs = [mk(*ext[i]) for i in range(n_frames)]
     t0 = time.perf_counter()
-    nm = 0
-    for i in range(n_pairs):
-        (k0, d0), (k1, d1) = ext[i], ext[i + 1]
-        F = _oracle.OracleFrame(d1, k1["x"], k1["y"], k1["octave"], k1["angle"], grid)
-        hold = np.full(len(k1), -1, np.int32)
-        one = np.ones(len(k0), np.uint8)
-        nm += om.projection_lastframe(F, one, k0["x"] - 2, k0["y"] - 1, k0["octave"], k0["angle"], d0, one, 7.0, sf, hold)[0]
+    nm1 = nm2 = 0
+    for i in range(2, n_frames):
+        (k1, d1), (k2, d2) = ext[i - 1], ext[i - 2]
+        hold = np.full(len(ext[i][0]), -1, np.int32)
+        one = np.ones(len(k1), np.uint8)
+        r = M9.projection_lastframe(Fs[i], one, k1["x"] - 2, k1["y"] - 1, k1["octave"], k1["angle"], d1, one, 7.0, sf, hold)
+        nm1 += r if ref else r[0]
         hold[:] = -1
-        nm += om.projection_mappoints(F, one, k0["x"] - 2, k0["y"] - 1, k0["octave"], one.astype(np.float32), d0, one, 1.0, sf, hold)[0]
+        one = np.ones(len(k2), np.uint8)
+        r = M8.projection_mappoints(Fs[i], one, k2["x"] - 4, k2["y"] - 2, k2["octave"], one.astype(np.float32), d2, one, 1.0, sf, hold)
+        nm2 += r if ref else r[0]
     dt = time.perf_counter() - t0
-    return n_pairs / dt, nm / n_pairs
+    n = n_frames - 2
+    return n / dt, nm1 / n, nm2 / n, "reference" if ref else "port"
 
 
 def cpu_allpairs_baseline(nq=64, nt=200000):
@@ -540,14 +577,26 @@ def run_ours(args, wl, rank, world, local_rank):
     clocks = sampler.stop() if rank == 0 else None
     n_kp_host = int(sum(out_n[:]))
 
+    import bench_legs
+    # the e2e copy pattern alone, every rank at once: what the host link of this box allows for this traffic
+    link_ms = bench_legs.link_ceiling(torch, dev, B, w, h, cap, max(10, min(args.steps, 50)), barrier)
+    barrier()
+    single, single_launches = (bench_legs.single_frame(torch, local_rank, w, h, nf, nl, frames[0]) if rank == 0 else ({}, 0))
+    barrier()
+
     ham = None
     if not args.no_match:
         ham = hamming_legs(args, torch, dist, dev, rank, world, ex, ext, d_frames, d_kp, d_desc, d_n, cap, w, h, pitch, barrier)
-    t = torch.tensor([dev_ms, e2e_s * 1e3, ham["_ap_ms"] if ham else 0.0, ham["_tr_ms"] if ham else 0.0],
+        c4, c4_launches = bench_legs.c4_leg(torch, dist, rank, world, local_rank, barrier, ham["_voc"], nf, nl, w, h)
+        ham["c4"] = c4; ham["_launches"] += c4_launches
+        if rank == 0:
+            ham["searches"], n_calls = bench_legs.searches_leg(calls=64)
+        barrier()
+    t = torch.tensor([dev_ms, e2e_s * 1e3, ham["_ap_ms"] if ham else 0.0, ham["_tr_ms"] if ham else 0.0, link_ms],
                      dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)          # max over ranks
-    dev_ms, e2e_ms, ap_ms, tr_ms = float(t[0]), float(t[1]), float(t[2]), float(t[3])
+    dev_ms, e2e_ms, ap_ms, tr_ms, link_ms = float(t[0]), float(t[1]), float(t[2]), float(t[3]), float(t[4])
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -568,6 +617,8 @@ def run_ours(args, wl, rank, world, local_rank):
             tj = json.load(f)
         if tj.get("workload") == args.workload and tj.get("frames_per_launch") == B:   # only for the captured configuration
             traffic = tj["bytes"].get(STAGES[dom])
+    issue = issue_roofline(args.workload, B, dict(zip(STAGES, per_launch_ms)), torch.cuda.get_device_properties(dev).multi_processor_count,
+                           w, h, nl)
     line = {
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -582,14 +633,20 @@ def run_ours(args, wl, rank, world, local_rank):
                      "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": per_launch_ms[dom]},
         "roofline_pipeline": {"bound": "hbm", "achieved": value / world * pipeline_bytes / 1e9, "peak": peak, "unit": "GB/s",
                               "frac": value / world * pipeline_bytes / 1e9 / peak, "algorithmic_bytes_per_frame": pipeline_bytes},
+        "roofline_issue": issue,
         "stage_ms_per_step": dict(zip(STAGES, per_launch_ms)),
         "e2e": {"value": e2e, "unit": "frames/s", "h2d_bytes_per_step": B * w * h,
                 "d2h_bytes_per_step": B * cap * 56 + 4 * B, "keypoints_per_frame": n_kp_host / B,
                 "api": "ccm_orb_extract_batch_submit / _wait, two batches in flight (copy-in of batch i+1 overlaps the kernels of batch i)",
-                "synchronous_call_frames_per_s": B * args.steps / e2e_sync_s, "host_numa_node_rank0": numa_node},
-        "gpu_launches": int(launches),
+                "synchronous_call_frames_per_s": B * args.steps / e2e_sync_s, "host_numa_node_rank0": numa_node,
+                "h2d_ceiling_frames_per_s": B * world / (link_ms * 1e-3), "frac_of_link_ceiling": e2e / (B * world / (link_ms * 1e-3)),
+                "link_ceiling": "the same copies with no kernel in between (pinned host -> device on one stream, device -> pinned host on another), "
+                                "all %d ranks at once, max over ranks: %.3f ms per step; the limiter of the host entry point is cudaMemcpyAsync "
+                                "from pinned host memory, there is no collective on this path" % (world, link_ms)},
+        "gpu_launches": int(launches) + int(single_launches),
         "clocks": clocks,
     }
+    line["e2e"].update(single)
     if ham:
         sms = torch.cuda.get_device_properties(dev).multi_processor_count
         sm_max = (clocks or {}).get("sm_max_mhz") or 1965.0
@@ -598,8 +655,10 @@ def run_ours(args, wl, rank, world, local_rank):
         ham["allpairs"].update({"gpairs_per_s": gp, "ms_per_query_keyframe": ap_ms})
         ham["allpairs"]["roofline"] = {
             "bound": "int-pipe (POPC)", "achieved": gp / world, "peak": peak_pairs, "unit": "Gpair/s per GPU", "frac": gp / world / peak_pairs,
-            "peak_kind": "SMs x 16 POPC/clk (measured 15.9, profiles/r1_ubench_int.json) x %.0f MHz / 8 POPC per pair; the kernel's carry-save "
-                         "LOP3 tree needs 4 POPC per pair, so frac can exceed 1 (microbenchmarked ceiling of that loop: 680 Gpair/s)" % sm_max}
+            "peak_kind": "textbook loop, 8 POPC per pair: SMs x 16 POPC/clk (measured 15.9, profiles/r1_ubench_int.json) x %.0f MHz / 8. The kernel's "
+                         "carry-save LOP3 tree needs 4 POPC per pair, so frac exceeds 1 against this denominator" % sm_max,
+            "frac_of_4popc_bound": gp / world / (2 * peak_pairs),
+            "own_bound": "4 POPC + 18 LOP3/XOR + 3 min/max per pair: POPC bound %.0f Gpair/s per GPU; ncu (profiles/r1q): ALU pipe 83 %% busy" % (2 * peak_pairs)}
         ham["tracking"].update({"frames_per_s": B * world / (tr_ms * 1e-3), "ms_per_step": tr_ms})
         line["hamming"] = {k: v for k, v in ham.items() if not k.startswith("_")}
         line["gpu_launches"] += int(ham["_launches"])
@@ -607,8 +666,12 @@ def run_ours(args, wl, rank, world, local_rank):
         cores = os.cpu_count() or 1
         fpt = 48                                             # ~15 s of CPU work on 16 threads
         fps, dt, kind = cpu_reference_fps(frames[0], nf, nl, cores, fpt)
+        fps1, dt1, _ = cpu_reference_fps(frames[0], nf, nl, 1, 96)      # how the reference runs: one spinOnce thread per agent (ClientNode.cpp:48-52)
         line["cpu_baseline"] = {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
-                                "sample": "%d threads x %d frames of the same stream, %.1f s" % (cores, fpt, dt)}
+                                "sample": "%d threads x %d frames of the same stream, %.1f s" % (cores, fpt, dt),
+                                "single_thread": {"value": fps1, "unit": "frames/s", "cores": 1, "sample": "96 frames, %.1f s" % dt1},
+                                "note": "cslam/src/ORBextractor.cpp compiled unmodified over a scalar restatement of the five OpenCV primitives "
+                                        "(oracle/cv_primitives.cpp, no SIMD): an upper bound on the speed-up over a production OpenCV build"}
         if ham:
             sys.path.insert(0, os.path.join(ROOT, "tests"))
             from _oracle import oracle_vocab_transform
@@ -618,10 +681,12 @@ def run_ours(args, wl, rank, world, local_rank):
             oracle_vocab_transform(ham["_voc"], db, 4)
             line["cpu_baseline"]["bow_transform"] = {"descriptors_per_s": len(db) / (time.perf_counter() - t0), "cores": 1, "kind": "port",
                                                      "sample": "20000 uniform descriptors through the same vocabulary"}
-            pps, nmm = cpu_matcher_baseline(frames[0], nf, nl)
+            pps, nm1, nm2, mkind = cpu_matcher_baseline(frames[0], nf, nl)
             line["cpu_baseline"]["matcher"] = {
-                "tracking_searches_frame_pairs_per_s": pps, "matches_per_pair": nmm, "allpairs_gpairs_per_s": cpu_allpairs_baseline(),
-                "cores": 1, "kind": "port", "sample": "6 consecutive frame pairs (both SearchByProjection calls); 64 x 200000 descriptor pairs"}
+                "tracking_searches_frames_per_s": pps, "matches_per_frame_lastframe": nm1, "matches_per_frame_mappoints": nm2,
+                "cores": 1, "kind": mkind, "sample": "6 frames of the stream, both SearchByProjection calls per frame, the GPU leg's queries",
+                "allpairs_gpairs_per_s": cpu_allpairs_baseline(), "allpairs_kind": "port (the database search has no reference function: it is the inner "
+                "loop of SearchByBoW(KF,KF) restated; 64 x 200000 descriptor pairs)"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

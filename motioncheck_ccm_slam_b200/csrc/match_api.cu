@@ -413,11 +413,11 @@ static int fill_params(ccm_matcher* m, const ccm_window_params* prm, WindowParam
     return CCM_OK;
 }
 
-// scratch of one job, carved from MB_SCRATCH: head[cap] claim0[qs] claim1[qs] qbest[3*qs]
-static size_t job_scratch_ints(int cap, int qs) { return (size_t)cap + (7 + 2 * WIN_TOPK) * (size_t)qs + 32; }
+// scratch of one job, carved from MB_SCRATCH: head[3*cap] claim0[qs] claim1[qs] qbest[3*qs] total[qs] fb[qs] keys[TOPK*qs]
+static size_t job_scratch_ints(int cap, int qs) { return 3 * (size_t)cap + (7 + 2 * WIN_TOPK) * (size_t)qs + 32; }
 
 static void carve_job(WindowJob& J, int* s, int cap, int qs) {
-    J.head = s; s += cap;
+    J.head = s; s += 3 * (size_t)cap;          // three rotating lowest-claimant arrays (k_window_resolve)
     J.claim[0] = s; s += qs;
     J.claim[1] = s; s += qs;
     J.qbest = s; s += 3 * (size_t)qs;

@@ -52,7 +52,7 @@ struct WindowJob {
     MatchResultDev* res;       // [nq] or null
     int* nmatches;             // [1]
     // scratch (per job, carved from the matcher's arena)
-    int* head;                 // [pack.cap]   lowest blocking claimant per target (INIT: vMatchedDistance)
+    int* head;                 // [3 * pack.cap] lowest blocking claimant per target, three rotating copies (INIT: vMatchedDistance in the first)
     int* claim[2];             // [nq_cap] x2  claimed target per query (ping-pong), -1 none (INIT: vnMatches12, accept bin)
     int* qbest;                // [nq_cap] x3  best idx, best dist, best dist2 of the last evaluation
     unsigned long long* keys;  // [nq_cap] x WIN_TOPK  best candidate keys of the static pass (k_window_eval)

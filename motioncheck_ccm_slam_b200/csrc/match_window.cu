@@ -283,85 +283,88 @@ __device__ __forceinline__ bool accept_rule(const PackDev& P, const WindowParams
 
 template <int MODE>
 __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
-    __shared__ int s_nfb, s_nm, s_hist[32], s_keep[3];
+    __shared__ int s_nfb[3], s_nm, s_hist[32], s_keep[3];
     const PackDev& P = J.pack;
     const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
     const int n = min(*P.n, P.cap);
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
-    int* minclaim = J.head;
     const bool stateful = (MODE != WIN_MODE_BEST);
+    // Three "lowest blocking claimant per target" arrays rotate through the rounds: round `it` READS mc[it % 3] (built while
+    // round it-1 ran, from that round's claims), BUILDS mc[(it+1) % 3] with an atomicMin per blocking claim as the claims are
+    // decided, and CLEARS mc[(it+2) % 3] for the round after. A round is therefore one pass over the queries and ONE barrier
+    // (it used to be clear / rebuild / evaluate with five); the iteration itself is unchanged: every query is evaluated against
+    // the claims of the previous round (Jacobi), until no claim changes.
+    int* mc[3] = {J.head, J.head + P.cap, J.head + 2 * P.cap};
 
-    if (threadIdx.x == 0) { s_nm = 0; }
+    if (threadIdx.x == 0) { s_nm = 0; s_nfb[0] = 0; s_nfb[1] = 0; s_nfb[2] = 0; }
     if (threadIdx.x < 32) s_hist[threadIdx.x] = 0;
-    for (int i = threadIdx.x; i < nq; i += blockDim.x) { J.claim[0][i] = -1; J.claim[1][i] = -1; }
+    for (int i = threadIdx.x; i < nq; i += blockDim.x) J.claim[0][i] = -1;           // claims of the previous round
+    if (stateful)
+        for (int i = threadIdx.x; i < n; i += blockDim.x) { mc[0][i] = 0x7fffffff; mc[1][i] = 0x7fffffff; }
     __syncthreads();
 
-    int cur = 0;
     for (int it = 0; it <= nq; it++) {
-        cur = it & 1;
-        const int prev = cur ^ 1;
-        if (stateful) {
-            for (int i = threadIdx.x; i < n; i += blockDim.x) minclaim[i] = 0x7fffffff;
-            __syncthreads();
-            if (it > 0)
-                for (int i = threadIdx.x; i < nq; i += blockDim.x) {
-                    const int t = J.claim[prev][i];
-                    if (t >= 0 && (J.q[i].flags & WQ_BLOCKS)) atomicMin(&minclaim[t], i);
-                }
-            __syncthreads();
-        }
-        int changed = 0;
-        if (threadIdx.x == 0) s_nfb = 0;
-        __syncthreads();
+        const int* __restrict__ mcur = mc[it % 3];
+        int* mnext = mc[(it + 1) % 3];
+        int* mclear = mc[(it + 2) % 3];
+        int* nfb = &s_nfb[it % 3];                           // this round's fallback count; next round's is reset now, the previous
+        int changed = 0;                                     // round's may still be read by a slow thread and is left alone
+        if (threadIdx.x == 0) s_nfb[(it + 1) % 3] = 0;
+        if (stateful)
+            for (int i = threadIdx.x; i < n; i += blockDim.x) mclear[i] = 0x7fffffff;
         // one thread per query, from the keys k_window_eval stored
         for (int i = threadIdx.x; i < nq; i += blockDim.x) {
-            const WindowQueryDev q = J.q[i];
+            const uint32_t flags = J.q[i].flags;
             WinEval e; e.b1 = KEY_NONE; e.b2 = KEY_NONE;
             bool fallback = false;
-            if (q.flags & WQ_VALID) {
+            if (flags & WQ_VALID) {
                 const int total = J.total[i];
                 const int have = min(total, WIN_TOPK);
                 int found = 0;
                 for (int r = 0; r < have; r++) {
                     const unsigned long long key = J.keys[(size_t)WIN_TOPK * i + r];
-                    if (stateful && minclaim[(int)(key & 0xffff)] < i) continue;
+                    if (stateful && mcur[(int)(key & 0xffff)] < i) continue;
                     if (found == 0) e.b1 = key; else { e.b2 = key; }
                     if (++found == 2) break;
                 }
                 const int need = (MODE == WIN_MODE_MAPPOINTS) ? 2 : 1;
                 fallback = found < need && total > WIN_TOPK;
             }
-            if (fallback) { J.fb[atomicAdd(&s_nfb, 1)] = i; continue; }
+            if (fallback) { J.fb[atomicAdd(nfb, 1)] = i; continue; }
             int bestIdx, bestDist, bestDist2;
             const bool acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
             const int c = acc ? bestIdx : -1;
-            if (c != J.claim[prev][i]) changed = 1;
-            J.claim[cur][i] = c;
+            if (c != J.claim[0][i]) { changed = 1; J.claim[0][i] = c; }
+            if (stateful && c >= 0 && (flags & WQ_BLOCKS)) atomicMin(&mnext[c], i);
             J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist;
             J.qbest[3 * i + 2] = (MODE == WIN_MODE_MAPPOINTS) ? bestDist2 : 256;
         }
-        __syncthreads();
-        // truncated key lists that ran dry: exact re-walk of the grid, one warp per query
-        const int nfb = s_nfb;
-        for (int j = wid; j < nfb; j += nw) {
-            const int i = J.fb[j];
-            const WindowQueryDev q = J.q[i];
-            int bestIdx = -1, bestDist = 256, bestDist2 = 256;
-            const WinEval e = eval_query<MODE>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i, J.holder, minclaim, nullptr, lane);
-            const bool acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
-            if (lane == 0) {
-                const int c = acc ? bestIdx : -1;
-                if (c != J.claim[prev][i]) changed = 1;
-                J.claim[cur][i] = c;
-                J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist;
-                J.qbest[3 * i + 2] = (MODE == WIN_MODE_MAPPOINTS) ? bestDist2 : 256;
+        int any = __syncthreads_or(changed);               // the round's barrier: claims, mnext and the fallback list are complete
+        // truncated key lists that ran dry: exact re-walk of the grid, one warp per query, against the same mcur (rare)
+        const int cnt = *nfb;
+        if (cnt > 0) {
+            changed = 0;
+            for (int j = wid; j < cnt; j += nw) {
+                const int i = J.fb[j];
+                const WindowQueryDev q = J.q[i];
+                int bestIdx = -1, bestDist = 256, bestDist2 = 256;
+                const WinEval e = eval_query<MODE>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i, J.holder, mcur, nullptr, lane);
+                const bool acc = accept_rule<MODE>(P, prm, e, bestIdx, bestDist, bestDist2);
+                if (lane == 0) {
+                    const int c = acc ? bestIdx : -1;
+                    if (c != J.claim[0][i]) { changed = 1; J.claim[0][i] = c; }
+                    if (stateful && c >= 0 && (q.flags & WQ_BLOCKS)) atomicMin(&mnext[c], i);
+                    J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist;
+                    J.qbest[3 * i + 2] = (MODE == WIN_MODE_MAPPOINTS) ? bestDist2 : 256;
+                }
             }
+            any |= __syncthreads_or(changed);
         }
-        if (!stateful) break;
-        if (!__syncthreads_or(changed)) break;
+        if (!stateful || !any) break;
     }
     __syncthreads();
+    const int cur = 0;
 
     // ---- outcome: res[], holder[], nmatches, rotation histogram (LASTFRAME, :1436-1465) ----
     const bool ori = (MODE == WIN_MODE_LASTFRAME) && prm.check_orientation;

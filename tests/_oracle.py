@@ -299,13 +299,6 @@ class OracleMatcher:
                                                    holder.ctypes.data, res.ctypes.data)
         return nm, res
 
-    def projection_reloc(self, F, q_state, q_u, q_v, q_level, q_angle, q_desc, th, orb_dist, sf, holder):
-        """SearchByProjection(Frame&, kfptr, sAlreadyFound, th, ORBdist), ORBmatcher.cpp:1478-1605"""
-        st, u_, v_, l, a, d, s = (_a(q_state, np.uint8), _a(q_u, np.float32), _a(q_v, np.float32), _a(q_level, np.int32),
-                                  _a(q_angle, np.float32), _a(q_desc, np.uint8), _a(sf, np.float32))
-        return self.L.rm_search_projection_reloc(F.h, len(u_), st.ctypes.data, u_.ctypes.data, v_.ctypes.data, l.ctypes.data, a.ctypes.data,
-                                                 d.ctypes.data, th, int(orb_dist), s.ctypes.data, self.ori, holder.ctypes.data)
-
     def projection_kf_sim3(self, F, q_valid, q_u, q_v, q_level, q_desc, q_claims, th, sf, holder):
         n = len(q_u)
         res = np.zeros(n, RESULT_DTYPE)
