@@ -579,7 +579,7 @@ def run_ours(args, wl, rank, world, local_rank):
 
     import bench_legs
     # the e2e copy pattern alone, every rank at once: what the host link of this box allows for this traffic
-    link_ms = bench_legs.link_ceiling(torch, dev, B, w, h, cap, max(10, min(args.steps, 50)), barrier)
+    link_ms = bench_legs.link_ceiling(torch, dev, pin, out_kp2, out_desc2, max(10, min(args.steps, 50)), barrier)
     barrier()
     single, single_launches = (bench_legs.single_frame(torch, local_rank, w, h, nf, nl, frames[0]) if rank == 0 else ({}, 0))
     barrier()

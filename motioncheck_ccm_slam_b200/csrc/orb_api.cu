@@ -71,6 +71,7 @@ struct ccm_orb {
     size_t graph1_pitch = 0;
     long long graph1_launches = 0;
     bool graph1_failed = false;
+    bool blur_ocv24 = false;                           // CCM_ORB_BLUR=opencv2: OpenCV 2.4.13's 8-bit Gaussian taps (orb_describe.cu)
     // optional per-stage CUDA-event timing (ccm_orb_set_stage_timing): events bracket each stage of run_pipeline
     bool stage_timing = false;
     cudaEvent_t ev[CCM_N_STAGES + 1] = {};
@@ -427,7 +428,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[2], s));
         if (fork) CK(cudaEventRecord(LN.fork, s));
         if (!fork) {
-            k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
+            if (h->blur_ocv24) k_blur_levels<true><<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T); else k_blur_levels<false><<<dim3(T.total_blur_tiles, n), 256, 0, s>>>(T);
             CKL("k_blur_levels", cudaSuccess);
             h->launches++;
         }
@@ -439,7 +440,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         h->launches++;
         if (fork) {
             CK(cudaStreamWaitEvent(LN.aux, LN.fork, 0));
-            k_blur_levels<<<dim3(T.total_blur_tiles, n), 256, 0, LN.aux>>>(T);
+            if (h->blur_ocv24) k_blur_levels<true><<<dim3(T.total_blur_tiles, n), 256, 0, LN.aux>>>(T); else k_blur_levels<false><<<dim3(T.total_blur_tiles, n), 256, 0, LN.aux>>>(T);
             CKL("k_blur_levels", cudaSuccess);
             h->launches++;
             CK(cudaEventRecord(LN.join, LN.aux));
@@ -478,6 +479,7 @@ int ccm_orb_create(const ccm_orb_config* cfg, ccm_orb** out) {
     }
     ccm_orb* h = new ccm_orb();
     h->cfg = *cfg;
+    if (const char* e = std::getenv("CCM_ORB_BLUR")) h->blur_ocv24 = std::strcmp(e, "opencv2") == 0;
     // ORBextractor::ORBextractor, cslam/src/ORBextractor.cpp:579-615 — float/double mix kept as written
     const int L = cfg->nlevels;
     const double scaleFactor = cfg->scale_factor;

@@ -37,8 +37,20 @@ __device__ __forceinline__ void blur_tail_selectors(int w, uint32_t& sel_lo, uin
     sel_hi = (uint32_t)(0x3456123400120000ull >> (16 * (e - 1))) & 0xffffu;     // e = 1: 0x0000, 2: 0x0012, 3: 0x1234, 4: 0x3456
 }
 
+// Tap sets. OCV24 = false: OpenCV >= 3.4.1 / 4.x fixed-point GaussianBlur, 8.8 kernel {18,34,48,56,48,34,18} (sums to 256),
+// pinned to cv2 4.13.0 golden vectors. OCV24 = true: the integer path OpenCV 2.4.13's FilterEngine takes for CV_8U with a
+// symmetric smoothing kernel (createSeparableLinearFilter: getGaussianKernel(7, 2) in float, each tap times 256 and rounded on
+// its own -> {18,34,49,55,49,34,18}, which sums to 257; same exact integer passes, (sum + 2^15) >> 16, saturated to 255).
+// The reference's CMakeLists pins 2.4.13; its source is a missing blob, so that variant is a restatement from knowledge of
+// the 2.4 sources and cannot be checked against a build here. Selected with CCM_ORB_BLUR=opencv2.
+template <bool OCV24> struct BlurTaps {
+    static constexpr uint32_t k0 = 18u, k1 = 34u, k2 = OCV24 ? 49u : 48u, k3 = OCV24 ? 55u : 56u;
+};
+
+template <bool OCV24>
 __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint32_t own, int x, int x0, int w, int lane,
                                           uint32_t sel_lo, uint32_t sel_hi, uint32_t (&hs)[4]) {
+    typedef BlurTaps<OCV24> K;
     uint32_t prev = __shfl_up_sync(0xffffffffu, own, 1);
     uint32_t next = __shfl_down_sync(0xffffffffu, own, 1);
 #if !BLUR_OVERLAP
@@ -51,10 +63,10 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint3
         const uint32_t lo = __byte_perm(prev, own, sel_lo), hi = __byte_perm(prev, own, sel_hi);
         own = lo; next = hi;
     } else if (x == wa - 4) next = __byte_perm(own, next, sel_lo);
-    const uint32_t C1 = 18u | (34u << 8) | (48u << 16) | (56u << 24), C2 = 48u | (34u << 8) | (18u << 16);
+    const uint32_t C1 = K::k0 | (K::k1 << 8) | (K::k2 << 16) | (K::k3 << 24), C2 = K::k2 | (K::k1 << 8) | (K::k0 << 16);
     const uint32_t wm3 = __byte_perm(prev, own, 0x4321), wm2 = __byte_perm(prev, own, 0x5432), wm1 = __byte_perm(prev, own, 0x6543);
     const uint32_t wp1 = __byte_perm(own, next, 0x4321), wp2 = __byte_perm(own, next, 0x5432), wp3 = __byte_perm(own, next, 0x6543);
-    hs[0] = __dp4a(wm3, C1, __dp4a(wp1, C2, 0u));     // <= 65280
+    hs[0] = __dp4a(wm3, C1, __dp4a(wp1, C2, 0u));     // <= 255 * 257 = 65535
     hs[1] = __dp4a(wm2, C1, __dp4a(wp2, C2, 0u));
     hs[2] = __dp4a(wm1, C1, __dp4a(wp3, C2, 0u));
     hs[3] = __dp4a(own, C1, __dp4a(next, C2, 0u));
@@ -63,9 +75,11 @@ __device__ __forceinline__ void blur_hrow(const uint8_t* __restrict__ row, uint3
 // Levels narrower than 16 px (the last levels of very small images): the word tricks of blur_hrow do not apply, and such a
 // level is a few hundred pixels - each lane evaluates its 4 outputs tap by tap with reflect-101 (same integers: the
 // horizontal sums are exact, the vertical pass rounds once). Out of line so that the unrolled main loop stays small.
+template <bool OCV24>
 __device__ __noinline__ void blur_small_level(const uint8_t* __restrict__ img, int pitch, uint8_t* __restrict__ out, int opitch,
                                               int w, int h, int x, int wy0) {
-    const int cf[7] = {18, 34, 48, 56, 48, 34, 18};
+    typedef BlurTaps<OCV24> K;
+    const int cf[7] = {(int)K::k0, (int)K::k1, (int)K::k2, (int)K::k3, (int)K::k2, (int)K::k1, (int)K::k0};
 #pragma unroll 1
     for (int oy = wy0; oy < min(wy0 + BLUR_RPW, h); oy++) {
         if (x >= w) continue;
@@ -82,13 +96,15 @@ __device__ __noinline__ void blur_small_level(const uint8_t* __restrict__ img, i
                 for (int dx = -3; dx <= 3; dx++) hs += (uint32_t)cf[dx + 3] * row[ccm_reflect101(px + dx, w)];
                 acc += (uint32_t)cf[dy + 3] * hs;
             }
-            packed |= ((acc + 32768u) >> 16) << (8 * i);
+            packed |= min((acc + 32768u) >> 16, 255u) << (8 * i);
         }
         *reinterpret_cast<uint32_t*>(out + (size_t)oy * opitch + x) = packed;
     }
 }
 
+template <bool OCV24>
 __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ LevelTable T) {
+    typedef BlurTaps<OCV24> K;
     int lvl = 0;
 #pragma unroll 1
     while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].blur_tile_base) lvl++;
@@ -105,7 +121,7 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int pitch = L.img_pitch;
     uint8_t* __restrict__ outp = L.blur + (size_t)f * L.blur_stride + (size_t)wy0 * L.blur_pitch + x;
-    if (w < 16) { blur_small_level(img, pitch, L.blur + (size_t)f * L.blur_stride, L.blur_pitch, w, h, out_lane ? x : w, wy0); return; }   // warp-uniform
+    if (w < 16) { blur_small_level<OCV24>(img, pitch, L.blur + (size_t)f * L.blur_stride, L.blur_pitch, w, h, out_lane ? x : w, wy0); return; }   // warp-uniform
     uint32_t ring[7][4];
     uint32_t sel_lo, sel_hi;
     blur_tail_selectors(w, sel_lo, sel_hi);
@@ -118,16 +134,17 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     for (int r = 0; r < BLUR_RPW + 6; r++) {
         const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
         const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
-        blur_hrow(row, own, x, x0, w, lane, sel_lo, sel_hi, ring[r % 7]);
+        blur_hrow<OCV24>(row, own, x, x0, w, lane, sel_lo, sel_hi, ring[r % 7]);
         row = row_n; own = own_n;
         if (r >= 6) {
             const int oy = wy0 + r - 6;
             uint32_t packed = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const uint32_t acc = 18 * (ring[(r - 6) % 7][k] + ring[r % 7][k]) + 34 * (ring[(r - 5) % 7][k] + ring[(r - 1) % 7][k]) +
-                                     48 * (ring[(r - 4) % 7][k] + ring[(r - 2) % 7][k]) + 56 * ring[(r - 3) % 7][k];
-                packed |= ((acc + 32768u) >> 16) << (8 * k);
+                const uint32_t acc = K::k0 * (ring[(r - 6) % 7][k] + ring[r % 7][k]) + K::k1 * (ring[(r - 5) % 7][k] + ring[(r - 1) % 7][k]) +
+                                     K::k2 * (ring[(r - 4) % 7][k] + ring[(r - 2) % 7][k]) + K::k3 * ring[(r - 3) % 7][k];
+                const uint32_t v = (acc + 32768u) >> 16;
+                packed |= (OCV24 ? min(v, 255u) : v) << (8 * k);
             }
             if (out_lane && oy < h && x < w) *reinterpret_cast<uint32_t*>(outp) = packed;   // pitch multiple of 32: in-bounds
             outp += L.blur_pitch;

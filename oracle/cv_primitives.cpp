@@ -109,9 +109,31 @@ void ocv_border_reflect101_u8(const uint8_t* src, int w, int h, size_t sstep,
 /* OpenCV 4.x GaussianBlur CV_8U fixed-point path (smooth.simd.hpp): 8.8 ufixedpoint16 kernel
  * {18,34,48,56,48,34,18}/256 for ksize 7, sigma 2 (recovered from cv2 and pinned by test),
  * exact integer row+column accumulation, one final round-half-up: (sum + 2^15) >> 16. */
+static void gaussian7_fixed(const int* k, const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep);
+static int g_blur_variant = 0;                         /* 0: OpenCV 4.13 taps (pinned), 1: OpenCV 2.4.13 taps (see below) */
+extern "C" void ocv_set_blur_variant(int v) { g_blur_variant = v; }
 void ocv_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep) {
     static const int k[7] = {18, 34, 48, 56, 48, 34, 18};
-    std::vector<uint16_t> hbuf((size_t)w * h);          /* row sums <= 255*256 fit u16 */
+    if (g_blur_variant == 1) { ocv24_gaussian7_sigma2_u8(src, w, h, sstep, dst, dstep); return; }
+    gaussian7_fixed(k, src, w, h, sstep, dst, dstep);
+}
+
+/* OpenCV 2.4.13 (the version cslam/CMakeLists.txt:36-38,86-90 pins; its source zip is a missing blob, so this is a
+ * restatement FROM KNOWLEDGE of the 2.4 sources that no build here can confirm): GaussianBlur on CV_8U goes through
+ * createSeparableLinearFilter's integer branch for symmetric smoothing kernels (filter.cpp): getGaussianKernel(7, 2, CV_32F)
+ * = {0.07015933, 0.13107488, 0.19071282, 0.21610594, ...}, each tap times 2^8 and rounded on its own (convertTo CV_32S) =
+ * {18, 34, 49, 55, 49, 34, 18} - they sum to 257, not 256 - row pass 8U -> 32S exact, column pass 32S -> 8U through
+ * FixedPtCastEx<int, uchar>(16): saturate_cast<uchar>((sum + 2^15) >> 16). (Its SSE2 column filter evaluates the same sum
+ * in float and rounds to nearest-even: a difference only at exact halves.) Used by tests/test_oracle_cv.py to MEASURE how
+ * far a reference built against 2.4.13 is from the 4.13 semantics this repo pins; selectable on the GPU with
+ * CCM_ORB_BLUR=opencv2. */
+void ocv24_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep) {
+    static const int k[7] = {18, 34, 49, 55, 49, 34, 18};
+    gaussian7_fixed(k, src, w, h, sstep, dst, dstep);
+}
+
+static void gaussian7_fixed(const int* k, const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep) {
+    std::vector<uint16_t> hbuf((size_t)w * h);          /* row sums <= 255*257 fit u16 */
     std::vector<uint8_t> pad((size_t)w + 6);
     for (int y = 0; y < h; y++) {
         const uint8_t* s = src + (size_t)y * sstep;
@@ -127,7 +149,8 @@ void ocv_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uin
         uint8_t* d = dst + (size_t)y * dstep;
         for (int x = 0; x < w; x++) {
             const int acc = k[0] * (r[0][x] + r[6][x]) + k[1] * (r[1][x] + r[5][x]) + k[2] * (r[2][x] + r[4][x]) + k[3] * r[3][x];
-            d[x] = (uint8_t)((acc + 32768) >> 16);
+            const int v = (acc + 32768) >> 16;
+            d[x] = (uint8_t)(v > 255 ? 255 : v);
         }
     }
 }

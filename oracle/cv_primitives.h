@@ -47,6 +47,8 @@ void ocv_border_reflect101_u8(const uint8_t* src, int w, int h, size_t sstep,
 
 /* cv::GaussianBlur(src, dst, Size(7,7), 2, 2, BORDER_REFLECT_101) for CV_8UC1 (4.x fixed-point path) */
 void ocv_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep);
+/* the same call with OpenCV 2.4.13's taps {18,34,49,55,49,34,18} (restated from knowledge of the 2.4 sources, unverifiable here) */
+void ocv24_gaussian7_sigma2_u8(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep);
 
 /* FAST-9/16 corner score of one interior pixel (3 px away from every edge) */
 int ocv_fast_score_9_16(const uint8_t* p, size_t step);

@@ -360,3 +360,28 @@ def test_four_agents_share_one_gpu(cuda_lib):
     assert_same(got[0][0][0][0], got[0][0][1][0], ko, do, "agent 0 frame 0")
     for e in exs:
         e.close()
+
+
+def test_opencv2_blur_switch(cuda_lib, monkeypatch):
+    """CCM_ORB_BLUR=opencv2 selects OpenCV 2.4.13's 8-bit Gaussian taps {18,34,49,55,..} (sum 257, saturated) in k_blur_levels:
+    blurred levels and descriptors then equal the oracle run with the same variant; keypoints do not depend on the blur."""
+    from _oracle import oracle_lib
+    monkeypatch.setenv("CCM_ORB_BLUR", "opencv2")
+    frames = make_stream(1000, 2)
+    ex = make(cuda_lib, 1000, 1.2, 8, 20, 7, max_batch=2)
+    orc = OracleExtractor(1000, 1.2, 8, 20, 7)
+    L = oracle_lib()
+    kps, descs = ex.extract_batch(list(frames))
+    try:
+        L.ocv_set_blur_variant(1)
+        for f in range(2):
+            ko, do = orc(frames[f])
+            assert_same(kps[f], descs[f], ko, do, "opencv2 blur, frame %d" % f)
+            for l in (0, 3, 7):
+                assert np.array_equal(ex.pyramid_level(l, f, blurred=True), orc.level_image(l, True)), ("blur", f, l)
+        L.ocv_set_blur_variant(0)
+        ko, do = orc(frames[0])
+        assert not np.array_equal(descs[0], do)            # and it is a different result from the default taps
+    finally:
+        L.ocv_set_blur_variant(0)
+    ex.close()
