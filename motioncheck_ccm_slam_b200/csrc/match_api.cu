@@ -423,8 +423,7 @@ static void carve_job(WindowJob& J, int* s, int cap, int qs) {
     J.qbest = s; s += 3 * (size_t)qs;
     J.total = s; s += qs;
     J.fb = s; s += qs;
-    s += ((uintptr_t)s & 4) ? 1 : 0;            // 8-byte alignment for the keys
-    J.keys = (unsigned long long*)s;
+    J.keys = (uint32_t*)s;
 }
 
 int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs, int n_jobs, const ccm_window_params* prm,

@@ -181,11 +181,21 @@ __device__ __forceinline__ WinEval eval_query(const PackDev& P, const WindowPara
 
 // static pass: candidates under the query-independent filters (window, levels, gate, the holder state the call
 // started with), best WIN_TOPK keys in keys[] (ascending, KEY_NONE padded) and the number of candidates that passed
+// Keys of the static pass are 32 bits: distance << 16 | CSR position of the candidate in the pack's grid. The CSR is in
+// (ix * rows + iy) cell order with ascending feature indices inside a cell, i.e. positions inside one window ascend exactly in
+// the order GetFeaturesInArea emits the features, so the position is both the reference's first-wins tie-break and (through
+// items[]) the feature index. One REDUX per warp minimum instead of five 64-bit shuffle steps.
+#define KEY32_NONE 0xffffffffu
+__device__ __forceinline__ unsigned long long key32_to_key64(const PackDev& P, uint32_t k) {
+    const uint32_t p = k & 0xffffu;
+    return ((unsigned long long)(k >> 16) << 32) | ((unsigned long long)p << 16) | (unsigned)P.items[p];
+}
+
 template <int MODE>
 __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowParamsDev& prm, const WindowQueryDev& q,
                                                 const uint4 qd0, const uint4 qd1, const int* __restrict__ holder, int lane,
-                                                unsigned long long (&keys)[WIN_TOPK], int& total) {
-    unsigned long long k0 = KEY_NONE, k1 = KEY_NONE, k2 = KEY_NONE, k3 = KEY_NONE;
+                                                uint32_t (&keys)[WIN_TOPK], int& total) {
+    uint32_t k0 = KEY32_NONE, k1 = KEY32_NONE, k2 = KEY32_NONE, k3 = KEY32_NONE;
     int cnt = 0;
     const float fx = __fsub_rn(q.u, P.min_x), fy = __fsub_rn(q.v, P.min_y);
     const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(fx, q.r), P.inv_w)));
@@ -198,7 +208,6 @@ __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowPa
         // cells top to bottom, features in index order): lane j fetches the CSR range of column cx0 + j, an inclusive scan gives
         // every column's first position, and the lanes then stride over all candidates of up to 32 columns at once. The
         // dependent load chain (range -> item -> fields -> descriptor) is paid once per 32 candidates, not once per column.
-        int pos_base = 0;
         for (int cx0 = minCX; cx0 <= maxCX; cx0 += 32) {
             const int ix = cx0 + lane;
             int s = 0, n = 0;
@@ -231,29 +240,24 @@ __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowPa
                 if (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) { if (holder[k] == -2) continue; }
                 else if (MODE == WIN_MODE_KF_SIM3) { if (holder[k] != -1) continue; }
                 const int dist = hamming256(qd0, qd1, desc[2 * (size_t)k], desc[2 * (size_t)k + 1]);
-                unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned long long)(pos_base + c) << 16) | (unsigned)k;
+                uint32_t key = ((uint32_t)dist << 16) | (uint32_t)p;
                 cnt++;
                 if (key < k3) {
                     k3 = key;
-                    if (k3 < k2) { const unsigned long long t2 = k2; k2 = k3; k3 = t2; }
-                    if (k2 < k1) { const unsigned long long t1 = k1; k1 = k2; k2 = t1; }
-                    if (k1 < k0) { const unsigned long long t0 = k0; k0 = k1; k1 = t0; }
+                    if (k3 < k2) { const uint32_t t2 = k2; k2 = k3; k3 = t2; }
+                    if (k2 < k1) { const uint32_t t1 = k1; k1 = k2; k2 = t1; }
+                    if (k1 < k0) { const uint32_t t0 = k0; k0 = k1; k1 = t0; }
                 }
             }
-            pos_base += tot;
         }
     }
 #pragma unroll
     for (int r = 0; r < WIN_TOPK; r++) {
-        unsigned long long m = k0;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+        const uint32_t m = __reduce_min_sync(0xffffffffu, k0);
         keys[r] = m;
-        if (k0 == m && m != KEY_NONE) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY_NONE; }   // keys are unique: one lane pops
+        if (k0 == m && m != KEY32_NONE) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY32_NONE; }   // keys are unique: one lane pops
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-    total = cnt;
+    total = __reduce_add_sync(0xffffffffu, cnt);
 }
 
 template <int MODE>
@@ -323,7 +327,7 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
                 const int have = min(total, WIN_TOPK);
                 int found = 0;
                 for (int r = 0; r < have; r++) {
-                    const unsigned long long key = J.keys[(size_t)WIN_TOPK * i + r];
+                    const unsigned long long key = key32_to_key64(P, J.keys[(size_t)WIN_TOPK * i + r]);
                     if (stateful && mcur[(int)(key & 0xffff)] < i) continue;
                     if (found == 0) e.b1 = key; else { e.b2 = key; }
                     if (++found == 2) break;
@@ -468,14 +472,14 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
 template <int MODE>
 __device__ __forceinline__ void window_eval_job(const WindowJob& J, const WindowParamsDev& prm, int i, int lane) {
     const WindowQueryDev q = J.q[i];
-    unsigned long long keys[WIN_TOPK];
+    uint32_t keys[WIN_TOPK];
     int total = 0;
     if (q.flags & WQ_VALID) {
         const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
         eval_query_topk<MODE>(J.pack, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], J.holder, lane, keys, total);
     } else {
 #pragma unroll
-        for (int r = 0; r < WIN_TOPK; r++) keys[r] = KEY_NONE;
+        for (int r = 0; r < WIN_TOPK; r++) keys[r] = KEY32_NONE;
     }
 #pragma unroll
     for (int r = 0; r < WIN_TOPK; r++) if (lane == r) J.keys[(size_t)WIN_TOPK * i + r] = keys[r];

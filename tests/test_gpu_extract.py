@@ -97,6 +97,30 @@ def test_sparse_and_flat_images(cuda_lib):
     assert_same(kp, desc, ko, do, "checker")
 
 
+def test_dense_candidates_and_high_thresholds(cuda_lib):
+    """k_fast_chunks corner cases: (1) white noise and a 1-px checkerboard make almost every pixel a prefilter candidate, so a
+    warp's candidate list overflows, is drained, and the NMS walks the score map instead of the list; (2) FAST thresholds
+    >= 128 take the other form of the byte compare (fc_gt<true>), also mixed with a fallback threshold below 128."""
+    rng = np.random.default_rng(9)
+    noise = rng.integers(0, 256, (300, 400), dtype=np.uint8)
+    fine = (np.indices((300, 400)).sum(0) % 2 * 255).astype(np.uint8)
+    salt = np.full((300, 400), 30, np.uint8)
+    salt[rng.random((300, 400)) < 0.02] = 250                      # isolated bright pixels on a dark field: |d| = 220
+    blocks = (rng.integers(0, 2, (19, 25)) * 255).astype(np.uint8).repeat(16, 0).repeat(16, 1)[:300, :400]
+    for name, img, args in [("noise", noise, (500, 1.2, 4, 20, 7)), ("fine checkerboard", fine, (500, 1.2, 4, 20, 7)),
+                            ("noise, th 60/30", noise, (800, 1.2, 3, 60, 30)),
+                            ("salt, th 200/150", salt, (500, 1.2, 3, 200, 150)), ("salt, th 140/100", salt, (500, 1.2, 3, 140, 100)),
+                            ("blocks, th 250/128", blocks, (500, 1.2, 3, 250, 128)), ("noise, th 128/127", noise, (500, 1.2, 2, 128, 127))]:
+        ex = make(cuda_lib, *args, max_width=400, max_height=300)
+        orc = OracleExtractor(*args)
+        kp, desc = ex(img)
+        ko, do = orc(img)
+        assert_same(kp, desc, ko, do, name)
+        for l in range(args[2]):
+            assert np.array_equal(ex.level_corners(l, 0), orc.level_corners(l)), (name, "corners", l)
+        ex.close()
+
+
 def test_strided_input_and_empty(cuda_lib):
     ex = make(cuda_lib, 300, 1.2, 4, 20, 7, max_width=320, max_height=240)
     big = np.zeros((260, 400), np.uint8)
