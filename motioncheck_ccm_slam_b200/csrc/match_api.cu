@@ -461,10 +461,8 @@ int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs,
     }
     // pageable -> device copy is staged by the runtime before it returns, so `jobs` may die at scope exit
     MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(WindowJob) * n_jobs, cudaMemcpyHostToDevice, m->stream));
-    if (P.mode != CCM_WIN_INIT) {
-        k_window_eval<<<dim3((q_stride + 7) / 8, n_jobs), 256, 0, m->stream>>>(djobs, P);
-        m->launches++;
-    }
+    k_window_eval<<<dim3((q_stride + 7) / 8, n_jobs), 256, 0, m->stream>>>(djobs, P);
+    m->launches++;
     k_window_resolve<<<n_jobs, WIN_THREADS, 0, m->stream>>>(djobs, P);
     m->launches++;
     MCK(cudaGetLastError());

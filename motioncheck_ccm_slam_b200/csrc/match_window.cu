@@ -405,10 +405,18 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
     if (threadIdx.x == 0) *J.nmatches = s_nm;
 }
 
-// SearchForInitialization (ORBmatcher.cpp:448-563): queries in order on warp 0; holder = vnMatches21 (output),
-// head = vMatchedDistance, claim[0] = vnMatches12, claim[1] = rotation bin of the accept event.
+// SearchForInitialization (ORBmatcher.cpp:448-563): holder = vnMatches21 (output), head = vMatchedDistance, claim[0] =
+// vnMatches12, claim[1] = rotation bin of the accept event. The steal-back rule (:487-513) makes a query's candidate set
+// depend on the DISTANCES of earlier accepts (`if(vMatchedDistance[i2]<=dist) continue`), so the queries are resolved in
+// order by one warp; but the distances themselves do not depend on that state, so k_window_eval has already walked every
+// window in parallel and left each query's WIN_TOPK best keys. The ordered pass only filters those keys against
+// vMatchedDistance (lanes 0..3 = the four keys; 32 queries' keys are staged in shared memory at a time so that the loop never
+// waits on global memory) and re-walks the window exactly only when fewer than two keys of a truncated list survive.
 __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) {
     __shared__ int s_hist[32], s_keep[3], s_nm;
+    __shared__ uint32_t s_key[32][WIN_TOPK];
+    __shared__ int s_idx[32][WIN_TOPK], s_total[32];
+    __shared__ uint32_t s_flags[32];
     const PackDev& P = J.pack;
     const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
     const int n = min(*P.n, P.cap);
@@ -422,28 +430,60 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
     __syncthreads();
     if (threadIdx.x < 32) {
         int nm = 0;
-        for (int i = 0; i < nq; i++) {
-            const WindowQueryDev q = J.q[i];
-            int bestIdx = -1, bestDist = 256, bestDist2 = 256;
-            bool acc = false;
-            if (q.flags & WQ_VALID) {
-                const WinEval e = eval_query<WIN_MODE_INIT>(P, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i,
-                                                            J.holder, nullptr, mdist, lane);
-                acc = accept_rule<WIN_MODE_INIT>(P, prm, e, bestIdx, bestDist, bestDist2);
-            }
-            if (lane == 0) {
-                J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist; J.qbest[3 * i + 2] = bestDist2;
-                if (acc) {
-                    const int old = J.holder[bestIdx];
-                    if (old >= 0) { J.claim[0][old] = -1; nm--; }          // steal-back, :506-510
-                    J.claim[0][i] = bestIdx; J.holder[bestIdx] = i; mdist[bestIdx] = bestDist; nm++;
-                    if (prm.check_orientation) {
-                        const int b = rot_bin(q.angle, P.angle[bestIdx]);
-                        J.claim[1][i] = b; s_hist[b]++;
-                    }
+        for (int i0 = 0; i0 < nq; i0 += 32) {
+            {   // stage the keys of queries i0 .. i0+31: lane = query
+                const int i = i0 + lane;
+                uint32_t fl = 0; int tot = 0;
+                if (i < nq) { fl = J.q[i].flags; tot = J.total[i]; }
+#pragma unroll
+                for (int r = 0; r < WIN_TOPK; r++) {
+                    const uint32_t k = i < nq ? J.keys[(size_t)WIN_TOPK * i + r] : KEY32_NONE;
+                    s_key[lane][r] = k;
+                    s_idx[lane][r] = k != KEY32_NONE ? P.items[k & 0xffffu] : 0;
                 }
+                s_flags[lane] = fl; s_total[lane] = tot;
             }
             __syncwarp();
+            const int jn = min(32, nq - i0);
+            for (int j = 0; j < jn; j++) {
+                const int i = i0 + j;
+                int bestIdx = -1, bestDist = 256, bestDist2 = 256;
+                bool acc = false;
+                if (s_flags[j] & WQ_VALID) {
+                    const int total = s_total[j];
+                    uint32_t key = KEY32_NONE; int idx = 0;
+                    if (lane < WIN_TOPK) { key = s_key[j][lane]; idx = s_idx[j][lane]; }
+                    const int dist = (int)(key >> 16);
+                    const bool ok = key != KEY32_NONE && mdist[idx] > dist;              // vMatchedDistance, :487-488
+                    const uint32_t b = __ballot_sync(0xffffffffu, ok);
+                    if (__popc(b) < 2 && total > WIN_TOPK) {                              // truncated list ran dry: exact re-walk
+                        const WinEval e = eval_query<WIN_MODE_INIT>(P, prm, J.q[i], qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i,
+                                                                    J.holder, nullptr, mdist, lane);
+                        acc = accept_rule<WIN_MODE_INIT>(P, prm, e, bestIdx, bestDist, bestDist2);
+                    } else if (b) {
+                        const int first = __ffs(b) - 1;
+                        const uint32_t rest = b & (b - 1);
+                        WinEval e;
+                        const unsigned long long k64 = ((unsigned long long)dist << 32) | ((unsigned long long)(key & 0xffffu) << 16) | (unsigned)idx;
+                        e.b1 = __shfl_sync(0xffffffffu, k64, first);
+                        e.b2 = rest ? __shfl_sync(0xffffffffu, k64, __ffs(rest) - 1) : KEY_NONE;
+                        acc = accept_rule<WIN_MODE_INIT>(P, prm, e, bestIdx, bestDist, bestDist2);
+                    }
+                }
+                if (lane == 0) {
+                    J.qbest[3 * i] = bestIdx; J.qbest[3 * i + 1] = bestDist; J.qbest[3 * i + 2] = bestDist2;
+                    if (acc) {
+                        const int old = J.holder[bestIdx];
+                        if (old >= 0) { J.claim[0][old] = -1; nm--; }          // steal-back, :506-510
+                        J.claim[0][i] = bestIdx; J.holder[bestIdx] = i; mdist[bestIdx] = bestDist; nm++;
+                        if (prm.check_orientation) {
+                            const int bb = rot_bin(J.q[i].angle, P.angle[bestIdx]);
+                            J.claim[1][i] = bb; s_hist[bb]++;
+                        }
+                    }
+                }
+                __syncwarp();
+            }
         }
         if (lane == 0) s_nm = nm;
     }
@@ -486,7 +526,7 @@ __device__ __forceinline__ void window_eval_job(const WindowJob& J, const Window
     if (lane == 0) J.total[i] = total;
 }
 
-// grid (query groups of 8, jobs); warp = one query of one job. Not used by CCM_WIN_INIT.
+// grid (query groups of 8, jobs); warp = one query of one job (CCM_WIN_INIT takes the filter-free instantiation).
 #ifndef WIN_EVAL_MIN_CTAS
 #define WIN_EVAL_MIN_CTAS 6
 #endif
