@@ -24,6 +24,9 @@ struct ccm_matcher {
     cudaStream_t stream = nullptr;
     long long launches = 0;
     struct Buf { void* p = nullptr; size_t cap = 0; } buf[MB_COUNT];
+    // pinned host mirror of a call's device blob: the host entry points gather their input arrays here and send ONE copy up,
+    // and bring ONE copy back (a pageable cudaMemcpyAsync per array costs ~10 us each: 13 of them per SearchByBoW call)
+    uint8_t* h_stage = nullptr; size_t h_stage_cap = 0;
     std::string err;
 };
 
@@ -61,6 +64,19 @@ template <typename Tp> static int mbuf(ccm_matcher* m, int slot, size_t count, T
     return CCM_OK;
 }
 
+static int stage_host(ccm_matcher* m, size_t bytes, uint8_t** out) {
+    if (m->h_stage_cap < bytes) {
+        MCK(cudaStreamSynchronize(m->stream));
+        if (m->h_stage) cudaFreeHost(m->h_stage);
+        m->h_stage = nullptr; m->h_stage_cap = 0;
+        const size_t want = bytes + bytes / 2 + 4096;
+        MCK(cudaMallocHost((void**)&m->h_stage, want));
+        m->h_stage_cap = want;
+    }
+    *out = m->h_stage;
+    return CCM_OK;
+}
+
 extern "C" {
 
 int ccm_matcher_create(int device, ccm_matcher** out) {
@@ -90,6 +106,7 @@ void ccm_matcher_destroy(ccm_matcher* m) {
     cudaSetDevice(m->device);
     if (m->stream) { cudaStreamSynchronize(m->stream); cudaStreamDestroy(m->stream); }
     for (auto& b : m->buf) if (b.p) cudaFree(b.p);
+    if (m->h_stage) cudaFreeHost(m->h_stage);
     delete m;
 }
 
@@ -477,29 +494,33 @@ int ccm_search_window(ccm_matcher* m, ccm_frame_pack* targets, const ccm_window_
     if (nq == 0) { if (nmatches) *nmatches = 0; return CCM_OK; }
     cudaSetDevice(m->device);
     int rc;
-    WindowQueryDev* dq; uint8_t* dqd; int* dh; MatchResultDev* dres; int* dnm;
     const int cap = targets->cap;
-    if ((rc = mbuf(m, MB_Q, (size_t)nq, &dq))) return rc;
-    if ((rc = mbuf(m, MB_QDESC, (size_t)nq * 32, &dqd))) return rc;
-    if ((rc = mbuf(m, MB_HOLDER, (size_t)cap, &dh))) return rc;
-    if ((rc = mbuf(m, MB_RES, (size_t)nq, &dres))) return rc;
-    if ((rc = mbuf(m, MB_NM, (size_t)1, &dnm))) return rc;
     int n_t = 0;
     if ((rc = ccm_frame_pack_count(targets, &n_t))) return rc;
-    MCK(cudaMemcpyAsync(dq, q, sizeof(WindowQueryDev) * nq, cudaMemcpyHostToDevice, m->stream));
-    MCK(cudaMemcpyAsync(dqd, q_desc, (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
+    // device blob [queries | query descriptors | holder | nmatches | results] with a pinned host mirror: the first three go up
+    // in one copy, the last three come back in one
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_q = 0, o_qd = o_q + up(sizeof(WindowQueryDev) * (size_t)nq), o_h = o_qd + up((size_t)nq * 32), o_nm = o_h + up(sizeof(int) * (size_t)cap),
+                 o_res = o_nm + 256, total = o_res + up(sizeof(MatchResultDev) * (size_t)nq);
+    uint8_t *dbase, *hbase;
+    if ((rc = mbuf(m, MB_Q, total, &dbase))) return rc;
+    if ((rc = stage_host(m, total, &hbase))) return rc;
     const bool holder_in = holder && prm->mode != CCM_WIN_BEST && prm->mode != CCM_WIN_INIT;
-    if (holder_in && n_t > 0) MCK(cudaMemcpyAsync(dh, holder, sizeof(int) * n_t, cudaMemcpyHostToDevice, m->stream));
+    std::memcpy(hbase + o_q, q, sizeof(WindowQueryDev) * (size_t)nq);
+    std::memcpy(hbase + o_qd, q_desc, (size_t)nq * 32);
+    if (holder_in && n_t > 0) std::memcpy(hbase + o_h, holder, sizeof(int) * (size_t)n_t);
+    MCK(cudaMemcpyAsync(dbase, hbase, holder_in && n_t > 0 ? o_h + sizeof(int) * (size_t)n_t : o_qd + (size_t)nq * 32, cudaMemcpyHostToDevice, m->stream));
     ccm_frame_pack* packs[1] = {targets};
-    rc = ccm_search_window_batch_device(m, packs, 1, prm, nullptr, nq, (const ccm_window_query*)dq, dqd, dh, cap,
-                                        res ? (ccm_match_result*)dres : nullptr, dnm);
+    rc = ccm_search_window_batch_device(m, packs, 1, prm, nullptr, nq, (const ccm_window_query*)(dbase + o_q), dbase + o_qd, (int*)(dbase + o_h), cap,
+                                        res ? (ccm_match_result*)(dbase + o_res) : nullptr, (int*)(dbase + o_nm));
     if (rc) return rc;
-    int nm = 0;
-    MCK(cudaMemcpyAsync(&nm, dnm, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
-    if (res) MCK(cudaMemcpyAsync(res, dres, sizeof(MatchResultDev) * nq, cudaMemcpyDeviceToHost, m->stream));
-    if (holder && prm->mode != CCM_WIN_BEST && n_t > 0) MCK(cudaMemcpyAsync(holder, dh, sizeof(int) * n_t, cudaMemcpyDeviceToHost, m->stream));
+    const bool holder_out = holder && prm->mode != CCM_WIN_BEST && n_t > 0;
+    const size_t d0 = holder_out ? o_h : o_nm, d1 = res ? o_res + sizeof(MatchResultDev) * (size_t)nq : o_nm + sizeof(int);
+    MCK(cudaMemcpyAsync(hbase + d0, dbase + d0, d1 - d0, cudaMemcpyDeviceToHost, m->stream));
     MCK(cudaStreamSynchronize(m->stream));
-    if (nmatches) *nmatches = nm;
+    if (nmatches) std::memcpy(nmatches, hbase + o_nm, sizeof(int));
+    if (res) std::memcpy(res, hbase + o_res, sizeof(MatchResultDev) * (size_t)nq);
+    if (holder_out) std::memcpy(holder, hbase + o_h, sizeof(int) * (size_t)n_t);
     return CCM_OK;
 }
 
@@ -545,43 +566,41 @@ static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_or
         else ib = eb;
     }
     int rc;
-    uint8_t *dda, *ddb, *dva, *dvb; float *daa, *dab; int *doa, *dob, *dma, *dmb, *dnm; BowNode* dn; MatchResultDev* dres;
-    uint8_t* blob_a; uint8_t* blob_b;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     const size_t A = (size_t)n_a, B = (size_t)n_b;
-    // side A blob: desc | valid | angle | order | match | res ; side B blob: desc | valid | angle | order | match
-    // (triangulation adds x | y | node index per order position to A and x | y | octave to B)
-    const size_t a_desc = 0, a_val = a_desc + up(A * 32), a_ang = a_val + up(A), a_ord = a_ang + up(A * 4), a_mat = a_ord + up(A * 4),
-                 a_res = a_mat + up(A * 4), a_x = a_res + up(A * 16), a_y = a_x + up(A * 4), a_nod = a_y + up(A * 4),
-                 a_tot = tri ? a_nod + up(A * 4) : a_x;
-    const size_t b_desc = 0, b_val = b_desc + up(B * 32), b_ang = b_val + up(B), b_ord = b_ang + up(B * 4), b_mat = b_ord + up(B * 4),
-                 b_x = b_mat + up(B * 4), b_y = b_x + up(B * 4), b_oct = b_y + up(B * 4), b_tot = tri ? b_oct + up(B * 4) : b_x;
-    if ((rc = mbuf(m, MB_A, a_tot, &blob_a))) return rc;
-    if ((rc = mbuf(m, MB_B, b_tot, &blob_b))) return rc;
-    if ((rc = mbuf(m, MB_C, nodes.size() + 1, &dn))) return rc;
-    if ((rc = mbuf(m, MB_NM, (size_t)1, &dnm))) return rc;
-    dda = blob_a + a_desc; dva = blob_a + a_val; daa = (float*)(blob_a + a_ang); doa = (int*)(blob_a + a_ord); dma = (int*)(blob_a + a_mat);
-    dres = (MatchResultDev*)(blob_a + a_res);
-    ddb = blob_b + b_desc; dvb = blob_b + b_val; dab = (float*)(blob_b + b_ang); dob = (int*)(blob_b + b_ord); dmb = (int*)(blob_b + b_mat);
-    MCK(cudaMemcpyAsync(dda, desc_a, A * 32, cudaMemcpyHostToDevice, m->stream));
-    MCK(cudaMemcpyAsync(dva, valid_a, A, cudaMemcpyHostToDevice, m->stream));
-    MCK(cudaMemcpyAsync(daa, angle_a, A * 4, cudaMemcpyHostToDevice, m->stream));
-    if (!oa.empty()) MCK(cudaMemcpyAsync(doa, oa.data(), oa.size() * 4, cudaMemcpyHostToDevice, m->stream));
-    MCK(cudaMemcpyAsync(ddb, desc_b, B * 32, cudaMemcpyHostToDevice, m->stream));
-    if (valid_b) MCK(cudaMemcpyAsync(dvb, valid_b, B, cudaMemcpyHostToDevice, m->stream));
-    MCK(cudaMemcpyAsync(dab, angle_b, B * 4, cudaMemcpyHostToDevice, m->stream));
-    if (!ob.empty()) MCK(cudaMemcpyAsync(dob, ob.data(), ob.size() * 4, cudaMemcpyHostToDevice, m->stream));
-    if (!nodes.empty()) MCK(cudaMemcpyAsync(dn, nodes.data(), nodes.size() * sizeof(BowNode), cudaMemcpyHostToDevice, m->stream));
+    // one device blob with a pinned host mirror. Inputs (one copy up): side A desc | valid | angle | order (triangulation: + x |
+    // y | node index per order position), side B desc | valid | angle | order (+ x | y | octave), shared-node table. Outputs
+    // (one copy back): nmatches | match_a | match_b | res_a.
+    size_t o = 0;
+    auto take = [&](size_t bytes) { const size_t at = o; o += up(bytes); return at; };
+    const size_t a_desc = take(A * 32), a_val = take(A), a_ang = take(A * 4), a_ord = take(A * 4);
+    const size_t a_x = tri ? take(A * 4) : 0, a_y = tri ? take(A * 4) : 0, a_nod = tri ? take(A * 4) : 0;
+    const size_t b_desc = take(B * 32), b_val = take(B), b_ang = take(B * 4), b_ord = take(B * 4);
+    const size_t b_x = tri ? take(B * 4) : 0, b_y = tri ? take(B * 4) : 0, b_oct = tri ? take(B * 4) : 0;
+    const size_t o_nodes = take((nodes.size() + 1) * sizeof(BowNode));
+    const size_t in_total = o;
+    const size_t o_nm = take(sizeof(int)), o_ma = take(A * 4), o_mb = take(B * 4), o_res = take(A * sizeof(MatchResultDev));
+    const size_t total = o;
+    uint8_t *dbase, *hbase;
+    if ((rc = mbuf(m, MB_A, total, &dbase))) return rc;
+    if ((rc = stage_host(m, total, &hbase))) return rc;
+    std::memcpy(hbase + a_desc, desc_a, A * 32); std::memcpy(hbase + a_val, valid_a, A); std::memcpy(hbase + a_ang, angle_a, A * 4);
+    if (!oa.empty()) std::memcpy(hbase + a_ord, oa.data(), oa.size() * 4);
+    std::memcpy(hbase + b_desc, desc_b, B * 32); if (valid_b) std::memcpy(hbase + b_val, valid_b, B); std::memcpy(hbase + b_ang, angle_b, B * 4);
+    if (!ob.empty()) std::memcpy(hbase + b_ord, ob.data(), ob.size() * 4);
+    if (!nodes.empty()) std::memcpy(hbase + o_nodes, nodes.data(), nodes.size() * sizeof(BowNode));
     BowJob J;
-    J.desc_a = dda; J.desc_b = ddb; J.valid_a = dva; J.valid_b = valid_b ? dvb : nullptr; J.angle_a = daa; J.angle_b = dab;
-    J.order_a = doa; J.order_b = dob; J.nodes = dn; J.n_nodes = (int)nodes.size(); J.n_a = n_a; J.n_b = n_b;
-    J.match_a = dma; J.match_b = dmb; J.res_a = res_a ? dres : nullptr; J.nmatches = dnm;
+    J.desc_a = dbase + a_desc; J.desc_b = dbase + b_desc; J.valid_a = dbase + a_val; J.valid_b = valid_b ? dbase + b_val : nullptr;
+    J.angle_a = (const float*)(dbase + a_ang); J.angle_b = (const float*)(dbase + b_ang);
+    J.order_a = (const int*)(dbase + a_ord); J.order_b = (const int*)(dbase + b_ord); J.nodes = (const BowNode*)(dbase + o_nodes);
+    J.n_nodes = (int)nodes.size(); J.n_a = n_a; J.n_b = n_b;
+    J.match_a = (int*)(dbase + o_ma); J.match_b = (int*)(dbase + o_mb); J.res_a = res_a ? (MatchResultDev*)(dbase + o_res) : nullptr;
+    J.nmatches = (int*)(dbase + o_nm);
     J.mode = mode; J.nnratio = nnratio; J.th_low = CCM_TH_LOW; J.check_orientation = check_orientation;
-    k_bow_init<<<(std::max(n_a, n_b) + 255) / 256, 256, 0, m->stream>>>(J);
+    TriGeom G;
     if (tri) {
-        TriGeom G;
-        G.x_a = (const float*)(blob_a + a_x); G.y_a = (const float*)(blob_a + a_y);
-        G.x_b = (const float*)(blob_b + b_x); G.y_b = (const float*)(blob_b + b_y); G.oct_b = (const int*)(blob_b + b_oct);
+        G.x_a = (const float*)(dbase + a_x); G.y_a = (const float*)(dbase + a_y);
+        G.x_b = (const float*)(dbase + b_x); G.y_b = (const float*)(dbase + b_y); G.oct_b = (const int*)(dbase + b_oct);
         std::memcpy(G.f, tri->g->f12, sizeof(G.f));
         G.ex = tri->g->ex; G.ey = tri->g->ey;
         for (int l = 0; l < 16; l++) {
@@ -593,28 +612,28 @@ static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_or
             G.line_th[l] = tf;
         }
         // position in order_a -> index of its shared node (-1: the node does not occur in pKF2's vector)
-        std::vector<int> a_node(oa.size() ? oa.size() : 1, -1);
+        int* a_node = (int*)(hbase + a_nod);
+        for (size_t k = 0; k < std::max<size_t>(oa.size(), 1); k++) a_node[k] = -1;
         for (size_t k = 0; k < nodes.size(); k++) for (int i = nodes[k].a0; i < nodes[k].a1; i++) a_node[i] = (int)k;
-        MCK(cudaMemcpyAsync(blob_a + a_nod, a_node.data(), a_node.size() * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(blob_a + a_x, tri->x_a, A * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(blob_a + a_y, tri->y_a, A * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(blob_b + b_x, tri->x_b, B * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(blob_b + b_y, tri->y_b, B * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(blob_b + b_oct, tri->oct_b, B * 4, cudaMemcpyHostToDevice, m->stream));
+        std::memcpy(hbase + a_x, tri->x_a, A * 4); std::memcpy(hbase + a_y, tri->y_a, A * 4);
+        std::memcpy(hbase + b_x, tri->x_b, B * 4); std::memcpy(hbase + b_y, tri->y_b, B * 4); std::memcpy(hbase + b_oct, tri->oct_b, B * 4);
+    }
+    MCK(cudaMemcpyAsync(dbase, hbase, in_total, cudaMemcpyHostToDevice, m->stream));
+    k_bow_init<<<(std::max(n_a, n_b) + 255) / 256, 256, 0, m->stream>>>(J);
+    if (tri) {
         J.n_a = (int)oa.size();                       // the search walks order_a positions
-        if (J.n_nodes > 0 && J.n_a > 0) k_tri_search<<<(J.n_a + 7) / 8, 256, 0, m->stream>>>(J, G, (const int*)(blob_a + a_nod));
+        if (J.n_nodes > 0 && J.n_a > 0) k_tri_search<<<(J.n_a + 7) / 8, 256, 0, m->stream>>>(J, G, (const int*)(dbase + a_nod));
         J.n_a = n_a;
     } else if (J.n_nodes > 0) k_bow_search<<<(J.n_nodes + 7) / 8, 256, 0, m->stream>>>(J);
     k_bow_finish<<<1, 1024, 0, m->stream>>>(J);
     m->launches += J.n_nodes > 0 ? 3 : 2;
     MCK(cudaGetLastError());
-    int nm = 0;
-    MCK(cudaMemcpyAsync(&nm, dnm, sizeof(int), cudaMemcpyDeviceToHost, m->stream));
-    if (match_a) MCK(cudaMemcpyAsync(match_a, dma, A * 4, cudaMemcpyDeviceToHost, m->stream));
-    if (match_b) MCK(cudaMemcpyAsync(match_b, dmb, B * 4, cudaMemcpyDeviceToHost, m->stream));
-    if (res_a) MCK(cudaMemcpyAsync(res_a, dres, A * sizeof(MatchResultDev), cudaMemcpyDeviceToHost, m->stream));
+    MCK(cudaMemcpyAsync(hbase + o_nm, dbase + o_nm, (res_a ? total : o_res) - o_nm, cudaMemcpyDeviceToHost, m->stream));
     MCK(cudaStreamSynchronize(m->stream));
-    if (nmatches) *nmatches = nm;
+    if (match_a) std::memcpy(match_a, hbase + o_ma, A * 4);
+    if (match_b) std::memcpy(match_b, hbase + o_mb, B * 4);
+    if (res_a) std::memcpy(res_a, hbase + o_res, A * sizeof(MatchResultDev));
+    if (nmatches) std::memcpy(nmatches, hbase + o_nm, sizeof(int));
     return CCM_OK;
 }
 
