@@ -122,7 +122,11 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const int pitch = L.img_pitch;
     uint8_t* __restrict__ outp = L.blur + (size_t)f * L.blur_stride + (size_t)wy0 * L.blur_pitch + x;
     if (w < 16) { blur_small_level<OCV24>(img, pitch, L.blur + (size_t)f * L.blur_stride, L.blur_pitch, w, h, out_lane ? x : w, wy0); return; }   // warp-uniform
-    uint32_t ring[7][4];
+    // Vertical pass on row PAIRS: pr[j][k] = hsum(row j-1) | hsum(row j) << 16 of pixel k (the sums are <= 65535), so that one
+    // IDP2A applies two taps: out(c) = dp2a(pr[c-2], k0|k1) + dp2a(pr[c], k2|k3) + dp2a(pr[c+2], k2|k1) + dp2a(pr[c+3], 0|k0)
+    // = 4 instructions per pixel (+ one PRMT to form the pair) instead of 3 adds + 4 multiply-adds.
+    uint32_t pr[6][4];                 // pairs ending at the last six rows
+    uint32_t last[4] = {0u, 0u, 0u, 0u};
     uint32_t sel_lo, sel_hi;
     blur_tail_selectors(w, sel_lo, sel_hi);
     // source row of window row r is wy0 + r - 3 (rows past the bottom only feed outputs that are never stored).
@@ -130,20 +134,24 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const bool inner = wy0 >= 3 && wy0 + BLUR_RPW + 3 <= h;   // warp-uniform
     const uint8_t* row = img + (size_t)ccm_reflect101(min(wy0 - 3, h + 2), h) * pitch;
     uint32_t own = blur_load(row, x, w);
+    const uint32_t W01 = K::k0 | (K::k1 << 8), W23 = K::k2 | (K::k3 << 8), W21 = K::k2 | (K::k1 << 8), W_0 = K::k0 << 8;
 #pragma unroll
     for (int r = 0; r < BLUR_RPW + 6; r++) {
         const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
         const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
-        blur_hrow<OCV24>(row, own, x, x0, w, lane, sel_lo, sel_hi, ring[r % 7]);
+        uint32_t hs[4];
+        blur_hrow<OCV24>(row, own, x, x0, w, lane, sel_lo, sel_hi, hs);
         row = row_n; own = own_n;
+#pragma unroll
+        for (int k = 0; k < 4; k++) { pr[r % 6][k] = __byte_perm(last[k], hs[k], 0x5410); last[k] = hs[k]; }   // (row r-1, row r)
         if (r >= 6) {
-            const int oy = wy0 + r - 6;
+            const int oy = wy0 + r - 6;               // centre row c = r - 3: pairs ending at c-2, c, c+2, c+3 = r-5, r-3, r-1, r
             uint32_t packed = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
-                const uint32_t acc = K::k0 * (ring[(r - 6) % 7][k] + ring[r % 7][k]) + K::k1 * (ring[(r - 5) % 7][k] + ring[(r - 1) % 7][k]) +
-                                     K::k2 * (ring[(r - 4) % 7][k] + ring[(r - 2) % 7][k]) + K::k3 * ring[(r - 3) % 7][k];
-                const uint32_t v = (acc + 32768u) >> 16;
+                const uint32_t acc = __dp2a_lo(pr[(r - 5) % 6][k], W01, __dp2a_lo(pr[(r - 3) % 6][k], W23, __dp2a_lo(pr[(r - 1) % 6][k], W21,
+                                               __dp2a_lo(pr[r % 6][k], W_0, 32768u))));
+                const uint32_t v = acc >> 16;
                 packed |= (OCV24 ? min(v, 255u) : v) << (8 * k);
             }
             if (out_lane && oy < h && x < w) *reinterpret_cast<uint32_t*>(outp) = packed;   // pitch multiple of 32: in-bounds
