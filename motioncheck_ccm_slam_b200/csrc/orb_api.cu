@@ -41,6 +41,7 @@ struct ccm_orb {
     bool fc_tma = false;                               // tensor maps of the arena levels are encoded (box FC_TW x tile_rows)
     FastTma fc_tmaps = {};
     float4* d_pat = nullptr;                           // k_orient_describe's test pattern table
+    uint8_t* d_desc_block_level = nullptr;             // level of every CTA of k_orient_describe's grid
     uint32_t* d_corners = nullptr; int* d_corner_count = nullptr; uint16_t* d_node_of = nullptr;
     uint32_t* d_level_kps = nullptr; int* d_level_kp_count = nullptr;
     ccm_keypoint* d_kp = nullptr; uint8_t* d_desc = nullptr; int* d_n = nullptr;
@@ -321,6 +322,11 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         orb_pattern_table(pt);
         if ((rc = dev_alloc(h, &h->d_pat, 256))) return rc;
         CK(cudaMemcpy(h->d_pat, pt, sizeof(pt), cudaMemcpyHostToDevice));
+        std::vector<uint8_t> bl((size_t)std::max(desc_blocks, 1), 0);
+        for (int l = 0; l < L; l++)
+            for (int b = T.l[l].desc_block_base; b < (l + 1 < L ? T.l[l + 1].desc_block_base : desc_blocks); b++) bl[b] = (uint8_t)l;
+        if ((rc = dev_alloc(h, &h->d_desc_block_level, bl.size()))) return rc;
+        CK(cudaMemcpy(h->d_desc_block_level, bl.data(), bl.size(), cudaMemcpyHostToDevice));
     }
     if (!h->encode_tiled && !std::getenv("CCM_ORB_NO_TMA")) {
         cudaDriverEntryPointQueryResult q;
@@ -447,7 +453,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
             CK(cudaStreamWaitEvent(s, LN.join, 0));
         }
         if (st) CK(cudaEventRecord(h->ev[4], s));
-        k_orient_describe<<<dim3(T.total_desc_blocks, n), 256, 0, s>>>(T, h->d_pat, A.level_kps, A.level_kp_count,
+        k_orient_describe<<<dim3(T.total_desc_blocks, n), 256, 0, s>>>(T, h->d_pat, h->d_desc_block_level, A.level_kps, A.level_kp_count,
                                                                             (ccm_keypoint_dev*)d_kp, d_desc, d_n, capacity);
         CKL("k_orient_describe", cudaSuccess);
         h->launches++;

@@ -209,6 +209,7 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 
 __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__ LevelTable T,
                                                          const float4* __restrict__ pat_table,       // [8][32], see below (host-built)
+                                                         const uint8_t* __restrict__ block_level,    // [total_desc_blocks] level of each CTA
                                                          const uint32_t* __restrict__ level_kps,     // [frames][kps_per_frame]
                                                          const int* __restrict__ level_kp_count,     // [frames][CCM_MAX_LEVELS]
                                                          ccm_keypoint_dev* __restrict__ out_kp,      // [frames][capacity]
@@ -223,9 +224,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     if (tid < CCM_MAX_LEVELS) s_cnt[tid] = tid < T.nlevels ? level_kp_count[f * CCM_MAX_LEVELS + tid] : 0;
     // A CTA's 8 slots belong to one level (host grid: desc_block_base), so the level, its image bases and pitches are
     // CTA-uniform: they live in uniform registers and every pixel load below is [uniform base + 32-bit offset].
-    int lvl = 0;
-#pragma unroll 1
-    while (lvl + 1 < T.nlevels && (int)blockIdx.x >= T.l[lvl + 1].desc_block_base) lvl++;
+    const int lvl = __ldg(block_level + blockIdx.x);          // host table (configure_shape): level of every CTA of the grid
     const LevelDesc& L = T.l[lvl];
     __syncthreads();
     // keypoints of the lower levels come first in the output (:1239-1276): lane l holds level l's count
