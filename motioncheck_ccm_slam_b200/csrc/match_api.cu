@@ -421,7 +421,7 @@ static int fill_params(ccm_matcher* m, const ccm_window_params* prm, WindowParam
     if (!prm || prm->mode < CCM_WIN_PROJ_MAPPOINTS || prm->mode > CCM_WIN_INIT) { m->err = "bad window mode"; return CCM_E_BADARG; }
     std::memset(d, 0, sizeof(*d));
     d->mode = prm->mode; d->nnratio = prm->nnratio; d->th_dist = prm->th_dist; d->check_orientation = prm->check_orientation;
-    d->use_gate = 0;
+    d->use_gate = 0; d->mc_smem_ints = 0;
     if (prm->mode == CCM_WIN_BEST && prm->inv_sigma2) {
         if (prm->n_levels <= 0 || prm->n_levels > CCM_MATCH_MAX_LEVELS) { m->err = "n_levels must be 1..16 with inv_sigma2"; return CCM_E_BADARG; }
         d->use_gate = 1;
@@ -480,7 +480,10 @@ int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs,
     MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(WindowJob) * n_jobs, cudaMemcpyHostToDevice, m->stream));
     k_window_eval<<<dim3((q_stride + 7) / 8, n_jobs), 256, 0, m->stream>>>(djobs, P);
     m->launches++;
-    k_window_resolve<<<n_jobs, WIN_THREADS, 0, m->stream>>>(djobs, P);
+    // the resolver's three lowest-claimant arrays in shared memory when they fit next to its static use (<= 40 KB)
+    const size_t mc_bytes = 3 * (size_t)max_cap * sizeof(int);
+    P.mc_smem_ints = (P.mode != CCM_WIN_BEST && P.mode != CCM_WIN_INIT && mc_bytes <= 40 * 1024) ? 3 * max_cap : 0;
+    k_window_resolve<<<n_jobs, WIN_THREADS, (size_t)P.mc_smem_ints * sizeof(int), m->stream>>>(djobs, P);
     m->launches++;
     MCK(cudaGetLastError());
     return CCM_OK;

@@ -66,6 +66,7 @@ struct WindowParamsDev {
     int th_dist;
     int check_orientation;
     int use_gate;
+    int mc_smem_ints;          // dynamic shared memory of k_window_resolve in ints (0: the claimant arrays stay in global scratch)
     float inv_sigma2[CCM_MATCH_MAX_LEVELS];
 };
 

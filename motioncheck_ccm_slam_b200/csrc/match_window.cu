@@ -299,7 +299,22 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
     // decided, and CLEARS mc[(it+2) % 3] for the round after. A round is therefore one pass over the queries and ONE barrier
     // (it used to be clear / rebuild / evaluate with five); the iteration itself is unchanged: every query is evaluated against
     // the claims of the previous round (Jacobi), until no claim changes.
-    int* mc[3] = {J.head, J.head + P.cap, J.head + 2 * P.cap};
+    // The three arrays live in shared memory when the host reserved it for this launch (3 * cap ints), else in the job's scratch.
+    extern __shared__ int s_mc[];
+    int* mcbase = prm.mc_smem_ints >= 3 * P.cap ? s_mc : J.head;
+    int* mc[3] = {mcbase, mcbase + P.cap, mcbase + 2 * P.cap};
+    // the keys of a thread's first query stay in registers over the rounds (every query when nq <= blockDim.x): 64-bit form,
+    // i.e. the feature index is fetched from items[] once, not once per round
+    unsigned long long rk[WIN_TOPK];
+    uint32_t rflags = 0; int rtotal = 0;
+    if ((int)threadIdx.x < nq) {
+        rflags = J.q[threadIdx.x].flags; rtotal = J.total[threadIdx.x];
+#pragma unroll
+        for (int r = 0; r < WIN_TOPK; r++) {
+            const uint32_t k = J.keys[(size_t)WIN_TOPK * threadIdx.x + r];
+            rk[r] = (r < min(rtotal, WIN_TOPK) && k != KEY32_NONE) ? key32_to_key64(P, k) : KEY_NONE;
+        }
+    }
 
     if (threadIdx.x == 0) { s_nm = 0; s_nfb[0] = 0; s_nfb[1] = 0; s_nfb[2] = 0; }
     if (threadIdx.x < 32) s_hist[threadIdx.x] = 0;
@@ -319,18 +334,22 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
             for (int i = threadIdx.x; i < n; i += blockDim.x) mclear[i] = 0x7fffffff;
         // one thread per query, from the keys k_window_eval stored
         for (int i = threadIdx.x; i < nq; i += blockDim.x) {
-            const uint32_t flags = J.q[i].flags;
+            const bool first = i == (int)threadIdx.x;
+            const uint32_t flags = first ? rflags : J.q[i].flags;
             WinEval e; e.b1 = KEY_NONE; e.b2 = KEY_NONE;
             bool fallback = false;
             if (flags & WQ_VALID) {
-                const int total = J.total[i];
+                const int total = first ? rtotal : J.total[i];
                 const int have = min(total, WIN_TOPK);
                 int found = 0;
-                for (int r = 0; r < have; r++) {
-                    const unsigned long long key = key32_to_key64(P, J.keys[(size_t)WIN_TOPK * i + r]);
+#pragma unroll
+                for (int r = 0; r < WIN_TOPK; r++) {
+                    if (r >= have || found == 2) break;
+                    const unsigned long long key = first ? rk[r] : key32_to_key64(P, J.keys[(size_t)WIN_TOPK * i + r]);
+                    if (key == KEY_NONE) break;
                     if (stateful && mcur[(int)(key & 0xffff)] < i) continue;
                     if (found == 0) e.b1 = key; else { e.b2 = key; }
-                    if (++found == 2) break;
+                    ++found;
                 }
                 const int need = (MODE == WIN_MODE_MAPPOINTS) ? 2 : 1;
                 fallback = found < need && total > WIN_TOPK;
