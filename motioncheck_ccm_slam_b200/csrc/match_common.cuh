@@ -55,7 +55,7 @@ struct WindowJob {
     int* head;                 // [3 * pack.cap] lowest blocking claimant per target, three rotating copies (INIT: vMatchedDistance in the first)
     int* claim[2];             // [nq_cap] x2  claimed target per query (ping-pong), -1 none (INIT: vnMatches12, accept bin)
     int* qbest;                // [nq_cap] x3  best idx, best dist, best dist2 of the last evaluation
-    uint32_t* keys;            // [nq_cap] x WIN_TOPK  best candidate keys of the static pass (k_window_eval): distance << 16 | CSR position
+    uint32_t* keys;            // [nq_cap] x WIN_TOPK  best candidates of the static pass (k_window_eval), best first: distance << 16 | feature index; an exact prefix of the window's ranking, 0xffffffff after it
     int* total;                // [nq_cap]   candidates that passed the static filters
     int* fb;                   // [nq_cap]   queries that must re-walk the grid this round
 };

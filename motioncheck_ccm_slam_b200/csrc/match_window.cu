@@ -31,7 +31,7 @@
 #define WQ_VALID 1u
 #define WQ_BLOCKS 2u
 #define KEY_NONE 0xffffffffffffffffull
-#define WIN_TOPK 4
+#define WIN_TOPK 8
 
 // ---- frame pack construction ----------------------------------------------------------------------------------
 // ccm_keypoint (AoS, extractor output) -> pack SoA, one CTA per pack; xy_un overrides the positions (mvKeysUn of a
@@ -181,20 +181,20 @@ __device__ __forceinline__ WinEval eval_query(const PackDev& P, const WindowPara
 
 // static pass: candidates under the query-independent filters (window, levels, gate, the holder state the call
 // started with), best WIN_TOPK keys in keys[] (ascending, KEY_NONE padded) and the number of candidates that passed
-// Keys of the static pass are 32 bits: distance << 16 | CSR position of the candidate in the pack's grid. The CSR is in
+// While a window is walked its keys are 32 bits: distance << 16 | CSR position of the candidate in the pack's grid (the
+// position is swapped for the feature index when the list is stored). The CSR is in
 // (ix * rows + iy) cell order with ascending feature indices inside a cell, i.e. positions inside one window ascend exactly in
 // the order GetFeaturesInArea emits the features, so the position is both the reference's first-wins tie-break and (through
 // items[]) the feature index. One REDUX per warp minimum instead of five 64-bit shuffle steps.
 #define KEY32_NONE 0xffffffffu
-__device__ __forceinline__ unsigned long long key32_to_key64(const PackDev& P, uint32_t k) {
-    const uint32_t p = k & 0xffffu;
-    return ((unsigned long long)(k >> 16) << 32) | ((unsigned long long)p << 16) | (unsigned)P.items[p];
+__device__ __forceinline__ unsigned long long key32_to_key64(uint32_t k) {      // stored key (distance << 16 | feature) -> WinEval key
+    return ((unsigned long long)(k >> 16) << 32) | (unsigned long long)(k & 0xffffu);
 }
 
 template <int MODE>
 __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowParamsDev& prm, const WindowQueryDev& q,
                                                 const uint4 qd0, const uint4 qd1, const int* __restrict__ holder, int lane,
-                                                uint32_t (&keys)[WIN_TOPK], int& total) {
+                                                uint32_t& mine, int& total) {
     uint32_t k0 = KEY32_NONE, k1 = KEY32_NONE, k2 = KEY32_NONE, k3 = KEY32_NONE;
     int cnt = 0;
     const float fx = __fsub_rn(q.u, P.min_x), fy = __fsub_rn(q.v, P.min_y);
@@ -251,12 +251,28 @@ __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowPa
             }
         }
     }
+    // A lane keeps its own four best. The warp's WIN_TOPK best are popped off the lanes in order; once a lane that saw more than
+    // four candidates has given all four away, its fifth (unknown) might be the next one, so the list ends there: the keys
+    // stored are always an exact PREFIX of the window's ranking, KEY32_NONE after it, and the resolve pass compares `total`
+    // with the number of keys it was given to know whether the list is complete.
+    int left = min(cnt, 4);
+    const bool risky = __any_sync(0xffffffffu, cnt > 4);
+    bool open = true;
 #pragma unroll
     for (int r = 0; r < WIN_TOPK; r++) {
-        const uint32_t m = __reduce_min_sync(0xffffffffu, k0);
-        keys[r] = m;
-        if (k0 == m && m != KEY32_NONE) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY32_NONE; }   // keys are unique: one lane pops
+        uint32_t m = KEY32_NONE;
+        if (open) {                                        // warp-uniform
+            m = __reduce_min_sync(0xffffffffu, k0);
+            if (m == KEY32_NONE) open = false;
+            else {
+                if (k0 == m) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY32_NONE; --left; }      // keys are unique: one lane pops
+                if (risky && __any_sync(0xffffffffu, left == 0 && cnt > 4)) open = false;
+            }
+        }
+        if (lane == r) mine = m;                            // lane r keeps the r-th best
     }
+    // the resolve pass wants the feature, not its CSR position (the list order already carries the first-wins tie-break)
+    if (mine != KEY32_NONE) mine = (mine & 0xffff0000u) | (uint32_t)P.items[mine & 0xffffu];
     total = __reduce_add_sync(0xffffffffu, cnt);
 }
 
@@ -305,14 +321,14 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
     int* mc[3] = {mcbase, mcbase + P.cap, mcbase + 2 * P.cap};
     // the keys of a thread's first query stay in registers over the rounds (every query when nq <= blockDim.x): 64-bit form,
     // i.e. the feature index is fetched from items[] once, not once per round
-    unsigned long long rk[WIN_TOPK];
+    uint32_t rk[WIN_TOPK];
     uint32_t rflags = 0; int rtotal = 0;
     if ((int)threadIdx.x < nq) {
         rflags = J.q[threadIdx.x].flags; rtotal = J.total[threadIdx.x];
 #pragma unroll
         for (int r = 0; r < WIN_TOPK; r++) {
             const uint32_t k = J.keys[(size_t)WIN_TOPK * threadIdx.x + r];
-            rk[r] = (r < min(rtotal, WIN_TOPK) && k != KEY32_NONE) ? key32_to_key64(P, k) : KEY_NONE;
+            rk[r] = r < min(rtotal, WIN_TOPK) ? k : KEY32_NONE;
         }
     }
 
@@ -341,18 +357,20 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
             if (flags & WQ_VALID) {
                 const int total = first ? rtotal : J.total[i];
                 const int have = min(total, WIN_TOPK);
-                int found = 0;
+                int found = 0, given = 0;                  // given: keys seen (counts the whole list whenever found < need)
 #pragma unroll
                 for (int r = 0; r < WIN_TOPK; r++) {
                     if (r >= have || found == 2) break;
-                    const unsigned long long key = first ? rk[r] : key32_to_key64(P, J.keys[(size_t)WIN_TOPK * i + r]);
-                    if (key == KEY_NONE) break;
+                    const uint32_t k32 = first ? rk[r] : J.keys[(size_t)WIN_TOPK * i + r];
+                    if (k32 == KEY32_NONE) break;
+                    const unsigned long long key = key32_to_key64(k32);
+                    ++given;
                     if (stateful && mcur[(int)(key & 0xffff)] < i) continue;
                     if (found == 0) e.b1 = key; else { e.b2 = key; }
                     ++found;
                 }
                 const int need = (MODE == WIN_MODE_MAPPOINTS) ? 2 : 1;
-                fallback = found < need && total > WIN_TOPK;
+                fallback = found < need && total > given;
             }
             if (fallback) { J.fb[atomicAdd(nfb, 1)] = i; continue; }
             int bestIdx, bestDist, bestDist2;
@@ -384,6 +402,9 @@ __device__ void window_job(const WindowJob& J, const WindowParamsDev& prm) {
             }
             any |= __syncthreads_or(changed);
         }
+#ifdef CCM_DEBUG_ROUNDS
+        if (threadIdx.x == 0 && blockIdx.x < 3) printf("mode %d job %d round %d nfb %d any %d nq %d n %d\n", MODE, blockIdx.x, it, cnt, any, nq, n);
+#endif
         if (!stateful || !any) break;
     }
     __syncthreads();
@@ -458,7 +479,7 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
                 for (int r = 0; r < WIN_TOPK; r++) {
                     const uint32_t k = i < nq ? J.keys[(size_t)WIN_TOPK * i + r] : KEY32_NONE;
                     s_key[lane][r] = k;
-                    s_idx[lane][r] = k != KEY32_NONE ? P.items[k & 0xffffu] : 0;
+                    s_idx[lane][r] = k != KEY32_NONE ? (int)(k & 0xffffu) : 0;
                 }
                 s_flags[lane] = fl; s_total[lane] = tot;
             }
@@ -475,7 +496,8 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
                     const int dist = (int)(key >> 16);
                     const bool ok = key != KEY32_NONE && mdist[idx] > dist;              // vMatchedDistance, :487-488
                     const uint32_t b = __ballot_sync(0xffffffffu, ok);
-                    if (__popc(b) < 2 && total > WIN_TOPK) {                              // truncated list ran dry: exact re-walk
+                    const int given = __popc(__ballot_sync(0xffffffffu, key != KEY32_NONE));
+                    if (__popc(b) < 2 && total > given) {                              // truncated list ran dry: exact re-walk
                         const WinEval e = eval_query<WIN_MODE_INIT>(P, prm, J.q[i], qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], i,
                                                                     J.holder, nullptr, mdist, lane);
                         acc = accept_rule<WIN_MODE_INIT>(P, prm, e, bestIdx, bestDist, bestDist2);
@@ -531,17 +553,13 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
 template <int MODE>
 __device__ __forceinline__ void window_eval_job(const WindowJob& J, const WindowParamsDev& prm, int i, int lane) {
     const WindowQueryDev q = J.q[i];
-    uint32_t keys[WIN_TOPK];
+    uint32_t mine = KEY32_NONE;
     int total = 0;
     if (q.flags & WQ_VALID) {
         const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
-        eval_query_topk<MODE>(J.pack, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], J.holder, lane, keys, total);
-    } else {
-#pragma unroll
-        for (int r = 0; r < WIN_TOPK; r++) keys[r] = KEY32_NONE;
+        eval_query_topk<MODE>(J.pack, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], J.holder, lane, mine, total);
     }
-#pragma unroll
-    for (int r = 0; r < WIN_TOPK; r++) if (lane == r) J.keys[(size_t)WIN_TOPK * i + r] = keys[r];
+    if (lane < WIN_TOPK) J.keys[(size_t)WIN_TOPK * i + lane] = mine;
     if (lane == 0) J.total[i] = total;
 }
 
