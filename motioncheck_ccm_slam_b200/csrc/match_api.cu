@@ -478,7 +478,13 @@ int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs,
     }
     // pageable -> device copy is staged by the runtime before it returns, so `jobs` may die at scope exit
     MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(WindowJob) * n_jobs, cudaMemcpyHostToDevice, m->stream));
-    k_window_eval<<<dim3((q_stride + 7) / 8, n_jobs), 256, 0, m->stream>>>(djobs, P);
+    {   // lanes per query by the number of queries in flight: a batch is bound by resident warps (8 lanes each), one frame by
+        // the latency of its own walk (a whole warp each); measured 0.519 / 0.533 / 0.560 ms per tracking step at 8 / 16 / 32
+        const long long in_flight = (long long)q_stride * n_jobs;
+        if (in_flight >= 16384) k_window_eval<8><<<dim3((q_stride + 31) / 32, n_jobs), 256, 0, m->stream>>>(djobs, P);
+        else if (in_flight >= 4096) k_window_eval<16><<<dim3((q_stride + 15) / 16, n_jobs), 256, 0, m->stream>>>(djobs, P);
+        else k_window_eval<32><<<dim3((q_stride + 7) / 8, n_jobs), 256, 0, m->stream>>>(djobs, P);
+    }
     m->launches++;
     // the resolver's three lowest-claimant arrays in shared memory when they fit next to its static use (<= 40 KB)
     const size_t mc_bytes = 3 * (size_t)max_cap * sizeof(int);

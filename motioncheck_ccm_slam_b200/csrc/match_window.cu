@@ -191,89 +191,98 @@ __device__ __forceinline__ unsigned long long key32_to_key64(uint32_t k) {      
     return ((unsigned long long)(k >> 16) << 32) | (unsigned long long)(k & 0xffffu);
 }
 
-template <int MODE>
+// G lanes per query (8, 16 or 32; the launch picks by the number of queries in flight): a window holds a handful of candidates, so thirty-two lanes were mostly idle and the
+// kernel was bound by the number of resident warps times the length of the dependent load chain. The two halves run in
+// lock step (loop trip counts are the maximum over the warp, shuffles are G wide), `valid` = this group has a query at all.
+// Few queries in flight (one frame) are latency-bound instead and take G = 32.
+template <int MODE, int G>
 __device__ __forceinline__ void eval_query_topk(const PackDev& P, const WindowParamsDev& prm, const WindowQueryDev& q,
                                                 const uint4 qd0, const uint4 qd1, const int* __restrict__ holder, int lane,
-                                                uint32_t& mine, int& total) {
+                                                bool valid, uint32_t& mine, int& total) {
+    const unsigned FULL = 0xffffffffu;
+    const int sub = lane & (G - 1);
+    const unsigned gmask = (0xffffffffu >> (32 - G)) << (lane & (32 - G));
     uint32_t k0 = KEY32_NONE, k1 = KEY32_NONE, k2 = KEY32_NONE, k3 = KEY32_NONE;
     int cnt = 0;
     const float fx = __fsub_rn(q.u, P.min_x), fy = __fsub_rn(q.v, P.min_y);
-    const int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(fx, q.r), P.inv_w)));
-    const int maxCX = min(P.cols - 1, (int)ceilf(__fmul_rn(__fadd_rn(fx, q.r), P.inv_w)));
+    int minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(fx, q.r), P.inv_w)));
+    int maxCX = min(P.cols - 1, (int)ceilf(__fmul_rn(__fadd_rn(fx, q.r), P.inv_w)));
     const int minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(fy, q.r), P.inv_h)));
     const int maxCY = min(P.rows - 1, (int)ceilf(__fmul_rn(__fadd_rn(fy, q.r), P.inv_h)));
-    if (minCX < P.cols && maxCX >= 0 && minCY < P.rows && maxCY >= 0) {
-        const uint4* __restrict__ desc = reinterpret_cast<const uint4*>(P.desc);
-        // The window's grid columns are walked as ONE flattened candidate list (GetFeaturesInArea order: column by column,
-        // cells top to bottom, features in index order): lane j fetches the CSR range of column cx0 + j, an inclusive scan gives
-        // every column's first position, and the lanes then stride over all candidates of up to 32 columns at once. The
-        // dependent load chain (range -> item -> fields -> descriptor) is paid once per 32 candidates, not once per column.
-        for (int cx0 = minCX; cx0 <= maxCX; cx0 += 32) {
-            const int ix = cx0 + lane;
-            int s = 0, n = 0;
-            if (ix <= maxCX) { s = P.cell_start[ix * P.rows + minCY]; n = P.cell_start[ix * P.rows + maxCY + 1] - s; }
-            int inc = n;
+    if (!(valid && minCX < P.cols && maxCX >= 0 && minCY < P.rows && maxCY >= 0)) { minCX = 0; maxCX = -1; }
+    const int ncol = max(0, maxCX - minCX + 1);
+    int ncol_max = ncol;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += v; }
-            const int tot = __shfl_sync(0xffffffffu, inc, 31);
-            const int exc = inc - n;                       // position of this column's first candidate
-            for (int c0 = 0; c0 < tot; c0 += 32) {         // warp-uniform trip count: the shuffles below need all lanes
-                const int c = c0 + lane;
-                // column of candidate c = the first lane whose inclusive count exceeds c (binary search over the lanes by shuffle)
-                int lo = 0;
+    for (int o = G; o < 32; o <<= 1) ncol_max = max(ncol_max, __shfl_xor_sync(FULL, ncol_max, o));
+    const uint4* __restrict__ desc = reinterpret_cast<const uint4*>(P.desc);
+    // The window's grid columns are walked as ONE flattened candidate list (GetFeaturesInArea order: column by column,
+    // cells top to bottom, features in index order): lane j fetches the CSR range of column cb + j, an inclusive scan gives
+    // every column's first position, and the lanes then stride over all candidates of up to G columns at once. The
+    // dependent load chain (range -> item -> fields -> descriptor) is paid once per G candidates, not once per column.
+    for (int cb = 0; cb < ncol_max; cb += G) {
+        const int ix = minCX + cb + sub;
+        int s = 0, n = 0;
+        if (ix <= maxCX) { s = P.cell_start[ix * P.rows + minCY]; n = P.cell_start[ix * P.rows + maxCY + 1] - s; }
+        int inc = n;
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) { const int v = __shfl_sync(0xffffffffu, inc, lo + o - 1); if (v <= c) lo += o; }
-                const int s_j = __shfl_sync(0xffffffffu, s, lo), exc_j = __shfl_sync(0xffffffffu, exc, lo);
-                if (c >= tot) continue;
-                const int p = s_j + (c - exc_j);
-                const int k = P.items[p];
-                const int oct = P.octave[k];
-                if (oct < q.min_level) continue;
-                if (q.max_level >= 0 && oct > q.max_level) continue;
-                const float dx = __fsub_rn(P.x[k], q.u), dy = __fsub_rn(P.y[k], q.v);
-                if (!(fabsf(dx) < q.r && fabsf(dy) < q.r)) continue;
-                if (MODE == WIN_MODE_BEST && prm.use_gate) {
-                    const float ex = __fsub_rn(q.u, P.x[k]), ey = __fsub_rn(q.v, P.y[k]);
-                    const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
-                    if ((double)__fmul_rn(e2, prm.inv_sigma2[oct]) > 5.99) continue;
-                }
-                if (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) { if (holder[k] == -2) continue; }
-                else if (MODE == WIN_MODE_KF_SIM3) { if (holder[k] != -1) continue; }
-                const int dist = hamming256(qd0, qd1, desc[2 * (size_t)k], desc[2 * (size_t)k + 1]);
-                uint32_t key = ((uint32_t)dist << 16) | (uint32_t)p;
-                cnt++;
-                if (key < k3) {
-                    k3 = key;
-                    if (k3 < k2) { const uint32_t t2 = k2; k2 = k3; k3 = t2; }
-                    if (k2 < k1) { const uint32_t t1 = k1; k1 = k2; k2 = t1; }
-                    if (k1 < k0) { const uint32_t t0 = k0; k0 = k1; k1 = t0; }
-                }
+        for (int o = 1; o < G; o <<= 1) { const int v = __shfl_up_sync(FULL, inc, o, G); if (sub >= o) inc += v; }
+        const int tot = __shfl_sync(FULL, inc, G - 1, G);
+        const int exc = inc - n;                           // position of this column's first candidate
+        int tot_max = tot;
+#pragma unroll
+        for (int o = G; o < 32; o <<= 1) tot_max = max(tot_max, __shfl_xor_sync(FULL, tot_max, o));
+        for (int c0 = 0; c0 < tot_max; c0 += G) {         // warp-uniform trip count: the shuffles below need all lanes
+            const int c = c0 + sub;
+            // column of candidate c = the first lane whose inclusive count exceeds c (binary search over the lanes by shuffle)
+            int lo = 0;
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) { const int v = __shfl_sync(FULL, inc, lo + o - 1, G); if (v <= c) lo += o; }
+            const int s_j = __shfl_sync(FULL, s, lo, G), exc_j = __shfl_sync(FULL, exc, lo, G);
+            if (c >= tot) continue;
+            const int p = s_j + (c - exc_j);
+            const int k = P.items[p];
+            const int oct = P.octave[k];
+            if (oct < q.min_level) continue;
+            if (q.max_level >= 0 && oct > q.max_level) continue;
+            const float dx = __fsub_rn(P.x[k], q.u), dy = __fsub_rn(P.y[k], q.v);
+            if (!(fabsf(dx) < q.r && fabsf(dy) < q.r)) continue;
+            if (MODE == WIN_MODE_BEST && prm.use_gate) {
+                const float ex = __fsub_rn(q.u, P.x[k]), ey = __fsub_rn(q.v, P.y[k]);
+                const float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                if ((double)__fmul_rn(e2, prm.inv_sigma2[oct]) > 5.99) continue;
+            }
+            if (MODE == WIN_MODE_MAPPOINTS || MODE == WIN_MODE_LASTFRAME) { if (holder[k] == -2) continue; }
+            else if (MODE == WIN_MODE_KF_SIM3) { if (holder[k] != -1) continue; }
+            const int dist = hamming256(qd0, qd1, desc[2 * (size_t)k], desc[2 * (size_t)k + 1]);
+            uint32_t key = ((uint32_t)dist << 16) | (uint32_t)p;
+            cnt++;
+            if (key < k3) {
+                k3 = key;
+                if (k3 < k2) { const uint32_t t2 = k2; k2 = k3; k3 = t2; }
+                if (k2 < k1) { const uint32_t t1 = k1; k1 = k2; k2 = t1; }
+                if (k1 < k0) { const uint32_t t0 = k0; k0 = k1; k1 = t0; }
             }
         }
     }
-    // A lane keeps its own four best. The warp's WIN_TOPK best are popped off the lanes in order; once a lane that saw more than
-    // four candidates has given all four away, its fifth (unknown) might be the next one, so the list ends there: the keys
-    // stored are always an exact PREFIX of the window's ranking, KEY32_NONE after it, and the resolve pass compares `total`
-    // with the number of keys it was given to know whether the list is complete.
+    // A lane keeps its own four best. The query's WIN_TOPK best are popped off its lanes in order; once a lane that saw more
+    // than four candidates has given all four away, its fifth (unknown) might be the next one, so the list ends there: the
+    // keys stored are always an exact PREFIX of the window's ranking, KEY32_NONE after it, and the resolve pass compares
+    // `total` with the number of keys it was given to know whether the list is complete.
     int left = min(cnt, 4);
-    const bool risky = __any_sync(0xffffffffu, cnt > 4);
     bool open = true;
 #pragma unroll
     for (int r = 0; r < WIN_TOPK; r++) {
-        uint32_t m = KEY32_NONE;
-        if (open) {                                        // warp-uniform
-            m = __reduce_min_sync(0xffffffffu, k0);
-            if (m == KEY32_NONE) open = false;
-            else {
-                if (k0 == m) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY32_NONE; --left; }      // keys are unique: one lane pops
-                if (risky && __any_sync(0xffffffffu, left == 0 && cnt > 4)) open = false;
-            }
-        }
-        if (lane == r) mine = m;                            // lane r keeps the r-th best
+        uint32_t m = __reduce_min_sync(gmask, k0);         // the two halves reduce side by side, each over its own lanes
+        if (!open) m = KEY32_NONE;
+        if (m == KEY32_NONE) open = false;
+        else if (k0 == m) { k0 = k1; k1 = k2; k2 = k3; k3 = KEY32_NONE; --left; }          // keys are unique: one lane pops
+        if (sub == r) mine = m;                            // lane r of the half keeps the r-th best
+        if (__ballot_sync(FULL, left == 0 && cnt > 4) & gmask) open = false;
+        if (!__any_sync(FULL, open)) break;
     }
     // the resolve pass wants the feature, not its CSR position (the list order already carries the first-wins tie-break)
     if (mine != KEY32_NONE) mine = (mine & 0xffff0000u) | (uint32_t)P.items[mine & 0xffffu];
-    total = __reduce_add_sync(0xffffffffu, cnt);
+    total = __reduce_add_sync(gmask, cnt);
 }
 
 template <int MODE>
@@ -550,33 +559,38 @@ __device__ void window_job_init(const WindowJob& J, const WindowParamsDev& prm) 
     if (threadIdx.x == 0) *J.nmatches = s_nm;
 }
 
-template <int MODE>
-__device__ __forceinline__ void window_eval_job(const WindowJob& J, const WindowParamsDev& prm, int i, int lane) {
-    const WindowQueryDev q = J.q[i];
+template <int MODE, int G>
+__device__ __forceinline__ void window_eval_job(const WindowJob& J, const WindowParamsDev& prm, int i, int nq, int lane) {
+    const bool have = i < nq;
+    WindowQueryDev q = J.q[have ? i : 0];
+    const bool valid = have && (q.flags & WQ_VALID);
+    const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
+    const size_t iq = have ? i : 0;
     uint32_t mine = KEY32_NONE;
     int total = 0;
-    if (q.flags & WQ_VALID) {
-        const uint4* __restrict__ qdesc = reinterpret_cast<const uint4*>(J.q_desc);
-        eval_query_topk<MODE>(J.pack, prm, q, qdesc[2 * (size_t)i], qdesc[2 * (size_t)i + 1], J.holder, lane, mine, total);
-    }
-    if (lane < WIN_TOPK) J.keys[(size_t)WIN_TOPK * i + lane] = mine;
-    if (lane == 0) J.total[i] = total;
+    eval_query_topk<MODE, G>(J.pack, prm, q, qdesc[2 * iq], qdesc[2 * iq + 1], J.holder, lane, valid, mine, total);
+    if (!have) return;
+    const int sub = lane & (G - 1);
+    if (sub < WIN_TOPK) J.keys[(size_t)WIN_TOPK * i + sub] = mine;
+    if (sub == 0) J.total[i] = total;
 }
 
-// grid (query groups of 8, jobs); warp = one query of one job (CCM_WIN_INIT takes the filter-free instantiation).
+// grid (query groups of 256 / G, jobs); G lanes = one query of one job (CCM_WIN_INIT takes the filter-free instantiation).
 #ifndef WIN_EVAL_MIN_CTAS
 #define WIN_EVAL_MIN_CTAS 6
 #endif
+template <int G>
 __global__ void __launch_bounds__(256, WIN_EVAL_MIN_CTAS) k_window_eval(const WindowJob* __restrict__ jobs, WindowParamsDev prm) {
     const WindowJob& J = jobs[blockIdx.y];
     const int nq = J.nq_ptr ? min(*J.nq_ptr, J.nq) : J.nq;
-    const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (i >= nq) return;
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (256 / G) + threadIdx.x / G;
+    if (i - lane / G >= nq) return;                        // the warp's first query is past the end: the whole warp leaves
     switch (prm.mode) {
-        case WIN_MODE_MAPPOINTS: window_eval_job<WIN_MODE_MAPPOINTS>(J, prm, i, lane); break;
-        case WIN_MODE_LASTFRAME: window_eval_job<WIN_MODE_LASTFRAME>(J, prm, i, lane); break;
-        case WIN_MODE_KF_SIM3: window_eval_job<WIN_MODE_KF_SIM3>(J, prm, i, lane); break;
-        default: window_eval_job<WIN_MODE_BEST>(J, prm, i, lane); break;
+        case WIN_MODE_MAPPOINTS: window_eval_job<WIN_MODE_MAPPOINTS, G>(J, prm, i, nq, lane); break;
+        case WIN_MODE_LASTFRAME: window_eval_job<WIN_MODE_LASTFRAME, G>(J, prm, i, nq, lane); break;
+        case WIN_MODE_KF_SIM3: window_eval_job<WIN_MODE_KF_SIM3, G>(J, prm, i, nq, lane); break;
+        default: window_eval_job<WIN_MODE_BEST, G>(J, prm, i, nq, lane); break;
     }
 }
 

@@ -265,7 +265,8 @@ def test_allpairs_sharded_merge_equals_single(gm):
     assert merged["idx"][7] == 100 and merged["d2"][7] == 0
 
 
-def test_extractor_to_matcher_zero_copy_batch(gm):
+@pytest.mark.parametrize("B", [4, 10, 24])      # queries in flight ~3 k / ~9 k / ~23 k: k_window_eval at 32 / 16 / 8 lanes per query
+def test_extractor_to_matcher_zero_copy_batch(gm, B):
     """Extractor output stays in HBM: packs are built from it on the device, frame t is searched with frame t-1's
     keypoints as queries (SearchByProjection(Frame, LastFrame)), all frames of the batch in one launch. Checked against
     the oracle fed with the host copies of the same extractor output."""
@@ -275,7 +276,7 @@ def test_extractor_to_matcher_zero_copy_batch(gm):
     from motioncheck_ccm_slam_b200.matcher import (FramePack, QUERY_DTYPE, RESULT_DTYPE, WIN_PROJ_LASTFRAME, Q_VALID, Q_OBS,
                                                    frame_grid, packs_from_extractor_batch_device, search_window_batch_device)
     from motioncheck_ccm_slam_b200.synth import make_stream
-    B, w, h = 4, 640, 400
+    w, h = 640, 400
     frames = make_stream(4242, B, w, h)
     ex = ORBextractor(800, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=B, device=0)
     cap = ex.max_keypoints()
