@@ -16,17 +16,19 @@ static_assert(sizeof(Best2Dev) == sizeof(ccm_best2) && sizeof(ccm_best2) == 8, "
 
 static thread_local std::string g_match_create_error = "";
 
-enum { MB_JOBS, MB_Q, MB_QDESC, MB_HOLDER, MB_RES, MB_NM, MB_SCRATCH, MB_PARTS, MB_A, MB_B, MB_C, MB_D, MB_E, MB_F, MB_G, MB_H, MB_COUNT };
+enum { MB_JOBS, MB_JOBS2, MB_Q, MB_QDESC, MB_HOLDER, MB_RES, MB_NM, MB_SCRATCH, MB_PARTS, MB_A, MB_B, MB_C, MB_D, MB_E, MB_F, MB_G, MB_H, MB_COUNT };
 
 struct ccm_matcher {
     int device = 0;
     int sms = 0;
     cudaStream_t stream = nullptr;
     long long launches = 0;
-    struct Buf { void* p = nullptr; size_t cap = 0; } buf[MB_COUNT];
+    struct Buf { void* p = nullptr; size_t cap = 0; std::vector<uint8_t> shadow; bool shadow_ok = false; } buf[MB_COUNT];
     // pinned host mirror of a call's device blob: the host entry points gather their input arrays here and send ONE copy up,
     // and bring ONE copy back (a pageable cudaMemcpyAsync per array costs ~10 us each: 13 of them per SearchByBoW call)
     uint8_t* h_stage = nullptr; size_t h_stage_cap = 0;
+    int jobs_turn = 0;                 // which of MB_JOBS / MB_JOBS2 the next new window job table replaces
+    size_t grid_smem_optin = 0;        // dynamic shared memory k_build_grid has been allowed on this device
     std::string err;
 };
 
@@ -60,7 +62,24 @@ template <typename Tp> static int mbuf(ccm_matcher* m, int slot, size_t count, T
         MCK(cudaMalloc(&b.p, want));
         b.cap = want;
     }
+    b.shadow_ok = false;               // whoever takes the buffer this way writes it himself
     *out = (Tp*)b.p;
+    return CCM_OK;
+}
+
+// A job table (pointers into packs and scratch) built on the host and sent to the device. A tracking loop sends the same
+// table call after call, so the last one sent through each slot is remembered and an identical table is not sent again
+// (a pageable cudaMemcpyAsync costs a staging copy on the host and a ~2 us copy operation in front of the kernel).
+template <typename Tp> static int mbuf_upload(ccm_matcher* m, int slot, const Tp* host, size_t count, Tp** out) {
+    ccm_matcher::Buf& b = m->buf[slot];
+    const size_t bytes = count * sizeof(Tp);
+    const bool same = b.shadow_ok && b.p && b.shadow.size() == bytes && memcmp(b.shadow.data(), host, bytes) == 0;
+    if (same) { *out = (Tp*)b.p; return CCM_OK; }
+    int rc;
+    if ((rc = mbuf(m, slot, count, out))) return rc;
+    MCK(cudaMemcpyAsync(*out, host, bytes, cudaMemcpyHostToDevice, m->stream));
+    b.shadow.assign((const uint8_t*)host, (const uint8_t*)host + bytes);
+    b.shadow_ok = true;
     return CCM_OK;
 }
 
@@ -167,6 +186,7 @@ void ccm_frame_pack_destroy(ccm_frame_pack* p) {
 
 static PackDev pack_dev(const ccm_frame_pack* p) {
     PackDev d;
+    memset(&d, 0, sizeof d);           // job tables are compared byte-wise (mbuf_upload): no stray padding
     d.desc = p->desc_view; d.x = p->x; d.y = p->y; d.angle = p->angle; d.octave = p->octave;
     d.cell_start = p->cell_start; d.items = p->items; d.n = p->n; d.cap = p->cap;
     d.min_x = p->g.min_x; d.min_y = p->g.min_y; d.inv_w = p->g.inv_w; d.inv_h = p->g.inv_h; d.cols = p->g.cols; d.rows = p->g.rows;
@@ -186,9 +206,24 @@ static int launch_build_grid(ccm_matcher* m, ccm_frame_pack* const* packs, int n
     for (int j = 0; j < n_packs; j++) jobs[j] = GridJob{pack_dev(packs[j]), packs[j]->cell_start, packs[j]->items};
     GridJob* djobs;
     int rc;
-    if ((rc = mbuf(m, MB_E, (size_t)n_packs, &djobs))) return rc;
-    MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(GridJob) * n_packs, cudaMemcpyHostToDevice, m->stream));
-    k_build_grid<<<n_packs, 1024, 0, m->stream>>>(djobs);
+    if ((rc = mbuf_upload(m, MB_E, jobs.data(), (size_t)n_packs, &djobs))) return rc;
+    // shared-memory working set of the largest pack: ncell ints | cap u32 | cap u16 (k_build_grid); the global-memory form otherwise
+    int max_cap = 0, max_cells = 0;
+    for (int j = 0; j < n_packs; j++) {
+        max_cap = std::max(max_cap, packs[j]->cap);
+        max_cells = std::max(max_cells, packs[j]->g.cols * packs[j]->g.rows);
+    }
+    const int smem_cap = (max_cap + 1) & ~1;
+    const size_t smem = (size_t)max_cells * 4 + (size_t)smem_cap * 6;
+    if (max_cap <= 65536 && smem <= 160 * 1024) {
+        if (smem > 48 * 1024 && smem > m->grid_smem_optin) {
+            MCK(cudaFuncSetAttribute(k_build_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            m->grid_smem_optin = smem;
+        }
+        k_build_grid<<<n_packs, 1024, smem, m->stream>>>(djobs, smem_cap);
+    } else {
+        k_build_grid_global<<<n_packs, 1024, 0, m->stream>>>(djobs);
+    }
     m->launches++;
     MCK(cudaGetLastError());
     return CCM_OK;
@@ -311,8 +346,7 @@ static int pack_from_extractor(ccm_frame_pack* const* packs, int n_packs, const 
         fills[j] = PackFill{p->x, p->y, p->angle, p->octave, p->n, p->cap};
     }
     PackFill* dfills;
-    if ((rc = mbuf(m, MB_D, (size_t)n_packs, &dfills))) return rc;
-    MCK(cudaMemcpyAsync(dfills, fills.data(), sizeof(PackFill) * n_packs, cudaMemcpyHostToDevice, m->stream));
+    if ((rc = mbuf_upload(m, MB_D, fills.data(), (size_t)n_packs, &dfills))) return rc;
     k_pack_from_keypoints<<<n_packs, 256, 0, m->stream>>>(dfills, (const ccm_keypoint_dev*)d_kp, d_xy_un, d_n, kp_stride, c);
     m->launches++;
     MCK(cudaGetLastError());
@@ -462,7 +496,6 @@ int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs,
     const size_t per = job_scratch_ints(max_cap, q_stride);
     int* scratch; WindowJob* djobs;
     if ((rc = mbuf(m, MB_SCRATCH, per * n_jobs, &scratch))) return rc;
-    if ((rc = mbuf(m, MB_JOBS, (size_t)n_jobs, &djobs))) return rc;
     std::vector<WindowJob> jobs(n_jobs);
     for (int j = 0; j < n_jobs; j++) {
         WindowJob& J = jobs[j];
@@ -476,8 +509,18 @@ int ccm_search_window_batch_device(ccm_matcher* m, ccm_frame_pack* const* packs,
         J.nmatches = d_nmatches + j;
         carve_job(J, scratch + per * j, max_cap, q_stride);
     }
-    // pageable -> device copy is staged by the runtime before it returns, so `jobs` may die at scope exit
-    MCK(cudaMemcpyAsync(djobs, jobs.data(), sizeof(WindowJob) * n_jobs, cudaMemcpyHostToDevice, m->stream));
+    // Two tables are remembered (a tracking loop alternates between its LastFrame and its map-point search); a new one
+    // replaces them in turn. pageable -> device copy is staged by the runtime before it returns, so `jobs` may die at scope exit
+    {
+        const size_t bytes = sizeof(WindowJob) * n_jobs;
+        int slot = -1;
+        for (int sl : {MB_JOBS, MB_JOBS2}) {
+            const ccm_matcher::Buf& b = m->buf[sl];
+            if (b.shadow_ok && b.p && b.shadow.size() == bytes && memcmp(b.shadow.data(), jobs.data(), bytes) == 0) slot = sl;
+        }
+        if (slot < 0) { slot = m->jobs_turn ? MB_JOBS2 : MB_JOBS; m->jobs_turn ^= 1; }
+        if ((rc = mbuf_upload(m, slot, jobs.data(), (size_t)n_jobs, &djobs))) return rc;
+    }
     {   // lanes per query by the number of queries in flight: a batch is bound by resident warps (8 lanes each), one frame by
         // the latency of its own walk (a whole warp each); measured 0.519 / 0.533 / 0.560 ms per tracking step at 8 / 16 / 32
         const long long in_flight = (long long)q_stride * n_jobs;

@@ -68,27 +68,20 @@ __global__ void __launch_bounds__(256) k_undistort_keypoints(const CameraDev cam
 }
 
 // Frame::AssignFeaturesToGrid + PosInGrid (Frame.cpp:103-118, 255-265; note round(), not floor()): one CTA per pack.
-// Counting pass, block scan, scatter, then an insertion sort inside each cell restores ascending feature index
-// (what push_back in index order produces).
+// Everything between reading x / y and writing the CSR happens in shared memory: a counting pass that also hands every
+// feature its (cell, arrival rank), a block scan, a scatter without atomics, an insertion sort inside each cell that
+// restores ascending feature index (what push_back in index order produces), and one coalesced store of items[].
+// Dynamic shared memory: ncell ints | cap u32 (cell << 16 | rank) | cap u16 (items); packs too large for that
+// (cap > 65536 or more than the launch reserved) take k_build_grid_global below.
 struct GridJob { PackDev pack; int* cell_start; int* items; };
-__global__ void __launch_bounds__(1024) k_build_grid(const GridJob* __restrict__ jobs) {
-    const PackDev P = jobs[blockIdx.x].pack;
-    int* cell_start = jobs[blockIdx.x].cell_start;
-    int* items = jobs[blockIdx.x].items;
-    __shared__ int cnt[CCM_MAX_GRID_CELLS];
-    __shared__ int wsum[32];
-    const int ncell = P.cols * P.rows;
-    const int n = min(*P.n, P.cap);
-    for (int c = threadIdx.x; c < ncell; c += blockDim.x) cnt[c] = 0;
-    __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const int px = (int)roundf(__fmul_rn(__fsub_rn(P.x[i], P.min_x), P.inv_w));
-        const int py = (int)roundf(__fmul_rn(__fsub_rn(P.y[i], P.min_y), P.inv_h));
-        if (px < 0 || px >= P.cols || py < 0 || py >= P.rows) continue;
-        atomicAdd(&cnt[px * P.rows + py], 1);
-    }
-    __syncthreads();
-    // exclusive scan of cnt[0..ncell): each thread owns a contiguous run of cells
+__device__ __forceinline__ int grid_cell_of(const PackDev& P, int i) {
+    const int px = (int)roundf(__fmul_rn(__fsub_rn(P.x[i], P.min_x), P.inv_w));
+    const int py = (int)roundf(__fmul_rn(__fsub_rn(P.y[i], P.min_y), P.inv_h));
+    if (px < 0 || px >= P.cols || py < 0 || py >= P.rows) return -1;
+    return px * P.rows + py;
+}
+// exclusive block scan of cnt[0..ncell) in place (each thread owns a contiguous run of cells); returns the total to all threads
+__device__ __forceinline__ int grid_scan(int* cnt, int ncell, int* cell_start, int* wsum) {
     const int per = (ncell + blockDim.x - 1) / blockDim.x;
     const int c0 = min(threadIdx.x * per, ncell), c1 = min(c0 + per, ncell);
     int s = 0;
@@ -104,17 +97,75 @@ __global__ void __launch_bounds__(1024) k_build_grid(const GridJob* __restrict__
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += u; }
         wsum[lane] = w - v;
+        if (lane == 31) wsum[32] = w;
     }
     __syncthreads();
     int run = wsum[wid] + incl - s;
     for (int c = c0; c < c1; c++) { const int k = cnt[c]; cell_start[c] = run; cnt[c] = run; run += k; }
-    if (threadIdx.x == blockDim.x - 1) cell_start[ncell] = run;
+    const int total = wsum[32];
+    if (threadIdx.x == 0) cell_start[ncell] = total;
+    return total;
+}
+
+__global__ void __launch_bounds__(1024) k_build_grid(const GridJob* __restrict__ jobs, int smem_cap) {
+    const PackDev P = jobs[blockIdx.x].pack;
+    int* cell_start = jobs[blockIdx.x].cell_start;
+    int* items = jobs[blockIdx.x].items;
+    extern __shared__ int g_sm[];
+    __shared__ int wsum[33];
+    const int ncell = P.cols * P.rows;
+    const int n = min(*P.n, P.cap);
+    int* cnt = g_sm;
+    uint32_t* cr = reinterpret_cast<uint32_t*>(cnt + ncell);
+    uint16_t* its = reinterpret_cast<uint16_t*>(cr + smem_cap);
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) cnt[c] = 0;
     __syncthreads();
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
-        const int px = (int)roundf(__fmul_rn(__fsub_rn(P.x[i], P.min_x), P.inv_w));
-        const int py = (int)roundf(__fmul_rn(__fsub_rn(P.y[i], P.min_y), P.inv_h));
-        if (px < 0 || px >= P.cols || py < 0 || py >= P.rows) continue;
-        items[atomicAdd(&cnt[px * P.rows + py], 1)] = i;
+        const int cell = grid_cell_of(P, i);
+        cr[i] = cell < 0 ? 0xffffffffu : ((uint32_t)cell << 16) | (uint32_t)atomicAdd(&cnt[cell], 1);
+    }
+    __syncthreads();
+    const int total = grid_scan(cnt, ncell, cell_start, wsum);
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const uint32_t v = cr[i];
+        if (v != 0xffffffffu) its[cnt[v >> 16] + (v & 0xffffu)] = (uint16_t)i;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+        const int a = cnt[c], b = c + 1 < ncell ? cnt[c + 1] : total;
+        for (int i = a + 1; i < b; i++) {
+            const uint16_t v = its[i];
+            int j = i - 1;
+            while (j >= a && its[j] > v) { its[j + 1] = its[j]; j--; }
+            its[j + 1] = v;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += blockDim.x) items[i] = its[i];
+}
+
+// the same with items[] sorted in global memory: packs whose working set does not fit in shared memory
+__global__ void __launch_bounds__(1024) k_build_grid_global(const GridJob* __restrict__ jobs) {
+    const PackDev P = jobs[blockIdx.x].pack;
+    int* cell_start = jobs[blockIdx.x].cell_start;
+    int* items = jobs[blockIdx.x].items;
+    __shared__ int cnt[CCM_MAX_GRID_CELLS];
+    __shared__ int wsum[33];
+    const int ncell = P.cols * P.rows;
+    const int n = min(*P.n, P.cap);
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int cell = grid_cell_of(P, i);
+        if (cell >= 0) atomicAdd(&cnt[cell], 1);
+    }
+    __syncthreads();
+    grid_scan(cnt, ncell, cell_start, wsum);
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int cell = grid_cell_of(P, i);
+        if (cell >= 0) items[atomicAdd(&cnt[cell], 1)] = i;
     }
     __syncthreads();
     for (int c = threadIdx.x; c < ncell; c += blockDim.x) {

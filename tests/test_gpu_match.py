@@ -53,8 +53,9 @@ def test_descriptor_distance(gm):
     assert d[5] == 256 and d[0] == 0
 
 
-@pytest.mark.parametrize("seed,n", [(11, 1000), (12, 2000), (13, 1), (14, 0), (15, 5000)])
-def test_grid_matches_frame_assign(gm, seed, n):
+@pytest.mark.parametrize("seed,n,cap", [(11, 1000, None), (12, 2000, None), (13, 1, None), (14, 0, None), (15, 5000, None),
+                                        (16, 3000, 70000)])      # cap > 65536: the grid is built in global memory
+def test_grid_matches_frame_assign(gm, seed, n, cap):
     from motioncheck_ccm_slam_b200.matcher import frame_grid
     from motioncheck_ccm_slam_b200.synth import make_feature_frame
     fr = make_feature_frame(seed, max(n, 1), W, H)
@@ -64,7 +65,7 @@ def test_grid_matches_frame_assign(gm, seed, n):
         fr["y"][:4] = [10.0, 10.0, H + 9.0, -0.49]
         fr["x"][4:8] = [5.0133333, 10.026666, 15.04, 20.053333]
     grid = frame_grid(W, H, min_x=-3.5, min_y=-2.25) if seed % 2 else frame_grid(W, H)
-    p, of = _pack(gm, fr, grid, cap=max(n, 1) + 7)
+    p, of = _pack(gm, fr, grid, cap=cap or max(n, 1) + 7)
     cs, items = p.get_grid()
     ocs, oitems = of.csr()
     assert np.array_equal(cs, ocs) and np.array_equal(items, oitems)
