@@ -278,7 +278,7 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
     int cap = 32; while (cap < max_node_cap) cap <<= 1;
     h->qt_cap = cap;
     h->qt_ccap = 4096;                                   // corners per (frame, level) cached in shared memory: 24 KB
-    h->qt_smem = (size_t)cap * 60 + 32 * sizeof(int) + (size_t)h->qt_ccap * 6;
+    h->qt_smem = (size_t)cap * 80 + 32 * sizeof(int) + (size_t)h->qt_ccap * 6;
     CK(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->qt_smem));
 
     for (int l = 0; l < L; l++) {

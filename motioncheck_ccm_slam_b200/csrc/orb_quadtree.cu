@@ -60,11 +60,47 @@ __device__ __forceinline__ int quadrant(const QNode& p, int x, int y) {
 
 }  // namespace
 
+__device__ __forceinline__ int n_children(const int* cc, int i) {
+    return (cc[4 * i] > 0) + (cc[4 * i + 1] > 0) + (cc[4 * i + 2] > 0) + (cc[4 * i + 3] > 0);
+}
+// One node of the old list goes into the new list B: a node that is split leaves its non-empty children (creation index
+// `created`.., push_front order: later-created sits closer to the front, so child c lands on C - 1 - c), any other node
+// keeps its place behind the C new children, moved up by the `before` split nodes in front of it.
+__device__ __forceinline__ void place_node(const QNode* A, QNode* B, const int* cc, int* newpos, short* childpos, int* s_expand,
+                                           int i, bool split, int created, int before, int C) {
+    const QNode nd = A[i];
+    if (split) {
+        int expand = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const int cnt = cc[4 * i + q];
+            if (cnt > 0) {
+                const int pos = C - 1 - created;
+                QNode c; child_bounds(nd, q, c); c.cnt = cnt;
+                B[pos] = c;
+                childpos[4 * i + q] = (short)pos;
+                created++;
+                expand += cnt > 1;
+            }
+        }
+        newpos[i] = -1;
+        if (expand) atomicAdd(s_expand, expand);
+    } else {
+        const int pos = C + i - before;
+        B[pos] = nd;
+        newpos[i] = pos;
+    }
+}
+
 // dynamic smem layout (cap = node capacity rounded up to a power of two, >= 32):
-//   QNode A[cap], B[cap]; int cc[4*cap]; int key[cap]; int aux[cap]; int newpos[cap]; short childpos[4*cap];
-//   int scratch[32]; uint32_t corner_cache[ccap]; uint16_t node_cache[ccap]
+//   QNode A[cap], B[cap]; int cc0[4*cap], cc1[4*cap]; int key[cap]; int aux[cap]; int aux2[cap]; int newpos[cap];
+//   short childpos[4*cap]; int scratch[32]; uint32_t corner_cache[ccap]; uint16_t node_cache[ccap]     (80 B per node)
 // A (frame, level) with at most ccap corners keeps its corner list and the corner -> node map in shared memory for the
-// whole run (every round walks both twice); larger ones work on the global arrays.
+// whole run (every round walks both once); larger ones work on the global arrays.
+// A round is few barriers on purpose (one frame's latency is this kernel's barrier count): the node lists A / B and the
+// child-occupancy tables ping-pong; the pass that moves every corner to its new node also counts the occupancy of that
+// node's children for the next round; in a sweep round the creation index of a node's children and the number of split
+// nodes in front of it come out of ONE scan of a packed value. Sweep round: 4 barriers, greedy round: 10 (was 14 / 20).
 __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap,
                                                   const uint32_t* corners, const int* corner_count,   // written by the PDL predecessor: no __restrict__, so these are coherent loads the compiler cannot hoist above pdl_wait()
                                                   uint16_t* __restrict__ node_of,          // [frames][corners_per_frame]
@@ -79,10 +115,12 @@ __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constan
 
     QNode* A = reinterpret_cast<QNode*>(smem_raw);
     QNode* B = A + cap;
-    int* cc = reinterpret_cast<int*>(B + cap);
-    int* key = cc + 4 * cap;
+    int* cc = reinterpret_cast<int*>(B + cap);          // child occupancy of the current list
+    int* cc_next = cc + 4 * cap;                        // ... of the list being built
+    int* key = cc_next + 4 * cap;
     int* aux = key + cap;
-    int* newpos = aux + cap;
+    int* aux2 = aux + cap;
+    int* newpos = aux2 + cap;
     short* childpos = reinterpret_cast<short*>(newpos + cap);
     int* scratch = reinterpret_cast<int*>(childpos + 4 * cap);
     __shared__ int s_n, s_expand, s_P, s_C;
@@ -100,13 +138,14 @@ __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constan
     const int H = L.h - 2 * CCM_MIN_BORDER;   // maxY-minY
 
     // ---- initial nodes (:711-741) ----
-    for (int i = tid; i < cap; i += NT) { A[i].cnt = 0; }
-    __syncthreads();
     if (tid < L.nIni) {
-        A[tid].ulx = (short)(int)(L.hX * (float)tid);
-        A[tid].brx = (short)(int)(L.hX * (float)(tid + 1));
-        A[tid].uly = 0; A[tid].bry = (short)H;
+        QNode nd;
+        nd.ulx = (short)(int)(L.hX * (float)tid);
+        nd.brx = (short)(int)(L.hX * (float)(tid + 1));
+        nd.uly = 0; nd.bry = (short)H; nd.cnt = 0;
+        A[tid] = nd;
     }
+    for (int i = tid; i < 4 * L.nIni; i += NT) cc_next[i] = 0;
     __syncthreads();
     for (int k = tid; k < nC; k += NT) {
         const uint32_t c = ck[k];
@@ -124,40 +163,43 @@ __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constan
     }
     __syncthreads();
     int n = s_n;
-    for (int k = tid; k < nC; k += NT) nof[k] = (uint16_t)newpos[nof[k]];
-    for (int i = tid; i < n; i += NT) A[i] = B[i];
+    for (int k = tid; k < nC; k += NT) {
+        const int np = newpos[nof[k]];
+        nof[k] = (uint16_t)np;
+        const QNode nn = B[np];
+        if (nn.cnt > 1) {
+            const uint32_t c = ck[k];
+            atomicAdd(&cc_next[4 * np + quadrant(nn, (int)(c & 4095u) - CCM_MIN_BORDER, (int)((c >> 12) & 4095u) - CCM_MIN_BORDER)], 1);
+        }
+    }
     __syncthreads();
+    { QNode* t = A; A = B; B = t; int* u = cc; cc = cc_next; cc_next = u; }
 
     bool greedy = false;
 #pragma unroll 1
     while (true) {
-        // child occupancy of every node holding more than one corner
-        for (int i = tid; i < 4 * n; i += NT) cc[i] = 0;
-        __syncthreads();
-        for (int k = tid; k < nC; k += NT) {
-            const int nd = nof[k];
-            if (A[nd].cnt > 1) {
-                const uint32_t c = ck[k];
-                const int q = quadrant(A[nd], (int)(c & 4095u) - CCM_MIN_BORDER, (int)((c >> 12) & 4095u) - CCM_MIN_BORDER);
-                atomicAdd(&cc[4 * nd + q], 1);
-            }
-        }
-        __syncthreads();
-
-        // ---- choose the nodes split this round and their split order: key[r] = list position of the r-th split ----
-        int P;   // number of nodes split
+        int P, C;
         if (!greedy) {
-            for (int i = tid; i < n; i += NT) aux[i] = A[i].cnt > 1 ? 1 : 0;
+            // sweep (:767-830): every node holding more than one corner is split, in list order. One scan of
+            // (children | 1 << 16) per split node gives a node both the creation index of its first child and the number
+            // of split nodes in front of it.
+            if (tid == 0) s_expand = 0;
+            for (int i = tid; i < n; i += NT) aux[i] = A[i].cnt > 1 ? (n_children(cc, i) | 0x10000) : 0;
             __syncthreads();
-            P = block_exclusive_scan(aux, n, scratch);
-            for (int i = tid; i < n; i += NT) if (A[i].cnt > 1) key[aux[i]] = i;
-            __syncthreads();
+            const int tot = block_exclusive_scan(aux, n, scratch);
+            C = tot & 0xffff; P = tot >> 16;
+            for (int i = tid; i < 4 * (C + n - P); i += NT) cc_next[i] = 0;
+            for (int i = tid; i < n; i += NT)
+                place_node(A, B, cc, newpos, childpos, &s_expand, i, A[i].cnt > 1, aux[i] & 0xffff, aux[i] >> 16, C);
         } else {
-            // sort descending by (count, earlier list position first). Keys are distinct (the position is part of the
-            // key), so a candidate's place is the number of larger keys: one pass of broadcast reads, no barrier ladder
-            for (int i = tid; i < cap; i += NT) {
-                key[i] = (i < n && A[i].cnt > 1) ? ((min(A[i].cnt, 0x7FFFF) << 12) | (4095 - i)) : 0;
-                newpos[i] = 0;
+            // greedy (:841-905): candidates sorted descending by (count, earlier list position first). Keys are distinct
+            // (the position is part of the key), so a candidate's place is the number of larger keys: one pass of broadcast
+            // reads, no barrier ladder
+            if (tid == 0) { s_expand = 0; s_P = 0; s_C = 0; }
+            for (int i = tid; i < n; i += NT) {
+                key[i] = A[i].cnt > 1 ? ((min(A[i].cnt, 0x7FFFF) << 12) | (4095 - i)) : 0;
+                newpos[i] = 0;                                // sorted keys
+                aux2[i] = 0;                                  // 1 = split this round
             }
             __syncthreads();
             for (int i = tid; i < n; i += NT) {
@@ -169,84 +211,52 @@ __global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constan
                 }
             }
             __syncthreads();
-            for (int i = tid; i < cap; i += NT) key[i] = newpos[i];
-            __syncthreads();
             // aux[r] = growth of the list when the r-th candidate is split (children - 1); prefix -> cut (:895-896)
-            for (int r = tid; r < cap; r += NT) {
-                int g = 0;
-                if (key[r] != 0) {
-                    const int i = 4095 - (key[r] & 4095);
-                    g = (cc[4 * i] > 0) + (cc[4 * i + 1] > 0) + (cc[4 * i + 2] > 0) + (cc[4 * i + 3] > 0) - 1;
-                }
-                aux[r] = g;
+            for (int r = tid; r < n; r += NT) {
+                const int k = newpos[r];
+                aux[r] = k ? n_children(cc, 4095 - (k & 4095)) - 1 : 0;
+                key[r] = -1;                                  // from here: creation index of a split node's first child
             }
             __syncthreads();
-            block_exclusive_scan(aux, cap, scratch);      // aux[r] = growth before splitting candidate r
-            if (tid == 0) s_P = 0;
-            __syncthreads();
-            for (int r = tid; r < cap; r += NT)
-                if (key[r] != 0 && n + aux[r] < N) atomicAdd(&s_P, 1);   // candidates form a prefix: growth is monotone
-            __syncthreads();
-            P = s_P;
-            for (int r = tid; r < P; r += NT) key[r] = 4095 - (key[r] & 4095);
-            __syncthreads();
-        }
-
-        // ---- creation index of every child, in split order (n1..n4 within a node) ----
-        for (int r = tid; r < P; r += NT) {
-            const int i = key[r];
-            aux[r] = (cc[4 * i] > 0) + (cc[4 * i + 1] > 0) + (cc[4 * i + 2] > 0) + (cc[4 * i + 3] > 0);
-        }
-        __syncthreads();
-        const int C = block_exclusive_scan(aux, P, scratch);
-        if (tid == 0) s_expand = 0;
-        for (int i = tid; i < n; i += NT) newpos[i] = 0;      // 1 marks "split this round"
-        __syncthreads();
-        for (int r = tid; r < P; r += NT) {
-            const int i = key[r];
-            newpos[i] = 1;
-            int created = aux[r], expand = 0;
-            for (int q = 0; q < 4; q++) {
-                const int cnt = cc[4 * i + q];
-                if (cnt > 0) {
-                    const int pos = C - 1 - created;            // push_front: later-created sits closer to the front
-                    QNode c; child_bounds(A[i], q, c); c.cnt = cnt;
-                    B[pos] = c;
-                    childpos[4 * i + q] = (short)pos;
-                    created++;
-                    expand += cnt > 1;
+            block_exclusive_scan(aux, n, scratch);            // aux[r] = growth before splitting candidate r
+            for (int r = tid; r < n; r += NT) {
+                const int k = newpos[r];
+                if (k != 0 && n + aux[r] < N) {               // candidates split form a prefix: growth is monotone
+                    const int i = 4095 - (k & 4095);
+                    key[i] = aux[r] + r;                      // children created before it = growth before it + one per candidate
+                    aux2[i] = 1;
+                    atomicAdd(&s_P, 1);
+                    atomicAdd(&s_C, n_children(cc, i));
                 }
             }
-            if (expand) atomicAdd(&s_expand, expand);
+            __syncthreads();
+            P = s_P; C = s_C;
+            block_exclusive_scan(aux2, n, scratch);           // aux2[i] = number of split nodes before list position i
+            for (int i = tid; i < 4 * (C + n - P); i += NT) cc_next[i] = 0;
+            for (int i = tid; i < n; i += NT)
+                place_node(A, B, cc, newpos, childpos, &s_expand, i, key[i] >= 0, key[i], aux2[i], C);
         }
         __syncthreads();
-        // survivors keep their relative order behind the new children
-        for (int i = tid; i < n; i += NT) aux[i] = newpos[i];
-        __syncthreads();
-        block_exclusive_scan(aux, n, scratch);                  // aux[i] = number of split nodes before position i
-        for (int i = tid; i < n; i += NT) {
-            if (!newpos[i]) { const int pos = C + i - aux[i]; B[pos] = A[i]; newpos[i] = pos; }
-            else newpos[i] = -1;
-        }
-        __syncthreads();
+        const int n_new = C + n - P;
+        const int nToExpand = s_expand;
+        const bool last = n_new >= N || n_new == n;              // :833-836 / :901-902
+        // every corner moves to its new node and, unless this was the last round, is counted in that node's child occupancy
         for (int k = tid; k < nC; k += NT) {
             const int nd = nof[k];
             int np = newpos[nd];
-            if (np < 0) {
-                const uint32_t c = ck[k];
-                const int q = quadrant(A[nd], (int)(c & 4095u) - CCM_MIN_BORDER, (int)((c >> 12) & 4095u) - CCM_MIN_BORDER);
-                np = childpos[4 * nd + q];
-            }
+            const uint32_t c = ck[k];
+            const int x = (int)(c & 4095u) - CCM_MIN_BORDER, y = (int)((c >> 12) & 4095u) - CCM_MIN_BORDER;
+            if (np < 0) np = childpos[4 * nd + quadrant(A[nd], x, y)];
             nof[k] = (uint16_t)np;
+            if (!last) {
+                const QNode nn = B[np];
+                if (nn.cnt > 1) atomicAdd(&cc_next[4 * np + quadrant(nn, x, y)], 1);
+            }
         }
-        const int n_new = C + n - P;
-        const int nToExpand = s_expand;
         __syncthreads();
-        for (int i = tid; i < n_new; i += NT) A[i] = B[i];
-        __syncthreads();
-        const int prev = n;
+        { QNode* t = A; A = B; B = t; int* u = cc; cc = cc_next; cc_next = u; }
         n = n_new;
-        if (n >= N || n == prev) break;                          // :833-836 / :901-902
+        if (last) break;
         if (!greedy && n + nToExpand * 3 > N) greedy = true;     // :838
     }
 
