@@ -37,6 +37,9 @@ struct ccm_orb {
     void* encode_tiled = nullptr;                      // cuTensorMapEncodeTiled, fetched through the runtime
     // k_fast_chunks: two warps per chunk of whole cells (orb_fast_chunks.cu)
     uint4* d_chunks = nullptr; int n_chunks = 0;
+    int chunk_off[CCM_MAX_LEVELS + 1] = {};   // chunks are in level order: level l owns [chunk_off[l], chunk_off[l + 1])
+    // single-frame graph: one branch per level (FAST + quadtree of level l start when level l exists) and one for the blur
+    cudaStream_t lvl_s[CCM_MAX_LEVELS + 1] = {}; cudaEvent_t lvl_ready[CCM_MAX_LEVELS + 1] = {}, lvl_done[CCM_MAX_LEVELS + 1] = {};
     FastChunkSmem fc_smem = {};
     bool fc_tma = false;                               // tensor maps of the arena levels are encoded (box FC_TW x tile_rows)
     FastTma fc_tmaps = {};
@@ -339,6 +342,9 @@ static int configure_shape(ccm_orb* h, int rows, int cols) {
         int fc_max_ch = 1;
         fast_chunk_table(T, chunks, &fc_max_ch);
         h->n_chunks = (int)(chunks.size() / 2);
+        for (int l = 0; l <= CCM_MAX_LEVELS; l++) h->chunk_off[l] = 0;
+        for (size_t c = 0; c < chunks.size(); c += 2) h->chunk_off[(chunks[c].z & 0xffu) + 1]++;
+        for (int l = 0; l < CCM_MAX_LEVELS; l++) h->chunk_off[l + 1] += h->chunk_off[l];
         h->fc_smem = fast_chunk_smem(fc_max_ch);
         if ((rc = dev_alloc(h, &h->d_chunks, chunks.size()))) return rc;
         CK(cudaMemcpy(h->d_chunks, chunks.data(), chunks.size() * sizeof(uint4), cudaMemcpyHostToDevice));
@@ -441,7 +447,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[3], s));
     }
     {
-        CKL("k_quadtree", launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(512), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, (const uint32_t*)A.corners,
+        CKL("k_quadtree", launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(512), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, 0, (const uint32_t*)A.corners,
                                      (const int*)A.corner_count, A.node_of, A.level_kps, A.level_kp_count));
         h->launches++;
         if (fork) {
@@ -526,6 +532,11 @@ void ccm_orb_destroy(ccm_orb* h) {
     for (cudaStream_t st : {h->s_in, h->stream, h->lane[1].s, h->lane[0].aux, h->lane[1].aux, h->s_out}) if (st) cudaStreamSynchronize(st);
     free_arena(h);
     if (h->graph1) cudaGraphExecDestroy(h->graph1);
+    for (int l = 0; l <= CCM_MAX_LEVELS; l++) {
+        if (h->lvl_s[l]) cudaStreamDestroy(h->lvl_s[l]);
+        if (h->lvl_ready[l]) cudaEventDestroy(h->lvl_ready[l]);
+        if (h->lvl_done[l]) cudaEventDestroy(h->lvl_done[l]);
+    }
     for (int i = 0; i <= CCM_N_STAGES; i++) if (h->ev[i]) cudaEventDestroy(h->ev[i]);
     for (int t = 0; t < CCM_MAX_TICKETS; t++) {
         for (int i = 0; i < CCM_MAX_CHUNKS; i++) {
@@ -822,6 +833,70 @@ int ccm_orb_extract_batch(ccm_orb* h, const uint8_t* const* imgs, int n, int row
     return ccm_orb_extract_batch_wait(h, ticket);
 }
 
+// One frame, enqueued for capture into the single-frame graph: the frame fills ~7 % of the machine, so its latency is the
+// length of the dependency chain, not the work. FAST and the quadtree of level l need nothing but level l: each level gets
+// its own branch that starts when its resize has finished (level 0 at once), the blur is one more branch behind the last
+// resize, and k_orient_describe joins them all and writes keypoints, descriptors and the count straight into the handle's
+// pinned host mirrors (mapped into the device's address space: no device-to-host copy node at all).
+static int run_pipeline_single_levels(ccm_orb* h, const uint8_t* l0, size_t l0_pitch) {
+    const size_t l0_stride = l0_pitch * (size_t)h->rows;
+    tl_pdl = true;
+    h->T.l[0].img = const_cast<uint8_t*>(l0);
+    h->T.l[0].img_pitch = (int)l0_pitch;
+    h->T.l[0].img_stride = l0_stride;
+    h->last_l0 = l0; h->last_l0_pitch = l0_pitch; h->last_l0_stride = l0_stride; h->last_frames = 1;
+    const LevelTable& T = h->T;
+    const int L = T.nlevels;
+    cudaStream_t s = h->stream;
+    for (int l = 0; l <= L; l++) {
+        if (!h->lvl_s[l]) CK(cudaStreamCreateWithFlags(&h->lvl_s[l], cudaStreamNonBlocking));
+        if (!h->lvl_ready[l]) CK(cudaEventCreateWithFlags(&h->lvl_ready[l], cudaEventDisableTiming));
+        if (!h->lvl_done[l]) CK(cudaEventCreateWithFlags(&h->lvl_done[l], cudaEventDisableTiming));
+    }
+    FastTma tm = h->fc_tmaps;
+    const bool tma = h->fc_tma && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, 1, FC_TW, h->fc_smem.tile_rows);
+    CK(cudaMemsetAsync(h->d_corner_count, 0, sizeof(int) * CCM_MAX_LEVELS, s));
+    for (int l = 0; l < L; l++) {
+        if (l > 0) {
+            dim3 g((T.l[l].w + 127) / 128, (T.l[l].h + 7) / 8, 1);
+            if (T.l[l].resize_mlp) CKL("k_resize_level_mlp", launch_pdl(k_resize_level_mlp, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), 1), dim3(32, 8), 0, s, T, l));
+            else if (T.l[l].xgrp) CKL("k_resize_level", launch_pdl(k_resize_level, dim3(g.x, (T.l[l].h + 8 * RESIZE_ROWS - 1) / (8 * RESIZE_ROWS), 1), dim3(32, 8), 0, s, T, l));
+            else { k_resize_level_generic<<<g, dim3(32, 8), 0, s>>>(T, l); CKL("k_resize_level_generic", cudaSuccess); }
+            h->launches++;
+        }
+        CK(cudaEventRecord(h->lvl_ready[l], s));
+        cudaStream_t x = h->lvl_s[l];
+        CK(cudaStreamWaitEvent(x, h->lvl_ready[l], 0));
+        const int c0 = h->chunk_off[l], nc = h->chunk_off[l + 1] - c0;
+        if (nc > 0) {
+            const uint4* items = h->d_chunks + 2 * (size_t)c0;
+            if (tma) k_fast_chunks<true><<<dim3(nc, 1), dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, x>>>(T, items, h->d_corners, h->d_corner_count, h->fc_smem, 0, tm);
+            else k_fast_chunks<false><<<dim3(nc, 1), dim3(32 * FC_WARPS), (size_t)h->fc_smem.total, x>>>(T, items, h->d_corners, h->d_corner_count, h->fc_smem, 0, tm);
+            CKL("k_fast_chunks (one level)", cudaSuccess);
+            h->launches++;
+        }
+        k_quadtree<<<dim3(1, 1), dim3(512), h->qt_smem, x>>>(T, h->qt_cap, h->qt_ccap, l, (const uint32_t*)h->d_corners, (const int*)h->d_corner_count,
+                                                                 h->d_node_of, h->d_level_kps, h->d_level_kp_count);
+        CKL("k_quadtree (one level)", cudaSuccess);
+        h->launches++;
+        CK(cudaEventRecord(h->lvl_done[l], x));
+    }
+    {
+        cudaStream_t x = h->lvl_s[L];
+        CK(cudaStreamWaitEvent(x, h->lvl_ready[L - 1], 0));
+        if (h->blur_ocv24) k_blur_levels<true><<<dim3(T.total_blur_tiles, 1), 256, 0, x>>>(T); else k_blur_levels<false><<<dim3(T.total_blur_tiles, 1), 256, 0, x>>>(T);
+        CKL("k_blur_levels", cudaSuccess);
+        h->launches++;
+        CK(cudaEventRecord(h->lvl_done[L], x));
+    }
+    for (int l = 0; l <= L; l++) CK(cudaStreamWaitEvent(s, h->lvl_done[l], 0));
+    k_orient_describe<<<dim3(T.total_desc_blocks, 1), 256, 0, s>>>(T, h->d_pat, h->d_desc_block_level, h->d_level_kps, h->d_level_kp_count,
+                                                                     (ccm_keypoint_dev*)h->h_kp, h->h_desc, h->h_n, h->max_kps);
+    CKL("k_orient_describe", cudaSuccess);
+    h->launches++;
+    return CCM_OK;
+}
+
 // One frame, synchronously, as Frame::ExtractORB calls the extractor (cslam/src/Frame.cpp:120-123): copy-in, ONE graph launch
 // (memset, 7 resize levels, FAST, quadtree next to the blur, orientation + descriptors, copy-out of slot 0 into the pinned
 // staging), wait, hand the results over. The graph is captured from run_pipeline itself on first use, so it is the same
@@ -849,11 +924,16 @@ static int extract_single_graph(ccm_orb* h, const uint8_t* img, int rows, int co
         cudaGraph_t g = nullptr;
         cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
         if (e == cudaSuccess) {
-            rc = run_pipeline(h, 1, l0, pitch, pitch * (size_t)rows, h->d_kp, h->d_desc, h->d_n, cap, 0, false, 0, true);
-            if (rc == CCM_OK) {
-                cudaMemcpyAsync(h->h_n, h->d_n, sizeof(int), cudaMemcpyDeviceToHost, s);
-                cudaMemcpyAsync(h->h_kp, h->d_kp, sizeof(ccm_keypoint) * (size_t)cap, cudaMemcpyDeviceToHost, s);
-                cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * cap, cudaMemcpyDeviceToHost, s);
+            static const bool flat_graph = std::getenv("CCM_ORB_GRAPH_FLAT") != nullptr;     // A/B knob: the batch pipeline's launch order + three copies
+            if (flat_graph) {
+                rc = run_pipeline(h, 1, l0, pitch, pitch * (size_t)rows, h->d_kp, h->d_desc, h->d_n, cap, 0, false, 0, true);
+                if (rc == CCM_OK) {
+                    cudaMemcpyAsync(h->h_n, h->d_n, sizeof(int), cudaMemcpyDeviceToHost, s);
+                    cudaMemcpyAsync(h->h_kp, h->d_kp, sizeof(ccm_keypoint) * (size_t)cap, cudaMemcpyDeviceToHost, s);
+                    cudaMemcpyAsync(h->h_desc, h->d_desc, (size_t)32 * cap, cudaMemcpyDeviceToHost, s);
+                }
+            } else {
+                rc = run_pipeline_single_levels(h, l0, pitch);
             }
             e = cudaStreamEndCapture(s, &g);
             if (e == cudaSuccess && rc == CCM_OK) e = cudaGraphInstantiate(&h->graph1, g, 0);

@@ -101,13 +101,13 @@ __device__ __forceinline__ void place_node(const QNode* A, QNode* B, const int* 
 // child-occupancy tables ping-pong; the pass that moves every corner to its new node also counts the occupancy of that
 // node's children for the next round; in a sweep round the creation index of a node's children and the number of split
 // nodes in front of it come out of ONE scan of a packed value. Sweep round: 4 barriers, greedy round: 10 (was 14 / 20).
-__global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap,
+__global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap, int lvl0,   // CTA x handles level lvl0 + x
                                                   const uint32_t* corners, const int* corner_count,   // written by the PDL predecessor: no __restrict__, so these are coherent loads the compiler cannot hoist above pdl_wait()
                                                   uint16_t* __restrict__ node_of,          // [frames][corners_per_frame]
                                                   uint32_t* __restrict__ level_kps,        // [frames][kps_per_frame] packed x|y<<12|score<<24
                                                   int* __restrict__ level_kp_count) {      // [frames][CCM_MAX_LEVELS]
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int lvl = blockIdx.x, f = blockIdx.y;
+    const int lvl = lvl0 + blockIdx.x, f = blockIdx.y;
     const LevelDesc& L = T.l[lvl];
     const int tid = threadIdx.x, NT = blockDim.x;
     pdl_launch();
