@@ -5,17 +5,22 @@
 // K6: cv::GaussianBlur(level.clone(), 7x7, sigma 2, BORDER_REFLECT_101), cslam/src/ORBextractor.cpp:1258-1259.
 // OpenCV 4.x CV_8U fixed-point path: 8.8 kernel {18,34,48,56,48,34,18}/256, exact integer row and column
 // accumulation, single rounding (sum + 2^15) >> 16.
-// All levels of all frames in ONE launch. A warp owns a 128-px x 16-row strip: each lane loads one aligned 32-bit
+// All levels of all frames in ONE launch. A warp owns a 120-px x BLUR_RPW-row strip (128-px windows overlapping by one word): each lane loads one aligned 32-bit
 // word per source row (a warp reads 128 contiguous bytes), takes its left/right neighbour words by shuffle, forms the
 // four horizontal sums of its 4 pixels, and keeps the last seven row results in registers as a sliding window for the
-// vertical pass: no shared memory, every source byte is loaded once per strip (22 rows for 16 outputs), the output
+// vertical pass: no shared memory, every source byte is loaded once per strip (BLUR_RPW + 6 rows for BLUR_RPW outputs), the output
 // is one coalesced 32-bit store per lane. Reflect-101 borders take a per-byte path only in the lanes that touch them.
 // ---------------------------------------------------------------------------------------------
 #ifndef BLUR_OVERLAP
 #define BLUR_OVERLAP 1                  // warps overlap by one word on each side: lanes 0 / 31 only feed their neighbours, no edge loads
 #endif
 #define BLUR_TW (BLUR_OVERLAP ? 120 : 128)   // output pixels per warp row
-#define BLUR_RPW 16                      // output rows per warp
+#ifndef BLUR_ROLLED
+#define BLUR_ROLLED 1
+#endif
+#ifndef BLUR_RPW
+#define BLUR_RPW 30                      // output rows per warp (a multiple of 6 in the rolled form)
+#endif
 #define BLUR_TH (8 * BLUR_RPW)           // rows per CTA (8 warps)
 
 // own word of this lane for one source row (0 beyond the row); issued one row ahead of its use
@@ -135,6 +140,39 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const uint8_t* row = img + (size_t)ccm_reflect101(min(wy0 - 3, h + 2), h) * pitch;
     uint32_t own = blur_load(row, x, w);
     const uint32_t W01 = K::k0 | (K::k1 << 8), W23 = K::k2 | (K::k3 << 8), W21 = K::k2 | (K::k1 << 8), W_0 = K::k0 << 8;
+#if BLUR_ROLLED
+    // rows in blocks of six (the pair ring's period): the first block only fills the ring, every later block is the same code
+    // with r = 6 * blk + j, so the loop body is 6 rows long instead of BLUR_RPW + 6 (instruction cache) and BLUR_RPW can grow
+    // (6 halo rows per BLUR_RPW outputs).
+    static_assert(BLUR_RPW % 6 == 0, "BLUR_RPW must be a multiple of 6");
+#pragma unroll 1
+    for (int blk = 0; blk <= BLUR_RPW / 6; blk++) {
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+            const int r = 6 * blk + j;
+            const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
+            const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
+            uint32_t hs[4];
+            blur_hrow<OCV24>(row, own, x, x0, w, lane, sel_lo, sel_hi, hs);
+            row = row_n; own = own_n;
+#pragma unroll
+            for (int k = 0; k < 4; k++) { pr[j][k] = __byte_perm(last[k], hs[k], 0x5410); last[k] = hs[k]; }   // (row r-1, row r)
+            if (blk > 0) {
+                const int oy = wy0 + r - 6;
+                uint32_t packed = 0;
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const uint32_t acc = __dp2a_lo(pr[(j + 1) % 6][k], W01, __dp2a_lo(pr[(j + 3) % 6][k], W23, __dp2a_lo(pr[(j + 5) % 6][k], W21,
+                                                   __dp2a_lo(pr[j][k], W_0, 32768u))));
+                    const uint32_t v = acc >> 16;
+                    packed |= (OCV24 ? min(v, 255u) : v) << (8 * k);
+                }
+                if (out_lane && oy < h && x < w) *reinterpret_cast<uint32_t*>(outp) = packed;   // pitch multiple of 32: in-bounds
+                outp += L.blur_pitch;
+            }
+        }
+    }
+#else
 #pragma unroll
     for (int r = 0; r < BLUR_RPW + 6; r++) {
         const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
@@ -158,6 +196,7 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
             outp += L.blur_pitch;
         }
     }
+#endif
 }
 
 // ---------------------------------------------------------------------------------------------
