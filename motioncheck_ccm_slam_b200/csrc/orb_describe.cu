@@ -15,6 +15,9 @@
 #define BLUR_OVERLAP 1                  // warps overlap by one word on each side: lanes 0 / 31 only feed their neighbours, no edge loads
 #endif
 #define BLUR_TW (BLUR_OVERLAP ? 120 : 128)   // output pixels per warp row
+#ifndef BLUR_PF
+#define BLUR_PF 3                        // rows of prefetch (divides 6): 0.0903 / 0.0811 / 0.0804 ms per 64 frames at 1 / 2 / 3
+#endif
 #ifndef BLUR_ROLLED
 #define BLUR_ROLLED 1
 #endif
@@ -138,7 +141,18 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     // Strips that touch neither the top nor the bottom border step the row pointer; the others reflect per row.
     const bool inner = wy0 >= 3 && wy0 + BLUR_RPW + 3 <= h;   // warp-uniform
     const uint8_t* row = img + (size_t)ccm_reflect101(min(wy0 - 3, h + 2), h) * pitch;
+#if BLUR_ROLLED
+    // the lane's words of the next BLUR_PF rows are in flight while a row is worked on (q[t % BLUR_PF] = window row t)
+    uint32_t q[BLUR_PF];
+    q[0] = blur_load(row, x, w);
+#pragma unroll
+    for (int d = 1; d < BLUR_PF; d++) {
+        row = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + d - 3, h + 2), h) * pitch;
+        q[d] = blur_load(row, x, w);
+    }
+#else
     uint32_t own = blur_load(row, x, w);
+#endif
     const uint32_t W01 = K::k0 | (K::k1 << 8), W23 = K::k2 | (K::k3 << 8), W21 = K::k2 | (K::k1 << 8), W_0 = K::k0 << 8;
 #if BLUR_ROLLED
     // rows in blocks of six (the pair ring's period): the first block only fills the ring, every later block is the same code
@@ -150,11 +164,11 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
 #pragma unroll
         for (int j = 0; j < 6; j++) {
             const int r = 6 * blk + j;
-            const uint8_t* row_n = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r - 2, h + 2), h) * pitch;
-            const uint32_t own_n = (r + 1 < BLUR_RPW + 6) ? blur_load(row_n, x, w) : 0u;
+            const uint32_t own = q[j % BLUR_PF];
+            row = inner ? row + pitch : img + (size_t)ccm_reflect101(min(wy0 + r + BLUR_PF - 3, h + 2), h) * pitch;   // window row r + BLUR_PF
+            q[j % BLUR_PF] = (r + BLUR_PF < BLUR_RPW + 6) ? blur_load(row, x, w) : 0u;
             uint32_t hs[4];
             blur_hrow<OCV24>(row, own, x, x0, w, lane, sel_lo, sel_hi, hs);
-            row = row_n; own = own_n;
 #pragma unroll
             for (int k = 0; k < 4; k++) { pr[j][k] = __byte_perm(last[k], hs[k], 0x5410); last[k] = hs[k]; }   // (row r-1, row r)
             if (blk > 0) {
