@@ -64,14 +64,21 @@ def single_frame(torch, local_rank, w, h, nf, nl, frames, calls=300):
     for i in range(20):
         ex.extract_raw(ptrs[i % len(ptrs)], h, w, w, okp.data_ptr(), ode.data_ptr(), cap, ctypes.byref(on))
     l0 = ex.launch_count()
+    per = np.empty(calls)
     t0 = time.perf_counter()
     for i in range(calls):
+        ta = time.perf_counter()
         ex.extract_raw(ptrs[i % len(ptrs)], h, w, w, okp.data_ptr(), ode.data_ptr(), cap, ctypes.byref(on))
+        per[i] = time.perf_counter() - ta
     dt = time.perf_counter() - t0
     launches = ex.launch_count() - l0
     ex.close()
-    return {"single_frame_latency_us": 1e6 * dt / calls, "single_frame_frames_per_s": calls / dt,
-            "single_frame_api": "ccm_orb_extract: copy-in, one CUDA graph (kernel sequence + copy-out), wait; %d calls, %d kernel launches replayed" % (calls, launches)}, launches
+    q = np.percentile(per, [10, 50, 90]) * 1e6
+    return {"single_frame_latency_us": 1e6 * dt / calls, "single_frame_latency_us_p10_p50_p90": [float(q[0]), float(q[1]), float(q[2])],
+            "single_frame_frames_per_s": calls / dt,
+            "single_frame_api": "ccm_orb_extract: copy-in, one CUDA graph (a branch per pyramid level: FAST + quadtree of level l behind its resize; blur "
+                                "branch; k_orient_describe writes into the pinned host mirrors), wait; %d calls back to back, mean and percentiles "
+                                "of the per-call host time, %d kernel launches replayed" % (calls, launches)}, launches
 
 
 # ----------------------------------------------------------------------------------------------------------

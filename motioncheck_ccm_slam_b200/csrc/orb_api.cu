@@ -447,7 +447,7 @@ static int run_pipeline(ccm_orb* h, int n, const uint8_t* l0, size_t l0_pitch, s
         if (st) CK(cudaEventRecord(h->ev[3], s));
     }
     {
-        CKL("k_quadtree", launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(512), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, 0, (const uint32_t*)A.corners,
+        CKL("k_quadtree", launch_pdl(k_quadtree, dim3(T.nlevels, n), dim3(QT_THREADS), h->qt_smem, s, T, h->qt_cap, h->qt_ccap, 0, (const uint32_t*)A.corners,
                                      (const int*)A.corner_count, A.node_of, A.level_kps, A.level_kp_count));
         h->launches++;
         if (fork) {
@@ -855,6 +855,7 @@ static int run_pipeline_single_levels(ccm_orb* h, const uint8_t* l0, size_t l0_p
     }
     FastTma tm = h->fc_tmaps;
     const bool tma = h->fc_tma && encode_level_map(h, &tm.m[0], l0, l0_pitch, T.l[0].h, l0_stride, 1, FC_TW, h->fc_smem.tile_rows);
+    static const int qt_single = std::getenv("CCM_ORB_QT_SINGLE") ? std::atoi(std::getenv("CCM_ORB_QT_SINGLE")) : QT_THREADS_SINGLE;   // tuning knob
     CK(cudaMemsetAsync(h->d_corner_count, 0, sizeof(int) * CCM_MAX_LEVELS, s));
     for (int l = 0; l < L; l++) {
         if (l > 0) {
@@ -875,7 +876,7 @@ static int run_pipeline_single_levels(ccm_orb* h, const uint8_t* l0, size_t l0_p
             CKL("k_fast_chunks (one level)", cudaSuccess);
             h->launches++;
         }
-        k_quadtree<<<dim3(1, 1), dim3(512), h->qt_smem, x>>>(T, h->qt_cap, h->qt_ccap, l, (const uint32_t*)h->d_corners, (const int*)h->d_corner_count,
+        k_quadtree<<<dim3(1, 1), dim3(qt_single), h->qt_smem, x>>>(T, h->qt_cap, h->qt_ccap, l, (const uint32_t*)h->d_corners, (const int*)h->d_corner_count,
                                                                  h->d_node_of, h->d_level_kps, h->d_level_kp_count);
         CKL("k_quadtree (one level)", cudaSuccess);
         h->launches++;

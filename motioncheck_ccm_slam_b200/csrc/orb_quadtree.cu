@@ -20,13 +20,14 @@ namespace {
 
 struct QNode { short ulx, uly, brx, bry; int cnt; };
 
-// exclusive prefix sum of v[0..n) in place (block-wide, QT_THREADS threads); returns the total. scratch: 32 ints.
-// Each thread owns a contiguous run of ceil(n / QT_THREADS) elements; the per-thread sums are scanned inside every warp
-// at once and the 16 warp totals by every warp redundantly, so the call costs two barriers and ten shuffle steps.
-#define QT_THREADS 512
+// exclusive prefix sum of v[0..n) in place (block-wide, any multiple of 32 threads up to 1024); returns the total. scratch: 32 ints.
+// Each thread owns a contiguous run of ceil(n / threads) elements; the per-thread sums are scanned inside every warp
+// at once and the warp totals by every warp redundantly, so the call costs two barriers and ten shuffle steps.
+#define QT_THREADS 256               // batch launch: CTA = (level, frame); 0.0399 / 0.0364 / 0.0355 ms per 64 frames at 512 / 384 / 256
+#define QT_THREADS_SINGLE 384        // one frame, one launch per level: latency, not throughput
 __device__ int block_exclusive_scan(int* v, int n, int* scratch) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int per = (n + QT_THREADS - 1) / QT_THREADS;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, NW = NT >> 5;
+    const int per = (n + NT - 1) / NT;
     const int b = min(tid * per, n), e = min(b + per, n);
     int s = 0;
     for (int i = b; i < e; i++) s += v[i];
@@ -35,11 +36,11 @@ __device__ int block_exclusive_scan(int* v, int n, int* scratch) {
     for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
     if (lane == 31) scratch[warp] = inc;
     __syncthreads();
-    const int wt = lane < QT_THREADS / 32 ? scratch[lane] : 0;
+    const int wt = lane < NW ? scratch[lane] : 0;
     int winc = wt;
 #pragma unroll
-    for (int o = 1; o < QT_THREADS / 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += y; }
-    const int total = __shfl_sync(0xffffffffu, winc, QT_THREADS / 32 - 1);
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += y; }
+    const int total = __shfl_sync(0xffffffffu, winc, 31);
     int run = __shfl_sync(0xffffffffu, winc - wt, warp) + inc - s;
     for (int i = b; i < e; i++) { const int x = v[i]; v[i] = run; run += x; }
     __syncthreads();
@@ -101,7 +102,7 @@ __device__ __forceinline__ void place_node(const QNode* A, QNode* B, const int* 
 // child-occupancy tables ping-pong; the pass that moves every corner to its new node also counts the occupancy of that
 // node's children for the next round; in a sweep round the creation index of a node's children and the number of split
 // nodes in front of it come out of ONE scan of a packed value. Sweep round: 4 barriers, greedy round: 10 (was 14 / 20).
-__global__ void __launch_bounds__(QT_THREADS, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap, int lvl0,   // CTA x handles level lvl0 + x
+__global__ void __launch_bounds__(512, 4) k_quadtree(const __grid_constant__ LevelTable T, int cap, int ccap, int lvl0,   // CTA x handles level lvl0 + x
                                                   const uint32_t* corners, const int* corner_count,   // written by the PDL predecessor: no __restrict__, so these are coherent loads the compiler cannot hoist above pdl_wait()
                                                   uint16_t* __restrict__ node_of,          // [frames][corners_per_frame]
                                                   uint32_t* __restrict__ level_kps,        // [frames][kps_per_frame] packed x|y<<12|score<<24

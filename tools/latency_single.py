@@ -26,9 +26,14 @@ for mb in (1, 8):
                        ("ccm_orb_extract_batch n=1", lambda i: ex.extract_batch_raw(ptrs[i % 16], 1, h, w, w, okp.data_ptr(), ode.data_ptr(), cap, on))):
         for i in range(20):
             call(i)
+        per = np.empty(N)
         t0 = time.perf_counter()
         for i in range(N):
+            ta = time.perf_counter()
             call(i)
+            per[i] = time.perf_counter() - ta
         dt = time.perf_counter() - t0
-        print("max_batch %d, %s: %.1f us per frame, %.0f frames/s, %d keypoints" % (mb, name, 1e6 * dt / N, N / dt, on[0]))
+        q = np.percentile(per, [10, 50, 90]) * 1e6
+        print("max_batch %d, %s: %.1f us per frame (p10 %.1f, p50 %.1f, p90 %.1f), %.0f frames/s, %d keypoints"
+              % (mb, name, 1e6 * dt / N, q[0], q[1], q[2], N / dt, on[0]))
     ex.close()
