@@ -155,7 +155,8 @@ int ccm_descriptor_distance(ccm_matcher* m, const uint8_t* a, const uint8_t* b, 
 
 /* ---- frame packs ------------------------------------------------------------------------------------------ */
 int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
-    if (!m || !out || capacity <= 0 || capacity > 65535) return CCM_E_BADARG;
+    if (!m || !out) return CCM_E_BADARG;
+    if (capacity <= 0 || capacity > 65535) { m->err = "frame pack capacity must be 1..65535 (feature indices are 16 bits in the candidate keys)"; return CCM_E_BADARG; }
     *out = nullptr;
     cudaSetDevice(m->device);
     ccm_frame_pack* p = new ccm_frame_pack();
@@ -215,7 +216,7 @@ static int launch_build_grid(ccm_matcher* m, ccm_frame_pack* const* packs, int n
     }
     const int smem_cap = (max_cap + 1) & ~1;
     const size_t smem = (size_t)max_cells * 4 + (size_t)smem_cap * 6;
-    if (max_cap <= 65536 && smem <= 160 * 1024) {
+    if (smem <= 160 * 1024) {                       // capacities are <= 65535 (ccm_frame_pack_create): items fit the u16 staging
         if (smem > 48 * 1024 && smem > m->grid_smem_optin) {
             MCK(cudaFuncSetAttribute(k_build_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             m->grid_smem_optin = smem;

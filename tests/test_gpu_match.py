@@ -54,7 +54,7 @@ def test_descriptor_distance(gm):
 
 
 @pytest.mark.parametrize("seed,n,cap", [(11, 1000, None), (12, 2000, None), (13, 1, None), (14, 0, None), (15, 5000, None),
-                                        (16, 3000, 70000)])      # cap > 65536: the grid is built in global memory
+                                        (16, 3000, 30000)])      # a pack too large for the shared-memory working set: the grid is built in global memory
 def test_grid_matches_frame_assign(gm, seed, n, cap):
     from motioncheck_ccm_slam_b200.matcher import frame_grid
     from motioncheck_ccm_slam_b200.synth import make_feature_frame
