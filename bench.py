@@ -659,6 +659,12 @@ def run_ours(args, wl, rank, world, local_rank):
                          "carry-save LOP3 tree needs 4 POPC per pair, so frac exceeds 1 against this denominator" % sm_max,
             "frac_of_4popc_bound": gp / world / (2 * peak_pairs),
             "own_bound": "4 POPC + 18 LOP3/XOR + 3 min/max per pair: POPC bound %.0f Gpair/s per GPU; ncu (profiles/r1q): ALU pipe 83 %% busy" % (2 * peak_pairs)}
+        loop = measured_loop_ceiling()
+        if loop:
+            ham["allpairs"]["roofline"].update({
+                "measured_loop_ceiling": loop, "frac_of_measured_loop_ceiling": gp / world / loop,
+                "measured_loop_ceiling_kind": "the product kernel's inner loop (LOP3 carry-save tree, 4 POPC, packed best/second keys, register "
+                                              "prefetch) in tools/ubench_int.cu on an L2-resident random database, Gpair/s per GPU (profiles/r2_ubench_int.json)"})
         ham["tracking"].update({"frames_per_s": B * world / (tr_ms * 1e-3), "ms_per_step": tr_ms})
         line["hamming"] = {k: v for k, v in ham.items() if not k.startswith("_")}
         line["gpu_launches"] += int(ham["_launches"])
@@ -690,6 +696,15 @@ def run_ours(args, wl, rank, world, local_rank):
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def measured_loop_ceiling():
+    """Gpair/s of the all-pairs inner loop as tools/ubench_int.cu measured it on a B200 (committed evidence; None if absent)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_ubench_int.json")) as f:
+            return float(json.load(f)["hamming_q4_csa_Gpairs_per_s"])
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 def main():

@@ -3,6 +3,7 @@
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o tools/ubench_int tools/ubench_int.cu
 #include <cstdio>
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 #define ITERS 4096
@@ -28,22 +29,31 @@ template <int OP> __global__ void k(uint32_t* out, uint32_t seed) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
-// Hamming inner loops: Q query descriptors in registers vs targets streamed from shared memory
-template <int Q, int CSA> __global__ void hamming(const uint4* __restrict__ tg, int nt, uint32_t* out, uint32_t seed) {
+// Hamming inner loops: Q query descriptors in registers vs targets streamed from shared memory.
+// CSA = 0: the textbook loop (8 XOR + 8 POPC + adds per pair). CSA = 1: the loop of the product kernel k_allpairs_best2
+// (motioncheck_ccm_slam_b200/csrc/match_allpairs.cu) restated instruction for instruction - carry-save tree as explicit LOP3
+// (0x96 = xor3, 0xe8 = majority), 4 POPC, packed (distance << 23 | index) keys with a branch-free best / second-best
+// update, next tile prefetched into registers while the current one is used - on a database that stays in L2, so the
+// figure is the ceiling of THAT loop and the product kernel (which also streams its shard from HBM) cannot beat it.
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) { uint32_t d; asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+__device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { uint32_t d; asm("lop3.b32 %0, %1, %2, %3, 0xe8;" : "=r"(d) : "r"(a), "r"(b), "r"(c)); return d; }
+template <int Q, int CSA> __global__ void __launch_bounds__(256) hamming(const uint4* __restrict__ tg, int nt, uint32_t* out, uint32_t seed) {
     __shared__ uint4 st[2 * 256];
     uint32_t q[Q][8];
 #pragma unroll
     for (int j = 0; j < Q; j++)
 #pragma unroll
         for (int i = 0; i < 8; i++) q[j][i] = seed * (threadIdx.x * Q + j + 1) + i * 0x9e3779b9u;
-    uint32_t best[Q];
+    uint32_t b1[Q], b2[Q];
 #pragma unroll
-    for (int j = 0; j < Q; j++) best[j] = 0xffffffffu;
+    for (int j = 0; j < Q; j++) b1[j] = b2[j] = 0xffffffffu;
+    uint4 p0 = tg[threadIdx.x], p1 = tg[threadIdx.x + 256];
     for (int base = 0; base < nt; base += 256) {
         __syncthreads();
-        for (int i = threadIdx.x; i < 512; i += blockDim.x) st[i] = tg[(size_t)base * 2 + i];
+        st[threadIdx.x] = p0; st[threadIdx.x + 256] = p1;
         __syncthreads();
-#pragma unroll 4
+        if (base + 256 < nt) { p0 = tg[(size_t)(base + 256) * 2 + threadIdx.x]; p1 = tg[(size_t)(base + 256) * 2 + threadIdx.x + 256]; }
+#pragma unroll 2
         for (int t = 0; t < 256; t++) {
             const uint4 lo = st[2 * t], hi = st[2 * t + 1];
             const uint32_t w[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
@@ -58,21 +68,22 @@ template <int Q, int CSA> __global__ void hamming(const uint4* __restrict__ tg, 
                     uint32_t x[8];
 #pragma unroll
                     for (int i = 0; i < 8; i++) x[i] = q[j][i] ^ w[i];
-                    // carry-save adders: 7 words -> ones/twos/fours, plus the eighth word
-                    const uint32_t o0 = x[0] ^ x[1] ^ x[2], t0 = (x[0] & x[1]) | (x[2] & (x[0] | x[1]));
-                    const uint32_t o1 = x[3] ^ x[4] ^ x[5], t1 = (x[3] & x[4]) | (x[5] & (x[3] | x[4]));
-                    const uint32_t o2 = o0 ^ o1 ^ x[6], t2 = (o0 & o1) | (x[6] & (o0 | o1));
-                    const uint32_t tw = t0 ^ t1 ^ t2, fo = (t0 & t1) | (t2 & (t0 | t1));
+                    const uint32_t o0 = xor3(x[0], x[1], x[2]), t0 = maj3(x[0], x[1], x[2]);
+                    const uint32_t o1 = xor3(x[3], x[4], x[5]), t1 = maj3(x[3], x[4], x[5]);
+                    const uint32_t o2 = xor3(o0, o1, x[6]), t2 = maj3(o0, o1, x[6]);
+                    const uint32_t tw = xor3(t0, t1, t2), fo = maj3(t0, t1, t2);
                     d = __popc(o2) + __popc(x[7]) + 2 * __popc(tw) + 4 * __popc(fo);
                 }
-                const uint32_t key = (d << 22) | (uint32_t)(base + t);
-                best[j] = min(best[j], key);
+                const uint32_t key = (d << 23) + (uint32_t)(base + t);
+                const uint32_t m = max(b1[j], key);
+                b1[j] = min(b1[j], key);
+                b2[j] = min(b2[j], m);
             }
         }
     }
     uint32_t acc = 0;
 #pragma unroll
-    for (int j = 0; j < Q; j++) acc ^= best[j];
+    for (int j = 0; j < Q; j++) acc ^= b1[j] ^ b2[j];
     out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
@@ -102,13 +113,25 @@ int main() {
                ops / (ms[i] * 1e-3) / sms / (clk * 1e3));
     }
     const int nt = 1 << 16;
-    uint4* tg; cudaMalloc(&tg, (size_t)nt * 32); cudaMemset(tg, 0x5a, (size_t)nt * 32);
+    uint4* tg; cudaMalloc(&tg, (size_t)nt * 32);
+    {   // random descriptors: constant data toggles few bits and flatters the loop
+        uint32_t* h = (uint32_t*)malloc((size_t)nt * 32);
+        uint32_t x = 0x12345678u;
+        for (size_t i = 0; i < (size_t)nt * 8; i++) { x ^= x << 13; x ^= x >> 17; x ^= x << 5; h[i] = x; }
+        cudaMemcpy(tg, h, (size_t)nt * 32, cudaMemcpyHostToDevice);
+        free(h);
+    }
     auto rep = [&](const char* name, float m, int Q) {
         const double pairs = (double)blocks * threads * Q * nt;
         printf(", \"%s_Gpairs_per_s\": %.1f", name, pairs / m / 1e6);
     };
     rep("hamming_q4_popc", timeit([&] { hamming<4, 0><<<blocks, threads>>>(tg, nt, out, 7); }), 4);
     rep("hamming_q4_csa", timeit([&] { hamming<4, 1><<<blocks, threads>>>(tg, nt, out, 7); }), 4);
+    {   // the product kernel's geometry: one wave, three CTAs per SM (73 registers)
+        const int b3 = sms * 3;
+        const float m3 = timeit([&] { hamming<4, 1><<<b3, threads>>>(tg, nt, out, 7); });
+        printf(", \"hamming_q4_csa_one_wave_Gpairs_per_s\": %.1f", (double)b3 * threads * 4 * nt / m3 / 1e6);
+    }
     rep("hamming_q8_popc", timeit([&] { hamming<8, 0><<<blocks, threads>>>(tg, nt, out, 7); }), 8);
     rep("hamming_q8_csa", timeit([&] { hamming<8, 1><<<blocks, threads>>>(tg, nt, out, 7); }), 8);
     printf("}\n");
