@@ -828,12 +828,12 @@ static int allpairs_chunks(ccm_matcher* m, const uint8_t* d_q, int nq, const uin
     // queries per thread: as many as keep (almost) every thread of a query tile busy
     const int Q = nq >= 896 ? 4 : (nq >= 384 ? 2 : 1);
     const int q_tiles = (nq + AP_THREADS * Q - 1) / (AP_THREADS * Q);
-    // chunks of the target range: two waves of the three CTAs an SM holds (whole waves: 8 per SM is slower than 6), chunk a
-    // multiple of the tile, <= 2^23
+    // chunks of the target range: two waves of the three CTAs an SM holds (whole waves: 8 per SM is slower than 6), chunk <= 2^23
     static const int per_sm = std::getenv("CCM_AP_CTAS_PER_SM") ? std::max(1, std::atoi(std::getenv("CCM_AP_CTAS_PER_SM"))) : 6;   // tuning knob; 3 are resident (73 registers): 764 / 772 / 783 / 760 / 783 Gpair/s at 3 / 4 / 6 / 8 / 12
     long long want = std::max<long long>(1, ((long long)m->sms * per_sm + q_tiles - 1) / q_tiles);
+    // (not rounded to whole tiles: the kernel takes a partial last tile, and rounding left the second wave of a 0.5 M shard
+    // half empty: 648 -> 710 Gpair/s there, 783 -> 799 at 4 M)
     long long chunk = std::max<long long>(AP_TILE, (nt + want - 1) / want);
-    chunk = (chunk + AP_TILE - 1) / AP_TILE * AP_TILE;
     chunk = std::min<long long>(chunk, AP_MAX_CHUNK);
     const long long n_chunks = std::max<long long>(1, (nt + chunk - 1) / chunk);
     if (n_chunks > 65535) { m->err = "target shard too large for one launch (> 2^39 descriptors)"; return CCM_E_BADARG; }
