@@ -828,8 +828,12 @@ static int allpairs_chunks(ccm_matcher* m, const uint8_t* d_q, int nq, const uin
     // queries per thread: as many as keep (almost) every thread of a query tile busy
     const int Q = nq >= 896 ? 4 : (nq >= 384 ? 2 : 1);
     const int q_tiles = (nq + AP_THREADS * Q - 1) / (AP_THREADS * Q);
-    // chunks of the target range: two waves of the three CTAs an SM holds (whole waves: 8 per SM is slower than 6), chunk <= 2^23
-    static const int per_sm = std::getenv("CCM_AP_CTAS_PER_SM") ? std::max(1, std::atoi(std::getenv("CCM_AP_CTAS_PER_SM"))) : 6;   // tuning knob; 3 are resident (73 registers): 764 / 772 / 783 / 760 / 783 Gpair/s at 3 / 4 / 6 / 8 / 12
+    // chunks of the target range, each <= 2^23 targets
+    // Whole waves of the three CTAs an SM holds (73 registers): two waves once a chunk is at least four tiles long, one wave for
+    // smaller shards, where the per-CTA prologue shows (0.5 M targets: 731 / 708 / 674 Gpair/s at 3 / 6 / 9 per SM; 4 M: 780 /
+    // 799 / 802; 8 per SM = 2.67 waves is slower than 6). CCM_AP_CTAS_PER_SM overrides.
+    static const int env_per_sm = std::getenv("CCM_AP_CTAS_PER_SM") ? std::max(1, std::atoi(std::getenv("CCM_AP_CTAS_PER_SM"))) : 0;
+    const int per_sm = env_per_sm ? env_per_sm : (nt / ((long long)m->sms * 6) >= 4 * AP_TILE ? 6 : 3);
     long long want = std::max<long long>(1, ((long long)m->sms * per_sm + q_tiles - 1) / q_tiles);
     // (not rounded to whole tiles: the kernel takes a partial last tile, and rounding left the second wave of a 0.5 M shard
     // half empty: 648 -> 710 Gpair/s there, 783 -> 799 at 4 M)
