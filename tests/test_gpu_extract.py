@@ -56,7 +56,9 @@ def test_reference_fixtures(cuda_lib, name):
 
 @pytest.mark.parametrize("w,h,nf,nl,seed", [(1241, 376, 2000, 8, 3000), (752, 480, 2000, 8, 11), (641, 479, 700, 6, 5),
                                              (320, 240, 300, 4, 7), (400, 300, 20, 5, 2), (752, 480, 5000, 8, 13),
-                                             (512, 512, 1500, 7, 17), (380, 560, 600, 5, 19)])
+                                             (512, 512, 1500, 7, 17), (380, 560, 600, 5, 19),
+                                             (1920, 1080, 3000, 8, 23),      # full HD: 2.4 M pyramid pixels, ~650 nodes on level 0
+                                             (4095, 131, 1500, 3, 29)])      # the widest image the handle accepts, three cell rows
 def test_shapes_and_quotas(cuda_lib, w, h, nf, nl, seed):
     ex = make(cuda_lib, nf, 1.2, nl, 20, 7, max_width=w, max_height=h, max_batch=2)
     orc = OracleExtractor(nf, 1.2, nl, 20, 7)
@@ -65,6 +67,8 @@ def test_shapes_and_quotas(cuda_lib, w, h, nf, nl, seed):
     for f in range(2):
         ko, do = orc(frames[f])
         assert_same(kps[f], descs[f], ko, do, (w, h, nf, f))
+    k1, d1 = ex(frames[1])                       # the single-frame entry point (one CUDA graph, a branch per level)
+    assert np.array_equal(k1, kps[1]) and np.array_equal(d1, descs[1])
 
 
 def test_other_scale_and_thresholds(cuda_lib):
