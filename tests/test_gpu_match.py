@@ -330,6 +330,50 @@ def test_extractor_to_matcher_zero_copy_batch(gm, B):
     ex.close()
 
 
+@pytest.mark.parametrize("n_jobs", [1, 6, 20])      # 1 k / 6 k / 20 k queries in flight: 32 / 16 / 8 lanes per query in k_window_eval
+def test_dense_windows_batch_all_lane_widths(gm, n_jobs):
+    """Windows of 60-150 candidates (radius 120 px x scale): every lane of a query's group sees more than its four best, so the
+    stored candidate lists end early and the resolver has to know it; hundreds of queries compete for the same features."""
+    torch = pytest.importorskip("torch")
+    from motioncheck_ccm_slam_b200.matcher import (QUERY_DTYPE, RESULT_DTYPE, WIN_PROJ_LASTFRAME, Q_VALID, Q_OBS, frame_grid,
+                                                   search_window_batch_device)
+    dev = torch.device("cuda", 0)
+    n, th = 1000, 120.0
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    grid = frame_grid(W, H)
+    packs, ofs, q, qd, rng = [], [], np.zeros((n_jobs, n), QUERY_DTYPE), np.zeros((n_jobs, n, 32), np.uint8), np.random.default_rng(77)
+    inputs = []
+    for j in range(n_jobs):
+        a, b, _ = _frames(500 + 3 * j, n)
+        p, of = _pack(gm, b, grid, cap=n)
+        packs.append(p); ofs.append(of)
+        u = (a["x"] + rng.normal(0, 3, n)).astype(np.float32); v = (a["y"] + rng.normal(0, 3, n)).astype(np.float32)
+        q["u"][j] = u; q["v"][j] = v; q["angle"][j] = a["angle"]
+        q["r"][j] = np.float32(th) * sf[a["octave"]]
+        q["min_level"][j] = a["octave"] - 1; q["max_level"][j] = a["octave"] + 1
+        q["flags"][j] = Q_VALID | Q_OBS
+        qd[j] = a["desc"]
+        inputs.append((a, u, v))
+    d_q = torch.from_numpy(q.view(np.uint8).reshape(n_jobs, n, 24)).to(dev)
+    d_qd = torch.from_numpy(qd).to(dev)
+    d_holder = torch.full((n_jobs, n), -1, dtype=torch.int32, device=dev)
+    d_res = torch.zeros((n_jobs, n, 4), dtype=torch.int32, device=dev)
+    d_nm = torch.zeros((n_jobs,), dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    search_window_batch_device(gm, packs, WIN_PROJ_LASTFRAME, 0.9, 100, True, None, n, d_q.data_ptr(), d_qd.data_ptr(),
+                               d_holder.data_ptr(), n, d_res.data_ptr(), d_nm.data_ptr())
+    gm.sync()
+    holder, res, nm = d_holder.cpu().numpy(), d_res.cpu().numpy().view(RESULT_DTYPE).reshape(n_jobs, n), d_nm.cpu().numpy()
+    for j in range(n_jobs):
+        a, u, v = inputs[j]
+        hc = np.full(n, -1, np.int32)
+        nm_c, res_c = OracleMatcher(0.9, True).projection_lastframe(ofs[j], np.ones(n), u, v, a["octave"], a["angle"], a["desc"], np.ones(n), th, sf, hc)
+        _same_res(res[j], res_c)
+        assert nm[j] == nm_c and np.array_equal(holder[j], hc)
+    for p in packs:
+        p.close()
+
+
 def test_dropin_cpp_matcher_matches_reference_class(cuda_lib):
     """The drop-in C++ ORBmatcher bodies (motioncheck_ccm_slam_b200/host/ORBmatcher.cpp, compiled against the
     reference's own <cslam/ORBmatcher.h>) and the reference's ORBmatcher.cpp, both driven through the same glue with
