@@ -83,6 +83,9 @@ template <typename Tp> static int mbuf_upload(ccm_matcher* m, int slot, const Tp
     return CCM_OK;
 }
 
+static double mnow_us() { timespec t; clock_gettime(CLOCK_MONOTONIC, &t); return t.tv_sec * 1e6 + t.tv_nsec * 1e-3; }
+static const bool g_match_trace = std::getenv("CCM_MATCH_TRACE") != nullptr;   // per-call host timeline of the BoW-grouped searches on stderr
+
 static int stage_host(ccm_matcher* m, size_t bytes, uint8_t** out) {
     if (m->h_stage_cap < bytes) {
         MCK(cudaStreamSynchronize(m->stream));
@@ -579,10 +582,26 @@ int ccm_search_window(ccm_matcher* m, ccm_frame_pack* targets, const ccm_window_
 
 /* ---- BoW-guided searches ---------------------------------------------------------------------------------- */
 // FeatureVector iteration order: (node id, feature index) ascending, features with node < 0 absent
+// features that have a node, by node id, index order inside a node (what iterating a DBoW2 FeatureVector gives): a stable
+// LSD radix sort on the node id, 8 bits a pass (the input is in index order, so stability gives the order inside a node).
+// Comparison sorts cost 25-35 us per 1000 features on the GPU boxes' hosts - half of a SearchByBoW call; this is ~3 us.
 static void feature_vector_order(int n, const int* node, std::vector<int>& order) {
+    static thread_local std::vector<int> tmp;
     order.clear();
-    for (int i = 0; i < n; i++) if (node[i] >= 0) order.push_back(i);
-    std::stable_sort(order.begin(), order.end(), [node](int a, int b) { return node[a] < node[b]; });
+    unsigned mx = 0;
+    for (int i = 0; i < n; i++) if (node[i] >= 0) { order.push_back(i); mx = std::max(mx, (unsigned)node[i]); }
+    tmp.resize(order.size());
+    int* src = order.data();
+    int* dst = tmp.data();
+    const size_t cnt = order.size();
+    for (int shift = 0; shift < 32 && (mx >> shift) != 0; shift += 8) {
+        size_t hist[257] = {};
+        for (size_t k = 0; k < cnt; k++) hist[(((unsigned)node[src[k]]) >> shift & 255u) + 1]++;
+        for (int d = 0; d < 256; d++) hist[d + 1] += hist[d];
+        for (size_t k = 0; k < cnt; k++) dst[hist[((unsigned)node[src[k]]) >> shift & 255u]++] = src[k];
+        std::swap(src, dst);
+    }
+    if (src != order.data()) std::memcpy(order.data(), src, cnt * sizeof(int));
 }
 
 // extra per-feature inputs of SearchForTriangulation (host pointers)
@@ -603,11 +622,13 @@ static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_or
         return CCM_OK;
     }
     cudaSetDevice(m->device);
+    const double t0 = g_match_trace ? mnow_us() : 0.0;
     // merge-join of the two vectors on node id (ORBmatcher.cpp:203-278): shared nodes, ascending
-    std::vector<int> oa, ob;
+    static thread_local std::vector<int> oa, ob;
     feature_vector_order(n_a, node_a, oa);
     feature_vector_order(n_b, node_b, ob);
-    std::vector<BowNode> nodes;
+    static thread_local std::vector<BowNode> nodes;
+    nodes.clear();
     size_t ia = 0, ib = 0;
     while (ia < oa.size() && ib < ob.size()) {
         const int na = node_a[oa[ia]], nb = node_b[ob[ib]];
@@ -618,6 +639,7 @@ static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_or
         else if (na < nb) ia = ea;
         else ib = eb;
     }
+    const double t1 = g_match_trace ? mnow_us() : 0.0;
     int rc;
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
     const size_t A = (size_t)n_a, B = (size_t)n_b;
@@ -671,6 +693,7 @@ static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_or
         std::memcpy(hbase + a_x, tri->x_a, A * 4); std::memcpy(hbase + a_y, tri->y_a, A * 4);
         std::memcpy(hbase + b_x, tri->x_b, B * 4); std::memcpy(hbase + b_y, tri->y_b, B * 4); std::memcpy(hbase + b_oct, tri->oct_b, B * 4);
     }
+    const double t2 = g_match_trace ? mnow_us() : 0.0;
     MCK(cudaMemcpyAsync(dbase, hbase, in_total, cudaMemcpyHostToDevice, m->stream));
     k_bow_init<<<(std::max(n_a, n_b) + 255) / 256, 256, 0, m->stream>>>(J);
     if (tri) {
@@ -682,11 +705,16 @@ static int bow_search_impl(ccm_matcher* m, int mode, float nnratio, int check_or
     m->launches += J.n_nodes > 0 ? 3 : 2;
     MCK(cudaGetLastError());
     MCK(cudaMemcpyAsync(hbase + o_nm, dbase + o_nm, (res_a ? total : o_res) - o_nm, cudaMemcpyDeviceToHost, m->stream));
+    const double t3 = g_match_trace ? mnow_us() : 0.0;
     MCK(cudaStreamSynchronize(m->stream));
+    const double t4 = g_match_trace ? mnow_us() : 0.0;
     if (match_a) std::memcpy(match_a, hbase + o_ma, A * 4);
     if (match_b) std::memcpy(match_b, hbase + o_mb, B * 4);
     if (res_a) std::memcpy(res_a, hbase + o_res, A * sizeof(MatchResultDev));
     if (nmatches) std::memcpy(nmatches, hbase + o_nm, sizeof(int));
+    if (g_match_trace)
+        fprintf(stderr, "[ccm_match trace] bow/tri %d x %d, %zu shared nodes: order + join %.1f us, stage %.1f us, enqueue %.1f us, wait %.1f us, copy out %.1f us\n",
+                n_a, n_b, nodes.size(), t1 - t0, t2 - t1, t3 - t2, t4 - t3, mnow_us() - t4);
     return CCM_OK;
 }
 
