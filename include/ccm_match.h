@@ -50,6 +50,7 @@ typedef struct ccm_grid_params {
 } ccm_grid_params;
 
 int ccm_frame_pack_create(ccm_matcher* m, int capacity /* <= 65535 features */, ccm_frame_pack** out);
+/* May be called before or after ccm_matcher_destroy of the matcher the pack was created on (it does not touch it). */
 void ccm_frame_pack_destroy(ccm_frame_pack* p);
 /* host arrays of n features: desc [n][32], x/y = mvKeysUn[i].pt, octave, angle (degrees) */
 int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, const uint8_t* desc, const float* x,
@@ -181,6 +182,7 @@ int ccm_search_triangulation(ccm_matcher* m, int check_orientation, const ccm_ep
 typedef struct ccm_vocabulary ccm_vocabulary;
 int ccm_vocabulary_create(ccm_matcher* m, int n_nodes, const int* child_start, const int* child_ids, const uint8_t* node_desc,
                           const int* node_word, int depth_levels, ccm_vocabulary** out);
+/* May be called before or after ccm_matcher_destroy (it does not touch the matcher). */
 void ccm_vocabulary_destroy(ccm_vocabulary* v);
 /* word [n] = word id of feature i, node [n] = the node `levelsup` levels above the leaves on its path (0 = root when
  * depth_levels - levelsup <= 0, and when the path ends above that level, which upstream leaves undefined). */

@@ -34,6 +34,7 @@ struct ccm_matcher {
 
 struct ccm_frame_pack {
     ccm_matcher* m = nullptr;
+    int device = 0;       // copy of m->device: destroying a pack must not need the matcher
     int cap = 0;
     int n_host = -1;      // -1: count lives on the device only
     uint8_t* desc = nullptr; float* x = nullptr; float* y = nullptr; float* angle = nullptr; int* octave = nullptr;
@@ -163,7 +164,7 @@ int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
     *out = nullptr;
     cudaSetDevice(m->device);
     ccm_frame_pack* p = new ccm_frame_pack();
-    p->m = m; p->cap = capacity;
+    p->m = m; p->device = m->device; p->cap = capacity;
     const size_t c = (size_t)capacity;
     // one allocation, 256-B aligned sections
     auto up = [](size_t v) { return (v + 255) / 256 * 256; };
@@ -182,9 +183,8 @@ int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
 
 void ccm_frame_pack_destroy(ccm_frame_pack* p) {
     if (!p) return;
-    cudaSetDevice(p->m->device);
-    cudaStreamSynchronize(p->m->stream);
-    cudaFree(p->desc);
+    cudaSetDevice(p->device);                          // not through p->m: the matcher may have been destroyed first
+    cudaFree(p->desc);                                  // synchronises the device: no search still reads the pack
     delete p;
 }
 
@@ -743,6 +743,7 @@ int ccm_search_triangulation(ccm_matcher* m, int check_orientation, const ccm_ep
 /* ---- vocabulary transform ------------------------------------------------------------------------------------ */
 struct ccm_vocabulary {
     ccm_matcher* m = nullptr;
+    int device = 0;
     int n_nodes = 0, depth = 0;
     void* base = nullptr;
     VocabDev dev = {};
@@ -765,7 +766,7 @@ int ccm_vocabulary_create(ccm_matcher* m, int n_nodes, const int* child_start, c
     std::vector<uint8_t> cdesc((size_t)n_edges * 32);
     for (int p = 0; p < n_edges; p++) std::memcpy(&cdesc[(size_t)32 * p], node_desc + (size_t)32 * child_ids[p], 32);   // CSR order
     ccm_vocabulary* v = new ccm_vocabulary();
-    v->m = m; v->n_nodes = n_nodes; v->depth = depth_levels;
+    v->m = m; v->device = m->device; v->n_nodes = n_nodes; v->depth = depth_levels;
     cudaError_t e = cudaMalloc(&v->base, total);
     if (e != cudaSuccess) { m->err = std::string("cudaMalloc(vocabulary): ") + cudaGetErrorString(e); delete v; return CCM_E_CUDA; }
     uint8_t* b = (uint8_t*)v->base;
@@ -785,9 +786,8 @@ int ccm_vocabulary_create(ccm_matcher* m, int n_nodes, const int* child_start, c
 
 void ccm_vocabulary_destroy(ccm_vocabulary* v) {
     if (!v) return;
-    cudaSetDevice(v->m->device);
-    cudaStreamSynchronize(v->m->stream);
-    cudaFree(v->base);
+    cudaSetDevice(v->device);                          // not through v->m: the matcher may have been destroyed first
+    cudaFree(v->base);                                  // synchronises the device
     delete v;
 }
 

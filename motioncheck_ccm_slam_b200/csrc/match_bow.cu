@@ -49,13 +49,74 @@ __global__ void k_bow_init(BowJob J) {
     }
 }
 
+__device__ __forceinline__ uint4 shfl_u4(uint4 v, int src) {
+    return make_uint4(__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src), __shfl_sync(0xffffffffu, v.z, src),
+                      __shfl_sync(0xffffffffu, v.w, src));
+}
+
+// One warp per shared vocabulary node; the A-side features are taken in FeatureVector order, each against the node's B-side
+// features that no earlier A-feature has taken (:221-251 / :605-645). A feature belongs to one node, so that state is private to
+// the warp: for nodes of up to 32 B-features (every node of a real vocabulary at 1000-2000 features) lane l keeps B-feature l -
+// index, descriptor, "taken by" - in registers, the A-features are loaded 32 at a time (lane = feature) and handed round by
+// shuffle, and an A-feature costs two REDUX minima over (distance << 16 | position) instead of a chain of four dependent
+// global loads: 80 -> 8 us for 1000 x 1000 features in 95 nodes. Larger nodes take the streaming loop below.
 __global__ void __launch_bounds__(256) k_bow_search(BowJob J) {
+    const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int node = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (node >= J.n_nodes) return;
     const BowNode N = J.nodes[node];
     const uint4* __restrict__ da = reinterpret_cast<const uint4*>(J.desc_a);
     const uint4* __restrict__ db = reinterpret_cast<const uint4*>(J.desc_b);
+    const int nb = N.b1 - N.b0;
+    if (nb <= 32) {
+        int b = -1, taken_by = -1;
+        bool ok_b = false;
+        uint4 d0 = make_uint4(0, 0, 0, 0), d1 = d0;
+        if (lane < nb) {
+            b = J.order_b[N.b0 + lane];
+            ok_b = J.mode != BOW_MODE_KF_KF || J.valid_b[b];                // :619-623
+            d0 = db[2 * (size_t)b]; d1 = db[2 * (size_t)b + 1];
+        }
+        for (int ia0 = N.a0; ia0 < N.a1; ia0 += 32) {
+            int a = -1, va = 0, my_match = -1;
+            uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+            if (ia0 + lane < N.a1) {
+                a = J.order_a[ia0 + lane];
+                va = J.valid_a[a] ? 1 : 0;                                   // no good map point, :213-219 / :597-603
+                q0 = da[2 * (size_t)a]; q1 = da[2 * (size_t)a + 1];
+            }
+            MatchResultDev r; r.best_idx = -1; r.best_dist = 256; r.best_dist2 = 256; r.accepted = 0;
+            bool has_r = false;
+            const int cnt = min(32, N.a1 - ia0);
+            for (int j = 0; j < cnt; j++) {
+                if (!__shfl_sync(full, va, j)) continue;                     // warp-uniform
+                const uint4 x0 = shfl_u4(q0, j), x1 = shfl_u4(q1, j);
+                uint32_t key = 0xffffffffu;
+                if (ok_b && taken_by < 0) key = ((uint32_t)hamming256(x0, x1, d0, d1) << 16) | (uint32_t)lane;   // vpMapPointMatches[realIdxF] / vbMatched2[idx2]
+                const uint32_t k1 = __reduce_min_sync(full, key);
+                if (k1 == 0xffffffffu) continue;
+                const uint32_t k2 = __reduce_min_sync(full, key == k1 ? 0xffffffffu : key);
+                const int best_lane = (int)(k1 & 0xffffu), bestDist = (int)(k1 >> 16);
+                const int bestDist2 = k2 == 0xffffffffu ? 256 : (int)(k2 >> 16);
+                const bool under = J.mode == BOW_MODE_KF_KF ? bestDist < J.th_low : bestDist <= J.th_low;   // :641 vs :241
+                const bool acc = under && (float)bestDist < __fmul_rn(J.nnratio, (float)bestDist2);
+                const int bestIdx = __shfl_sync(full, b, best_lane), aj = __shfl_sync(full, a, j);
+                if (acc && lane == best_lane) taken_by = aj;
+                if (lane == j) {
+                    if (acc) my_match = bestIdx;
+                    r.best_idx = bestIdx; r.best_dist = bestDist; r.best_dist2 = bestDist2; r.accepted = acc;
+                    has_r = true;
+                }
+            }
+            if (a >= 0) {
+                if (my_match >= 0) J.match_a[a] = my_match;
+                if (has_r && J.res_a) J.res_a[a] = r;
+            }
+        }
+        if (taken_by >= 0) J.match_b[b] = taken_by;
+        return;
+    }
     for (int ia = N.a0; ia < N.a1; ia++) {
         const int a = J.order_a[ia];
         if (!J.valid_a[a]) continue;                                   // no good map point, :213-219 / :597-603

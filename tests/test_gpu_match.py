@@ -896,3 +896,16 @@ def test_allpairs_exchange_two_gpus(cuda_lib):
         x.close()
     for m in ms:
         m.close()
+
+
+def test_children_outlive_their_matcher(cuda_lib):
+    """Frame packs and vocabularies may be destroyed after the matcher they were created on (a Python interpreter tears objects
+    down in no particular order; a C++ host may hold packs in Frame objects that outlive the matcher singleton)."""
+    from motioncheck_ccm_slam_b200.matcher import FramePack, Matcher, Vocabulary
+    from motioncheck_ccm_slam_b200.synth import make_vocabulary_complete
+    m = Matcher(0)
+    p = FramePack(m, 100)
+    v = Vocabulary(m, make_vocabulary_complete(3, 4, 3))
+    m.close()
+    p.close()
+    v.close()
