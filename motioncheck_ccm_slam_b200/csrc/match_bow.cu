@@ -59,8 +59,11 @@ __device__ __forceinline__ uint4 shfl_u4(uint4 v, int src) {
 // the warp: for nodes of up to 32 B-features (every node of a real vocabulary at 1000-2000 features) lane l keeps B-feature l -
 // index, descriptor, "taken by" - in registers, the A-features are loaded 32 at a time (lane = feature) and handed round by
 // shuffle, and an A-feature costs two REDUX minima over (distance << 16 | position) instead of a chain of four dependent
-// global loads: 80 -> 8 us for 1000 x 1000 features in 95 nodes. Larger nodes take the streaming loop below.
+// global loads. Nodes of up to 128 B-features stage the B side in shared memory, larger ones take the streaming loop at the end.
+#define BOW_SMEM_B 128               // B-features of a node staged in shared memory (per warp: 4 KB of descriptors + 1 KB)
 __global__ void __launch_bounds__(256) k_bow_search(BowJob J) {
+    __shared__ uint4 s_bdesc[8][2 * BOW_SMEM_B];
+    __shared__ int s_bidx[8][BOW_SMEM_B], s_btaken[8][BOW_SMEM_B];
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int node = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -115,6 +118,79 @@ __global__ void __launch_bounds__(256) k_bow_search(BowJob J) {
             }
         }
         if (taken_by >= 0) J.match_b[b] = taken_by;
+        return;
+    }
+    if (nb <= BOW_SMEM_B) {
+        // up to 128 B-features: descriptors, indices and "taken by" staged in the warp's slice of shared memory, "taken" also as
+        // a bit mask in (warp-uniform) registers with the B-features that may not be matched at all (KF-KF: no map point) set
+        // from the start; an A-feature is ceil(nb / 32) shared-memory steps and two REDUX minima
+        const int warp = threadIdx.x >> 5;
+        uint4* sd = s_bdesc[warp];
+        int* sb = s_bidx[warp];
+        int* st = s_btaken[warp];
+        uint32_t taken[BOW_SMEM_B / 32];
+#pragma unroll
+        for (int c = 0; c < BOW_SMEM_B / 32; c++) {
+            const int bl = 32 * c + lane;
+            bool blocked = true;
+            if (bl < nb) {
+                const int b = J.order_b[N.b0 + bl];
+                sb[bl] = b; st[bl] = -1;
+                sd[2 * bl] = db[2 * (size_t)b]; sd[2 * bl + 1] = db[2 * (size_t)b + 1];
+                blocked = J.mode == BOW_MODE_KF_KF && !J.valid_b[b];        // :619-623
+            }
+            taken[c] = __ballot_sync(full, blocked);
+        }
+        __syncwarp();
+        for (int ia0 = N.a0; ia0 < N.a1; ia0 += 32) {
+            int a = -1, va = 0, my_match = -1;
+            uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+            if (ia0 + lane < N.a1) {
+                a = J.order_a[ia0 + lane];
+                va = J.valid_a[a] ? 1 : 0;
+                q0 = da[2 * (size_t)a]; q1 = da[2 * (size_t)a + 1];
+            }
+            MatchResultDev r; r.best_idx = -1; r.best_dist = 256; r.best_dist2 = 256; r.accepted = 0;
+            bool has_r = false;
+            const int cnt = min(32, N.a1 - ia0);
+            for (int j = 0; j < cnt; j++) {
+                if (!__shfl_sync(full, va, j)) continue;                     // warp-uniform
+                const uint4 x0 = shfl_u4(q0, j), x1 = shfl_u4(q1, j);
+                uint32_t ka = 0xffffffffu, kb = 0xffffffffu;                 // this lane's best two
+#pragma unroll
+                for (int c = 0; c < BOW_SMEM_B / 32; c++) {
+                    const int bl = 32 * c + lane;
+                    if (32 * c < nb && !((taken[c] >> lane) & 1u)) {
+                        const uint32_t key = ((uint32_t)hamming256(x0, x1, sd[2 * bl], sd[2 * bl + 1]) << 16) | (uint32_t)bl;
+                        if (key < ka) { kb = ka; ka = key; } else if (key < kb) kb = key;
+                    }
+                }
+                const uint32_t k1 = __reduce_min_sync(full, ka);
+                if (k1 == 0xffffffffu) continue;
+                const uint32_t k2 = __reduce_min_sync(full, ka == k1 ? kb : ka);
+                const int best_bl = (int)(k1 & 0xffffu), bestDist = (int)(k1 >> 16);
+                const int bestDist2 = k2 == 0xffffffffu ? 256 : (int)(k2 >> 16);
+                const bool under = J.mode == BOW_MODE_KF_KF ? bestDist < J.th_low : bestDist <= J.th_low;   // :641 vs :241
+                const bool acc = under && (float)bestDist < __fmul_rn(J.nnratio, (float)bestDist2);
+                const int bestIdx = sb[best_bl], aj = __shfl_sync(full, a, j);
+                if (acc) {
+#pragma unroll
+                    for (int c = 0; c < BOW_SMEM_B / 32; c++) if ((best_bl >> 5) == c) taken[c] |= 1u << (best_bl & 31);
+                    if (lane == 0) st[best_bl] = aj;
+                }
+                if (lane == j) {
+                    if (acc) my_match = bestIdx;
+                    r.best_idx = bestIdx; r.best_dist = bestDist; r.best_dist2 = bestDist2; r.accepted = acc;
+                    has_r = true;
+                }
+            }
+            if (a >= 0) {
+                if (my_match >= 0) J.match_a[a] = my_match;
+                if (has_r && J.res_a) J.res_a[a] = r;
+            }
+        }
+        __syncwarp();
+        for (int bl = lane; bl < nb; bl += 32) if (st[bl] >= 0) J.match_b[sb[bl]] = st[bl];
         return;
     }
     for (int ia = N.a0; ia < N.a1; ia++) {
