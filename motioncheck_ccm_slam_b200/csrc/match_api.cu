@@ -37,6 +37,7 @@ struct ccm_frame_pack {
     int device = 0;       // copy of m->device: destroying a pack must not need the matcher
     int cap = 0;
     int n_host = -1;      // -1: count lives on the device only
+    uint8_t* base = nullptr;   // the allocation (count first, see PackLayout)
     uint8_t* desc = nullptr; float* x = nullptr; float* y = nullptr; float* angle = nullptr; int* octave = nullptr;
     int* cell_start = nullptr; int* items = nullptr; int* n = nullptr;
     const uint8_t* desc_view = nullptr;   // descriptors borrowed from the extractor (zero-copy), else == desc
@@ -158,6 +159,15 @@ int ccm_descriptor_distance(ccm_matcher* m, const uint8_t* a, const uint8_t* b, 
 }
 
 /* ---- frame packs ------------------------------------------------------------------------------------------ */
+struct PackLayout {
+    size_t o_n, o_desc, o_x, o_y, o_ang, o_oct, o_cs, o_it, total;
+    explicit PackLayout(int capacity) {
+        const size_t c = (size_t)capacity;
+        auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+        o_n = 0; o_desc = 256; o_x = o_desc + up(c * 32); o_y = o_x + up(c * 4); o_ang = o_y + up(c * 4); o_oct = o_ang + up(c * 4);
+        o_cs = o_oct + up(c * 4); o_it = o_cs + up((CCM_MAX_GRID_CELLS + 1) * 4); total = o_it + up(c * 4);
+    }
+};
 int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
     if (!m || !out) return CCM_E_BADARG;
     if (capacity <= 0 || capacity > 65535) { m->err = "frame pack capacity must be 1..65535 (feature indices are 16 bits in the candidate keys)"; return CCM_E_BADARG; }
@@ -165,16 +175,16 @@ int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
     cudaSetDevice(m->device);
     ccm_frame_pack* p = new ccm_frame_pack();
     p->m = m; p->device = m->device; p->cap = capacity;
-    const size_t c = (size_t)capacity;
-    // one allocation, 256-B aligned sections
-    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
-    const size_t o_desc = 0, o_x = o_desc + up(c * 32), o_y = o_x + up(c * 4), o_ang = o_y + up(c * 4), o_oct = o_ang + up(c * 4),
-                 o_cs = o_oct + up(c * 4), o_it = o_cs + up((CCM_MAX_GRID_CELLS + 1) * 4), o_n = o_it + up(c * 4), total = o_n + 256;
+    // one allocation, 256-B aligned sections; what a host upload writes (count, descriptors, x, y, angle, octave) comes first and
+    // contiguous, so that ccm_frame_pack_upload is ONE copy from a pinned mirror of the same layout
+    const PackLayout Lo(capacity);
+    const size_t total = Lo.total;
     uint8_t* base = nullptr;
     cudaError_t e = cudaMalloc(&base, total);
     if (e != cudaSuccess) { m->err = std::string("cudaMalloc(frame pack): ") + cudaGetErrorString(e); delete p; return CCM_E_CUDA; }
-    p->desc = base + o_desc; p->x = (float*)(base + o_x); p->y = (float*)(base + o_y); p->angle = (float*)(base + o_ang);
-    p->octave = (int*)(base + o_oct); p->cell_start = (int*)(base + o_cs); p->items = (int*)(base + o_it); p->n = (int*)(base + o_n);
+    p->n = (int*)(base + Lo.o_n); p->desc = base + Lo.o_desc; p->x = (float*)(base + Lo.o_x); p->y = (float*)(base + Lo.o_y);
+    p->angle = (float*)(base + Lo.o_ang); p->octave = (int*)(base + Lo.o_oct); p->cell_start = (int*)(base + Lo.o_cs); p->items = (int*)(base + Lo.o_it);
+    p->base = base;
     p->desc_view = p->desc;
     cudaMemsetAsync(base, 0, total, m->stream);
     *out = p;
@@ -184,7 +194,7 @@ int ccm_frame_pack_create(ccm_matcher* m, int capacity, ccm_frame_pack** out) {
 void ccm_frame_pack_destroy(ccm_frame_pack* p) {
     if (!p) return;
     cudaSetDevice(p->device);                          // not through p->m: the matcher may have been destroyed first
-    cudaFree(p->desc);                                  // synchronises the device: no search still reads the pack
+    cudaFree(p->base);                                  // synchronises the device: no search still reads the pack
     delete p;
 }
 
@@ -243,16 +253,20 @@ int ccm_frame_pack_upload(ccm_frame_pack* p, const ccm_grid_params* g, int n, co
     if (rc) return rc;
     cudaSetDevice(m->device);
     p->g = *g; p->n_host = n; p->desc_view = p->desc;
-    if (n > 0) {
-        MCK(cudaMemcpyAsync(p->desc, desc, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(p->x, x, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(p->y, y, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(p->octave, octave, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
-        MCK(cudaMemcpyAsync(p->angle, angle, (size_t)n * 4, cudaMemcpyHostToDevice, m->stream));
+    {   // count | descriptors | x | y | angle | octave gathered in the pinned mirror at the pack's own offsets: one copy
+        const PackLayout Lo(p->cap);
+        const size_t bytes = n > 0 ? Lo.o_oct + (size_t)n * 4 : sizeof(int);
+        uint8_t* hb;
+        if ((rc = stage_host(m, bytes, &hb))) return rc;
+        std::memcpy(hb + Lo.o_n, &n, sizeof(int));
+        if (n > 0) {
+            std::memcpy(hb + Lo.o_desc, desc, (size_t)n * 32); std::memcpy(hb + Lo.o_x, x, (size_t)n * 4); std::memcpy(hb + Lo.o_y, y, (size_t)n * 4);
+            std::memcpy(hb + Lo.o_ang, angle, (size_t)n * 4); std::memcpy(hb + Lo.o_oct, octave, (size_t)n * 4);
+        }
+        MCK(cudaMemcpyAsync(p->base, hb, bytes, cudaMemcpyHostToDevice, m->stream));
     }
-    MCK(cudaMemcpyAsync(p->n, &p->n_host, sizeof(int), cudaMemcpyHostToDevice, m->stream));
     { int rc2 = launch_build_grid(m, &p, 1); if (rc2) return rc2; }
-    MCK(cudaStreamSynchronize(m->stream));    // host arrays (and &p->n_host) may be reused by the caller
+    MCK(cudaStreamSynchronize(m->stream));    // the pinned mirror may be reused by the next call
     return CCM_OK;
 }
 
@@ -807,16 +821,20 @@ int ccm_vocabulary_transform(ccm_matcher* m, const ccm_vocabulary* v, int n, con
     if (!m || !v || v->m != m || n < 0 || levelsup < 0 || (n > 0 && (!desc || !word || !node))) return CCM_E_BADARG;
     if (n == 0) return CCM_OK;
     cudaSetDevice(m->device);
-    uint8_t* dd; int *dw, *dn;
+    // device blob [descriptors | word | node] with a pinned mirror: one copy up, one copy back
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_w = up((size_t)n * 32), o_n = o_w + up((size_t)n * 4), total = o_n + (size_t)n * 4;
+    uint8_t *dbase, *hbase;
     int rc;
-    if ((rc = mbuf(m, MB_A, (size_t)n * 32, &dd))) return rc;
-    if ((rc = mbuf(m, MB_B, (size_t)n, &dw))) return rc;
-    if ((rc = mbuf(m, MB_C, (size_t)n, &dn))) return rc;
-    MCK(cudaMemcpyAsync(dd, desc, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
-    if ((rc = ccm_vocabulary_transform_device(m, v, n, dd, levelsup, dw, dn))) return rc;
-    MCK(cudaMemcpyAsync(word, dw, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
-    MCK(cudaMemcpyAsync(node, dn, (size_t)n * 4, cudaMemcpyDeviceToHost, m->stream));
+    if ((rc = mbuf(m, MB_A, total, &dbase))) return rc;
+    if ((rc = stage_host(m, total, &hbase))) return rc;
+    std::memcpy(hbase, desc, (size_t)n * 32);
+    MCK(cudaMemcpyAsync(dbase, hbase, (size_t)n * 32, cudaMemcpyHostToDevice, m->stream));
+    if ((rc = ccm_vocabulary_transform_device(m, v, n, dbase, levelsup, (int*)(dbase + o_w), (int*)(dbase + o_n)))) return rc;
+    MCK(cudaMemcpyAsync(hbase + o_w, dbase + o_w, total - o_w, cudaMemcpyDeviceToHost, m->stream));
     MCK(cudaStreamSynchronize(m->stream));
+    std::memcpy(word, hbase + o_w, (size_t)n * 4);
+    std::memcpy(node, hbase + o_n, (size_t)n * 4);
     return CCM_OK;
 }
 
