@@ -576,6 +576,7 @@ int ccm_search_window(ccm_matcher* m, ccm_frame_pack* targets, const ccm_window_
     if ((rc = mbuf(m, MB_Q, total, &dbase))) return rc;
     if ((rc = stage_host(m, total, &hbase))) return rc;
     const bool holder_in = holder && prm->mode != CCM_WIN_BEST && prm->mode != CCM_WIN_INIT;
+    const double t0 = g_match_trace ? mnow_us() : 0.0;
     std::memcpy(hbase + o_q, q, sizeof(WindowQueryDev) * (size_t)nq);
     std::memcpy(hbase + o_qd, q_desc, (size_t)nq * 32);
     if (holder_in && n_t > 0) std::memcpy(hbase + o_h, holder, sizeof(int) * (size_t)n_t);
@@ -587,7 +588,9 @@ int ccm_search_window(ccm_matcher* m, ccm_frame_pack* targets, const ccm_window_
     const bool holder_out = holder && prm->mode != CCM_WIN_BEST && n_t > 0;
     const size_t d0 = holder_out ? o_h : o_nm, d1 = res ? o_res + sizeof(MatchResultDev) * (size_t)nq : o_nm + sizeof(int);
     MCK(cudaMemcpyAsync(hbase + d0, dbase + d0, d1 - d0, cudaMemcpyDeviceToHost, m->stream));
+    const double t1 = g_match_trace ? mnow_us() : 0.0;
     MCK(cudaStreamSynchronize(m->stream));
+    if (g_match_trace) fprintf(stderr, "[ccm_match trace] window mode %d, %d queries: stage + enqueue %.1f us, wait %.1f us\n", prm->mode, nq, t1 - t0, mnow_us() - t1);
     if (nmatches) std::memcpy(nmatches, hbase + o_nm, sizeof(int));
     if (res) std::memcpy(res, hbase + o_res, sizeof(MatchResultDev) * (size_t)nq);
     if (holder_out) std::memcpy(holder, hbase + o_h, sizeof(int) * (size_t)n_t);
