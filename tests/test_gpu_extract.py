@@ -413,3 +413,23 @@ def test_opencv2_blur_switch(cuda_lib, monkeypatch):
     finally:
         L.ocv_set_blur_variant(0)
     ex.close()
+
+
+@pytest.mark.gpu
+def test_one_handle_changing_shapes_and_entry_points(cuda_lib):
+    """One handle fed images of different sizes and through different entry points in turn: the single-frame CUDA graph is
+    rebuilt when the shape (arena) changes, and a batch call in between leaves it valid."""
+    ex = make(cuda_lib, 500, 1.2, 6, 20, 7, max_width=752, max_height=480, max_batch=4)
+    orc = OracleExtractor(500, 1.2, 6, 20, 7)
+    shapes = [(752, 480), (640, 400), (752, 480), (401, 303), (640, 400)]
+    for k, (w, h) in enumerate(shapes):
+        img = make_frame(50 + k, w, h)
+        ko, do = orc(img)
+        kp, desc = ex(img)                                   # graph path
+        assert_same(kp, desc, ko, do, ("single", w, h, k))
+        kps, descs = ex.extract_batch([img, img])            # batch path on the same handle and shape
+        for f in range(2):
+            assert_same(kps[f], descs[f], ko, do, ("batch", w, h, k, f))
+        kp2, desc2 = ex(img)                                 # and the graph again
+        assert np.array_equal(kp2, kp) and np.array_equal(desc2, desc)
+    ex.close()
