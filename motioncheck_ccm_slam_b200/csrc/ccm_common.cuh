@@ -70,3 +70,16 @@ __device__ __forceinline__ int ccm_reflect101(int p, int len) {
 // normal launch. Everything a kernel reads before pdl_wait() must be data no earlier kernel of the chain writes (host tables).
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Debug build only (-DCCM_DEBUG_TS): the first thread of a kernel's first CTA notes globaltimer when it is past its dependency
+// wait and the last thread to leave... is not known, so only starts are kept; slot = kind * 16 + level.
+#ifdef CCM_DEBUG_TS
+__device__ unsigned long long g_dbg_ts[128];
+__device__ __forceinline__ void dbg_ts(int slot) {
+    unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_dbg_ts[slot] = t;
+}
+#define CCM_TS(cond, slot) do { if (cond) dbg_ts(slot); } while (0)
+#else
+#define CCM_TS(cond, slot) do { } while (0)
+#endif

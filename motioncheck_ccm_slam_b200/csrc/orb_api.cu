@@ -1040,3 +1040,9 @@ int ccm_orb_debug_level_corners(ccm_orb* h, int frame, int level, int* xys, int 
 }
 
 }  // extern "C"
+
+#ifdef CCM_DEBUG_TS
+extern "C" int ccm_debug_ts(unsigned long long* out) {            // debug builds only: kernel start stamps, see ccm_common.cuh
+    return cudaMemcpyFromSymbol(out, g_dbg_ts, sizeof(unsigned long long) * 128) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -125,6 +125,7 @@ __global__ void __launch_bounds__(256, 5) k_blur_levels(const __grid_constant__ 
     const bool out_lane = !BLUR_OVERLAP || (lane >= 1 && lane <= 30);
     const int wy0 = tyi * BLUR_TH + warp * BLUR_RPW;
     const int w = L.w, h = L.h;
+    CCM_TS(blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0, 65);
     if (wy0 >= h) return;                                    // warp-uniform
     const uint8_t* __restrict__ img = L.img + (size_t)f * L.img_stride;
     const int pitch = L.img_pitch;
@@ -289,6 +290,7 @@ __global__ void __launch_bounds__(256) k_orient_describe(const __grid_constant__
     // A CTA's 8 slots belong to one level (host grid: desc_block_base), so the level, its image bases and pitches are
     // CTA-uniform: they live in uniform registers and every pixel load below is [uniform base + 32-bit offset].
     const int lvl = __ldg(block_level + blockIdx.x);          // host table (configure_shape): level of every CTA of the grid
+    CCM_TS(blockIdx.x == 0 && blockIdx.y == 0 && tid == 0, 64);
     const LevelDesc& L = T.l[lvl];
     __syncthreads();
     // keypoints of the lower levels come first in the output (:1239-1276): lane l holds level l's count

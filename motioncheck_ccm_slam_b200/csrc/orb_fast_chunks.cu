@@ -306,6 +306,7 @@ __global__ void __launch_bounds__(32 * FC_WARPS) k_fast_chunks(const __grid_cons
     C.list_s = smem_addr(C.list);
     pdl_launch();
     pdl_wait();                                 // the pyramid (previous kernels of the chain) is complete
+    CCM_TS(blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0, 16 + C.lvl);
     const LevelDesc& L = T.l[C.lvl];
 
     // (A) tile rows 0 .. ch+5 = image rows y0-3 .. y0+ch+2, columns gxa .. gxa+143

@@ -116,6 +116,7 @@ __global__ void __launch_bounds__(256, RESIZE_MLP_CTAS) k_resize_level_mlp(const
     const uint8_t* src = S.img + (size_t)f * S.img_stride + base;
     uint8_t* dst = D.img + (size_t)f * D.img_stride + (size_t)y0 * D.img_pitch + x4;
     pdl_wait();                                               // level lvl-1 is complete
+    CCM_TS(blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0 && threadIdx.y == 0, lvl);
     uint32_t u[RESIZE_SRC_ROWS][3];
 #pragma unroll
     for (int k = 0; k < RESIZE_SRC_ROWS; k++) {

@@ -113,6 +113,7 @@ __global__ void __launch_bounds__(512, 4) k_quadtree(const __grid_constant__ Lev
     const int tid = threadIdx.x, NT = blockDim.x;
     pdl_launch();
     pdl_wait();                              // the corner lists of k_fast_chunks are complete
+    CCM_TS(blockIdx.y == 0 && threadIdx.x == 0, 32 + lvl);
 
     QNode* A = reinterpret_cast<QNode*>(smem_raw);
     QNode* B = A + cap;
@@ -280,4 +281,5 @@ __global__ void __launch_bounds__(512, 4) k_quadtree(const __grid_constant__ Lev
         out[i] = (uint32_t)(v & 0xFFFFFFu) | ((uint32_t)(v >> 56) << 24);
     }
     if (tid == 0) level_kp_count[f * CCM_MAX_LEVELS + lvl] = n;
+    CCM_TS(blockIdx.y == 0 && threadIdx.x == 0, 48 + lvl);
 }
